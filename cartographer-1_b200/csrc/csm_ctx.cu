@@ -1,0 +1,119 @@
+// Context, error reporting and scratch-memory helpers of libcsm_b200.so.
+#include <cstdarg>
+#include <cstring>
+
+#include "csm_internal.cuh"
+
+namespace csm {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+int DevBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return CSM_OK;
+  if (p) {
+    CSM_CUDA(cudaFree(p));
+    p = nullptr;
+    cap = 0;
+  }
+  size_t want = bytes + bytes / 4 + 256;
+  CSM_CUDA(cudaMalloc(&p, want));
+  cap = want;
+  return CSM_OK;
+}
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+}
+int PinBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return CSM_OK;
+  if (p) {
+    CSM_CUDA(cudaFreeHost(p));
+    p = nullptr;
+    cap = 0;
+  }
+  size_t want = bytes + bytes / 4 + 256;
+  CSM_CUDA(cudaHostAlloc(&p, want, cudaHostAllocDefault));
+  cap = want;
+  return CSM_OK;
+}
+void PinBuf::release() {
+  if (p) cudaFreeHost(p);
+  p = nullptr;
+  cap = 0;
+}
+
+}  // namespace csm
+
+extern "C" {
+
+const char* csm_last_error(void) { return csm::g_error; }
+
+int csm_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int csm_ctx_create(int device, csm_ctx** out) {
+  CSM_REQUIRE(out != nullptr, "out must not be NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    csm::set_error("no CUDA device available (%s); this library has no CPU fallback",
+                   e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return CSM_ERR_CUDA;
+  }
+  CSM_REQUIRE(device >= 0 && device < n, "device index out of range");
+  CSM_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CSM_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    csm::set_error("device %d is sm_%d%d; this library is built for sm_100a only", device,
+                   prop.major, prop.minor);
+    return CSM_ERR_CUDA;
+  }
+  csm_ctx* c = new csm_ctx;
+  c->device = device;
+  c->num_sms = prop.multiProcessorCount;
+  CSM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CSM_CUDA(cudaEventCreate(&c->ev0));
+  CSM_CUDA(cudaEventCreate(&c->ev1));
+  *out = c;
+  return CSM_OK;
+}
+
+void csm_ctx_destroy(csm_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  c->tmp0.release();
+  c->tmp1.release();
+  c->tmp2.release();
+  c->pin0.release();
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int csm_ctx_synchronize(csm_ctx* c) {
+  CSM_REQUIRE(c != nullptr, "ctx must not be NULL");
+  CSM_CUDA(cudaSetDevice(c->device));
+  CSM_CUDA(cudaStreamSynchronize(c->stream));
+  return CSM_OK;
+}
+
+}  // extern "C"

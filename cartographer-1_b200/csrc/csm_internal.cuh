@@ -1,0 +1,80 @@
+// Internal declarations shared by the CUDA translation units of libcsm_b200.so.
+// Not part of the ABI (include/csm_b200.h is).
+#ifndef CSM_INTERNAL_CUH_
+#define CSM_INTERNAL_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "csm_b200.h"
+
+namespace csm {
+
+void set_error(const char* fmt, ...);
+
+#define CSM_CUDA(call)                                                                 \
+  do {                                                                                 \
+    cudaError_t _e = (call);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      csm::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, \
+                     __LINE__);                                                        \
+      return CSM_ERR_CUDA;                                                             \
+    }                                                                                  \
+  } while (0)
+
+#define CSM_REQUIRE(cond, msg)                                        \
+  do {                                                                \
+    if (!(cond)) {                                                    \
+      csm::set_error("invalid argument: %s (%s)", msg, #cond);        \
+      return CSM_ERR_ARG;                                             \
+    }                                                                 \
+  } while (0)
+
+// Grow-only device / pinned-host scratch buffer owned by a context.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);  // keeps contents only if no regrowth is needed
+  void release();
+  template <typename T>
+  T* as() const {
+    return static_cast<T*>(p);
+  }
+};
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);
+  void release();
+  template <typename T>
+  T* as() const {
+    return static_cast<T*>(p);
+  }
+};
+
+}  // namespace csm
+
+struct csm_ctx {
+  int device = 0;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // scratch for csm_discretize2d / stack builds
+  csm::DevBuf tmp0, tmp1, tmp2;
+  csm::PinBuf pin0;
+};
+
+struct csm_stack2d {
+  int device = 0;
+  int num_x = 0, num_y = 0, depth = 0;
+  uint8_t* base = nullptr;                // one allocation for all levels
+  size_t level_off[CSM_MAX_DEPTH] = {0};  // byte offset of level i inside base
+  size_t bytes = 0;
+  uint8_t* q_lut_dev = nullptr;  // 65536 bytes
+};
+
+#endif  // CSM_INTERNAL_CUH_

@@ -1,0 +1,175 @@
+/* csm_b200.h -- C ABI of the B200-native correlative scan matcher.
+ *
+ * This is the drop-in boundary: everything the reference's scan-matching classes
+ * compute on the CPU between "grid + point cloud in" and "best candidate out" is
+ * behind these entry points, implemented as hand-written sm_100a CUDA kernels.
+ * There is no CPU fallback: every entry point fails with CSM_ERR_CUDA when no
+ * usable device exists.
+ *
+ * The reference (juwangvsu/cartographer-1) has no FFI layer; the interface each
+ * entry point replaces is a C++ member function.  Citations are relative to
+ * cartographer/mapping/internal/2d/scan_matching/ unless a path is given:
+ *   FCSM2D = fast_correlative_scan_matcher_2d.{h,cc}
+ *   CSM2D  = correlative_scan_matcher_2d.{h,cc}
+ *   RT2D   = real_time_correlative_scan_matcher_2d.{h,cc}
+ *
+ * What stays on the host side of the boundary (libm-dependent, O(num_scans)):
+ * SearchParameters construction (CSM2D.cc:27-55: sqrtf/acos/ceil), the per-scan
+ * half-angle (cosf, sinf) table for GenerateRotatedScans (CSM2D.cc:99-106), the
+ * uint16 -> uint8 quantisation table of PrecomputationGrid2D::ComputeCellValue
+ * (FCSM2D.cc:163-169) and the candidate -> pose conversion (CSM2D.h:81-87,
+ * FCSM2D.cc:253-260).  cartographer-1_b200/host/ holds that host code behind the
+ * reference's own class signatures.
+ *
+ * All pointers are plain host pointers unless the name says "_dev".  All functions
+ * return 0 on success and a negative csm_status otherwise; csm_last_error() gives a
+ * thread-local message.  "No match above min_score" is a normal result
+ * (found == 0), not an error (FCSM2D.cc:253-261).
+ *
+ * Thread safety: a csm_ctx owns one CUDA stream and its scratch memory and must be
+ * used by one host thread at a time; create one ctx per worker thread.  Stacks are
+ * immutable after construction and may be shared by any number of contexts on the
+ * same device, matching FastCorrelativeScanMatcher2D::Match being const and called
+ * concurrently (constraints/constraint_builder_2d.cc:102-111).
+ */
+#ifndef CSM_B200_H_
+#define CSM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSM_MAX_DEPTH 16
+
+typedef enum {
+  CSM_OK = 0,
+  CSM_ERR_ARG = -1,      /* invalid argument (the reference would CHECK-fail) */
+  CSM_ERR_CUDA = -2,     /* CUDA runtime error or no device */
+  CSM_ERR_CAPACITY = -3  /* an internal work list overflowed even after regrowth */
+} csm_status;
+
+typedef struct csm_ctx csm_ctx;
+typedef struct csm_stack2d csm_stack2d;
+typedef struct csm_batch2d csm_batch2d;
+
+const char* csm_last_error(void);
+int csm_device_count(void);
+
+/* One context = one device + one stream + scratch arenas. */
+int csm_ctx_create(int device, csm_ctx** out);
+void csm_ctx_destroy(csm_ctx* ctx);
+int csm_ctx_synchronize(csm_ctx* ctx);
+
+/* ---- PrecomputationGridStack2D (FCSM2D.cc:91-186, FCSM2D.h:49-109) ----------
+ * cells:  the Grid2D correspondence-cost cells, row-major, flat = num_x*y + x
+ *         (cartographer/mapping/2d/grid_2d.h:113-116).
+ * q_lut:  65536 bytes, q_lut[v] = ComputeCellValue(1.f - |table[v]|) with `table`
+ *         the grid's value-to-correspondence-cost table
+ *         (cartographer/mapping/value_conversion_tables.cc:29-67); computed by the
+ *         host with the reference's fp32 ops so the device work is integer-exact.
+ * depth:  branch_and_bound_depth (>= 1); level i has width 1 << i.
+ * Level i holds (num_x + 2^i - 1) x (num_y + 2^i - 1) bytes, byte-identical to
+ * PrecomputationGrid2D::cells_ of the reference.
+ */
+int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
+                      const uint8_t* q_lut, int depth, csm_stack2d** out);
+/* Same, with `cells_dev` already resident in device memory (benchmark path). */
+int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, int num_y,
+                          const uint8_t* q_lut, int depth, csm_stack2d** out);
+/* Rebuilds an existing stack in place from device-resident cells; asynchronous on
+ * the context's stream (used to time the build kernels alone). */
+int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* cells_dev);
+/* Copies level `level` to `out` (may be NULL to query the size only). */
+int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* stack, int level, uint8_t* out,
+                      int* wide_x, int* wide_y);
+int csm_stack2d_depth(const csm_stack2d* stack);
+size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
+void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* stack);
+
+/* ---- FastCorrelativeScanMatcher2D::MatchWithSearchParameters (FCSM2D.cc:227-262)
+ * One job = one (node, submap) search.  The host supplies the search parameters it
+ * computed with libm; the device does GenerateRotatedScans, DiscretizeScans,
+ * ShrinkToFit, ComputeLowestResolutionCandidates and BranchAndBound.
+ */
+typedef struct {
+  const csm_stack2d* stack;   /* precomputation stack of the submap               */
+  const float* points_xyz;    /* num_points x 3 fp32, sensor frame                */
+  int32_t num_points;
+  int32_t num_scans;          /* SearchParameters::num_scans (CSM2D.cc:45)         */
+  const float* scan_quat;     /* num_scans x 2: (cosf(a/2), sinf(a/2)) of the     */
+                              /* fp32-narrowed delta_theta of each scan            */
+  float init_quat_w;          /* cosf/sinf of half the fp32-narrowed initial yaw   */
+  float init_quat_s;          /* (FCSM2D.cc:235-239)                               */
+  float init_tx, init_ty;     /* initial translation narrowed to fp32 (:244-245)   */
+  double max_x, max_y;        /* MapLimits::max()                                  */
+  double resolution;          /* MapLimits::resolution()                           */
+  int32_t linear_bound;       /* initial +-bound in cells (CSM2D.cc:48-54)         */
+  float min_score;            /* strict threshold (FCSM2D.cc:253)                  */
+  float score_offset;         /* PrecomputationGrid2D::min_score_ (FCSM2D.cc:97)   */
+  float score_scale;          /* (max_score_ - min_score_) / 255.f (FCSM2D.h:74-76)*/
+} csm_job2d;
+
+typedef struct {
+  int32_t found;              /* best.score > min_score                            */
+  int32_t scan_index;         /* Candidate2D::scan_index of the winner             */
+  int32_t x_index_offset;     /* Candidate2D::x_index_offset                       */
+  int32_t y_index_offset;     /* Candidate2D::y_index_offset                       */
+  float score;                /* Candidate2D::score (bit-identical fp32)           */
+  int32_t tie_resolution;     /* 0: unique on device, 1: host replay of std::sort  */
+  uint64_t candidates_scored; /* candidate scores evaluated for this job           */
+} csm_result2d;
+
+/* Synchronous convenience: upload + run + fetch. */
+int csm_match2d_batch(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_result2d* results);
+
+/* Split form, so a caller can keep inputs resident and overlap work:
+ *   upload : host -> device copy of points / tables (asynchronous)
+ *   run    : all kernels, asynchronous on the context's stream
+ *   fetch  : device -> host copy of results, waits, resolves rare top-level ties
+ *            with the reference's own std::sort order on the host
+ */
+int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_batch2d** out);
+int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* batch);
+int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* batch, csm_result2d* results);
+void csm_batch2d_destroy(csm_ctx* ctx, csm_batch2d* batch);
+
+/* ---- DiscretizeScans + ShrinkToFit alone (CSM2D.cc:73-127), for the bit-exact
+ * cell-index parity test.  out_xy: num_scans*num_points*2 int32 (x, y);
+ * out_bounds: num_scans*4 int32 (min_x, max_x, min_y, max_y).
+ */
+int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, int shrink,
+                     int32_t* out_xy, int32_t* out_bounds);
+
+/* ---- RealTimeCorrelativeScanMatcher2D::Match (RT2D.cc:117-176) -----------------
+ * Exhaustive search directly on the live uint16 grid (no precomputation).
+ * cost_table: the grid's 65536-entry value-to-correspondence-cost table.
+ * penalty:    num_scans x (2*linear_bound+1)^2 doubles, the host-computed
+ *             exp(-(hypot(x,y)*w_t + |theta|*w_r)^2) factor per candidate in
+ *             generation order scan -> x -> y (RT2D.cc:170-174).
+ */
+typedef struct {
+  const uint16_t* cells;      /* live grid cells, host                             */
+  int32_t num_x, num_y;
+  const float* cost_table;    /* 65536 floats                                      */
+  const float* points_xyz;
+  int32_t num_points;
+  int32_t num_scans;
+  const float* scan_quat;
+  float init_quat_w, init_quat_s;
+  float init_tx, init_ty;
+  double max_x, max_y, resolution;
+  int32_t linear_bound;
+  const double* penalty;
+} csm_rt_job2d;
+
+int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
+                         csm_result2d* results);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* CSM_B200_H_ */

@@ -1,0 +1,261 @@
+// TEST INFRASTRUCTURE ONLY (see csm_oracle.h).  Flat C entry points over the oracle
+// for ctypes: used by tests/ as the checker and by bench.py as the timed CPU
+// baseline.  Never linked into the product library.
+#include <chrono>
+#include <cstring>
+
+#include "cpu_pool.h"
+#include "csm_oracle.h"
+
+using namespace oracle;
+
+extern "C" {
+
+struct oracle_result2d {
+  int32_t found;
+  int32_t scan_index, x_index_offset, y_index_offset;
+  float score;
+  int32_t num_scans;
+  double pose_x, pose_y, pose_theta;
+  uint64_t scored_top, scored_lower;
+};
+
+static PointCloud ToCloud(const float* xyz, int n) {
+  PointCloud c(n);
+  for (int i = 0; i < n; ++i) c[i] = Vec3f{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]};
+  return c;
+}
+static MapLimits MakeLimits(double res, double max_x, double max_y, int nx, int ny) {
+  MapLimits l;
+  l.resolution = res;
+  l.max_x = max_x;
+  l.max_y = max_y;
+  l.cell_limits.num_x_cells = nx;
+  l.cell_limits.num_y_cells = ny;
+  return l;
+}
+
+// --- tables -----------------------------------------------------------------
+void oracle_correspondence_cost_table(float* out65536) {
+  std::memcpy(out65536, ValueToCorrespondenceCostTable().data(), 65536 * sizeof(float));
+}
+uint16_t oracle_probability_to_cost_value(float probability) {
+  return CorrespondenceCostToValue(1.f - probability);
+}
+
+// --- grid / matcher handles ---------------------------------------------------
+void* oracle_grid2d_create(const uint16_t* cells, int nx, int ny, double res, double max_x,
+                           double max_y) {
+  return new ProbabilityGrid(MakeLimits(res, max_x, max_y, nx, ny), cells);
+}
+void oracle_grid2d_destroy(void* g) { delete static_cast<ProbabilityGrid*>(g); }
+
+void* oracle_fcsm2d_create(void* grid, double linear_window, double angular_window, int depth) {
+  FastCorrelativeScanMatcherOptions2D o;
+  o.linear_search_window = linear_window;
+  o.angular_search_window = angular_window;
+  o.branch_and_bound_depth = depth;
+  return new FastCorrelativeScanMatcher2D(*static_cast<ProbabilityGrid*>(grid), o);
+}
+void oracle_fcsm2d_destroy(void* m) { delete static_cast<FastCorrelativeScanMatcher2D*>(m); }
+
+// Copies precomputation level `level` (wide_x * wide_y bytes) if out != NULL.
+int oracle_fcsm2d_level(void* m, int level, uint8_t* out, int* wide_x, int* wide_y) {
+  const auto* fm = static_cast<FastCorrelativeScanMatcher2D*>(m);
+  if (level < 0 || level > fm->stack().max_depth()) return -1;
+  const PrecomputationGrid2D& pg = fm->stack().Get(level);
+  *wide_x = pg.wide_x();
+  *wide_y = pg.wide_y();
+  if (out) std::memcpy(out, pg.cells().data(), pg.cells().size());
+  return 0;
+}
+
+static void Fill(oracle_result2d* out, bool ok, const FastCorrelativeScanMatcher2D::Winner& w,
+                 float score, const Rigid2d& pose, const MatchStats& st) {
+  out->found = ok ? 1 : 0;
+  out->scan_index = w.scan_index;
+  out->x_index_offset = w.x_index_offset;
+  out->y_index_offset = w.y_index_offset;
+  out->score = ok ? score : w.score;
+  out->num_scans = static_cast<int32_t>(st.num_scans);
+  out->pose_x = pose.tx;
+  out->pose_y = pose.ty;
+  out->pose_theta = pose.angle;
+  out->scored_top = st.scored_top;
+  out->scored_lower = st.scored_lower;
+}
+
+int oracle_fcsm2d_match(void* m, int full_submap, double init_x, double init_y, double init_theta,
+                        const float* xyz, int n, float min_score, oracle_result2d* out) {
+  const auto* fm = static_cast<FastCorrelativeScanMatcher2D*>(m);
+  const PointCloud cloud = ToCloud(xyz, n);
+  float score = 0.f;
+  Rigid2d pose;
+  FastCorrelativeScanMatcher2D::Winner w;
+  MatchStats st;
+  bool ok;
+  if (full_submap) {
+    ok = fm->MatchFullSubmap(cloud, min_score, &score, &pose, &w, &st);
+  } else {
+    Rigid2d init;
+    init.tx = init_x;
+    init.ty = init_y;
+    init.angle = init_theta;
+    ok = fm->Match(init, cloud, min_score, &score, &pose, &w, &st);
+  }
+  Fill(out, ok, w, score, pose, st);
+  return 0;
+}
+
+// --- search parameters + discretisation (for the bit-exact index test) --------
+int oracle_search_parameters2d(double linear_window, double angular_window, const float* xyz, int n,
+                               double res, int* num_angular_perturbations, double* step,
+                               int* num_scans, int* num_linear_perturbations) {
+  const SearchParameters sp(linear_window, angular_window, ToCloud(xyz, n), res);
+  *num_angular_perturbations = sp.num_angular_perturbations;
+  *step = sp.angular_perturbation_step_size;
+  *num_scans = sp.num_scans;
+  *num_linear_perturbations = sp.linear_bounds.empty() ? 0 : sp.linear_bounds[0].max_x;
+  return 0;
+}
+
+// Rotates by init_theta, generates the rotated scans, discretises them and shrinks
+// the bounds exactly like MatchWithSearchParameters does
+// (fast_correlative_scan_matcher_2d.cc:234-246).  out_xy: S*n*2 int32 (x, y);
+// out_bounds: S*4 int32 (min_x, max_x, min_y, max_y).
+int oracle_discretize2d(double res, double max_x, double max_y, int nx, int ny, const float* xyz,
+                        int n, double init_x, double init_y, double init_theta,
+                        int num_linear_perturbations, int num_angular_perturbations, double step,
+                        int shrink, int32_t* out_xy, int32_t* out_bounds) {
+  const MapLimits limits = MakeLimits(res, max_x, max_y, nx, ny);
+  SearchParameters sp(num_linear_perturbations, num_angular_perturbations, step, res);
+  const PointCloud rotated = RotatePointCloudYaw(ToCloud(xyz, n), static_cast<float>(init_theta));
+  const std::vector<PointCloud> scans = GenerateRotatedScans(rotated, sp);
+  const std::vector<DiscreteScan2D> d =
+      DiscretizeScans(limits, scans, static_cast<float>(init_x), static_cast<float>(init_y));
+  if (shrink) sp.ShrinkToFit(d, limits.cell_limits);
+  for (int s = 0; s < sp.num_scans; ++s) {
+    for (int i = 0; i < n; ++i) {
+      out_xy[(static_cast<size_t>(s) * n + i) * 2 + 0] = d[s][i].x;
+      out_xy[(static_cast<size_t>(s) * n + i) * 2 + 1] = d[s][i].y;
+    }
+    out_bounds[4 * s + 0] = sp.linear_bounds[s].min_x;
+    out_bounds[4 * s + 1] = sp.linear_bounds[s].max_x;
+    out_bounds[4 * s + 2] = sp.linear_bounds[s].min_y;
+    out_bounds[4 * s + 3] = sp.linear_bounds[s].max_y;
+  }
+  return 0;
+}
+
+// --- real-time matcher ---------------------------------------------------------
+double oracle_rt_match2d(void* grid, double linear_window, double angular_window,
+                         double translation_delta_cost_weight, double rotation_delta_cost_weight,
+                         double init_x, double init_y, double init_theta, const float* xyz, int n,
+                         oracle_result2d* out) {
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.linear_search_window = linear_window;
+  o.angular_search_window = angular_window;
+  o.translation_delta_cost_weight = translation_delta_cost_weight;
+  o.rotation_delta_cost_weight = rotation_delta_cost_weight;
+  const RealTimeCorrelativeScanMatcher2D matcher(o);
+  Rigid2d init, pose;
+  init.tx = init_x;
+  init.ty = init_y;
+  init.angle = init_theta;
+  FastCorrelativeScanMatcher2D::Winner w;
+  const double score =
+      matcher.Match(init, ToCloud(xyz, n), *static_cast<ProbabilityGrid*>(grid), &pose, &w);
+  MatchStats st;
+  Fill(out, true, w, static_cast<float>(score), pose, st);
+  return score;
+}
+
+// --- thread-pooled constraint builder (timed CPU baseline) ---------------------
+// grids[num_submaps], submap_pose[num_submaps*3]; searches: submap index, node id,
+// full flag, relative pose [3], cloud given by offsets into xyz (offsets has
+// num_searches+1 entries, in points).  One NotifyEndOfNode per search (the caller
+// models one node per search).  Results in submission order; found==0 rows are the
+// reference's null constraint slots.  Returns wall seconds from the first
+// MaybeAdd* call until the WhenDone callback has run (matcher construction
+// included, exactly as in the reference where it is one more pool task).
+double oracle_constraint_batch(int num_threads, void* const* grids, const double* submap_pose,
+                               int num_submaps, int num_searches, const int32_t* search_submap,
+                               const int32_t* search_full, const double* search_rel_pose,
+                               const float* xyz, const int64_t* offsets, double sampling_ratio,
+                               double max_constraint_distance, double min_score,
+                               double global_min_score, double linear_window, double angular_window,
+                               int depth, oracle_result2d* out, double* out_stats4) {
+  ConstraintBuilderOptions o;
+  o.sampling_ratio = sampling_ratio;
+  o.max_constraint_distance = max_constraint_distance;
+  o.min_score = min_score;
+  o.global_localization_min_score = global_min_score;
+  o.fast_correlative_scan_matcher_options.linear_search_window = linear_window;
+  o.fast_correlative_scan_matcher_options.angular_search_window = angular_window;
+  o.fast_correlative_scan_matcher_options.branch_and_bound_depth = depth;
+  std::vector<ConstraintBuilder2D::Submap> submaps(num_submaps);
+  for (int i = 0; i < num_submaps; ++i) {
+    submaps[i].grid = static_cast<const ProbabilityGrid*>(grids[i]);
+    submaps[i].local_pose.tx = submap_pose[3 * i];
+    submaps[i].local_pose.ty = submap_pose[3 * i + 1];
+    submaps[i].local_pose.angle = submap_pose[3 * i + 2];
+  }
+  std::vector<PointCloud> clouds(num_searches);
+  for (int i = 0; i < num_searches; ++i)
+    clouds[i] = ToCloud(xyz + 3 * offsets[i], static_cast<int>(offsets[i + 1] - offsets[i]));
+  for (int i = 0; i < num_searches; ++i) out[i] = oracle_result2d{};
+
+  ThreadPool pool(num_threads);
+  ConstraintBuilder2D builder(o, &pool);
+  std::mutex m;
+  std::condition_variable cv;
+  bool done = false;
+  std::vector<OracleConstraint> result;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (int i = 0; i < num_searches; ++i) {
+    const int s = search_submap[i];
+    if (search_full[i]) {
+      builder.MaybeAddGlobalConstraint(s, &submaps[s], i, &clouds[i]);
+    } else {
+      Rigid2d rel;
+      rel.tx = search_rel_pose[3 * i];
+      rel.ty = search_rel_pose[3 * i + 1];
+      rel.angle = search_rel_pose[3 * i + 2];
+      builder.MaybeAddConstraint(s, &submaps[s], i, &clouds[i], rel);
+    }
+    builder.NotifyEndOfNode();
+  }
+  builder.WhenDone([&](const std::vector<OracleConstraint>& r) {
+    std::lock_guard<std::mutex> l(m);
+    result = r;
+    done = true;
+    cv.notify_all();
+  });
+  {
+    std::unique_lock<std::mutex> l(m);
+    cv.wait(l, [&] { return done; });
+  }
+  const auto t1 = std::chrono::steady_clock::now();
+  for (const OracleConstraint& c : result) {
+    oracle_result2d& r = out[c.node_id];
+    r.found = 1;
+    r.scan_index = c.winner.scan_index;
+    r.x_index_offset = c.winner.x_index_offset;
+    r.y_index_offset = c.winner.y_index_offset;
+    r.score = c.score;
+    r.pose_x = c.tx;
+    r.pose_y = c.ty;
+    r.pose_theta = c.angle;
+  }
+  const MatchStats st = builder.stats();
+  if (out_stats4) {
+    out_stats4[0] = static_cast<double>(st.scored_top);
+    out_stats4[1] = static_cast<double>(st.scored_lower);
+    out_stats4[2] = static_cast<double>(st.num_scans);
+    out_stats4[3] = static_cast<double>(st.num_points);
+  }
+  for (int i = 0; i < num_submaps; ++i) builder.DeleteScanMatcher(i);
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+}  // extern "C"

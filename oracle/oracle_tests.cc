@@ -1,0 +1,457 @@
+// TEST INFRASTRUCTURE ONLY (see csm_oracle.h).
+//
+// Ports of the reference's own unit tests for the hot path onto the oracle.  The
+// oracle is only trusted once every one of these known-answer tests passes.  Each
+// test cites the reference test it restates (paths relative to
+// /root/reference/cartographer/).  No gtest in this image: a tiny EXPECT harness is
+// used instead, and the process exit code is the number of failed expectations.
+#include <cstring>
+#include <random>
+#include <string>
+
+#include "cpu_pool.h"
+#include "csm_oracle.h"
+
+namespace {
+
+int g_failures = 0;
+int g_checks = 0;
+const char* g_test = "";
+
+#define EXPECT_TRUE(c)                                                        \
+  do {                                                                        \
+    ++g_checks;                                                               \
+    if (!(c)) {                                                               \
+      ++g_failures;                                                           \
+      std::fprintf(stderr, "[%s] EXPECT_TRUE(%s) failed at line %d\n", g_test, #c, __LINE__); \
+    }                                                                         \
+  } while (0)
+#define EXPECT_EQ(a, b) EXPECT_TRUE((a) == (b))
+#define EXPECT_LT(a, b) EXPECT_TRUE((a) < (b))
+#define EXPECT_GT(a, b) EXPECT_TRUE((a) > (b))
+#define EXPECT_NEAR(a, b, tol)                                                  \
+  do {                                                                          \
+    ++g_checks;                                                                 \
+    const double _a = (a), _b = (b);                                            \
+    if (!(std::abs(_a - _b) <= (tol))) {                                        \
+      ++g_failures;                                                             \
+      std::fprintf(stderr, "[%s] EXPECT_NEAR(%s=%.9g, %s=%.9g, %g) failed at line %d\n", g_test, \
+                   #a, _a, #b, _b, static_cast<double>(tol), __LINE__);         \
+    }                                                                           \
+  } while (0)
+
+using namespace oracle;
+
+MapLimits Limits(double res, double max_x, double max_y, int nx, int ny) {
+  MapLimits l;
+  l.resolution = res;
+  l.max_x = max_x;
+  l.max_y = max_y;
+  l.cell_limits.num_x_cells = nx;
+  l.cell_limits.num_y_cells = ny;
+  return l;
+}
+
+// Fixture-only float rigid transform (transform/rigid_transform.h:34-103,
+// transform/transform.h Embed3D) used to build the reference tests' inputs.
+struct Rigid2f {
+  float tx, ty, angle;
+};
+Rigid2f Inverse(const Rigid2f& t) {
+  const float a = -t.angle;
+  const float c = std::cos(a), s = std::sin(a);
+  return Rigid2f{-(c * t.tx + -s * t.ty), -(s * t.tx + c * t.ty), a};
+}
+Rigid2f Mul(const Rigid2f& l, const Rigid2f& r) {
+  const float c = std::cos(l.angle), s = std::sin(l.angle);
+  return Rigid2f{(c * r.tx + -s * r.ty) + l.tx, (s * r.tx + c * r.ty) + l.ty, l.angle + r.angle};
+}
+PointCloud TransformEmbed3D(const PointCloud& cloud, const Rigid2f& t) {
+  const Quatf q = QuatFromYaw(t.angle);
+  PointCloud out;
+  for (const Vec3f& p : cloud) {
+    Vec3f r = QuatRotate(q, p);
+    r.x += t.tx;
+    r.y += t.ty;
+    r.z += 0.f;
+    out.push_back(r);
+  }
+  return out;
+}
+
+// fast_correlative_scan_matcher_2d_test.cc:37-77 and :79-117.
+void PrecomputationGridAgainstBruteForce(const char* name, ProbabilityGrid* grid, int x0, int y0,
+                                         std::initializer_list<int> widths) {
+  g_test = name;
+  std::mt19937 prng(42);
+  std::uniform_int_distribution<int> distribution(0, 255);
+  std::vector<float> scratch;
+  const CellLimits cl = grid->limits().cell_limits;
+  PrecomputationGrid2D dummy(*grid, cl, 1, &scratch);
+  for (int y = y0; y < cl.num_y_cells; ++y)
+    for (int x = x0; x < cl.num_x_cells; ++x) {
+      Array2i c;
+      c.x = x;
+      c.y = y;
+      grid->SetProbability(c, dummy.ToScore(distribution(prng)));
+    }
+  scratch.clear();
+  for (const int width : widths) {
+    PrecomputationGrid2D pg(*grid, cl, width, &scratch);
+    for (int y = 0; y < cl.num_y_cells; ++y)
+      for (int x = 0; x < cl.num_x_cells; ++x) {
+        float max_score = -std::numeric_limits<float>::infinity();
+        for (int dy = 0; dy != width; ++dy)
+          for (int dx = 0; dx != width; ++dx) {
+            Array2i c;
+            c.x = x + dx;
+            c.y = y + dy;
+            max_score = std::max<float>(max_score, grid->GetProbability(c));
+          }
+        Array2i c;
+        c.x = x;
+        c.y = y;
+        EXPECT_NEAR(max_score, pg.ToScore(pg.GetValue(c)), 1e-4);
+      }
+  }
+}
+
+void TestPrecomputationGridCorrectValues() {
+  ProbabilityGrid grid(Limits(0.05, 5., 5., 250, 250));
+  PrecomputationGridAgainstBruteForce("PrecomputationGridTest.CorrectValues", &grid, 50, 50,
+                                      {1, 2, 3, 8});
+}
+void TestPrecomputationGridTiny() {
+  ProbabilityGrid grid(Limits(0.05, 0.1, 0.1, 4, 4));
+  PrecomputationGridAgainstBruteForce("PrecomputationGridTest.TinyProbabilityGrid", &grid, 0, 0,
+                                      {1, 2, 3, 8, 200});
+}
+
+// correlative_scan_matcher_test.cc:26-40
+void TestSearchParametersConstruction() {
+  g_test = "SearchParameters.Construction";
+  const SearchParameters sp(4, 5, 0.03, 0.05);
+  EXPECT_EQ(5, sp.num_angular_perturbations);
+  EXPECT_NEAR(0.03, sp.angular_perturbation_step_size, 1e-9);
+  EXPECT_NEAR(0.05, sp.resolution, 1e-9);
+  EXPECT_EQ(11, sp.num_scans);
+  EXPECT_EQ(11u, sp.linear_bounds.size());
+  for (const LinearBounds& lb : sp.linear_bounds) {
+    EXPECT_EQ(-4, lb.min_x);
+    EXPECT_EQ(4, lb.max_x);
+    EXPECT_EQ(-4, lb.min_y);
+    EXPECT_EQ(4, lb.max_y);
+  }
+}
+// correlative_scan_matcher_test.cc:42-56
+void TestCandidateConstruction() {
+  g_test = "Candidate.Construction";
+  const SearchParameters sp(4, 5, 0.03, 0.05);
+  const Candidate2D c(3, 4, -5, sp);
+  EXPECT_EQ(3, c.scan_index);
+  EXPECT_EQ(4, c.x_index_offset);
+  EXPECT_EQ(-5, c.y_index_offset);
+  EXPECT_NEAR(0.25, c.x, 1e-9);
+  EXPECT_NEAR(-0.2, c.y, 1e-9);
+  EXPECT_NEAR(-0.06, c.orientation, 1e-9);
+  EXPECT_NEAR(0., c.score, 1e-9);
+  Candidate2D bigger(3, 4, 5, sp);
+  bigger.score = 1.;
+  EXPECT_TRUE(c < bigger);
+}
+// correlative_scan_matcher_test.cc:58-70
+void TestGenerateRotatedScans() {
+  g_test = "GenerateRotatedScans";
+  PointCloud cloud;
+  cloud.push_back(Vec3f{-1.f, 1.f, 0.f});
+  const std::vector<PointCloud> scans =
+      GenerateRotatedScans(cloud, SearchParameters(0, 1, M_PI / 2., 0.));
+  EXPECT_EQ(3u, scans.size());
+  EXPECT_NEAR(1., scans[0][0].x, 1e-6);
+  EXPECT_NEAR(1., scans[0][0].y, 1e-6);
+  EXPECT_NEAR(-1., scans[1][0].x, 1e-6);
+  EXPECT_NEAR(1., scans[1][0].y, 1e-6);
+  EXPECT_NEAR(-1., scans[2][0].x, 1e-6);
+  EXPECT_NEAR(-1., scans[2][0].y, 1e-6);
+}
+PointCloud SevenPointCloud() {
+  PointCloud cloud;
+  cloud.push_back(Vec3f{0.025f, 0.175f, 0.f});
+  cloud.push_back(Vec3f{-0.025f, 0.175f, 0.f});
+  cloud.push_back(Vec3f{-0.075f, 0.175f, 0.f});
+  cloud.push_back(Vec3f{-0.125f, 0.175f, 0.f});
+  cloud.push_back(Vec3f{-0.125f, 0.125f, 0.f});
+  cloud.push_back(Vec3f{-0.125f, 0.075f, 0.f});
+  cloud.push_back(Vec3f{-0.125f, 0.025f, 0.f});
+  return cloud;
+}
+// correlative_scan_matcher_test.cc:72-96 -- exact integer cell indices.
+void TestDiscretizeScans() {
+  g_test = "DiscretizeScans";
+  const PointCloud cloud = SevenPointCloud();
+  const MapLimits limits = Limits(0.05, 0.05, 0.25, 6, 6);
+  const std::vector<PointCloud> scans = GenerateRotatedScans(cloud, SearchParameters(0, 0, 0., 0.));
+  const std::vector<DiscreteScan2D> d = DiscretizeScans(limits, scans, 0.f, 0.f);
+  EXPECT_EQ(1u, d.size());
+  EXPECT_EQ(7u, d[0].size());
+  const int expect[7][2] = {{1, 0}, {1, 1}, {1, 2}, {1, 3}, {2, 3}, {3, 3}, {4, 3}};
+  for (int i = 0; i < 7; ++i) {
+    EXPECT_EQ(expect[i][0], d[0][i].x);
+    EXPECT_EQ(expect[i][1], d[0][i].y);
+  }
+}
+
+bool IsNearly(const Rigid2f& expected, const Rigid2d& actual, float tol) {
+  // transform/rigid_transform_test_helpers.h:31-46: Eigen isApprox on the 3x3
+  // affine matrices, i.e. |a - b|_F^2 <= tol^2 * min(|a|_F^2, |b|_F^2).
+  const float m0[9] = {std::cos(expected.angle), -std::sin(expected.angle), expected.tx,
+                       std::sin(expected.angle), std::cos(expected.angle),  expected.ty,
+                       0.f, 0.f, 1.f};
+  const float aa = static_cast<float>(actual.angle);
+  const float m1[9] = {std::cos(aa), -std::sin(aa), static_cast<float>(actual.tx),
+                       std::sin(aa), std::cos(aa),  static_cast<float>(actual.ty),
+                       0.f, 0.f, 1.f};
+  float d2 = 0.f, n0 = 0.f, n1 = 0.f;
+  for (int i = 0; i < 9; ++i) {
+    d2 += (m0[i] - m1[i]) * (m0[i] - m1[i]);
+    n0 += m0[i] * m0[i];
+    n1 += m1[i] * m1[i];
+  }
+  return d2 <= tol * tol * std::min(n0, n1);
+}
+
+// fast_correlative_scan_matcher_2d_test.cc:144-192
+void TestFastCorrectPose() {
+  g_test = "FastCorrelativeScanMatcherTest.CorrectPose";
+  std::mt19937 prng(42);
+  std::uniform_real_distribution<float> distribution(-1.f, 1.f);
+  const ProbabilityGridRangeDataInserter2D inserter(0.7, 0.4, true);
+  constexpr float kMinScore = 0.1f;
+  FastCorrelativeScanMatcherOptions2D options;
+  options.linear_search_window = 3.;
+  options.angular_search_window = 1.;
+  options.branch_and_bound_depth = 3;
+  PointCloud cloud;
+  cloud.push_back(Vec3f{-2.5f, 0.5f, 0.f});
+  cloud.push_back(Vec3f{-2.f, 0.5f, 0.f});
+  cloud.push_back(Vec3f{0.f, -0.5f, 0.f});
+  cloud.push_back(Vec3f{0.5f, -1.6f, 0.f});
+  cloud.push_back(Vec3f{2.5f, 0.5f, 0.f});
+  cloud.push_back(Vec3f{2.5f, 1.7f, 0.f});
+  for (int i = 0; i != 50; ++i) {
+    const float ex = static_cast<float>(2. * distribution(prng));
+    const float ey = static_cast<float>(2. * distribution(prng));
+    const float ea = static_cast<float>(0.5 * distribution(prng));
+    const Rigid2f expected{ex, ey, ea};
+    ProbabilityGrid grid(Limits(0.05, 5., 5., 200, 200));
+    RangeData rd;
+    rd.origin = Vec3f{expected.tx, expected.ty, 0.f};
+    rd.returns = TransformEmbed3D(cloud, expected);
+    inserter.Insert(rd, &grid);
+    grid.FinishUpdate();
+    FastCorrelativeScanMatcher2D matcher(grid, options);
+    Rigid2d pose;
+    float score = 0.f;
+    EXPECT_TRUE(matcher.Match(Rigid2d(), cloud, kMinScore, &score, &pose));
+    EXPECT_LT(kMinScore, score);
+    EXPECT_TRUE(IsNearly(expected, pose, 0.03f));
+    if (!IsNearly(expected, pose, 0.03f)) std::fprintf(stderr, "  exp %.4f %.4f %.4f got %.4f %.4f %.4f score %.4f\n", expected.tx, expected.ty, expected.angle, pose.tx, pose.ty, pose.angle, score);
+  }
+}
+
+// fast_correlative_scan_matcher_2d_test.cc:194-246
+void TestFastFullSubmapMatching() {
+  g_test = "FastCorrelativeScanMatcherTest.FullSubmapMatching";
+  std::mt19937 prng(42);
+  std::uniform_real_distribution<float> distribution(-1.f, 1.f);
+  const ProbabilityGridRangeDataInserter2D inserter(0.7, 0.4, true);
+  constexpr float kMinScore = 0.1f;
+  FastCorrelativeScanMatcherOptions2D options;
+  options.linear_search_window = 3.;
+  options.angular_search_window = 1.;
+  options.branch_and_bound_depth = 6;
+  PointCloud unperturbed;
+  unperturbed.push_back(Vec3f{-2.5f, 0.5f, 0.f});
+  unperturbed.push_back(Vec3f{-2.25f, 0.5f, 0.f});
+  unperturbed.push_back(Vec3f{0.f, 0.5f, 0.f});
+  unperturbed.push_back(Vec3f{0.25f, 1.6f, 0.f});
+  unperturbed.push_back(Vec3f{2.5f, 0.5f, 0.f});
+  unperturbed.push_back(Vec3f{2.f, 1.8f, 0.f});
+  for (int i = 0; i != 20; ++i) {
+    const float px = static_cast<float>(10. * distribution(prng));
+    const float py = static_cast<float>(10. * distribution(prng));
+    const float pa = static_cast<float>(1.6 * distribution(prng));
+    const Rigid2f perturbation{px, py, pa};
+    const PointCloud cloud = TransformEmbed3D(unperturbed, perturbation);
+    const float qx = static_cast<float>(2. * distribution(prng));
+    const float qy = static_cast<float>(2. * distribution(prng));
+    const float qa = static_cast<float>(0.5 * distribution(prng));
+    const Rigid2f expected = Mul(Rigid2f{qx, qy, qa}, Inverse(perturbation));
+    ProbabilityGrid grid(Limits(0.05, 5., 5., 200, 200));
+    const Rigid2f origin_pose = Mul(expected, perturbation);
+    RangeData rd;
+    rd.origin = Vec3f{origin_pose.tx, origin_pose.ty, 0.f};
+    rd.returns = TransformEmbed3D(cloud, expected);
+    inserter.Insert(rd, &grid);
+    grid.FinishUpdate();
+    FastCorrelativeScanMatcher2D matcher(grid, options);
+    Rigid2d pose;
+    float score = 0.f;
+    EXPECT_TRUE(matcher.MatchFullSubmap(cloud, kMinScore, &score, &pose));
+    EXPECT_LT(kMinScore, score);
+    EXPECT_TRUE(IsNearly(expected, pose, 0.03f));
+  }
+}
+
+// real_time_correlative_scan_matcher_2d_test.cc:125-142 and :162-180
+void TestRealTimeScores() {
+  g_test = "RealTimeCorrelativeScanMatcherTest.*ProbabilityGrid";
+  const PointCloud cloud = SevenPointCloud();
+  ProbabilityGrid grid(Limits(0.05, 0.05, 0.25, 6, 6));
+  const ProbabilityGridRangeDataInserter2D inserter(0.7, 0.4, true);
+  RangeData rd;
+  rd.origin = Vec3f{0.f, 0.f, 0.f};
+  rd.returns = cloud;
+  inserter.Insert(rd, &grid);
+  grid.FinishUpdate();
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.linear_search_window = 0.6;
+  o.angular_search_window = 0.16;
+  o.translation_delta_cost_weight = 0.;
+  o.rotation_delta_cost_weight = 0.;
+  const RealTimeCorrelativeScanMatcher2D matcher(o);
+  const SearchParameters sp(0, 0, 0., 0.);
+  const std::vector<PointCloud> scans = GenerateRotatedScans(cloud, sp);
+  const std::vector<DiscreteScan2D> d = DiscretizeScans(grid.limits(), scans, 0.f, 0.f);
+  {
+    std::vector<Candidate2D> cands;
+    cands.emplace_back(0, 0, 0, sp);
+    matcher.ScoreCandidates(grid, d, sp, &cands);
+    EXPECT_EQ(0, cands[0].scan_index);
+    EXPECT_EQ(0, cands[0].x_index_offset);
+    EXPECT_EQ(0, cands[0].y_index_offset);
+    EXPECT_NEAR(0.7, cands[0].score, 1e-2);
+  }
+  {
+    std::vector<Candidate2D> cands;
+    cands.emplace_back(0, 0, 1, sp);
+    matcher.ScoreCandidates(grid, d, sp, &cands);
+    EXPECT_EQ(1, cands[0].y_index_offset);
+    EXPECT_LT(0.7 * 3. / 7., cands[0].score);
+    EXPECT_GT(0.7, cands[0].score);
+  }
+}
+
+// constraint_builder_2d_test.cc:58-112 (CallsBack, FindsConstraints): protocol test
+// on an empty 100x110 @1.0 grid with min_score 0 and pose_graph.lua defaults ->
+// every search yields a constraint, in submission order.
+void TestConstraintBuilderProtocol() {
+  g_test = "ConstraintBuilder2DTest";
+  ThreadPool pool(1);
+  ConstraintBuilderOptions o;  // defaults = configuration_files/pose_graph.lua:17-29
+  o.sampling_ratio = 1.;
+  o.min_score = 0.;
+  o.global_localization_min_score = 0.;
+  auto wait_done = [](ConstraintBuilder2D* b) {
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    size_t got = 0;
+    b->WhenDone([&](const std::vector<OracleConstraint>& r) {
+      std::lock_guard<std::mutex> l(m);
+      got = r.size();
+      done = true;
+      cv.notify_all();
+    });
+    std::unique_lock<std::mutex> l(m);
+    cv.wait(l, [&] { return done; });
+    return got;
+  };
+  {  // CallsBack
+    ConstraintBuilder2D builder(o, &pool);
+    EXPECT_EQ(0, builder.GetNumFinishedNodes());
+    builder.NotifyEndOfNode();
+    EXPECT_EQ(0u, wait_done(&builder));
+    EXPECT_EQ(1, builder.GetNumFinishedNodes());
+  }
+  ConstraintBuilder2D builder(o, &pool);
+  ProbabilityGrid grid(Limits(1., 2., 3., 100, 110));
+  Rigid2d local_pose;
+  local_pose.tx = 4.;
+  local_pose.ty = 5.;
+  ConstraintBuilder2D::Submap submap{&grid, local_pose};
+  PointCloud cloud;
+  cloud.push_back(Vec3f{0.1f, 0.2f, 0.3f});
+  int expected_nodes = 0;
+  for (int i = 0; i < 2; ++i) {
+    EXPECT_EQ(expected_nodes, builder.GetNumFinishedNodes());
+    for (int j = 0; j < 2; ++j) builder.MaybeAddConstraint(1, &submap, 0, &cloud, Rigid2d());
+    builder.MaybeAddGlobalConstraint(1, &submap, 0, &cloud);
+    builder.NotifyEndOfNode();
+    builder.NotifyEndOfNode();
+    expected_nodes += 2;
+    EXPECT_EQ(3u, wait_done(&builder));
+    EXPECT_EQ(expected_nodes, builder.GetNumFinishedNodes());
+    builder.DeleteScanMatcher(1);
+  }
+}
+
+// Not a reference test: cross-check of the deque sliding maximum against the
+// closed form the CUDA path relies on (SURVEY.md 8(a) dagger): level i equals the
+// uint8 window max of Q[cell] with Q = quantise(1 - |LUT[cell]|), zero outside.
+void TestStackEqualsQuantisedWindowMax() {
+  g_test = "StackEqualsQuantisedWindowMax";
+  std::mt19937 prng(7);
+  for (int trial = 0; trial < 6; ++trial) {
+    const int nx = 1 + prng() % 70, ny = 1 + prng() % 70;
+    std::vector<uint16_t> cells(static_cast<size_t>(nx) * ny);
+    for (auto& c : cells) c = (prng() % 4 == 0) ? 0 : static_cast<uint16_t>(1 + prng() % 32767);
+    ProbabilityGrid grid(Limits(0.05, 1., 1., nx, ny), cells.data());
+    const int depth = 1 + trial;
+    PrecomputationGridStack2D stack(grid, depth);
+    const std::vector<float>& lut = ValueToCorrespondenceCostTable();
+    const float mn = 1.f - kMaxCorrespondenceCost, mx = 1.f - kMinCorrespondenceCost;
+    auto q = [&](uint16_t v) {
+      return RoundToInt(((1.f - std::abs(lut[v])) - mn) * (255.f / (mx - mn)));
+    };
+    for (int lvl = 0; lvl < depth; ++lvl) {
+      const int w = 1 << lvl;
+      const PrecomputationGrid2D& pg = stack.Get(lvl);
+      for (int y = -w + 1; y < ny; ++y)
+        for (int x = -w + 1; x < nx; ++x) {
+          int best = 0;
+          for (int dy = 0; dy < w; ++dy)
+            for (int dx = 0; dx < w; ++dx) {
+              const int xx = x + dx, yy = y + dy;
+              if (xx < 0 || yy < 0 || xx >= nx || yy >= ny) continue;
+              best = std::max(best, q(cells[xx + yy * nx]));
+            }
+          Array2i c;
+          c.x = x;
+          c.y = y;
+          EXPECT_EQ(best, pg.GetValue(c));
+        }
+    }
+  }
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  const bool quick = argc > 1 && std::strcmp(argv[1], "--quick") == 0;
+  TestSearchParametersConstruction();
+  TestCandidateConstruction();
+  TestGenerateRotatedScans();
+  TestDiscretizeScans();
+  TestPrecomputationGridTiny();
+  TestRealTimeScores();
+  TestStackEqualsQuantisedWindowMax();
+  TestConstraintBuilderProtocol();
+  if (!quick) {
+    TestPrecomputationGridCorrectValues();
+    TestFastCorrectPose();
+    TestFastFullSubmapMatching();
+  }
+  std::printf("oracle_tests: %d checks, %d failures\n", g_checks, g_failures);
+  return g_failures == 0 ? 0 : 1;
+}
