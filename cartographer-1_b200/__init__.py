@@ -1,0 +1,177 @@
+"""ctypes view of the B200 correlative scan matcher (test / bench driver only).
+
+The product is native: `libcsm_b200.so` (C ABI of include/csm_b200.h, CUDA kernels
+for sm_100a) and `libcsm_host.so` (C++ host layer with the reference's class
+interfaces).  This module only loads them; it contains no algorithmic code and no
+fallback: importing it without the built libraries raises, and creating a context
+without a CUDA device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_ABI = os.path.join(_HERE, "libcsm_b200.so")
+LIB_HOST = os.path.join(_HERE, "libcsm_host.so")
+
+
+class Result2D(C.Structure):
+    _fields_ = [
+        ("found", C.c_int32),
+        ("scan_index", C.c_int32),
+        ("x_index_offset", C.c_int32),
+        ("y_index_offset", C.c_int32),
+        ("score", C.c_float),
+        ("tie_resolution", C.c_int32),
+        ("pose_x", C.c_double),
+        ("pose_y", C.c_double),
+        ("pose_theta", C.c_double),
+        ("candidates_scored", C.c_uint64),
+    ]
+
+
+# Symbols include/csm_b200.h declares; tests check every one is exported.
+ABI_SYMBOLS = [
+    "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
+    "csm_ctx_synchronize", "csm_stack2d_build", "csm_stack2d_build_dev",
+    "csm_stack2d_rebuild_dev", "csm_stack2d_level", "csm_stack2d_depth",
+    "csm_stack2d_device_bytes", "csm_stack2d_destroy", "csm_match2d_batch",
+    "csm_batch2d_upload", "csm_batch2d_run", "csm_batch2d_fetch", "csm_batch2d_destroy",
+    "csm_discretize2d", "csm_rt_match2d_batch",
+]
+
+_abi = None
+_host = None
+
+
+def abi():
+    global _abi
+    if _abi is None:
+        if not os.path.exists(LIB_ABI):
+            raise RuntimeError("libcsm_b200.so is not built (run __graft_entry__.build()); "
+                               "there is no CPU fallback")
+        _abi = C.CDLL(LIB_ABI, mode=C.RTLD_GLOBAL)
+        _abi.csm_last_error.restype = C.c_char_p
+        _abi.csm_ctx_stream.restype = C.c_void_p
+        _abi.csm_ctx_stream.argtypes = [C.c_void_p]
+        _abi.csm_stack2d_device_bytes.restype = C.c_size_t
+    return _abi
+
+
+def host():
+    global _host
+    if _host is not None:
+        return _host
+    abi()
+    if not os.path.exists(LIB_HOST):
+        raise RuntimeError("libcsm_host.so is not built (run __graft_entry__.build())")
+    L = C.CDLL(LIB_HOST)
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    L.csmh_context_create.restype = C.c_void_p
+    L.csmh_context_create.argtypes = [C.c_int]
+    L.csmh_context_destroy.argtypes = [C.c_void_p]
+    L.csmh_context_raw.restype = C.c_void_p
+    L.csmh_context_raw.argtypes = [C.c_void_p]
+    L.csmh_grid_create.restype = C.c_void_p
+    L.csmh_grid_create.argtypes = [u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    L.csmh_grid_destroy.argtypes = [C.c_void_p]
+    L.csmh_quantization_table.argtypes = [C.c_void_p, u8p]
+    L.csmh_matcher_create.restype = C.c_void_p
+    L.csmh_matcher_create.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int]
+    L.csmh_matcher_destroy.argtypes = [C.c_void_p]
+    L.csmh_matcher_stack.restype = C.c_void_p
+    L.csmh_matcher_stack.argtypes = [C.c_void_p]
+    L.csmh_matcher_level.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                     C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.csmh_match_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), i32p, f64p, f32p,
+                                   i64p, f32p, C.POINTER(Result2D)]
+    _host = L
+    return L
+
+
+class Context:
+    def __init__(self, device=0):
+        self.h = host().csmh_context_create(device)
+        if not self.h:
+            raise RuntimeError("no CUDA device %d: the scan matcher has no CPU fallback" % device)
+        self.raw = host().csmh_context_raw(self.h)
+
+    def close(self):
+        if self.h:
+            host().csmh_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+class Grid:
+    """ProbabilityGrid holder: cells uint16 [ny, nx]."""
+
+    def __init__(self, cells, res, max_x, max_y):
+        cells = np.ascontiguousarray(cells, dtype=np.uint16)
+        self.ny, self.nx = cells.shape
+        self.res, self.max_x, self.max_y = res, max_x, max_y
+        self.h = host().csmh_grid_create(cells, self.nx, self.ny, res, max_x, max_y)
+
+    def quantization_table(self):
+        out = np.empty(65536, dtype=np.uint8)
+        host().csmh_quantization_table(self.h, out)
+        return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            host().csmh_grid_destroy(self.h)
+            self.h = None
+
+
+class Matcher:
+    """FastCorrelativeScanMatcher2D on the device."""
+
+    def __init__(self, ctx, grid, linear_window, angular_window, depth):
+        self.ctx, self.grid, self.depth = ctx, grid, depth
+        self.h = host().csmh_matcher_create(ctx.h, grid.h, linear_window, angular_window, depth)
+
+    def level(self, i):
+        wx, wy = C.c_int(), C.c_int()
+        rc = host().csmh_matcher_level(self.ctx.h, self.h, i, None, C.byref(wx), C.byref(wy))
+        assert rc == 0, abi().csm_last_error()
+        out = np.empty((wy.value, wx.value), dtype=np.uint8)
+        rc = host().csmh_matcher_level(self.ctx.h, self.h, i, out.ctypes.data_as(C.c_void_p),
+                                       C.byref(wx), C.byref(wy))
+        assert rc == 0, abi().csm_last_error()
+        return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            host().csmh_matcher_destroy(self.h)
+            self.h = None
+
+
+def match_batch(ctx, matchers, clouds, min_scores, initial=None):
+    """initial[i] = None -> MatchFullSubmap, else (x, y, theta) -> Match."""
+    n = len(clouds)
+    handles = (C.c_void_p * n)(*[m.h for m in matchers])
+    full = np.zeros(n, dtype=np.int32)
+    init = np.zeros((n, 3), dtype=np.float64)
+    for i in range(n):
+        if initial is None or initial[i] is None:
+            full[i] = 1
+        else:
+            init[i] = initial[i]
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, c in enumerate(clouds):
+        offsets[i + 1] = offsets[i] + len(c)
+    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
+                                               for c in clouds], axis=0), dtype=np.float32)
+    out = (Result2D * n)()
+    rc = host().csmh_match_batch(ctx.h, n, handles, full, init.reshape(-1), xyz, offsets,
+                                 np.ascontiguousarray(min_scores, dtype=np.float32), out)
+    assert rc == 0
+    return out

@@ -1,0 +1,148 @@
+// Device-side data structures of the batched 2D branch-and-bound matcher.
+#ifndef CSM_MATCH2D_CUH_
+#define CSM_MATCH2D_CUH_
+
+#include "csm_internal.cuh"
+
+namespace csm {
+
+// One (node, submap) search as the kernels see it.  All offsets index the batch's
+// shared device arrays.
+struct JobDev {
+  const uint8_t* level[CSM_MAX_DEPTH];  // precomputation level i, row-major bytes
+  int num_x, num_y;                     // grid cell limits
+  int depth;                            // branch_and_bound_depth
+  int n;                                // points per scan
+  int S;                                // num_scans
+  int lin;                              // initial +-linear bound (cells)
+  long long pts_off;                    // float3 index into points
+  long long quat_off;                   // float2 index into scan quaternions
+  long long xy_off;                     // int2 index into discrete scans (S*n)
+  long long scan_off;                   // index into per-scan arrays (S)
+  long long cand_off;                   // index into top-level score array
+  long long cand_cap;                   // reserved top-level candidates
+  float q0w, q0s;                       // initial-yaw quaternion (w, z)
+  float tx, ty;                         // fp32 initial translation
+  double max_x, max_y, res;             // MapLimits
+  float min_score;
+  float score_offset, score_scale;      // ToScore
+  float n_float;                        // float(n)
+};
+
+// Per-scan search window after ShrinkToFit plus the lowest-resolution lattice.
+struct ScanInfo {
+  int min_x, max_x, min_y, max_y;
+  int nx, ny;        // lowest-resolution candidates per axis (0 if the window is empty)
+  int base;          // exclusive prefix of nx*ny inside the job
+  int pad;
+};
+
+// Mutable per-job search state.
+struct JobState {
+  unsigned long long best;      // (ordered leaf score bits << 32) | ordered top score of its ancestor
+  unsigned long long top_best;  // (ordered top-level score bits << 32) | candidate index
+  unsigned long long win;       // phase 2: min over tied contenders of (cand index << 32 | list slot)
+  unsigned int group_best;      // phase 2: ordered top score of the winning group
+  unsigned int tie_count;       // phase 2: contenders in the winning group that hold an S*-leaf
+  unsigned int total;           // top-level candidates of this job
+  unsigned int pad;
+  unsigned long long scored;    // candidate scores evaluated
+};
+
+// Branch-and-bound node: 16 bytes.
+struct Node {
+  int job_scan;  // job << 16 | scan   (job < 65536 per chunk, scan < 65536)
+  int x, y;      // x_index_offset, y_index_offset
+  float score;
+};
+
+// Phase-2 contender: a top-level candidate that may contain the winning leaf.
+struct Contender {
+  int job, scan, x, y;
+  unsigned int cand;    // generation index inside the job
+  float score;          // its top-level score
+  int leaf_x, leaf_y;   // first S*-leaf in reference DFS order, valid if has_leaf
+  int has_leaf;
+  int pad[3];
+};
+
+// Order-preserving map float -> uint32 (works for negative values too).
+__host__ __device__ inline unsigned int float_to_ordered(float f) {
+#ifdef __CUDA_ARCH__
+  unsigned int u = __float_as_uint(f);
+#else
+  unsigned int u;
+  memcpy(&u, &f, 4);
+#endif
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ inline float ordered_to_float(unsigned int o) {
+  unsigned int u = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(u);
+#else
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+#endif
+}
+
+
+#ifdef __CUDACC__
+// Eigen's quaternion * vector for a pure yaw quaternion (w, 0, 0, s), fp32, in
+// Eigen 3.3's op order uv = 2 * (vec x v); v' = (v + w*uv) + vec x uv, with the
+// terms that are exactly zero dropped (see oracle/csm_oracle.h QuatRotate).
+__device__ __forceinline__ void yaw_rotate(float w, float s, float& vx, float& vy) {
+  float uvx = -__fmul_rn(s, vy);
+  float uvy = __fmul_rn(s, vx);
+  uvx = __fadd_rn(uvx, uvx);
+  uvy = __fadd_rn(uvy, uvy);
+  const float cx = -__fmul_rn(s, uvy);
+  const float cy = __fmul_rn(s, uvx);
+  const float rx = __fadd_rn(__fadd_rn(vx, __fmul_rn(w, uvx)), cx);
+  const float ry = __fadd_rn(__fadd_rn(vy, __fmul_rn(w, uvy)), cy);
+  vx = rx;
+  vy = ry;
+}
+
+// MapLimits::GetCellIndex (cartographer/mapping/2d/map_limits.h:69-76), fp64; the
+// cell x comes from the world y coordinate and vice versa.
+__device__ __forceinline__ void cell_index(double max_x, double max_y, double res, float wx,
+                                           float wy, int& cx, int& cy) {
+  const double fx = __dsub_rn(__ddiv_rn(__dsub_rn(max_y, static_cast<double>(wy)), res), 0.5);
+  const double fy = __dsub_rn(__ddiv_rn(__dsub_rn(max_x, static_cast<double>(wx)), res), 0.5);
+  cx = static_cast<int>(lround(fx));
+  cy = static_cast<int>(lround(fy));
+}
+#endif
+
+}  // namespace csm
+
+struct csm_batch2d {
+  int num_jobs = 0;
+  std::vector<csm::JobDev> jobs_host;
+  std::vector<int> empty_job;          // jobs with zero points: not found, no device work
+  int max_scans = 0;
+  long long total_pts = 0, total_scans = 0, total_xy = 0, total_cand = 0;
+  // device arrays
+  csm::JobDev* jobs = nullptr;
+  float* points = nullptr;             // total_pts * 3
+  float* quats = nullptr;              // total_scans * 2
+  int2* xy = nullptr;                  // total_xy
+  csm::ScanInfo* scans = nullptr;      // total_scans
+  float* top_scores = nullptr;         // total_cand
+  csm::JobState* state = nullptr;      // num_jobs
+  csm::Node* frontier[2] = {nullptr, nullptr};
+  unsigned long long frontier_cap = 0;
+  csm::Contender* contenders = nullptr;
+  unsigned int contender_cap = 0;
+  unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
+  csm_result2d* results_dev = nullptr;
+  void* arena = nullptr;               // single cudaMalloc backing all of the above
+  size_t arena_bytes = 0;
+  void* pinned = nullptr;              // staging for uploads / results
+  size_t pinned_bytes = 0;
+  bool uploaded = false, ran = false;
+};
+
+#endif  // CSM_MATCH2D_CUH_

@@ -1,0 +1,199 @@
+// RealTimeCorrelativeScanMatcher2D::Match on the device: exhaustive search on the
+// live uint16 grid, no precomputation.
+//
+// Replaces /root/reference/cartographer/mapping/internal/2d/scan_matching/
+// real_time_correlative_scan_matcher_2d.cc:61-75 (ComputeCandidateScore on a
+// ProbabilityGrid), :83-115 (GenerateExhaustiveSearchCandidates), :117-176 (Match,
+// ScoreCandidates).  One block per (job, scan): the scan is rotated and discretised
+// into shared memory once, then every thread scores whole candidates, summing the
+// probabilities in point order with sequential fp32 adds exactly like the CPU loop
+// (the sum is order-sensitive, so it is not parallelised across points).  The
+// motion penalty exp(-(hypot*w_t + |theta|*w_r)^2) is evaluated by the host with
+// glibc in fp64 and applied here as float(double(score) * penalty).  The winner is
+// std::max_element's: the first maximum in generation order scan -> x -> y.
+#include <map>
+
+#include "csm_match2d.cuh"
+
+namespace csm {
+
+struct RtJobDev {
+  const uint16_t* cells;
+  const float* cost_table;
+  const double* penalty;
+  int num_x, num_y, n, S, lin;
+  long long pts_off, quat_off;
+  float q0w, q0s, tx, ty;
+  double max_x, max_y, res;
+  float oob;
+};
+
+__global__ void __launch_bounds__(256)
+k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
+           const float* __restrict__ quats, unsigned long long* __restrict__ best) {
+  extern __shared__ int2 cell[];
+  const RtJobDev& j = jobs[blockIdx.y];
+  const int scan = blockIdx.x;
+  if (scan >= j.S) return;
+  const float qw = quats[2 * (j.quat_off + scan)], qs = quats[2 * (j.quat_off + scan) + 1];
+  for (int p = threadIdx.x; p < j.n; p += blockDim.x) {
+    float vx = points[3 * (j.pts_off + p)], vy = points[3 * (j.pts_off + p) + 1];
+    yaw_rotate(j.q0w, j.q0s, vx, vy);  // RT2D.cc:124-127
+    yaw_rotate(qw, qs, vx, vy);
+    const float wx = __fadd_rn(j.tx, vx), wy = __fadd_rn(j.ty, vy);
+    int cx, cy;
+    cell_index(j.max_x, j.max_y, j.res, wx, wy, cx, cy);
+    cell[p] = make_int2(cx, cy);
+  }
+  __syncthreads();
+  const int side = 2 * j.lin + 1;
+  const int count = side * side;
+  const float n_float = static_cast<float>(j.n);
+  unsigned long long local = 0ull;
+  for (int c = threadIdx.x; c < count; c += blockDim.x) {
+    const int x = c / side - j.lin, y = c % side - j.lin;  // x outer, y inner (RT2D.cc:100-112)
+    float sum = 0.f;
+    for (int p = 0; p < j.n; ++p) {
+      const int px = cell[p].x + x, py = cell[p].y + y;
+      float prob = j.oob;
+      if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
+          static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
+        const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
+        prob = __fsub_rn(1.f, __ldg(j.cost_table + v));
+      }
+      sum = __fadd_rn(sum, prob);
+    }
+    float score = __fdiv_rn(sum, n_float);
+    const unsigned int cand = static_cast<unsigned int>(scan) * count + c;
+    score = __double2float_rn(__dmul_rn(static_cast<double>(score), j.penalty[cand]));
+    const unsigned long long key =
+        (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
+    local = max(local, key);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local = max(local, __shfl_xor_sync(0xFFFFFFFFu, local, o));
+  if ((threadIdx.x & 31) == 0 && local != 0ull) atomicMax(&best[blockIdx.y], local);
+}
+
+}  // namespace csm
+
+using namespace csm;
+
+extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
+                                    csm_result2d* results) {
+  CSM_REQUIRE(ctx != nullptr && jobs != nullptr && results != nullptr, "NULL argument");
+  CSM_REQUIRE(num_jobs >= 1 && num_jobs <= 65535, "num_jobs must be in [1, 65535]");
+  CSM_CUDA(cudaSetDevice(ctx->device));
+  auto up = [](size_t v) { return (v + 255) & ~static_cast<size_t>(255); };
+  // Layout of one upload blob: [jobs | points | quats | penalties | tables | grids | best]
+  std::vector<RtJobDev> dev(num_jobs);
+  std::map<const void*, size_t> grid_at, table_at;
+  size_t n_pts = 0, n_scans = 0, n_pen = 0, grid_bytes = 0, table_bytes = 0;
+  int max_scans = 0, max_n = 0;
+  for (int i = 0; i < num_jobs; ++i) {
+    const csm_rt_job2d& in = jobs[i];
+    CSM_REQUIRE(in.cells && in.cost_table && in.points_xyz && in.scan_quat && in.penalty,
+                "rt job has a NULL array");
+    CSM_REQUIRE(in.num_points >= 1 && in.num_scans >= 1 && in.num_x >= 1 && in.num_y >= 1 &&
+                    in.linear_bound >= 0 && in.linear_bound <= 1024 && in.resolution > 0.,
+                "rt job sizes out of range");
+    const size_t side = 2 * static_cast<size_t>(in.linear_bound) + 1;
+    CSM_REQUIRE(side * side * in.num_scans < 0xFFFFFFFFull, "too many rt candidates");
+    if (!grid_at.count(in.cells)) {
+      grid_at[in.cells] = grid_bytes;
+      grid_bytes += up(sizeof(uint16_t) * static_cast<size_t>(in.num_x) * in.num_y);
+    }
+    if (!table_at.count(in.cost_table)) {
+      table_at[in.cost_table] = table_bytes;
+      table_bytes += up(sizeof(float) * 65536);
+    }
+    RtJobDev& j = dev[i];
+    j.num_x = in.num_x;
+    j.num_y = in.num_y;
+    j.n = in.num_points;
+    j.S = in.num_scans;
+    j.lin = in.linear_bound;
+    j.pts_off = static_cast<long long>(n_pts);
+    j.quat_off = static_cast<long long>(n_scans);
+    j.q0w = in.init_quat_w;
+    j.q0s = in.init_quat_s;
+    j.tx = in.init_tx;
+    j.ty = in.init_ty;
+    j.max_x = in.max_x;
+    j.max_y = in.max_y;
+    j.res = in.resolution;
+    j.oob = in.out_of_bounds_probability;
+    n_pts += in.num_points;
+    n_scans += in.num_scans;
+    n_pen += side * side * in.num_scans;
+    max_scans = std::max(max_scans, in.num_scans);
+    max_n = std::max(max_n, in.num_points);
+  }
+  const size_t smem = sizeof(int2) * static_cast<size_t>(max_n);
+  CSM_REQUIRE(smem <= 200 * 1024, "point cloud too large for the real-time matcher (25600 points)");
+  const size_t o_jobs = 0;
+  const size_t o_pts = o_jobs + up(sizeof(RtJobDev) * num_jobs);
+  const size_t o_quat = o_pts + up(sizeof(float) * 3 * n_pts);
+  const size_t o_pen = o_quat + up(sizeof(float) * 2 * n_scans);
+  const size_t o_tab = o_pen + up(sizeof(double) * n_pen);
+  const size_t o_grid = o_tab + table_bytes;
+  const size_t o_best = o_grid + grid_bytes;
+  const size_t total = o_best + up(sizeof(unsigned long long) * num_jobs);
+  int rc = ctx->tmp2.reserve(total);
+  if (rc == CSM_OK) rc = ctx->pin0.reserve(total);
+  if (rc != CSM_OK) return rc;
+  char* pin = ctx->pin0.as<char>();
+  char* base = ctx->tmp2.as<char>();
+  size_t pen_at = 0;
+  for (int i = 0; i < num_jobs; ++i) {
+    const csm_rt_job2d& in = jobs[i];
+    RtJobDev& j = dev[i];
+    const size_t side = 2 * static_cast<size_t>(in.linear_bound) + 1;
+    const size_t pen_n = side * side * in.num_scans;
+    memcpy(pin + o_pts + sizeof(float) * 3 * j.pts_off, in.points_xyz, sizeof(float) * 3 * j.n);
+    memcpy(pin + o_quat + sizeof(float) * 2 * j.quat_off, in.scan_quat, sizeof(float) * 2 * j.S);
+    memcpy(pin + o_pen + sizeof(double) * pen_at, in.penalty, sizeof(double) * pen_n);
+    j.penalty = reinterpret_cast<const double*>(base + o_pen) + pen_at;
+    j.cells = reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
+    j.cost_table = reinterpret_cast<const float*>(base + o_tab + table_at[in.cost_table]);
+    pen_at += pen_n;
+  }
+  for (const auto& kv : grid_at) {
+    for (int i = 0; i < num_jobs; ++i)
+      if (jobs[i].cells == kv.first) {
+        memcpy(pin + o_grid + kv.second, kv.first,
+               sizeof(uint16_t) * static_cast<size_t>(jobs[i].num_x) * jobs[i].num_y);
+        break;
+      }
+  }
+  for (const auto& kv : table_at) memcpy(pin + o_tab + kv.second, kv.first, sizeof(float) * 65536);
+  memcpy(pin + o_jobs, dev.data(), sizeof(RtJobDev) * num_jobs);
+  memset(pin + o_best, 0, sizeof(unsigned long long) * num_jobs);
+  cudaStream_t st = ctx->stream;
+  CSM_CUDA(cudaMemcpyAsync(base, pin, total, cudaMemcpyHostToDevice, st));
+  CSM_CUDA(cudaFuncSetAttribute(k_rt_score, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(std::max<size_t>(smem, 1024))));
+  k_rt_score<<<dim3(max_scans, num_jobs), 256, smem, st>>>(
+      reinterpret_cast<const RtJobDev*>(base + o_jobs), reinterpret_cast<const float*>(base + o_pts),
+      reinterpret_cast<const float*>(base + o_quat),
+      reinterpret_cast<unsigned long long*>(base + o_best));
+  CSM_CUDA(cudaGetLastError());
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(pin + o_best);
+  CSM_CUDA(cudaMemcpyAsync(best, base + o_best, sizeof(unsigned long long) * num_jobs,
+                           cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaStreamSynchronize(st));
+  for (int i = 0; i < num_jobs; ++i) {
+    const int side = 2 * jobs[i].linear_bound + 1;
+    const unsigned int cand = 0xFFFFFFFFu - static_cast<unsigned int>(best[i] & 0xFFFFFFFFull);
+    csm_result2d& r = results[i];
+    r.found = 1;
+    r.scan_index = static_cast<int>(cand / (side * side));
+    const int c = static_cast<int>(cand % (side * side));
+    r.x_index_offset = c / side - jobs[i].linear_bound;
+    r.y_index_offset = c % side - jobs[i].linear_bound;
+    r.score = ordered_to_float(static_cast<unsigned int>(best[i] >> 32));
+    r.tie_resolution = 0;
+    r.candidates_scored = static_cast<uint64_t>(side) * side * jobs[i].num_scans;
+  }
+  return CSM_OK;
+}

@@ -173,10 +173,8 @@ size_t csm_stack2d_device_bytes(const csm_stack2d* s) { return s ? s->bytes + 65
 
 void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* s) {
   if (!s) return;
-  if (ctx) {
-    cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-  }
+  cudaSetDevice(s->device);
+  if (ctx) cudaStreamSynchronize(ctx->stream); else cudaDeviceSynchronize();
   if (s->base) cudaFree(s->base);
   if (s->q_lut_dev) cudaFree(s->q_lut_dev);
   delete s;

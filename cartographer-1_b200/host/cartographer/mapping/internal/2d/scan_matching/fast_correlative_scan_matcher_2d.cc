@@ -1,0 +1,202 @@
+#include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace cartographer {
+namespace mapping {
+namespace scan_matching {
+namespace {
+
+// The reference aborts on violated preconditions (glog CHECK); device errors get
+// the same treatment, with the C ABI's message.
+void CheckOk(int status, const char* what) {
+  if (status != CSM_OK) {
+    std::fprintf(stderr, "%s failed: %s\n", what, csm_last_error());
+    std::abort();
+  }
+}
+
+DeviceContext* ThreadDefaultContext() {
+  thread_local DeviceContext context(0);
+  return &context;
+}
+
+}  // namespace
+
+DeviceContext::DeviceContext(int device) : device_(device) {
+  CheckOk(csm_ctx_create(device, &ctx_), "csm_ctx_create");
+}
+DeviceContext::~DeviceContext() { csm_ctx_destroy(ctx_); }
+
+std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid) {
+  const float min_score = 1.f - grid.GetMaxCorrespondenceCost();
+  const float max_score = 1.f - grid.GetMinCorrespondenceCost();
+  const float scale = 255.f / (max_score - min_score);
+  const std::vector<float>& cost = grid.value_to_correspondence_cost_table();
+  std::vector<uint8> table(65536);
+  for (size_t v = 0; v != table.size(); ++v) {
+    const float probability = 1.f - std::abs(cost[v]);
+    const int q = common::RoundToInt((probability - min_score) * scale);
+    CSM_CHECK(q >= 0);
+    CSM_CHECK(q <= 255);
+    table[v] = static_cast<uint8>(q);
+  }
+  return table;
+}
+
+FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
+    const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options)
+    : options_(options), limits_(grid.limits()), context_(ThreadDefaultContext()) {
+  Build(grid);
+}
+
+FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
+    const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options,
+    DeviceContext* context)
+    : options_(options), limits_(grid.limits()), context_(context) {
+  Build(grid);
+}
+
+void FastCorrelativeScanMatcher2D::Build(const Grid2D& grid) {
+  CSM_CHECK(options_.branch_and_bound_depth() >= 1);
+  min_score_ = 1.f - grid.GetMaxCorrespondenceCost();
+  max_score_ = 1.f - grid.GetMinCorrespondenceCost();
+  const std::vector<uint8> q = ComputeQuantizationTable(grid);
+  const CellLimits& cells = limits_.cell_limits();
+  CheckOk(csm_stack2d_build(context_->get(), grid.correspondence_cost_cells().data(),
+                            cells.num_x_cells, cells.num_y_cells, q.data(),
+                            options_.branch_and_bound_depth(), &stack_),
+          "csm_stack2d_build");
+}
+
+FastCorrelativeScanMatcher2D::~FastCorrelativeScanMatcher2D() {
+  // The constructing thread's context may already be gone; the stack knows its device.
+  csm_stack2d_destroy(nullptr, stack_);
+}
+
+bool FastCorrelativeScanMatcher2D::Match(const transform::Rigid2d& initial_pose_estimate,
+                                         const sensor::PointCloud& point_cloud,
+                                         const float min_score, float* score,
+                                         transform::Rigid2d* pose_estimate) const {
+  CSM_CHECK(score != nullptr);
+  CSM_CHECK(pose_estimate != nullptr);
+  Query q;
+  q.point_cloud = &point_cloud;
+  q.full_submap = false;
+  q.initial_pose_estimate = initial_pose_estimate;
+  q.min_score = min_score;
+  // A matcher built on another thread's context still runs on the caller's own one.
+  DeviceContext* ctx = ThreadDefaultContext();
+  if (ctx->device() != context_->device()) ctx = context_;
+  const Answer a = MatchBatch(ctx, {{this, q}})[0];
+  if (!a.found) return false;
+  *score = a.score;
+  *pose_estimate = a.pose_estimate;
+  return true;
+}
+
+bool FastCorrelativeScanMatcher2D::MatchFullSubmap(const sensor::PointCloud& point_cloud,
+                                                   const float min_score, float* score,
+                                                   transform::Rigid2d* pose_estimate) const {
+  CSM_CHECK(score != nullptr);
+  CSM_CHECK(pose_estimate != nullptr);
+  Query q;
+  q.point_cloud = &point_cloud;
+  q.full_submap = true;
+  q.min_score = min_score;
+  DeviceContext* ctx = ThreadDefaultContext();
+  if (ctx->device() != context_->device()) ctx = context_;
+  const Answer a = MatchBatch(ctx, {{this, q}})[0];
+  if (!a.found) return false;
+  *score = a.score;
+  *pose_estimate = a.pose_estimate;
+  return true;
+}
+
+std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::MatchBatch(
+    DeviceContext* context,
+    const std::vector<std::pair<const FastCorrelativeScanMatcher2D*, Query>>& queries) {
+  const size_t n = queries.size();
+  std::vector<Answer> answers(n);
+  if (n == 0) return answers;
+  std::vector<SearchParameters> params;
+  std::vector<transform::Rigid2d> initial(n);
+  std::vector<std::vector<float>> xyz(n), quats(n);
+  std::vector<csm_job2d> jobs(n);
+  params.reserve(n);
+  for (size_t i = 0; i != n; ++i) {
+    const FastCorrelativeScanMatcher2D& m = *queries[i].first;
+    const Query& q = queries[i].second;
+    CSM_CHECK(q.point_cloud != nullptr);
+    const double res = m.limits_.resolution();
+    if (q.full_submap) {
+      // Window around the submap centre that includes it fully
+      // (reference: fast_correlative_scan_matcher_2d.cc:215-222).
+      params.emplace_back(1e6 * res, M_PI, *q.point_cloud, res);
+      const double half_res = 0.5 * res;
+      initial[i] = transform::Rigid2d::Translation(transform::Vector2d(
+          m.limits_.max().x() - half_res * m.limits_.cell_limits().num_y_cells,
+          m.limits_.max().y() - half_res * m.limits_.cell_limits().num_x_cells));
+    } else {
+      params.emplace_back(m.options_.linear_search_window(), m.options_.angular_search_window(),
+                          *q.point_cloud, res);
+      initial[i] = q.initial_pose_estimate;
+    }
+    const SearchParameters& sp = params.back();
+    xyz[i].resize(3 * q.point_cloud->size());
+    for (size_t p = 0; p != q.point_cloud->size(); ++p) {
+      const sensor::Vector3f& v = (*q.point_cloud)[p].position;
+      xyz[i][3 * p] = v.x();
+      xyz[i][3 * p + 1] = v.y();
+      xyz[i][3 * p + 2] = v.z();
+    }
+    quats[i] = sp.ScanQuaternionTable();
+    csm_job2d& job = jobs[i];
+    std::memset(&job, 0, sizeof(job));
+    job.stack = m.stack_;
+    job.points_xyz = xyz[i].data();
+    job.num_points = static_cast<int32_t>(q.point_cloud->size());
+    job.num_scans = sp.num_scans;
+    job.scan_quat = quats[i].data();
+    // Rotation2Dd -> Rotation2Df -> AngleAxisf -> Quaternionf (reference :235-239)
+    const float yaw = static_cast<float>(initial[i].rotation().angle());
+    const float half_yaw = 0.5f * yaw;
+    job.init_quat_w = std::cos(half_yaw);
+    job.init_quat_s = std::sin(half_yaw);
+    job.init_tx = static_cast<float>(initial[i].translation().x());
+    job.init_ty = static_cast<float>(initial[i].translation().y());
+    job.max_x = m.limits_.max().x();
+    job.max_y = m.limits_.max().y();
+    job.resolution = res;
+    job.linear_bound = sp.linear_bounds.empty() ? 0 : sp.linear_bounds[0].max_x;
+    job.min_score = q.min_score;
+    job.score_offset = m.min_score_;
+    job.score_scale = (m.max_score_ - m.min_score_) / 255.f;
+  }
+  std::vector<csm_result2d> results(n);
+  CheckOk(csm_match2d_batch(context->get(), jobs.data(), static_cast<int>(n), results.data()),
+          "csm_match2d_batch");
+  for (size_t i = 0; i != n; ++i) {
+    const csm_result2d& r = results[i];
+    Answer& a = answers[i];
+    a.found = r.found == 1;
+    a.candidates_scored = r.candidates_scored;
+    a.tie_resolution = r.tie_resolution;
+    a.best_candidate =
+        Candidate2D(r.scan_index, r.x_index_offset, r.y_index_offset, params[i]);
+    a.best_candidate.score = r.score;
+    a.score = r.score;
+    if (a.found) {  // reference :253-260
+      a.pose_estimate = transform::Rigid2d(
+          transform::Vector2d(initial[i].translation().x() + a.best_candidate.x,
+                              initial[i].translation().y() + a.best_candidate.y),
+          initial[i].rotation() * transform::Rotation2Dd(a.best_candidate.orientation));
+    }
+  }
+  return answers;
+}
+
+}  // namespace scan_matching
+}  // namespace mapping
+}  // namespace cartographer

@@ -1,0 +1,105 @@
+// B200 implementation behind the reference's FastCorrelativeScanMatcher2D interface
+// (cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h:112-164).
+//
+// Construction uploads the grid and builds the precomputation stack on the device
+// (csm_stack2d_build); Match / MatchFullSubmap keep the reference's signatures and
+// semantics and forward to csm_match2d_batch.  MatchBatch is the additional entry
+// the constraint builder uses to coalesce many (node, submap) searches into one
+// launch sequence.  There is no CPU fallback: construction aborts (CHECK semantics)
+// when no CUDA device is usable.
+#ifndef CARTOGRAPHER_MAPPING_INTERNAL_2D_SCAN_MATCHING_FAST_CORRELATIVE_SCAN_MATCHER_2D_H_
+#define CARTOGRAPHER_MAPPING_INTERNAL_2D_SCAN_MATCHING_FAST_CORRELATIVE_SCAN_MATCHER_2D_H_
+
+#include <memory>
+#include <vector>
+
+#include "cartographer/mapping/internal/2d/scan_matching/correlative_scan_matcher_2d.h"
+#include "cartographer_compat.h"
+#include "csm_b200.h"
+
+namespace cartographer {
+namespace mapping {
+namespace scan_matching {
+
+// Owns one csm_ctx per device and hands it to matchers; thread-compatible (callers
+// serialise use of one context, see include/csm_b200.h).
+class DeviceContext {
+ public:
+  explicit DeviceContext(int device = 0);
+  ~DeviceContext();
+  DeviceContext(const DeviceContext&) = delete;
+  DeviceContext& operator=(const DeviceContext&) = delete;
+  csm_ctx* get() const { return ctx_; }
+  int device() const { return device_; }
+
+ private:
+  csm_ctx* ctx_ = nullptr;
+  int device_ = 0;
+};
+
+// uint16 cell value -> uint8 precomputation value, i.e. the reference's
+// ComputeCellValue(1.f - |GetCorrespondenceCost|) for every possible cell value
+// (fast_correlative_scan_matcher_2d.cc:97-98,112-113,163-169).
+std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid);
+
+class FastCorrelativeScanMatcher2D {
+ public:
+  FastCorrelativeScanMatcher2D(const Grid2D& grid,
+                               const proto::FastCorrelativeScanMatcherOptions2D& options);
+  // Same, on an explicit device context (multi-GPU sharding).
+  FastCorrelativeScanMatcher2D(const Grid2D& grid,
+                               const proto::FastCorrelativeScanMatcherOptions2D& options,
+                               DeviceContext* context);
+  ~FastCorrelativeScanMatcher2D();
+
+  FastCorrelativeScanMatcher2D(const FastCorrelativeScanMatcher2D&) = delete;
+  FastCorrelativeScanMatcher2D& operator=(const FastCorrelativeScanMatcher2D&) = delete;
+
+  // Reference semantics: true iff a score above 'min_score' (strictly) exists; only
+  // then 'score' and 'pose_estimate' are written.
+  bool Match(const transform::Rigid2d& initial_pose_estimate,
+             const sensor::PointCloud& point_cloud, float min_score, float* score,
+             transform::Rigid2d* pose_estimate) const;
+  bool MatchFullSubmap(const sensor::PointCloud& point_cloud, float min_score, float* score,
+                       transform::Rigid2d* pose_estimate) const;
+
+  // One search of a batch; 'full_submap' selects MatchFullSubmap semantics.
+  struct Query {
+    const sensor::PointCloud* point_cloud = nullptr;
+    bool full_submap = false;
+    transform::Rigid2d initial_pose_estimate;
+    float min_score = 0.f;
+  };
+  struct Answer {
+    bool found = false;
+    float score = 0.f;
+    transform::Rigid2d pose_estimate;
+    Candidate2D best_candidate{0, 0, 0, SearchParameters(0, 0, 0., 0.)};
+    uint64_t candidates_scored = 0;
+    int tie_resolution = 0;
+  };
+  // All queries may target different matchers on the same device context.
+  static std::vector<Answer> MatchBatch(
+      DeviceContext* context,
+      const std::vector<std::pair<const FastCorrelativeScanMatcher2D*, Query>>& queries);
+
+  const csm_stack2d* stack() const { return stack_; }
+  const MapLimits& limits() const { return limits_; }
+  DeviceContext* context() const { return context_; }
+
+ private:
+  void Build(const Grid2D& grid);
+
+  const proto::FastCorrelativeScanMatcherOptions2D options_;
+  MapLimits limits_;
+  float min_score_ = 0.f;  // PrecomputationGrid2D::min_score_
+  float max_score_ = 0.f;  // PrecomputationGrid2D::max_score_
+  DeviceContext* context_ = nullptr;
+  csm_stack2d* stack_ = nullptr;
+};
+
+}  // namespace scan_matching
+}  // namespace mapping
+}  // namespace cartographer
+
+#endif  // CARTOGRAPHER_MAPPING_INTERNAL_2D_SCAN_MATCHING_FAST_CORRELATIVE_SCAN_MATCHER_2D_H_

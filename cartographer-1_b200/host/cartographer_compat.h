@@ -1,0 +1,259 @@
+// Minimal stand-ins for the Cartographer value types the scan-matching boundary
+// uses.  This image has no Eigen / protobuf / glog, so the host layer compiles
+// against these; in a full Cartographer tree the real headers replace this file
+// (same names, same accessors, same semantics):
+//   transform::Rigid2d            cartographer/transform/rigid_transform.h:34-103
+//   sensor::PointCloud            cartographer/sensor/point_cloud.h:33-92
+//   mapping::CellLimits           cartographer/mapping/2d/xy_index.h:33-45
+//   mapping::MapLimits            cartographer/mapping/2d/map_limits.h:39-98
+//   mapping::ValueConversionTables cartographer/mapping/value_conversion_tables.{h,cc}
+//   mapping::Grid2D/ProbabilityGrid cartographer/mapping/2d/grid_2d.h:38-128,
+//                                  cartographer/mapping/2d/probability_grid.{h,cc}
+//   proto::*Options               cartographer/mapping/proto/scan_matching/*.proto,
+//                                  cartographer/mapping/proto/pose_graph/constraint_builder_options.proto
+#ifndef CSM_HOST_CARTOGRAPHER_COMPAT_H_
+#define CSM_HOST_CARTOGRAPHER_COMPAT_H_
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <memory>
+#include <tuple>
+#include <vector>
+
+#define CSM_CHECK(cond)                                                               \
+  do {                                                                                \
+    if (!(cond)) {                                                                    \
+      std::fprintf(stderr, "Check failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__);  \
+      std::abort();                                                                   \
+    }                                                                                 \
+  } while (0)
+
+namespace cartographer {
+
+using uint8 = uint8_t;
+using uint16 = uint16_t;
+
+namespace common {
+inline int RoundToInt(const float x) { return static_cast<int>(std::lround(x)); }
+inline int RoundToInt(const double x) { return static_cast<int>(std::lround(x)); }
+}  // namespace common
+
+namespace transform {
+struct Vector2d {
+  double v[2] = {0., 0.};
+  Vector2d() = default;
+  Vector2d(double x, double y) : v{x, y} {}
+  double x() const { return v[0]; }
+  double y() const { return v[1]; }
+  double norm() const { return std::sqrt(v[0] * v[0] + v[1] * v[1]); }
+};
+// Rotation kept as its angle, like Eigen::Rotation2Dd.
+class Rotation2Dd {
+ public:
+  Rotation2Dd() = default;
+  explicit Rotation2Dd(double angle) : angle_(angle) {}
+  double angle() const { return angle_; }
+  Rotation2Dd operator*(const Rotation2Dd& o) const { return Rotation2Dd(angle_ + o.angle_); }
+  Rotation2Dd inverse() const { return Rotation2Dd(-angle_); }
+  Vector2d operator*(const Vector2d& p) const {
+    const double s = std::sin(angle_), c = std::cos(angle_);
+    return Vector2d(c * p.x() + -s * p.y(), s * p.x() + c * p.y());
+  }
+
+ private:
+  double angle_ = 0.;
+};
+class Rigid2d {
+ public:
+  Rigid2d() = default;
+  Rigid2d(const Vector2d& t, const Rotation2Dd& r) : translation_(t), rotation_(r) {}
+  Rigid2d(const Vector2d& t, double r) : translation_(t), rotation_(r) {}
+  static Rigid2d Identity() { return Rigid2d(); }
+  static Rigid2d Translation(const Vector2d& t) { return Rigid2d(t, Rotation2Dd()); }
+  static Rigid2d Rotation(double r) { return Rigid2d(Vector2d(), r); }
+  const Vector2d& translation() const { return translation_; }
+  Rotation2Dd rotation() const { return rotation_; }
+  Rigid2d inverse() const {
+    const Rotation2Dd r = rotation_.inverse();
+    const Vector2d t = r * translation_;
+    return Rigid2d(Vector2d(-t.x(), -t.y()), r);
+  }
+
+ private:
+  Vector2d translation_;
+  Rotation2Dd rotation_;
+};
+inline Rigid2d operator*(const Rigid2d& l, const Rigid2d& r) {
+  const Vector2d t = l.rotation() * r.translation();
+  return Rigid2d(Vector2d(t.x() + l.translation().x(), t.y() + l.translation().y()),
+                 l.rotation() * r.rotation());
+}
+}  // namespace transform
+
+namespace sensor {
+struct Vector3f {
+  float v[3] = {0.f, 0.f, 0.f};
+  Vector3f() = default;
+  Vector3f(float x, float y, float z) : v{x, y, z} {}
+  float x() const { return v[0]; }
+  float y() const { return v[1]; }
+  float z() const { return v[2]; }
+};
+struct RangefinderPoint {
+  Vector3f position;
+};
+class PointCloud {
+ public:
+  PointCloud() = default;
+  explicit PointCloud(std::vector<RangefinderPoint> p) : points_(std::move(p)) {}
+  size_t size() const { return points_.size(); }
+  bool empty() const { return points_.empty(); }
+  const std::vector<RangefinderPoint>& points() const { return points_; }
+  const RangefinderPoint& operator[](size_t i) const { return points_[i]; }
+  void push_back(RangefinderPoint p) { points_.push_back(p); }
+  std::vector<RangefinderPoint>::const_iterator begin() const { return points_.begin(); }
+  std::vector<RangefinderPoint>::const_iterator end() const { return points_.end(); }
+
+ private:
+  std::vector<RangefinderPoint> points_;
+};
+}  // namespace sensor
+
+namespace mapping {
+
+struct CellLimits {
+  CellLimits() = default;
+  CellLimits(int x, int y) : num_x_cells(x), num_y_cells(y) {}
+  int num_x_cells = 0;
+  int num_y_cells = 0;
+};
+
+class MapLimits {
+ public:
+  MapLimits(double resolution, const transform::Vector2d& max, const CellLimits& cell_limits)
+      : resolution_(resolution), max_(max), cell_limits_(cell_limits) {
+    CSM_CHECK(resolution_ > 0.);
+    CSM_CHECK(cell_limits.num_x_cells > 0);
+    CSM_CHECK(cell_limits.num_y_cells > 0);
+  }
+  double resolution() const { return resolution_; }
+  const transform::Vector2d& max() const { return max_; }
+  const CellLimits& cell_limits() const { return cell_limits_; }
+
+ private:
+  double resolution_;
+  transform::Vector2d max_;
+  CellLimits cell_limits_;
+};
+
+constexpr float kMinProbability = 0.1f;
+constexpr float kMaxProbability = 1.f - kMinProbability;
+constexpr float kMinCorrespondenceCost = 1.f - kMaxProbability;
+constexpr float kMaxCorrespondenceCost = 1.f - kMinProbability;
+
+// value_conversion_tables.cc:29-67
+class ValueConversionTables {
+ public:
+  const std::vector<float>* GetConversionTable(float unknown_result, float lower_bound,
+                                               float upper_bound) {
+    const auto key = std::make_tuple(unknown_result, lower_bound, upper_bound);
+    auto it = tables_.find(key);
+    if (it != tables_.end()) return it->second.get();
+    auto table = std::make_unique<std::vector<float>>();
+    table->reserve(65536);
+    const float scale = (upper_bound - lower_bound) / 32766.f;
+    for (uint32_t v = 0; v != 65536; ++v) {
+      const uint16 masked = static_cast<uint16>(v) & 0x7FFF;
+      table->push_back(masked == 0 ? unknown_result : masked * scale + (lower_bound - scale));
+    }
+    return tables_.emplace(key, std::move(table)).first->second.get();
+  }
+
+ private:
+  std::map<std::tuple<float, float, float>, std::unique_ptr<const std::vector<float>>> tables_;
+};
+
+enum class GridType { PROBABILITY_GRID, TSDF };
+
+class Grid2D {
+ public:
+  Grid2D(const MapLimits& limits, float min_correspondence_cost, float max_correspondence_cost,
+         ValueConversionTables* conversion_tables)
+      : limits_(limits),
+        correspondence_cost_cells_(
+            static_cast<size_t>(limits.cell_limits().num_x_cells) * limits.cell_limits().num_y_cells, 0),
+        min_correspondence_cost_(min_correspondence_cost),
+        max_correspondence_cost_(max_correspondence_cost),
+        value_to_correspondence_cost_table_(conversion_tables->GetConversionTable(
+            max_correspondence_cost, min_correspondence_cost, max_correspondence_cost)) {
+    CSM_CHECK(min_correspondence_cost_ < max_correspondence_cost_);
+  }
+  virtual ~Grid2D() {}
+  const MapLimits& limits() const { return limits_; }
+  float GetMinCorrespondenceCost() const { return min_correspondence_cost_; }
+  float GetMaxCorrespondenceCost() const { return max_correspondence_cost_; }
+  virtual GridType GetGridType() const = 0;
+  // Accessors the device path needs in place of per-cell GetCorrespondenceCost().
+  const std::vector<uint16>& correspondence_cost_cells() const { return correspondence_cost_cells_; }
+  std::vector<uint16>* mutable_correspondence_cost_cells() { return &correspondence_cost_cells_; }
+  const std::vector<float>& value_to_correspondence_cost_table() const {
+    return *value_to_correspondence_cost_table_;
+  }
+
+ private:
+  MapLimits limits_;
+  std::vector<uint16> correspondence_cost_cells_;
+  float min_correspondence_cost_;
+  float max_correspondence_cost_;
+  const std::vector<float>* value_to_correspondence_cost_table_;
+};
+
+class ProbabilityGrid : public Grid2D {
+ public:
+  ProbabilityGrid(const MapLimits& limits, ValueConversionTables* conversion_tables)
+      : Grid2D(limits, kMinCorrespondenceCost, kMaxCorrespondenceCost, conversion_tables) {}
+  GridType GetGridType() const override { return GridType::PROBABILITY_GRID; }
+};
+
+namespace scan_matching {
+namespace proto {
+// fast_correlative_scan_matcher_options_2d.proto
+class FastCorrelativeScanMatcherOptions2D {
+ public:
+  double linear_search_window() const { return linear_search_window_; }
+  double angular_search_window() const { return angular_search_window_; }
+  int branch_and_bound_depth() const { return branch_and_bound_depth_; }
+  void set_linear_search_window(double v) { linear_search_window_ = v; }
+  void set_angular_search_window(double v) { angular_search_window_ = v; }
+  void set_branch_and_bound_depth(int v) { branch_and_bound_depth_ = v; }
+
+ private:
+  double linear_search_window_ = 0.;
+  double angular_search_window_ = 0.;
+  int branch_and_bound_depth_ = 0;
+};
+// real_time_correlative_scan_matcher_options.proto
+class RealTimeCorrelativeScanMatcherOptions {
+ public:
+  double linear_search_window() const { return linear_search_window_; }
+  double angular_search_window() const { return angular_search_window_; }
+  double translation_delta_cost_weight() const { return translation_delta_cost_weight_; }
+  double rotation_delta_cost_weight() const { return rotation_delta_cost_weight_; }
+  void set_linear_search_window(double v) { linear_search_window_ = v; }
+  void set_angular_search_window(double v) { angular_search_window_ = v; }
+  void set_translation_delta_cost_weight(double v) { translation_delta_cost_weight_ = v; }
+  void set_rotation_delta_cost_weight(double v) { rotation_delta_cost_weight_ = v; }
+
+ private:
+  double linear_search_window_ = 0., angular_search_window_ = 0.;
+  double translation_delta_cost_weight_ = 0., rotation_delta_cost_weight_ = 0.;
+};
+}  // namespace proto
+}  // namespace scan_matching
+}  // namespace mapping
+}  // namespace cartographer
+
+#endif  // CSM_HOST_CARTOGRAPHER_COMPAT_H_

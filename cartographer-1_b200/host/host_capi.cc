@@ -1,0 +1,109 @@
+// Flat C entry points over the C++ host layer, for ctypes-driven parity tests and
+// bench.py.  Product code: goes through the reference-shaped classes and the C ABI
+// only; never touches oracle/.
+#include <cstring>
+#include <memory>
+
+#include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+
+using namespace cartographer;
+using mapping::scan_matching::DeviceContext;
+using mapping::scan_matching::FastCorrelativeScanMatcher2D;
+
+extern "C" {
+
+struct csmh_result2d {
+  int32_t found;
+  int32_t scan_index, x_index_offset, y_index_offset;
+  float score;
+  int32_t tie_resolution;
+  double pose_x, pose_y, pose_theta;
+  uint64_t candidates_scored;
+};
+
+void* csmh_context_create(int device) {
+  if (csm_device_count() <= device) return nullptr;
+  return new DeviceContext(device);
+}
+void csmh_context_destroy(void* c) { delete static_cast<DeviceContext*>(c); }
+void* csmh_context_raw(void* c) { return static_cast<DeviceContext*>(c)->get(); }
+
+struct GridHolder {
+  mapping::ValueConversionTables tables;
+  std::unique_ptr<mapping::ProbabilityGrid> grid;
+};
+
+void* csmh_grid_create(const uint16_t* cells, int nx, int ny, double res, double max_x,
+                       double max_y) {
+  GridHolder* h = new GridHolder;
+  h->grid.reset(new mapping::ProbabilityGrid(
+      mapping::MapLimits(res, transform::Vector2d(max_x, max_y), mapping::CellLimits(nx, ny)),
+      &h->tables));
+  std::memcpy(h->grid->mutable_correspondence_cost_cells()->data(), cells,
+              sizeof(uint16_t) * static_cast<size_t>(nx) * ny);
+  return h;
+}
+void csmh_grid_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+
+void csmh_quantization_table(void* g, uint8_t* out65536) {
+  const std::vector<uint8_t> t =
+      mapping::scan_matching::ComputeQuantizationTable(*static_cast<GridHolder*>(g)->grid);
+  std::memcpy(out65536, t.data(), 65536);
+}
+
+void* csmh_matcher_create(void* ctx, void* grid, double linear_window, double angular_window,
+                          int depth) {
+  mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions2D o;
+  o.set_linear_search_window(linear_window);
+  o.set_angular_search_window(angular_window);
+  o.set_branch_and_bound_depth(depth);
+  return new FastCorrelativeScanMatcher2D(*static_cast<GridHolder*>(grid)->grid, o,
+                                          static_cast<DeviceContext*>(ctx));
+}
+void csmh_matcher_destroy(void* m) { delete static_cast<FastCorrelativeScanMatcher2D*>(m); }
+const void* csmh_matcher_stack(void* m) {
+  return static_cast<FastCorrelativeScanMatcher2D*>(m)->stack();
+}
+
+int csmh_matcher_level(void* ctx, void* m, int level, uint8_t* out, int* wide_x, int* wide_y) {
+  return csm_stack2d_level(static_cast<DeviceContext*>(ctx)->get(),
+                           static_cast<FastCorrelativeScanMatcher2D*>(m)->stack(), level, out,
+                           wide_x, wide_y);
+}
+
+// n searches; matcher[i] handles, full[i] flag, init_pose[3i..] (x, y, theta) for
+// local searches, clouds concatenated in xyz with offsets[n+1] (in points).
+int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* full,
+                     const double* init_pose, const float* xyz, const int64_t* offsets,
+                     const float* min_score, csmh_result2d* out) {
+  std::vector<sensor::PointCloud> clouds(n);
+  std::vector<std::pair<const FastCorrelativeScanMatcher2D*, FastCorrelativeScanMatcher2D::Query>> q(n);
+  for (int i = 0; i < n; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    q[i].first = static_cast<const FastCorrelativeScanMatcher2D*>(matchers[i]);
+    q[i].second.point_cloud = &clouds[i];
+    q[i].second.full_submap = full[i] != 0;
+    q[i].second.initial_pose_estimate = transform::Rigid2d(
+        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
+    q[i].second.min_score = min_score[i];
+  }
+  const auto answers =
+      FastCorrelativeScanMatcher2D::MatchBatch(static_cast<DeviceContext*>(ctx), q);
+  for (int i = 0; i < n; ++i) {
+    const auto& a = answers[i];
+    out[i].found = a.found ? 1 : 0;
+    out[i].scan_index = a.best_candidate.scan_index;
+    out[i].x_index_offset = a.best_candidate.x_index_offset;
+    out[i].y_index_offset = a.best_candidate.y_index_offset;
+    out[i].score = a.score;
+    out[i].tie_resolution = a.tie_resolution;
+    out[i].pose_x = a.pose_estimate.translation().x();
+    out[i].pose_y = a.pose_estimate.translation().y();
+    out[i].pose_theta = a.pose_estimate.rotation().angle();
+    out[i].candidates_scored = a.candidates_scored;
+  }
+  return 0;
+}
+
+}  // extern "C"

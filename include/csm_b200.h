@@ -62,6 +62,8 @@ int csm_device_count(void);
 int csm_ctx_create(int device, csm_ctx** out);
 void csm_ctx_destroy(csm_ctx* ctx);
 int csm_ctx_synchronize(csm_ctx* ctx);
+/* The context's cudaStream_t, so a caller can record its own CUDA events on it. */
+void* csm_ctx_stream(csm_ctx* ctx);
 
 /* ---- PrecomputationGridStack2D (FCSM2D.cc:91-186, FCSM2D.h:49-109) ----------
  * cells:  the Grid2D correspondence-cost cells, row-major, flat = num_x*y + x
@@ -163,6 +165,8 @@ typedef struct {
   double max_x, max_y, resolution;
   int32_t linear_bound;
   const double* penalty;
+  float out_of_bounds_probability; /* kMinProbability for a ProbabilityGrid            */
+                                   /* (cartographer/mapping/2d/probability_grid.cc:78-82)*/
 } csm_rt_job2d;
 
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,

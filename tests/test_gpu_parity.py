@@ -1,0 +1,113 @@
+"""GPU parity tests proper: the CUDA path through the C ABI against the oracle."""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _tiny_grid(seed, nx, ny):
+    rng = np.random.default_rng(seed)
+    cells = rng.integers(1, 32768, size=(ny, nx)).astype(np.uint16)
+    cells[rng.random((ny, nx)) < 0.25] = 0
+    return cells
+
+
+@pytest.mark.parametrize("nx,ny,depth", [(250, 250, 4), (4, 4, 8), (1, 1, 3), (37, 5, 7),
+                                         (400, 400, 7), (129, 257, 6)])
+def test_stack_bytes_identical(csm, gpu_ctx, nx, ny, depth):
+    cells = _tiny_grid(nx * 1000 + ny, nx, ny)
+    og = ob.OracleGrid(cells, 0.05, 1.0, 1.0)
+    om = ob.OracleFCSM2D(og, 1.0, 0.1, depth)
+    g = csm.Grid(cells, 0.05, 1.0, 1.0)
+    m = csm.Matcher(gpu_ctx, g, 1.0, 0.1, depth)
+    for lvl in range(depth):
+        a, b = om.level(lvl), m.level(lvl)
+        assert a.shape == b.shape
+        assert np.array_equal(a, b), "level %d differs" % lvl
+
+
+def _compare(r_o, r_g):
+    assert r_g.found == r_o.found
+    if r_o.found:
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
+        assert r_g.pose_x == r_o.pose_x and r_g.pose_y == r_o.pose_y
+        assert r_g.pose_theta == r_o.pose_theta
+
+
+@pytest.mark.parametrize("size,depth,min_score", [(200, 5, 0.5), (200, 5, 0.1), (400, 7, 0.6),
+                                                  (300, 3, 0.3)])
+def test_match_full_submap_bit_exact(csm, gpu_ctx, size, depth, min_score):
+    w = synth.World(size, size, seed=size + depth)
+    other = synth.World(size, size, seed=size + depth + 1)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    om = ob.OracleFCSM2D(og, 7.0, np.deg2rad(30.0), depth)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    m = csm.Matcher(gpu_ctx, g, 7.0, np.deg2rad(30.0), depth)
+    clouds = []
+    for i in range(6):
+        _, pts = synth.make_scan(w if i % 2 == 0 else other, 40 + i, max_range=8.0)
+        clouds.append(pts)
+    res = csm.match_batch(gpu_ctx, [m] * len(clouds), clouds, [min_score] * len(clouds))
+    for pts, r_g in zip(clouds, res):
+        _compare(om.match(pts, min_score), r_g)
+
+
+def test_match_local_window_bit_exact(csm, gpu_ctx):
+    w = synth.World(300, 300, seed=77)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    om = ob.OracleFCSM2D(og, 3.0, 0.6, 6)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    m = csm.Matcher(gpu_ctx, g, 3.0, 0.6, 6)
+    rng = np.random.default_rng(5)
+    clouds, inits = [], []
+    for i in range(8):
+        pose, pts = synth.make_scan(w, 90 + i, max_range=8.0)
+        clouds.append(pts)
+        inits.append((pose[0] + rng.uniform(-1, 1), pose[1] + rng.uniform(-1, 1),
+                      pose[2] + rng.uniform(-0.3, 0.3)))
+    res = csm.match_batch(gpu_ctx, [m] * 8, clouds, [0.4] * 8, initial=inits)
+    for pts, init, r_g in zip(clouds, inits, res):
+        _compare(om.match(pts, 0.4, initial=init), r_g)
+
+
+def test_tie_cases_follow_reference_order(csm, gpu_ctx):
+    # ConstraintBuilder2DTest shape: empty grid, min_score 0 -> every candidate ties.
+    cells = np.zeros((110, 100), dtype=np.uint16)
+    og = ob.OracleGrid(cells, 1.0, 2.0, 3.0)
+    g = csm.Grid(cells, 1.0, 2.0, 3.0)
+    pts = np.array([[0.1, 0.2, 0.3]], dtype=np.float32)
+    for depth in (1, 3, 7):
+        om = ob.OracleFCSM2D(og, 7.0, np.deg2rad(30.0), depth)
+        m = csm.Matcher(gpu_ctx, g, 7.0, np.deg2rad(30.0), depth)
+        r_g = csm.match_batch(gpu_ctx, [m, m], [pts, pts], [0.0, 0.0],
+                              initial=[None, (4.0, 5.0, 0.0)])
+        _compare(om.match(pts, 0.0), r_g[0])
+        _compare(om.match(pts, 0.0, initial=(4.0, 5.0, 0.0)), r_g[1])
+    # symmetric corridor: two parallel walls, many equal-score poses
+    cells = np.zeros((200, 200), dtype=np.uint16)
+    wall = synth.probability_to_value(np.float32(0.8))
+    cells[60:62, :] = wall
+    cells[140:142, :] = wall
+    og = ob.OracleGrid(cells, 0.05, 5.0, 5.0)
+    g = csm.Grid(cells, 0.05, 5.0, 5.0)
+    om = ob.OracleFCSM2D(og, 7.0, np.deg2rad(30.0), 6)
+    m = csm.Matcher(gpu_ctx, g, 7.0, np.deg2rad(30.0), 6)
+    ys = np.linspace(-3, 3, 40, dtype=np.float32)
+    pts = np.concatenate([np.stack([np.full(40, 2.0, np.float32), ys, np.zeros(40, np.float32)], 1),
+                          np.stack([np.full(40, -2.0, np.float32), ys, np.zeros(40, np.float32)], 1)])
+    r_g = csm.match_batch(gpu_ctx, [m], [pts], [0.3])
+    _compare(om.match(pts, 0.3), r_g[0])
+
+
+def test_empty_cloud_is_not_found(csm, gpu_ctx):
+    w = synth.World(100, 100, seed=3)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    m = csm.Matcher(gpu_ctx, g, 7.0, 0.5, 4)
+    _, pts = synth.make_scan(w, 1, max_range=4.0)
+    res = csm.match_batch(gpu_ctx, [m, m], [np.zeros((0, 3), np.float32), pts], [0.1, 0.1])
+    assert res[0].found == 0
