@@ -91,6 +91,13 @@ def host():
                                      C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.csmh_match_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), i32p, f64p, f32p,
                                    i64p, f32p, C.POINTER(Result2D)]
+    L.csmh_batch_create.restype = C.c_void_p
+    L.csmh_batch_create.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), i32p, f64p, f32p,
+                                    i64p, f32p]
+    L.csmh_batch_run.argtypes = [C.c_void_p]
+    L.csmh_batch_fetch.argtypes = [C.c_void_p, C.POINTER(Result2D)]
+    L.csmh_batch_destroy.argtypes = [C.c_void_p]
+    L.csmh_matcher_rebuild_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     _host = L
     return L
 
@@ -154,8 +161,7 @@ class Matcher:
             self.h = None
 
 
-def match_batch(ctx, matchers, clouds, min_scores, initial=None):
-    """initial[i] = None -> MatchFullSubmap, else (x, y, theta) -> Match."""
+def _pack(matchers, clouds, min_scores, initial):
     n = len(clouds)
     handles = (C.c_void_p * n)(*[m.h for m in matchers])
     full = np.zeros(n, dtype=np.int32)
@@ -170,8 +176,40 @@ def match_batch(ctx, matchers, clouds, min_scores, initial=None):
         offsets[i + 1] = offsets[i] + len(c)
     xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
                                                for c in clouds], axis=0), dtype=np.float32)
+    return n, handles, full, init.reshape(-1), xyz, offsets, \
+        np.ascontiguousarray(min_scores, dtype=np.float32)
+
+
+def match_batch(ctx, matchers, clouds, min_scores, initial=None):
+    """initial[i] = None -> MatchFullSubmap, else (x, y, theta) -> Match."""
+    n, handles, full, init, xyz, offsets, ms = _pack(matchers, clouds, min_scores, initial)
     out = (Result2D * n)()
-    rc = host().csmh_match_batch(ctx.h, n, handles, full, init.reshape(-1), xyz, offsets,
-                                 np.ascontiguousarray(min_scores, dtype=np.float32), out)
+    rc = host().csmh_match_batch(ctx.h, n, handles, full, init, xyz, offsets, ms, out)
     assert rc == 0
     return out
+
+
+class PreparedBatch:
+    """Host parameters computed and inputs uploaded; run() is asynchronous."""
+
+    def __init__(self, ctx, matchers, clouds, min_scores, initial=None):
+        self.n, handles, full, init, xyz, offsets, ms = _pack(matchers, clouds, min_scores, initial)
+        self.keep = (matchers, ctx)
+        self.h = host().csmh_batch_create(ctx.h, self.n, handles, full, init, xyz, offsets, ms)
+        self.h2d_bytes = xyz.nbytes
+
+    def run(self):
+        host().csmh_batch_run(self.h)
+
+    def fetch(self):
+        out = (Result2D * self.n)()
+        host().csmh_batch_fetch(self.h, out)
+        return out
+
+    def close(self):
+        if self.h:
+            host().csmh_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()

@@ -103,6 +103,8 @@ void csm_ctx_destroy(csm_ctx* c) {
   c->tmp1.release();
   c->tmp2.release();
   c->pin0.release();
+  c->frontier[0].release();
+  c->frontier[1].release();
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);

@@ -66,6 +66,16 @@ struct csm_ctx {
   // scratch for csm_discretize2d / stack builds
   csm::DevBuf tmp0, tmp1, tmp2;
   csm::PinBuf pin0;
+  // Branch-and-bound frontier ping-pong buffers, shared by every batch that runs on
+  // this context (runs are stream-ordered, the frontier is pure scratch).
+  csm::DevBuf frontier[2];
+  unsigned long long frontier_cap = 0;  // nodes per buffer
+  // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
+  static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2
+  bool profiling = false;
+  double phase_ms[kPhases] = {0, 0, 0, 0, 0};
+  double phase_scored[kPhases] = {0, 0, 0, 0, 0};  // candidate scores evaluated per phase
+  int profiled_runs = 0;
 };
 
 struct csm_stack2d {

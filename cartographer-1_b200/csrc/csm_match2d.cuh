@@ -46,7 +46,8 @@ struct JobState {
   unsigned int tie_count;       // phase 2: contenders in the winning group that hold an S*-leaf
   unsigned int total;           // top-level candidates of this job
   unsigned int pad;
-  unsigned long long scored;    // candidate scores evaluated
+  unsigned long long scored;    // candidate scores evaluated (all phases)
+  unsigned long long scored_phase[4];  // score_top, dive, expand, phase 2
 };
 
 // Branch-and-bound node: 16 bytes.
@@ -132,8 +133,7 @@ struct csm_batch2d {
   csm::ScanInfo* scans = nullptr;      // total_scans
   float* top_scores = nullptr;         // total_cand
   csm::JobState* state = nullptr;      // num_jobs
-  csm::Node* frontier[2] = {nullptr, nullptr};
-  unsigned long long frontier_cap = 0;
+  unsigned long long frontier_want = 0;  // nodes per frontier buffer this batch asks for
   csm::Contender* contenders = nullptr;
   unsigned int contender_cap = 0;
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
@@ -143,6 +143,7 @@ struct csm_batch2d {
   void* pinned = nullptr;              // staging for uploads / results
   size_t pinned_bytes = 0;
   bool uploaded = false, ran = false;
+  std::vector<cudaEvent_t> prof_events;  // kPhases + 1 events of the last profiled run
 };
 
 #endif  // CSM_MATCH2D_CUH_

@@ -1,5 +1,6 @@
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -115,16 +116,21 @@ bool FastCorrelativeScanMatcher2D::MatchFullSubmap(const sensor::PointCloud& poi
 }
 
 std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::MatchBatch(
-    DeviceContext* context,
-    const std::vector<std::pair<const FastCorrelativeScanMatcher2D*, Query>>& queries) {
+    DeviceContext* context, const QueryList& queries) {
+  if (queries.empty()) return {};
+  Batch batch(context, queries);
+  batch.Run();
+  return batch.Fetch();
+}
+
+FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryList& queries)
+    : context_(context) {
   const size_t n = queries.size();
-  std::vector<Answer> answers(n);
-  if (n == 0) return answers;
-  std::vector<SearchParameters> params;
-  std::vector<transform::Rigid2d> initial(n);
+  initial_.resize(n);
   std::vector<std::vector<float>> xyz(n), quats(n);
   std::vector<csm_job2d> jobs(n);
-  params.reserve(n);
+  std::vector<double> lattice_estimate(n);
+  params_.reserve(n);
   for (size_t i = 0; i != n; ++i) {
     const FastCorrelativeScanMatcher2D& m = *queries[i].first;
     const Query& q = queries[i].second;
@@ -133,23 +139,25 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
     if (q.full_submap) {
       // Window around the submap centre that includes it fully
       // (reference: fast_correlative_scan_matcher_2d.cc:215-222).
-      params.emplace_back(1e6 * res, M_PI, *q.point_cloud, res);
+      params_.emplace_back(1e6 * res, M_PI, *q.point_cloud, res);
       const double half_res = 0.5 * res;
-      initial[i] = transform::Rigid2d::Translation(transform::Vector2d(
+      initial_[i] = transform::Rigid2d::Translation(transform::Vector2d(
           m.limits_.max().x() - half_res * m.limits_.cell_limits().num_y_cells,
           m.limits_.max().y() - half_res * m.limits_.cell_limits().num_x_cells));
     } else {
-      params.emplace_back(m.options_.linear_search_window(), m.options_.angular_search_window(),
-                          *q.point_cloud, res);
-      initial[i] = q.initial_pose_estimate;
+      params_.emplace_back(m.options_.linear_search_window(), m.options_.angular_search_window(),
+                           *q.point_cloud, res);
+      initial_[i] = q.initial_pose_estimate;
     }
-    const SearchParameters& sp = params.back();
+    const SearchParameters& sp = params_.back();
     xyz[i].resize(3 * q.point_cloud->size());
+    double reach = 0.;
     for (size_t p = 0; p != q.point_cloud->size(); ++p) {
       const sensor::Vector3f& v = (*q.point_cloud)[p].position;
       xyz[i][3 * p] = v.x();
       xyz[i][3 * p + 1] = v.y();
       xyz[i][3 * p + 2] = v.z();
+      reach = std::max(reach, std::hypot(static_cast<double>(v.x()), static_cast<double>(v.y())));
     }
     quats[i] = sp.ScanQuaternionTable();
     csm_job2d& job = jobs[i];
@@ -160,12 +168,12 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
     job.num_scans = sp.num_scans;
     job.scan_quat = quats[i].data();
     // Rotation2Dd -> Rotation2Df -> AngleAxisf -> Quaternionf (reference :235-239)
-    const float yaw = static_cast<float>(initial[i].rotation().angle());
+    const float yaw = static_cast<float>(initial_[i].rotation().angle());
     const float half_yaw = 0.5f * yaw;
     job.init_quat_w = std::cos(half_yaw);
     job.init_quat_s = std::sin(half_yaw);
-    job.init_tx = static_cast<float>(initial[i].translation().x());
-    job.init_ty = static_cast<float>(initial[i].translation().y());
+    job.init_tx = static_cast<float>(initial_[i].translation().x());
+    job.init_ty = static_cast<float>(initial_[i].translation().y());
     job.max_x = m.limits_.max().x();
     job.max_y = m.limits_.max().y();
     job.resolution = res;
@@ -173,25 +181,63 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
     job.min_score = q.min_score;
     job.score_offset = m.min_score_;
     job.score_scale = (m.max_score_ - m.min_score_) / 255.f;
+    // Rough size of the lowest-resolution lattice, to bound the device footprint.
+    const double step = static_cast<double>(1 << (m.options_.branch_and_bound_depth() - 1));
+    const double ext = 2. * reach / res + 4.;
+    const double wx = std::min(2. * job.linear_bound, m.limits_.cell_limits().num_x_cells + ext);
+    const double wy = std::min(2. * job.linear_bound, m.limits_.cell_limits().num_y_cells + ext);
+    lattice_estimate[i] = sp.num_scans * (wx / step + 1.) * (wy / step + 1.);
   }
+  // Split into device batches of bounded footprint.
+  constexpr double kLatticeBudget = 48e6;
+  constexpr size_t kMaxJobs = 4096;
+  size_t begin = 0;
+  while (begin < n) {
+    size_t end = begin;
+    double sum = 0.;
+    while (end < n && end - begin < kMaxJobs && (end == begin || sum + lattice_estimate[end] <= kLatticeBudget)) {
+      sum += lattice_estimate[end];
+      ++end;
+    }
+    csm_batch2d* device_batch = nullptr;
+    CheckOk(csm_batch2d_upload(context_->get(), jobs.data() + begin, static_cast<int>(end - begin),
+                               &device_batch),
+            "csm_batch2d_upload");
+    chunks_.emplace_back(begin, end);
+    device_batches_.push_back(device_batch);
+    begin = end;
+  }
+}
+
+FastCorrelativeScanMatcher2D::Batch::~Batch() {
+  for (csm_batch2d* b : device_batches_) csm_batch2d_destroy(context_->get(), b);
+}
+
+void FastCorrelativeScanMatcher2D::Batch::Run() {
+  for (csm_batch2d* b : device_batches_) CheckOk(csm_batch2d_run(context_->get(), b), "csm_batch2d_run");
+}
+
+std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::Fetch() {
+  const size_t n = initial_.size();
   std::vector<csm_result2d> results(n);
-  CheckOk(csm_match2d_batch(context->get(), jobs.data(), static_cast<int>(n), results.data()),
-          "csm_match2d_batch");
+  for (size_t c = 0; c != chunks_.size(); ++c)
+    CheckOk(csm_batch2d_fetch(context_->get(), device_batches_[c], results.data() + chunks_[c].first),
+            "csm_batch2d_fetch");
+  std::vector<Answer> answers(n);
   for (size_t i = 0; i != n; ++i) {
     const csm_result2d& r = results[i];
     Answer& a = answers[i];
     a.found = r.found == 1;
     a.candidates_scored = r.candidates_scored;
     a.tie_resolution = r.tie_resolution;
-    a.best_candidate =
-        Candidate2D(r.scan_index, r.x_index_offset, r.y_index_offset, params[i]);
+    a.best_candidate = Candidate2D(r.scan_index, r.x_index_offset, r.y_index_offset, params_[i]);
     a.best_candidate.score = r.score;
     a.score = r.score;
     if (a.found) {  // reference :253-260
       a.pose_estimate = transform::Rigid2d(
-          transform::Vector2d(initial[i].translation().x() + a.best_candidate.x,
-                              initial[i].translation().y() + a.best_candidate.y),
-          initial[i].rotation() * transform::Rotation2Dd(a.best_candidate.orientation));
+          transform::Vector2d(initial_[i].translation().x() + a.best_candidate.x,
+                              initial_[i].translation().y() + a.best_candidate.y),
+          initial_[i].rotation() * transform::Rotation2Dd(a.best_candidate.orientation));
     }
   }
   return answers;

@@ -78,10 +78,32 @@ class FastCorrelativeScanMatcher2D {
     uint64_t candidates_scored = 0;
     int tie_resolution = 0;
   };
+  using QueryList = std::vector<std::pair<const FastCorrelativeScanMatcher2D*, Query>>;
   // All queries may target different matchers on the same device context.
-  static std::vector<Answer> MatchBatch(
-      DeviceContext* context,
-      const std::vector<std::pair<const FastCorrelativeScanMatcher2D*, Query>>& queries);
+  static std::vector<Answer> MatchBatch(DeviceContext* context, const QueryList& queries);
+
+  // The same in three steps, so that a caller can keep a prepared batch resident on
+  // the device and overlap host work: the constructor computes the search
+  // parameters (libm) and uploads; Run() enqueues every kernel on the context's
+  // stream without waiting; Fetch() waits, copies the results back and converts the
+  // winning candidates to poses.  Run() may be repeated.
+  class Batch {
+   public:
+    Batch(DeviceContext* context, const QueryList& queries);
+    ~Batch();
+    Batch(const Batch&) = delete;
+    Batch& operator=(const Batch&) = delete;
+    void Run();
+    std::vector<Answer> Fetch();
+    size_t size() const { return initial_.size(); }
+
+   private:
+    DeviceContext* context_;
+    std::vector<SearchParameters> params_;
+    std::vector<transform::Rigid2d> initial_;
+    std::vector<std::pair<size_t, size_t>> chunks_;  // [begin, end) job ranges
+    std::vector<csm_batch2d*> device_batches_;
+  };
 
   const csm_stack2d* stack() const { return stack_; }
   const MapLimits& limits() const { return limits_; }

@@ -71,26 +71,14 @@ int csmh_matcher_level(void* ctx, void* m, int level, uint8_t* out, int* wide_x,
                            wide_x, wide_y);
 }
 
-// n searches; matcher[i] handles, full[i] flag, init_pose[3i..] (x, y, theta) for
-// local searches, clouds concatenated in xyz with offsets[n+1] (in points).
-int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* full,
-                     const double* init_pose, const float* xyz, const int64_t* offsets,
-                     const float* min_score, csmh_result2d* out) {
-  std::vector<sensor::PointCloud> clouds(n);
-  std::vector<std::pair<const FastCorrelativeScanMatcher2D*, FastCorrelativeScanMatcher2D::Query>> q(n);
-  for (int i = 0; i < n; ++i) {
-    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
-      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
-    q[i].first = static_cast<const FastCorrelativeScanMatcher2D*>(matchers[i]);
-    q[i].second.point_cloud = &clouds[i];
-    q[i].second.full_submap = full[i] != 0;
-    q[i].second.initial_pose_estimate = transform::Rigid2d(
-        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
-    q[i].second.min_score = min_score[i];
-  }
-  const auto answers =
-      FastCorrelativeScanMatcher2D::MatchBatch(static_cast<DeviceContext*>(ctx), q);
-  for (int i = 0; i < n; ++i) {
+struct BatchHolder {
+  std::vector<sensor::PointCloud> clouds;
+  std::unique_ptr<FastCorrelativeScanMatcher2D::Batch> batch;
+};
+
+static void Convert(const std::vector<FastCorrelativeScanMatcher2D::Answer>& answers,
+                    csmh_result2d* out) {
+  for (size_t i = 0; i < answers.size(); ++i) {
     const auto& a = answers[i];
     out[i].found = a.found ? 1 : 0;
     out[i].scan_index = a.best_candidate.scan_index;
@@ -103,7 +91,53 @@ int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* ful
     out[i].pose_theta = a.pose_estimate.rotation().angle();
     out[i].candidates_scored = a.candidates_scored;
   }
+}
+
+// n searches; matcher[i] handles, full[i] flag, init_pose[3i..] (x, y, theta) for
+// local searches, clouds concatenated in xyz with offsets[n+1] (in points).
+// Prepares (host libm work + upload) without running.
+void* csmh_batch_create(void* ctx, int n, void* const* matchers, const int32_t* full,
+                        const double* init_pose, const float* xyz, const int64_t* offsets,
+                        const float* min_score) {
+  BatchHolder* h = new BatchHolder;
+  h->clouds.resize(n);
+  FastCorrelativeScanMatcher2D::QueryList q(n);
+  for (int i = 0; i < n; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      h->clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    q[i].first = static_cast<const FastCorrelativeScanMatcher2D*>(matchers[i]);
+    q[i].second.point_cloud = &h->clouds[i];
+    q[i].second.full_submap = full[i] != 0;
+    q[i].second.initial_pose_estimate = transform::Rigid2d(
+        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
+    q[i].second.min_score = min_score[i];
+  }
+  h->batch.reset(new FastCorrelativeScanMatcher2D::Batch(static_cast<DeviceContext*>(ctx), q));
+  return h;
+}
+void csmh_batch_run(void* b) { static_cast<BatchHolder*>(b)->batch->Run(); }
+void csmh_batch_fetch(void* b, csmh_result2d* out) {
+  Convert(static_cast<BatchHolder*>(b)->batch->Fetch(), out);
+}
+void csmh_batch_destroy(void* b) { delete static_cast<BatchHolder*>(b); }
+
+int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* full,
+                     const double* init_pose, const float* xyz, const int64_t* offsets,
+                     const float* min_score, csmh_result2d* out) {
+  if (n == 0) return 0;
+  void* b = csmh_batch_create(ctx, n, matchers, full, init_pose, xyz, offsets, min_score);
+  csmh_batch_run(b);
+  csmh_batch_fetch(b, out);
+  csmh_batch_destroy(b);
   return 0;
+}
+
+// Rebuilds the matcher's precomputation stack from cells already in device memory
+// (asynchronous on the context's stream).
+int csmh_matcher_rebuild_dev(void* ctx, void* m, const uint16_t* cells_dev) {
+  return csm_stack2d_rebuild_dev(
+      static_cast<DeviceContext*>(ctx)->get(),
+      const_cast<csm_stack2d*>(static_cast<FastCorrelativeScanMatcher2D*>(m)->stack()), cells_dev);
 }
 
 }  // extern "C"

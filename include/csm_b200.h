@@ -64,6 +64,13 @@ void csm_ctx_destroy(csm_ctx* ctx);
 int csm_ctx_synchronize(csm_ctx* ctx);
 /* The context's cudaStream_t, so a caller can record its own CUDA events on it. */
 void* csm_ctx_stream(csm_ctx* ctx);
+/* Per-phase CUDA-event timing of csm_batch2d_run on the context's own stream
+ * (measurement aid for bench.py).  Phases: 0 rotate/discretise, 1 lowest-resolution
+ * scoring, 2 greedy dive, 3 level-synchronous expansion, 4 tie-order phase.
+ * phase_ms5 / phase_scored5: accumulated milliseconds and candidate scores evaluated
+ * per phase since profiling was switched on; runs: number of profiled batch runs. */
+int csm_ctx_set_profiling(csm_ctx* ctx, int enabled);
+int csm_ctx_get_profile(csm_ctx* ctx, double* phase_ms5, double* phase_scored5, int* runs);
 
 /* ---- PrecomputationGridStack2D (FCSM2D.cc:91-186, FCSM2D.h:49-109) ----------
  * cells:  the Grid2D correspondence-cost cells, row-major, flat = num_x*y + x
