@@ -78,11 +78,34 @@ struct csm_ctx {
   int profiled_runs = 0;
 };
 
+namespace csm {
+// Device-resident description of one precomputation stack (what the kernels read).
+//
+// level[l]: the reference's PrecomputationGrid2D::cells_ of width 2^l, row-major bytes.
+// quad[l]:  the same level re-laid out for the matcher ("quad-phase" layout): one
+//           uint32 per window start (x, y), x in [-2s+1, num_x-1], s = 2^l, holding the
+//           four values a branch-and-bound parent needs for its children in generation
+//           order: byte0 = G(x, y), byte1 = G(x, y+s), byte2 = G(x+s, y), byte3 =
+//           G(x+s, y+s).  Words are grouped by phase (u mod 2s, v mod 2s) with
+//           u = x + 2s - 1, v = y + 2s - 1, so that parents 2s cells apart -- neighbours
+//           on the search lattice -- sit in neighbouring words:
+//           index = ((v%2s * 2s + u%2s) * jn + v/2s) * in + u/2s.
+struct StackDev {
+  int num_x, num_y, depth, pad;
+  const uint8_t* level[CSM_MAX_DEPTH];
+  const uint32_t* quad[CSM_MAX_DEPTH];
+  int in[CSM_MAX_DEPTH], jn[CSM_MAX_DEPTH];
+};
+}  // namespace csm
+
 struct csm_stack2d {
   int device = 0;
   int num_x = 0, num_y = 0, depth = 0;
   uint8_t* base = nullptr;                // one allocation for all levels
   size_t level_off[CSM_MAX_DEPTH] = {0};  // byte offset of level i inside base
+  size_t quad_off[CSM_MAX_DEPTH] = {0};   // byte offset of quad level i inside base
+  csm::StackDev host_view;                // copy of *dev
+  csm::StackDev* dev = nullptr;           // device-resident descriptor
   size_t bytes = 0;
   uint8_t* q_lut_dev = nullptr;  // 65536 bytes
 };

@@ -9,7 +9,7 @@ namespace csm {
 // One (node, submap) search as the kernels see it.  All offsets index the batch's
 // shared device arrays.
 struct JobDev {
-  const uint8_t* level[CSM_MAX_DEPTH];  // precomputation level i, row-major bytes
+  const StackDev* sd;                   // precomputation stack (device descriptor)
   int num_x, num_y;                     // grid cell limits
   int depth;                            // branch_and_bound_depth
   int n;                                // points per scan
@@ -21,6 +21,8 @@ struct JobDev {
   long long scan_off;                   // index into per-scan arrays (S)
   long long cand_off;                   // index into top-level score array
   long long cand_cap;                   // reserved top-level candidates
+  long long alive_off;                  // uint32 index of this job's alive bitmaps
+  int nx_cap, ny_cap;                   // upper bound of the lowest-resolution lattice per scan
   float q0w, q0s;                       // initial-yaw quaternion (w, z)
   float tx, ty;                         // fp32 initial translation
   double max_x, max_y, res;             // MapLimits
@@ -136,6 +138,8 @@ struct csm_batch2d {
   unsigned long long frontier_want = 0;  // nodes per frontier buffer this batch asks for
   csm::Contender* contenders = nullptr;
   unsigned int contender_cap = 0;
+  unsigned int* alive = nullptr;       // dense-level alive bitmaps
+  long long total_alive = 0;           // uint32 words
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
   void* arena = nullptr;               // single cudaMalloc backing all of the above

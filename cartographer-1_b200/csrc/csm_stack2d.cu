@@ -15,6 +15,8 @@
 //
 // Data layout in HBM: one allocation per stack; level i is a dense row-major
 // (num_x + 2^i - 1) x (num_y + 2^i - 1) byte image at a 256-byte aligned offset.
+#include <cstring>
+
 #include "csm_internal.cuh"
 
 namespace {
@@ -62,6 +64,33 @@ k_stack_level_up(const uint8_t* __restrict__ in, int in_w, int in_h, uint8_t* __
   out[static_cast<size_t>(Y) * out_w + X] = static_cast<uint8_t>(max(a, b));
 }
 
+// Byte level -> quad-phase layout (see StackDev).  One thread per output word, so the
+// 4-byte stores are coalesced; the four byte taps are strided gathers served by L2.
+__global__ void __launch_bounds__(kThreads)
+k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, uint32_t* __restrict__ out,
+              int log2s, int in, int jn) {
+  const int two_s = 2 << log2s, s = 1 << log2s;
+  const size_t total = static_cast<size_t>(two_s) * two_s * in * jn;
+  const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
+  for (size_t idx = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; idx < total;
+       idx += stride) {
+    const int i = static_cast<int>(idx % in);
+    size_t r = idx / in;
+    const int j = static_cast<int>(r % jn);
+    r /= jn;
+    const int pu = static_cast<int>(r % two_s), pv = static_cast<int>(r / two_s);
+    // u = x + 2s - 1; the level's wide index of window start x is X = x + s - 1 = u - s.
+    const int X = i * two_s + pu - s, Y = j * two_s + pv - s;
+    auto tap = [&](int x, int y) -> uint32_t {
+      if (static_cast<unsigned>(x) >= static_cast<unsigned>(wide_x) ||
+          static_cast<unsigned>(y) >= static_cast<unsigned>(wide_y))
+        return 0u;
+      return lvl[static_cast<size_t>(y) * wide_x + x];
+    };
+    out[idx] = tap(X, Y) | (tap(X, Y + s) << 8) | (tap(X + s, Y) << 16) | (tap(X + s, Y + s) << 24);
+  }
+}
+
 int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const size_t n = static_cast<size_t>(s->num_x) * s->num_y;
   int blocks = static_cast<int>(std::min<size_t>((n / 4 + kThreads - 1) / kThreads + 1,
@@ -76,6 +105,16 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     dim3 grid((out_w + block.x - 1) / block.x, (out_h + block.y - 1) / block.y);
     k_stack_level_up<<<grid, block, 0, ctx->stream>>>(s->base + s->level_off[i], in_w, in_h,
                                                       s->base + s->level_off[i + 1], out_w, out_h, h);
+  }
+  for (int i = 0; i < s->depth; ++i) {
+    const int w = s->num_x + (1 << i) - 1, hgt = s->num_y + (1 << i) - 1;
+    const int in = s->host_view.in[i], jn = s->host_view.jn[i];
+    const size_t total = static_cast<size_t>(4) * (1u << (2 * i)) * in * jn;
+    const int qblocks = static_cast<int>(
+        std::min<size_t>((total + kThreads - 1) / kThreads, static_cast<size_t>(ctx->num_sms) * 16));
+    k_stack_quads<<<qblocks, kThreads, 0, ctx->stream>>>(
+        s->base + s->level_off[i], w, hgt, reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]), i,
+        in, jn);
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
@@ -101,16 +140,37 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
     s->level_off[i] = off;
     off += (w * hgt + 255) & ~static_cast<size_t>(255);
   }
+  memset(&s->host_view, 0, sizeof(s->host_view));
+  for (int i = 0; i < depth; ++i) {
+    const int two_s = 2 << i;
+    const int in = (num_x + two_s - 1 + two_s - 1) / two_s;  // ceil((num_x + 2s - 1) / 2s)
+    const int jn = (num_y + two_s - 1 + two_s - 1) / two_s;
+    s->host_view.in[i] = in;
+    s->host_view.jn[i] = jn;
+    s->quad_off[i] = off;
+    off += (static_cast<size_t>(two_s) * two_s * in * jn * 4 + 255) & ~static_cast<size_t>(255);
+  }
   s->bytes = off;
   cudaError_t e = cudaMalloc(&s->base, s->bytes);
   if (e == cudaSuccess) e = cudaMalloc(&s->q_lut_dev, 65536);
+  if (e == cudaSuccess) e = cudaMalloc(&s->dev, sizeof(csm::StackDev));
   if (e != cudaSuccess) {
     csm::set_error("cudaMalloc of a %zu-byte stack failed: %s", s->bytes, cudaGetErrorString(e));
     if (s->base) cudaFree(s->base);
     delete s;
     return CSM_ERR_CUDA;
   }
+  s->host_view.num_x = num_x;
+  s->host_view.num_y = num_y;
+  s->host_view.depth = depth;
+  for (int i = 0; i < depth; ++i) {
+    s->host_view.level[i] = s->base + s->level_off[i];
+    s->host_view.quad[i] = reinterpret_cast<const uint32_t*>(s->base + s->quad_off[i]);
+  }
+  CSM_CUDA(cudaMemcpyAsync(s->dev, &s->host_view, sizeof(csm::StackDev), cudaMemcpyHostToDevice,
+                           ctx->stream));
   CSM_CUDA(cudaMemcpyAsync(s->q_lut_dev, q_lut, 65536, cudaMemcpyHostToDevice, ctx->stream));
+  CSM_CUDA(cudaStreamSynchronize(ctx->stream));  // host_view/q_lut are read from pageable memory
   *out = s;
   return CSM_OK;
 }
@@ -177,6 +237,7 @@ void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* s) {
   if (ctx) cudaStreamSynchronize(ctx->stream); else cudaDeviceSynchronize();
   if (s->base) cudaFree(s->base);
   if (s->q_lut_dev) cudaFree(s->q_lut_dev);
+  if (s->dev) cudaFree(s->dev);
   delete s;
 }
 
