@@ -8,19 +8,26 @@
 //
 // Reformulation.  The reference walks the branch-and-bound tree depth first, one
 // search per CPU thread.  Here the tree is swept breadth first, level by level, for
-// all searches of the batch together:
+// all searches of the batch together, and the unit of work is a TILE: kTW x kTH
+// lattice-adjacent parents of one (job, scan) with a 32-bit alive mask, one per
+// warp, lane = parent.  The precomputation stack is stored in the quad-phase layout
+// (csm_internal.cuh): one 32-bit word holds the four child values of a parent, and
+// parents that are neighbours on the search lattice sit in neighbouring words.  So
+// for every scan point the warp issues ONE load instruction that touches kTH
+// contiguous kTW-word segments and yields the 4 x 32 child values of the tile.
 //   1. k_discretize     one block per (job, scan): rotate + discretise every point
 //                       (fp32/fp64 op order of Eigen/MapLimits, no FMA contraction)
 //                       and reduce the per-scan ShrinkToFit bounds.
 //   2. k_scan_prefix    per job: lattice sizes and generation-order bases.
-//   3. k_score_top      every lowest-resolution candidate, one thread each.
+//   3. k_score_top      every lowest-resolution candidate, as children of virtual
+//                       parents one level above the stack (all alive).
 //   4. k_dive           one warp per job: greedy descent from the best bound to a
 //                       leaf; a real leaf score is a valid pruning incumbent.
-//   5. k_seed / k_expand  frontier of nodes with bound > max(min_score, incumbent);
-//                       one warp per parent scores its <= 4 children; leaves feed a
-//                       64-bit atomicMax.  Strict pruning never discards a subtree
-//                       holding a strictly better leaf, so the maximum leaf score S*
-//                       equals the reference's.
+//   5. k_seed / k_expand  tiles of nodes with bound > max(min_score, incumbent);
+//                       children that survive are re-tiled with warp votes; leaves
+//                       feed a 64-bit atomicMax.  Strict pruning never discards a
+//                       subtree holding a strictly better leaf, so the maximum leaf
+//                       score S* equals the reference's.
 //   6. phase 2          the reference returns the DFS-first leaf attaining S*, where
 //                       DFS order = sorted order of siblings (stable for <= 4
 //                       children, libstdc++ introsort order at the top level).  Only
@@ -47,6 +54,11 @@ constexpr int kCntContenders = 32;
 constexpr int kCntOverflow = 33;
 constexpr int kNumCounters = 40;
 
+// Tile shape: kTW x kTH parents, lane = lj * kTW + li.
+constexpr int kLogTW = 3, kLogTH = 2;
+constexpr int kTW = 1 << kLogTW, kTH = 1 << kLogTH;
+static_assert(kLogTW + kLogTH == 5 && kLogTW >= 1 && kLogTH >= 1, "a tile is one warp");
+
 // ---------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------
@@ -71,14 +83,11 @@ __device__ __forceinline__ uint32_t quad_at(const StackDev& sd, int lvl, int x, 
   return __ldg(sd.quad[lvl] + idx);
 }
 
-__device__ __forceinline__ int warp_sum(int v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
-  return v;
-}
+__device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(kFull, v); }
 
-// Scores the <= 4 children of the node (scan, x, y) at depth `d` (children live on
-// level d-1, half = 2^(d-1)); whole warp cooperates, lanes stride the points.
+// Scores the <= 4 children of ONE node (scan, x, y) at depth `d` (children live on
+// level d-1, half = 2^(d-1)); whole warp cooperates, lanes stride the points.  Used by
+// the greedy dive and the ordered DFS of phase 2, which follow single paths.
 // Children outside the search window are not generated by the reference
 // (FCSM2D.cc:353-367); their slot gets valid = false.
 struct Children {
@@ -125,6 +134,63 @@ __device__ __forceinline__ Children score_children(const JobDev& j, const int2* 
   c.score[2] = to_score(j, s2);
   c.score[3] = to_score(j, s3);
   return c;
+}
+
+// The dense kernel core.  The warp holds one tile of parents whose children live on
+// level `lvl` (children lattice step s = 2^lvl, parents 2s apart).  Parent (li, lj)
+// of the tile has the window start (X0 + 2s*li, Y0 + 2s*lj); bx = X0 + 2s - 1 and
+// by = Y0 + 2s - 1 are passed in.  For a scan point c the phase of the window start
+// is the same for every parent of the tile, so the words the 32 lanes need are
+// quad[idx0 + lj*in + li]: kTH contiguous runs of kTW words.
+// The per-point address terms are computed once per 32 points (lane = point) and
+// broadcast through a 512-byte shared staging buffer private to the warp.
+// Result: sum[k] = sum over points of child k's value, k = 2*cx + cy.
+__device__ __forceinline__ void tile_sums(const StackDev& sd, const int2* __restrict__ pts, int n,
+                                          int lvl, int bx, int by, bool alive, int lane,
+                                          int4* __restrict__ stage, int (&sum)[4]) {
+  const int sh = lvl + 1, two_s = 2 << lvl, msk = two_s - 1;
+  const int in = sd.in[lvl], jn = sd.jn[lvl];
+  const uint32_t* __restrict__ quad = sd.quad[lvl];
+  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
+  const uint32_t* __restrict__ qlane = quad + (lj * in + li);
+  int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+  uint32_t lo = 0, hi = 0;
+  int chunks = 0;
+  for (int p0 = 0; p0 < n; p0 += kWarp) {
+    int4 e = make_int4(0, 0x40000000, 0x40000000, 0);
+    if (p0 + lane < n) {
+      const int2 c = pts[p0 + lane];
+      const int u = c.x + bx, v = c.y + by;
+      const int ca = u >> sh, ra = v >> sh;  // arithmetic shift = floor
+      e.x = ((((v & msk) << sh) + (u & msk)) * jn + ra) * in + ca;
+      e.y = ca;
+      e.z = ra;
+    }
+    __syncwarp();
+    stage[lane] = e;
+    __syncwarp();
+    const int cnt = min(kWarp, n - p0);
+#pragma unroll 8
+    for (int k = 0; k < cnt; ++k) {
+      const int4 t = stage[k];
+      const bool ok = alive && static_cast<unsigned>(t.y + li) < static_cast<unsigned>(in) &&
+                      static_cast<unsigned>(t.z + lj) < static_cast<unsigned>(jn);
+      uint32_t w = 0u;
+      if (ok) w = __ldg(qlane + t.x);
+      lo += w & 0x00FF00FFu;
+      hi += __byte_perm(w, 0u, 0x4341);  // (w >> 8) & 0x00FF00FF
+    }
+    if (++chunks == 8) {  // 256 points: flush before a 16-bit field can overflow
+      s0 += lo & 0xFFFF; s2 += lo >> 16; s1 += hi & 0xFFFF; s3 += hi >> 16;
+      lo = hi = 0;
+      chunks = 0;
+    }
+  }
+  s0 += lo & 0xFFFF; s2 += lo >> 16; s1 += hi & 0xFFFF; s3 += hi >> 16;
+  sum[0] = s0;
+  sum[1] = s1;
+  sum[2] = s2;
+  sum[3] = s3;
 }
 
 // ---------------------------------------------------------------------------
@@ -239,42 +305,58 @@ k_scan_prefix(const JobDev* __restrict__ jobs, ScanInfo* __restrict__ scans,
 }
 
 // ---------------------------------------------------------------------------
-// 3. lowest-resolution candidates (FCSM2D.cc:264-333).  grid = (max_scans, jobs);
-//    one thread per candidate of the scan, generation order x outer / y inner.
+// 3. lowest-resolution candidates (FCSM2D.cc:264-333).  grid = (max_scans, jobs).
+//    The candidates of a scan form an nx x ny lattice with step 2^(depth-1); they are
+//    scored as the children of virtual parents with step 2^depth, one tile per warp.
+//    Scores are stored in generation order (x outer, y inner).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int kTopWarps = 4;
+__global__ void __launch_bounds__(kTopWarps * kWarp)
 k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
             const ScanInfo* __restrict__ scans, float* __restrict__ top_scores,
             JobState* __restrict__ state) {
+  __shared__ int4 stage_all[kTopWarps][kWarp];
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
   if (scan >= j.S) return;
   const ScanInfo si = scans[j.scan_off + scan];
   const int count = si.nx * si.ny;
+  if (count == 0) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int4* stage = stage_all[warp];
+  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
   const int lvl = j.depth - 1;
-  const int step = 1 << lvl;
+  const int two_s = 2 << lvl;
+  const int nvx = (si.nx + 1) >> 1, nvy = (si.ny + 1) >> 1;  // virtual parents
+  const int tiles_x = (nvx + kTW - 1) >> kLogTW, tiles_y = (nvy + kTH - 1) >> kLogTH;
   const int2* pts = xy + j.xy_off + static_cast<long long>(scan) * j.n;
+  const StackDev& sd = *j.sd;
   unsigned long long local_best = 0ull;
-  for (int c = threadIdx.x; c < count; c += blockDim.x) {
-    const int ix = c / si.ny, iy = c - ix * si.ny;
-    const int x = si.min_x + ix * step, y = si.min_y + iy * step;
-    int sum = 0;
-    for (int p = 0; p < j.n; ++p) {
-      const int2 q = pts[p];
-      sum += grid_value(j, lvl, q.x + x, q.y + y);
+  for (int t = warp; t < tiles_x * tiles_y; t += kTopWarps) {
+    const int ti = t % tiles_x, tj = t / tiles_x;
+    const int pi = kTW * ti + li, pj = kTH * tj + lj;
+    const bool alive = pi < nvx && pj < nvy;
+    int sum[4];
+    tile_sums(sd, pts, j.n, lvl, si.min_x + (two_s - 1) + two_s * kTW * ti,
+              si.min_y + (two_s - 1) + two_s * kTH * tj, alive, lane, stage, sum);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int ci = 2 * pi + (k >> 1), cj = 2 * pj + (k & 1);
+      if (alive && ci < si.nx && cj < si.ny) {
+        const float score = to_score(j, sum[k]);
+        const unsigned int cand = static_cast<unsigned int>(si.base + ci * si.ny + cj);
+        top_scores[j.cand_off + cand] = score;
+        const unsigned long long key =
+            (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
+        local_best = max(local_best, key);
+      }
     }
-    const float score = to_score(j, sum);
-    const unsigned int cand = static_cast<unsigned int>(si.base + c);
-    top_scores[j.cand_off + cand] = score;
-    const unsigned long long key =
-        (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
-    local_best = max(local_best, key);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1)
     local_best = max(local_best, __shfl_xor_sync(kFull, local_best, o));
-  if ((threadIdx.x & 31) == 0 && local_best != 0ull) atomicMax(&state[blockIdx.y].top_best, local_best);
-  if (threadIdx.x == 0 && count > 0) {
+  if (lane == 0 && local_best != 0ull) atomicMax(&state[blockIdx.y].top_best, local_best);
+  if (threadIdx.x == 0) {
     atomicAdd(&state[blockIdx.y].scored, static_cast<unsigned long long>(count));
     atomicAdd(&state[blockIdx.y].scored_phase[0], static_cast<unsigned long long>(count));
   }
@@ -298,11 +380,13 @@ __device__ inline void decode_candidate(const JobDev& j, const ScanInfo* __restr
   y = si.min_y + iy * step;
 }
 
+__device__ __forceinline__ unsigned long long leaf_key(float leaf_score, float top_score) {
+  return (static_cast<unsigned long long>(float_to_ordered(leaf_score)) << 32) |
+         float_to_ordered(top_score);
+}
+
 __device__ __forceinline__ void offer_leaf(JobState* st, float leaf_score, float top_score) {
-  const unsigned long long key =
-      (static_cast<unsigned long long>(float_to_ordered(leaf_score)) << 32) |
-      float_to_ordered(top_score);
-  atomicMax(&st->best, key);
+  atomicMax(&st->best, leaf_key(leaf_score, top_score));
 }
 
 // Current pruning threshold of a job: max(min_score, best leaf so far).
@@ -354,10 +438,10 @@ k_dive(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
   }
 }
 
-// Appends nodes with warp-aggregated atomics; returns false on overflow.
-__device__ __forceinline__ void push_node(Node* __restrict__ out, unsigned int* __restrict__ counter,
+// Appends tiles with warp-aggregated atomics; sets the overflow flag when full.
+__device__ __forceinline__ void push_tile(Tile* __restrict__ out, unsigned int* __restrict__ counter,
                                           unsigned long long cap, unsigned int* overflow, bool want,
-                                          const Node& nd) {
+                                          const Tile& tl) {
   const unsigned int mask = __ballot_sync(__activemask(), want);
   if (!want) return;
   const int leader = __ffs(mask) - 1;
@@ -366,100 +450,143 @@ __device__ __forceinline__ void push_node(Node* __restrict__ out, unsigned int* 
   if (lane == leader) base = atomicAdd(counter, __popc(mask));
   base = __shfl_sync(mask, base, leader);
   const unsigned int slot = base + __popc(mask & ((1u << lane) - 1u));
-  if (slot < cap) out[slot] = nd; else atomicOr(overflow, 1u);
+  if (slot < cap) out[slot] = tl; else atomicOr(overflow, 1u);
 }
 
 // ---------------------------------------------------------------------------
-// 5a. seed the frontier with lowest-resolution candidates above the threshold.
+// 5a. seed the frontier: tiles of lowest-resolution candidates above the threshold.
+//     grid = (max_scans, jobs); only jobs whose top depth is `slot` take part.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int kSeedWarps = 4;
+__global__ void __launch_bounds__(kSeedWarps * kWarp)
 k_seed(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans,
        const float* __restrict__ top_scores, const JobState* __restrict__ state,
-       Node* __restrict__ out, unsigned int* __restrict__ counters, int slot,
+       Tile* __restrict__ out, unsigned int* __restrict__ counters, int slot,
        unsigned long long cap) {
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
   if (scan >= j.S || j.depth - 1 != slot) return;
   const ScanInfo si = scans[j.scan_off + scan];
-  const int count = si.nx * si.ny;
+  if (si.nx == 0) return;
   const float thr = threshold(j, &state[blockIdx.y]);
-  const int step = 1 << (j.depth - 1);
-  const int rounds = (count + blockDim.x - 1) / blockDim.x;
-  for (int r = 0; r < rounds; ++r) {
-    const int c = r * blockDim.x + threadIdx.x;
-    bool want = false;
-    Node nd;
-    if (c < count) {
-      const float score = top_scores[j.cand_off + si.base + c];
-      want = score > thr;
-      const int ix = c / si.ny, iy = c - ix * si.ny;
-      nd.job_scan = (static_cast<int>(blockIdx.y) << 16) | scan;
-      nd.x = si.min_x + ix * step;
-      nd.y = si.min_y + iy * step;
-      nd.score = score;
-    }
-    push_node(out, &counters[slot], cap, &counters[kCntOverflow], want, nd);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
+  const int tiles_x = (si.nx + kTW - 1) >> kLogTW, tiles_y = (si.ny + kTH - 1) >> kLogTH;
+  for (int t = warp; t < tiles_x * tiles_y; t += kSeedWarps) {
+    const int ti = t % tiles_x, tj = t / tiles_x;
+    const int ci = kTW * ti + li, cj = kTH * tj + lj;
+    bool alive = false;
+    if (ci < si.nx && cj < si.ny)
+      alive = top_scores[j.cand_off + si.base + ci * si.ny + cj] > thr;
+    Tile tl;
+    tl.job_scan = (static_cast<int>(blockIdx.y) << 16) | scan;
+    tl.tij = ti | (tj << 16);
+    tl.mask = __ballot_sync(kFull, alive);
+    tl.pad = 0;
+    push_tile(out, &counters[slot], cap, &counters[kCntOverflow], lane == 0 && tl.mask != 0u, tl);
   }
 }
 
 // ---------------------------------------------------------------------------
-// 5b. expand one level: one warp per parent at depth d.
+// 5b. expand one level: one warp per tile of parents at depth d.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int kExpandWarps = 8;
+__global__ void __launch_bounds__(kExpandWarps * kWarp)
 k_expand(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
          const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
-         JobState* __restrict__ state, const Node* __restrict__ in, Node* __restrict__ out,
+         JobState* __restrict__ state, const Tile* __restrict__ in, Tile* __restrict__ out,
          unsigned int* __restrict__ counters, int in_slot, int out_slot, int d,
          unsigned long long cap) {
+  __shared__ int4 stage_all[kExpandWarps][kWarp];
   const unsigned int count = min(static_cast<unsigned long long>(counters[in_slot]), cap);
   const int lane = threadIdx.x & 31;
-  const unsigned int warps = gridDim.x * (blockDim.x >> 5);
-  for (unsigned int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < count; i += warps) {
-    const Node nd = in[i];
-    const int job = static_cast<unsigned int>(nd.job_scan) >> 16, scan = nd.job_scan & 0xFFFF;
+  int4* stage = stage_all[threadIdx.x >> 5];
+  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
+  const unsigned int warps = gridDim.x * kExpandWarps;
+  const int lvl = d - 1;
+  const int two_s = 2 << lvl;
+  int acc_job = -1;
+  unsigned long long acc_scored = 0ull;
+  for (unsigned int i = blockIdx.x * kExpandWarps + (threadIdx.x >> 5); i < count; i += warps) {
+    const Tile tl = in[i];
+    const int job = static_cast<unsigned int>(tl.job_scan) >> 16, scan = tl.job_scan & 0xFFFF;
     const JobDev& j = jobs[job];
-    if (d > j.depth - 1) continue;  // cannot happen; frontier slots are per depth
     JobState* st = &state[job];
     // The threshold moves under concurrent atomics: read once, keep the warp uniform.
-    float thr0 = threshold(j, st);
-    thr0 = __shfl_sync(kFull, thr0, 0);
-    if (!(nd.score > thr0)) continue;  // incumbent improved since it was queued
+    float thr = threshold(j, st);
+    thr = __shfl_sync(kFull, thr, 0);
     const ScanInfo si = scans[j.scan_off + scan];
-    const Children c = score_children(j, xy, si, scan, nd.x, nd.y, d, lane);
-    const int half = 1 << (d - 1);
-    if (lane == 0) {
-      int nvalid = 0;
-      for (int k = 0; k < 4; ++k) nvalid += c.valid[k] ? 1 : 0;
-      atomicAdd(&st->scored, static_cast<unsigned long long>(nvalid));
-      atomicAdd(&st->scored_phase[2], static_cast<unsigned long long>(nvalid));
+    const int ti = tl.tij & 0xFFFF, tj = static_cast<unsigned int>(tl.tij) >> 16;
+    const bool alive = (tl.mask >> lane) & 1u;
+    int sum[4];
+    tile_sums(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
+              si.min_x + (two_s - 1) + two_s * kTW * ti, si.min_y + (two_s - 1) + two_s * kTH * tj,
+              alive, lane, stage, sum);
+    // Children lattice of this scan on level lvl (FCSM2D.cc:353-367: a child beyond
+    // max_x / max_y is not generated).
+    const int nxl = ((si.max_x - si.min_x) >> lvl) + 1, nyl = ((si.max_y - si.min_y) >> lvl) + 1;
+    const int ci0 = 2 * (kTW * ti + li), cj0 = 2 * (kTH * tj + lj);
+    bool pass[4];
+    float sc[4];
+    int nvalid = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const bool valid = alive && ci0 + (k >> 1) < nxl && cj0 + (k & 1) < nyl;
+      sc[k] = to_score(j, sum[k]);
+      pass[k] = valid && sc[k] > thr;
+      nvalid += valid ? 1 : 0;
     }
-    if (d == 1) {
-      if (lane == 0) {
-        float best = -INFINITY;
-        for (int k = 0; k < 4; ++k)
-          if (c.valid[k]) best = fmaxf(best, c.score[k]);
-        if (best > j.min_score) {
-          // top-level ancestor of this leaf
-          const int step = 1 << (j.depth - 1);
-          const int ix = (nd.x - si.min_x) / step, iy = (nd.y - si.min_y) / step;
-          const float ts = top_scores[j.cand_off + si.base + ix * si.ny + iy];
-          offer_leaf(st, best, ts);
-        }
+    const int tot = __reduce_add_sync(kFull, nvalid);
+    if (job != acc_job) {
+      if (lane == 0 && acc_job >= 0) {
+        atomicAdd(&state[acc_job].scored, acc_scored);
+        atomicAdd(&state[acc_job].scored_phase[2], acc_scored);
+      }
+      acc_job = job;
+      acc_scored = 0ull;
+    }
+    acc_scored += static_cast<unsigned long long>(tot);
+    if (lvl == 0) {
+      // Leaves.  Rare: only a leaf above the current incumbent reaches the atomic.
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (!pass[k]) continue;
+        const int ci = ci0 + (k >> 1), cj = cj0 + (k & 1);
+        const int ix = ci >> (j.depth - 1), iy = cj >> (j.depth - 1);  // top-level ancestor
+        const float ts = top_scores[j.cand_off + si.base + ix * si.ny + iy];
+        const unsigned long long key = leaf_key(sc[k], ts);
+        const unsigned long long cur =
+            *reinterpret_cast<const volatile unsigned long long*>(&st->best);
+        if (key > cur) atomicMax(&st->best, key);
       }
     } else {
-      float thr = threshold(j, st);
-      thr = __shfl_sync(kFull, thr, 0);
-      bool want = false;
-      Node ch;
-      if (lane < 4) {
-        want = c.valid[lane] && c.score[lane] > thr;
-        ch.job_scan = nd.job_scan;
-        ch.x = nd.x + ((lane & 2) ? half : 0);
-        ch.y = nd.y + ((lane & 1) ? half : 0);
-        ch.score = c.score[lane];
+      // Re-tile the surviving children: the 2x2 child tiles of this tile each take
+      // the children of a (kTW/2 x kTH/2) quadrant of its parents.
+      unsigned int m = 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int bit = ((2 * (lj & (kTH / 2 - 1)) + (k & 1)) << kLogTW) +
+                        2 * (li & (kTW / 2 - 1)) + (k >> 1);
+        if (pass[k]) m |= 1u << bit;
       }
-      push_node(out, &counters[out_slot], cap, &counters[kCntOverflow], want, ch);
+      const int g = (li >> (kLogTW - 1)) + 2 * (lj >> (kLogTH - 1));
+      unsigned int mine = 0u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const unsigned int mq = __reduce_or_sync(kFull, g == q ? m : 0u);
+        if (lane == q) mine = mq;
+      }
+      Tile ch;
+      ch.job_scan = tl.job_scan;
+      ch.tij = (2 * ti + (lane & 1)) | ((2 * tj + ((lane >> 1) & 1)) << 16);
+      ch.mask = mine;
+      ch.pad = 0;
+      push_tile(out, &counters[out_slot], cap, &counters[kCntOverflow], lane < 4 && mine != 0u, ch);
     }
+  }
+  if (lane == 0 && acc_job >= 0) {
+    atomicAdd(&state[acc_job].scored, acc_scored);
+    atomicAdd(&state[acc_job].scored_phase[2], acc_scored);
   }
 }
 
@@ -761,7 +888,7 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
       return CSM_ERR_ARG;
     }
     const csm_stack2d* s = in.stack;
-    for (int l = 0; l < s->depth; ++l) j.level[l] = s->base + s->level_off[l];
+    j.sd = s->dev;
     j.num_x = s->num_x;
     j.num_y = s->num_y;
     j.depth = s->depth;
@@ -833,7 +960,8 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
     if (j.n > 0) memcpy(ppts + 3 * j.pts_off, jobs[i].points_xyz, sizeof(float) * 3 * j.n);
     if (j.S > 0) memcpy(pquat + 2 * j.quat_off, jobs[i].scan_quat, sizeof(float) * 2 * j.S);
   }
-  b->frontier_want = static_cast<unsigned long long>(b->total_cand) * 4ull + (1ull << 20);
+  // Tiles per frontier buffer; an overflow regrows it and replays the batch (fetch).
+  b->frontier_want = static_cast<unsigned long long>(b->total_cand) / 2ull + (1ull << 20);
   int rc = allocate_batch(b, 1u << 20);
   if (rc == CSM_OK) rc = copy_inputs(ctx, b);
   if (rc != CSM_OK) {
@@ -852,12 +980,12 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   if (ctx->frontier_cap < b->frontier_want) {
     CSM_CUDA(cudaStreamSynchronize(st));  // earlier batches may still use the old buffers
     ctx->frontier_cap = 0;
-    int rc = ctx->frontier[0].reserve(sizeof(Node) * b->frontier_want);
-    if (rc == CSM_OK) rc = ctx->frontier[1].reserve(sizeof(Node) * b->frontier_want);
+    int rc = ctx->frontier[0].reserve(sizeof(Tile) * b->frontier_want);
+    if (rc == CSM_OK) rc = ctx->frontier[1].reserve(sizeof(Tile) * b->frontier_want);
     if (rc != CSM_OK) return rc;
     ctx->frontier_cap = b->frontier_want;
   }
-  Node* const fbuf[2] = {ctx->frontier[0].as<Node>(), ctx->frontier[1].as<Node>()};
+  Tile* const fbuf[2] = {ctx->frontier[0].as<Tile>(), ctx->frontier[1].as<Tile>()};
   const unsigned long long fcap = ctx->frontier_cap;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters, st));
   const int nj = b->num_jobs;
@@ -876,7 +1004,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
     k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans, 1);
     k_scan_prefix<<<nj, 256, 0, st>>>(b->jobs, b->scans, b->state, b->counters);
     mark();
-    k_score_top<<<grid_sj, 256, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state);
+    k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state);
     mark();
     k_dive<<<(nj + 3) / 4, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state, nj);
     mark();
@@ -890,9 +1018,9 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       bool any = false;
       for (const JobDev& j : b->jobs_host) any = any || (j.depth - 1 == d && j.S > 0);
       if (any)
-        k_seed<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
+        k_seed<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
                                         fbuf[d & 1], b->counters, d, fcap);
-      k_expand<<<ctx->num_sms * 8, 256, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
+      k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
                                                  fbuf[d & 1], fbuf[(d - 1) & 1], b->counters, d,
                                                  d - 1, d, fcap);
     }

@@ -21,8 +21,6 @@ struct JobDev {
   long long scan_off;                   // index into per-scan arrays (S)
   long long cand_off;                   // index into top-level score array
   long long cand_cap;                   // reserved top-level candidates
-  long long alive_off;                  // uint32 index of this job's alive bitmaps
-  int nx_cap, ny_cap;                   // upper bound of the lowest-resolution lattice per scan
   float q0w, q0s;                       // initial-yaw quaternion (w, z)
   float tx, ty;                         // fp32 initial translation
   double max_x, max_y, res;             // MapLimits
@@ -52,11 +50,16 @@ struct JobState {
   unsigned long long scored_phase[4];  // score_top, dive, expand, phase 2
 };
 
-// Branch-and-bound node: 16 bytes.
-struct Node {
-  int job_scan;  // job << 16 | scan   (job < 65536 per chunk, scan < 65536)
-  int x, y;      // x_index_offset, y_index_offset
-  float score;
+// Branch-and-bound work item: a tile of kTW x kTH lattice-adjacent nodes of one
+// (job, scan) at one depth, 16 bytes.  Node (li, lj) of tile (ti, tj) is the lattice
+// point (kTW*ti + li, kTH*tj + lj), i.e. the offset (min_x + step*(kTW*ti + li),
+// min_y + step*(kTH*tj + lj)) with step = 2^depth; bit lj*kTW + li of `mask` says
+// whether its bound survived pruning.
+struct Tile {
+  int job_scan;       // job << 16 | scan   (job < 65536 per chunk, scan < 65536)
+  int tij;            // ti | tj << 16
+  unsigned int mask;  // alive nodes
+  int pad;
 };
 
 // Phase-2 contender: a top-level candidate that may contain the winning leaf.
@@ -138,8 +141,6 @@ struct csm_batch2d {
   unsigned long long frontier_want = 0;  // nodes per frontier buffer this batch asks for
   csm::Contender* contenders = nullptr;
   unsigned int contender_cap = 0;
-  unsigned int* alive = nullptr;       // dense-level alive bitmaps
-  long long total_alive = 0;           // uint32 words
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
   void* arena = nullptr;               // single cudaMalloc backing all of the above
