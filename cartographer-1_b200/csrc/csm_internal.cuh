@@ -76,6 +76,7 @@ struct csm_ctx {
   double phase_ms[kPhases] = {0, 0, 0, 0, 0};
   double phase_scored[kPhases] = {0, 0, 0, 0, 0};  // candidate scores evaluated per phase
   int profiled_runs = 0;
+  double tile_hist[CSM_MAX_DEPTH * 33] = {0};  // expanded tiles by [depth][alive nodes]
 };
 
 namespace csm {

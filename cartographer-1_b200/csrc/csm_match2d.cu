@@ -55,9 +55,12 @@ constexpr int kCntOverflow = 33;
 constexpr int kNumCounters = 40;
 
 // Tile shape: kTW x kTH parents, lane = lj * kTW + li.
-constexpr int kLogTW = 3, kLogTH = 2;
+#ifndef CSM_LOG_TW
+#define CSM_LOG_TW 3
+#endif
+constexpr int kLogTW = CSM_LOG_TW, kLogTH = 5 - CSM_LOG_TW;
 constexpr int kTW = 1 << kLogTW, kTH = 1 << kLogTH;
-static_assert(kLogTW + kLogTH == 5 && kLogTW >= 1 && kLogTH >= 1, "a tile is one warp");
+static_assert(kLogTW >= 1 && kLogTW <= 5, "a tile is one warp");
 
 // ---------------------------------------------------------------------------
 // device helpers
@@ -145,40 +148,73 @@ __device__ __forceinline__ Children score_children(const JobDev& j, const int2* 
 // The per-point address terms are computed once per 32 points (lane = point) and
 // broadcast through a 512-byte shared staging buffer private to the warp.
 // Result: sum[k] = sum over points of child k's value, k = 2*cx + cy.
+__device__ __forceinline__ uint32_t ldg_pred(const uint32_t* base, int word_offset, uint32_t on) {
+  // Predicated 32-bit read-only load: no branch, no memory access when `on` is 0.
+  uint32_t w;
+  asm("{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .s64 a;\n\t"
+      "setp.ne.u32 p, %3, 0;\n\t"
+      "mad.wide.s32 a, %2, 4, %1;\n\t"
+      "mov.u32 %0, 0;\n\t"
+      "@p ld.global.nc.u32 %0, [a];\n\t"
+      "}"
+      : "=r"(w)
+      : "l"(base), "r"(word_offset), "r"(on));
+  return w;
+}
+
 __device__ __forceinline__ void tile_sums(const StackDev& sd, const int2* __restrict__ pts, int n,
-                                          int lvl, int bx, int by, bool alive, int lane,
-                                          int4* __restrict__ stage, int (&sum)[4]) {
+                                          int lvl, int bx, int by, uint32_t alive_mask, int lane,
+                                          int2* __restrict__ stage, int (&sum)[4]) {
   const int sh = lvl + 1, two_s = 2 << lvl, msk = two_s - 1;
   const int in = sd.in[lvl], jn = sd.jn[lvl];
   const uint32_t* __restrict__ quad = sd.quad[lvl];
   const int li = lane & (kTW - 1), lj = lane >> kLogTW;
   const uint32_t* __restrict__ qlane = quad + (lj * in + li);
+  const uint32_t lane_bit = 1u << lane;
   int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
   uint32_t lo = 0, hi = 0;
   int chunks = 0;
   for (int p0 = 0; p0 < n; p0 += kWarp) {
-    int4 e = make_int4(0, 0x40000000, 0x40000000, 0);
+    // Lane = point: the word index of the tile's first parent for this point, and
+    // the mask of tile lanes whose word lies inside the plane (others read as 0).
+    int2 e = make_int2(0, 0);
     if (p0 + lane < n) {
       const int2 c = pts[p0 + lane];
       const int u = c.x + bx, v = c.y + by;
       const int ca = u >> sh, ra = v >> sh;  // arithmetic shift = floor
       e.x = ((((v & msk) << sh) + (u & msk)) * jn + ra) * in + ca;
-      e.y = ca;
-      e.z = ra;
+      const int clo = max(0, -ca), chi = min(kTW, in - ca);
+      uint32_t vmask = 0u;
+      if (chi > clo) {
+        const uint32_t cols = (chi >= 32 ? 0xFFFFFFFFu : (1u << chi) - 1u) & ~((1u << clo) - 1u);
+#pragma unroll
+        for (int r = 0; r < kTH; ++r)
+          if (static_cast<unsigned>(ra + r) < static_cast<unsigned>(jn)) vmask |= cols << (r * kTW);
+      }
+      e.y = static_cast<int>(vmask & alive_mask);
     }
     __syncwarp();
     stage[lane] = e;
     __syncwarp();
     const int cnt = min(kWarp, n - p0);
-#pragma unroll 8
-    for (int k = 0; k < cnt; ++k) {
-      const int4 t = stage[k];
-      const bool ok = alive && static_cast<unsigned>(t.y + li) < static_cast<unsigned>(in) &&
-                      static_cast<unsigned>(t.z + lj) < static_cast<unsigned>(jn);
-      uint32_t w = 0u;
-      if (ok) w = __ldg(qlane + t.x);
-      lo += w & 0x00FF00FFu;
-      hi += __byte_perm(w, 0u, 0x4341);  // (w >> 8) & 0x00FF00FF
+    if (cnt == kWarp) {
+#pragma unroll
+      for (int k = 0; k < kWarp; ++k) {
+        const int2 t = stage[k];
+        const uint32_t w = ldg_pred(qlane, t.x, static_cast<uint32_t>(t.y) & lane_bit);
+        lo += w & 0x00FF00FFu;
+        hi += __byte_perm(w, 0u, 0x4341);  // (w >> 8) & 0x00FF00FF
+      }
+    } else {
+#pragma unroll 4
+      for (int k = 0; k < cnt; ++k) {
+        const int2 t = stage[k];
+        const uint32_t w = ldg_pred(qlane, t.x, static_cast<uint32_t>(t.y) & lane_bit);
+        lo += w & 0x00FF00FFu;
+        hi += __byte_perm(w, 0u, 0x4341);
+      }
     }
     if (++chunks == 8) {  // 256 points: flush before a 16-bit field can overflow
       s0 += lo & 0xFFFF; s2 += lo >> 16; s1 += hi & 0xFFFF; s3 += hi >> 16;
@@ -199,7 +235,7 @@ __device__ __forceinline__ void tile_sums(const StackDev& sd, const int2* __rest
 __global__ void __launch_bounds__(128)
 k_discretize(const JobDev* __restrict__ jobs, const float* __restrict__ points,
              const float* __restrict__ quats, int2* __restrict__ xy, ScanInfo* __restrict__ scans,
-             int shrink) {
+             unsigned long long* __restrict__ scan_best, int shrink) {
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
   if (scan >= j.S) return;
@@ -260,6 +296,7 @@ k_discretize(const JobDev* __restrict__ jobs, const float* __restrict__ points,
     si.base = 0;
     si.pad = 0;
     scans[j.scan_off + scan] = si;
+    if (scan_best != nullptr) scan_best[j.scan_off + scan] = 0ull;
   }
 }
 
@@ -314,8 +351,8 @@ constexpr int kTopWarps = 4;
 __global__ void __launch_bounds__(kTopWarps * kWarp)
 k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
             const ScanInfo* __restrict__ scans, float* __restrict__ top_scores,
-            JobState* __restrict__ state) {
-  __shared__ int4 stage_all[kTopWarps][kWarp];
+            JobState* __restrict__ state, unsigned long long* __restrict__ scan_best) {
+  __shared__ int2 stage_all[kTopWarps][kWarp];
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
   if (scan >= j.S) return;
@@ -323,7 +360,7 @@ k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
   const int count = si.nx * si.ny;
   if (count == 0) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int4* stage = stage_all[warp];
+  int2* stage = stage_all[warp];
   const int li = lane & (kTW - 1), lj = lane >> kLogTW;
   const int lvl = j.depth - 1;
   const int two_s = 2 << lvl;
@@ -338,7 +375,8 @@ k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
     const bool alive = pi < nvx && pj < nvy;
     int sum[4];
     tile_sums(sd, pts, j.n, lvl, si.min_x + (two_s - 1) + two_s * kTW * ti,
-              si.min_y + (two_s - 1) + two_s * kTH * tj, alive, lane, stage, sum);
+              si.min_y + (two_s - 1) + two_s * kTH * tj, __ballot_sync(kFull, alive), lane, stage,
+              sum);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int ci = 2 * pi + (k >> 1), cj = 2 * pj + (k & 1);
@@ -355,7 +393,10 @@ k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1)
     local_best = max(local_best, __shfl_xor_sync(kFull, local_best, o));
-  if (lane == 0 && local_best != 0ull) atomicMax(&state[blockIdx.y].top_best, local_best);
+  if (lane == 0 && local_best != 0ull) {
+    atomicMax(&state[blockIdx.y].top_best, local_best);
+    atomicMax(&scan_best[j.scan_off + scan], local_best);
+  }
   if (threadIdx.x == 0) {
     atomicAdd(&state[blockIdx.y].scored, static_cast<unsigned long long>(count));
     atomicAdd(&state[blockIdx.y].scored_phase[0], static_cast<unsigned long long>(count));
@@ -398,41 +439,51 @@ __device__ __forceinline__ float threshold(const JobDev& j, const JobState* st) 
 }
 
 // ---------------------------------------------------------------------------
-// 4. greedy dive: one warp per job, from the highest lowest-resolution bound down
-//    to a leaf.  Any real leaf score above min_score is a valid incumbent.
+// 4. greedy dives: one warp per (job, scan), from the scan's best lowest-resolution
+//    bound down to a leaf.  Any real leaf score above min_score is a valid
+//    incumbent; one dive per angular slice makes it a strong one, which is what lets
+//    the level-synchronous sweep prune as hard as the reference's depth-first search.
+//    grid = (ceil(max_scans / 4), jobs)
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+constexpr int kDiveWarps = 4;
+__global__ void __launch_bounds__(kDiveWarps * kWarp)
 k_dive(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
-       const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
-       JobState* __restrict__ state, int num_jobs) {
-  const int job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+       const ScanInfo* __restrict__ scans, const unsigned long long* __restrict__ scan_best,
+       JobState* __restrict__ state) {
+  const JobDev& j = jobs[blockIdx.y];
+  const int scan = blockIdx.x * kDiveWarps + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  if (job >= num_jobs) return;
-  const JobDev& j = jobs[job];
-  JobState* st = &state[job];
-  const unsigned long long tb = st->top_best;
+  if (scan >= j.S) return;
+  JobState* st = &state[blockIdx.y];
+  const unsigned long long tb = scan_best[j.scan_off + scan];
   if (tb == 0ull) return;
   const unsigned int cand = 0xFFFFFFFFu - static_cast<unsigned int>(tb & 0xFFFFFFFFull);
   const float top_score = ordered_to_float(static_cast<unsigned int>(tb >> 32));
   if (!(top_score > j.min_score)) return;
-  int scan, x, y;
-  decode_candidate(j, scans, cand, scan, x, y);
   const ScanInfo si = scans[j.scan_off + scan];
+  const int c = static_cast<int>(cand) - si.base;
+  const int ix = c / si.ny, iy = c - ix * si.ny;
+  int x = si.min_x + (ix << (j.depth - 1)), y = si.min_y + (iy << (j.depth - 1));
   float score = top_score;
   unsigned long long scored = 0;
   for (int d = j.depth - 1; d >= 1; --d) {
-    const Children c = score_children(j, xy, si, scan, x, y, d, lane);
+    // A bound that cannot beat the incumbent any more ends the dive early.
+    float thr = threshold(j, st);
+    thr = __shfl_sync(kFull, thr, 0);
+    if (!(score > thr)) break;
+    const Children ch = score_children(j, xy, si, scan, x, y, d, lane);
     const int half = 1 << (d - 1);
     int bi = 0;
     for (int k = 1; k < 4; ++k)
-      if (c.valid[k] && c.score[k] > c.score[bi]) bi = k;
-    for (int k = 0; k < 4; ++k) scored += c.valid[k] ? 1 : 0;
+      if (ch.valid[k] && ch.score[k] > ch.score[bi]) bi = k;
+    for (int k = 0; k < 4; ++k) scored += ch.valid[k] ? 1 : 0;
     x += (bi & 2) ? half : 0;
     y += (bi & 1) ? half : 0;
-    score = c.score[bi];
+    score = ch.score[bi];
+    if (d == 1 && lane == 0 && score > j.min_score) offer_leaf(st, score, top_score);
   }
-  if (lane == 0) {
-    if (score > j.min_score) offer_leaf(st, score, top_score);
+  if (j.depth == 1 && lane == 0 && score > j.min_score) offer_leaf(st, score, top_score);
+  if (lane == 0 && scored != 0ull) {
     atomicAdd(&st->scored, scored);
     atomicAdd(&st->scored_phase[1], scored);
   }
@@ -496,11 +547,11 @@ k_expand(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
          const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
          JobState* __restrict__ state, const Tile* __restrict__ in, Tile* __restrict__ out,
          unsigned int* __restrict__ counters, int in_slot, int out_slot, int d,
-         unsigned long long cap) {
-  __shared__ int4 stage_all[kExpandWarps][kWarp];
+         unsigned long long cap, unsigned long long* __restrict__ hist) {
+  __shared__ int2 stage_all[kExpandWarps][kWarp];
   const unsigned int count = min(static_cast<unsigned long long>(counters[in_slot]), cap);
   const int lane = threadIdx.x & 31;
-  int4* stage = stage_all[threadIdx.x >> 5];
+  int2* stage = stage_all[threadIdx.x >> 5];
   const int li = lane & (kTW - 1), lj = lane >> kLogTW;
   const unsigned int warps = gridDim.x * kExpandWarps;
   const int lvl = d - 1;
@@ -518,10 +569,11 @@ k_expand(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
     const ScanInfo si = scans[j.scan_off + scan];
     const int ti = tl.tij & 0xFFFF, tj = static_cast<unsigned int>(tl.tij) >> 16;
     const bool alive = (tl.mask >> lane) & 1u;
+    if (hist != nullptr && lane == 0) atomicAdd(&hist[d * 33 + __popc(tl.mask)], 1ull);
     int sum[4];
     tile_sums(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
               si.min_x + (two_s - 1) + two_s * kTW * ti, si.min_y + (two_s - 1) + two_s * kTH * tj,
-              alive, lane, stage, sum);
+              tl.mask, lane, stage, sum);
     // Children lattice of this scan on level lvl (FCSM2D.cc:353-367: a child beyond
     // max_x / max_y is not generated).
     const int nxl = ((si.max_x - si.min_x) >> lvl) + 1, nyl = ((si.max_y - si.min_y) >> lvl) + 1;
@@ -560,20 +612,20 @@ k_expand(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
         if (key > cur) atomicMax(&st->best, key);
       }
     } else {
-      // Re-tile the surviving children: the 2x2 child tiles of this tile each take
-      // the children of a (kTW/2 x kTH/2) quadrant of its parents.
-      unsigned int m = 0u;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int bit = ((2 * (lj & (kTH / 2 - 1)) + (k & 1)) << kLogTW) +
-                        2 * (li & (kTW / 2 - 1)) + (k >> 1);
-        if (pass[k]) m |= 1u << bit;
-      }
-      const int g = (li >> (kLogTW - 1)) + 2 * (lj >> (kLogTH - 1));
+      // Re-tile the surviving children: child (2*li + cx, 2*lj + cy) of the tile's
+      // 2kTW x 2kTH child area goes to child tile (a, b) = (that index / kTW, / kTH).
       unsigned int mine = 0u;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const unsigned int mq = __reduce_or_sync(kFull, g == q ? m : 0u);
+        unsigned int m = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int ci = 2 * li + (k >> 1), cj = 2 * lj + (k & 1);
+          const int tile_of_k = (ci >> kLogTW) + 2 * (cj >> kLogTH);
+          const int bit = ((cj & (kTH - 1)) << kLogTW) + (ci & (kTW - 1));
+          if (tile_of_k == q && pass[k]) m |= 1u << bit;
+        }
+        const unsigned int mq = __reduce_or_sync(kFull, m);
         if (lane == q) mine = mq;
       }
       Tile ch;
@@ -790,11 +842,13 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   const size_t o_quat = take(sizeof(float) * 2 * b->total_scans);
   const size_t o_xy = take(sizeof(int2) * b->total_xy);
   const size_t o_scans = take(sizeof(ScanInfo) * b->total_scans);
+  const size_t o_sbest = take(sizeof(unsigned long long) * b->total_scans);
   const size_t o_top = take(sizeof(float) * b->total_cand);
   const size_t o_state = take(sizeof(JobState) * b->num_jobs);
   const size_t o_cont = take(sizeof(Contender) * contender_cap);
   const size_t o_cnt = take(sizeof(unsigned int) * kNumCounters);
   const size_t o_res = take(sizeof(csm_result2d) * b->num_jobs);
+  const size_t o_hist = take(sizeof(unsigned long long) * CSM_MAX_DEPTH * 33);
   cudaError_t e = cudaMalloc(&b->arena, off);
   if (e != cudaSuccess) {
     b->arena = nullptr;
@@ -808,11 +862,13 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   b->quats = reinterpret_cast<float*>(base + o_quat);
   b->xy = reinterpret_cast<int2*>(base + o_xy);
   b->scans = reinterpret_cast<ScanInfo*>(base + o_scans);
+  b->scan_best = reinterpret_cast<unsigned long long*>(base + o_sbest);
   b->top_scores = reinterpret_cast<float*>(base + o_top);
   b->state = reinterpret_cast<JobState*>(base + o_state);
   b->contenders = reinterpret_cast<Contender*>(base + o_cont);
   b->counters = reinterpret_cast<unsigned int*>(base + o_cnt);
   b->results_dev = reinterpret_cast<csm_result2d*>(base + o_res);
+  b->hist = reinterpret_cast<unsigned long long*>(base + o_hist);
   return CSM_OK;
 }
 
@@ -840,6 +896,7 @@ int csm_ctx_set_profiling(csm_ctx* ctx, int enabled) {
   CSM_REQUIRE(ctx != nullptr, "ctx must not be NULL");
   ctx->profiling = enabled != 0;
   for (int k = 0; k < csm_ctx::kPhases; ++k) ctx->phase_ms[k] = ctx->phase_scored[k] = 0.;
+  for (double& v : ctx->tile_hist) v = 0.;
   ctx->profiled_runs = 0;
   return CSM_OK;
 }
@@ -851,6 +908,12 @@ int csm_ctx_get_profile(csm_ctx* ctx, double* phase_ms5, double* phase_scored5, 
     phase_scored5[k] = ctx->phase_scored[k];
   }
   if (runs) *runs = ctx->profiled_runs;
+  return CSM_OK;
+}
+
+int csm_ctx_get_tile_histogram(csm_ctx* ctx, double* hist) {
+  CSM_REQUIRE(ctx != nullptr && hist != nullptr, "NULL argument");
+  for (int k = 0; k < CSM_MAX_DEPTH * 33; ++k) hist[k] = ctx->tile_hist[k];
   return CSM_OK;
 }
 
@@ -988,6 +1051,8 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   Tile* const fbuf[2] = {ctx->frontier[0].as<Tile>(), ctx->frontier[1].as<Tile>()};
   const unsigned long long fcap = ctx->frontier_cap;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters, st));
+  if (ctx->profiling)
+    CSM_CUDA(cudaMemsetAsync(b->hist, 0, sizeof(unsigned long long) * CSM_MAX_DEPTH * 33, st));
   const int nj = b->num_jobs;
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   b->prof_events.clear();
@@ -1001,12 +1066,15 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   mark();
   if (b->max_scans > 0) {
     const dim3 grid_sj(b->max_scans, nj);
-    k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans, 1);
+    k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans,
+                                          b->scan_best, 1);
     k_scan_prefix<<<nj, 256, 0, st>>>(b->jobs, b->scans, b->state, b->counters);
     mark();
-    k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state);
+    k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores,
+                                                         b->state, b->scan_best);
     mark();
-    k_dive<<<(nj + 3) / 4, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state, nj);
+    k_dive<<<dim3((b->max_scans + kDiveWarps - 1) / kDiveWarps, nj), kDiveWarps * kWarp, 0, st>>>(
+        b->jobs, b->xy, b->scans, b->scan_best, b->state);
     mark();
     int max_depth = 0;
     for (const JobDev& j : b->jobs_host) max_depth = std::max(max_depth, j.depth);
@@ -1022,7 +1090,8 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
                                         fbuf[d & 1], b->counters, d, fcap);
       k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
                                                  fbuf[d & 1], fbuf[(d - 1) & 1], b->counters, d,
-                                                 d - 1, d, fcap);
+                                                 d - 1, d, fcap,
+                                                 ctx->profiling ? b->hist : nullptr);
     }
     mark();
     k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
@@ -1144,6 +1213,11 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
         ctx->phase_scored[3] += static_cast<double>(s.scored_phase[2]);
         ctx->phase_scored[4] += static_cast<double>(s.scored_phase[3]);
       }
+      std::vector<unsigned long long> hist(CSM_MAX_DEPTH * 33);
+      CSM_CUDA(cudaMemcpyAsync(hist.data(), b->hist, sizeof(unsigned long long) * hist.size(),
+                               cudaMemcpyDeviceToHost, ctx->stream));
+      CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+      for (size_t k = 0; k < hist.size(); ++k) ctx->tile_hist[k] += static_cast<double>(hist[k]);
       ++ctx->profiled_runs;
     }
     for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
@@ -1232,7 +1306,7 @@ int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, i
   CSM_CUDA(cudaMemcpyAsync(d_job, &j, sizeof(j), cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_pts, job->points_xyz, sizeof(float) * 3 * j.n, cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_quat, job->scan_quat, sizeof(float) * 2 * j.S, cudaMemcpyHostToDevice, st));
-  k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, shrink);
+  k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, shrink);
   CSM_CUDA(cudaGetLastError());
   std::vector<ScanInfo> scans(j.S);
   CSM_CUDA(cudaMemcpyAsync(out_xy, d_xy, sizeof(int2) * static_cast<size_t>(j.S) * j.n,

@@ -136,6 +136,7 @@ struct csm_batch2d {
   float* quats = nullptr;              // total_scans * 2
   int2* xy = nullptr;                  // total_xy
   csm::ScanInfo* scans = nullptr;      // total_scans
+  unsigned long long* scan_best = nullptr;  // total_scans: best lowest-resolution key per scan
   float* top_scores = nullptr;         // total_cand
   csm::JobState* state = nullptr;      // num_jobs
   unsigned long long frontier_want = 0;  // nodes per frontier buffer this batch asks for
@@ -143,6 +144,7 @@ struct csm_batch2d {
   unsigned int contender_cap = 0;
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
+  unsigned long long* hist = nullptr;  // [depth][alive nodes per tile] tile counts (profiling)
   void* arena = nullptr;               // single cudaMalloc backing all of the above
   size_t arena_bytes = 0;
   void* pinned = nullptr;              // staging for uploads / results

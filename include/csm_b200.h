@@ -71,6 +71,10 @@ void* csm_ctx_stream(csm_ctx* ctx);
  * per phase since profiling was switched on; runs: number of profiled batch runs. */
 int csm_ctx_set_profiling(csm_ctx* ctx, int enabled);
 int csm_ctx_get_profile(csm_ctx* ctx, double* phase_ms5, double* phase_scored5, int* runs);
+/* Expanded branch-and-bound tiles since profiling was switched on, as a histogram
+ * hist[depth * 33 + alive] (CSM_MAX_DEPTH x 33 doubles): tiles of parents at `depth`
+ * that held `alive` surviving nodes. */
+int csm_ctx_get_tile_histogram(csm_ctx* ctx, double* hist);
 
 /* ---- PrecomputationGridStack2D (FCSM2D.cc:91-186, FCSM2D.h:49-109) ----------
  * cells:  the Grid2D correspondence-cost cells, row-major, flat = num_x*y + x
