@@ -99,6 +99,12 @@ def host():
     L.csmh_batch_fetch.argtypes = [C.c_void_p, C.POINTER(Result2D)]
     L.csmh_batch_destroy.argtypes = [C.c_void_p]
     L.csmh_matcher_rebuild_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.csmh_rt_match_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), f64p, f64p, f32p,
+                                      i64p, C.POINTER(Result2D)]
+    L.csmh_constraint_builder_run.restype = C.c_double
+    L.csmh_constraint_builder_run.argtypes = [
+        C.c_int, i32p, C.c_int, C.c_int, C.c_int, f64p, C.c_int, C.POINTER(C.c_void_p), f64p,
+        C.c_int, i32p, i32p, f64p, f32p, i64p, i32p, f64p, f64p]
     _host = L
     return L
 
@@ -188,6 +194,58 @@ def match_batch(ctx, matchers, clouds, min_scores, initial=None):
     rc = host().csmh_match_batch(ctx.h, n, handles, full, init, xyz, offsets, ms, out)
     assert rc == 0
     return out
+
+
+def rt_match_batch(ctx, grids, clouds, initial, linear_search_window=0.1,
+                   angular_search_window=float(np.deg2rad(20.0)),
+                   translation_delta_cost_weight=0.1, rotation_delta_cost_weight=0.1):
+    """RealTimeCorrelativeScanMatcher2D::Match for every (grid, cloud, initial pose)."""
+    n = len(clouds)
+    handles = (C.c_void_p * n)(*[g.h for g in grids])
+    opts = np.array([linear_search_window, angular_search_window, translation_delta_cost_weight,
+                     rotation_delta_cost_weight], dtype=np.float64)
+    init = np.ascontiguousarray(initial, dtype=np.float64).reshape(-1)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, c in enumerate(clouds):
+        offsets[i + 1] = offsets[i] + len(c)
+    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
+                                               for c in clouds], axis=0), dtype=np.float32)
+    out = (Result2D * n)()
+    rc = host().csmh_rt_match_batch(ctx.h, n, handles, opts, init, xyz, offsets, out)
+    assert rc == 0
+    return out
+
+
+def constraint_builder_run(grids, submap_poses, search_submap, search_full, rel_poses, clouds,
+                           devices=(0,), pool_threads=4, flush_threshold=256, depth=7,
+                           sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
+                           global_min_score=0.6, linear_window=7.0,
+                           angular_window=float(np.deg2rad(30.0)), translation_weight=1.1e4,
+                           rotation_weight=1e5):
+    """Drives ConstraintBuilder2D (MaybeAdd*Constraint / NotifyEndOfNode / WhenDone) over the
+    given searches; returns (seconds, found[int32 n], transform[n, 3], stats[4])."""
+    n = len(clouds)
+    handles = (C.c_void_p * len(grids))(*[g.h for g in grids])
+    dev = np.ascontiguousarray(devices, dtype=np.int32)
+    opts = np.array([sampling_ratio, max_constraint_distance, min_score, global_min_score,
+                     linear_window, angular_window, translation_weight, rotation_weight],
+                    dtype=np.float64)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, c in enumerate(clouds):
+        offsets[i + 1] = offsets[i] + len(c)
+    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
+                                               for c in clouds], axis=0), dtype=np.float32)
+    found = np.zeros(n, dtype=np.int32)
+    transform = np.zeros((n, 3), dtype=np.float64)
+    stats = np.zeros(4, dtype=np.float64)
+    secs = host().csmh_constraint_builder_run(
+        len(dev), dev, pool_threads, flush_threshold, depth, opts, len(grids), handles,
+        np.ascontiguousarray(submap_poses, dtype=np.float64).reshape(-1), n,
+        np.ascontiguousarray(search_submap, dtype=np.int32),
+        np.ascontiguousarray(search_full, dtype=np.int32),
+        np.ascontiguousarray(rel_poses, dtype=np.float64).reshape(-1), xyz, offsets, found,
+        transform.reshape(-1), stats)
+    return secs, found, transform, stats
 
 
 class PreparedBatch:

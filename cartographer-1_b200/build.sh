@@ -8,7 +8,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
   -Xcompiler -fPIC -shared -I"$HERE/../include" -I"$HERE/csrc" \
   -o "$HERE/libcsm_b200.so" "$HERE"/csrc/*.cu "$@"
-g++ -O3 -DNDEBUG -std=c++17 -fPIC -ffp-contract=off -Wall -shared \
+g++ -O3 -DNDEBUG -std=c++17 -fPIC -ffp-contract=off -Wall -pthread -shared \
   -I"$HERE/../include" -I"$HERE/host" \
   -o "$HERE/libcsm_host.so" \
   $(find "$HERE/host" -name '*.cc') \

@@ -18,12 +18,12 @@ void CheckOk(int status, const char* what) {
   }
 }
 
-DeviceContext* ThreadDefaultContext() {
+}  // namespace
+
+DeviceContext* DeviceContext::ThreadDefault() {
   thread_local DeviceContext context(0);
   return &context;
 }
-
-}  // namespace
 
 DeviceContext::DeviceContext(int device) : device_(device) {
   CheckOk(csm_ctx_create(device, &ctx_), "csm_ctx_create");
@@ -48,7 +48,7 @@ std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid) {
 
 FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
     const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options)
-    : options_(options), limits_(grid.limits()), context_(ThreadDefaultContext()) {
+    : options_(options), limits_(grid.limits()), context_(DeviceContext::ThreadDefault()) {
   Build(grid);
 }
 
@@ -88,7 +88,7 @@ bool FastCorrelativeScanMatcher2D::Match(const transform::Rigid2d& initial_pose_
   q.initial_pose_estimate = initial_pose_estimate;
   q.min_score = min_score;
   // A matcher built on another thread's context still runs on the caller's own one.
-  DeviceContext* ctx = ThreadDefaultContext();
+  DeviceContext* ctx = DeviceContext::ThreadDefault();
   if (ctx->device() != context_->device()) ctx = context_;
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return false;
@@ -106,7 +106,7 @@ bool FastCorrelativeScanMatcher2D::MatchFullSubmap(const sensor::PointCloud& poi
   q.point_cloud = &point_cloud;
   q.full_submap = true;
   q.min_score = min_score;
-  DeviceContext* ctx = ThreadDefaultContext();
+  DeviceContext* ctx = DeviceContext::ThreadDefault();
   if (ctx->device() != context_->device()) ctx = context_;
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return false;

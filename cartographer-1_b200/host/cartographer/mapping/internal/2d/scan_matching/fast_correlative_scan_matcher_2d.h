@@ -30,6 +30,9 @@ class DeviceContext {
   DeviceContext(const DeviceContext&) = delete;
   DeviceContext& operator=(const DeviceContext&) = delete;
   csm_ctx* get() const { return ctx_; }
+  // One lazily created context on device 0 per calling thread (the reference's
+  // Match* are called concurrently from pool threads; a csm_ctx is single-threaded).
+  static DeviceContext* ThreadDefault();
   int device() const { return device_; }
 
  private:

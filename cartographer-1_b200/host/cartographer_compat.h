@@ -91,6 +91,56 @@ inline Rigid2d operator*(const Rigid2d& l, const Rigid2d& r) {
   return Rigid2d(Vector2d(t.x() + l.translation().x(), t.y() + l.translation().y()),
                  l.rotation() * r.rotation());
 }
+
+// Minimal Rigid3d (translation + unit quaternion w, x, y, z), enough for
+// Embed3D / Project2D (reference: transform/transform.h:34-115,
+// transform/rigid_transform.h:116-196).
+struct Vector3d {
+  double v[3] = {0., 0., 0.};
+  Vector3d() = default;
+  Vector3d(double x, double y, double z) : v{x, y, z} {}
+  double x() const { return v[0]; }
+  double y() const { return v[1]; }
+  double z() const { return v[2]; }
+};
+struct Quaterniond {
+  double w_ = 1., x_ = 0., y_ = 0., z_ = 0.;
+  Quaterniond() = default;
+  Quaterniond(double w, double x, double y, double z) : w_(w), x_(x), y_(y), z_(z) {}
+  double w() const { return w_; }
+  double x() const { return x_; }
+  double y() const { return y_; }
+  double z() const { return z_; }
+};
+class Rigid3d {
+ public:
+  Rigid3d() = default;
+  Rigid3d(const Vector3d& t, const Quaterniond& r) : translation_(t), rotation_(r) {}
+  static Rigid3d Identity() { return Rigid3d(); }
+  const Vector3d& translation() const { return translation_; }
+  const Quaterniond& rotation() const { return rotation_; }
+
+ private:
+  Vector3d translation_;
+  Quaterniond rotation_;
+};
+// transform.h:86-91: AngleAxis(rotation.angle(), UnitZ) -> quaternion.
+inline Rigid3d Embed3D(const Rigid2d& t) {
+  const double half = 0.5 * t.rotation().angle();
+  return Rigid3d(Vector3d(t.translation().x(), t.translation().y(), 0.),
+                 Quaterniond(std::cos(half), 0., 0., std::sin(half)));
+}
+// transform.h:57-61: yaw of the rotated x axis.
+inline double GetYaw(const Quaterniond& q) {
+  // direction = q * UnitX
+  const double dx = 1. - 2. * (q.y() * q.y() + q.z() * q.z());
+  const double dy = 2. * (q.x() * q.y() + q.w() * q.z());
+  return std::atan2(dy, dx);
+}
+// transform.h:79-84
+inline Rigid2d Project2D(const Rigid3d& t) {
+  return Rigid2d(Vector2d(t.translation().x(), t.translation().y()), GetYaw(t.rotation()));
+}
 }  // namespace transform
 
 namespace sensor {
@@ -218,6 +268,76 @@ class ProbabilityGrid : public Grid2D {
   GridType GetGridType() const override { return GridType::PROBABILITY_GRID; }
 };
 
+// mapping/id.h:42-95
+struct NodeId {
+  NodeId(int trajectory_id, int node_index) : trajectory_id(trajectory_id), node_index(node_index) {}
+  int trajectory_id;
+  int node_index;
+  bool operator==(const NodeId& o) const {
+    return std::forward_as_tuple(trajectory_id, node_index) ==
+           std::forward_as_tuple(o.trajectory_id, o.node_index);
+  }
+  bool operator<(const NodeId& o) const {
+    return std::forward_as_tuple(trajectory_id, node_index) <
+           std::forward_as_tuple(o.trajectory_id, o.node_index);
+  }
+};
+struct SubmapId {
+  SubmapId(int trajectory_id, int submap_index)
+      : trajectory_id(trajectory_id), submap_index(submap_index) {}
+  int trajectory_id;
+  int submap_index;
+  bool operator==(const SubmapId& o) const {
+    return std::forward_as_tuple(trajectory_id, submap_index) ==
+           std::forward_as_tuple(o.trajectory_id, o.submap_index);
+  }
+  bool operator<(const SubmapId& o) const {
+    return std::forward_as_tuple(trajectory_id, submap_index) <
+           std::forward_as_tuple(o.trajectory_id, o.submap_index);
+  }
+};
+
+// The parts of Submap2D the constraint builder reads (mapping/2d/submap_2d.h:42-70,
+// mapping/submaps.h:62-91).
+class Submap2D {
+ public:
+  Submap2D(const transform::Rigid3d& local_pose, const Grid2D* grid)
+      : local_pose_(local_pose), grid_(grid) {}
+  transform::Rigid3d local_pose() const { return local_pose_; }
+  const Grid2D* grid() const { return grid_; }
+
+ private:
+  transform::Rigid3d local_pose_;
+  const Grid2D* grid_;
+};
+
+// mapping/trajectory_node.h:43-70 (only the field this path uses).
+struct TrajectoryNode {
+  struct Data {
+    sensor::PointCloud filtered_gravity_aligned_point_cloud;
+  };
+};
+
+// mapping/pose_graph_interface.h:36-59
+class PoseGraphInterface {
+ public:
+  struct Constraint {
+    struct Pose {
+      transform::Rigid3d zbar_ij;
+      double translation_weight;
+      double rotation_weight;
+    };
+    SubmapId submap_id;
+    NodeId node_id;
+    Pose pose;
+    enum Tag { INTRA_SUBMAP, INTER_SUBMAP } tag;
+  };
+};
+
+namespace metrics {
+class FamilyFactory;
+}  // namespace metrics
+
 namespace scan_matching {
 namespace proto {
 // fast_correlative_scan_matcher_options_2d.proto
@@ -253,6 +373,43 @@ class RealTimeCorrelativeScanMatcherOptions {
 };
 }  // namespace proto
 }  // namespace scan_matching
+namespace constraints {
+namespace proto {
+// mapping/proto/pose_graph/constraint_builder_options.proto
+class ConstraintBuilderOptions {
+ public:
+  double sampling_ratio() const { return sampling_ratio_; }
+  double max_constraint_distance() const { return max_constraint_distance_; }
+  double min_score() const { return min_score_; }
+  double global_localization_min_score() const { return global_localization_min_score_; }
+  double loop_closure_translation_weight() const { return loop_closure_translation_weight_; }
+  double loop_closure_rotation_weight() const { return loop_closure_rotation_weight_; }
+  bool log_matches() const { return log_matches_; }
+  const scan_matching::proto::FastCorrelativeScanMatcherOptions2D&
+  fast_correlative_scan_matcher_options() const {
+    return fast_correlative_scan_matcher_options_;
+  }
+  scan_matching::proto::FastCorrelativeScanMatcherOptions2D*
+  mutable_fast_correlative_scan_matcher_options() {
+    return &fast_correlative_scan_matcher_options_;
+  }
+  void set_sampling_ratio(double v) { sampling_ratio_ = v; }
+  void set_max_constraint_distance(double v) { max_constraint_distance_ = v; }
+  void set_min_score(double v) { min_score_ = v; }
+  void set_global_localization_min_score(double v) { global_localization_min_score_ = v; }
+  void set_loop_closure_translation_weight(double v) { loop_closure_translation_weight_ = v; }
+  void set_loop_closure_rotation_weight(double v) { loop_closure_rotation_weight_ = v; }
+  void set_log_matches(bool v) { log_matches_ = v; }
+
+ private:
+  double sampling_ratio_ = 0., max_constraint_distance_ = 0., min_score_ = 0.;
+  double global_localization_min_score_ = 0.;
+  double loop_closure_translation_weight_ = 0., loop_closure_rotation_weight_ = 0.;
+  bool log_matches_ = false;
+  scan_matching::proto::FastCorrelativeScanMatcherOptions2D fast_correlative_scan_matcher_options_;
+};
+}  // namespace proto
+}  // namespace constraints
 }  // namespace mapping
 }  // namespace cartographer
 

@@ -1,10 +1,15 @@
 // Flat C entry points over the C++ host layer, for ctypes-driven parity tests and
 // bench.py.  Product code: goes through the reference-shaped classes and the C ABI
 // only; never touches oracle/.
+#include <chrono>
+#include <condition_variable>
 #include <cstring>
 #include <memory>
+#include <mutex>
 
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/constraints/constraint_builder_2d.h"
 
 using namespace cartographer;
 using mapping::scan_matching::DeviceContext;
@@ -138,6 +143,144 @@ int csmh_matcher_rebuild_dev(void* ctx, void* m, const uint16_t* cells_dev) {
   return csm_stack2d_rebuild_dev(
       static_cast<DeviceContext*>(ctx)->get(),
       const_cast<csm_stack2d*>(static_cast<FastCorrelativeScanMatcher2D*>(m)->stack()), cells_dev);
+}
+
+// RealTimeCorrelativeScanMatcher2D::Match for n scans in one device batch.
+// options4 = {linear_search_window, angular_search_window,
+// translation_delta_cost_weight, rotation_delta_cost_weight}; grids[i] handles from
+// csmh_grid_create; init_pose[3i..] = (x, y, theta).
+int csmh_rt_match_batch(void* ctx, int n, void* const* grids, const double* options4,
+                        const double* init_pose, const float* xyz, const int64_t* offsets,
+                        csmh_result2d* out) {
+  using mapping::scan_matching::RealTimeCorrelativeScanMatcher2D;
+  mapping::scan_matching::proto::RealTimeCorrelativeScanMatcherOptions o;
+  o.set_linear_search_window(options4[0]);
+  o.set_angular_search_window(options4[1]);
+  o.set_translation_delta_cost_weight(options4[2]);
+  o.set_rotation_delta_cost_weight(options4[3]);
+  const RealTimeCorrelativeScanMatcher2D matcher(o, static_cast<DeviceContext*>(ctx));
+  std::vector<sensor::PointCloud> clouds(n);
+  std::vector<RealTimeCorrelativeScanMatcher2D::Query> q(n);
+  for (int i = 0; i < n; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    q[i].point_cloud = &clouds[i];
+    q[i].grid = static_cast<GridHolder*>(grids[i])->grid.get();
+    q[i].initial_pose_estimate = transform::Rigid2d(
+        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
+  }
+  const auto answers = matcher.MatchBatch(q);
+  for (int i = 0; i < n; ++i) {
+    const auto& a = answers[i];
+    out[i].found = 1;
+    out[i].scan_index = a.best_candidate.scan_index;
+    out[i].x_index_offset = a.best_candidate.x_index_offset;
+    out[i].y_index_offset = a.best_candidate.y_index_offset;
+    out[i].score = a.best_candidate.score;
+    out[i].tie_resolution = 0;
+    out[i].pose_x = a.pose_estimate.translation().x();
+    out[i].pose_y = a.pose_estimate.translation().y();
+    out[i].pose_theta = a.pose_estimate.rotation().angle();
+    out[i].candidates_scored = 0;
+  }
+  return 0;
+}
+
+// ConstraintBuilder2D driven like PoseGraph2D does (one NotifyEndOfNode per search),
+// on `num_devices` GPUs.  options8 = {sampling_ratio, max_constraint_distance,
+// min_score, global_localization_min_score, linear_search_window,
+// angular_search_window, loop_closure_translation_weight,
+// loop_closure_rotation_weight}.  Outputs per search i (node index i): found[i] and
+// the constraint transform submap <- node as (x, y, yaw) in transform3[3i..].
+// stats4 = {searches run, constraints found, candidates scored, flushes}.
+// Returns wall seconds from the first MaybeAdd* call to the WhenDone callback.
+double csmh_constraint_builder_run(int num_devices, const int* devices, int num_pool_threads,
+                                   int flush_threshold, int depth, const double* options8,
+                                   int num_submaps, void* const* grids, const double* submap_pose,
+                                   int num_searches, const int32_t* search_submap,
+                                   const int32_t* search_full, const double* search_rel_pose,
+                                   const float* xyz, const int64_t* offsets, int32_t* found,
+                                   double* transform3, double* stats4) {
+  using mapping::constraints::ConstraintBuilder2D;
+  mapping::constraints::proto::ConstraintBuilderOptions o;
+  o.set_sampling_ratio(options8[0]);
+  o.set_max_constraint_distance(options8[1]);
+  o.set_min_score(options8[2]);
+  o.set_global_localization_min_score(options8[3]);
+  o.mutable_fast_correlative_scan_matcher_options()->set_linear_search_window(options8[4]);
+  o.mutable_fast_correlative_scan_matcher_options()->set_angular_search_window(options8[5]);
+  o.mutable_fast_correlative_scan_matcher_options()->set_branch_and_bound_depth(depth);
+  o.set_loop_closure_translation_weight(options8[6]);
+  o.set_loop_closure_rotation_weight(options8[7]);
+  std::vector<mapping::Submap2D> submaps;
+  for (int i = 0; i < num_submaps; ++i) {
+    submaps.emplace_back(
+        transform::Embed3D(transform::Rigid2d(
+            transform::Vector2d(submap_pose[3 * i], submap_pose[3 * i + 1]), submap_pose[3 * i + 2])),
+        static_cast<GridHolder*>(grids[i])->grid.get());
+  }
+  std::vector<mapping::TrajectoryNode::Data> nodes(num_searches);
+  for (int i = 0; i < num_searches; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      nodes[i].filtered_gravity_aligned_point_cloud.push_back(
+          {sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    found[i] = 0;
+  }
+  double seconds = 0.;
+  {
+    common::ThreadPool pool(num_pool_threads);
+    ConstraintBuilder2D builder(o, &pool, std::vector<int>(devices, devices + num_devices));
+    builder.set_flush_threshold(flush_threshold);
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    ConstraintBuilder2D::Result result;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < num_searches; ++i) {
+      const int s = search_submap[i];
+      if (search_full[i]) {
+        builder.MaybeAddGlobalConstraint(mapping::SubmapId{0, s}, &submaps[s],
+                                         mapping::NodeId{0, i}, &nodes[i]);
+      } else {
+        builder.MaybeAddConstraint(
+            mapping::SubmapId{0, s}, &submaps[s], mapping::NodeId{0, i}, &nodes[i],
+            transform::Rigid2d(transform::Vector2d(search_rel_pose[3 * i], search_rel_pose[3 * i + 1]),
+                               search_rel_pose[3 * i + 2]));
+      }
+      builder.NotifyEndOfNode();
+    }
+    builder.WhenDone([&](const ConstraintBuilder2D::Result& r) {
+      std::lock_guard<std::mutex> l(m);
+      result = r;
+      done = true;
+      cv.notify_all();
+    });
+    {
+      std::unique_lock<std::mutex> l(m);
+      cv.wait(l, [&] { return done; });
+    }
+    seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    int last = -1;
+    for (const auto& c : result) {
+      const int i = c.node_id.node_index;
+      CSM_CHECK(i > last);  // submission order
+      last = i;
+      found[i] = 1;
+      transform3[3 * i] = c.pose.zbar_ij.translation().x();
+      transform3[3 * i + 1] = c.pose.zbar_ij.translation().y();
+      transform3[3 * i + 2] = 2. * std::atan2(c.pose.zbar_ij.rotation().z(), c.pose.zbar_ij.rotation().w());
+    }
+    const auto st = builder.stats();
+    if (stats4) {
+      stats4[0] = static_cast<double>(st.searches);
+      stats4[1] = static_cast<double>(st.found);
+      stats4[2] = static_cast<double>(st.candidates_scored);
+      stats4[3] = static_cast<double>(st.flushes);
+    }
+    CSM_CHECK(builder.GetNumFinishedNodes() == num_searches);
+    for (int s = 0; s < num_submaps; ++s) builder.DeleteScanMatcher(mapping::SubmapId{0, s});
+  }
+  return seconds;
 }
 
 }  // extern "C"

@@ -111,3 +111,99 @@ def test_empty_cloud_is_not_found(csm, gpu_ctx):
     _, pts = synth.make_scan(w, 1, max_range=4.0)
     res = csm.match_batch(gpu_ctx, [m, m], [np.zeros((0, 3), np.float32), pts], [0.1, 0.1])
     assert res[0].found == 0
+
+
+def test_real_time_matcher_bit_exact(csm, gpu_ctx):
+    # C2: live 400x400 grid, ~250 points, +-0.1 m / +-20 deg, delta weights 0.1.
+    w = synth.World(400, 400, seed=21)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    opts = {"linear_search_window": 0.1, "angular_search_window": float(np.deg2rad(20.0)),
+            "translation_delta_cost_weight": 0.1, "rotation_delta_cost_weight": 0.1}
+    rng = np.random.default_rng(9)
+    clouds, inits = [], []
+    for i in range(12):
+        pose, pts = synth.make_scan(w, 300 + i)
+        pts = pts[::max(1, len(pts) // 250)]
+        clouds.append(np.ascontiguousarray(pts))
+        inits.append((pose[0] + rng.uniform(-0.08, 0.08), pose[1] + rng.uniform(-0.08, 0.08),
+                      pose[2] + rng.uniform(-0.26, 0.26)))
+    res = csm.rt_match_batch(gpu_ctx, [g] * len(clouds), clouds, inits, **opts)
+    for pts, init, r_g in zip(clouds, inits, res):
+        r_o = ob.rt_match(og, opts, init, pts)
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
+        assert r_g.pose_x == r_o.pose_x and r_g.pose_y == r_o.pose_y
+        assert r_g.pose_theta == r_o.pose_theta
+
+
+def test_real_time_matcher_edge_cases(csm, gpu_ctx):
+    # scan partly outside the grid (out-of-limits cells read kMinProbability), a wide
+    # window, zero weights, and a single-point cloud.
+    w = synth.World(120, 90, seed=22)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    pose, pts = synth.make_scan(w, 7, max_range=6.0)
+    cases = [
+        ({"linear_search_window": 0.3, "angular_search_window": 0.5,
+          "translation_delta_cost_weight": 0.0, "rotation_delta_cost_weight": 0.0},
+         (pose[0] + 2.5, pose[1] - 1.0, pose[2] + 0.4), pts),
+        ({"linear_search_window": 0.05, "angular_search_window": 0.05,
+          "translation_delta_cost_weight": 10.0, "rotation_delta_cost_weight": 40.0},
+         (pose[0], pose[1], pose[2]), pts),
+        ({"linear_search_window": 0.2, "angular_search_window": 0.3,
+          "translation_delta_cost_weight": 0.1, "rotation_delta_cost_weight": 0.1},
+         (0.3, -0.2, 1.0), pts[:1]),
+    ]
+    for opts, init, cloud in cases:
+        r_g = csm.rt_match_batch(gpu_ctx, [g], [np.ascontiguousarray(cloud)], [init], **opts)[0]
+        r_o = ob.rt_match(og, opts, init, np.ascontiguousarray(cloud))
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
+        assert (r_g.pose_x, r_g.pose_y, r_g.pose_theta) == (r_o.pose_x, r_o.pose_y, r_o.pose_theta)
+
+
+def _builder_case(seed, n_sub=3, n_search=24, size=240):
+    rng = np.random.default_rng(seed)
+    worlds = [synth.World(size, size, seed=seed * 10 + k) for k in range(n_sub)]
+    poses = np.array([[rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(-1.5, 1.5)]
+                      for _ in range(n_sub)])
+    sub, full, rel, clouds = [], [], [], []
+    for i in range(n_search):
+        s = int(rng.integers(0, n_sub))
+        src = worlds[s] if i % 3 != 2 else worlds[(s + 1) % n_sub]
+        pose, pts = synth.make_scan(src, seed * 1000 + i, max_range=6.0)
+        sub.append(s)
+        full.append(1 if i % 2 == 0 else 0)
+        # The grid is expressed in the local (map) frame, so the node's map pose is
+        # `pose`; relative to the submap origin that is local_pose^-1 * pose.
+        c, sn = np.cos(-poses[s][2]), np.sin(-poses[s][2])
+        dx, dy = pose[0] - poses[s][0], pose[1] - poses[s][1]
+        rel.append([c * dx - sn * dy + rng.uniform(-0.5, 0.5), sn * dx + c * dy + rng.uniform(-0.5, 0.5),
+                    pose[2] - poses[s][2] + rng.uniform(-0.2, 0.2)])
+        clouds.append(pts)
+    rel[5] = [40.0, 0.0, 0.0]  # beyond max_constraint_distance: never searched
+    return worlds, poses, sub, full, np.array(rel), clouds
+
+
+@pytest.mark.parametrize("sampling_ratio,flush", [(1.0, 256), (0.5, 4)])
+def test_constraint_builder_matches_reference_semantics(csm, sampling_ratio, flush):
+    worlds, poses, sub, full, rel, clouds = _builder_case(5)
+    ograds = [ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    grids = [csm.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    kw = dict(sampling_ratio=sampling_ratio, max_constraint_distance=15.0, min_score=0.45,
+              global_min_score=0.5, linear_window=3.0, angular_window=0.5, depth=5)
+    _, o_out, _ = ob.constraint_batch(4, ograds, poses, sub, full, rel, clouds, **kw)
+    _, found, tf, stats = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds,
+                                                    flush_threshold=flush, **kw)
+    assert found.sum() > 0
+    for i in range(len(clouds)):
+        assert found[i] == o_out[i].found, i
+        if found[i]:
+            assert abs(tf[i][0] - o_out[i].pose_x) <= 1e-9 * max(1.0, abs(o_out[i].pose_x))
+            assert abs(tf[i][1] - o_out[i].pose_y) <= 1e-9 * max(1.0, abs(o_out[i].pose_y))
+            d = (tf[i][2] - o_out[i].pose_theta + np.pi) % (2 * np.pi) - np.pi
+            assert abs(d) <= 1e-9
+    assert stats[1] == found.sum()
