@@ -101,6 +101,9 @@ def host():
     L.csmh_matcher_rebuild_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.csmh_rt_match_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), f64p, f64p, f32p,
                                       i64p, C.POINTER(Result2D)]
+    L.csmh_discretize.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
+                                  f32p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                                  C.c_double, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
     L.csmh_constraint_builder_run.restype = C.c_double
     L.csmh_constraint_builder_run.argtypes = [
         C.c_int, i32p, C.c_int, C.c_int, C.c_int, f64p, C.c_int, C.POINTER(C.c_void_p), f64p,
@@ -214,6 +217,24 @@ def rt_match_batch(ctx, grids, clouds, initial, linear_search_window=0.1,
     rc = host().csmh_rt_match_batch(ctx.h, n, handles, opts, init, xyz, offsets, out)
     assert rc == 0
     return out
+
+
+def discretize(ctx, res, max_x, max_y, nx, ny, pts, init, linear_window, angular_window,
+               shrink=True):
+    """Device GenerateRotatedScans + DiscretizeScans (+ ShrinkToFit); returns
+    (xy[int32 S, n, 2], bounds[int32 S, 4])."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    ns = C.c_int()
+    args = (ctx.h, res, max_x, max_y, nx, ny, pts, len(pts), init[0], init[1], init[2],
+            linear_window, angular_window, 1 if shrink else 0, C.byref(ns))
+    rc = host().csmh_discretize(*args, None, None)
+    assert rc == 0, abi().csm_last_error()
+    xy = np.empty((ns.value, len(pts), 2), dtype=np.int32)
+    bounds = np.empty((ns.value, 4), dtype=np.int32)
+    rc = host().csmh_discretize(*args, xy.ctypes.data_as(C.c_void_p),
+                                bounds.ctypes.data_as(C.c_void_p))
+    assert rc == 0, abi().csm_last_error()
+    return xy, bounds
 
 
 def constraint_builder_run(grids, submap_poses, search_submap, search_full, rel_poses, clouds,

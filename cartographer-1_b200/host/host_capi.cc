@@ -2,6 +2,7 @@
 // bench.py.  Product code: goes through the reference-shaped classes and the C ABI
 // only; never touches oracle/.
 #include <chrono>
+#include <cmath>
 #include <condition_variable>
 #include <cstring>
 #include <memory>
@@ -281,6 +282,40 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
     for (int s = 0; s < num_submaps; ++s) builder.DeleteScanMatcher(mapping::SubmapId{0, s});
   }
   return seconds;
+}
+
+// GenerateRotatedScans + DiscretizeScans (+ ShrinkToFit when `shrink`) on the device
+// for one cloud, with the search parameters the reference would compute.  Call with
+// out_xy == NULL to query num_scans.  out_xy: num_scans * n * 2 int32, out_bounds:
+// num_scans * 4 int32 (min_x, max_x, min_y, max_y).
+int csmh_discretize(void* ctx, double res, double max_x, double max_y, int nx, int ny,
+                    const float* xyz, int n, double init_x, double init_y, double init_theta,
+                    double linear_window, double angular_window, int shrink, int* num_scans,
+                    int32_t* out_xy, int32_t* out_bounds) {
+  sensor::PointCloud cloud;
+  for (int p = 0; p < n; ++p)
+    cloud.push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+  const mapping::scan_matching::SearchParameters sp(linear_window, angular_window, cloud, res);
+  *num_scans = sp.num_scans;
+  if (out_xy == nullptr) return 0;
+  const std::vector<float> quats = sp.ScanQuaternionTable();
+  csm_job2d job;
+  std::memset(&job, 0, sizeof(job));
+  job.points_xyz = xyz;
+  job.num_points = n;
+  job.num_scans = sp.num_scans;
+  job.scan_quat = quats.data();
+  const float half_yaw = 0.5f * static_cast<float>(init_theta);
+  job.init_quat_w = std::cos(half_yaw);
+  job.init_quat_s = std::sin(half_yaw);
+  job.init_tx = static_cast<float>(init_x);
+  job.init_ty = static_cast<float>(init_y);
+  job.max_x = max_x;
+  job.max_y = max_y;
+  job.resolution = res;
+  job.linear_bound = sp.linear_bounds[0].max_x;
+  return csm_discretize2d(static_cast<DeviceContext*>(ctx)->get(), &job, nx, ny, shrink, out_xy,
+                          out_bounds);
 }
 
 }  // extern "C"
