@@ -10,7 +10,8 @@ step against its own submaps).  One step = every rank builds the precomputation 
 of its `--submaps` submaps and runs `--submaps x --nodes` searches against them.
 
   value : searches/s over all ranks with inputs (cells, points, tables) resident in
-          HBM when the timed region starts; max-over-ranks time.
+          HBM when the timed region starts; CUDA-event time on the context's stream,
+          max over ranks; L2 flushed (untimed) between steps.
   e2e   : the same through the public host API from HOST buffers (grid upload, stack
           build, search, results back on the host) every step.
   --impl reference : the reference algorithm (oracle restatement, thread-pooled like
@@ -44,8 +45,8 @@ def parse():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--grid", type=int, default=1000, help="submap cells per side")
-    p.add_argument("--submaps", type=int, default=2, help="submaps per rank per step")
-    p.add_argument("--nodes", type=int, default=24, help="searches per submap per step")
+    p.add_argument("--submaps", type=int, default=4, help="submaps per rank per step")
+    p.add_argument("--nodes", type=int, default=25, help="searches per submap per step")
     p.add_argument("--cpu-searches", type=int, default=0, help="CPU sample size (0 = auto)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     return p.parse_args()
@@ -137,41 +138,69 @@ def cpu_reference_run(args, worlds, clouds, target, n_searches, threads):
     return secs, out, stats, n
 
 
+
+
+def workload_config(args, world, n_search, n_pts):
+    return {"workload": "C3 2D global loop closure: MatchFullSubmap on %dx%d submaps, depth %d, "
+                        "min_score %.2f, 30%% true positives" % (args.grid, args.grid, DEPTH, MIN_SCORE),
+            "submaps_per_rank_per_step": args.submaps, "searches_per_rank_per_step": n_search,
+            "mean_points_per_scan": n_pts,
+            "l2": "flushed between steps (256 MiB write, untimed); stacks + work lists of a step "
+                  "exceed L2",
+            "parallelism": "independent searches sharded over %d ranks by submap, no collective" % world}
+
+
 def run_reference(args):
+    """The reference algorithm on the host cores: thread-pooled oracle restatement driven
+    like ConstraintBuilder2D (one pool task per stack build, one per search).  The
+    reference's own sources cannot be built here (Eigen, glog, abseil, protobuf, Lua,
+    Ceres absent), so kind = "port".  Each step is a bounded sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     worlds, clouds, target = make_workload(args, 0)
-    n = args.cpu_searches or max(4, min(len(clouds), threads))
+    n = args.cpu_searches or max(4, min(len(clouds), 2 * threads))
     times, total_scored = [], 0.0
-    for it in range(args.warmup + args.steps):
+    steps, warmup = args.steps, args.warmup
+    it = 0
+    while it < warmup + steps:
         secs, out, stats, n_done = cpu_reference_run(args, worlds, clouds, target, n, threads)
-        if it >= args.warmup:
+        if it >= warmup:
             times.append(secs)
             total_scored += stats[0] + stats[1]
-        if it == 0 and secs * (args.warmup + args.steps) > 240 and args.warmup > 0:
-            args.warmup = 0  # keep the whole arm within a few minutes
+        if it == 0 and secs * (warmup + steps) > 200:
+            warmup = min(warmup, 1)  # keep the whole arm within a few minutes
+            steps = max(1, min(steps, int(200 / secs) - warmup))
+        it += 1
     total = sum(times)
     value = n_done * len(times) / total
+    n_pts = float(np.mean([len(c) for c in clouds]))
     line = {
         "impl": "reference", "metric": "MatchFullSubmap constraint searches/sec",
         "value": value, "unit": "searches/s", "n_gpus": args.gpus, "steps": len(times),
-        "warmup": args.warmup, "ms_per_step": 1000.0 * total / len(times),
+        "warmup": warmup, "ms_per_step": 1000.0 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": "C3 2D global loop closure: MatchFullSubmap on %dx%d submaps, "
-                               "depth %d, min_score %.2f" % (args.grid, args.grid, DEPTH, MIN_SCORE),
-                   "searches_per_step": n_done},
+        "config": workload_config(args, max(1, args.gpus), len(clouds), n_pts),
         "candidate_scores_per_s": total_scored / total,
         "cpu_baseline": {"value": value, "unit": "searches/s", "cores": threads, "kind": "port",
-                         "sample": "%d searches per step over %d submaps, thread-pooled oracle "
-                                   "restatement (reference sources unbuildable here)" %
+                         "sample": "%d searches per step over %d submaps (stack builds included), "
+                                   "thread-pooled oracle restatement of ConstraintBuilder2D; the "
+                                   "reference sources are unbuildable here" %
                                    (n_done, len(set(target[:n_done])))},
         "e2e": {"value": value, "unit": "searches/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
+
+
+def num_scans_of(cloud, res):
+    """SearchParameters::num_scans for a full-submap search (CSM2D.cc:27-55), for byte counts."""
+    r = max(3.0 * res, float(np.sqrt((cloud[:, 0].astype(np.float64) ** 2 +
+                                      cloud[:, 1].astype(np.float64) ** 2).max())))
+    step = (1.0 - 1e-3) * np.arccos(1.0 - res * res / (2.0 * r * r))
+    return 2 * int(np.ceil(np.pi / step)) + 1
 
 
 def run_b200(args):
@@ -196,132 +225,167 @@ def run_b200(args):
     worlds, clouds, target = make_workload(args, rank)
     n_search = len(clouds)
     ctx = pkg.Context(local)
+    raw = C.c_void_p(ctx.raw)
     grids = [pkg.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
     matchers = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
     cells_dev = [torch.from_numpy(w.cells.view(np.int16)).cuda() for w in worlds]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     batch = pkg.PreparedBatch(ctx, [matchers[t] for t in target], clouds, [MIN_SCORE] * n_search)
     abi = pkg.abi()
-    stream = torch.cuda.ExternalStream(abi.csm_ctx_stream(C.c_void_p(ctx.raw)))
-    abi.csm_ctx_set_profiling(C.c_void_p(ctx.raw), 1)
+    stream = torch.cuda.ExternalStream(abi.csm_ctx_stream(raw))
 
-    build_events = []
-
-    def resident_step(timed):
-        flush.fill_(1)  # L2 flush between iterations (256 MiB > 126 MB L2)
+    def timed(fn):
+        """One step: L2 flush (untimed), then `fn` bracketed by CUDA events on the
+        context's stream.  Returns (result, milliseconds)."""
+        flush.fill_(1)  # 256 MiB write > 126 MB L2
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        out = fn()
+        e1.record(stream)
+        e1.synchronize()
+        return out, e0.elapsed_time(e1)
+
+    build_ms = []
+
+    def resident_step():
+        # inputs already in HBM: cells of every submap, points / tables of every search
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0.record(stream)
         for m, c in zip(matchers, cells_dev):
             rc = pkg.host().csmh_matcher_rebuild_dev(ctx.h, m.h, C.c_void_p(c.data_ptr()))
             assert rc == 0, abi.csm_last_error()
-        e1.record(stream)
+        b1.record(stream)
         batch.run()
         res = batch.fetch()
-        if timed:
-            build_events.append((e0, e1))
+        build_ms.append((b0, b1))
         return res
 
-    # ---- device-resident arm ---------------------------------------------------
+    def e2e_step():
+        # host buffers in, host results out: grid H2D + stack build + upload + search + D2H
+        ms = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
+        return pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
+
+    # ---- device-resident arm ---------------------------------------------------------
     for _ in range(args.warmup):
-        resident_step(False)
-    abi.csm_ctx_set_profiling(C.c_void_p(ctx.raw), 1)  # reset accumulators
+        timed(resident_step)
+    build_ms.clear()
+    abi.csm_ctx_set_profiling(raw, 1)  # per-phase events; resets the accumulators
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    t0 = time.perf_counter()
+    launches0 = abi.csm_ctx_launch_count(raw)
+    ms_resident = 0.0
     for _ in range(args.steps):
-        res = resident_step(True)
+        res, ms = timed(resident_step)
+        ms_resident += ms
+    launches = abi.csm_ctx_launch_count(raw) - launches0
     barrier()
-    dt = time.perf_counter() - t0
     clocks = sampler.stop()
     phase_ms = (C.c_double * 5)()
     phase_scored = (C.c_double * 5)()
     runs = C.c_int()
-    abi.csm_ctx_get_profile(C.c_void_p(ctx.raw), phase_ms, phase_scored, C.byref(runs))
-    abi.csm_ctx_set_profiling(C.c_void_p(ctx.raw), 0)
-    build_ms = sum(a.elapsed_time(b) for a, b in build_events) / max(1, len(build_events))
+    abi.csm_ctx_get_profile(raw, phase_ms, phase_scored, C.byref(runs))
+    abi.csm_ctx_set_profiling(raw, 0)
+    build = sum(a.elapsed_time(b) for a, b in build_ms) / max(1, len(build_ms))
     scored_per_step = sum(r.candidates_scored for r in res)
+    lookups_per_step = float(sum(r.candidates_scored * len(c) for r, c in zip(res, clouds)))
     found = sum(1 for r in res if r.found)
     ties = sum(1 for r in res if r.tie_resolution)
 
-    # ---- end-to-end arm: host buffers in, host results out, every step ----------
-    def e2e_step():
-        ms = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]  # H2D + stack build
-        out = pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
-        return out
-
-    for _ in range(min(args.warmup, 1)):
-        e2e_step()
+    # ---- end-to-end arm ----------------------------------------------------------------
+    for _ in range(min(args.warmup, 3)):
+        timed(e2e_step)
     barrier()
-    t1 = time.perf_counter()
+    ms_e2e = 0.0
     for _ in range(args.steps):
-        out = e2e_step()
+        out, ms = timed(e2e_step)
+        ms_e2e += ms
     barrier()
-    dt_e2e = time.perf_counter() - t1
     for a, b in zip(out, res):
         assert (a.found, a.scan_index, a.x_index_offset, a.y_index_offset) == \
                (b.found, b.scan_index, b.x_index_offset, b.y_index_offset)
 
-    times = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
+    times = torch.tensor([ms_resident, ms_e2e], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    dt, dt_e2e = float(times[0]), float(times[1])
+    ms_resident, ms_e2e = float(times[0]), float(times[1])
     total_searches = world * n_search * args.steps
-    value = total_searches / dt
-    e2e_value = total_searches / dt_e2e
+    value = total_searches / (ms_resident * 1e-3)
+    e2e_value = total_searches / (ms_e2e * 1e-3)
 
     n_pts = float(np.mean([len(c) for c in clouds]))
-    h2d = sum(w.cells.nbytes + 65536 for w in worlds) + sum(c.nbytes for c in clouds) + \
-        n_search * (1300 * 8 + 256)
-    d2h = n_search * 32
+    res0 = worlds[0].res
+    h2d = sum(w.cells.nbytes + 65536 for w in worlds) + sum(
+        c.nbytes + 8 * num_scans_of(c, res0) + 160 for c in clouds)
+    d2h = n_search * 40
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured"
     else:
         peak, peak_src = 6650.0, "fallback"
-    # Dominant kernel: the level-synchronous expansion (phase 3).  Algorithmic bytes =
-    # 1 byte per (candidate, point) lookup.
-    steps = max(1, runs.value)
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
+    traffic = json.load(open(traffic_path)) if os.path.exists(traffic_path) else {}
+
+    # Dominant kernel: k_expand, the level-synchronous tile expansion (6 launches per
+    # batch).  Algorithmic bytes = 1 B per (candidate, point) lookup (SURVEY.md 8(d)).
+    steps = max(1, runs.value)  # profiled batch runs (a step may split into several)
+    names = ["k_discretize", "k_score_top", "k_dive", "k_expand", "phase2"]
     dom = int(np.argmax(list(phase_ms)))
-    dom_names = ["k_discretize", "k_score_top", "k_dive", "k_expand", "phase2"]
+    launches_of_dom = {"k_expand": DEPTH - 1}.get(names[dom], 1) * steps
     dom_bytes = phase_scored[dom] * n_pts
     dom_s = phase_ms[dom] / 1000.0
     achieved = dom_bytes / dom_s / 1e9 if dom_s > 0 else 0.0
+
+    # Gather roofline G_L2 (SURVEY.md 8(d)): naive 1-byte gathers, warp per candidate,
+    # lane per point, L2-resident table of the stack's size, this workload's scan shape.
+    xy, _ = pkg.discretize(ctx, res0, worlds[0].max_x, worlds[0].max_y, args.grid, args.grid,
+                           clouds[0], (0.0, 0.0, 0.3), 1.0, 0.0, shrink=False)
+    pts_xy = np.ascontiguousarray(xy[0], dtype=np.int32)
+    stack_bytes = sum((args.grid + 2 ** i - 1) ** 2 for i in range(DEPTH))
+    g_l2 = C.c_double()
+    rc = abi.csm_measure_gather_rate(raw, C.c_size_t(stack_bytes), args.grid + 63,
+                                     pts_xy.ctypes.data_as(C.c_void_p), len(pts_xy), 1 << 21, 3,
+                                     C.byref(g_l2))
+    assert rc == 0, abi.csm_last_error()
+    search_ms = sum(phase_ms) / steps
     line = {
         "metric": "MatchFullSubmap constraint searches/sec", "value": value, "unit": "searches/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": ms_resident / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C3 2D global loop closure: MatchFullSubmap on %dx%d submaps, "
-                               "depth %d, min_score %.2f, 30%% true positives" %
-                               (args.grid, args.grid, DEPTH, MIN_SCORE),
-                   "submaps_per_rank_per_step": args.submaps,
-                   "searches_per_rank_per_step": n_search, "mean_points_per_scan": n_pts,
-                   "l2": "flushed between steps (256 MiB write); stacks+work lists exceed L2",
-                   "parallelism": "independent searches sharded over %d ranks, no collective" % world},
-        "candidate_scores_per_s": world * scored_per_step * args.steps / dt,
+        "config": workload_config(args, world, n_search, n_pts),
+        "candidate_scores_per_s": world * scored_per_step * args.steps / (ms_resident * 1e-3),
         "candidates_scored_per_search": scored_per_step / n_search,
         "found": found, "host_tie_replays": ties,
         "e2e": {"value": e2e_value, "unit": "searches/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h)},
-        "gpu_launches": int(args.steps * (len(matchers) * DEPTH + 8 + 3 * (DEPTH - 1) + 2)),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": dom_names[dom], "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic.get(names[dom]),
                      "peak_source": peak_src,
+                     "launch_ms": phase_ms[dom] / launches_of_dom,
+                     "algorithmic_bytes_per_launch": dom_bytes / launches_of_dom,
                      "note": "algorithmic bytes = 1 B per (candidate, point) lookup; the stack is "
-                             "L2-resident, so HBM bandwidth is a loose bound (see DESIGN.md)"},
-        "phase_ms_per_step": {n: phase_ms[i] / steps for i, n in enumerate(dom_names)},
-        "phase_candidates_per_step": {n: phase_scored[i] / steps for i, n in enumerate(dom_names)},
-        "stack_build": {"ms_per_step": build_ms, "submaps": len(matchers),
-                        "algorithmic_gbs": (len(matchers) * (2 * args.grid ** 2 + sum(
-                            (args.grid + 2 ** i - 1) ** 2 for i in range(DEPTH)))) / (build_ms * 1e6)
-                        if build_ms > 0 else None},
+                             "L2-resident, so the HBM peak is a loose bound and the L2 gather "
+                             "rate below is the one that binds (DESIGN.md)"},
+        "gather_roofline": {"g_l2_lookups_per_s": g_l2.value,
+                            "achieved_lookups_per_s": lookups_per_step / (search_ms * 1e-3),
+                            "frac": lookups_per_step / (search_ms * 1e-3) / g_l2.value,
+                            "searches_per_s_at_g_l2": g_l2.value / (lookups_per_step / n_search),
+                            "how": "csm_measure_gather_rate: %d-byte table, %d-point scan, 2^21 "
+                                   "candidates x 3" % (stack_bytes, len(pts_xy))},
+        "phase_ms_per_step": {n: phase_ms[i] / args.steps for i, n in enumerate(names)},
+        "phase_candidates_per_step": {n: phase_scored[i] / args.steps for i, n in enumerate(names)},
+        "stack_build": {"ms_per_step": build, "submaps": len(matchers),
+                        "algorithmic_gbs": (len(matchers) * (2 * args.grid ** 2 + stack_bytes)) /
+                        (build * 1e6) if build > 0 else None},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        n = args.cpu_searches or max(4, min(n_search, threads))
+        n = args.cpu_searches or max(4, min(n_search, 4 * threads))
         secs, cpu_out, stats, n_done = cpu_reference_run(args, worlds, clouds, target, n, threads)
         for i in range(n_done):  # the oracle doubles as a full-size parity check
             a, b = cpu_out[i], res[i]
@@ -331,8 +395,8 @@ def run_b200(args):
         line["cpu_baseline"] = {
             "value": n_done / secs, "unit": "searches/s", "cores": threads, "kind": "port",
             "sample": "first %d searches of the step, thread-pooled oracle restatement "
-                      "(ConstraintBuilder2D shape), %.1f s; results identical to the GPU's" %
-                      (n_done, secs),
+                      "(ConstraintBuilder2D shape, stack builds included), %.1f s; results "
+                      "identical to the GPU's" % (n_done, secs),
             "candidate_scores_per_s": (stats[0] + stats[1]) / secs}
     if rank == 0:
         print(json.dumps(line))

@@ -39,7 +39,7 @@ ABI_SYMBOLS = [
     "csm_stack2d_rebuild_dev", "csm_stack2d_level", "csm_stack2d_depth",
     "csm_stack2d_device_bytes", "csm_stack2d_destroy", "csm_match2d_batch",
     "csm_batch2d_upload", "csm_batch2d_run", "csm_batch2d_fetch", "csm_batch2d_destroy",
-    "csm_discretize2d", "csm_rt_match2d_batch",
+    "csm_discretize2d", "csm_rt_match2d_batch", "csm_ctx_launch_count", "csm_measure_gather_rate",
 ]
 
 _abi = None
@@ -57,6 +57,10 @@ def abi():
         _abi.csm_ctx_stream.restype = C.c_void_p
         _abi.csm_ctx_stream.argtypes = [C.c_void_p]
         _abi.csm_stack2d_device_bytes.restype = C.c_size_t
+        _abi.csm_ctx_launch_count.restype = C.c_ulonglong
+        _abi.csm_ctx_launch_count.argtypes = [C.c_void_p]
+        _abi.csm_measure_gather_rate.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int,
+                                                 C.c_uint, C.c_int, C.POINTER(C.c_double)]
     return _abi
 
 

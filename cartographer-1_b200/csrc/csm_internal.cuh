@@ -72,10 +72,11 @@ struct csm_ctx {
   unsigned long long frontier_cap = 0;  // nodes per buffer
   // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
   static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2
-  bool profiling = false;
+  int profiling = 0;  // 0 off, 1 phase events, 2 + tile histogram
   double phase_ms[kPhases] = {0, 0, 0, 0, 0};
   double phase_scored[kPhases] = {0, 0, 0, 0, 0};  // candidate scores evaluated per phase
   int profiled_runs = 0;
+  unsigned long long launches = 0;  // kernels launched through this context so far
   double tile_hist[CSM_MAX_DEPTH * 33] = {0};  // expanded tiles by [depth][alive nodes]
 };
 

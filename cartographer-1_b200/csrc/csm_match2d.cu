@@ -894,7 +894,7 @@ void* csm_ctx_stream(csm_ctx* ctx) { return ctx ? static_cast<void*>(ctx->stream
 
 int csm_ctx_set_profiling(csm_ctx* ctx, int enabled) {
   CSM_REQUIRE(ctx != nullptr, "ctx must not be NULL");
-  ctx->profiling = enabled != 0;
+  ctx->profiling = enabled;
   for (int k = 0; k < csm_ctx::kPhases; ++k) ctx->phase_ms[k] = ctx->phase_scored[k] = 0.;
   for (double& v : ctx->tile_hist) v = 0.;
   ctx->profiled_runs = 0;
@@ -1051,7 +1051,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   Tile* const fbuf[2] = {ctx->frontier[0].as<Tile>(), ctx->frontier[1].as<Tile>()};
   const unsigned long long fcap = ctx->frontier_cap;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters, st));
-  if (ctx->profiling)
+  if (ctx->profiling >= 2)
     CSM_CUDA(cudaMemsetAsync(b->hist, 0, sizeof(unsigned long long) * CSM_MAX_DEPTH * 33, st));
   const int nj = b->num_jobs;
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
@@ -1066,14 +1066,14 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   mark();
   if (b->max_scans > 0) {
     const dim3 grid_sj(b->max_scans, nj);
-    k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans,
+    ++ctx->launches, k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans,
                                           b->scan_best, 1);
-    k_scan_prefix<<<nj, 256, 0, st>>>(b->jobs, b->scans, b->state, b->counters);
+    ++ctx->launches, k_scan_prefix<<<nj, 256, 0, st>>>(b->jobs, b->scans, b->state, b->counters);
     mark();
-    k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores,
+    ++ctx->launches, k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores,
                                                          b->state, b->scan_best);
     mark();
-    k_dive<<<dim3((b->max_scans + kDiveWarps - 1) / kDiveWarps, nj), kDiveWarps * kWarp, 0, st>>>(
+    ++ctx->launches, k_dive<<<dim3((b->max_scans + kDiveWarps - 1) / kDiveWarps, nj), kDiveWarps * kWarp, 0, st>>>(
         b->jobs, b->xy, b->scans, b->scan_best, b->state);
     mark();
     int max_depth = 0;
@@ -1086,25 +1086,25 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       bool any = false;
       for (const JobDev& j : b->jobs_host) any = any || (j.depth - 1 == d && j.S > 0);
       if (any)
-        k_seed<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
+        ++ctx->launches, k_seed<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
                                         fbuf[d & 1], b->counters, d, fcap);
-      k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
+      ++ctx->launches, k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
                                                  fbuf[d & 1], fbuf[(d - 1) & 1], b->counters, d,
                                                  d - 1, d, fcap,
-                                                 ctx->profiling ? b->hist : nullptr);
+                                                 ctx->profiling >= 2 ? b->hist : nullptr);
     }
     mark();
-    k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
+    ++ctx->launches, k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
                                        b->counters, b->contender_cap);
-    k_ordered_dfs<<<ctx->num_sms * 8, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->state,
+    ++ctx->launches, k_ordered_dfs<<<ctx->num_sms * 8, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->state,
                                                     b->contenders, b->counters, b->contender_cap);
-    k_pick<<<(b->contender_cap + 255) / 256, 256, 0, st>>>(b->state, b->contenders, b->counters,
+    ++ctx->launches, k_pick<<<(b->contender_cap + 255) / 256, 256, 0, st>>>(b->state, b->contenders, b->counters,
                                                            b->contender_cap);
   } else {
     CSM_CUDA(cudaMemsetAsync(b->state, 0, sizeof(JobState) * nj, st));
     for (int k = 0; k < 4; ++k) mark();
   }
-  k_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
+  ++ctx->launches, k_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
   mark();
   CSM_CUDA(cudaGetLastError());
   b->ran = true;
@@ -1213,11 +1213,13 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
         ctx->phase_scored[3] += static_cast<double>(s.scored_phase[2]);
         ctx->phase_scored[4] += static_cast<double>(s.scored_phase[3]);
       }
-      std::vector<unsigned long long> hist(CSM_MAX_DEPTH * 33);
-      CSM_CUDA(cudaMemcpyAsync(hist.data(), b->hist, sizeof(unsigned long long) * hist.size(),
-                               cudaMemcpyDeviceToHost, ctx->stream));
-      CSM_CUDA(cudaStreamSynchronize(ctx->stream));
-      for (size_t k = 0; k < hist.size(); ++k) ctx->tile_hist[k] += static_cast<double>(hist[k]);
+      if (ctx->profiling >= 2) {
+        std::vector<unsigned long long> hist(CSM_MAX_DEPTH * 33);
+        CSM_CUDA(cudaMemcpyAsync(hist.data(), b->hist, sizeof(unsigned long long) * hist.size(),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+        CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (size_t k = 0; k < hist.size(); ++k) ctx->tile_hist[k] += static_cast<double>(hist[k]);
+      }
       ++ctx->profiled_runs;
     }
     for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
@@ -1306,7 +1308,7 @@ int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, i
   CSM_CUDA(cudaMemcpyAsync(d_job, &j, sizeof(j), cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_pts, job->points_xyz, sizeof(float) * 3 * j.n, cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_quat, job->scan_quat, sizeof(float) * 2 * j.S, cudaMemcpyHostToDevice, st));
-  k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, shrink);
+  ++ctx->launches, k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, shrink);
   CSM_CUDA(cudaGetLastError());
   std::vector<ScanInfo> scans(j.S);
   CSM_CUDA(cudaMemcpyAsync(out_xy, d_xy, sizeof(int2) * static_cast<size_t>(j.S) * j.n,

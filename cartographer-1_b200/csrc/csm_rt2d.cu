@@ -173,7 +173,7 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   CSM_CUDA(cudaMemcpyAsync(base, pin, total, cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaFuncSetAttribute(k_rt_score, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(std::max<size_t>(smem, 1024))));
-  k_rt_score<<<dim3(max_scans, num_jobs), 256, smem, st>>>(
+  ++ctx->launches, k_rt_score<<<dim3(max_scans, num_jobs), 256, smem, st>>>(
       reinterpret_cast<const RtJobDev*>(base + o_jobs), reinterpret_cast<const float*>(base + o_pts),
       reinterpret_cast<const float*>(base + o_quat),
       reinterpret_cast<unsigned long long*>(base + o_best));

@@ -95,7 +95,7 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const size_t n = static_cast<size_t>(s->num_x) * s->num_y;
   int blocks = static_cast<int>(std::min<size_t>((n / 4 + kThreads - 1) / kThreads + 1,
                                                  static_cast<size_t>(ctx->num_sms) * 8));
-  k_stack_level0<<<blocks, kThreads, 0, ctx->stream>>>(cells_dev, s->q_lut_dev,
+  ++ctx->launches, k_stack_level0<<<blocks, kThreads, 0, ctx->stream>>>(cells_dev, s->q_lut_dev,
                                                        s->base + s->level_off[0], n);
   for (int i = 0; i + 1 < s->depth; ++i) {
     const int h = 1 << i;
@@ -103,7 +103,7 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     const int out_w = s->num_x + 2 * h - 1, out_h = s->num_y + 2 * h - 1;
     dim3 block(64, 4);
     dim3 grid((out_w + block.x - 1) / block.x, (out_h + block.y - 1) / block.y);
-    k_stack_level_up<<<grid, block, 0, ctx->stream>>>(s->base + s->level_off[i], in_w, in_h,
+    ++ctx->launches, k_stack_level_up<<<grid, block, 0, ctx->stream>>>(s->base + s->level_off[i], in_w, in_h,
                                                       s->base + s->level_off[i + 1], out_w, out_h, h);
   }
   for (int i = 0; i < s->depth; ++i) {
@@ -112,7 +112,7 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     const size_t total = static_cast<size_t>(4) * (1u << (2 * i)) * in * jn;
     const int qblocks = static_cast<int>(
         std::min<size_t>((total + kThreads - 1) / kThreads, static_cast<size_t>(ctx->num_sms) * 16));
-    k_stack_quads<<<qblocks, kThreads, 0, ctx->stream>>>(
+    ++ctx->launches, k_stack_quads<<<qblocks, kThreads, 0, ctx->stream>>>(
         s->base + s->level_off[i], w, hgt, reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]), i,
         in, jn);
   }

@@ -68,7 +68,8 @@ void* csm_ctx_stream(csm_ctx* ctx);
  * (measurement aid for bench.py).  Phases: 0 rotate/discretise, 1 lowest-resolution
  * scoring, 2 greedy dive, 3 level-synchronous expansion, 4 tie-order phase.
  * phase_ms5 / phase_scored5: accumulated milliseconds and candidate scores evaluated
- * per phase since profiling was switched on; runs: number of profiled batch runs. */
+ * per phase since profiling was switched on; runs: number of profiled batch runs.
+ * enabled: 0 off, 1 phase timing, 2 phase timing + tile histogram (adds atomics). */
 int csm_ctx_set_profiling(csm_ctx* ctx, int enabled);
 int csm_ctx_get_profile(csm_ctx* ctx, double* phase_ms5, double* phase_scored5, int* runs);
 /* Expanded branch-and-bound tiles since profiling was switched on, as a histogram
@@ -182,6 +183,20 @@ typedef struct {
 
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
                          csm_result2d* results);
+
+/* ---- measurement aids (bench.py) ------------------------------------------------
+ * csm_ctx_launch_count: kernels launched through `ctx` since it was created.
+ * csm_measure_gather_rate: the L2 gather roofline G_L2 of the scoring loop
+ * (FCSM2D.cc:314-333): a micro-kernel with one warp per candidate and one lane per
+ * scan point gathers single bytes from a `table_bytes` table (the size of a
+ * precomputation stack, L2-resident) at table[candidate_base + y*row_pitch + x] for
+ * the given discretised scan `point_xy` (num_points x 2 int32).  Writes the
+ * sustained rate in lookups per second.
+ */
+unsigned long long csm_ctx_launch_count(csm_ctx* ctx);
+int csm_measure_gather_rate(csm_ctx* ctx, size_t table_bytes, int row_pitch, const int32_t* point_xy,
+                            int num_points, unsigned int num_candidates, int repeats,
+                            double* lookups_per_second);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,7 @@ def main():
     abi = pkg.abi()
     batch.run()
     batch.fetch()
-    abi.csm_ctx_set_profiling(C.c_void_p(ctx.raw), 1)
+    abi.csm_ctx_set_profiling(C.c_void_p(ctx.raw), 2)
     batch.run()
     res = batch.fetch()
     hist = (C.c_double * (16 * 33))()
