@@ -191,6 +191,9 @@ void ConstraintBuilder2D::RunFlush(const std::vector<PendingSearch>& searches,
     scored += a.candidates_scored;
     if (!a.found) continue;  // below-threshold searches leave a null slot (.cc:225-241)
     ++found;
+    // [Ceres hook] In a full Cartographer tree the reference's refinement goes here:
+    // ceres_scan_matcher_.Match(pose.translation(), pose, cloud, *grid, &pose, &summary)
+    // (reference .cc:245-249).  Ceres is outside this path and absent from this image.
     // constraint_transform = ComputeSubmapPose(*submap).inverse() * pose_estimate
     const transform::Rigid2d constraint_transform =
         ComputeSubmapPose(*s.submap).inverse() * a.pose_estimate;
