@@ -15,6 +15,8 @@
 //
 // Data layout in HBM: one allocation per stack; level i is a dense row-major
 // (num_x + 2^i - 1) x (num_y + 2^i - 1) byte image at a 256-byte aligned offset.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "csm_internal.cuh"
@@ -91,7 +93,280 @@ k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, uint32_t*
   }
 }
 
+// ---------------------------------------------------------------------------
+// Fused build: every byte level AND every quad-phase level in one launch.
+//
+// All levels share the "window end" coordinate X (cell x sits at X = x): level i at X
+// is the maximum of level 0 over [X - (2^i - 1), X], so level i+1 at X is the 4-tap
+// maximum of level i at {X, X - 2^i}^2, and the quad word of level i at (u, v) = (X, Y)
+// is exactly those four taps packed (byte0 (X-s, Y-s), byte1 (X-s, Y), byte2 (X, Y-s),
+// byte3 (X, Y); see StackDev).  One block owns a kFusedTile^2 tile of output
+// coordinates and stages the cells of [X0 - P, X0 + T), P = 2^depth - 1, as level-0
+// bytes in shared memory (row staging: coalesced 2-byte loads, LUT through L1), then
+// doubles level by level between two shared buffers, 4 bytes per thread with
+// __vmaxu4, writing the tile's bytes of every level and its quad words as it goes.
+// HBM traffic: the cells once (plus halo re-reads served by L2) and every output once.
+// ---------------------------------------------------------------------------
+constexpr int kFusedLogTile = 6;
+constexpr int kFusedTile = 1 << kFusedLogTile;
+constexpr int kFusedMaxDepth = 7;
+constexpr int kFusedThreads = 512;
+
+// Byte-wise maximum of four words with the 16x2 SIMD min/max unit (VIMNMX3.U16x2):
+// even and odd bytes are widened to 16-bit lanes, reduced, and re-interleaved.
+__device__ __forceinline__ uint32_t max4_u8x4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  const uint32_t me = __vmaxu2(__vimax3_u16x2(a & 0x00FF00FFu, b & 0x00FF00FFu, c & 0x00FF00FFu),
+                               d & 0x00FF00FFu);
+  const uint32_t mo = __vmaxu2(__vimax3_u16x2(__byte_perm(a, 0u, 0x4341), __byte_perm(b, 0u, 0x4341),
+                                              __byte_perm(c, 0u, 0x4341)),
+                               __byte_perm(d, 0u, 0x4341));
+  return __byte_perm(me, mo, 0x6240);
+}
+
+// Quad-phase layout from the byte levels, all levels in one launch.  A block owns one
+// output row coordinate v of one level: it stages the two byte rows it needs (Y = v
+// and Y = v - s, zero outside the level) in shared memory with coalesced loads, then
+// writes, phase by phase, the contiguous runs of `in` words that v contributes to
+// every phase plane -- full-sector stores, no gather from global memory.
+struct QuadArgs {
+  const uint8_t* level[CSM_MAX_DEPTH];
+  uint32_t* quad[CSM_MAX_DEPTH];
+  int in[CSM_MAX_DEPTH], jn[CSM_MAX_DEPTH];
+  int num_x, num_y, depth;
+};
+
+__global__ void __launch_bounds__(kThreads)
+k_stack_quad_rows(const QuadArgs a) {
+  extern __shared__ uint8_t rows8[];
+  const int i = blockIdx.y;
+  const int s = 1 << i, two_s = 2 << i, sh = i + 1;
+  const int in = a.in[i], jn = a.jn[i];
+  const int v = blockIdx.x;
+  if (v >= jn * two_s) return;
+  const int wide_x = a.num_x + s - 1, wide_y = a.num_y + s - 1;
+  const int span = in * two_s;          // u range of the plane rows
+  const int pitch = (span + s + 3) & ~3;  // staged row: s zero cells, then X = 0 .. span-1
+  uint8_t* cur = rows8;                 // Y = v
+  uint8_t* up = rows8 + pitch;          // Y = v - s
+  const uint8_t* lvl = a.level[i];
+  for (int r = 0; r < 2; ++r) {
+    const int Y = r == 0 ? v : v - s;
+    uint8_t* dst = r == 0 ? cur : up;
+    const bool row_ok = static_cast<unsigned>(Y) < static_cast<unsigned>(wide_y);
+    const uint8_t* src = lvl + static_cast<size_t>(row_ok ? Y : 0) * wide_x;
+    for (int x = threadIdx.x; x < pitch; x += kThreads) {
+      const int X = x - s;
+      dst[x] = (row_ok && static_cast<unsigned>(X) < static_cast<unsigned>(wide_x)) ? __ldg(src + X)
+                                                                                    : static_cast<uint8_t>(0);
+    }
+  }
+  __syncthreads();
+  uint32_t* out = a.quad[i];
+  const size_t rowbase = (static_cast<size_t>((v & (two_s - 1)) << sh) * jn + (v >> sh)) * in;
+  const size_t plane = static_cast<size_t>(in) * jn;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (i >= 2) {
+    // Four adjacent phases per thread from four aligned shared-memory words: a 4x4 byte
+    // transpose gives the four quad words; a warp's lanes walk ii, so every store is one
+    // contiguous run inside a phase plane.
+    const uint32_t* cur32 = reinterpret_cast<const uint32_t*>(cur);
+    const uint32_t* up32 = reinterpret_cast<const uint32_t*>(up);
+    const int sw = s >> 2, pitch_ok = pitch;  // pitch is a multiple of 4 => `up` is word-aligned
+    (void)pitch_ok;
+    for (int pg = warp; pg < (two_s >> 2); pg += kThreads / 32) {  // group of 4 phases
+      uint32_t* o = out + rowbase + static_cast<size_t>(pg << 2) * plane;
+      for (int ii = lane; ii < in; ii += 32) {
+        const int xw = ((ii << sh) + (pg << 2) + s) >> 2;  // staged word index of X = u
+        const uint32_t c0 = cur32[xw], l0 = cur32[xw - sw], c1 = up32[xw], l1 = up32[xw - sw];
+        // q_j = l1.b_j | l0.b_j << 8 | c1.b_j << 16 | c0.b_j << 24
+        const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+        const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+        o[ii] = __byte_perm(a_lo, b_lo, 0x5410);
+        o[plane + ii] = __byte_perm(a_lo, b_lo, 0x7632);
+        o[2 * plane + ii] = __byte_perm(a_hi, b_hi, 0x5410);
+        o[3 * plane + ii] = __byte_perm(a_hi, b_hi, 0x7632);
+      }
+    }
+  } else {
+    for (int pu = 0; pu < two_s; ++pu) {
+      for (int ii = threadIdx.x; ii < in; ii += kThreads) {
+        const int x = (ii << sh) + pu + s;  // staged index of X = u
+        const uint32_t w = static_cast<uint32_t>(up[x - s]) | (static_cast<uint32_t>(cur[x - s]) << 8) |
+                           (static_cast<uint32_t>(up[x]) << 16) | (static_cast<uint32_t>(cur[x]) << 24);
+        out[rowbase + pu * plane + ii] = w;
+      }
+    }
+  }
+}
+
+struct FusedArgs {
+  const uint16_t* cells;
+  const uint8_t* q_lut;
+  uint8_t* level[kFusedMaxDepth];
+  uint32_t* quad[kFusedMaxDepth];
+  int in[kFusedMaxDepth], jn[kFusedMaxDepth];
+  int num_x, num_y, depth;
+};
+
+__global__ void __launch_bounds__(kFusedThreads)
+k_stack_fused(const FusedArgs a) {
+  extern __shared__ uint32_t smem32[];
+  // Region = tile plus a low-side halo of P = 2^(depth-1) cells: one more than the
+  // widest window needs, which keeps the tile word-aligned inside the region.
+  const int P = a.depth >= 3 ? (1 << (a.depth - 1)) : 4;
+  const int R = kFusedTile + P;  // region side in bytes, a multiple of 4
+  const int Rw = R >> 2;         // words per region row
+  uint32_t* bufA = smem32;
+  uint32_t* bufB = smem32 + Rw * R;
+  const int X0 = blockIdx.x * kFusedTile, Y0 = blockIdx.y * kFusedTile;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kFusedThreads / 32;
+
+  // level 0 of the region: LUT[cell], 0 outside the grid.  Row staging: a warp takes a
+  // region row, issues all its cell loads, then all LUT loads, then the stores, so
+  // the two dependent global loads are pipelined across the row instead of serialised.
+  {
+    uint8_t* A8 = reinterpret_cast<uint8_t*>(bufA);
+    constexpr int kMaxPerLane = (kFusedTile + (1 << (kFusedMaxDepth - 1))) / 32;  // 4
+    for (int ry = warp; ry < R; ry += kWarps) {
+      const int y = Y0 - P + ry;
+      const bool row_ok = static_cast<unsigned>(y) < static_cast<unsigned>(a.num_y);
+      const uint16_t* crow = a.cells + static_cast<size_t>(row_ok ? y : 0) * a.num_x;
+      uint16_t c[kMaxPerLane];
+      bool ok[kMaxPerLane];
+#pragma unroll
+      for (int k = 0; k < kMaxPerLane; ++k) {
+        const int rx = lane + 32 * k;
+        const int x = X0 - P + rx;
+        ok[k] = row_ok && rx < R && static_cast<unsigned>(x) < static_cast<unsigned>(a.num_x);
+        c[k] = ok[k] ? __ldg(crow + x) : static_cast<uint16_t>(0);
+      }
+      uint8_t v[kMaxPerLane];
+#pragma unroll
+      for (int k = 0; k < kMaxPerLane; ++k) v[k] = ok[k] ? __ldg(a.q_lut + c[k]) : static_cast<uint8_t>(0);
+#pragma unroll
+      for (int k = 0; k < kMaxPerLane; ++k) {
+        const int rx = lane + 32 * k;
+        if (rx < R) A8[ry * R + rx] = v[k];
+      }
+    }
+  }
+  __syncthreads();
+
+  for (int i = 0; i < a.depth; ++i) {
+    const int h = 1 << i;
+    // (a) the tile's bytes of level i
+    {
+      const uint8_t* A8 = reinterpret_cast<const uint8_t*>(bufA);
+      const int wide_x = a.num_x + h - 1, wide_y = a.num_y + h - 1;
+      uint8_t* out = a.level[i];
+      for (int e = tid; e < kFusedTile * kFusedTile; e += kFusedThreads) {
+        const int lx = e & (kFusedTile - 1), ly = e >> kFusedLogTile;
+        const int X = X0 + lx, Y = Y0 + ly;
+        if (X < wide_x && Y < wide_y)
+          out[static_cast<size_t>(Y) * wide_x + X] = A8[(P + ly) * R + P + lx];
+      }
+    }
+    // Tap words of level i for the word k of region row ry: c = (X, .), l = (X - h, .),
+    // rows ry and ry - h.  Reads that fall before the row start land in the previous
+    // row's tail: they only feed cells inside the halo's unusable low margin (rx < h).
+    const int hw = h >> 2;  // tap distance in words when h >= 4
+    auto taps = [&](int ry, int k, uint32_t& c0, uint32_t& l0, uint32_t& c1, uint32_t& l1) {
+      const uint32_t* row = bufA + ry * Rw + k;
+      const uint32_t* up = row - h * Rw;
+      c0 = row[0];
+      c1 = up[0];
+      if (h >= 4) {
+        l0 = row[-hw];
+        l1 = up[-hw];
+      } else {
+        l0 = __funnelshift_l(row[-1], c0, 8 * h);
+        l1 = __funnelshift_l(up[-1], c1, 8 * h);
+      }
+    };
+    const bool make_next = i + 1 < a.depth;
+    if (make_next) {
+      // (c) level i+1 of the whole region: byte-wise max of the tap words
+      for (int ry = h + warp; ry < R; ry += kWarps) {
+        for (int k = lane; k < Rw; k += 32) {
+          if (ry == h && k < (hw > 0 ? hw : 1)) continue;  // would read before the buffer
+          uint32_t c0, l0, c1, l1;
+          taps(ry, k, c0, l0, c1, l1);
+          bufB[ry * Rw + k] = max4_u8x4(c0, l0, c1, l1);
+        }
+      }
+    }
+    __syncthreads();
+    uint32_t* t = bufA;
+    bufA = bufB;
+    bufB = t;
+  }
+}
+
+int launch_build_fused(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  FusedArgs a;
+  memset(&a, 0, sizeof(a));
+  a.cells = cells_dev;
+  a.q_lut = s->q_lut_dev;
+  a.num_x = s->num_x;
+  a.num_y = s->num_y;
+  a.depth = s->depth;
+  for (int i = 0; i < s->depth; ++i) {
+    a.level[i] = s->base + s->level_off[i];
+    a.quad[i] = reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]);
+    a.in[i] = s->host_view.in[i];
+    a.jn[i] = s->host_view.jn[i];
+  }
+  // Tiles cover the widest byte level.
+  const int ext_x = s->num_x + (1 << (s->depth - 1)) - 1, ext_y = s->num_y + (1 << (s->depth - 1)) - 1;
+  const int R = kFusedTile + (s->depth >= 3 ? (1 << (s->depth - 1)) : 4);
+  const size_t smem = static_cast<size_t>(2) * (R / 4) * R * sizeof(uint32_t);
+  {  // per device, cheap: allow the 128 KB of dynamic shared memory
+    constexpr int kMaxR = kFusedTile + (1 << (kFusedMaxDepth - 1));
+    CSM_CUDA(cudaFuncSetAttribute(k_stack_fused, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  2 * (kMaxR / 4) * kMaxR * 4));
+  }
+  dim3 grid((ext_x + kFusedTile - 1) / kFusedTile, (ext_y + kFusedTile - 1) / kFusedTile);
+  ++ctx->launches, k_stack_fused<<<grid, kFusedThreads, smem, ctx->stream>>>(a);
+  {  // every quad-phase level from the byte levels
+    QuadArgs q;
+    memset(&q, 0, sizeof(q));
+    q.num_x = s->num_x;
+    q.num_y = s->num_y;
+    q.depth = s->depth;
+    int max_v = 0;
+    size_t max_pitch = 0;
+    for (int i = 0; i < s->depth; ++i) {
+      q.level[i] = a.level[i];
+      q.quad[i] = a.quad[i];
+      q.in[i] = a.in[i];
+      q.jn[i] = a.jn[i];
+      max_v = std::max(max_v, a.jn[i] << (i + 1));
+      max_pitch = std::max<size_t>(max_pitch, (static_cast<size_t>(a.in[i]) << (i + 1)) + (1 << i) + 4);
+    }
+    const size_t qsmem = 2 * max_pitch;
+    CSM_CUDA(cudaFuncSetAttribute(k_stack_quad_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(std::max<size_t>(qsmem, 48 * 1024))));
+    ++ctx->launches, k_stack_quad_rows<<<dim3(max_v, s->depth), kThreads, qsmem, ctx->stream>>>(q);
+  }
+  CSM_CUDA(cudaGetLastError());
+  return CSM_OK;
+}
+
+int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev);
+
 int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  // Deep stacks (2^depth halo does not fit shared memory) and CSM_STACK_BUILD=levelwise
+  // take the one-launch-per-level path.
+  static const bool force_levelwise = [] {
+    const char* e = getenv("CSM_STACK_BUILD");
+    return e != nullptr && strcmp(e, "levelwise") == 0;
+  }();
+  if (s->depth <= kFusedMaxDepth && !force_levelwise) return launch_build_fused(ctx, s, cells_dev);
+  return launch_build_levelwise(ctx, s, cells_dev);
+}
+
+int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const size_t n = static_cast<size_t>(s->num_x) * s->num_y;
   int blocks = static_cast<int>(std::min<size_t>((n / 4 + kThreads - 1) / kThreads + 1,
                                                  static_cast<size_t>(ctx->num_sms) * 8));
