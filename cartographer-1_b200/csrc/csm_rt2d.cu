@@ -28,15 +28,23 @@ struct RtJobDev {
   float oob;
 };
 
-__global__ void __launch_bounds__(256)
+// One warp per (job, scan); a block carries kRtWarps scans of one job.  The scan is
+// rotated and discretised into the warp's slice of shared memory, then each lane
+// scores candidates (lane, lane + 32, ...).  The fp32 sum runs in point order exactly
+// like the CPU loop; the loads of 8 points are issued together ahead of their adds so
+// that the two dependent reads (cell, then table) are pipelined, not serialised.
+constexpr int kRtWarps = 8;
+__global__ void __launch_bounds__(kRtWarps * 32)
 k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
-           const float* __restrict__ quats, unsigned long long* __restrict__ best) {
-  extern __shared__ int2 cell[];
+           const float* __restrict__ quats, unsigned long long* __restrict__ best, int max_n) {
+  extern __shared__ int2 cell_all[];
   const RtJobDev& j = jobs[blockIdx.y];
-  const int scan = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int scan = blockIdx.x * kRtWarps + warp;
   if (scan >= j.S) return;
+  int2* cell = cell_all + static_cast<size_t>(warp) * max_n;
   const float qw = quats[2 * (j.quat_off + scan)], qs = quats[2 * (j.quat_off + scan) + 1];
-  for (int p = threadIdx.x; p < j.n; p += blockDim.x) {
+  for (int p = lane; p < j.n; p += 32) {
     float vx = points[3 * (j.pts_off + p)], vy = points[3 * (j.pts_off + p) + 1];
     yaw_rotate(j.q0w, j.q0s, vx, vy);  // RT2D.cc:124-127
     yaw_rotate(qw, qs, vx, vy);
@@ -45,23 +53,31 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
     cell_index(j.max_x, j.max_y, j.res, wx, wy, cx, cy);
     cell[p] = make_int2(cx, cy);
   }
-  __syncthreads();
+  __syncwarp();
   const int side = 2 * j.lin + 1;
   const int count = side * side;
   const float n_float = static_cast<float>(j.n);
   unsigned long long local = 0ull;
-  for (int c = threadIdx.x; c < count; c += blockDim.x) {
+  for (int c = lane; c < count; c += 32) {
     const int x = c / side - j.lin, y = c % side - j.lin;  // x outer, y inner (RT2D.cc:100-112)
     float sum = 0.f;
-    for (int p = 0; p < j.n; ++p) {
-      const int px = cell[p].x + x, py = cell[p].y + y;
-      float prob = j.oob;
-      if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
-          static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
-        const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
-        prob = __fsub_rn(1.f, __ldg(j.cost_table + v));
+    for (int p0 = 0; p0 < j.n; p0 += 8) {
+      float prob[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        prob[k] = j.oob;
+        if (p0 + k < j.n) {
+          const int px = cell[p0 + k].x + x, py = cell[p0 + k].y + y;
+          if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
+              static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
+            const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
+            prob[k] = __fsub_rn(1.f, __ldg(j.cost_table + v));
+          }
+        }
       }
-      sum = __fadd_rn(sum, prob);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (p0 + k < j.n) sum = __fadd_rn(sum, prob[k]);
     }
     float score = __fdiv_rn(sum, n_float);
     const unsigned int cand = static_cast<unsigned int>(scan) * count + c;
@@ -72,7 +88,7 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) local = max(local, __shfl_xor_sync(0xFFFFFFFFu, local, o));
-  if ((threadIdx.x & 31) == 0 && local != 0ull) atomicMax(&best[blockIdx.y], local);
+  if (lane == 0 && local != 0ull) atomicMax(&best[blockIdx.y], local);
 }
 
 }  // namespace csm
@@ -129,8 +145,8 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     max_scans = std::max(max_scans, in.num_scans);
     max_n = std::max(max_n, in.num_points);
   }
-  const size_t smem = sizeof(int2) * static_cast<size_t>(max_n);
-  CSM_REQUIRE(smem <= 200 * 1024, "point cloud too large for the real-time matcher (25600 points)");
+  const size_t smem = sizeof(int2) * static_cast<size_t>(max_n) * kRtWarps;
+  CSM_REQUIRE(smem <= 200 * 1024, "point cloud too large for the real-time matcher (3200 points)");
   const size_t o_jobs = 0;
   const size_t o_pts = o_jobs + up(sizeof(RtJobDev) * num_jobs);
   const size_t o_quat = o_pts + up(sizeof(float) * 3 * n_pts);
@@ -173,10 +189,10 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   CSM_CUDA(cudaMemcpyAsync(base, pin, total, cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaFuncSetAttribute(k_rt_score, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(std::max<size_t>(smem, 1024))));
-  ++ctx->launches, k_rt_score<<<dim3(max_scans, num_jobs), 256, smem, st>>>(
+  ++ctx->launches, k_rt_score<<<dim3((max_scans + kRtWarps - 1) / kRtWarps, num_jobs), kRtWarps * 32, smem, st>>>(
       reinterpret_cast<const RtJobDev*>(base + o_jobs), reinterpret_cast<const float*>(base + o_pts),
       reinterpret_cast<const float*>(base + o_quat),
-      reinterpret_cast<unsigned long long*>(base + o_best));
+      reinterpret_cast<unsigned long long*>(base + o_best), max_n);
   CSM_CUDA(cudaGetLastError());
   unsigned long long* best = reinterpret_cast<unsigned long long*>(pin + o_best);
   CSM_CUDA(cudaMemcpyAsync(best, base + o_best, sizeof(unsigned long long) * num_jobs,

@@ -107,14 +107,39 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
       xyz[i][3 * p + 2] = v.z();
     }
     quats[i] = sp.ScanQuaternionTable();
-    // Motion penalty per candidate, generation order (reference :170-174), fp64.
-    const std::vector<Candidate2D> candidates = GenerateExhaustiveSearchCandidates(sp);
-    penalty[i].resize(candidates.size());
-    for (size_t c = 0; c != candidates.size(); ++c) {
-      const double t =
-          std::hypot(candidates[c].x, candidates[c].y) * options_.translation_delta_cost_weight() +
-          std::abs(candidates[c].orientation) * options_.rotation_delta_cost_weight();
-      penalty[i][c] = std::exp(-(t * t));
+    // Motion penalty per candidate, generation order scan -> x -> y (reference :100-112,
+    // :170-174), fp64: exp(-(hypot(x, y) * w_t + |orientation| * w_r)^2) with
+    // x = -y_offset * resolution, y = -x_offset * resolution and orientation =
+    // (scan - num_angular_perturbations) * step.  The value depends only on
+    // (|x_offset|, |y_offset|, |scan - nap|), so it is evaluated once per distinct
+    // triple with exactly the reference's operations and copied to the mirror images.
+    {
+      const int lin = sp.linear_bounds[0].max_x;
+      const int side = 2 * lin + 1;
+      const int nap = sp.num_angular_perturbations;
+      std::vector<double> reach(static_cast<size_t>(lin + 1) * (lin + 1));
+      for (int ax = 0; ax <= lin; ++ax)
+        for (int ay = 0; ay <= lin; ++ay) {
+          const Candidate2D c(nap, ax, ay, sp);
+          reach[ax * (lin + 1) + ay] = std::hypot(c.x, c.y) * options_.translation_delta_cost_weight();
+        }
+      std::vector<double> table(static_cast<size_t>(nap + 1) * reach.size());
+      for (int a = 0; a <= nap; ++a) {
+        const Candidate2D c(nap + a, 0, 0, sp);
+        const double turn = std::abs(c.orientation) * options_.rotation_delta_cost_weight();
+        for (size_t k = 0; k != reach.size(); ++k) {
+          const double t = reach[k] + turn;
+          table[a * reach.size() + k] = std::exp(-(t * t));
+        }
+      }
+      penalty[i].resize(static_cast<size_t>(sp.num_scans) * side * side);
+      size_t at = 0;
+      for (int scan = 0; scan != sp.num_scans; ++scan) {
+        const double* row = table.data() + static_cast<size_t>(std::abs(scan - nap)) * reach.size();
+        for (int x = -lin; x <= lin; ++x)
+          for (int y = -lin; y <= lin; ++y)
+            penalty[i][at++] = row[std::abs(x) * (lin + 1) + std::abs(y)];
+      }
     }
     csm_rt_job2d& job = jobs[i];
     std::memset(&job, 0, sizeof(job));
