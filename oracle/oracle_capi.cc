@@ -6,6 +6,7 @@
 
 #include "cpu_pool.h"
 #include "csm_oracle.h"
+#include "csm_oracle3d.h"
 
 using namespace oracle;
 
@@ -256,6 +257,172 @@ double oracle_constraint_batch(int num_threads, void* const* grids, const double
   }
   for (int i = 0; i < num_submaps; ++i) builder.DeleteScanMatcher(i);
   return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// --- 3D path ---------------------------------------------------------------------
+struct oracle_result3d {
+  int32_t found, scan_index, offset[3], num_scans;
+  float score, rotational_score, low_resolution_score;
+  float pose[7];  // tx, ty, tz, qw, qx, qy, qz
+  uint64_t candidates_scored;
+};
+
+void* oracle_grid3d_create(float resolution, const int32_t* xyz, const uint16_t* values, int n) {
+  HybridGrid* g = new HybridGrid(resolution);
+  for (int i = 0; i < n; ++i)
+    *g->mutable_value(Array3i{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}) = values[i];
+  return g;
+}
+void oracle_grid3d_destroy(void* g) { delete static_cast<HybridGrid*>(g); }
+// RangeDataInserter3D::Insert of one range data (test fixture builder).
+void oracle_grid3d_insert(void* g, const float* origin3, const float* returns, int n, float hit_probability,
+                          float miss_probability, int num_free_space_voxels) {
+  std::vector<Vec3f> r;
+  for (int i = 0; i < n; ++i) r.push_back(Vec3f{returns[3 * i], returns[3 * i + 1], returns[3 * i + 2]});
+  RangeDataInserter3D(hit_probability, miss_probability, num_free_space_voxels)
+      .Insert(Vec3f{origin3[0], origin3[1], origin3[2]}, r, static_cast<HybridGrid*>(g));
+}
+// Stored cells with a non-zero value, as the reference's HybridGrid::Iterator visits
+// them (hybrid_grid.h:327-419 skips default values); NULL outputs: count only.
+int oracle_grid3d_cells(void* g, int32_t* xyz, uint16_t* values) {
+  int n = 0;
+  static_cast<HybridGrid*>(g)->ForEach([&](const Array3i& i, uint16_t v) {
+    if (v == 0) return;
+    if (xyz != nullptr) {
+      xyz[3 * n] = i.x;
+      xyz[3 * n + 1] = i.y;
+      xyz[3 * n + 2] = i.z;
+      values[n] = v;
+    }
+    ++n;
+  });
+  return n;
+}
+int oracle_grid3d_size(void* g) { return static_cast<HybridGrid*>(g)->grid_size(); }
+
+static FastCorrelativeScanMatcherOptions3D Options3D(const double* o7) {
+  FastCorrelativeScanMatcherOptions3D o;
+  o.branch_and_bound_depth = static_cast<int>(o7[0]);
+  o.full_resolution_depth = static_cast<int>(o7[1]);
+  o.min_rotational_score = o7[2];
+  o.min_low_resolution_score = o7[3];
+  o.linear_xy_search_window = o7[4];
+  o.linear_z_search_window = o7[5];
+  o.angular_search_window = o7[6];
+  return o;
+}
+
+struct Matcher3DHolder {
+  Histogram submap_histogram;
+  std::unique_ptr<FastCorrelativeScanMatcher3D> matcher;
+};
+
+void* oracle_fcsm3d_create(void* grid, void* low_grid, const float* hist, int n_hist,
+                           const double* options7) {
+  Matcher3DHolder* h = new Matcher3DHolder;
+  h->submap_histogram.assign(hist, hist + n_hist);
+  h->matcher.reset(new FastCorrelativeScanMatcher3D(*static_cast<HybridGrid*>(grid),
+                                                    static_cast<HybridGrid*>(low_grid),
+                                                    &h->submap_histogram, Options3D(options7)));
+  return h;
+}
+void oracle_fcsm3d_destroy(void* m) { delete static_cast<Matcher3DHolder*>(m); }
+
+// Dense copy of precomputation level `level`: first call with out == NULL fills the
+// bounding box (lo/hi inclusive over stored cells, all zero if the level is empty).
+int oracle_fcsm3d_level(void* m, int level, int32_t* lo3, int32_t* hi3, uint8_t* out) {
+  const PrecomputationGrid3D& g = static_cast<Matcher3DHolder*>(m)->matcher->stack().Get(level);
+  if (out == nullptr) {
+    bool first = true;
+    g.ForEach([&](const Array3i& i, uint8_t) {
+      const int v[3] = {i.x, i.y, i.z};
+      for (int k = 0; k < 3; ++k) {
+        lo3[k] = first ? v[k] : std::min(lo3[k], v[k]);
+        hi3[k] = first ? v[k] : std::max(hi3[k], v[k]);
+      }
+      first = false;
+    });
+    if (first) for (int k = 0; k < 3; ++k) lo3[k] = hi3[k] = 0;
+    return static_cast<int>(g.size());
+  }
+  const int64_t nx = hi3[0] - lo3[0] + 1, ny = hi3[1] - lo3[1] + 1, nz = hi3[2] - lo3[2] + 1;
+  std::fill(out, out + nx * ny * nz, uint8_t(0));
+  g.ForEach([&](const Array3i& i, uint8_t v) {
+    if (i.x < lo3[0] || i.x > hi3[0] || i.y < lo3[1] || i.y > hi3[1] || i.z < lo3[2] || i.z > hi3[2]) return;
+    out[((i.z - lo3[2]) * ny + (i.y - lo3[1])) * nx + (i.x - lo3[0])] = v;
+  });
+  return static_cast<int>(g.size());
+}
+
+static NodeData3D MakeNode(const float* hi, int n_hi, const float* lo, int n_lo, const float* hist,
+                           int n_hist, const double* gravity4) {
+  NodeData3D d;
+  for (int i = 0; i < n_hi; ++i) d.high_resolution_point_cloud.push_back(Vec3f{hi[3 * i], hi[3 * i + 1], hi[3 * i + 2]});
+  for (int i = 0; i < n_lo; ++i) d.low_resolution_point_cloud.push_back(Vec3f{lo[3 * i], lo[3 * i + 1], lo[3 * i + 2]});
+  d.rotational_scan_matcher_histogram.assign(hist, hist + n_hist);
+  for (int k = 0; k < 4; ++k) d.gravity_alignment[k] = gravity4[k];
+  return d;
+}
+static Rigid3f Pose7(const float* p) {
+  Rigid3f r;
+  r.t = Vec3f{p[0], p[1], p[2]};
+  r.q = Quat4f{p[3], p[4], p[5], p[6]};
+  return r;
+}
+
+// full != 0: MatchFullSubmap with the rotations of node_pose7 / submap_pose7.
+void oracle_fcsm3d_match(void* m, int full, const float* node_pose7, const float* submap_pose7,
+                         const float* hi, int n_hi, const float* lo, int n_lo, const float* hist,
+                         int n_hist, const double* gravity4, float min_score, oracle_result3d* out) {
+  const FastCorrelativeScanMatcher3D& matcher = *static_cast<Matcher3DHolder*>(m)->matcher;
+  const NodeData3D d = MakeNode(hi, n_hi, lo, n_lo, hist, n_hist, gravity4);
+  const Result3D r = full ? matcher.MatchFullSubmap(Pose7(node_pose7).q, Pose7(submap_pose7).q, d, min_score)
+                          : matcher.Match(Pose7(node_pose7), Pose7(submap_pose7), d, min_score);
+  *out = oracle_result3d{};
+  out->found = r.found ? 1 : 0;
+  out->scan_index = r.scan_index;
+  out->offset[0] = r.offset.x;
+  out->offset[1] = r.offset.y;
+  out->offset[2] = r.offset.z;
+  out->num_scans = r.num_scans;
+  out->score = r.score;
+  out->rotational_score = r.rotational_score;
+  out->low_resolution_score = r.low_resolution_score;
+  const float p[7] = {r.pose_estimate.t.x, r.pose_estimate.t.y, r.pose_estimate.t.z, r.pose_estimate.q.w,
+                      r.pose_estimate.q.x, r.pose_estimate.q.y, r.pose_estimate.q.z};
+  for (int k = 0; k < 7; ++k) out->pose[k] = p[k];
+  out->candidates_scored = r.candidates_scored;
+}
+
+// Discrete scans of a local Match: returns the number of surviving scans; with non-NULL
+// outputs fills poses (S x 7), rotational scores (S) and full-resolution cell indices
+// (S x n_hi x 3).
+int oracle_fcsm3d_discrete_scans(void* m, const double* options7, float resolution,
+                                 const float* node_pose7, const float* submap_pose7, const float* hi,
+                                 int n_hi, const float* hist, int n_hist, const double* gravity4,
+                                 float* poses, float* rot_scores, int32_t* cells) {
+  const FastCorrelativeScanMatcher3D& matcher = *static_cast<Matcher3DHolder*>(m)->matcher;
+  const FastCorrelativeScanMatcherOptions3D o = Options3D(options7);
+  const NodeData3D d = MakeNode(hi, n_hi, nullptr, 0, hist, n_hist, gravity4);
+  const FastCorrelativeScanMatcher3D::SearchParameters sp{
+      RoundToInt(o.linear_xy_search_window / resolution), RoundToInt(o.linear_z_search_window / resolution),
+      o.angular_search_window};
+  const auto scans = matcher.GenerateDiscreteScans(sp, d, Pose7(node_pose7), Pose7(submap_pose7));
+  if (poses != nullptr) {
+    for (size_t s = 0; s != scans.size(); ++s) {
+      const Rigid3f& p = scans[s].pose;
+      const float v[7] = {p.t.x, p.t.y, p.t.z, p.q.w, p.q.x, p.q.y, p.q.z};
+      for (int k = 0; k < 7; ++k) poses[7 * s + k] = v[k];
+      rot_scores[s] = scans[s].rotational_score;
+      for (int i = 0; i < n_hi; ++i) {
+        const Array3i& c = scans[s].cell_indices_per_depth[0][i];
+        cells[(s * n_hi + i) * 3] = c.x;
+        cells[(s * n_hi + i) * 3 + 1] = c.y;
+        cells[(s * n_hi + i) * 3 + 2] = c.z;
+      }
+    }
+  }
+  return static_cast<int>(scans.size());
 }
 
 }  // extern "C"

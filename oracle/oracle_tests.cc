@@ -11,6 +11,7 @@
 
 #include "cpu_pool.h"
 #include "csm_oracle.h"
+#include "csm_oracle3d.h"
 
 namespace {
 
@@ -435,6 +436,185 @@ void TestStackEqualsQuantisedWindowMax() {
   }
 }
 
+// ---- 3D ---------------------------------------------------------------------
+// precomputation_grid_3d_test.cc:33-69 (TestAgainstNaiveAlgorithm)
+void TestPrecomputeGrid3DAgainstNaive() {
+  HybridGrid hybrid_grid(2.f);
+  std::mt19937 rng(23847);
+  std::uniform_int_distribution<int> coordinate_distribution(-50, 49);
+  std::uniform_real_distribution<float> value_distribution(kMinProbability, kMaxProbability);
+  for (int i = 0; i < 1000; ++i) {
+    const auto x = coordinate_distribution(rng);
+    const auto y = coordinate_distribution(rng);
+    const auto z = coordinate_distribution(rng);
+    hybrid_grid.SetProbability(Array3i{x, y, z}, value_distribution(rng));
+  }
+  std::vector<PrecomputationGrid3D> grids;
+  grids.push_back(ConvertToPrecomputationGrid(hybrid_grid));
+  for (int depth = 1; depth <= 3; ++depth) {
+    const int s = 1 << (depth - 1);
+    grids.push_back(PrecomputeGrid(grids.back(), false, Array3i{s, s, s}));
+  }
+  for (int depth = 0; depth <= 3; ++depth) {
+    const int width = 1 << depth;
+    for (int i = 0; i < 100; ++i) {
+      const auto x = coordinate_distribution(rng);
+      const auto y = coordinate_distribution(rng);
+      const auto z = coordinate_distribution(rng);
+      float max_probability = 0.f;
+      for (int dx = 0; dx < width; ++dx)
+        for (int dy = 0; dy < width; ++dy)
+          for (int dz = 0; dz < width; ++dz)
+            max_probability =
+                std::max(max_probability, hybrid_grid.GetProbability(Array3i{x + dx, y + dy, z + dz}));
+      EXPECT_NEAR(max_probability, ToProbability3D(grids[depth].value(Array3i{x, y, z})), 1e-2);
+    }
+  }
+}
+
+// rotational_scan_matcher_test.cc:29-43
+void TestRotationalOnlySameHistogramIsScoreOne() {
+  const Histogram histogram{1.f, 43.f, 0.5f, 0.3123f, 23.f, 42.f, 0.f};
+  const std::vector<float> scores = RotationalMatch(histogram, histogram, 0.f, {0.f, 1.f});
+  EXPECT_EQ(scores.size(), size_t{2});
+  EXPECT_NEAR(1.f, scores[0], 1e-6);
+  EXPECT_LT(scores[1], 1.f);
+}
+
+// rotational_scan_matcher_test.cc:45-66
+void TestRotationalInterpolatesAsExpected() {
+  constexpr int kNumBuckets = 10;
+  constexpr float kAnglePerBucket = M_PI / kNumBuckets;
+  constexpr float kNoInitialRotation = 0.f;
+  Histogram unit3(kNumBuckets, 0.f), unit2(kNumBuckets, 0.f);
+  unit3[3] = 1.f;
+  unit2[2] = 1.f;
+  for (float t = 0.f; t < 1.f; t += 0.1f) {
+    // 't' is the fraction of overlap and we have to divide by the norm of the
+    // histogram to get the expected score.
+    const float expected_score = t / std::hypot(t, 1 - t);
+    // We rotate the 't'-th fraction of a bucket into the matcher's histogram.
+    const std::vector<float> scores =
+        RotationalMatch(unit3, unit2, kNoInitialRotation, {t * kAnglePerBucket});
+    EXPECT_EQ(scores.size(), size_t{1});
+    EXPECT_NEAR(expected_score, scores[0], 1e-6);
+  }
+}
+
+// low_resolution_matcher (low_resolution_matcher.cc:23-35): a point in a painted cell
+// scores that cell's probability, unknown space kMinProbability.
+void TestLowResolutionScore() {
+  HybridGrid grid(0.5f);
+  grid.SetProbability(Array3i{2, 0, 0}, 0.8f);
+  Rigid3f identity;
+  EXPECT_NEAR(LowResolutionScore(grid, {Vec3f{1.f, 0.f, 0.f}}, identity), 0.8f, 1e-4);
+  EXPECT_NEAR(LowResolutionScore(grid, {Vec3f{1.f, 0.f, 0.f}, Vec3f{-3.f, 0.f, 0.f}}, identity),
+              0.5f * (0.8f + kMinProbability), 1e-4);
+}
+
+// fast_correlative_scan_matcher_3d_test.cc:35-205
+class Fcsm3DFixture {
+ public:
+  Fcsm3DFixture() : inserter_(0.7f, 0.4f, 5), histogram_(10, 0.f) {
+    for (int axis = 0; axis != 3; ++axis)
+      for (const float d : {4.f, 4.5f, 5.f, 5.5f}) {
+        Vec3f p{0.f, 0.f, 0.f};
+        (axis == 0 ? p.x : axis == 1 ? p.y : p.z) = d;
+        point_cloud_.push_back(p);
+      }
+    options_.branch_and_bound_depth = 6;
+    options_.full_resolution_depth = 6;
+    options_.min_rotational_score = 0.1;
+    options_.min_low_resolution_score = 0.15;
+    options_.linear_xy_search_window = 0.8;
+    options_.linear_z_search_window = 0.8;
+    options_.angular_search_window = 0.3;
+  }
+  Rigid3f GetRandomPose() {
+    const float x = 0.7f * distribution_(prng_);
+    const float y = 0.7f * distribution_(prng_);
+    const float z = 0.7f * distribution_(prng_);
+    const float theta = 0.2f * distribution_(prng_);
+    Rigid3f pose;
+    pose.t = Vec3f{x, y, z};
+    pose.q = Quat4f{std::cos(0.5f * theta), 0.f, 0.f, std::sin(0.5f * theta)};
+    return pose;
+  }
+  std::unique_ptr<FastCorrelativeScanMatcher3D> GetMatcher(const Rigid3f& pose) {
+    hybrid_grid_.reset(new HybridGrid(0.05f));
+    std::vector<Vec3f> returns;
+    for (const Vec3f& p : point_cloud_) returns.push_back(Apply(pose, p));
+    inserter_.Insert(pose.t, returns, hybrid_grid_.get());
+    return std::unique_ptr<FastCorrelativeScanMatcher3D>(
+        new FastCorrelativeScanMatcher3D(*hybrid_grid_, hybrid_grid_.get(), &histogram_, options_));
+  }
+  NodeData3D CreateConstantData(const std::vector<Vec3f>& low_resolution_point_cloud) const {
+    NodeData3D d;
+    d.high_resolution_point_cloud = point_cloud_;
+    d.low_resolution_point_cloud = low_resolution_point_cloud;
+    d.rotational_scan_matcher_histogram = histogram_;
+    return d;
+  }
+  const std::vector<Vec3f>& point_cloud() const { return point_cloud_; }
+
+ private:
+  std::mt19937 prng_ = std::mt19937(42);
+  std::uniform_real_distribution<float> distribution_ =
+      std::uniform_real_distribution<float>(-1.f, 1.f);
+  RangeDataInserter3D inserter_;
+  FastCorrelativeScanMatcherOptions3D options_;
+  std::vector<Vec3f> point_cloud_;
+  std::unique_ptr<HybridGrid> hybrid_grid_;
+  Histogram histogram_;
+};
+
+// transform::IsNearly(rigid, 0.05f) of rigid_transform_test_helpers.h: translation and
+// rotation (as the angle of the relative quaternion) both within the bound.
+bool PoseIsNearly(const Rigid3f& a, const Rigid3f& b, const float eps) {
+  const float dt = Norm3(Vec3f{a.t.x - b.t.x, a.t.y - b.t.y, a.t.z - b.t.z});
+  const Quat4f d = QuatMul(QuatInverse(a.q), b.q);
+  const float angle = 2.f * std::atan2(std::sqrt(d.x * d.x + d.y * d.y + d.z * d.z), std::abs(d.w));
+  return dt < eps && angle < eps;
+}
+
+void TestFcsm3DCorrectPoseForMatch(const int iterations) {
+  Fcsm3DFixture f;
+  constexpr float kMinScore = 0.1f;
+  Rigid3f identity;
+  for (int i = 0; i != iterations; ++i) {
+    const Rigid3f expected_pose = f.GetRandomPose();
+    auto matcher = f.GetMatcher(expected_pose);
+    const Result3D result =
+        matcher->Match(identity, identity, f.CreateConstantData(f.point_cloud()), kMinScore);
+    EXPECT_TRUE(result.found);
+    EXPECT_LT(kMinScore, result.score);
+    EXPECT_LT(0.09f, result.rotational_score);
+    EXPECT_LT(0.14f, result.low_resolution_score);
+    EXPECT_TRUE(PoseIsNearly(expected_pose, result.pose_estimate, 0.05f));
+    const Result3D low_resolution_result =
+        matcher->Match(identity, identity, f.CreateConstantData({Vec3f{42.f, 42.f, 42.f}}), kMinScore);
+    EXPECT_TRUE(!low_resolution_result.found);
+  }
+}
+
+void TestFcsm3DCorrectPoseForMatchFullSubmap() {
+  Fcsm3DFixture f;
+  constexpr float kMinScore = 0.1f;
+  const Rigid3f expected_pose = f.GetRandomPose();
+  auto matcher = f.GetMatcher(expected_pose);
+  const Quat4f identity;
+  const Result3D result =
+      matcher->MatchFullSubmap(identity, identity, f.CreateConstantData(f.point_cloud()), kMinScore);
+  EXPECT_TRUE(result.found);
+  EXPECT_LT(kMinScore, result.score);
+  EXPECT_LT(0.09f, result.rotational_score);
+  EXPECT_LT(0.14f, result.low_resolution_score);
+  EXPECT_TRUE(PoseIsNearly(expected_pose, result.pose_estimate, 0.05f));
+  const Result3D low_resolution_result = matcher->MatchFullSubmap(
+      identity, identity, f.CreateConstantData({Vec3f{42.f, 42.f, 42.f}}), kMinScore);
+  EXPECT_TRUE(!low_resolution_result.found);
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -447,7 +627,13 @@ int main(int argc, char** argv) {
   TestRealTimeScores();
   TestStackEqualsQuantisedWindowMax();
   TestConstraintBuilderProtocol();
+  TestPrecomputeGrid3DAgainstNaive();
+  TestRotationalOnlySameHistogramIsScoreOne();
+  TestRotationalInterpolatesAsExpected();
+  TestLowResolutionScore();
+  TestFcsm3DCorrectPoseForMatch(quick ? 2 : 20);
   if (!quick) {
+    TestFcsm3DCorrectPoseForMatchFullSubmap();
     TestPrecomputationGridCorrectValues();
     TestFastCorrectPose();
     TestFastFullSubmapMatching();

@@ -30,8 +30,22 @@ class OracleResult2D(C.Structure):
     ]
 
 
+class OracleResult3D(C.Structure):
+    _fields_ = [
+        ("found", C.c_int32),
+        ("scan_index", C.c_int32),
+        ("offset", C.c_int32 * 3),
+        ("num_scans", C.c_int32),
+        ("score", C.c_float),
+        ("rotational_score", C.c_float),
+        ("low_resolution_score", C.c_float),
+        ("pose", C.c_float * 7),
+        ("candidates_scored", C.c_uint64),
+    ]
+
+
 def build_oracle(force=False):
-    srcs = [os.path.join(_ORACLE_DIR, f) for f in ("oracle_capi.cc", "csm_oracle.h", "cpu_pool.h")]
+    srcs = [os.path.join(_ORACLE_DIR, f) for f in ("oracle_capi.cc", "csm_oracle.h", "csm_oracle3d.h", "cpu_pool.h")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs)
     if force or stale:
@@ -81,6 +95,21 @@ def lib():
         C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
         C.POINTER(OracleResult2D), f64p]
     L.oracle_constraint_batch.restype = C.c_double
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    L.oracle_grid3d_create.argtypes = [C.c_float, i32p, u16p, C.c_int]
+    L.oracle_grid3d_create.restype = C.c_void_p
+    L.oracle_grid3d_destroy.argtypes = [C.c_void_p]
+    L.oracle_grid3d_size.argtypes = [C.c_void_p]
+    L.oracle_grid3d_insert.argtypes = [C.c_void_p, f32p, f32p, C.c_int, C.c_float, C.c_float, C.c_int]
+    L.oracle_grid3d_cells.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_fcsm3d_create.argtypes = [C.c_void_p, C.c_void_p, f32p, C.c_int, f64p]
+    L.oracle_fcsm3d_create.restype = C.c_void_p
+    L.oracle_fcsm3d_destroy.argtypes = [C.c_void_p]
+    L.oracle_fcsm3d_level.argtypes = [C.c_void_p, C.c_int, i32p, i32p, C.c_void_p]
+    L.oracle_fcsm3d_match.argtypes = [C.c_void_p, C.c_int, f32p, f32p, f32p, C.c_int, f32p, C.c_int,
+                                      f32p, C.c_int, f64p, C.c_float, C.POINTER(OracleResult3D)]
+    L.oracle_fcsm3d_discrete_scans.argtypes = [C.c_void_p, f64p, C.c_float, f32p, f32p, f32p, C.c_int,
+                                               f32p, C.c_int, f64p, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = L
     return L
 
@@ -176,3 +205,98 @@ def constraint_batch(num_threads, grids, submap_poses, search_submap, search_ful
         sampling_ratio, max_constraint_distance, min_score, global_min_score, linear_window,
         angular_window, depth, out, stats)
     return secs, out, stats
+
+
+# ---- 3D ---------------------------------------------------------------------------
+IDENTITY_POSE7 = np.array([0, 0, 0, 1, 0, 0, 0], np.float32)
+
+
+def options3d(depth=8, full_resolution_depth=3, min_rotational_score=0.77, min_low_resolution_score=0.55,
+              linear_xy_search_window=5., linear_z_search_window=1., angular_search_window=np.radians(15.)):
+    """FastCorrelativeScanMatcherOptions3D as the 7 doubles the C entries take."""
+    return np.array([depth, full_resolution_depth, min_rotational_score, min_low_resolution_score,
+                     linear_xy_search_window, linear_z_search_window, angular_search_window], np.float64)
+
+
+class OracleGrid3D:
+    """HybridGrid: sparse voxel -> uint16 value."""
+
+    def __init__(self, resolution, xyz=None, values=None):
+        xyz = np.zeros((0, 3), np.int32) if xyz is None else np.ascontiguousarray(xyz, np.int32)
+        values = np.zeros(0, np.uint16) if values is None else np.ascontiguousarray(values, np.uint16)
+        self.resolution = float(np.float32(resolution))
+        self.h = lib().oracle_grid3d_create(resolution, xyz.reshape(-1), values, len(values))
+
+    def insert(self, origin, returns, hit_probability=0.7, miss_probability=0.4, num_free_space_voxels=5):
+        returns = np.ascontiguousarray(returns, np.float32)
+        lib().oracle_grid3d_insert(self.h, np.ascontiguousarray(origin, np.float32), returns.reshape(-1),
+                                   len(returns), hit_probability, miss_probability, num_free_space_voxels)
+
+    def cells(self):
+        n = lib().oracle_grid3d_cells(self.h, None, None)
+        xyz = np.zeros((n, 3), np.int32)
+        values = np.zeros(n, np.uint16)
+        if n:
+            lib().oracle_grid3d_cells(self.h, xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
+        order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
+        return xyz[order], values[order]
+
+    @property
+    def grid_size(self):
+        return lib().oracle_grid3d_size(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_grid3d_destroy(self.h)
+            self.h = None
+
+
+class OracleFCSM3D:
+    def __init__(self, grid, low_grid, histogram, options):
+        self.grid, self.low_grid = grid, low_grid
+        self.options = np.ascontiguousarray(options, np.float64)
+        self.histogram = np.ascontiguousarray(histogram, np.float32)
+        self.h = lib().oracle_fcsm3d_create(grid.h, low_grid.h, self.histogram, len(self.histogram), self.options)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_fcsm3d_destroy(self.h)
+            self.h = None
+
+    def level(self, i):
+        """(lo[3], dense uint8 [nz, ny, nx]) over the bounding box of stored cells."""
+        lo, hi = np.zeros(3, np.int32), np.zeros(3, np.int32)
+        lib().oracle_fcsm3d_level(self.h, i, lo, hi, None)
+        shape = tuple(int(v) for v in (hi - lo + 1)[::-1])
+        out = np.zeros(shape, np.uint8)
+        lib().oracle_fcsm3d_level(self.h, i, lo, hi, out.ctypes.data_as(C.c_void_p))
+        return lo, out
+
+    def match(self, hi_pts, lo_pts, histogram, min_score, node_pose7=IDENTITY_POSE7,
+              submap_pose7=IDENTITY_POSE7, gravity=(1., 0., 0., 0.), full=False):
+        hi_pts = np.ascontiguousarray(hi_pts, np.float32)
+        lo_pts = np.ascontiguousarray(lo_pts, np.float32)
+        histogram = np.ascontiguousarray(histogram, np.float32)
+        r = OracleResult3D()
+        lib().oracle_fcsm3d_match(self.h, 1 if full else 0, np.ascontiguousarray(node_pose7, np.float32),
+                                  np.ascontiguousarray(submap_pose7, np.float32), hi_pts.reshape(-1),
+                                  len(hi_pts), lo_pts.reshape(-1), len(lo_pts), histogram, len(histogram),
+                                  np.ascontiguousarray(gravity, np.float64), min_score, C.byref(r))
+        return r
+
+    def discrete_scans(self, hi_pts, histogram, node_pose7=IDENTITY_POSE7, submap_pose7=IDENTITY_POSE7,
+                       gravity=(1., 0., 0., 0.)):
+        hi_pts = np.ascontiguousarray(hi_pts, np.float32)
+        histogram = np.ascontiguousarray(histogram, np.float32)
+        args = (self.h, self.options, self.grid.resolution, np.ascontiguousarray(node_pose7, np.float32),
+                np.ascontiguousarray(submap_pose7, np.float32), hi_pts.reshape(-1), len(hi_pts), histogram,
+                len(histogram), np.ascontiguousarray(gravity, np.float64))
+        n = lib().oracle_fcsm3d_discrete_scans(*args, None, None, None)
+        poses = np.zeros((n, 7), np.float32)
+        rot = np.zeros(n, np.float32)
+        cells = np.zeros((n, len(hi_pts), 3), np.int32)
+        if n:
+            lib().oracle_fcsm3d_discrete_scans(*args, poses.ctypes.data_as(C.c_void_p),
+                                               rot.ctypes.data_as(C.c_void_p),
+                                               cells.ctypes.data_as(C.c_void_p))
+        return poses, rot, cells
