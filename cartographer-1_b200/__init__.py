@@ -31,6 +31,21 @@ class Result2D(C.Structure):
     ]
 
 
+class Result3D(C.Structure):
+    _fields_ = [
+        ("found", C.c_int32),
+        ("scan_index", C.c_int32),
+        ("offset", C.c_int32 * 3),
+        ("num_scans", C.c_int32),
+        ("score", C.c_float),
+        ("rotational_score", C.c_float),
+        ("low_resolution_score", C.c_float),
+        ("tie_resolution", C.c_int32),
+        ("pose", C.c_double * 7),
+        ("candidates_scored", C.c_uint64),
+    ]
+
+
 # Symbols include/csm_b200.h declares; tests check every one is exported.
 ABI_SYMBOLS = [
     "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
@@ -40,6 +55,10 @@ ABI_SYMBOLS = [
     "csm_stack2d_device_bytes", "csm_stack2d_destroy", "csm_match2d_batch",
     "csm_batch2d_upload", "csm_batch2d_run", "csm_batch2d_fetch", "csm_batch2d_destroy",
     "csm_discretize2d", "csm_rt_match2d_batch", "csm_ctx_launch_count", "csm_measure_gather_rate",
+    "csm_stack3d_build", "csm_stack3d_level", "csm_stack3d_depth", "csm_stack3d_device_bytes",
+    "csm_stack3d_destroy", "csm_grid3d_build", "csm_grid3d_destroy", "csm_match3d_batch",
+    "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
+    "csm_discretize3d",
 ]
 
 _abi = None
@@ -112,6 +131,25 @@ def host():
     L.csmh_constraint_builder_run.argtypes = [
         C.c_int, i32p, C.c_int, C.c_int, C.c_int, f64p, C.c_int, C.POINTER(C.c_void_p), f64p,
         C.c_int, i32p, i32p, f64p, f32p, i64p, i32p, f64p, f64p]
+    L.csmh_fcsm3d_create.restype = C.c_void_p
+    L.csmh_fcsm3d_create.argtypes = [C.c_void_p, C.c_float, i32p, u16p, C.c_int, C.c_float, i32p, u16p,
+                                     C.c_int, f32p, C.c_int, f64p]
+    L.csmh_fcsm3d_destroy.argtypes = [C.c_void_p]
+    L.csmh_fcsm3d_grid_size.argtypes = [C.c_void_p]
+    L.csmh_fcsm3d_level.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, i32p, i32p]
+    L.csmh_node3d_create.restype = C.c_void_p
+    L.csmh_node3d_create.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int, f64p]
+    L.csmh_node3d_destroy.argtypes = [C.c_void_p]
+    L.csmh_batch3d_create.restype = C.c_void_p
+    L.csmh_batch3d_create.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                      i32p, f64p, f64p, f32p]
+    L.csmh_batch3d_run.argtypes = [C.c_void_p]
+    L.csmh_batch3d_fetch.argtypes = [C.c_void_p, C.POINTER(Result3D)]
+    L.csmh_batch3d_destroy.argtypes = [C.c_void_p]
+    L.csmh_fcsm3d_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f64p, f64p, C.c_float,
+                                    C.POINTER(Result3D)]
+    L.csmh_fcsm3d_discrete_scans.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, f64p, f64p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
     _host = L
     return L
 
@@ -297,3 +335,134 @@ class PreparedBatch:
 
     def __del__(self):
         self.close()
+
+
+# ---- 3D -----------------------------------------------------------------------------
+IDENTITY_POSE7 = np.array([0, 0, 0, 1, 0, 0, 0], np.float64)
+
+
+class Matcher3D:
+    """FastCorrelativeScanMatcher3D over voxel lists (cell index, uint16 value)."""
+
+    def __init__(self, ctx, resolution, xyz, values, low_resolution, low_xyz, low_values, histogram,
+                 options7):
+        self.ctx = ctx
+        xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)
+        low_xyz = np.ascontiguousarray(low_xyz, np.int32).reshape(-1)
+        values = np.ascontiguousarray(values, np.uint16)
+        low_values = np.ascontiguousarray(low_values, np.uint16)
+        histogram = np.ascontiguousarray(histogram, np.float32)
+        self.depth = int(options7[0])
+        self.h = host().csmh_fcsm3d_create(ctx.h, resolution, xyz, values, len(values), low_resolution,
+                                           low_xyz, low_values, len(low_values), histogram,
+                                           len(histogram), np.ascontiguousarray(options7, np.float64))
+
+    def level(self, i):
+        """(lo[3], uint8 [nz, ny, nx]) of precomputation level i."""
+        lo, dims = np.zeros(3, np.int32), np.zeros(3, np.int32)
+        rc = host().csmh_fcsm3d_level(self.ctx.h, self.h, i, None, lo, dims)
+        if rc != 0:
+            raise RuntimeError(abi().csm_last_error().decode())
+        out = np.zeros((int(dims[2]), int(dims[1]), int(dims[0])), np.uint8)
+        if out.size:
+            host().csmh_fcsm3d_level(self.ctx.h, self.h, i, out.ctypes.data_as(C.c_void_p), lo, dims)
+        return lo, out
+
+    @property
+    def grid_size(self):
+        return host().csmh_fcsm3d_grid_size(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            host().csmh_fcsm3d_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+class Node3D:
+    """TrajectoryNode::Data of one node (3D fields)."""
+
+    def __init__(self, high_points, low_points, histogram, gravity=(1., 0., 0., 0.)):
+        hi = np.ascontiguousarray(high_points, np.float32).reshape(-1, 3)
+        lo = np.ascontiguousarray(low_points, np.float32).reshape(-1, 3)
+        hist = np.ascontiguousarray(histogram, np.float32)
+        self.num_high, self.num_low = len(hi), len(lo)
+        self.h = host().csmh_node3d_create(hi.reshape(-1), len(hi), lo.reshape(-1), len(lo), hist, len(hist),
+                                           np.ascontiguousarray(gravity, np.float64))
+
+    def close(self):
+        if getattr(self, "h", None):
+            host().csmh_node3d_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+def match3d(matcher, node, min_score, node_pose7=IDENTITY_POSE7, submap_pose7=IDENTITY_POSE7, full=False):
+    """The reference's Match / MatchFullSubmap: Result3D or None."""
+    r = Result3D()
+    ok = host().csmh_fcsm3d_match(matcher.h, node.h, 1 if full else 0,
+                                  np.ascontiguousarray(node_pose7, np.float64),
+                                  np.ascontiguousarray(submap_pose7, np.float64), min_score, C.byref(r))
+    return r if ok else None
+
+
+def discrete_scans3d(ctx, matcher, node, node_pose7=IDENTITY_POSE7, submap_pose7=IDENTITY_POSE7):
+    args = (ctx.h, matcher.h, node.h, np.ascontiguousarray(node_pose7, np.float64),
+            np.ascontiguousarray(submap_pose7, np.float64))
+    n = host().csmh_fcsm3d_discrete_scans(*args, None, None, None)
+    poses = np.zeros((n, 7), np.float32)
+    rot = np.zeros(n, np.float32)
+    cells = np.zeros((n, node.num_high, 3), np.int32)
+    if n:
+        rc = host().csmh_fcsm3d_discrete_scans(*args, poses.ctypes.data_as(C.c_void_p),
+                                               rot.ctypes.data_as(C.c_void_p),
+                                               cells.ctypes.data_as(C.c_void_p))
+        if rc < 0:
+            raise RuntimeError(abi().csm_last_error().decode())
+    return poses, rot, cells
+
+
+class PreparedBatch3D:
+    """Host-side per-search work done and inputs uploaded; run() is asynchronous."""
+
+    def __init__(self, ctx, matchers, nodes, min_scores, node_poses=None, submap_poses=None, full=None):
+        n = len(matchers)
+        self.n = n
+        self.keep = (matchers, nodes, ctx)
+        mh = (C.c_void_p * n)(*[m.h for m in matchers])
+        nh = (C.c_void_p * n)(*[d.h for d in nodes])
+        ident = np.tile(IDENTITY_POSE7, (n, 1))
+        node_poses = ident if node_poses is None else np.ascontiguousarray(node_poses, np.float64)
+        submap_poses = ident if submap_poses is None else np.ascontiguousarray(submap_poses, np.float64)
+        full = np.zeros(n, np.int32) if full is None else np.ascontiguousarray(full, np.int32)
+        self.h = host().csmh_batch3d_create(ctx.h, n, mh, nh, full, node_poses.reshape(-1),
+                                            submap_poses.reshape(-1),
+                                            np.ascontiguousarray(min_scores, np.float32))
+
+    def run(self):
+        host().csmh_batch3d_run(self.h)
+
+    def fetch(self):
+        out = (Result3D * self.n)()
+        host().csmh_batch3d_fetch(self.h, out)
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            host().csmh_batch3d_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+def match3d_batch(ctx, matchers, nodes, min_scores, node_poses=None, submap_poses=None, full=None):
+    b = PreparedBatch3D(ctx, matchers, nodes, min_scores, node_poses, submap_poses, full)
+    b.run()
+    out = b.fetch()
+    b.close()
+    return out

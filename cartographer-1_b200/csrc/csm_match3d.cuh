@@ -1,0 +1,127 @@
+// Device-side data structures of the 3D path (precomputation stack over a dense-ified
+// HybridGrid, low-resolution probability grid, batched branch-and-bound matcher).
+#ifndef CSM_MATCH3D_CUH_
+#define CSM_MATCH3D_CUH_
+
+#include "csm_internal.cuh"
+#include "csm_match2d.cuh"  // float_to_ordered / ordered_to_float
+
+namespace csm {
+
+// One precomputation level: bytes [z][y][x] over the box lo .. lo + dim - 1 (cell
+// indices of that level's own resolution); everything outside the box is 0, the
+// default of the reference's sparse grid (hybrid_grid.h:263-279).
+struct Level3 {
+  const uint8_t* data;
+  int lo[3];
+  int dim[3];
+};
+
+struct Stack3Dev {
+  int depth;  // branch_and_bound_depth = number of levels
+  int frd;    // full_resolution_depth
+  Level3 level[CSM_MAX_DEPTH];
+};
+
+// Low-resolution grid: fp32 probabilities [z][y][x]; `unknown` outside the box.
+struct Grid3Dev {
+  const float* data;
+  int lo[3];
+  int dim[3];
+  float unknown;
+};
+
+struct Job3Dev {
+  const Stack3Dev* sd;
+  const Grid3Dev* low;
+  int depth, frd;
+  int n;        // high-resolution points
+  int n_low;    // low-resolution points
+  int S;        // discrete scans
+  int wxy, wz;  // linear windows in voxels
+  int nxy, nz;  // lowest-resolution candidates per axis
+  long long pts_off;    // float3 index into points
+  long long low_off;    // float3 index into low points
+  long long scan_off;   // index into per-scan arrays
+  long long cell_off;   // int4 index into discrete scans (S * n)
+  long long cand_off;   // index into top-level score array
+  float res, low_res;
+  float min_score;
+  float n_float;
+  double min_low;
+};
+
+struct Job3State {
+  unsigned int best;        // ordered bits of S* (best leaf score that passed the filter), 0 = none
+  unsigned int group_best;  // phase 2: ordered top score of the winning group
+  unsigned long long win;   // phase 2: min over tied contenders of (cand index << 32 | list slot)
+  unsigned int tie_count;
+  unsigned int total;       // top-level candidates
+  unsigned long long scored;
+};
+
+// Branch-and-bound work item: one node, 16 bytes.
+struct Node3 {
+  int job_scan;  // job << 16 | scan
+  int ox, oy, oz;
+};
+
+struct Contender3 {
+  int job, scan;
+  int ox, oy, oz;
+  unsigned int cand;
+  float score;
+  int leaf[3];
+  int has_leaf;
+  float leaf_low;
+};
+
+}  // namespace csm
+
+struct csm_stack3d {
+  int device = 0;
+  int depth = 0, frd = 0;
+  uint8_t* base = nullptr;
+  size_t level_off[CSM_MAX_DEPTH] = {0};
+  csm::Stack3Dev host_view;
+  csm::Stack3Dev* dev = nullptr;
+  size_t bytes = 0;
+};
+
+struct csm_grid3d {
+  int device = 0;
+  float* data = nullptr;
+  csm::Grid3Dev host_view;
+  csm::Grid3Dev* dev = nullptr;
+  size_t bytes = 0;
+};
+
+struct csm_batch3d {
+  int num_jobs = 0;
+  std::vector<csm::Job3Dev> jobs_host;
+  int max_scans = 0;
+  int max_depth = 0;
+  long long total_pts = 0, total_low = 0, total_scans = 0, total_cells = 0, total_cand = 0;
+  csm::Job3Dev* jobs = nullptr;
+  float* points = nullptr;       // total_pts * 3
+  float* low_points = nullptr;   // total_low * 3
+  float* scan_poses = nullptr;   // total_scans * 7
+  float* scan_leaf_q = nullptr;  // total_scans * 4
+  int4* cells = nullptr;         // total_cells
+  unsigned long long* scan_best = nullptr;  // total_scans
+  float* top_scores = nullptr;   // total_cand
+  csm::Job3State* state = nullptr;
+  csm::Contender3* contenders = nullptr;
+  unsigned int contender_cap = 0;
+  unsigned long long frontier_want = 0;
+  unsigned int* counters = nullptr;
+  csm_result3d* results_dev = nullptr;
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  void* pinned = nullptr;
+  size_t pinned_bytes = 0;
+  size_t pin_results_off = 0;
+  bool uploaded = false, ran = false;
+};
+
+#endif  // CSM_MATCH3D_CUH_

@@ -311,10 +311,15 @@ class Submap2D {
   const Grid2D* grid_;
 };
 
-// mapping/trajectory_node.h:43-70 (only the field this path uses).
+// mapping/trajectory_node.h:43-70 (the fields the scan-matching paths read; the
+// histogram is an Eigen::VectorXf in the reference).
 struct TrajectoryNode {
   struct Data {
+    transform::Quaterniond gravity_alignment;
     sensor::PointCloud filtered_gravity_aligned_point_cloud;
+    sensor::PointCloud high_resolution_point_cloud;
+    sensor::PointCloud low_resolution_point_cloud;
+    std::vector<float> rotational_scan_matcher_histogram;
   };
 };
 

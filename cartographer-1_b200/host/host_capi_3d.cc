@@ -1,0 +1,202 @@
+// Flat C entry points over the 3D host layer (FastCorrelativeScanMatcher3D), for
+// ctypes-driven parity tests and the C5 bench.  Product code: reference-shaped
+// classes + C ABI only; never touches oracle/.
+#include <cstring>
+#include <memory>
+
+#include "cartographer/mapping/internal/3d/scan_matching/fast_correlative_scan_matcher_3d.h"
+
+using namespace cartographer;
+using mapping::scan_matching::DeviceContext;
+using mapping::scan_matching::FastCorrelativeScanMatcher3D;
+
+namespace {
+
+struct Matcher3DHolder {
+  std::unique_ptr<mapping::HybridGrid> grid, low_grid;
+  Eigen::VectorXf histogram;
+  std::unique_ptr<FastCorrelativeScanMatcher3D> matcher;
+};
+
+struct Node3DHolder {
+  mapping::TrajectoryNode::Data data;
+};
+
+transform::Rigid3d Pose7(const double* p) {
+  return transform::Rigid3d(transform::Vector3d(p[0], p[1], p[2]), transform::Quaterniond(p[3], p[4], p[5], p[6]));
+}
+
+struct Batch3DHolder {
+  FastCorrelativeScanMatcher3D::QueryList queries;
+  std::unique_ptr<FastCorrelativeScanMatcher3D::Batch> batch;
+};
+
+}  // namespace
+
+extern "C" {
+
+struct csmh_result3d {
+  int32_t found;
+  int32_t scan_index;
+  int32_t offset[3];
+  int32_t num_scans;
+  float score, rotational_score, low_resolution_score;
+  int32_t tie_resolution;
+  double pose[7];  // tx, ty, tz, qw, qx, qy, qz
+  uint64_t candidates_scored;
+};
+
+// Grids arrive as voxel lists (cell index, uint16 value), the form
+// HybridGrid::Iterator yields.  options7: branch_and_bound_depth,
+// full_resolution_depth, min_rotational_score, min_low_resolution_score,
+// linear_xy_search_window, linear_z_search_window, angular_search_window.
+void* csmh_fcsm3d_create(void* ctx, float resolution, const int32_t* xyz, const uint16_t* values, int n,
+                         float low_resolution, const int32_t* low_xyz, const uint16_t* low_values,
+                         int n_low, const float* histogram, int n_histogram, const double* options7) {
+  Matcher3DHolder* h = new Matcher3DHolder;
+  h->grid.reset(new mapping::HybridGrid(resolution));
+  for (int i = 0; i < n; ++i)
+    *h->grid->mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  h->low_grid.reset(new mapping::HybridGrid(low_resolution));
+  for (int i = 0; i < n_low; ++i)
+    *h->low_grid->mutable_value(Eigen::Array3i(low_xyz[3 * i], low_xyz[3 * i + 1], low_xyz[3 * i + 2])) =
+        low_values[i];
+  h->histogram.assign(histogram, histogram + n_histogram);
+  mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions3D o;
+  o.set_branch_and_bound_depth(static_cast<int>(options7[0]));
+  o.set_full_resolution_depth(static_cast<int>(options7[1]));
+  o.set_min_rotational_score(options7[2]);
+  o.set_min_low_resolution_score(options7[3]);
+  o.set_linear_xy_search_window(options7[4]);
+  o.set_linear_z_search_window(options7[5]);
+  o.set_angular_search_window(options7[6]);
+  h->matcher.reset(new FastCorrelativeScanMatcher3D(*h->grid, h->low_grid.get(), &h->histogram, o,
+                                                    static_cast<DeviceContext*>(ctx)));
+  return h;
+}
+void csmh_fcsm3d_destroy(void* m) { delete static_cast<Matcher3DHolder*>(m); }
+int csmh_fcsm3d_grid_size(void* m) { return static_cast<Matcher3DHolder*>(m)->grid->grid_size(); }
+
+int csmh_fcsm3d_level(void* ctx, void* m, int level, uint8_t* out, int32_t* lo3, int32_t* dims3) {
+  return csm_stack3d_level(static_cast<DeviceContext*>(ctx)->get(),
+                           static_cast<Matcher3DHolder*>(m)->matcher->stack(), level, out, lo3, dims3);
+}
+
+// TrajectoryNode::Data of one node.
+void* csmh_node3d_create(const float* hi, int n_hi, const float* lo, int n_lo, const float* histogram,
+                         int n_histogram, const double* gravity4) {
+  Node3DHolder* h = new Node3DHolder;
+  for (int i = 0; i < n_hi; ++i)
+    h->data.high_resolution_point_cloud.push_back({sensor::Vector3f(hi[3 * i], hi[3 * i + 1], hi[3 * i + 2])});
+  for (int i = 0; i < n_lo; ++i)
+    h->data.low_resolution_point_cloud.push_back({sensor::Vector3f(lo[3 * i], lo[3 * i + 1], lo[3 * i + 2])});
+  h->data.rotational_scan_matcher_histogram.assign(histogram, histogram + n_histogram);
+  h->data.gravity_alignment = transform::Quaterniond(gravity4[0], gravity4[1], gravity4[2], gravity4[3]);
+  return h;
+}
+void csmh_node3d_destroy(void* n) { delete static_cast<Node3DHolder*>(n); }
+
+// A prepared batch: search i runs nodes[i] against matchers[i]; full[i] selects
+// MatchFullSubmap; node_poses / submap_poses are n x 7 doubles.
+void* csmh_batch3d_create(void* ctx, int n, void* const* matchers, void* const* nodes, const int32_t* full,
+                          const double* node_poses, const double* submap_poses, const float* min_scores) {
+  Batch3DHolder* h = new Batch3DHolder;
+  h->queries.reserve(n);
+  for (int i = 0; i < n; ++i) {
+    FastCorrelativeScanMatcher3D::Query q;
+    q.constant_data = &static_cast<Node3DHolder*>(nodes[i])->data;
+    q.full_submap = full[i] != 0;
+    q.global_node_pose = Pose7(node_poses + 7 * i);
+    q.global_submap_pose = Pose7(submap_poses + 7 * i);
+    q.min_score = min_scores[i];
+    h->queries.emplace_back(static_cast<Matcher3DHolder*>(matchers[i])->matcher.get(), q);
+  }
+  h->batch.reset(new FastCorrelativeScanMatcher3D::Batch(static_cast<DeviceContext*>(ctx), h->queries));
+  return h;
+}
+void csmh_batch3d_run(void* b) { static_cast<Batch3DHolder*>(b)->batch->Run(); }
+void csmh_batch3d_fetch(void* b, csmh_result3d* out) {
+  const std::vector<FastCorrelativeScanMatcher3D::Answer> answers = static_cast<Batch3DHolder*>(b)->batch->Fetch();
+  for (size_t i = 0; i != answers.size(); ++i) {
+    const FastCorrelativeScanMatcher3D::Answer& a = answers[i];
+    csmh_result3d& r = out[i];
+    std::memset(&r, 0, sizeof(r));
+    r.found = a.found ? 1 : 0;
+    r.scan_index = a.scan_index;
+    for (int k = 0; k < 3; ++k) r.offset[k] = a.offset[k];
+    r.num_scans = a.num_scans;
+    r.score = a.result.score;
+    r.rotational_score = a.result.rotational_score;
+    r.low_resolution_score = a.result.low_resolution_score;
+    r.tie_resolution = a.tie_resolution;
+    const transform::Rigid3d& p = a.result.pose_estimate;
+    const double v[7] = {p.translation().x(), p.translation().y(), p.translation().z(), p.rotation().w(),
+                         p.rotation().x(),    p.rotation().y(),    p.rotation().z()};
+    for (int k = 0; k < 7; ++k) r.pose[k] = v[k];
+    r.candidates_scored = a.candidates_scored;
+  }
+}
+void csmh_batch3d_destroy(void* b) { delete static_cast<Batch3DHolder*>(b); }
+
+// The reference's single-search entry points (Match / MatchFullSubmap returning a
+// unique_ptr<Result>): returns 1 and fills `out` iff a Result was returned.
+int csmh_fcsm3d_match(void* m, void* node, int full, const double* node_pose7, const double* submap_pose7,
+                      float min_score, csmh_result3d* out) {
+  const FastCorrelativeScanMatcher3D& matcher = *static_cast<Matcher3DHolder*>(m)->matcher;
+  const mapping::TrajectoryNode::Data& data = static_cast<Node3DHolder*>(node)->data;
+  const transform::Rigid3d np = Pose7(node_pose7), sp = Pose7(submap_pose7);
+  const std::unique_ptr<FastCorrelativeScanMatcher3D::Result> result =
+      full ? matcher.MatchFullSubmap(np.rotation(), sp.rotation(), data, min_score)
+           : matcher.Match(np, sp, data, min_score);
+  std::memset(out, 0, sizeof(*out));
+  if (result == nullptr) return 0;
+  out->found = 1;
+  out->score = result->score;
+  out->rotational_score = result->rotational_score;
+  out->low_resolution_score = result->low_resolution_score;
+  const transform::Rigid3d& p = result->pose_estimate;
+  const double v[7] = {p.translation().x(), p.translation().y(), p.translation().z(), p.rotation().w(),
+                       p.rotation().x(),    p.rotation().y(),    p.rotation().z()};
+  for (int k = 0; k < 7; ++k) out->pose[k] = v[k];
+  return 1;
+}
+
+// Discrete scans of a local Match: kept yaw slices' poses (S x 7), rotational scores
+// (S) and device-computed full-resolution cell indices (S x n_hi x 3).  Returns S;
+// outputs may be NULL to query S.
+int csmh_fcsm3d_discrete_scans(void* ctx, void* m, void* node, const double* node_pose7,
+                               const double* submap_pose7, float* poses, float* rotational_scores,
+                               int32_t* cells) {
+  const Matcher3DHolder* h = static_cast<Matcher3DHolder*>(m);
+  const mapping::TrajectoryNode::Data& data = static_cast<Node3DHolder*>(node)->data;
+  std::vector<float> scores;
+  const std::vector<float> p =
+      h->matcher->DiscreteScanPosesForTesting(Pose7(node_pose7), Pose7(submap_pose7), data, &scores);
+  const int S = static_cast<int>(scores.size());
+  if (poses == nullptr || S == 0) return S;
+  std::memcpy(poses, p.data(), sizeof(float) * p.size());
+  std::memcpy(rotational_scores, scores.data(), sizeof(float) * scores.size());
+  std::vector<float> pts;
+  for (const sensor::RangefinderPoint& point : data.high_resolution_point_cloud)
+    for (const float v : {point.position.x(), point.position.y(), point.position.z()}) pts.push_back(v);
+  std::vector<float> leaf(4 * S, 0.f);
+  const float one_low_point[3] = {0.f, 0.f, 0.f};
+  csm_job3d job;
+  std::memset(&job, 0, sizeof(job));
+  job.stack = h->matcher->stack();
+  job.points_xyz = pts.data();
+  job.num_points = static_cast<int32_t>(data.high_resolution_point_cloud.size());
+  job.low_points_xyz = one_low_point;
+  job.num_low_points = 1;
+  job.num_scans = S;
+  job.scan_poses = p.data();
+  job.scan_leaf_quat = leaf.data();
+  job.resolution = h->grid->resolution();
+  job.low_resolution = h->low_grid->resolution();
+  job.linear_xy_window = 0;
+  job.linear_z_window = 0;
+  job.low_resolution_grid = h->matcher->low_resolution_grid();
+  return csm_discretize3d(static_cast<DeviceContext*>(ctx)->get(), &job, cells) == CSM_OK ? S : -1;
+}
+
+}  // extern "C"

@@ -184,6 +184,95 @@ typedef struct {
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
                          csm_result2d* results);
 
+/* ==== 3D path ======================================================================
+ * Citations relative to cartographer/mapping/internal/3d/scan_matching/:
+ *   FCSM3D = fast_correlative_scan_matcher_3d.{h,cc}
+ *   PG3D   = precomputation_grid_3d.{h,cc}
+ *   LRM    = low_resolution_matcher.{h,cc}
+ * Host side of the boundary (libm-dependent, O(num_scans)): the search parameters
+ * (FCSM3D.cc:127-170), the angular step (acos, :255-264), RotationalScanMatcher::Match
+ * and the surviving DiscreteScan3D poses (:266-290; rotational_scan_matcher.cc:121-189)
+ * and the candidate -> pose conversion (:363-369).
+ */
+typedef struct csm_stack3d csm_stack3d;
+typedef struct csm_grid3d csm_grid3d;
+typedef struct csm_batch3d csm_batch3d;
+
+/* ---- PrecomputationGridStack3D (FCSM3D.cc:57-77, PG3D.cc:49-81) -------------------
+ * The HybridGrid arrives as the list of its non-default voxels, as
+ * HybridGrid::Iterator visits them (cartographer/mapping/3d/hybrid_grid.h:327-419):
+ * voxel_xyz num_voxels x 3 int32 cell indices, voxel_values the uint16 cells.
+ * q_lut: 65536 bytes, q_lut[v] = lround((ValueToProbability(v) - 0.1f) * (255.f / 0.8f))
+ *        (ConvertToPrecomputationGrid, PG3D.cc:49-61), host-computed in fp32.
+ * Level k is stored dense over a box that contains every voxel PrecomputeGrid would
+ * create; levels k >= full_resolution_depth are at half the resolution of level k-1.
+ */
+int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* voxel_values,
+                      int num_voxels, const uint8_t* q_lut, int depth, int full_resolution_depth,
+                      csm_stack3d** out);
+/* Copies level `level` ([z][y][x] bytes, dims3 = nx, ny, nz; lo3 = cell index of element
+ * 0) to `out` (may be NULL to query the box only). */
+int csm_stack3d_level(csm_ctx* ctx, const csm_stack3d* stack, int level, uint8_t* out, int32_t* lo3,
+                      int32_t* dims3);
+int csm_stack3d_depth(const csm_stack3d* stack);
+size_t csm_stack3d_device_bytes(const csm_stack3d* stack);
+void csm_stack3d_destroy(csm_ctx* ctx, csm_stack3d* stack);
+
+/* ---- low-resolution HybridGrid for the leaf filter (LRM.cc:23-35) ------------------
+ * Dense fp32 probabilities over the voxels' bounding box; probability_table is the
+ * 65536-entry ValueToProbability table, probability_table[0] the value of unknown
+ * space (cartographer/mapping/probability_values.cc:29-60). */
+int csm_grid3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* voxel_values,
+                     int num_voxels, const float* probability_table, csm_grid3d** out);
+void csm_grid3d_destroy(csm_ctx* ctx, csm_grid3d* grid);
+
+/* ---- FastCorrelativeScanMatcher3D::MatchWithSearchParameters (FCSM3D.cc:172-198) ---
+ * One job = one (node, submap) search over the discrete scans that survived the
+ * rotational prefilter.  The device does DiscretizeScan (:200-244),
+ * GenerateLowestResolutionCandidates (:297-326), ScoreCandidates (:328-352) and
+ * BranchAndBound (:371-440) including the low-resolution leaf filter (:382-402).
+ */
+typedef struct {
+  const csm_stack3d* stack;
+  const csm_grid3d* low_resolution_grid;
+  const float* points_xyz;        /* high_resolution_point_cloud, num_points x 3        */
+  int32_t num_points;
+  const float* low_points_xyz;    /* low_resolution_point_cloud, num_low_points x 3     */
+  int32_t num_low_points;
+  int32_t num_scans;              /* discrete scans kept by the rotational prefilter    */
+  const float* scan_poses;        /* num_scans x 7 fp32 (tx,ty,tz,qw,qx,qy,qz):         */
+                                  /* DiscreteScan3D::pose (FCSM3D.cc:282-290)            */
+  const float* scan_leaf_quat;    /* num_scans x 4 (w,x,y,z): rotation of               */
+                                  /* Translation(..) * scan.pose, i.e. the normalised   */
+                                  /* product GetPoseFromCandidate yields (:363-369)     */
+  float resolution;               /* HybridGrid::resolution() of the high-res grid      */
+  float low_resolution;           /* of the low-resolution grid                         */
+  int32_t linear_xy_window;       /* SearchParameters, in voxels (:131-134, :158-164)   */
+  int32_t linear_z_window;
+  float min_score;                /* strict threshold                                   */
+  double min_low_resolution_score;/* options.min_low_resolution_score() (:392)          */
+} csm_job3d;
+
+typedef struct {
+  int32_t found;
+  int32_t scan_index;             /* Candidate3D::scan_index (index among kept scans)   */
+  int32_t offset[3];              /* Candidate3D::offset                                */
+  float score;                    /* Candidate3D::score (bit-identical fp32)            */
+  float low_resolution_score;     /* Candidate3D::low_resolution_score                  */
+  int32_t tie_resolution;         /* 0: unique on device, 1: host replay of std::sort   */
+  uint64_t candidates_scored;
+} csm_result3d;
+
+int csm_match3d_batch(csm_ctx* ctx, const csm_job3d* jobs, int num_jobs, csm_result3d* results);
+int csm_batch3d_upload(csm_ctx* ctx, const csm_job3d* jobs, int num_jobs, csm_batch3d** out);
+int csm_batch3d_run(csm_ctx* ctx, csm_batch3d* batch);
+int csm_batch3d_fetch(csm_ctx* ctx, csm_batch3d* batch, csm_result3d* results);
+void csm_batch3d_destroy(csm_ctx* ctx, csm_batch3d* batch);
+
+/* DiscretizeScan alone for the bit-exact cell-index parity test: full-resolution cell
+ * indices, num_scans x num_points x 3 int32 (FCSM3D.cc:205-211). */
+int csm_discretize3d(csm_ctx* ctx, const csm_job3d* job, int32_t* out_xyz);
+
 /* ---- measurement aids (bench.py) ------------------------------------------------
  * csm_ctx_launch_count: kernels launched through `ctx` since it was created.
  * csm_measure_gather_rate: the L2 gather roofline G_L2 of the scoring loop
