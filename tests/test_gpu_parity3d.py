@@ -155,7 +155,7 @@ def _world_case(seed, depth, frd, **kw):
 
 def test_discretize3d_cells_identical(csm, gpu_ctx):
     w, xyz, val, lxyz, lval = _world_case(21, 6, 3, size_xy=8.0)
-    opt = ob.options3d(6, 3, 0.3, 0.4, 1.0, 0.5, np.radians(12))
+    opt = ob.options3d(6, 3, 0.0, 0.4, 1.0, 0.5, np.radians(12))
     om, gm = _pair(csm, gpu_ctx, 0.1, xyz, val, 0.45, lxyz, lval, w.submap_histogram(), opt)
     hi, lo, hist, grav, true = w.node([0.7, -1.1, 0.3], 0.4, gravity_yaw=0.15, tilt=(0.02, -0.03))
     init = true.copy()
