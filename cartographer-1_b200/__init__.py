@@ -148,6 +148,7 @@ def host():
     L.csmh_batch3d_destroy.argtypes = [C.c_void_p]
     L.csmh_fcsm3d_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f64p, f64p, C.c_float,
                                     C.POINTER(Result3D)]
+    L.csmh_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     L.csmh_fcsm3d_discrete_scans.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, f64p, f64p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
     _host = L
@@ -465,4 +466,14 @@ def match3d_batch(ctx, matchers, nodes, min_scores, node_poses=None, submap_pose
     b.run()
     out = b.fetch()
     b.close()
+    return out
+
+
+def rotational_match(submap_hist, hist, initial_angle, angles):
+    """RotationalScanMatcher::Match of the host layer (no device needed)."""
+    submap_hist = np.ascontiguousarray(submap_hist, np.float32)
+    hist = np.ascontiguousarray(hist, np.float32)
+    angles = np.ascontiguousarray(angles, np.float32)
+    out = np.zeros(len(angles), np.float32)
+    host().csmh_rotational_match(submap_hist, hist, len(hist), initial_angle, angles, len(angles), out)
     return out

@@ -38,7 +38,10 @@ constexpr int kWarp = 32;
 constexpr unsigned int kFull = 0xFFFFFFFFu;
 constexpr int kCntContenders = CSM_MAX_DEPTH;
 constexpr int kCntOverflow = CSM_MAX_DEPTH + 1;
-constexpr int kNumCounters3 = CSM_MAX_DEPTH + 2;
+constexpr int kCntWinners = CSM_MAX_DEPTH + 2;
+constexpr int kCntDeferred = CSM_MAX_DEPTH + 3;
+constexpr int kNumCounters3 = CSM_MAX_DEPTH + 4;
+constexpr unsigned int kDeferredPerJob = 1024;  // more than this: walk in order instead
 
 // PrecomputationGrid3D::ToProbability (precomputation_grid_3d.h:32-35) of the mean.
 __device__ __forceinline__ float to_score3(int sum, float n_float) {
@@ -326,45 +329,118 @@ k3_dive(const Job3Dev* __restrict__ jobs, const int4* __restrict__ cells,
   if (lane == 0 && scored) atomicAdd(&st->scored, scored);
 }
 
-struct Node3S {
-  int job_scan;
-  int ox, oy, oz;
-  float score;
-  int pad;
+// The incumbent as (has, value): a node is kept while its bound is strictly above the
+// incumbent (:407), a leaf while it ties or beats it -- the sweep has to see every leaf
+// that attains S* to reproduce which of them the reference reaches first.
+struct Incumbent {
+  bool has;
+  float thr;  // max(min_score, incumbent)
 };
+__device__ __forceinline__ Incumbent incumbent_raw(const Job3Dev& j, const Job3State* st) {
+  const unsigned int b = *reinterpret_cast<const volatile unsigned int*>(&st->best);
+  Incumbent inc;
+  inc.has = b != 0u;
+  inc.thr = b ? fmaxf(j.min_score, ordered_to_float(b)) : j.min_score;
+  return inc;
+}
+__device__ __forceinline__ Incumbent incumbent_of(const Job3Dev& j, const Job3State* st) {
+  const unsigned int b = __shfl_sync(kFull, *reinterpret_cast<const volatile unsigned int*>(&st->best), 0);
+  Incumbent inc;
+  inc.has = b != 0u;
+  inc.thr = b ? fmaxf(j.min_score, ordered_to_float(b)) : j.min_score;
+  return inc;
+}
+__device__ __forceinline__ bool keep_node(const Incumbent& inc, float score) { return score > inc.thr; }
+__device__ __forceinline__ bool keep_leaf(const Incumbent& inc, const Job3Dev& j, float score) {
+  return score > j.min_score && (!inc.has || score >= inc.thr);
+}
+// A bound exactly equal to the incumbent is pruned like the reference does, but an
+// S*-leaf may hide below it if that value turns out to be S*.  Such nodes are deferred:
+// after the sweep those whose bound equals the final S* are expanded with a non-strict
+// threshold.  A job that defers too many (a world of equal scores) is instead resolved
+// by walking the tree in the reference's order, which finds its winner immediately.
+struct Deferred {
+  Node3S* list;
+  unsigned int cap;
+  unsigned int* counter;
+};
+__device__ __forceinline__ void defer_if_equal(const Incumbent& inc, Job3State* st, const Deferred& df,
+                                               const Node3S& node, int depth) {
+  if (!(inc.has && node.score == inc.thr)) return;
+  if (atomicAdd(&st->eq_count, 1u) >= kDeferredPerJob) {
+    st->use_dfs = 1u;
+    return;
+  }
+  const unsigned int slot = atomicAdd(df.counter, 1u);
+  if (slot >= df.cap) {
+    st->use_dfs = 1u;
+    return;
+  }
+  Node3S n = node;
+  n.path = (n.path & 0x0FFFFFFFFFFFFFFFull) | (static_cast<unsigned long long>(depth) << 60);
+  df.list[slot] = n;
+}
 
-// Lowest-resolution candidates of the jobs whose top depth is d, bound > threshold.
+// Lowest-resolution candidates of the jobs whose top depth is d.
 __global__ void __launch_bounds__(256)
 k3_seed(const Job3Dev* __restrict__ jobs, const float* __restrict__ top_scores,
-        const Job3State* __restrict__ state, Node3S* __restrict__ out, unsigned int* __restrict__ counters,
-        int d, unsigned long long cap) {
+        Job3State* __restrict__ state, Node3S* __restrict__ out, unsigned int* __restrict__ counters,
+        int d, unsigned long long cap, Deferred df) {
   const Job3Dev& j = jobs[blockIdx.y];
   if (j.depth - 1 != d) return;
-  const float thr = threshold_raw(j, &state[blockIdx.y]);
+  Job3State* st = &state[blockIdx.y];
+  const Incumbent inc = incumbent_raw(j, st);
   const int per_scan = j.nz * j.nxy * j.nxy;
   const long long total = static_cast<long long>(j.S) * per_scan;
   const int step = 1 << d;
   for (long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; c < total;
        c += static_cast<long long>(gridDim.x) * blockDim.x) {
     const float score = top_scores[j.cand_off + c];
-    if (!(score > thr)) continue;
+    const bool keep = d == 0 ? keep_leaf(inc, j, score) : keep_node(inc, score);
+    if (!keep && !(d != 0 && inc.has && score == inc.thr)) continue;
     const int scan = static_cast<int>(c / per_scan);
     int r = static_cast<int>(c - static_cast<long long>(scan) * per_scan);
     const int iz = r / (j.nxy * j.nxy);
     r -= iz * j.nxy * j.nxy;
     const int iy = r / j.nxy, ix = r - iy * j.nxy;
-    const unsigned int slot = atomicAdd(&counters[d], 1u);
-    if (slot >= cap) {
-      atomicOr(&counters[kCntOverflow], 1u);
-      continue;
-    }
     Node3S nd;
     nd.job_scan = (blockIdx.y << 16) | scan;
     nd.ox = -j.wxy + ix * step;
     nd.oy = -j.wxy + iy * step;
     nd.oz = -j.wz + iz * step;
     nd.score = score;
-    nd.pad = 0;
+    nd.top_cand = static_cast<unsigned int>(c);
+    nd.path = 0ull;
+    if (!keep) {
+      defer_if_equal(inc, st, df, nd, d);
+      continue;
+    }
+    const unsigned int slot = atomicAdd(&counters[d], 1u);
+    if (slot >= cap) {
+      atomicOr(&counters[kCntOverflow], 1u);
+      continue;
+    }
+    out[slot] = nd;
+  }
+}
+
+// Second sweep: deferred nodes at depth d whose bound equals the final S*.
+__global__ void __launch_bounds__(256)
+k3_seed_deferred(const Job3Dev* __restrict__ jobs, const Job3State* __restrict__ state,
+                 const Node3S* __restrict__ deferred, unsigned int deferred_cap, Node3S* __restrict__ out,
+                 unsigned int* __restrict__ counters, int d, unsigned long long cap) {
+  const unsigned int count = min(counters[kCntDeferred], deferred_cap);
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    Node3S nd = deferred[i];
+    if (static_cast<int>(nd.path >> 60) != d) continue;
+    const Job3State& st = state[nd.job_scan >> 16];
+    if (st.use_dfs || float_to_ordered(nd.score) != st.best) continue;
+    nd.path &= 0x0FFFFFFFFFFFFFFFull;
+    const unsigned int slot = atomicAdd(&counters[d], 1u);
+    if (slot >= cap) {
+      atomicOr(&counters[kCntOverflow], 1u);
+      continue;
+    }
     out[slot] = nd;
   }
 }
@@ -372,20 +448,26 @@ k3_seed(const Job3Dev* __restrict__ jobs, const float* __restrict__ top_scores,
 constexpr int kExpandWarps3 = 8;
 
 // One warp per node at depth d: score its (up to) eight children at depth d - 1, keep
-// those whose bound beats the incumbent.
+// those whose bound beats the incumbent (leaves: ties it as well).
 __global__ void __launch_bounds__(kExpandWarps3 * kWarp)
 k3_expand(const Job3Dev* __restrict__ jobs, const int4* __restrict__ cells,
           Job3State* __restrict__ state, const Node3S* __restrict__ in, Node3S* __restrict__ out,
-          unsigned int* __restrict__ counters, int d, unsigned long long cap) {
+          unsigned int* __restrict__ counters, int d, unsigned long long cap, Deferred df, bool second) {
   const unsigned int count = static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[d]), cap));
   const int lane = threadIdx.x & 31;
   const unsigned int warps = gridDim.x * kExpandWarps3;
+  // the second sweep keeps whatever ties S*, like the first does for leaves
+  const bool to_leaves = d == 1 || second;
   for (unsigned int i = blockIdx.x * kExpandWarps3 + (threadIdx.x >> 5); i < count; i += warps) {
     const Node3S nd = in[i];
     const int job = nd.job_scan >> 16, scan = nd.job_scan & 0xFFFF;
     const Job3Dev& j = jobs[job];
     Job3State* st = &state[job];
-    if (!(nd.score > threshold_of(j, st))) continue;  // the incumbent improved meanwhile
+    Incumbent inc = incumbent_of(j, st);
+    if (!(second ? keep_leaf(inc, j, nd.score) : keep_node(inc, nd.score))) {  // the incumbent improved
+      if (lane == 0 && !second) defer_if_equal(inc, st, df, nd, d);
+      continue;
+    }
     int sums[8];
     const unsigned int valid = children_sums(j, cells + j.cell_off + static_cast<long long>(scan) * j.n, d,
                                              nd.ox, nd.oy, nd.oz, lane, sums);
@@ -393,8 +475,26 @@ k3_expand(const Job3Dev* __restrict__ jobs, const int4* __restrict__ cells,
 #pragma unroll
     for (int k = 0; k < 8; ++k) mine = (lane == k) ? sums[k] : mine;
     const float score = to_score3(mine, j.n_float);
-    const float thr = threshold_of(j, st);
-    const bool keep = lane < 8 && ((valid >> lane) & 1u) && score > thr;
+    // rank among the valid siblings after the reference's stable descending sort
+    int rank = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float other = __shfl_sync(kFull, score, k);
+      if (((valid >> k) & 1u) && (other > score || (other == score && k < lane))) ++rank;
+    }
+    inc = incumbent_of(j, st);
+    const bool is_child = lane < 8 && ((valid >> lane) & 1u);
+    const bool keep = is_child && (to_leaves ? keep_leaf(inc, j, score) : keep_node(inc, score));
+    const int half = 1 << (d - 1);
+    Node3S ch;
+    ch.job_scan = nd.job_scan;
+    ch.ox = nd.ox + ((lane & 1) ? half : 0);
+    ch.oy = nd.oy + ((lane & 2) ? half : 0);
+    ch.oz = nd.oz + ((lane & 4) ? half : 0);
+    ch.score = score;
+    ch.top_cand = nd.top_cand;
+    ch.path = (nd.path << 3) | static_cast<unsigned long long>(rank);
+    if (is_child && !keep && !to_leaves) defer_if_equal(inc, st, df, ch, d - 1);
     const unsigned int m = __ballot_sync(kFull, keep);
     if (m) {
       unsigned int base = 0;
@@ -403,14 +503,6 @@ k3_expand(const Job3Dev* __restrict__ jobs, const int4* __restrict__ cells,
       if (keep) {
         const unsigned int slot = base + __popc(m & ((1u << lane) - 1u));
         if (slot < cap) {
-          const int half = 1 << (d - 1);
-          Node3S ch;
-          ch.job_scan = nd.job_scan;
-          ch.ox = nd.ox + ((lane & 1) ? half : 0);
-          ch.oy = nd.oy + ((lane & 2) ? half : 0);
-          ch.oz = nd.oz + ((lane & 4) ? half : 0);
-          ch.score = score;
-          ch.pad = 0;
           out[slot] = ch;
         } else {
           atomicOr(&counters[kCntOverflow], 1u);
@@ -421,12 +513,13 @@ k3_expand(const Job3Dev* __restrict__ jobs, const int4* __restrict__ cells,
   }
 }
 
-// Leaves whose score still beats the incumbent go through the low-resolution filter.
+// Leaves that still tie or beat the incumbent go through the low-resolution filter;
+// those that pass raise the incumbent and are recorded.
 __global__ void __launch_bounds__(kExpandWarps3 * kWarp)
 k3_filter(const Job3Dev* __restrict__ jobs, const float* __restrict__ low_points,
           const float* __restrict__ poses, const float* __restrict__ leaf_q, Job3State* __restrict__ state,
-          const Node3S* __restrict__ leaves, const unsigned int* __restrict__ counters,
-          unsigned long long cap) {
+          const Node3S* __restrict__ leaves, unsigned int* __restrict__ counters, unsigned long long cap,
+          Winner3* __restrict__ winners, unsigned int winner_cap) {
   const unsigned int count = static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[0]), cap));
   const int lane = threadIdx.x & 31;
   const unsigned int warps = gridDim.x * kExpandWarps3;
@@ -435,10 +528,64 @@ k3_filter(const Job3Dev* __restrict__ jobs, const float* __restrict__ low_points
     const int job = nd.job_scan >> 16, scan = nd.job_scan & 0xFFFF;
     const Job3Dev& j = jobs[job];
     Job3State* st = &state[job];
-    if (!(nd.score > threshold_of(j, st))) continue;
+    if (!keep_leaf(incumbent_of(j, st), j, nd.score)) continue;
     const float low = low_resolution_score(j, low_points, poses + 7 * (j.scan_off + scan),
                                            leaf_q + 4 * (j.scan_off + scan), nd.ox, nd.oy, nd.oz, lane);
-    if (static_cast<double>(low) >= j.min_low && lane == 0) atomicMax(&st->best, float_to_ordered(nd.score));
+    if (static_cast<double>(low) >= j.min_low && lane == 0) {
+      atomicMax(&st->best, float_to_ordered(nd.score));
+      const unsigned int slot = atomicAdd(&counters[kCntWinners], 1u);
+      if (slot < winner_cap) {
+        Winner3 w;
+        w.job = job;
+        w.scan = scan;
+        w.leaf[0] = nd.ox;
+        w.leaf[1] = nd.oy;
+        w.leaf[2] = nd.oz;
+        w.cand = nd.top_cand;
+        w.score = nd.score;
+        w.low = low;
+        w.path = nd.path;
+        winners[slot] = w;
+      } else {
+        atomicOr(&counters[kCntOverflow], 8u);
+      }
+    }
+  }
+}
+
+// Which recorded S*-leaf does the reference reach first?  The one below the best-
+// ranked lowest-resolution candidate (score descending; equal scores are left to the
+// host's std::sort replay), and there the one with the smallest path.  One block: the
+// list is short, the four passes are separated by block barriers.
+__global__ void __launch_bounds__(1024)
+k3_pick_winner(const Job3Dev* __restrict__ jobs, const float* __restrict__ top_scores,
+               Job3State* __restrict__ state, const Winner3* __restrict__ winners,
+               const unsigned int* __restrict__ counters, unsigned int winner_cap) {
+  const unsigned int count = min(counters[kCntWinners], winner_cap);
+  for (int pass = 0; pass < 4; ++pass) {
+    for (unsigned int i = threadIdx.x; i < count; i += blockDim.x) {
+      const Winner3 w = winners[i];
+      Job3State* st = &state[w.job];
+      if (float_to_ordered(w.score) != st->best) continue;
+      const unsigned int top = float_to_ordered(top_scores[jobs[w.job].cand_off + w.cand]);
+      if (pass == 0) {
+        atomicMax(&st->w_group, top);
+        continue;
+      }
+      if (top != st->w_group) continue;
+      if (pass == 1) {
+        atomicMin(&st->w_cand_min, w.cand);
+        atomicMax(&st->w_cand_max, w.cand);
+        continue;
+      }
+      if (w.cand != st->w_cand_min) continue;
+      if (pass == 2) {
+        atomicMin(&st->w_path_min, w.path);
+        continue;
+      }
+      if (w.path == st->w_path_min) atomicMin(&st->w_slot, i);
+    }
+    __syncthreads();
   }
 }
 
@@ -449,7 +596,7 @@ k3_collect(const Job3Dev* __restrict__ jobs, const float* __restrict__ top_score
            unsigned int* __restrict__ counters, unsigned int cap) {
   const Job3Dev& j = jobs[blockIdx.y];
   const unsigned int best = state[blockIdx.y].best;
-  if (best == 0u) return;
+  if (best == 0u || !state[blockIdx.y].use_dfs) return;  // the sweep saw every S*-leaf
   const float s_star = ordered_to_float(best);
   const int per_scan = j.nz * j.nxy * j.nxy;
   const long long total = static_cast<long long>(j.S) * per_scan;
@@ -599,7 +746,8 @@ k3_pick(Job3State* __restrict__ state, const Contender3* __restrict__ list,
 
 __global__ void __launch_bounds__(128)
 k3_finalize(const Job3Dev* __restrict__ jobs, const Job3State* __restrict__ state,
-            const Contender3* __restrict__ list, csm_result3d* __restrict__ results, int num_jobs) {
+            const Contender3* __restrict__ list, const Winner3* __restrict__ winners,
+            csm_result3d* __restrict__ results, int num_jobs) {
   const int job = blockIdx.x * blockDim.x + threadIdx.x;
   if (job >= num_jobs) return;
   const Job3State st = state[job];
@@ -613,17 +761,30 @@ k3_finalize(const Job3Dev* __restrict__ jobs, const Job3State* __restrict__ stat
   r.candidates_scored = st.scored;
   if (st.best != 0u) {
     r.score = ordered_to_float(st.best);
-    if (st.win == ~0ull) {
+    if (st.use_dfs) {  // traversal-order fallback decided
+      if (st.win == ~0ull) {
+        r.found = -1;
+      } else {
+        const Contender3 ct = list[st.win & 0xFFFFFFFFull];
+        r.found = 1;
+        r.scan_index = ct.scan;
+        r.offset[0] = ct.leaf[0];
+        r.offset[1] = ct.leaf[1];
+        r.offset[2] = ct.leaf[2];
+        r.low_resolution_score = ct.leaf_low;
+        r.tie_resolution = st.tie_count > 1u ? 2 : 0;  // 2: host replays std::sort over contenders
+      }
+    } else if (st.w_slot == 0xFFFFFFFFu) {
       r.found = -1;
     } else {
-      const Contender3 ct = list[st.win & 0xFFFFFFFFull];
+      const Winner3 w = winners[st.w_slot];
       r.found = 1;
-      r.scan_index = ct.scan;
-      r.offset[0] = ct.leaf[0];
-      r.offset[1] = ct.leaf[1];
-      r.offset[2] = ct.leaf[2];
-      r.low_resolution_score = ct.leaf_low;
-      r.tie_resolution = static_cast<int32_t>(st.tie_count);
+      r.scan_index = w.scan;
+      r.offset[0] = w.leaf[0];
+      r.offset[1] = w.leaf[1];
+      r.offset[2] = w.leaf[2];
+      r.low_resolution_score = w.low;
+      r.tie_resolution = st.w_cand_min != st.w_cand_max ? 3 : 0;  // 3: replay over recorded leaves
     }
   }
   results[job] = r;
@@ -635,9 +796,16 @@ k3_state_init(Job3State* __restrict__ state, const Job3Dev* __restrict__ jobs, i
   if (job >= num_jobs) return;
   Job3State s;
   s.best = 0u;
+  s.eq_count = 0u;
+  s.w_group = 0u;
+  s.w_cand_min = 0xFFFFFFFFu;
+  s.w_cand_max = 0u;
+  s.w_slot = 0xFFFFFFFFu;
+  s.w_path_min = ~0ull;
   s.group_best = 0u;
   s.win = ~0ull;
   s.tie_count = 0u;
+  s.use_dfs = 0u;
   const Job3Dev& j = jobs[job];
   s.total = static_cast<unsigned int>(static_cast<long long>(j.S) * j.nz * j.nxy * j.nxy);
   s.scored = 0ull;
@@ -665,10 +833,11 @@ struct Carve {
   }
 };
 
-int allocate_batch3(csm_batch3d* b, unsigned int contender_cap) {
+int allocate_batch3(csm_batch3d* b, unsigned int contender_cap, unsigned int winner_cap) {
   if (b->arena) cudaFree(b->arena);
   b->arena = nullptr;
   b->contender_cap = contender_cap;
+  b->winner_cap = winner_cap;
   Carve c;
   const size_t o_jobs = c.take(sizeof(Job3Dev) * b->num_jobs);
   const size_t o_pts = c.take(sizeof(float) * 3 * b->total_pts);
@@ -680,6 +849,10 @@ int allocate_batch3(csm_batch3d* b, unsigned int contender_cap) {
   const size_t o_top = c.take(sizeof(float) * b->total_cand);
   const size_t o_state = c.take(sizeof(Job3State) * b->num_jobs);
   const size_t o_cont = c.take(sizeof(Contender3) * static_cast<size_t>(contender_cap));
+  const size_t o_win = c.take(sizeof(Winner3) * static_cast<size_t>(winner_cap));
+  b->deferred_cap = static_cast<unsigned int>(
+      std::min<unsigned long long>(static_cast<unsigned long long>(b->num_jobs) * kDeferredPerJob, 1ull << 20));
+  const size_t o_def = c.take(sizeof(Node3S) * static_cast<size_t>(b->deferred_cap));
   const size_t o_cnt = c.take(sizeof(unsigned int) * kNumCounters3);
   const size_t o_res = c.take(sizeof(csm_result3d) * b->num_jobs);
   b->arena_bytes = std::max<size_t>(c.at, 256);
@@ -700,6 +873,8 @@ int allocate_batch3(csm_batch3d* b, unsigned int contender_cap) {
   b->top_scores = reinterpret_cast<float*>(base + o_top);
   b->state = reinterpret_cast<Job3State*>(base + o_state);
   b->contenders = reinterpret_cast<Contender3*>(base + o_cont);
+  b->winners = reinterpret_cast<Winner3*>(base + o_win);
+  b->deferred = reinterpret_cast<Node3S*>(base + o_def);
   b->counters = reinterpret_cast<unsigned int*>(base + o_cnt);
   b->results_dev = reinterpret_cast<csm_result3d*>(base + o_res);
   return CSM_OK;
@@ -748,6 +923,7 @@ void csm_batch3d_destroy(csm_ctx* ctx, csm_batch3d* b) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
   }
+  for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   if (b->arena) cudaFree(b->arena);
   if (b->pinned) cudaFreeHost(b->pinned);
   delete b;
@@ -845,7 +1021,7 @@ int csm_batch3d_upload(csm_ctx* ctx, const csm_job3d* jobs, int num_jobs, csm_ba
   const unsigned long long ccap = std::min<unsigned long long>(
       std::max<unsigned long long>(static_cast<unsigned long long>(b->total_cand) / 4 + 4096ull, 1ull << 16),
       0xFFFFFFF0ull);
-  int rc = allocate_batch3(b, static_cast<unsigned int>(ccap));
+  int rc = allocate_batch3(b, static_cast<unsigned int>(ccap), 1u << 16);
   if (rc == CSM_OK) rc = copy_inputs3(ctx, b);
   if (rc != CSM_OK) return fail(rc);
   b->uploaded = true;
@@ -869,11 +1045,24 @@ int csm_batch3d_run(csm_ctx* ctx, csm_batch3d* b) {
       std::min(ctx->frontier[0].cap, ctx->frontier[1].cap) / sizeof(Node3S), 0xFFFFFFF0ull);
   const int nj = b->num_jobs;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters3, st));
+  for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
+  b->prof_events.clear();
+  // csm_ctx_set_profiling phases: 0 discretize, 1 lowest-resolution scoring, 2 dives,
+  // 3 sweep + leaf filter, 4 traversal-order phase.
+  auto mark = [&]() {
+    if (!ctx->profiling) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    b->prof_events.push_back(e);
+  };
+  mark();
   ++ctx->launches, k3_state_init<<<(nj + 127) / 128, 128, 0, st>>>(b->state, b->jobs, nj);
   if (b->max_scans > 0) {
     const dim3 grid_sj(b->max_scans, nj);
     const int wide = std::max(1, std::min(ctx->num_sms * 8, 65535));
     ++ctx->launches, k3_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->scan_poses, b->cells, b->scan_best);
+    mark();
     // enough blocks per job to cover its candidates, bounded so the grid stays modest
     long long max_cand = 0;
     for (const Job3Dev& j : b->jobs_host)
@@ -881,21 +1070,41 @@ int csm_batch3d_run(csm_ctx* ctx, csm_batch3d* b) {
     const int top_blocks = static_cast<int>(std::min<long long>((max_cand + kTopWarps3 - 1) / kTopWarps3, 4096));
     ++ctx->launches, k3_score_top<<<dim3(top_blocks, nj), kTopWarps3 * kWarp, 0, st>>>(b->jobs, b->cells, b->top_scores,
                                                                        b->state, b->scan_best);
+    mark();
     ++ctx->launches, k3_dive<<<dim3((b->max_scans + kDiveWarps3 - 1) / kDiveWarps3, nj), kDiveWarps3 * kWarp, 0, st>>>(
         b->jobs, b->cells, b->low_points, b->scan_poses, b->scan_leaf_q, b->scan_best, b->state);
+    mark();
     const int seed_blocks = static_cast<int>(std::min<long long>((max_cand + 255) / 256, 1024));
+    const Deferred df{b->deferred, b->deferred_cap, b->counters + kCntDeferred};
     for (int d = b->max_depth - 1; d >= 0; --d) {
       bool any = false;
       for (const Job3Dev& j : b->jobs_host) any = any || (j.depth - 1 == d && j.S > 0);
       if (any)
         ++ctx->launches, k3_seed<<<dim3(seed_blocks, nj), 256, 0, st>>>(b->jobs, b->top_scores, b->state, fbuf[d & 1],
-                                                         b->counters, d, fcap);
+                                                         b->counters, d, fcap, df);
       if (d >= 1)
         ++ctx->launches, k3_expand<<<wide, kExpandWarps3 * kWarp, 0, st>>>(b->jobs, b->cells, b->state, fbuf[d & 1],
-                                                            fbuf[(d - 1) & 1], b->counters, d, fcap);
+                                                            fbuf[(d - 1) & 1], b->counters, d, fcap, df, false);
     }
     ++ctx->launches, k3_filter<<<wide, kExpandWarps3 * kWarp, 0, st>>>(b->jobs, b->low_points, b->scan_poses,
-                                                        b->scan_leaf_q, b->state, fbuf[0], b->counters, fcap);
+                                                        b->scan_leaf_q, b->state, fbuf[0], b->counters, fcap,
+                                                        b->winners, b->winner_cap);
+    // Second sweep over the nodes deferred at bound == S* (usually none: small grids).
+    CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * CSM_MAX_DEPTH, st));
+    const int small = std::max(1, ctx->num_sms);
+    for (int d = b->max_depth - 1; d >= 0; --d) {
+      ++ctx->launches, k3_seed_deferred<<<32, 256, 0, st>>>(b->jobs, b->state, b->deferred, b->deferred_cap,
+                                             fbuf[d & 1], b->counters, d, fcap);
+      if (d >= 1)
+        ++ctx->launches, k3_expand<<<small, kExpandWarps3 * kWarp, 0, st>>>(b->jobs, b->cells, b->state, fbuf[d & 1],
+                                                             fbuf[(d - 1) & 1], b->counters, d, fcap, df, true);
+    }
+    ++ctx->launches, k3_filter<<<small, kExpandWarps3 * kWarp, 0, st>>>(b->jobs, b->low_points, b->scan_poses,
+                                                         b->scan_leaf_q, b->state, fbuf[0], b->counters, fcap,
+                                                         b->winners, b->winner_cap);
+    ++ctx->launches, k3_pick_winner<<<1, 1024, 0, st>>>(b->jobs, b->top_scores, b->state, b->winners, b->counters,
+                                         b->winner_cap);
+    mark();
     ++ctx->launches, k3_collect<<<dim3(seed_blocks, nj), 256, 0, st>>>(b->jobs, b->top_scores, b->state, b->contenders,
                                                         b->counters, b->contender_cap);
     ++ctx->launches, k3_ordered_dfs<<<wide, 128, 0, st>>>(b->jobs, b->cells, b->low_points, b->scan_poses,
@@ -903,8 +1112,12 @@ int csm_batch3d_run(csm_ctx* ctx, csm_batch3d* b) {
                                            b->contender_cap);
     ++ctx->launches, k3_pick<<<(b->contender_cap + 255) / 256, 256, 0, st>>>(b->state, b->contenders, b->counters,
                                                               b->contender_cap);
+  } else {
+    for (int k = 0; k < 4; ++k) mark();
   }
-  ++ctx->launches, k3_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
+  ++ctx->launches, k3_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->winners,
+                                                 b->results_dev, nj);
+  mark();
   CSM_CUDA(cudaGetLastError());
   b->ran = true;
   return CSM_OK;
@@ -953,6 +1166,40 @@ int resolve_tie3(csm_ctx* ctx, csm_batch3d* b, int job, const std::vector<Conten
   return CSM_OK;
 }
 
+// The same over the leaves the sweep recorded: best-ranked candidate, then smallest path.
+int resolve_tie3_winners(csm_ctx* ctx, csm_batch3d* b, int job, const std::vector<Winner3>& list,
+                         csm_result3d* r) {
+  const Job3Dev& j = b->jobs_host[job];
+  Job3State st;
+  CSM_CUDA(cudaMemcpyAsync(&st, b->state + job, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
+  CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+  std::vector<float> scores(st.total);
+  CSM_CUDA(cudaMemcpyAsync(scores.data(), b->top_scores + j.cand_off, sizeof(float) * st.total,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+  std::vector<ScoreIdx3> v(st.total);
+  for (unsigned int i = 0; i < st.total; ++i) v[i] = ScoreIdx3{scores[i], i};
+  std::sort(v.begin(), v.end(), std::greater<ScoreIdx3>());
+  std::vector<unsigned int> rank(st.total);
+  for (unsigned int i = 0; i < st.total; ++i) rank[v[i].idx] = i;
+  const Winner3* best = nullptr;
+  for (const Winner3& w : list) {
+    if (w.job != job || float_to_ordered(w.score) != st.best ||
+        float_to_ordered(scores[w.cand]) != st.w_group)
+      continue;
+    if (!best || rank[w.cand] < rank[best->cand] || (w.cand == best->cand && w.path < best->path)) best = &w;
+  }
+  if (!best) {
+    set_error("tie replay found no recorded leaf for 3D job %d", job);
+    return CSM_ERR_CUDA;
+  }
+  r->scan_index = best->scan;
+  for (int a = 0; a < 3; ++a) r->offset[a] = best->leaf[a];
+  r->low_resolution_score = best->low;
+  r->tie_resolution = 2;
+  return CSM_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -982,23 +1229,41 @@ int csm_batch3d_fetch(csm_ctx* ctx, csm_batch3d* b, csm_result3d* results) {
     unsigned long long ccap = (ov & 4u) ? static_cast<unsigned long long>(counters[kCntContenders]) + 1024ull
                                         : b->contender_cap;
     if (ccap > 0xFFFFFFF0ull) ccap = 0xFFFFFFF0ull;
+    unsigned long long wcap = (ov & 8u) ? static_cast<unsigned long long>(counters[kCntWinners]) * 2ull + 1024ull
+                                        : b->winner_cap;
+    if (wcap > 0xFFFFFFF0ull) wcap = 0xFFFFFFF0ull;
     int rc = CSM_OK;
-    if (ccap != b->contender_cap) {
-      rc = allocate_batch3(b, static_cast<unsigned int>(ccap));
+    if (ccap != b->contender_cap || wcap != b->winner_cap) {
+      rc = allocate_batch3(b, static_cast<unsigned int>(ccap), static_cast<unsigned int>(wcap));
       if (rc == CSM_OK) rc = copy_inputs3(ctx, b);
     }
     if (rc == CSM_OK) rc = csm_batch3d_run(ctx, b);
     if (rc != CSM_OK) return rc;
   }
+  if (ctx->profiling) {
+    if (static_cast<int>(b->prof_events.size()) == csm_ctx::kPhases + 1) {
+      const cudaEvent_t* ev = b->prof_events.data();
+      for (int k = 0; k < csm_ctx::kPhases; ++k) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ev[k], ev[k + 1]) == cudaSuccess) ctx->phase_ms[k] += ms;
+      }
+      for (int i = 0; i < b->num_jobs; ++i)
+        ctx->phase_scored[3] += static_cast<double>(pin_res[i].candidates_scored);
+      ++ctx->profiled_runs;
+    }
+    for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
+    b->prof_events.clear();
+  }
   std::vector<Contender3> list;
-  bool have_list = false;
+  std::vector<Winner3> wlist;
+  bool have_list = false, have_wlist = false;
   for (int i = 0; i < b->num_jobs; ++i) {
     csm_result3d r = pin_res[i];
     if (r.found < 0) {
-      set_error("3D job %d: no contender holds the best leaf (internal error)", i);
+      set_error("3D job %d: the best leaf was not recorded (internal error)", i);
       return CSM_ERR_CUDA;
     }
-    if (r.found == 1 && r.tie_resolution > 1) {
+    if (r.found == 1 && r.tie_resolution == 2) {
       if (!have_list) {
         const unsigned int n = std::min(counters[kCntContenders], b->contender_cap);
         list.resize(n);
@@ -1008,6 +1273,17 @@ int csm_batch3d_fetch(csm_ctx* ctx, csm_batch3d* b, csm_result3d* results) {
         have_list = true;
       }
       const int rc = resolve_tie3(ctx, b, i, list, &r);
+      if (rc != CSM_OK) return rc;
+    } else if (r.found == 1 && r.tie_resolution == 3) {
+      if (!have_wlist) {
+        const unsigned int n = std::min(counters[kCntWinners], b->winner_cap);
+        wlist.resize(n);
+        CSM_CUDA(cudaMemcpyAsync(wlist.data(), b->winners, sizeof(Winner3) * n, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+        CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+        have_wlist = true;
+      }
+      const int rc = resolve_tie3_winners(ctx, b, i, wlist, &r);
       if (rc != CSM_OK) return rc;
     } else {
       r.tie_resolution = 0;

@@ -53,17 +53,43 @@ struct Job3Dev {
 
 struct Job3State {
   unsigned int best;        // ordered bits of S* (best leaf score that passed the filter), 0 = none
-  unsigned int group_best;  // phase 2: ordered top score of the winning group
-  unsigned long long win;   // phase 2: min over tied contenders of (cand index << 32 | list slot)
+  unsigned int eq_count;    // nodes pruned while exactly equal to the incumbent (deferred)
+  // winner selection over the leaves the sweep itself found (the common case)
+  unsigned int w_group;     // ordered lowest-resolution score of the winning group
+  unsigned int w_cand_min, w_cand_max;  // lowest-resolution candidates of that group holding an S*-leaf
+  unsigned int w_slot;      // winners-list slot of the selected leaf
+  unsigned long long w_path_min;
+  // traversal-order fallback (only when use_dfs: too many deferred nodes, e.g. a world
+  // of equal scores, where walking in order finds the winner at once)
+  unsigned int group_best;  // ordered top score of the winning group
   unsigned int tie_count;
+  unsigned long long win;   // min over tied contenders of (cand index << 32 | list slot)
   unsigned int total;       // top-level candidates
+  unsigned int use_dfs;
   unsigned long long scored;
 };
 
-// Branch-and-bound work item: one node, 16 bytes.
-struct Node3 {
+// Branch-and-bound work item, 32 bytes.  `path` is the node's position in the
+// reference's traversal below its lowest-resolution ancestor `top_cand`: three bits
+// per level, the rank of the node among its (stably sorted) siblings, most significant
+// level first -- so smaller paths are visited earlier.  Bits 60..63 hold the node's
+// depth while it waits in the deferred list.
+struct Node3S {
   int job_scan;  // job << 16 | scan
   int ox, oy, oz;
+  float score;
+  unsigned int top_cand;
+  unsigned long long path;
+};
+
+// A leaf that exceeded min_score, tied or beat the incumbent and passed the filter.
+struct Winner3 {
+  int job, scan;
+  int leaf[3];
+  unsigned int cand;
+  float score;
+  float low;
+  unsigned long long path;
 };
 
 struct Contender3 {
@@ -113,6 +139,10 @@ struct csm_batch3d {
   csm::Job3State* state = nullptr;
   csm::Contender3* contenders = nullptr;
   unsigned int contender_cap = 0;
+  csm::Winner3* winners = nullptr;
+  unsigned int winner_cap = 0;
+  csm::Node3S* deferred = nullptr;   // nodes pruned at bound == incumbent
+  unsigned int deferred_cap = 0;
   unsigned long long frontier_want = 0;
   unsigned int* counters = nullptr;
   csm_result3d* results_dev = nullptr;
@@ -122,6 +152,7 @@ struct csm_batch3d {
   size_t pinned_bytes = 0;
   size_t pin_results_off = 0;
   bool uploaded = false, ran = false;
+  std::vector<cudaEvent_t> prof_events;  // kPhases + 1 events of the last profiled run
 };
 
 #endif  // CSM_MATCH3D_CUH_

@@ -161,6 +161,16 @@ int csmh_fcsm3d_match(void* m, void* node, int full, const double* node_pose7, c
   return 1;
 }
 
+// RotationalScanMatcher::Match alone (host code; needs no device).
+void csmh_rotational_match(const float* submap_hist, const float* hist, int n, float initial_angle,
+                           const float* angles, int n_angles, float* out) {
+  const Eigen::VectorXf submap(submap_hist, submap_hist + n);
+  const mapping::scan_matching::RotationalScanMatcher matcher(&submap);
+  const std::vector<float> scores = matcher.Match(Eigen::VectorXf(hist, hist + n), initial_angle,
+                                                  std::vector<float>(angles, angles + n_angles));
+  for (int i = 0; i < n_angles; ++i) out[i] = scores[i];
+}
+
 // Discrete scans of a local Match: kept yaw slices' poses (S x 7), rotational scores
 // (S) and device-computed full-resolution cell indices (S x n_hi x 3).  Returns S;
 // outputs may be NULL to query S.

@@ -259,7 +259,9 @@ typedef struct {
   int32_t offset[3];              /* Candidate3D::offset                                */
   float score;                    /* Candidate3D::score (bit-identical fp32)            */
   float low_resolution_score;     /* Candidate3D::low_resolution_score                  */
-  int32_t tie_resolution;         /* 0: unique on device, 1: host replay of std::sort   */
+  int32_t tie_resolution;         /* 0: unique on device; host replay of std::sort over  */
+                                  /* equal lowest-resolution scores: 1 among traversal-  */
+                                  /* order contenders, 2 among the sweep's recorded leaves*/
   uint64_t candidates_scored;
 } csm_result3d;
 

@@ -394,6 +394,15 @@ void oracle_fcsm3d_match(void* m, int full, const float* node_pose7, const float
   out->candidates_scored = r.candidates_scored;
 }
 
+// RotationalScanMatcher::Match (rotational_scan_matcher.cc:178-189).
+void oracle_rotational_match(const float* submap_hist, const float* hist, int n, float initial_angle,
+                             const float* angles, int n_angles, float* out) {
+  const std::vector<float> scores =
+      RotationalMatch(Histogram(submap_hist, submap_hist + n), Histogram(hist, hist + n), initial_angle,
+                      std::vector<float>(angles, angles + n_angles));
+  for (int i = 0; i < n_angles; ++i) out[i] = scores[i];
+}
+
 // Discrete scans of a local Match: returns the number of surviving scans; with non-NULL
 // outputs fills poses (S x 7), rotational scores (S) and full-resolution cell indices
 // (S x n_hi x 3).

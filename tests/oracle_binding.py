@@ -110,6 +110,7 @@ def lib():
                                       f32p, C.c_int, f64p, C.c_float, C.POINTER(OracleResult3D)]
     L.oracle_fcsm3d_discrete_scans.argtypes = [C.c_void_p, f64p, C.c_float, f32p, f32p, f32p, C.c_int,
                                                f32p, C.c_int, f64p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     _lib = L
     return L
 
@@ -300,3 +301,12 @@ class OracleFCSM3D:
                                                rot.ctypes.data_as(C.c_void_p),
                                                cells.ctypes.data_as(C.c_void_p))
         return poses, rot, cells
+
+
+def rotational_match(submap_hist, hist, initial_angle, angles):
+    submap_hist = np.ascontiguousarray(submap_hist, np.float32)
+    hist = np.ascontiguousarray(hist, np.float32)
+    angles = np.ascontiguousarray(angles, np.float32)
+    out = np.zeros(len(angles), np.float32)
+    lib().oracle_rotational_match(submap_hist, hist, len(hist), initial_angle, angles, len(angles), out)
+    return out

@@ -215,13 +215,16 @@ def test_match3d_full_submap_world(csm, gpu_ctx):
     _compare(r_o, r_g)
 
 
-def test_match3d_tie_order(csm, gpu_ctx):
+@pytest.mark.parametrize("window,mode", [(1.0, 2), (3.0, 1)])
+def test_match3d_tie_order(csm, gpu_ctx, window, mode):
     """Unknown space everywhere: every candidate scores kMinProbability, so the winner is
     decided purely by the reference's traversal order (std::sort of equal lowest-
-    resolution scores, then stable child order)."""
+    resolution scores, then stable child order).  The small window is resolved from the
+    deferred equal-bound nodes (tie_resolution 2), the large one defers too many and
+    takes the ordered-walk fallback (tie_resolution 1)."""
     xyz = np.array([[500, 500, 500]], np.int32)  # one voxel far away from every lookup
     val = synth3d.probability_to_value([0.9])
-    opt = ob.options3d(4, 2, 0.0, 0.05, 1.0, 0.4, np.radians(20))
+    opt = ob.options3d(4, 2, 0.0, 0.05, window, 0.4, np.radians(20))
     hist = np.ones(12, np.float32)
     om, gm = _pair(csm, gpu_ctx, 0.1, xyz, val, 0.45, xyz, val, hist, opt)
     rng = np.random.default_rng(5)
@@ -232,7 +235,7 @@ def test_match3d_tie_order(csm, gpu_ctx):
     r_g = csm.match3d_batch(gpu_ctx, [gm], [node], [0.05])[0]
     assert r_o.found and r_o.num_scans > 16
     _compare(r_o, r_g)
-    assert r_g.tie_resolution == 1
+    assert r_g.tie_resolution == mode
 
 
 def test_match3d_empty_clouds(csm, gpu_ctx):
@@ -244,3 +247,31 @@ def test_match3d_empty_clouds(csm, gpu_ctx):
     nodes = [csm.Node3D(empty, lo, hist, grav), csm.Node3D(hi, empty, hist, grav), csm.Node3D(hi, lo, hist, grav)]
     res = csm.match3d_batch(gpu_ctx, [gm] * 3, nodes, [0.4] * 3, np.tile(true, (3, 1)))
     assert not res[0].found and not res[1].found and res[2].found
+
+
+def test_match3d_periodic_world_top_level_ties(csm, gpu_ctx):
+    """A world that repeats every 16 voxels: leaves 16 voxels apart score identically and
+    sit below different lowest-resolution candidates with identical scores, so the
+    winner depends on the reference's std::sort order of equal lowest-resolution scores."""
+    rng = np.random.default_rng(77)
+    tile = np.unique(rng.integers(0, 16, size=(70, 3)) % [16, 16, 8], axis=0)
+    tiles = np.array([[i, j, 0] for i in range(-8, 8) for j in range(-8, 8)]) * [16, 16, 0]
+    xyz = (tile[None, :, :] + tiles[:, None, :]).reshape(-1, 3).astype(np.int32)
+    prob = np.tile(rng.uniform(0.55, 0.9, len(tile)), len(tiles))
+    val = synth3d.probability_to_value(prob)
+    lxyz = np.unique(rng.integers(-12, 12, size=(400, 3)), axis=0).astype(np.int32)
+    lval = synth3d.probability_to_value(rng.uniform(0.3, 0.9, len(lxyz)))
+    hist = np.ones(8, np.float32)
+    opt = ob.options3d(4, 2, 0.0, 0.1, 2.0, 0.4, np.radians(3))
+    om, gm = _pair(csm, gpu_ctx, 0.1, xyz, val, 0.45, lxyz, lval, hist, opt)
+    centre = xyz[(np.abs(xyz[:, 0]) < 30) & (np.abs(xyz[:, 1]) < 30)]
+    pick = centre[rng.choice(len(centre), 60, replace=False)]
+    true = np.array([0.3, -0.2, 0.1])
+    hi = (pick * 0.1 - true).astype(np.float32)
+    lo = rng.uniform(-1, 1, (20, 3)).astype(np.float32)
+    r_o = om.match(hi, lo, hist, 0.3)
+    node = csm.Node3D(hi, lo, hist)
+    r_g = csm.match3d_batch(gpu_ctx, [gm], [node], [0.3])[0]
+    assert r_o.found
+    _compare(r_o, r_g)
+    assert r_g.tie_resolution in (1, 2)
