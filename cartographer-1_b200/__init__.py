@@ -148,6 +148,10 @@ def host():
     L.csmh_batch3d_destroy.argtypes = [C.c_void_p]
     L.csmh_fcsm3d_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f64p, f64p, C.c_float,
                                     C.POINTER(Result3D)]
+    L.csmh_constraint_builder3d_run.restype = C.c_double
+    L.csmh_constraint_builder3d_run.argtypes = [
+        C.c_int, i32p, C.c_int, C.c_int, f64p, f64p, C.c_int, C.POINTER(C.c_void_p), C.c_int, i32p, i32p,
+        C.POINTER(C.c_void_p), f64p, f64p, i32p, f64p, f64p]
     L.csmh_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     L.csmh_fcsm3d_discrete_scans.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, f64p, f64p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
@@ -477,3 +481,27 @@ def rotational_match(submap_hist, hist, initial_angle, angles):
     out = np.zeros(len(angles), np.float32)
     host().csmh_rotational_match(submap_hist, hist, len(hist), initial_angle, angles, len(angles), out)
     return out
+
+
+def constraint_builder3d_run(submap_matchers, search_submap, search_full, nodes, node_poses, submap_poses,
+                             fcsm_options7, sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
+                             global_localization_min_score=0.6, devices=(0,), pool_threads=4,
+                             flush_threshold=256):
+    """Drives ConstraintBuilder3D (MaybeAdd(Global)Constraint / NotifyEndOfNode / WhenDone).
+    Returns (found[n], transform[n, 7], stats dict, seconds)."""
+    n = len(nodes)
+    sm = (C.c_void_p * len(submap_matchers))(*[m.h for m in submap_matchers])
+    nh = (C.c_void_p * n)(*[d.h for d in nodes])
+    found = np.zeros(n, np.int32)
+    transform = np.zeros((n, 7), np.float64)
+    stats = np.zeros(4, np.float64)
+    opts = np.array([sampling_ratio, max_constraint_distance, min_score, global_localization_min_score,
+                     1.1e4, 1e5], np.float64)
+    secs = host().csmh_constraint_builder3d_run(
+        len(devices), np.ascontiguousarray(devices, np.int32), pool_threads, flush_threshold, opts,
+        np.ascontiguousarray(fcsm_options7, np.float64), len(submap_matchers), sm, n,
+        np.ascontiguousarray(search_submap, np.int32), np.ascontiguousarray(search_full, np.int32), nh,
+        np.ascontiguousarray(node_poses, np.float64).reshape(-1),
+        np.ascontiguousarray(submap_poses, np.float64).reshape(-1), found, transform.reshape(-1), stats)
+    return found, transform, dict(searches=int(stats[0]), found=int(stats[1]),
+                                  candidates_scored=int(stats[2]), flushes=int(stats[3])), secs

@@ -361,6 +361,29 @@ class FastCorrelativeScanMatcherOptions2D {
   int branch_and_bound_depth_ = 0;
 };
 // real_time_correlative_scan_matcher_options.proto
+// fast_correlative_scan_matcher_options_3d.proto (fields 2, 8, 4, 9, 5, 6, 7)
+class FastCorrelativeScanMatcherOptions3D {
+ public:
+  int branch_and_bound_depth() const { return branch_and_bound_depth_; }
+  int full_resolution_depth() const { return full_resolution_depth_; }
+  double min_rotational_score() const { return min_rotational_score_; }
+  double min_low_resolution_score() const { return min_low_resolution_score_; }
+  double linear_xy_search_window() const { return linear_xy_search_window_; }
+  double linear_z_search_window() const { return linear_z_search_window_; }
+  double angular_search_window() const { return angular_search_window_; }
+  void set_branch_and_bound_depth(int v) { branch_and_bound_depth_ = v; }
+  void set_full_resolution_depth(int v) { full_resolution_depth_ = v; }
+  void set_min_rotational_score(double v) { min_rotational_score_ = v; }
+  void set_min_low_resolution_score(double v) { min_low_resolution_score_ = v; }
+  void set_linear_xy_search_window(double v) { linear_xy_search_window_ = v; }
+  void set_linear_z_search_window(double v) { linear_z_search_window_ = v; }
+  void set_angular_search_window(double v) { angular_search_window_ = v; }
+
+ private:
+  int branch_and_bound_depth_ = 0, full_resolution_depth_ = 0;
+  double min_rotational_score_ = 0., min_low_resolution_score_ = 0.;
+  double linear_xy_search_window_ = 0., linear_z_search_window_ = 0., angular_search_window_ = 0.;
+};
 class RealTimeCorrelativeScanMatcherOptions {
  public:
   double linear_search_window() const { return linear_search_window_; }
@@ -398,6 +421,14 @@ class ConstraintBuilderOptions {
   mutable_fast_correlative_scan_matcher_options() {
     return &fast_correlative_scan_matcher_options_;
   }
+  const scan_matching::proto::FastCorrelativeScanMatcherOptions3D&
+  fast_correlative_scan_matcher_options_3d() const {
+    return fast_correlative_scan_matcher_options_3d_;
+  }
+  scan_matching::proto::FastCorrelativeScanMatcherOptions3D*
+  mutable_fast_correlative_scan_matcher_options_3d() {
+    return &fast_correlative_scan_matcher_options_3d_;
+  }
   void set_sampling_ratio(double v) { sampling_ratio_ = v; }
   void set_max_constraint_distance(double v) { max_constraint_distance_ = v; }
   void set_min_score(double v) { min_score_ = v; }
@@ -412,6 +443,7 @@ class ConstraintBuilderOptions {
   double loop_closure_translation_weight_ = 0., loop_closure_rotation_weight_ = 0.;
   bool log_matches_ = false;
   scan_matching::proto::FastCorrelativeScanMatcherOptions2D fast_correlative_scan_matcher_options_;
+  scan_matching::proto::FastCorrelativeScanMatcherOptions3D fast_correlative_scan_matcher_options_3d_;
 };
 }  // namespace proto
 }  // namespace constraints

@@ -204,32 +204,29 @@ class HybridGrid {
   std::unordered_map<uint64_t, uint16> cells_;
 };
 
-namespace scan_matching {
-namespace proto {
-class FastCorrelativeScanMatcherOptions3D {
+// The parts of Submap3D the constraint builder reads (mapping/3d/submap_3d.h:43-95):
+// the two grids and the rotational histogram are borrowed, not owned.
+class Submap3D {
  public:
-  int branch_and_bound_depth() const { return branch_and_bound_depth_; }
-  int full_resolution_depth() const { return full_resolution_depth_; }
-  double min_rotational_score() const { return min_rotational_score_; }
-  double min_low_resolution_score() const { return min_low_resolution_score_; }
-  double linear_xy_search_window() const { return linear_xy_search_window_; }
-  double linear_z_search_window() const { return linear_z_search_window_; }
-  double angular_search_window() const { return angular_search_window_; }
-  void set_branch_and_bound_depth(int v) { branch_and_bound_depth_ = v; }
-  void set_full_resolution_depth(int v) { full_resolution_depth_ = v; }
-  void set_min_rotational_score(double v) { min_rotational_score_ = v; }
-  void set_min_low_resolution_score(double v) { min_low_resolution_score_ = v; }
-  void set_linear_xy_search_window(double v) { linear_xy_search_window_ = v; }
-  void set_linear_z_search_window(double v) { linear_z_search_window_ = v; }
-  void set_angular_search_window(double v) { angular_search_window_ = v; }
+  Submap3D(const transform::Rigid3d& local_pose, const HybridGrid* high_resolution_hybrid_grid,
+           const HybridGrid* low_resolution_hybrid_grid,
+           const Eigen::VectorXf* rotational_scan_matcher_histogram)
+      : local_pose_(local_pose),
+        high_(high_resolution_hybrid_grid),
+        low_(low_resolution_hybrid_grid),
+        histogram_(rotational_scan_matcher_histogram) {}
+  transform::Rigid3d local_pose() const { return local_pose_; }
+  const HybridGrid& high_resolution_hybrid_grid() const { return *high_; }
+  const HybridGrid& low_resolution_hybrid_grid() const { return *low_; }
+  const Eigen::VectorXf& rotational_scan_matcher_histogram() const { return *histogram_; }
 
  private:
-  int branch_and_bound_depth_ = 0, full_resolution_depth_ = 0;
-  double min_rotational_score_ = 0., min_low_resolution_score_ = 0.;
-  double linear_xy_search_window_ = 0., linear_z_search_window_ = 0., angular_search_window_ = 0.;
+  transform::Rigid3d local_pose_;
+  const HybridGrid* high_;
+  const HybridGrid* low_;
+  const Eigen::VectorXf* histogram_;
 };
-}  // namespace proto
-}  // namespace scan_matching
+
 }  // namespace mapping
 }  // namespace cartographer
 

@@ -1,10 +1,14 @@
 // Flat C entry points over the 3D host layer (FastCorrelativeScanMatcher3D), for
 // ctypes-driven parity tests and the C5 bench.  Product code: reference-shaped
 // classes + C ABI only; never touches oracle/.
+#include <chrono>
+#include <condition_variable>
 #include <cstring>
 #include <memory>
+#include <mutex>
 
 #include "cartographer/mapping/internal/3d/scan_matching/fast_correlative_scan_matcher_3d.h"
+#include "cartographer/mapping/internal/constraints/constraint_builder_3d.h"
 
 using namespace cartographer;
 using mapping::scan_matching::DeviceContext;
@@ -207,6 +211,100 @@ int csmh_fcsm3d_discrete_scans(void* ctx, void* m, void* node, const double* nod
   job.linear_z_window = 0;
   job.low_resolution_grid = h->matcher->low_resolution_grid();
   return csm_discretize3d(static_cast<DeviceContext*>(ctx)->get(), &job, cells) == CSM_OK ? S : -1;
+}
+
+// ConstraintBuilder3D driven like PoseGraph3D does (one NotifyEndOfNode per search) on
+// `num_devices` GPUs.  Submaps are given as matcher holders (their grids and
+// histogram are borrowed; the builder constructs its own matchers).  options6 =
+// {sampling_ratio, max_constraint_distance, min_score, global_localization_min_score,
+// loop_closure_translation_weight, loop_closure_rotation_weight}; fcsm_options7 as for
+// csmh_fcsm3d_create.  Per search i: found[i] and the constraint transform
+// submap <- node as 7 doubles.  Returns wall seconds from the first MaybeAdd* call to
+// the WhenDone callback.
+double csmh_constraint_builder3d_run(int num_devices, const int* devices, int num_pool_threads,
+                                     int flush_threshold, const double* options6,
+                                     const double* fcsm_options7, int num_submaps, void* const* submap_holders,
+                                     int num_searches, const int32_t* search_submap,
+                                     const int32_t* search_full, void* const* nodes,
+                                     const double* node_poses, const double* submap_poses, int32_t* found,
+                                     double* transform7, double* stats4) {
+  using mapping::constraints::ConstraintBuilder3D;
+  mapping::constraints::proto::ConstraintBuilderOptions o;
+  o.set_sampling_ratio(options6[0]);
+  o.set_max_constraint_distance(options6[1]);
+  o.set_min_score(options6[2]);
+  o.set_global_localization_min_score(options6[3]);
+  o.set_loop_closure_translation_weight(options6[4]);
+  o.set_loop_closure_rotation_weight(options6[5]);
+  auto* f = o.mutable_fast_correlative_scan_matcher_options_3d();
+  f->set_branch_and_bound_depth(static_cast<int>(fcsm_options7[0]));
+  f->set_full_resolution_depth(static_cast<int>(fcsm_options7[1]));
+  f->set_min_rotational_score(fcsm_options7[2]);
+  f->set_min_low_resolution_score(fcsm_options7[3]);
+  f->set_linear_xy_search_window(fcsm_options7[4]);
+  f->set_linear_z_search_window(fcsm_options7[5]);
+  f->set_angular_search_window(fcsm_options7[6]);
+  std::vector<mapping::Submap3D> submaps;
+  for (int i = 0; i < num_submaps; ++i) {
+    const Matcher3DHolder* h = static_cast<Matcher3DHolder*>(submap_holders[i]);
+    submaps.emplace_back(transform::Rigid3d::Identity(), h->grid.get(), h->low_grid.get(), &h->histogram);
+  }
+  for (int i = 0; i < num_searches; ++i) found[i] = 0;
+  double seconds = 0.;
+  {
+    common::ThreadPool pool(num_pool_threads);
+    ConstraintBuilder3D builder(o, &pool, std::vector<int>(devices, devices + num_devices));
+    builder.set_flush_threshold(flush_threshold);
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    ConstraintBuilder3D::Result result;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < num_searches; ++i) {
+      const int s = search_submap[i];
+      const mapping::TrajectoryNode::Data* data = &static_cast<Node3DHolder*>(nodes[i])->data;
+      const transform::Rigid3d np = Pose7(node_poses + 7 * i), sp = Pose7(submap_poses + 7 * i);
+      if (search_full[i]) {
+        builder.MaybeAddGlobalConstraint(mapping::SubmapId{0, s}, &submaps[s], mapping::NodeId{0, i}, data,
+                                         np.rotation(), sp.rotation());
+      } else {
+        builder.MaybeAddConstraint(mapping::SubmapId{0, s}, &submaps[s], mapping::NodeId{0, i}, data, np, sp);
+      }
+      builder.NotifyEndOfNode();
+    }
+    builder.WhenDone([&](const ConstraintBuilder3D::Result& r) {
+      std::lock_guard<std::mutex> l(m);
+      result = r;
+      done = true;
+      cv.notify_all();
+    });
+    {
+      std::unique_lock<std::mutex> l(m);
+      cv.wait(l, [&] { return done; });
+    }
+    seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    int last = -1;
+    for (const auto& c : result) {
+      const int i = c.node_id.node_index;
+      CSM_CHECK(i > last);  // submission order
+      last = i;
+      found[i] = 1;
+      const transform::Rigid3d& p = c.pose.zbar_ij;
+      const double v[7] = {p.translation().x(), p.translation().y(), p.translation().z(), p.rotation().w(),
+                           p.rotation().x(),    p.rotation().y(),    p.rotation().z()};
+      for (int k = 0; k < 7; ++k) transform7[7 * i + k] = v[k];
+    }
+    const auto st = builder.stats();
+    if (stats4) {
+      stats4[0] = static_cast<double>(st.searches);
+      stats4[1] = static_cast<double>(st.found);
+      stats4[2] = static_cast<double>(st.candidates_scored);
+      stats4[3] = static_cast<double>(st.flushes);
+    }
+    CSM_CHECK(builder.GetNumFinishedNodes() == num_searches);
+    for (int s = 0; s < num_submaps; ++s) builder.DeleteScanMatcher(mapping::SubmapId{0, s});
+  }
+  return seconds;
 }
 
 }  // extern "C"

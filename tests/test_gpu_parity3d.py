@@ -275,3 +275,53 @@ def test_match3d_periodic_world_top_level_ties(csm, gpu_ctx):
     assert r_o.found
     _compare(r_o, r_g)
     assert r_g.tie_resolution in (1, 2)
+
+
+def test_constraint_builder3d_protocol_and_results(csm, gpu_ctx):
+    """ConstraintBuilder3D (constraint_builder_3d_test.cc:61-115 protocol): every search
+    answered, non-null constraints in submission order, transforms identical to the
+    oracle's matcher on the same (node, submap) pairs, distance gate and sampler applied."""
+    worlds = [synth3d.World3D(61 + k, size_xy=8.0) for k in range(2)]
+    opt = ob.options3d(6, 3, 0.3, 0.4, 1.2, 0.4, np.radians(10))
+    oracle_m, gpu_m = [], []
+    for w in worlds:
+        xyz, val = w.voxels(w.res)
+        lxyz, lval = w.voxels(w.low_res)
+        om, gm = _pair(csm, gpu_ctx, 0.1, xyz, val, 0.45, lxyz, lval, w.submap_histogram(), opt)
+        oracle_m.append(om)
+        gpu_m.append(gm)
+    rng = np.random.default_rng(8)
+    nodes, raw, node_poses, search_submap, search_full = [], [], [], [], []
+    for i in range(12):
+        s = i % 2
+        hi, lo, hist, grav, true = worlds[s].node(np.append(rng.uniform(-2, 2, 2), 0.2), rng.uniform(-1, 1),
+                                                  n_high=200, n_low=50, max_range=5.0)
+        init = true.copy()
+        init[:3] += rng.uniform(-0.4, 0.4, 3) * [1, 1, 0.3]
+        if i == 7:
+            init[:3] += [100.0, 0, 0]  # beyond max_constraint_distance: never searched
+        full = 1 if i in (3, 8) else 0
+        if full:
+            init[:3] = 0.0
+        nodes.append(csm.Node3D(hi, lo, hist, grav))
+        raw.append((hi, lo, hist, grav))
+        node_poses.append(init.astype(np.float32).astype(np.float64))
+        search_submap.append(s)
+        search_full.append(full)
+    ident = np.tile(ob.IDENTITY_POSE7.astype(np.float64), (12, 1))
+    found, transform, stats, _ = csm.constraint_builder3d_run(
+        gpu_m, search_submap, search_full, nodes, np.array(node_poses), ident, opt, min_score=0.45,
+        global_localization_min_score=0.5, pool_threads=3, flush_threshold=5)
+    assert stats["searches"] == 11 and stats["flushes"] >= 2
+    for i in range(12):
+        hi, lo, hist, grav = raw[i]
+        if i == 7:
+            assert not found[i]
+            continue
+        r = oracle_m[search_submap[i]].match(hi, lo, hist, 0.5 if search_full[i] else 0.45,
+                                             node_poses[i].astype(np.float32), ob.IDENTITY_POSE7, grav,
+                                             bool(search_full[i]))
+        assert bool(found[i]) == bool(r.found)
+        if r.found:
+            assert np.array_equal(transform[i].astype(np.float32), np.array(r.pose, np.float32))
+    assert found.sum() == stats["found"] and found.sum() >= 6
