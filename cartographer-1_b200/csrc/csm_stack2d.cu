@@ -107,7 +107,10 @@ k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, uint32_t*
 // __vmaxu4, writing the tile's bytes of every level and its quad words as it goes.
 // HBM traffic: the cells once (plus halo re-reads served by L2) and every output once.
 // ---------------------------------------------------------------------------
-constexpr int kFusedLogTile = 6;
+#ifndef CSM_FUSED_LOG_TILE
+#define CSM_FUSED_LOG_TILE 6
+#endif
+constexpr int kFusedLogTile = CSM_FUSED_LOG_TILE;
 constexpr int kFusedTile = 1 << kFusedLogTile;
 constexpr int kFusedMaxDepth = 7;
 constexpr int kFusedThreads = 512;
@@ -227,7 +230,7 @@ k_stack_fused(const FusedArgs a) {
   // the two dependent global loads are pipelined across the row instead of serialised.
   {
     uint8_t* A8 = reinterpret_cast<uint8_t*>(bufA);
-    constexpr int kMaxPerLane = (kFusedTile + (1 << (kFusedMaxDepth - 1))) / 32;  // 4
+    constexpr int kMaxPerLane = (kFusedTile + (1 << (kFusedMaxDepth - 1))) / 32;
     for (int ry = warp; ry < R; ry += kWarps) {
       const int y = Y0 - P + ry;
       const bool row_ok = static_cast<unsigned>(y) < static_cast<unsigned>(a.num_y);
