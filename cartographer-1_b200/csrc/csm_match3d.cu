@@ -101,47 +101,57 @@ __device__ int node_sum(const Job3Dev& j, const int4* __restrict__ cells, int d,
 }
 
 // Children of the node (ox, oy, oz) at depth d >= 1 in generation order
-// k = 4*zbit + 2*ybit + xbit (:412-430).  Returns the valid-child mask.
+// k = 4*zbit + 2*ybit + xbit (:412-430).  Returns the valid-child mask.  One 8-byte
+// pack load per point delivers all eight child values; two children are accumulated
+// per 32-bit register as 16-bit halves and flushed before they can overflow.
 __device__ unsigned int children_sums(const Job3Dev& j, const int4* __restrict__ cells, int d, int ox,
                                       int oy, int oz, int lane, int sums[8]) {
   const int cd = d - 1;
   const int half = 1 << cd;
   const Level3& L = j.sd->level[cd];
   const int e = max(0, cd - j.frd + 1);
-  const int stride = half >> e;
+  const int stride = L.stride;  // == half >> e
   const int sx = -j.wxy, sz = -j.wz;
-  const int kx = (ox >> e) - (sx >> e) - L.lo[0];
-  const int ky = (oy >> e) - (sx >> e) - L.lo[1];
-  const int kz = (oz >> e) - (sz >> e) - L.lo[2];
-  const int nx = L.dim[0], ny = L.dim[1], nz = L.dim[2];
-  const uint8_t* __restrict__ data = L.data;
+  const int kx = (ox >> e) - (sx >> e) - L.lo[0] + stride;  // pack coordinates of the first child
+  const int ky = (oy >> e) - (sx >> e) - L.lo[1] + stride;
+  const int kz = (oz >> e) - (sz >> e) - L.lo[2] + stride;
+  const int px = L.pdim[0], py = L.pdim[1], pz = L.pdim[2];
+  const uint2* __restrict__ pack = L.pack;
   const bool vx = ox + half <= j.wxy, vy = oy + half <= j.wxy, vz = oz + half <= j.wz;
   unsigned int valid = 1u;
   for (int k = 1; k < 8; ++k)
     if ((!(k & 1) || vx) && (!(k & 2) || vy) && (!(k & 4) || vz)) valid |= 1u << k;
+  unsigned int p01 = 0, p23 = 0, p45 = 0, p67 = 0;
   int acc[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) acc[k] = 0;
-  for (int i = lane; i < j.n; i += kWarp) {
-    const int4 c = cells[i];
-    const int x0 = ((c.x + sx) >> e) + kx, y0 = ((c.y + sx) >> e) + ky, z0 = ((c.z + sz) >> e) + kz;
-    const int x1 = x0 + stride, y1 = y0 + stride, z1 = z0 + stride;
-    const bool ix0 = inside(x0, nx), ix1 = inside(x1, nx) && vx;
-    const bool iy0 = inside(y0, ny), iy1 = inside(y1, ny) && vy;
-    const bool iz0 = inside(z0, nz), iz1 = inside(z1, nz) && vz;
-    const int r00 = (z0 * ny + y0) * nx, r01 = (z0 * ny + y1) * nx;
-    const int r10 = (z1 * ny + y0) * nx, r11 = (z1 * ny + y1) * nx;
-    if (iz0 && iy0 && ix0) acc[0] += data[r00 + x0];
-    if (iz0 && iy0 && ix1) acc[1] += data[r00 + x1];
-    if (iz0 && iy1 && ix0) acc[2] += data[r01 + x0];
-    if (iz0 && iy1 && ix1) acc[3] += data[r01 + x1];
-    if (iz1 && iy0 && ix0) acc[4] += data[r10 + x0];
-    if (iz1 && iy0 && ix1) acc[5] += data[r10 + x1];
-    if (iz1 && iy1 && ix0) acc[6] += data[r11 + x0];
-    if (iz1 && iy1 && ix1) acc[7] += data[r11 + x1];
+  // 256 points per lane between flushes (256 * 255 < 65536)
+  for (int base = lane; base < j.n; base += 256 * kWarp) {
+    const int end = min(j.n, base + 256 * kWarp);
+#pragma unroll 4
+    for (int i = base; i < end; i += kWarp) {
+      const int4 c = cells[i];
+      const int xp = ((c.x + sx) >> e) + kx, yp = ((c.y + sx) >> e) + ky, zp = ((c.z + sz) >> e) + kz;
+      if (inside(xp, px) && inside(yp, py) && inside(zp, pz)) {
+        const uint2 v = pack[(zp * py + yp) * px + xp];
+        p01 += __byte_perm(v.x, 0u, 0x4140);
+        p23 += __byte_perm(v.x, 0u, 0x4342);
+        p45 += __byte_perm(v.y, 0u, 0x4140);
+        p67 += __byte_perm(v.y, 0u, 0x4342);
+      }
+    }
+    acc[0] += p01 & 0xFFFF;
+    acc[1] += p01 >> 16;
+    acc[2] += p23 & 0xFFFF;
+    acc[3] += p23 >> 16;
+    acc[4] += p45 & 0xFFFF;
+    acc[5] += p45 >> 16;
+    acc[6] += p67 & 0xFFFF;
+    acc[7] += p67 >> 16;
+    p01 = p23 = p45 = p67 = 0;
   }
 #pragma unroll
-  for (int k = 0; k < 8; ++k) sums[k] = __reduce_add_sync(kFull, acc[k]);
+  for (int k = 0; k < 8; ++k) sums[k] = ((valid >> k) & 1u) ? __reduce_add_sync(kFull, acc[k]) : 0;
   return valid;
 }
 

@@ -8,13 +8,25 @@
 
 namespace csm {
 
-// One precomputation level: bytes [z][y][x] over the box lo .. lo + dim - 1 (cell
-// indices of that level's own resolution); everything outside the box is 0, the
-// default of the reference's sparse grid (hybrid_grid.h:263-279).
+// One precomputation level over the box lo .. lo + dim - 1 (cell indices of that
+// level's own resolution); everything outside the box is 0, the default of the
+// reference's sparse grid (hybrid_grid.h:263-279).
+//   data: bytes [z][y][x], byte-identical to the reference's level (parity tests, lowest-
+//         resolution scoring, input of the next level's build).
+//   pack: what the branch-and-bound sweep reads.  Element [zp][yp][xp] with
+//         (xp, yp, zp) = (x, y, z) + stride in [0, pdim) holds the EIGHT values a parent
+//         needs for its children, byte k = value(x + stride*(k&1), y + stride*((k>>1)&1),
+//         z + stride*(k>>2)), k in the reference's generation order (FCSM3D.cc:412-430);
+//         `stride` is the distance in cells between sibling children on this level
+//         (2^level, divided by the per-level reduction of :335-342).  One 8-byte load per
+//         (parent, point) instead of eight scattered byte loads.
 struct Level3 {
   const uint8_t* data;
+  const uint2* pack;
   int lo[3];
   int dim[3];
+  int stride;
+  int pdim[3];  // dim + stride
 };
 
 struct Stack3Dev {
@@ -109,6 +121,7 @@ struct csm_stack3d {
   int depth = 0, frd = 0;
   uint8_t* base = nullptr;
   size_t level_off[CSM_MAX_DEPTH] = {0};
+  size_t pack_off[CSM_MAX_DEPTH] = {0};
   csm::Stack3Dev host_view;
   csm::Stack3Dev* dev = nullptr;
   size_t bytes = 0;

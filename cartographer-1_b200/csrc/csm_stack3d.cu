@@ -80,6 +80,34 @@ k3_level_up(const UpArgs a) {
   a.out[(static_cast<size_t>(z) * a.out_dim[1] + y) * a.out_dim[0] + x] = static_cast<uint8_t>(m);
 }
 
+// The sweep's layout: element (xp, yp, zp) gathers the eight child values of the parent
+// whose first child sits at (xp, yp, zp) - stride.  One thread per element, x fastest.
+struct PackArgs {
+  const uint8_t* in;
+  uint2* out;
+  int dim[3], pdim[3];
+  int stride;
+};
+__global__ void __launch_bounds__(256)
+k3_pack(const PackArgs a) {
+  const int xp = blockIdx.x * blockDim.x + threadIdx.x;
+  const int yp = blockIdx.y, zp = blockIdx.z;
+  if (xp >= a.pdim[0]) return;
+  unsigned int w[2] = {0u, 0u};
+  for (int k = 0; k < 8; ++k) {
+    const int x = xp - a.stride + ((k & 1) ? a.stride : 0);
+    const int y = yp - a.stride + ((k & 2) ? a.stride : 0);
+    const int z = zp - a.stride + ((k & 4) ? a.stride : 0);
+    unsigned int v = 0;
+    if (static_cast<unsigned int>(x) < static_cast<unsigned int>(a.dim[0]) &&
+        static_cast<unsigned int>(y) < static_cast<unsigned int>(a.dim[1]) &&
+        static_cast<unsigned int>(z) < static_cast<unsigned int>(a.dim[2]))
+      v = a.in[(static_cast<size_t>(z) * a.dim[1] + y) * a.dim[0] + x];
+    w[k >> 2] |= v << (8 * (k & 3));
+  }
+  a.out[(static_cast<size_t>(zp) * a.pdim[1] + yp) * a.pdim[0] + xp] = make_uint2(w[0], w[1]);
+}
+
 __global__ void __launch_bounds__(256)
 k3_grid_fill(float* __restrict__ out, size_t count, float v) {
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < count;
@@ -185,8 +213,23 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
         L.lo[a] = any ? l[a] : 0;
         L.dim[a] = any ? h[a] - l[a] + 1 : 0;
       }
+      // distance between sibling children of a parent whose children live on level k
+      L.stride = (1 << k) >> std::max(0, k - full_resolution_depth + 1);
+      size_t pack_elems = 1;
+      for (int a = 0; a < 3; ++a) {
+        L.pdim[a] = any ? L.dim[a] + L.stride : 0;
+        pack_elems *= static_cast<size_t>(L.pdim[a]);
+      }
+      if (pack_elems >= (1ull << 31) || L.pdim[1] > 65535 || L.pdim[2] > 65535) {
+        set_error("3D level %d is too large (%d x %d x %d)", k, L.dim[0], L.dim[1], L.dim[2]);
+        delete s;
+        return CSM_ERR_ARG;
+      }
       s->level_off[k] = total;
       total += align256(static_cast<size_t>(L.dim[0]) * L.dim[1] * L.dim[2]);
+      // the top level is never a child level: no pack
+      s->pack_off[k] = total;
+      if (k + 1 < depth) total += align256(sizeof(uint2) * pack_elems);
     }
   }
   s->bytes = total + align256(sizeof(Stack3Dev)) + 65536;
@@ -201,7 +244,11 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
   }
   uint8_t* lut_dev = s->base + total + align256(sizeof(Stack3Dev));
   s->dev = reinterpret_cast<Stack3Dev*>(s->base + total);
-  for (int k = 0; k < depth; ++k) s->host_view.level[k].data = s->base + s->level_off[k];
+  for (int k = 0; k < depth; ++k) {
+    s->host_view.level[k].data = s->base + s->level_off[k];
+    s->host_view.level[k].pack =
+        k + 1 < depth ? reinterpret_cast<const uint2*>(s->base + s->pack_off[k]) : nullptr;
+  }
   cudaStream_t st = ctx->stream;
   int rc = upload_voxels(ctx, voxel_xyz, voxel_values, num_voxels);
   if (rc != CSM_OK) return fail(rc);
@@ -235,6 +282,18 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
         return fail(CSM_ERR_ARG);
       }
       ++ctx->launches, k3_level_up<<<dim3((o.dim[0] + 255) / 256, o.dim[1], o.dim[2]), 256, 0, st>>>(a);
+    }
+    for (int k = 0; k + 1 < depth; ++k) {
+      const Level3& L = s->host_view.level[k];
+      PackArgs p;
+      p.in = L.data;
+      p.out = reinterpret_cast<uint2*>(s->base + s->pack_off[k]);
+      for (int c = 0; c < 3; ++c) {
+        p.dim[c] = L.dim[c];
+        p.pdim[c] = L.pdim[c];
+      }
+      p.stride = L.stride;
+      ++ctx->launches, k3_pack<<<dim3((L.pdim[0] + 255) / 256, L.pdim[1], L.pdim[2]), 256, 0, st>>>(p);
     }
   }
   if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
