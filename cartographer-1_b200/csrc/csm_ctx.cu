@@ -50,6 +50,47 @@ void PinBuf::release() {
   cap = 0;
 }
 
+int BlockPool::take(bool pin, size_t bytes, void** out, size_t* cap) {
+  std::vector<Block>& list = pin ? pinned : device;
+  int best = -1;
+  for (size_t i = 0; i != list.size(); ++i)
+    if (list[i].cap >= bytes && list[i].cap <= 4 * bytes + (1u << 20) &&
+        (best < 0 || list[i].cap < list[best].cap))
+      best = static_cast<int>(i);
+  if (best >= 0) {
+    *out = list[best].p;
+    *cap = list[best].cap;
+    list.erase(list.begin() + best);
+    return CSM_OK;
+  }
+  const size_t want = bytes + bytes / 8 + 4096;
+  if (pin) {
+    CSM_CUDA(cudaHostAlloc(out, want, cudaHostAllocDefault));
+  } else {
+    CSM_CUDA(cudaMalloc(out, want));
+  }
+  *cap = want;
+  return CSM_OK;
+}
+void BlockPool::give(bool pin, void* p, size_t cap) {
+  if (!p) return;
+  std::vector<Block>& list = pin ? pinned : device;
+  list.push_back(Block{p, cap});
+  if (list.size() > kMaxBlocks) {  // drop the smallest
+    size_t k = 0;
+    for (size_t i = 1; i != list.size(); ++i)
+      if (list[i].cap < list[k].cap) k = i;
+    if (pin) cudaFreeHost(list[k].p); else cudaFree(list[k].p);
+    list.erase(list.begin() + k);
+  }
+}
+void BlockPool::release() {
+  for (Block& b : device) cudaFree(b.p);
+  for (Block& b : pinned) cudaFreeHost(b.p);
+  device.clear();
+  pinned.clear();
+}
+
 }  // namespace csm
 
 extern "C" {
@@ -103,6 +144,7 @@ void csm_ctx_destroy(csm_ctx* c) {
   c->tmp1.release();
   c->tmp2.release();
   c->pin0.release();
+  c->pool.release();
   c->frontier[0].release();
   c->frontier[1].release();
   if (c->ev0) cudaEventDestroy(c->ev0);

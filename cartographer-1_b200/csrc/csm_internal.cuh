@@ -56,6 +56,22 @@ struct PinBuf {
   }
 };
 
+// Free lists of device / pinned blocks a context keeps between batches: a batch's arena
+// and staging buffer are a cudaMalloc + cudaHostAlloc + two frees otherwise (several
+// milliseconds per batch end to end).  Blocks are reused when at most 4x oversized; at
+// most kMaxBlocks are kept per kind.
+struct BlockPool {
+  struct Block {
+    void* p;
+    size_t cap;
+  };
+  static constexpr size_t kMaxBlocks = 6;
+  std::vector<Block> device, pinned;
+  int take(bool pin, size_t bytes, void** out, size_t* cap);
+  void give(bool pin, void* p, size_t cap);
+  void release();
+};
+
 }  // namespace csm
 
 struct csm_ctx {
@@ -66,6 +82,7 @@ struct csm_ctx {
   // scratch for csm_discretize2d / stack builds
   csm::DevBuf tmp0, tmp1, tmp2;
   csm::PinBuf pin0;
+  csm::BlockPool pool;
   // Branch-and-bound frontier ping-pong buffers, shared by every batch that runs on
   // this context (runs are stream-ordered, the frontier is pure scratch).
   csm::DevBuf frontier[2];

@@ -823,7 +823,10 @@ namespace {
 size_t align_up(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
 
 void free_batch_device(csm_batch2d* b) {
-  if (b->arena) cudaFree(b->arena);
+  if (b->arena) {
+    if (b->owner) b->owner->pool.give(false, b->arena, b->arena_cap);
+    else cudaFree(b->arena);
+  }
   b->arena = nullptr;
 }
 
@@ -849,10 +852,9 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   const size_t o_cnt = take(sizeof(unsigned int) * kNumCounters);
   const size_t o_res = take(sizeof(csm_result2d) * b->num_jobs);
   const size_t o_hist = take(sizeof(unsigned long long) * CSM_MAX_DEPTH * 33);
-  cudaError_t e = cudaMalloc(&b->arena, off);
-  if (e != cudaSuccess) {
+  if (b->owner->pool.take(false, off, &b->arena, &b->arena_cap) != CSM_OK) {
     b->arena = nullptr;
-    set_error("cudaMalloc of a %zu-byte batch arena failed: %s", off, cudaGetErrorString(e));
+    set_error("allocation of a %zu-byte batch arena failed: %s", off, cudaGetErrorString(cudaGetLastError()));
     return CSM_ERR_CUDA;
   }
   b->arena_bytes = off;
@@ -925,7 +927,10 @@ void csm_batch2d_destroy(csm_ctx* ctx, csm_batch2d* b) {
   }
   free_batch_device(b);
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
-  if (b->pinned) cudaFreeHost(b->pinned);
+  if (b->pinned) {
+    if (b->owner) b->owner->pool.give(true, b->pinned, b->pinned_cap);
+    else cudaFreeHost(b->pinned);
+  }
   delete b;
 }
 
@@ -1009,9 +1014,11 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
   const size_t s_quat = align_up(sizeof(float) * 2 * b->total_scans);
   const size_t s_res = align_up(sizeof(csm_result2d) * num_jobs);
   b->pinned_bytes = s_jobs + s_pts + s_quat + s_res;
-  cudaError_t e = cudaHostAlloc(&b->pinned, b->pinned_bytes, cudaHostAllocDefault);
-  if (e != cudaSuccess) {
-    set_error("cudaHostAlloc(%zu) failed: %s", b->pinned_bytes, cudaGetErrorString(e));
+  b->owner = ctx;
+  if (ctx->pool.take(true, b->pinned_bytes, &b->pinned, &b->pinned_cap) != CSM_OK) {
+    set_error("pinned allocation of %zu bytes failed: %s", b->pinned_bytes,
+              cudaGetErrorString(cudaGetLastError()));
+    b->pinned = nullptr;
     delete b;
     return CSM_ERR_CUDA;
   }

@@ -145,8 +145,10 @@ struct csm_batch2d {
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
   unsigned long long* hist = nullptr;  // [depth][alive nodes per tile] tile counts (profiling)
-  void* arena = nullptr;               // single cudaMalloc backing all of the above
-  size_t arena_bytes = 0;
+  csm_ctx* owner = nullptr;            // context whose block pool backs arena / pinned
+  void* arena = nullptr;               // single device block backing all of the above
+  size_t arena_bytes = 0, arena_cap = 0;
+  size_t pinned_cap = 0;
   void* pinned = nullptr;              // staging for uploads / results
   size_t pinned_bytes = 0;
   bool uploaded = false, ran = false;

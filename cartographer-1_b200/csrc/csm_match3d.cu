@@ -844,7 +844,7 @@ struct Carve {
 };
 
 int allocate_batch3(csm_batch3d* b, unsigned int contender_cap, unsigned int winner_cap) {
-  if (b->arena) cudaFree(b->arena);
+  if (b->arena) b->owner->pool.give(false, b->arena, b->arena_cap);
   b->arena = nullptr;
   b->contender_cap = contender_cap;
   b->winner_cap = winner_cap;
@@ -866,8 +866,8 @@ int allocate_batch3(csm_batch3d* b, unsigned int contender_cap, unsigned int win
   const size_t o_cnt = c.take(sizeof(unsigned int) * kNumCounters3);
   const size_t o_res = c.take(sizeof(csm_result3d) * b->num_jobs);
   b->arena_bytes = std::max<size_t>(c.at, 256);
-  if (cudaMalloc(&b->arena, b->arena_bytes) != cudaSuccess) {
-    set_error("cudaMalloc of %zu bytes for a 3D batch failed: %s", b->arena_bytes,
+  if (b->owner->pool.take(false, b->arena_bytes, &b->arena, &b->arena_cap) != CSM_OK) {
+    set_error("allocation of %zu bytes for a 3D batch failed: %s", b->arena_bytes,
               cudaGetErrorString(cudaGetLastError()));
     b->arena = nullptr;
     return CSM_ERR_CUDA;
@@ -934,8 +934,14 @@ void csm_batch3d_destroy(csm_ctx* ctx, csm_batch3d* b) {
     cudaStreamSynchronize(ctx->stream);
   }
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
-  if (b->arena) cudaFree(b->arena);
-  if (b->pinned) cudaFreeHost(b->pinned);
+  if (b->arena) {
+    if (b->owner) b->owner->pool.give(false, b->arena, b->arena_cap);
+    else cudaFree(b->arena);
+  }
+  if (b->pinned) {
+    if (b->owner) b->owner->pool.give(true, b->pinned, b->pinned_cap);
+    else cudaFreeHost(b->pinned);
+  }
   delete b;
 }
 
@@ -945,6 +951,7 @@ int csm_batch3d_upload(csm_ctx* ctx, const csm_job3d* jobs, int num_jobs, csm_ba
   CSM_CUDA(cudaSetDevice(ctx->device));
   *out = nullptr;
   csm_batch3d* b = new csm_batch3d;
+  b->owner = ctx;
   b->num_jobs = num_jobs;
   b->jobs_host.resize(num_jobs);
   auto fail = [&](int rc) {
@@ -1011,8 +1018,8 @@ int csm_batch3d_upload(csm_ctx* ctx, const csm_job3d* jobs, int num_jobs, csm_ba
   const PinLayout p = pin_layout(b);
   b->pinned_bytes = p.total;
   b->pin_results_off = p.res;
-  if (cudaMallocHost(&b->pinned, b->pinned_bytes) != cudaSuccess) {
-    set_error("cudaMallocHost of %zu bytes failed", b->pinned_bytes);
+  if (ctx->pool.take(true, b->pinned_bytes, &b->pinned, &b->pinned_cap) != CSM_OK) {
+    set_error("pinned allocation of %zu bytes failed", b->pinned_bytes);
     b->pinned = nullptr;
     return fail(CSM_ERR_CUDA);
   }

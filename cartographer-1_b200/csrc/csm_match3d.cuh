@@ -159,10 +159,11 @@ struct csm_batch3d {
   unsigned long long frontier_want = 0;
   unsigned int* counters = nullptr;
   csm_result3d* results_dev = nullptr;
+  csm_ctx* owner = nullptr;  // context whose block pool backs arena / pinned
   void* arena = nullptr;
-  size_t arena_bytes = 0;
+  size_t arena_bytes = 0, arena_cap = 0;
   void* pinned = nullptr;
-  size_t pinned_bytes = 0;
+  size_t pinned_bytes = 0, pinned_cap = 0;
   size_t pin_results_off = 0;
   bool uploaded = false, ran = false;
   std::vector<cudaEvent_t> prof_events;  // kPhases + 1 events of the last profiled run

@@ -4,6 +4,8 @@
 #include <cmath>
 #include <cstring>
 
+#include "parallel_for.h"
+
 namespace cartographer {
 namespace mapping {
 namespace scan_matching {
@@ -130,8 +132,9 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
   std::vector<std::vector<float>> xyz(n), quats(n);
   std::vector<csm_job2d> jobs(n);
   std::vector<double> lattice_estimate(n);
-  params_.reserve(n);
-  for (size_t i = 0; i != n; ++i) {
+  params_.assign(n, SearchParameters(0, 0, 0., 0.));
+  // Host side of every search (search parameters, angle tables: libm): independent.
+  common::ParallelFor(n, [&](const size_t i) {
     const FastCorrelativeScanMatcher2D& m = *queries[i].first;
     const Query& q = queries[i].second;
     CSM_CHECK(q.point_cloud != nullptr);
@@ -139,17 +142,17 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
     if (q.full_submap) {
       // Window around the submap centre that includes it fully
       // (reference: fast_correlative_scan_matcher_2d.cc:215-222).
-      params_.emplace_back(1e6 * res, M_PI, *q.point_cloud, res);
+      params_[i] = SearchParameters(1e6 * res, M_PI, *q.point_cloud, res);
       const double half_res = 0.5 * res;
       initial_[i] = transform::Rigid2d::Translation(transform::Vector2d(
           m.limits_.max().x() - half_res * m.limits_.cell_limits().num_y_cells,
           m.limits_.max().y() - half_res * m.limits_.cell_limits().num_x_cells));
     } else {
-      params_.emplace_back(m.options_.linear_search_window(), m.options_.angular_search_window(),
-                           *q.point_cloud, res);
+      params_[i] = SearchParameters(m.options_.linear_search_window(), m.options_.angular_search_window(),
+                                    *q.point_cloud, res);
       initial_[i] = q.initial_pose_estimate;
     }
-    const SearchParameters& sp = params_.back();
+    const SearchParameters& sp = params_[i];
     xyz[i].resize(3 * q.point_cloud->size());
     double reach = 0.;
     for (size_t p = 0; p != q.point_cloud->size(); ++p) {
@@ -187,7 +190,7 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
     const double wx = std::min(2. * job.linear_bound, m.limits_.cell_limits().num_x_cells + ext);
     const double wy = std::min(2. * job.linear_bound, m.limits_.cell_limits().num_y_cells + ext);
     lattice_estimate[i] = sp.num_scans * (wx / step + 1.) * (wy / step + 1.);
-  }
+  });
   // Split into device batches of bounded footprint.
   constexpr double kLatticeBudget = 48e6;
   constexpr size_t kMaxJobs = 4096;

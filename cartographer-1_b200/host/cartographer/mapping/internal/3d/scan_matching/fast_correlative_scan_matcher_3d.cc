@@ -4,6 +4,8 @@
 #include <cmath>
 #include <cstring>
 
+#include "parallel_for.h"
+
 namespace cartographer {
 namespace mapping {
 namespace scan_matching {
@@ -217,7 +219,8 @@ FastCorrelativeScanMatcher3D::Batch::Batch(DeviceContext* context, const QueryLi
   prepared_.resize(n);
   std::vector<csm_job3d> jobs(n);
   std::vector<double> footprint(n);
-  for (size_t i = 0; i != n; ++i) {
+  // Host side of every search (angles, rotational prefilter, slice poses): independent.
+  common::ParallelFor(n, [&](const size_t i) {
     const FastCorrelativeScanMatcher3D& m = *queries[i].first;
     const Query& q = queries[i].second;
     CSM_CHECK(q.constant_data != nullptr);
@@ -259,7 +262,7 @@ FastCorrelativeScanMatcher3D::Batch::Batch(DeviceContext* context, const QueryLi
     job.min_score = q.min_score;
     job.min_low_resolution_score = m.options_.min_low_resolution_score();
     footprint[i] = static_cast<double>(job.num_scans) * job.num_points;
-  }
+  });
   constexpr double kCellBudget = 128e6;  // discrete cells (16 B each) per device batch
   constexpr size_t kMaxJobs = 1024;
   size_t begin = 0;
