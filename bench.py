@@ -101,7 +101,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.samples.append([x.strip() for x in line.split(",")])
 
-    def stop(self):
+    def mark(self):
+        """Index of the next sample: call at the start of the timed region."""
+        return len(self.samples)
+
+    def stop(self, first=0):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -111,7 +115,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
+        # Samples of the timed region; a region shorter than nvidia-smi's period falls
+        # back to the last samples of the identical warm-up steps just before it.
+        chosen = self.samples[first:] or self.samples[-3:]
+        for s in chosen:
             try:
                 sm.append(float(s[0]))
                 mx.append(float(s[1]))
@@ -197,7 +204,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "searches/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def num_scans_of(cloud, res):
@@ -272,13 +279,14 @@ def run_b200(args):
         return pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
 
     # ---- device-resident arm ---------------------------------------------------------
+    sampler = ClockSampler(local)
+    sampler.start()  # before the warm-up: nvidia-smi needs a moment to deliver samples
     for _ in range(args.warmup):
         timed(resident_step)
     build_ms.clear()
     abi.csm_ctx_set_profiling(raw, 1)  # per-phase events; resets the accumulators
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
+    first_sample = sampler.mark()
     launches0 = abi.csm_ctx_launch_count(raw)
     ms_resident = 0.0
     for _ in range(args.steps):
@@ -286,7 +294,7 @@ def run_b200(args):
         ms_resident += ms
     launches = abi.csm_ctx_launch_count(raw) - launches0
     barrier()
-    clocks = sampler.stop()
+    clocks = sampler.stop(first_sample)
     phase_ms = (C.c_double * 5)()
     phase_scored = (C.c_double * 5)()
     runs = C.c_int()
@@ -404,13 +412,24 @@ def run_b200(args):
                       "identical to the GPU's" % (n_done, secs),
             "candidate_scores_per_s": (stats[0] + stats[1]) / secs}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The one JSON line goes to the real stdout; everything else a library prints there
+    (NCCL's version banner, torchrun notes) was redirected to stderr at start-up."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
 if __name__ == "__main__":
     a = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # fd 1 now points at stderr for this process and anything it loads
     if a.impl == "reference":
         run_reference(a)
     else:
