@@ -58,7 +58,7 @@ ABI_SYMBOLS = [
     "csm_stack3d_build", "csm_stack3d_level", "csm_stack3d_depth", "csm_stack3d_device_bytes",
     "csm_stack3d_destroy", "csm_grid3d_build", "csm_grid3d_destroy", "csm_match3d_batch",
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
-    "csm_discretize3d",
+    "csm_discretize3d", "csm_rt_match3d_batch",
 ]
 
 _abi = None
@@ -152,6 +152,10 @@ def host():
     L.csmh_constraint_builder3d_run.argtypes = [
         C.c_int, i32p, C.c_int, C.c_int, f64p, f64p, C.c_int, C.POINTER(C.c_void_p), C.c_int, i32p, i32p,
         C.POINTER(C.c_void_p), f64p, f64p, i32p, f64p, f64p]
+    L.csmh_rt_match3d.restype = C.c_float
+    L.csmh_rt_match3d.argtypes = [C.c_float, i32p, u16p, C.c_int, f64p, f64p, f32p, C.c_int, f64p]
+    L.csmh_rt_match3d_batch.argtypes = [C.c_void_p, C.c_float, i32p, u16p, C.c_int, f64p, C.c_int, f64p, f32p,
+                                        i64p, f32p, f64p, i32p, i32p]
     L.csmh_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     L.csmh_fcsm3d_discrete_scans.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, f64p, f64p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
@@ -505,3 +509,39 @@ def constraint_builder3d_run(submap_matchers, search_submap, search_full, nodes,
         np.ascontiguousarray(submap_poses, np.float64).reshape(-1), found, transform.reshape(-1), stats)
     return found, transform, dict(searches=int(stats[0]), found=int(stats[1]),
                                   candidates_scored=int(stats[2]), flushes=int(stats[3])), secs
+
+
+def rt_options(linear_search_window=0.15, angular_search_window=np.radians(1.0),
+               translation_delta_cost_weight=1e-1, rotation_delta_cost_weight=1e-1):
+    return np.array([linear_search_window, angular_search_window, translation_delta_cost_weight,
+                     rotation_delta_cost_weight], np.float64)
+
+
+def rt_match3d(resolution, xyz, values, options4, initial_pose7, points):
+    """RealTimeCorrelativeScanMatcher3D::Match (reference signature): (score, pose7)."""
+    xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)
+    values = np.ascontiguousarray(values, np.uint16)
+    pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+    pose = np.zeros(7, np.float64)
+    score = host().csmh_rt_match3d(resolution, xyz, values, len(values), np.ascontiguousarray(options4, np.float64),
+                                   np.ascontiguousarray(initial_pose7, np.float64), pts.reshape(-1), len(pts), pose)
+    return score, pose
+
+
+def rt_match3d_batch(ctx, resolution, xyz, values, options4, initial_poses7, clouds):
+    """Several clouds against one grid state: (scores, poses[n, 7], best_index, num_candidates)."""
+    xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)
+    values = np.ascontiguousarray(values, np.uint16)
+    n = len(clouds)
+    offsets = np.zeros(n + 1, np.int64)
+    offsets[1:] = np.cumsum([len(c) for c in clouds])
+    pts = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in clouds]))
+    scores = np.zeros(n, np.float32)
+    poses = np.zeros((n, 7), np.float64)
+    best = np.zeros(n, np.int32)
+    num = np.zeros(n, np.int32)
+    host().csmh_rt_match3d_batch(ctx.h, resolution, xyz, values, len(values),
+                                 np.ascontiguousarray(options4, np.float64), n,
+                                 np.ascontiguousarray(initial_poses7, np.float64).reshape(-1), pts.reshape(-1),
+                                 offsets, scores, poses.reshape(-1), best, num)
+    return scores, poses, best, num

@@ -8,6 +8,7 @@
 #include <mutex>
 
 #include "cartographer/mapping/internal/3d/scan_matching/fast_correlative_scan_matcher_3d.h"
+#include "cartographer/mapping/internal/3d/scan_matching/real_time_correlative_scan_matcher_3d.h"
 #include "cartographer/mapping/internal/constraints/constraint_builder_3d.h"
 
 using namespace cartographer;
@@ -305,6 +306,70 @@ double csmh_constraint_builder3d_run(int num_devices, const int* devices, int nu
     for (int s = 0; s < num_submaps; ++s) builder.DeleteScanMatcher(mapping::SubmapId{0, s});
   }
   return seconds;
+}
+
+// RealTimeCorrelativeScanMatcher3D::Match through the reference signature: the grid is
+// given as a voxel list.  options4 = {linear_search_window, angular_search_window,
+// translation_delta_cost_weight, rotation_delta_cost_weight}.  Returns the score.
+float csmh_rt_match3d(float resolution, const int32_t* xyz, const uint16_t* values, int n_voxels,
+                      const double* options4, const double* initial_pose7, const float* pts, int n,
+                      double* pose7_out) {
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n_voxels; ++i)
+    *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  mapping::scan_matching::proto::RealTimeCorrelativeScanMatcherOptions o;
+  o.set_linear_search_window(options4[0]);
+  o.set_angular_search_window(options4[1]);
+  o.set_translation_delta_cost_weight(options4[2]);
+  o.set_rotation_delta_cost_weight(options4[3]);
+  const mapping::scan_matching::RealTimeCorrelativeScanMatcher3D matcher(o);
+  sensor::PointCloud cloud;
+  for (int i = 0; i < n; ++i) cloud.push_back({sensor::Vector3f(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2])});
+  transform::Rigid3d pose;
+  const float score = matcher.Match(Pose7(initial_pose7), cloud, grid, &pose);
+  const double v[7] = {pose.translation().x(), pose.translation().y(), pose.translation().z(),
+                       pose.rotation().w(),    pose.rotation().x(),    pose.rotation().y(),
+                       pose.rotation().z()};
+  for (int k = 0; k < 7; ++k) pose7_out[k] = v[k];
+  return score;
+}
+
+// The same for a batch of clouds against one grid state resident on the device.
+int csmh_rt_match3d_batch(void* ctx, float resolution, const int32_t* xyz, const uint16_t* values,
+                          int n_voxels, const double* options4, int num, const double* initial_poses7,
+                          const float* pts, const int64_t* offsets, float* scores, double* poses7_out,
+                          int32_t* best_index, int32_t* num_candidates) {
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n_voxels; ++i)
+    *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  const mapping::scan_matching::DeviceHybridGrid device_grid(context, grid);
+  mapping::scan_matching::proto::RealTimeCorrelativeScanMatcherOptions o;
+  o.set_linear_search_window(options4[0]);
+  o.set_angular_search_window(options4[1]);
+  o.set_translation_delta_cost_weight(options4[2]);
+  o.set_rotation_delta_cost_weight(options4[3]);
+  const mapping::scan_matching::RealTimeCorrelativeScanMatcher3D matcher(o);
+  std::vector<sensor::PointCloud> clouds(num);
+  std::vector<mapping::scan_matching::RealTimeCorrelativeScanMatcher3D::Query> queries(num);
+  for (int i = 0; i < num; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2])});
+    queries[i].initial_pose_estimate = Pose7(initial_poses7 + 7 * i);
+    queries[i].point_cloud = &clouds[i];
+    queries[i].grid = &device_grid;
+  }
+  const auto answers = matcher.MatchBatch(context, queries);
+  for (int i = 0; i < num; ++i) {
+    scores[i] = answers[i].score;
+    best_index[i] = answers[i].best_index;
+    num_candidates[i] = answers[i].num_candidates;
+    const transform::Rigid3d& p = answers[i].pose_estimate;
+    const double v[7] = {p.translation().x(), p.translation().y(), p.translation().z(), p.rotation().w(),
+                         p.rotation().x(),    p.rotation().y(),    p.rotation().z()};
+    for (int k = 0; k < 7; ++k) poses7_out[7 * i + k] = v[k];
+  }
+  return num;
 }
 
 }  // extern "C"

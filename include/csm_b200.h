@@ -275,6 +275,32 @@ void csm_batch3d_destroy(csm_ctx* ctx, csm_batch3d* batch);
  * indices, num_scans x num_points x 3 int32 (FCSM3D.cc:205-211). */
 int csm_discretize3d(csm_ctx* ctx, const csm_job3d* job, int32_t* out_xyz);
 
+/* ---- RealTimeCorrelativeScanMatcher3D::Match
+ * (.../3d/scan_matching/real_time_correlative_scan_matcher_3d.cc:35-114) -------------
+ * Exhaustive search over the transforms of GenerateExhaustiveSearchTransforms (:55-98).
+ * The host generates them (AngleAxis -> quaternion needs libm), composes each with the
+ * initial pose and evaluates the motion penalty exp(-(|t| w_t + angle w_r)^2) in double
+ * (:108-112); the device transforms the cloud by every candidate pose, looks the
+ * probabilities up (grid = csm_grid3d_build of the live HybridGrid), sums them in point
+ * order in fp32 (:104-107) and returns the first maximum in generation order (:47-50).
+ */
+typedef struct {
+  const csm_grid3d* grid;
+  const float* points_xyz;
+  int32_t num_points;
+  int32_t num_candidates;
+  const float* candidate_poses;   /* num_candidates x 7 (tx,ty,tz,qw,qx,qy,qz): initial * transform */
+  const double* penalty;          /* num_candidates                                     */
+  float resolution;               /* HybridGrid::resolution()                           */
+} csm_rt_job3d;
+
+typedef struct {
+  int32_t best_index;             /* generation index of the winner                     */
+  float score;                    /* its score (bit-identical fp32)                     */
+} csm_rt_result3d;
+
+int csm_rt_match3d_batch(csm_ctx* ctx, const csm_rt_job3d* jobs, int num_jobs, csm_rt_result3d* results);
+
 /* ---- measurement aids (bench.py) ------------------------------------------------
  * csm_ctx_launch_count: kernels launched through `ctx` since it was created.
  * csm_measure_gather_rate: the L2 gather roofline G_L2 of the scoring loop

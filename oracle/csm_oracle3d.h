@@ -600,6 +600,82 @@ class FastCorrelativeScanMatcher3D {
   const Histogram* submap_histogram_;
 };
 
+// ---------------------------------------------------------------------------
+// RealTimeCorrelativeScanMatcher3D (real_time_correlative_scan_matcher_3d.cc:30-114)
+// ---------------------------------------------------------------------------
+// transform.h:33-37 with FloatType = float
+inline float GetAngle(const Rigid3f& t) {
+  return 2.f * std::atan2(Norm3(Vec3f{t.q.x, t.q.y, t.q.z}), std::abs(t.q.w));
+}
+
+class RealTimeCorrelativeScanMatcher3D {
+ public:
+  explicit RealTimeCorrelativeScanMatcher3D(const RealTimeCorrelativeScanMatcherOptions& o) : options_(o) {}
+
+  // :55-98
+  std::vector<Rigid3f> GenerateExhaustiveSearchTransforms(const float resolution,
+                                                          const std::vector<Vec3f>& cloud) const {
+    std::vector<Rigid3f> result;
+    const int linear_window_size = RoundToInt(options_.linear_search_window / resolution);
+    float max_scan_range = 3.f * resolution;
+    for (const Vec3f& p : cloud) max_scan_range = std::max(Norm3(p), max_scan_range);
+    const float kSafetyMargin = 1.f - 1e-3f;
+    const float angular_step_size =
+        kSafetyMargin *
+        std::acos(1.f - (resolution * resolution) / (2.f * (max_scan_range * max_scan_range)));
+    const int angular_window_size = RoundToInt(options_.angular_search_window / angular_step_size);
+    for (int z = -linear_window_size; z <= linear_window_size; ++z)
+      for (int y = -linear_window_size; y <= linear_window_size; ++y)
+        for (int x = -linear_window_size; x <= linear_window_size; ++x)
+          for (int rz = -angular_window_size; rz <= angular_window_size; ++rz)
+            for (int ry = -angular_window_size; ry <= angular_window_size; ++ry)
+              for (int rx = -angular_window_size; rx <= angular_window_size; ++rx) {
+                Rigid3f t;
+                t.t = Vec3f{x * resolution, y * resolution, z * resolution};
+                t.q = AngleAxisVectorToRotationQuaternion(
+                    Vec3f{rx * angular_step_size, ry * angular_step_size, rz * angular_step_size});
+                result.push_back(t);
+              }
+    return result;
+  }
+
+  // :100-114; the cloud is transformed point by point (sensor/point_cloud.cc:56-64)
+  float ScoreCandidate(const HybridGrid& grid, const std::vector<Vec3f>& cloud, const Rigid3f& candidate,
+                       const Rigid3f& transform) const {
+    float score = 0.f;
+    for (const Vec3f& p : cloud) score += grid.GetProbability(grid.GetCellIndex(Apply(candidate, p)));
+    score /= static_cast<float>(cloud.size());
+    const float angle = GetAngle(transform);
+    const double t = Norm3(transform.t) * options_.translation_delta_cost_weight +
+                     angle * options_.rotation_delta_cost_weight;
+    score *= std::exp(-(t * t));  // float *= double
+    ORACLE_CHECK(score > 0.f);
+    return score;
+  }
+
+  // :35-53.  best_index: position of the winner among the generated transforms.
+  float Match(const Rigid3f& initial_pose_estimate, const std::vector<Vec3f>& cloud, const HybridGrid& grid,
+              Rigid3f* pose_estimate, int* best_index = nullptr) const {
+    ORACLE_CHECK(pose_estimate != nullptr);
+    float best_score = -1.f;
+    int index = 0;
+    for (const Rigid3f& transform : GenerateExhaustiveSearchTransforms(grid.resolution(), cloud)) {
+      const Rigid3f candidate = Mul(initial_pose_estimate, transform);
+      const float score = ScoreCandidate(grid, cloud, candidate, transform);
+      if (score > best_score) {
+        best_score = score;
+        *pose_estimate = candidate;
+        if (best_index) *best_index = index;
+      }
+      ++index;
+    }
+    return best_score;
+  }
+
+ private:
+  RealTimeCorrelativeScanMatcherOptions options_;
+};
+
 }  // namespace oracle
 
 #endif  // ORACLE_CSM_ORACLE3D_H_

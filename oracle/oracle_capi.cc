@@ -394,6 +394,30 @@ void oracle_fcsm3d_match(void* m, int full, const float* node_pose7, const float
   out->candidates_scored = r.candidates_scored;
 }
 
+// RealTimeCorrelativeScanMatcher3D::Match.  options4 = {linear_search_window,
+// angular_search_window, translation_delta_cost_weight, rotation_delta_cost_weight}.
+// Returns the score; pose7_out = winning pose, *best_index its generation index,
+// *num_candidates the size of the search space.
+float oracle_rt_match3d(void* grid, const double* options4, const float* initial_pose7, const float* pts,
+                        int n, float* pose7_out, int* best_index, int* num_candidates) {
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.linear_search_window = options4[0];
+  o.angular_search_window = options4[1];
+  o.translation_delta_cost_weight = options4[2];
+  o.rotation_delta_cost_weight = options4[3];
+  const RealTimeCorrelativeScanMatcher3D matcher(o);
+  std::vector<Vec3f> cloud;
+  for (int i = 0; i < n; ++i) cloud.push_back(Vec3f{pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]});
+  const HybridGrid& g = *static_cast<HybridGrid*>(grid);
+  if (num_candidates)
+    *num_candidates = static_cast<int>(matcher.GenerateExhaustiveSearchTransforms(g.resolution(), cloud).size());
+  Rigid3f pose;
+  const float score = matcher.Match(Pose7(initial_pose7), cloud, g, &pose, best_index);
+  const float v[7] = {pose.t.x, pose.t.y, pose.t.z, pose.q.w, pose.q.x, pose.q.y, pose.q.z};
+  for (int k = 0; k < 7; ++k) pose7_out[k] = v[k];
+  return score;
+}
+
 // RotationalScanMatcher::Match (rotational_scan_matcher.cc:178-189).
 void oracle_rotational_match(const float* submap_hist, const float* hist, int n, float initial_angle,
                              const float* angles, int n_angles, float* out) {

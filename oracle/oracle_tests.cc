@@ -577,6 +577,34 @@ bool PoseIsNearly(const Rigid3f& a, const Rigid3f& b, const float eps) {
   return dt < eps && angle < eps;
 }
 
+// The literal matcher: ToEigen(a).isApprox(ToEigen(b), eps) on the 4x4 isometry
+// matrices, i.e. ||A - B||_F <= eps * min(||A||_F, ||B||_F)
+// (rigid_transform_test_helpers.h:36-46).
+bool IsometryIsApprox(const Rigid3f& a, const Rigid3f& b, const double eps) {
+  auto matrix = [](const Rigid3f& r, double m[16]) {
+    const double w = r.q.w, x = r.q.x, y = r.q.y, z = r.q.z;
+    const double rot[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                           2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                           2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)};
+    const double t[3] = {r.t.x, r.t.y, r.t.z};
+    for (int i = 0; i < 3; ++i) {
+      for (int j = 0; j < 3; ++j) m[4 * i + j] = rot[3 * i + j];
+      m[4 * i + 3] = t[i];
+    }
+    m[12] = m[13] = m[14] = 0.;
+    m[15] = 1.;
+  };
+  double ma[16], mb[16], d2 = 0., na = 0., nb = 0.;
+  matrix(a, ma);
+  matrix(b, mb);
+  for (int k = 0; k < 16; ++k) {
+    d2 += (ma[k] - mb[k]) * (ma[k] - mb[k]);
+    na += ma[k] * ma[k];
+    nb += mb[k] * mb[k];
+  }
+  return d2 <= eps * eps * std::min(na, nb);
+}
+
 void TestFcsm3DCorrectPoseForMatch(const int iterations) {
   Fcsm3DFixture f;
   constexpr float kMinScore = 0.1f;
@@ -615,6 +643,50 @@ void TestFcsm3DCorrectPoseForMatchFullSubmap() {
   EXPECT_TRUE(!low_resolution_result.found);
 }
 
+// real_time_correlative_scan_matcher_3d_test.cc:33-120: seven points painted into a
+// 0.1 m grid at the expected pose; every initial pose must come back to it within 1e-3.
+void TestRealTimeCorrelativeScanMatcher3D() {
+  HybridGrid grid(0.1f);
+  Rigid3f expected;
+  expected.t = Vec3f{-1.f, 0.f, 0.f};
+  std::vector<Vec3f> cloud;
+  for (const Vec3f& p : {Vec3f{-3.f, 2.f, 0.f}, Vec3f{-4.f, 2.f, 0.f}, Vec3f{-5.f, 2.f, 0.f},
+                         Vec3f{-6.f, 2.f, 0.f}, Vec3f{-6.f, 3.f, 1.f}, Vec3f{-6.f, 4.f, 2.f},
+                         Vec3f{-7.f, 3.f, 1.f}}) {
+    cloud.push_back(p);
+    grid.SetProbability(grid.GetCellIndex(Apply(expected, p)), 1.f);
+  }
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.linear_search_window = 0.3;
+  o.angular_search_window = 1. * M_PI / 180.;
+  o.translation_delta_cost_weight = 1e-1;
+  o.rotation_delta_cost_weight = 1.;
+  const RealTimeCorrelativeScanMatcher3D matcher(o);
+  const double a = 0.8 / 180. * M_PI;
+  struct Case {
+    Vec3f t;
+    int axis;  // -1: no rotation, 0: x, 1: y, 2: the (unnormalised) axis (0, 1, 1) of RotationAroundYZ
+  };
+  for (const Case& c : {Case{{-1.f, 0.f, 0.f}, -1}, Case{{-0.8f, 0.f, 0.f}, -1}, Case{{-1.f, 0.f, -0.2f}, -1},
+                        Case{{-0.9f, -0.2f, 0.2f}, -1}, Case{{-1.f, 0.f, 0.f}, 0}, Case{{-1.f, 0.f, 0.f}, 1},
+                        Case{{-1.f, 0.f, 0.f}, 2}}) {
+    Rigid3f initial;
+    initial.t = c.t;
+    if (c.axis >= 0) {
+      // Eigen::Quaterniond(AngleAxisd(a, axis)).cast<float>()
+      initial.q.w = static_cast<float>(std::cos(0.5 * a));
+      const float s = static_cast<float>(std::sin(0.5 * a));
+      if (c.axis == 0) initial.q.x = s;
+      if (c.axis >= 1) initial.q.y = s;
+      if (c.axis == 2) initial.q.z = s;
+    }
+    Rigid3f pose;
+    const float score = matcher.Match(initial, cloud, grid, &pose);
+    EXPECT_GT(score, 0.f);
+    EXPECT_TRUE(IsometryIsApprox(pose, expected, 1e-3));
+  }
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -631,6 +703,7 @@ int main(int argc, char** argv) {
   TestRotationalOnlySameHistogramIsScoreOne();
   TestRotationalInterpolatesAsExpected();
   TestLowResolutionScore();
+  TestRealTimeCorrelativeScanMatcher3D();
   TestFcsm3DCorrectPoseForMatch(quick ? 2 : 20);
   if (!quick) {
     TestFcsm3DCorrectPoseForMatchFullSubmap();

@@ -110,6 +110,9 @@ def lib():
                                       f32p, C.c_int, f64p, C.c_float, C.POINTER(OracleResult3D)]
     L.oracle_fcsm3d_discrete_scans.argtypes = [C.c_void_p, f64p, C.c_float, f32p, f32p, f32p, C.c_int,
                                                f32p, C.c_int, f64p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_rt_match3d.restype = C.c_float
+    L.oracle_rt_match3d.argtypes = [C.c_void_p, f64p, f32p, f32p, C.c_int, f32p, C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int)]
     L.oracle_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     _lib = L
     return L
@@ -310,3 +313,14 @@ def rotational_match(submap_hist, hist, initial_angle, angles):
     out = np.zeros(len(angles), np.float32)
     lib().oracle_rotational_match(submap_hist, hist, len(hist), initial_angle, angles, len(angles), out)
     return out
+
+
+def rt_match3d(grid, options4, initial_pose7, points):
+    """RealTimeCorrelativeScanMatcher3D::Match: (score, pose7 float32, best_index, num_candidates)."""
+    pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+    pose = np.zeros(7, np.float32)
+    best, num = C.c_int(), C.c_int()
+    score = lib().oracle_rt_match3d(grid.h, np.ascontiguousarray(options4, np.float64),
+                                    np.ascontiguousarray(initial_pose7, np.float32), pts.reshape(-1), len(pts),
+                                    pose, C.byref(best), C.byref(num))
+    return score, pose, best.value, num.value

@@ -325,3 +325,57 @@ def test_constraint_builder3d_protocol_and_results(csm, gpu_ctx):
         if r.found:
             assert np.array_equal(transform[i].astype(np.float32), np.array(r.pose, np.float32))
     assert found.sum() == stats["found"] and found.sum() >= 6
+
+
+RT_CLOUD = np.array([[-3, 2, 0], [-4, 2, 0], [-5, 2, 0], [-6, 2, 0], [-6, 3, 1], [-6, 4, 2], [-7, 3, 1]],
+                    np.float32)
+
+
+def _rt_fixture_grid():
+    """real_time_correlative_scan_matcher_3d_test.cc:36-48: the cloud painted at (-1, 0, 0)."""
+    cells = np.round((RT_CLOUD + np.array([-1, 0, 0], np.float32)) / np.float32(0.1)).astype(np.int32)
+    return cells, synth3d.probability_to_value(np.ones(len(cells)))
+
+
+def test_rt_match3d_reference_fixture(csm, gpu_ctx):
+    """RealTimeCorrelativeScanMatcher3DTest.* (:80-117): every initial pose returns to the
+    expected pose within the reference's 1e-3 isApprox bound, bit-identical to the oracle."""
+    xyz, val = _rt_fixture_grid()
+    og = ob.OracleGrid3D(0.1, xyz, val)
+    opt = csm.rt_options(0.3, np.radians(1.0), 1e-1, 1.0)
+    a = 0.8 / 180.0 * np.pi
+    s, c = np.sin(0.5 * a), np.cos(0.5 * a)
+    cases = [([-1, 0, 0], [1, 0, 0, 0]), ([-0.8, 0, 0], [1, 0, 0, 0]), ([-1, 0, -0.2], [1, 0, 0, 0]),
+             ([-0.9, -0.2, 0.2], [1, 0, 0, 0]), ([-1, 0, 0], [c, s, 0, 0]), ([-1, 0, 0], [c, 0, s, 0]),
+             ([-1, 0, 0], [c, 0, s, s])]
+    for t, q in cases:
+        init = np.array(list(t) + list(q), np.float64)
+        score_g, pose_g = csm.rt_match3d(0.1, xyz, val, opt, init, RT_CLOUD)
+        score_o, pose_o, best_o, num_o = ob.rt_match3d(og, opt, init.astype(np.float32), RT_CLOUD)
+        assert np.float32(score_g).tobytes() == np.float32(score_o).tobytes()
+        assert np.array_equal(pose_g.astype(np.float32), pose_o)
+        assert np.linalg.norm(pose_g[:3] - [-1, 0, 0]) < 2e-3 and abs(abs(pose_g[3]) - 1) < 1e-5
+
+
+def test_rt_match3d_world_bit_exact(csm, gpu_ctx):
+    w = synth3d.World3D(71, size_xy=8.0)
+    xyz, val = w.voxels(w.res)
+    og = ob.OracleGrid3D(0.1, xyz, val)
+    opt = csm.rt_options(0.15, np.radians(1.0), 1e-1, 1e-1)
+    rng = np.random.default_rng(72)
+    clouds, inits = [], []
+    for k in range(5):
+        hi, lo, hist, grav, true = w.node(np.append(rng.uniform(-2, 2, 2), 0.2), rng.uniform(-1, 1),
+                                          n_high=120 + 13 * k, n_low=10, max_range=4.0, tilt=(0.01, -0.02))
+        init = true.copy()
+        init[:3] += rng.uniform(-0.12, 0.12, 3)
+        init[3:] = synth3d.quat_mul(synth3d.yaw_quat(rng.uniform(-0.01, 0.01)), true[3:])
+        clouds.append(hi)
+        inits.append(init.astype(np.float32).astype(np.float64))
+    scores, poses, best, num = csm.rt_match3d_batch(gpu_ctx, 0.1, xyz, val, opt, np.array(inits), clouds)
+    for k in range(5):
+        score_o, pose_o, best_o, num_o = ob.rt_match3d(og, opt, inits[k].astype(np.float32), clouds[k])
+        assert num[k] == num_o and num_o > 100
+        assert best[k] == best_o
+        assert np.float32(scores[k]).tobytes() == np.float32(score_o).tobytes()
+        assert np.array_equal(poses[k].astype(np.float32), pose_o)
