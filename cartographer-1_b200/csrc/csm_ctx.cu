@@ -1,6 +1,7 @@
 // Context, error reporting and scratch-memory helpers of libcsm_b200.so.
 #include <cstdarg>
 #include <cstring>
+#include <set>
 
 #include "csm_internal.cuh"
 
@@ -50,7 +51,19 @@ void PinBuf::release() {
   cap = 0;
 }
 
+namespace {
+std::mutex g_live_mu;
+std::set<const csm_ctx*> g_live;
+}  // namespace
+
+bool ctx_alive_on(const csm_ctx* ctx, int device) {
+  if (ctx == nullptr) return false;
+  std::lock_guard<std::mutex> l(g_live_mu);
+  return g_live.count(ctx) != 0 && ctx->device == device;
+}
+
 int BlockPool::take(bool pin, size_t bytes, void** out, size_t* cap) {
+  std::lock_guard<std::mutex> l(mu);
   std::vector<Block>& list = pin ? pinned : device;
   int best = -1;
   for (size_t i = 0; i != list.size(); ++i)
@@ -74,6 +87,7 @@ int BlockPool::take(bool pin, size_t bytes, void** out, size_t* cap) {
 }
 void BlockPool::give(bool pin, void* p, size_t cap) {
   if (!p) return;
+  std::lock_guard<std::mutex> l(mu);
   std::vector<Block>& list = pin ? pinned : device;
   list.push_back(Block{p, cap});
   if (list.size() > kMaxBlocks) {  // drop the smallest
@@ -85,6 +99,7 @@ void BlockPool::give(bool pin, void* p, size_t cap) {
   }
 }
 void BlockPool::release() {
+  std::lock_guard<std::mutex> l(mu);
   for (Block& b : device) cudaFree(b.p);
   for (Block& b : pinned) cudaFreeHost(b.p);
   device.clear();
@@ -132,12 +147,20 @@ int csm_ctx_create(int device, csm_ctx** out) {
   CSM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CSM_CUDA(cudaEventCreate(&c->ev0));
   CSM_CUDA(cudaEventCreate(&c->ev1));
+  {
+    std::lock_guard<std::mutex> l(csm::g_live_mu);
+    csm::g_live.insert(c);
+  }
   *out = c;
   return CSM_OK;
 }
 
 void csm_ctx_destroy(csm_ctx* c) {
   if (!c) return;
+  {
+    std::lock_guard<std::mutex> l(csm::g_live_mu);
+    csm::g_live.erase(c);
+  }
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   c->tmp0.release();

@@ -7,6 +7,7 @@
 #include <stdint.h>
 
 #include <cstdio>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -59,7 +60,8 @@ struct PinBuf {
 // Free lists of device / pinned blocks a context keeps between batches: a batch's arena
 // and staging buffer are a cudaMalloc + cudaHostAlloc + two frees otherwise (several
 // milliseconds per batch end to end).  Blocks are reused when at most 4x oversized; at
-// most kMaxBlocks are kept per kind.
+// most kMaxBlocks are kept per kind.  take/give are internally locked: an object built on
+// a context may be destroyed from another thread than the one driving it.
 struct BlockPool {
   struct Block {
     void* p;
@@ -67,10 +69,15 @@ struct BlockPool {
   };
   static constexpr size_t kMaxBlocks = 6;
   std::vector<Block> device, pinned;
+  std::mutex mu;
   int take(bool pin, size_t bytes, void** out, size_t* cap);
   void give(bool pin, void* p, size_t cap);
   void release();
 };
+
+// True while `ctx` is a live context on `device` (registry of csm_ctx_create/destroy):
+// destroy entry points use it to decide whether a block can go back to a pool.
+bool ctx_alive_on(const csm_ctx* ctx, int device);
 
 }  // namespace csm
 
@@ -120,7 +127,8 @@ struct StackDev {
 struct csm_stack2d {
   int device = 0;
   int num_x = 0, num_y = 0, depth = 0;
-  uint8_t* base = nullptr;                // one allocation for all levels
+  uint8_t* base = nullptr;                // one allocation: levels, quads, descriptor, LUT
+  size_t base_cap = 0;                    // capacity of that block (pooled)
   size_t level_off[CSM_MAX_DEPTH] = {0};  // byte offset of level i inside base
   size_t quad_off[CSM_MAX_DEPTH] = {0};   // byte offset of quad level i inside base
   csm::StackDev host_view;                // copy of *dev

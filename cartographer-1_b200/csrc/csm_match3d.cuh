@@ -124,7 +124,7 @@ struct csm_stack3d {
   size_t pack_off[CSM_MAX_DEPTH] = {0};
   csm::Stack3Dev host_view;
   csm::Stack3Dev* dev = nullptr;
-  size_t bytes = 0;
+  size_t bytes = 0, cap = 0;  // cap: capacity of the pooled block behind base
 };
 
 struct csm_grid3d {
@@ -132,7 +132,7 @@ struct csm_grid3d {
   float* data = nullptr;
   csm::Grid3Dev host_view;
   csm::Grid3Dev* dev = nullptr;
-  size_t bytes = 0;
+  size_t bytes = 0, cap = 0;
 };
 
 struct csm_batch3d {

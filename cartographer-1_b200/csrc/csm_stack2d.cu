@@ -429,15 +429,18 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
     off += (static_cast<size_t>(two_s) * two_s * in * jn * 4 + 255) & ~static_cast<size_t>(255);
   }
   s->bytes = off;
-  cudaError_t e = cudaMalloc(&s->base, s->bytes);
-  if (e == cudaSuccess) e = cudaMalloc(&s->q_lut_dev, 65536);
-  if (e == cudaSuccess) e = cudaMalloc(&s->dev, sizeof(csm::StackDev));
-  if (e != cudaSuccess) {
-    csm::set_error("cudaMalloc of a %zu-byte stack failed: %s", s->bytes, cudaGetErrorString(e));
-    if (s->base) cudaFree(s->base);
+  // levels | quads | descriptor | quantisation table, one pooled block
+  const size_t o_dev = off, o_lut = o_dev + ((sizeof(csm::StackDev) + 255) & ~static_cast<size_t>(255));
+  void* block = nullptr;
+  if (ctx->pool.take(false, o_lut + 65536, &block, &s->base_cap) != CSM_OK) {
+    csm::set_error("allocation of a %zu-byte stack failed: %s", s->bytes,
+                   cudaGetErrorString(cudaGetLastError()));
     delete s;
     return CSM_ERR_CUDA;
   }
+  s->base = static_cast<uint8_t*>(block);
+  s->dev = reinterpret_cast<csm::StackDev*>(s->base + o_dev);
+  s->q_lut_dev = s->base + o_lut;
   s->host_view.num_x = num_x;
   s->host_view.num_y = num_y;
   s->host_view.depth = depth;
@@ -512,10 +515,15 @@ size_t csm_stack2d_device_bytes(const csm_stack2d* s) { return s ? s->bytes + 65
 void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* s) {
   if (!s) return;
   cudaSetDevice(s->device);
-  if (ctx) cudaStreamSynchronize(ctx->stream); else cudaDeviceSynchronize();
-  if (s->base) cudaFree(s->base);
-  if (s->q_lut_dev) cudaFree(s->q_lut_dev);
-  if (s->dev) cudaFree(s->dev);
+  // `ctx` may be stale (a matcher can outlive the context it was built on): only a
+  // live context of the stack's device gets the block back into its pool.
+  if (csm::ctx_alive_on(ctx, s->device)) {
+    cudaStreamSynchronize(ctx->stream);
+    ctx->pool.give(false, s->base, s->base_cap);
+  } else {
+    cudaDeviceSynchronize();
+    if (s->base) cudaFree(s->base);
+  }
   delete s;
 }
 

@@ -234,13 +234,17 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
   }
   s->bytes = total + align256(sizeof(Stack3Dev)) + 65536;
   auto fail = [&](int rc) {
-    if (s->base) cudaFree(s->base);
+    ctx->pool.give(false, s->base, s->cap);
     delete s;
     return rc;
   };
-  if (cudaMalloc(&s->base, s->bytes) != cudaSuccess) {
-    set_error("cudaMalloc of %zu bytes for a 3D precomputation stack failed", s->bytes);
-    return fail(CSM_ERR_CUDA);
+  {
+    void* block = nullptr;
+    if (ctx->pool.take(false, s->bytes, &block, &s->cap) != CSM_OK) {
+      set_error("allocation of %zu bytes for a 3D precomputation stack failed", s->bytes);
+      return fail(CSM_ERR_CUDA);
+    }
+    s->base = static_cast<uint8_t*>(block);
   }
   uint8_t* lut_dev = s->base + total + align256(sizeof(Stack3Dev));
   s->dev = reinterpret_cast<Stack3Dev*>(s->base + total);
@@ -327,8 +331,13 @@ size_t csm_stack3d_device_bytes(const csm_stack3d* s) { return s ? s->bytes : 0;
 
 void csm_stack3d_destroy(csm_ctx* ctx, csm_stack3d* s) {
   if (!s) return;
-  if (ctx) cudaSetDevice(ctx->device);
-  if (s->base) cudaFree(s->base);
+  cudaSetDevice(s->device);
+  if (ctx_alive_on(ctx, s->device)) {  // see csm_stack2d_destroy
+    cudaStreamSynchronize(ctx->stream);
+    ctx->pool.give(false, s->base, s->cap);
+  } else if (s->base) {
+    cudaFree(s->base);
+  }
   delete s;
 }
 
@@ -354,13 +363,17 @@ int csm_grid3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vox
   const size_t s_data = align256(sizeof(float) * count), s_desc = align256(sizeof(Grid3Dev));
   g->bytes = s_data + s_desc + sizeof(float) * 65536;
   auto fail = [&](int rc) {
-    if (g->data) cudaFree(g->data);
+    ctx->pool.give(false, g->data, g->cap);
     delete g;
     return rc;
   };
-  if (cudaMalloc(&g->data, g->bytes) != cudaSuccess) {
-    set_error("cudaMalloc of %zu bytes for a low-resolution grid failed", g->bytes);
-    return fail(CSM_ERR_CUDA);
+  {
+    void* block = nullptr;
+    if (ctx->pool.take(false, g->bytes, &block, &g->cap) != CSM_OK) {
+      set_error("allocation of %zu bytes for a low-resolution grid failed", g->bytes);
+      return fail(CSM_ERR_CUDA);
+    }
+    g->data = static_cast<float*>(block);
   }
   char* base = reinterpret_cast<char*>(g->data);
   g->dev = reinterpret_cast<Grid3Dev*>(base + s_data);
@@ -392,8 +405,13 @@ int csm_grid3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vox
 
 void csm_grid3d_destroy(csm_ctx* ctx, csm_grid3d* g) {
   if (!g) return;
-  if (ctx) cudaSetDevice(ctx->device);
-  if (g->data) cudaFree(g->data);
+  cudaSetDevice(g->device);
+  if (ctx_alive_on(ctx, g->device)) {
+    cudaStreamSynchronize(ctx->stream);
+    ctx->pool.give(false, g->data, g->cap);
+  } else if (g->data) {
+    cudaFree(g->data);
+  }
   delete g;
 }
 

@@ -67,15 +67,17 @@ void FastCorrelativeScanMatcher2D::Build(const Grid2D& grid) {
   max_score_ = 1.f - grid.GetMinCorrespondenceCost();
   const std::vector<uint8> q = ComputeQuantizationTable(grid);
   const CellLimits& cells = limits_.cell_limits();
-  CheckOk(csm_stack2d_build(context_->get(), grid.correspondence_cost_cells().data(),
+  build_context_ = context_->get();
+  CheckOk(csm_stack2d_build(build_context_, grid.correspondence_cost_cells().data(),
                             cells.num_x_cells, cells.num_y_cells, q.data(),
                             options_.branch_and_bound_depth(), &stack_),
           "csm_stack2d_build");
 }
 
 FastCorrelativeScanMatcher2D::~FastCorrelativeScanMatcher2D() {
-  // The constructing thread's context may already be gone; the stack knows its device.
-  csm_stack2d_destroy(nullptr, stack_);
+  // The context the stack was built on may already be gone (the ABI checks its registry
+  // of live contexts before handing the block back to that context's pool).
+  csm_stack2d_destroy(build_context_, stack_);
 }
 
 bool FastCorrelativeScanMatcher2D::Match(const transform::Rigid2d& initial_pose_estimate,

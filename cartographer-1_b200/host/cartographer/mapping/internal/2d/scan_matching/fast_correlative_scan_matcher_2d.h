@@ -121,6 +121,7 @@ class FastCorrelativeScanMatcher2D {
   float max_score_ = 0.f;  // PrecomputationGrid2D::max_score_
   DeviceContext* context_ = nullptr;
   csm_stack2d* stack_ = nullptr;
+  csm_ctx* build_context_ = nullptr;  // raw handle: DeviceContext may be deleted before us
 };
 
 }  // namespace scan_matching

@@ -81,7 +81,8 @@ void FastCorrelativeScanMatcher3D::Build(const HybridGrid& hybrid_grid) {
   std::vector<uint16> values;
   hybrid_grid.Export(&xyz, &values);
   const std::vector<uint8> q = ComputeQuantizationTable3D();
-  CheckOk(csm_stack3d_build(context_->get(), xyz.data(), values.data(), static_cast<int>(values.size()),
+  build_context_ = context_->get();
+  CheckOk(csm_stack3d_build(build_context_, xyz.data(), values.data(), static_cast<int>(values.size()),
                             q.data(), options_.branch_and_bound_depth(),
                             options_.full_resolution_depth(), &stack_),
           "csm_stack3d_build");
@@ -92,8 +93,9 @@ void FastCorrelativeScanMatcher3D::Build(const HybridGrid& hybrid_grid) {
 }
 
 FastCorrelativeScanMatcher3D::~FastCorrelativeScanMatcher3D() {
-  csm_stack3d_destroy(nullptr, stack_);
-  csm_grid3d_destroy(nullptr, low_grid_);
+  // build_context_ may be stale by now; the ABI checks it against its live contexts.
+  csm_stack3d_destroy(build_context_, stack_);
+  csm_grid3d_destroy(build_context_, low_grid_);
 }
 
 std::unique_ptr<FastCorrelativeScanMatcher3D::Result> FastCorrelativeScanMatcher3D::Match(

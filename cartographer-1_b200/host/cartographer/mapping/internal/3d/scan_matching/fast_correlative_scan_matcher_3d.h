@@ -142,6 +142,7 @@ class FastCorrelativeScanMatcher3D {
   DeviceContext* context_ = nullptr;
   csm_stack3d* stack_ = nullptr;
   csm_grid3d* low_grid_ = nullptr;
+  csm_ctx* build_context_ = nullptr;  // raw handle the device blocks go back to
 };
 
 }  // namespace scan_matching

@@ -27,16 +27,16 @@ float GetAngle(const transform::Rigid3f& t) {
 }  // namespace
 
 DeviceHybridGrid::DeviceHybridGrid(DeviceContext* const context, const HybridGrid& hybrid_grid)
-    : resolution_(hybrid_grid.resolution()) {
+    : resolution_(hybrid_grid.resolution()), build_context_(context->get()) {
   std::vector<int32_t> xyz;
   std::vector<uint16> values;
   hybrid_grid.Export(&xyz, &values);
-  CheckOk(csm_grid3d_build(context->get(), xyz.data(), values.data(), static_cast<int>(values.size()),
+  CheckOk(csm_grid3d_build(build_context_, xyz.data(), values.data(), static_cast<int>(values.size()),
                            ValueToProbabilityTable().data(), &grid_),
           "csm_grid3d_build");
 }
 
-DeviceHybridGrid::~DeviceHybridGrid() { csm_grid3d_destroy(nullptr, grid_); }
+DeviceHybridGrid::~DeviceHybridGrid() { csm_grid3d_destroy(build_context_, grid_); }
 
 RealTimeCorrelativeScanMatcher3D::RealTimeCorrelativeScanMatcher3D(
     const proto::RealTimeCorrelativeScanMatcherOptions& options)

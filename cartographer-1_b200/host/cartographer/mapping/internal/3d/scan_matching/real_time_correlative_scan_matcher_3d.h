@@ -33,6 +33,7 @@ class DeviceHybridGrid {
  private:
   csm_grid3d* grid_ = nullptr;
   float resolution_;
+  csm_ctx* build_context_ = nullptr;
 };
 
 class RealTimeCorrelativeScanMatcher3D {

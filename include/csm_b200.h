@@ -101,6 +101,9 @@ int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* stack, int level, uint8_t
                       int* wide_x, int* wide_y);
 int csm_stack2d_depth(const csm_stack2d* stack);
 size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
+/* `ctx` may be NULL or a context that no longer exists: the stack's device block goes
+ * back to the block pool of `ctx` when that is still a live context on the stack's
+ * device (the next build reuses it without a cudaMalloc), and is freed otherwise. */
 void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* stack);
 
 /* ---- FastCorrelativeScanMatcher2D::MatchWithSearchParameters (FCSM2D.cc:227-262)
