@@ -1,5 +1,6 @@
 // Context, error reporting and scratch-memory helpers of libcsm_b200.so.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <set>
 
@@ -144,6 +145,10 @@ int csm_ctx_create(int device, csm_ctx** out) {
   csm_ctx* c = new csm_ctx;
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
+  {
+    const char* sweep = getenv("CSM_SWEEP");  // diagnostic: "tiles" selects the tile sweep
+    c->sweep_tiles = sweep != nullptr && strcmp(sweep, "tiles") == 0;
+  }
   CSM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CSM_CUDA(cudaEventCreate(&c->ev0));
   CSM_CUDA(cudaEventCreate(&c->ev1));
@@ -170,6 +175,7 @@ void csm_ctx_destroy(csm_ctx* c) {
   c->pool.release();
   c->frontier[0].release();
   c->frontier[1].release();
+  c->frontier_aux.release();
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);

@@ -93,7 +93,9 @@ struct csm_ctx {
   // Branch-and-bound frontier ping-pong buffers, shared by every batch that runs on
   // this context (runs are stream-ordered, the frontier is pure scratch).
   csm::DevBuf frontier[2];
-  unsigned long long frontier_cap = 0;  // nodes per buffer
+  csm::DevBuf frontier_aux;             // 2D node sweep: block descriptors | work items
+  bool sweep_tiles = false;             // CSM_SWEEP=tiles: the tile sweep instead of node lists
+  unsigned long long frontier_cap = 0;  // unused (capacities come from the buffers)
   // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
   static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2
   int profiling = 0;  // 0 off, 1 phase events, 2 + tile histogram

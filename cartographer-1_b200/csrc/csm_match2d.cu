@@ -52,7 +52,7 @@ constexpr int kWarp = 32;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kCntContenders = 32;
 constexpr int kCntOverflow = 33;
-constexpr int kNumCounters = 40;
+constexpr int kNumCounters = 96;
 
 // Tile shape: kTW x kTH parents, lane = lj * kTW + li.
 #ifndef CSM_LOG_TW
@@ -235,10 +235,13 @@ __device__ __forceinline__ void tile_sums(const StackDev& sd, const int2* __rest
 __global__ void __launch_bounds__(128)
 k_discretize(const JobDev* __restrict__ jobs, const float* __restrict__ points,
              const float* __restrict__ quats, int2* __restrict__ xy, ScanInfo* __restrict__ scans,
-             unsigned long long* __restrict__ scan_best, int shrink) {
+             unsigned long long* __restrict__ scan_best, unsigned int* __restrict__ bucket_js,
+             int shrink) {
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
   if (scan >= j.S) return;
+  if (bucket_js != nullptr && threadIdx.x == 0)
+    bucket_js[j.scan_off + scan] = (blockIdx.y << 16) | static_cast<unsigned int>(scan);
   const float qw = quats[2 * (j.quat_off + scan)], qs = quats[2 * (j.quat_off + scan) + 1];
   int mnx = 0, mny = 0, mxx = 0, mxy = 0;  // Array2i::Zero() seeds (CSM2D.cc:78-79)
   for (int p = threadIdx.x; p < j.n; p += blockDim.x) {
@@ -643,6 +646,386 @@ k_expand(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
 }
 
 // ---------------------------------------------------------------------------
+// 5'. Node-list sweep.  The tile sweep above keeps lane = lattice position, so a warp
+//     with 4 alive nodes of 32 still issues every instruction for 32 (mean occupancy
+//     on C3: 6.9 of 32).  Here the alive nodes of one (job, scan) -- a BUCKET -- are kept
+//     contiguous in one list, 4 bytes per node (i | j << 16 on the depth's lattice), and
+//     a warp takes 32 consecutive ones: lane = alive node.  For a scan point the word a
+//     node needs is quad[P(point) + j*in + i] with P the same for every node of the
+//     scan on that level (that is what the quad-phase layout buys), so the per-point
+//     term is staged once per warp and the per-(node, point) work is one broadcast
+//     shared-memory read, one address add, one load and the packed accumulate.
+//     Points whose window lies inside the plane for EVERY node of the chunk (by the
+//     chunk's bounding box) take the unchecked loop, points outside for every node are
+//     dropped, the rest takes a bounds-checked loop.
+//
+//     Keeping buckets contiguous: k_expand_nodes / k_seed_nodes append their survivors
+//     as BLOCKS to a scratch list (one atomic each on the scratch cursor, the bucket's
+//     counter and the block list), k_bucket_prefix turns the bucket counters into list
+//     offsets and k_place copies every block to its bucket's range and writes the work
+//     items (32-node chunks) of the next level.  Children are emitted in (parent lane,
+//     child) order, so lattice neighbours stay neighbours in the list.
+// ---------------------------------------------------------------------------
+struct NodeBlock {
+  unsigned int src, count, bucket, rel;  // scratch position, nodes, bucket, offset inside it
+};
+constexpr int kCntNodes = 0;     // + depth: nodes on the sorted list
+constexpr int kCntTmp = 48;      // + depth: scratch list fill
+constexpr int kCntBlocks = 64;   // + depth: blocks appended
+constexpr int kCntItems = 80;    // + depth: 32-node work items
+constexpr int kStagePoints = 128;
+
+struct NodeStage {
+  int in_p[kStagePoints];        // P of points inside for the whole chunk
+  int4 mix[kStagePoints];        // (P, ca0, ra0, -) of points that need the bounds check
+};
+
+// Sums of the four child values over all scan points for this lane's node (ni, nj).
+// Lanes beyond the chunk's node count carry a copy of lane 0's node.
+__device__ __forceinline__ void node_sums(const StackDev& sd, const int2* __restrict__ pts, int n,
+                                          int lvl, int x0, int y0, int ni, int nj, int lane,
+                                          NodeStage* __restrict__ stage, int (&sum)[4]) {
+  const int sh = lvl + 1, msk = (2 << lvl) - 1;
+  const int in = sd.in[lvl], jn = sd.jn[lvl];
+  const uint32_t* __restrict__ qb = sd.quad[lvl] + (static_cast<long long>(nj) * in + ni);
+  const int bi0 = __reduce_min_sync(kFull, ni), bi1 = __reduce_max_sync(kFull, ni);
+  const int bj0 = __reduce_min_sync(kFull, nj), bj1 = __reduce_max_sync(kFull, nj);
+  const uint32_t lt = (1u << lane) - 1u;
+  int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+  for (int p0 = 0; p0 < n; p0 += kStagePoints) {
+    int cin = 0, cmix = 0;
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < kStagePoints / kWarp; ++r) {
+      const int p = p0 + r * kWarp + lane;
+      bool inside = false, mixed = false;
+      int P = 0, ca0 = 0, ra0 = 0;
+      if (p < n) {
+        const int2 c = pts[p];
+        const int u0 = c.x + x0, v0 = c.y + y0;
+        ca0 = u0 >> sh;  // arithmetic shift = floor
+        ra0 = v0 >> sh;
+        P = ((((v0 & msk) << sh) + (u0 & msk)) * jn + ra0) * in + ca0;
+        const bool out = bi1 + ca0 < 0 || bi0 + ca0 >= in || bj1 + ra0 < 0 || bj0 + ra0 >= jn;
+        inside = bi0 + ca0 >= 0 && bi1 + ca0 < in && bj0 + ra0 >= 0 && bj1 + ra0 < jn;
+        mixed = !out && !inside;
+      }
+      const uint32_t m_in = __ballot_sync(kFull, inside), m_mix = __ballot_sync(kFull, mixed);
+      if (inside) stage->in_p[cin + __popc(m_in & lt)] = P;
+      if (mixed) stage->mix[cmix + __popc(m_mix & lt)] = make_int4(P, ca0, ra0, 0);
+      cin += __popc(m_in);
+      cmix += __popc(m_mix);
+    }
+    __syncwarp();
+    uint32_t lo = 0, hi = 0;  // two 16-bit fields each; 128 * 255 < 65536
+    int k = 0;
+    for (; k + 8 <= cin; k += 8) {
+      const int4 a = *reinterpret_cast<const int4*>(&stage->in_p[k]);
+      const int4 b = *reinterpret_cast<const int4*>(&stage->in_p[k + 4]);
+      const uint32_t w0 = __ldg(qb + a.x), w1 = __ldg(qb + a.y), w2 = __ldg(qb + a.z),
+                     w3 = __ldg(qb + a.w), w4 = __ldg(qb + b.x), w5 = __ldg(qb + b.y),
+                     w6 = __ldg(qb + b.z), w7 = __ldg(qb + b.w);
+      lo += (w0 & 0x00FF00FFu) + (w1 & 0x00FF00FFu) + (w2 & 0x00FF00FFu) + (w3 & 0x00FF00FFu) +
+            (w4 & 0x00FF00FFu) + (w5 & 0x00FF00FFu) + (w6 & 0x00FF00FFu) + (w7 & 0x00FF00FFu);
+      hi += __byte_perm(w0, 0u, 0x4341) + __byte_perm(w1, 0u, 0x4341) +
+            __byte_perm(w2, 0u, 0x4341) + __byte_perm(w3, 0u, 0x4341) +
+            __byte_perm(w4, 0u, 0x4341) + __byte_perm(w5, 0u, 0x4341) +
+            __byte_perm(w6, 0u, 0x4341) + __byte_perm(w7, 0u, 0x4341);
+    }
+    for (; k < cin; ++k) {
+      const uint32_t w = __ldg(qb + stage->in_p[k]);
+      lo += w & 0x00FF00FFu;
+      hi += __byte_perm(w, 0u, 0x4341);
+    }
+    for (k = 0; k < cmix; ++k) {
+      const int4 t = stage->mix[k];
+      const bool ok = static_cast<unsigned>(t.y + ni) < static_cast<unsigned>(in) &&
+                      static_cast<unsigned>(t.z + nj) < static_cast<unsigned>(jn);
+      const uint32_t w = ldg_pred(qb, t.x, ok ? 1u : 0u);
+      lo += w & 0x00FF00FFu;
+      hi += __byte_perm(w, 0u, 0x4341);
+    }
+    s0 += lo & 0xFFFF; s2 += lo >> 16; s1 += hi & 0xFFFF; s3 += hi >> 16;
+  }
+  sum[0] = s0;
+  sum[1] = s1;
+  sum[2] = s2;
+  sum[3] = s3;
+}
+
+// Appends `count` nodes of one bucket as a block: scratch range, bucket-relative offset
+// and descriptor.  Called by one lane; returns the scratch position or ~0u on overflow.
+__device__ __forceinline__ unsigned int open_block(unsigned int* __restrict__ counters,
+                                                   unsigned int* __restrict__ bucket_cnt,
+                                                   NodeBlock* __restrict__ blocks, int slot,
+                                                   unsigned int bucket, unsigned int count,
+                                                   unsigned long long cap,
+                                                   unsigned long long block_cap) {
+  const unsigned int src = atomicAdd(&counters[kCntTmp + slot], count);
+  const unsigned int rel = atomicAdd(&bucket_cnt[bucket], count);
+  const unsigned int q = atomicAdd(&counters[kCntBlocks + slot], 1u);
+  if (static_cast<unsigned long long>(src) + count > cap || q >= block_cap) {
+    atomicOr(&counters[kCntOverflow], 1u);
+    return ~0u;
+  }
+  NodeBlock nb;
+  nb.src = src;
+  nb.count = count;
+  nb.bucket = bucket;
+  nb.rel = rel;
+  blocks[q] = nb;
+  return src;
+}
+
+// 5'a. seeds: lowest-resolution candidates above the threshold, one block of threads
+//      per (job, scan), visited tile by tile; every warp batches up to 128 nodes.
+__global__ void __launch_bounds__(kSeedWarps * kWarp)
+k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans,
+             const float* __restrict__ top_scores, const JobState* __restrict__ state,
+             unsigned int* __restrict__ tmp, NodeBlock* __restrict__ blocks,
+             unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ counters, int slot,
+             unsigned long long cap, unsigned long long block_cap) {
+  __shared__ unsigned int buf_all[kSeedWarps][128];
+  const JobDev& j = jobs[blockIdx.y];
+  const int scan = blockIdx.x;
+  if (scan >= j.S || j.depth - 1 != slot) return;
+  const ScanInfo si = scans[j.scan_off + scan];
+  if (si.nx == 0) return;
+  const float thr = threshold(j, &state[blockIdx.y]);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned int* buf = buf_all[warp];
+  const unsigned int bucket = static_cast<unsigned int>(j.scan_off + scan);
+  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
+  const int tiles_x = (si.nx + kTW - 1) >> kLogTW, tiles_y = (si.ny + kTH - 1) >> kLogTH;
+  int held = 0;
+  auto flush = [&]() {
+    unsigned int src = 0u;
+    if (lane == 0)
+      src = open_block(counters, bucket_cnt, blocks, slot, bucket, held, cap, block_cap);
+    src = __shfl_sync(kFull, src, 0);
+    __syncwarp();
+    if (src != ~0u)
+      for (int t = lane; t < held; t += kWarp) tmp[src + t] = buf[t];
+    __syncwarp();
+    held = 0;
+  };
+  for (int t = warp; t < tiles_x * tiles_y; t += kSeedWarps) {
+    const int ti = t % tiles_x, tj = t / tiles_x;
+    const int ci = kTW * ti + li, cj = kTH * tj + lj;
+    bool alive = false;
+    if (ci < si.nx && cj < si.ny)
+      alive = top_scores[j.cand_off + si.base + ci * si.ny + cj] > thr;
+    const uint32_t m = __ballot_sync(kFull, alive);
+    if (alive) buf[held + __popc(m & ((1u << lane) - 1u))] = static_cast<unsigned int>(ci | (cj << 16));
+    held += __popc(m);
+    if (held > 96) flush();
+  }
+  if (held > 0) flush();
+}
+
+// 5'b. bucket counters -> list offsets and work-item offsets of depth `slot`; one block.
+__global__ void __launch_bounds__(1024)
+k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ bucket_start,
+                unsigned int* __restrict__ bucket_istart, unsigned int* __restrict__ counters,
+                int slot, unsigned int num_buckets, unsigned long long cap,
+                unsigned long long item_cap) {
+  __shared__ unsigned int wsum[2][32];
+  __shared__ unsigned int carry[2];
+  if (threadIdx.x == 0) carry[0] = carry[1] = 0u;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (unsigned int b0 = 0; b0 < num_buckets; b0 += 1024) {
+    const unsigned int b = b0 + threadIdx.x;
+    unsigned int c = 0u;
+    if (b < num_buckets) {
+      c = bucket_cnt[b];
+      bucket_cnt[b] = 0u;  // ready for the next level
+    }
+    const unsigned int it = (c + kWarp - 1) / kWarp;
+    unsigned int pc = c, pi = it;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int tc = __shfl_up_sync(kFull, pc, o), tI = __shfl_up_sync(kFull, pi, o);
+      if (lane >= o) {
+        pc += tc;
+        pi += tI;
+      }
+    }
+    if (lane == 31) {
+      wsum[0][warp] = pc;
+      wsum[1][warp] = pi;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      unsigned int a = wsum[0][lane], i2 = wsum[1][lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int ta = __shfl_up_sync(kFull, a, o), ti = __shfl_up_sync(kFull, i2, o);
+        if (lane >= o) {
+          a += ta;
+          i2 += ti;
+        }
+      }
+      wsum[0][lane] = a;
+      wsum[1][lane] = i2;
+    }
+    __syncthreads();
+    const unsigned int base_c = carry[0] + (warp ? wsum[0][warp - 1] : 0u);
+    const unsigned int base_i = carry[1] + (warp ? wsum[1][warp - 1] : 0u);
+    if (b < num_buckets) {
+      bucket_start[b] = base_c + pc - c;
+      bucket_istart[b] = base_i + pi - it;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      carry[0] += wsum[0][31];
+      carry[1] += wsum[1][31];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    bucket_start[num_buckets] = carry[0];
+    bucket_istart[num_buckets] = carry[1];
+    counters[kCntNodes + slot] = carry[0];
+    counters[kCntItems + slot] = carry[1];
+    if (carry[0] > cap || carry[1] > item_cap) atomicOr(&counters[kCntOverflow], 1u);
+  }
+}
+
+// 5'c. blocks -> bucket ranges of the sorted list; work items of depth `slot`.
+//      item = (list position, bucket * 32 + nodes - 1)
+__global__ void __launch_bounds__(256)
+k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ blocks,
+        const unsigned int* __restrict__ bucket_start, const unsigned int* __restrict__ bucket_istart,
+        unsigned int* __restrict__ nodes, uint2* __restrict__ items,
+        const unsigned int* __restrict__ counters, int slot, unsigned int num_buckets,
+        unsigned long long cap, unsigned long long block_cap, unsigned long long item_cap) {
+  if (counters[kCntOverflow] & 1u) return;  // the batch is replayed with larger lists
+  const int lane = threadIdx.x & 31;
+  const unsigned int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const unsigned int warps = gridDim.x * (blockDim.x >> 5);
+  const unsigned int nblocks =
+      static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[kCntBlocks + slot]), block_cap));
+  for (unsigned int q = warp; q < nblocks; q += warps) {
+    const NodeBlock nb = blocks[q];
+    const unsigned int dst = bucket_start[nb.bucket] + nb.rel;
+    for (unsigned int t = lane; t < nb.count; t += kWarp) nodes[dst + t] = tmp[nb.src + t];
+  }
+  for (unsigned int b = warp; b < num_buckets; b += warps) {
+    const unsigned int first = bucket_start[b], c = bucket_start[b + 1] - first;
+    const unsigned int ibase = bucket_istart[b];
+    for (unsigned int t = lane; t * kWarp < c; t += kWarp)
+      items[ibase + t] = make_uint2(first + t * kWarp, b * kWarp + (min(c - t * kWarp, 32u) - 1u));
+  }
+}
+
+// 5'd. expand the nodes of depth d: one warp per work item, lane = alive node.
+__global__ void __launch_bounds__(kExpandWarps * kWarp)
+k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
+               const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
+               JobState* __restrict__ state, const unsigned int* __restrict__ bucket_js,
+               const unsigned int* __restrict__ nodes, const uint2* __restrict__ items,
+               unsigned int* __restrict__ tmp, NodeBlock* __restrict__ blocks,
+               unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ counters, int d,
+               unsigned long long cap, unsigned long long block_cap, unsigned long long item_cap,
+               unsigned long long* __restrict__ hist) {
+  __shared__ NodeStage stage_all[kExpandWarps];
+  if (counters[kCntOverflow] & 1u) return;
+  const unsigned int count =
+      static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[kCntItems + d]), item_cap));
+  const int lane = threadIdx.x & 31;
+  NodeStage* stage = &stage_all[threadIdx.x >> 5];
+  const unsigned int warps = gridDim.x * kExpandWarps;
+  const int lvl = d - 1;
+  const int two_s = 2 << lvl;
+  int acc_job = -1;
+  unsigned long long acc_scored = 0ull;
+  for (unsigned int it = blockIdx.x * kExpandWarps + (threadIdx.x >> 5); it < count; it += warps) {
+    const uint2 item = items[it];
+    const unsigned int bucket = item.y >> 5;
+    const int cnt = static_cast<int>(item.y & 31u) + 1;
+    const unsigned int js = bucket_js[bucket];
+    const int job = js >> 16, scan = js & 0xFFFF;
+    const JobDev& j = jobs[job];
+    JobState* st = &state[job];
+    float thr = threshold(j, st);
+    thr = __shfl_sync(kFull, thr, 0);
+    const ScanInfo si = scans[j.scan_off + scan];
+    const bool alive = lane < cnt;
+    const unsigned int node = nodes[item.x + (alive ? lane : 0)];
+    const int ni = node & 0xFFFF, nj = node >> 16;
+    if (hist != nullptr && lane == 0) atomicAdd(&hist[d * 33 + cnt], 1ull);
+    int sum[4];
+    node_sums(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
+              si.min_x + (two_s - 1), si.min_y + (two_s - 1), ni, nj, lane, stage, sum);
+    // Children lattice of this scan on level lvl (FCSM2D.cc:353-367: a child beyond
+    // max_x / max_y is not generated).
+    const int nxl = ((si.max_x - si.min_x) >> lvl) + 1, nyl = ((si.max_y - si.min_y) >> lvl) + 1;
+    const int ci0 = 2 * ni, cj0 = 2 * nj;
+    bool pass[4];
+    float sc[4];
+    int nvalid = 0, npass = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const bool valid = alive && ci0 + (k >> 1) < nxl && cj0 + (k & 1) < nyl;
+      sc[k] = to_score(j, sum[k]);
+      pass[k] = valid && sc[k] > thr;
+      nvalid += valid ? 1 : 0;
+      npass += pass[k] ? 1 : 0;
+    }
+    const int tot = __reduce_add_sync(kFull, nvalid);
+    if (job != acc_job) {
+      if (lane == 0 && acc_job >= 0) {
+        atomicAdd(&state[acc_job].scored, acc_scored);
+        atomicAdd(&state[acc_job].scored_phase[2], acc_scored);
+      }
+      acc_job = job;
+      acc_scored = 0ull;
+    }
+    acc_scored += static_cast<unsigned long long>(tot);
+    if (lvl == 0) {
+      // Leaves.  Rare: only a leaf above the current incumbent reaches the atomic.
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (!pass[k]) continue;
+        const int ci = ci0 + (k >> 1), cj = cj0 + (k & 1);
+        const int ix = ci >> (j.depth - 1), iy = cj >> (j.depth - 1);  // top-level ancestor
+        const float ts = top_scores[j.cand_off + si.base + ix * si.ny + iy];
+        const unsigned long long key = leaf_key(sc[k], ts);
+        const unsigned long long cur =
+            *reinterpret_cast<const volatile unsigned long long*>(&st->best);
+        if (key > cur) atomicMax(&st->best, key);
+      }
+    } else {
+      int pre = npass;  // inclusive scan over lanes
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(kFull, pre, o);
+        if (lane >= o) pre += t;
+      }
+      const int total = __shfl_sync(kFull, pre, 31);
+      if (total > 0) {
+        unsigned int src = 0u;
+        if (lane == 0)
+          src = open_block(counters, bucket_cnt, blocks, d - 1, bucket, total, cap, block_cap);
+        src = __shfl_sync(kFull, src, 0);
+        if (src != ~0u) {
+          unsigned int at = src + pre - npass;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (pass[k])
+              tmp[at++] = static_cast<unsigned int>((ci0 + (k >> 1)) | ((cj0 + (k & 1)) << 16));
+        }
+      }
+    }
+  }
+  if (lane == 0 && acc_job >= 0) {
+    atomicAdd(&state[acc_job].scored, acc_scored);
+    atomicAdd(&state[acc_job].scored_phase[2], acc_scored);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // 6. phase 2: which leaf attaining S* does the reference's DFS reach first?
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -852,6 +1235,11 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   const size_t o_cnt = take(sizeof(unsigned int) * kNumCounters);
   const size_t o_res = take(sizeof(csm_result2d) * b->num_jobs);
   const size_t o_hist = take(sizeof(unsigned long long) * CSM_MAX_DEPTH * 33);
+  // per bucket (= scan of a job): owner, counter, list offset, work-item offset
+  const size_t o_bjs = take(sizeof(unsigned int) * b->total_scans);
+  const size_t o_bcnt = take(sizeof(unsigned int) * b->total_scans);
+  const size_t o_bstart = take(sizeof(unsigned int) * (b->total_scans + 1));
+  const size_t o_bistart = take(sizeof(unsigned int) * (b->total_scans + 1));
   if (b->owner->pool.take(false, off, &b->arena, &b->arena_cap) != CSM_OK) {
     b->arena = nullptr;
     set_error("allocation of a %zu-byte batch arena failed: %s", off, cudaGetErrorString(cudaGetLastError()));
@@ -871,6 +1259,10 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   b->counters = reinterpret_cast<unsigned int*>(base + o_cnt);
   b->results_dev = reinterpret_cast<csm_result2d*>(base + o_res);
   b->hist = reinterpret_cast<unsigned long long*>(base + o_hist);
+  b->bucket_js = reinterpret_cast<unsigned int*>(base + o_bjs);
+  b->bucket_cnt = reinterpret_cast<unsigned int*>(base + o_bcnt);
+  b->bucket_start = reinterpret_cast<unsigned int*>(base + o_bstart);
+  b->bucket_istart = reinterpret_cast<unsigned int*>(base + o_bistart);
   return CSM_OK;
 }
 
@@ -1047,16 +1439,33 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   CSM_REQUIRE(ctx != nullptr && b != nullptr && b->uploaded, "batch was not uploaded");
   CSM_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
-  if (ctx->frontier_cap < b->frontier_want) {
+  // Scratch lists of the sweep, owned by the context (runs are stream-ordered).
+  //   node lists: frontier[0] = bucket-sorted nodes of the level being expanded,
+  //               frontier[1] = survivors in arrival order; aux = blocks | work items
+  //   tile lists (CSM_SWEEP=tiles): two ping-pong tile lists
+  const bool tiles = ctx->sweep_tiles;
+  const unsigned long long nbuckets = static_cast<unsigned long long>(b->total_scans);
+  const unsigned long long node_cap = 2ull * b->frontier_want;
+  const unsigned long long block_cap = node_cap / 16ull + 8ull * nbuckets + 4096ull;
+  const unsigned long long item_cap = node_cap / 16ull + nbuckets + 4096ull;
+  const size_t want_list = tiles ? sizeof(Tile) * b->frontier_want : sizeof(unsigned int) * node_cap;
+  const size_t o_items = align_up(sizeof(NodeBlock) * block_cap);
+  const size_t want_aux = tiles ? 0 : o_items + sizeof(uint2) * item_cap;
+  if (ctx->frontier[0].cap < want_list || ctx->frontier[1].cap < want_list ||
+      ctx->frontier_aux.cap < want_aux) {
     CSM_CUDA(cudaStreamSynchronize(st));  // earlier batches may still use the old buffers
-    ctx->frontier_cap = 0;
-    int rc = ctx->frontier[0].reserve(sizeof(Tile) * b->frontier_want);
-    if (rc == CSM_OK) rc = ctx->frontier[1].reserve(sizeof(Tile) * b->frontier_want);
+    int rc = ctx->frontier[0].reserve(want_list);
+    if (rc == CSM_OK) rc = ctx->frontier[1].reserve(want_list);
+    if (rc == CSM_OK && want_aux) rc = ctx->frontier_aux.reserve(want_aux);
     if (rc != CSM_OK) return rc;
-    ctx->frontier_cap = b->frontier_want;
   }
   Tile* const fbuf[2] = {ctx->frontier[0].as<Tile>(), ctx->frontier[1].as<Tile>()};
-  const unsigned long long fcap = ctx->frontier_cap;
+  const unsigned long long fcap = b->frontier_want;
+  unsigned int* const node_list = ctx->frontier[0].as<unsigned int>();
+  unsigned int* const node_tmp = ctx->frontier[1].as<unsigned int>();
+  NodeBlock* const node_blocks = ctx->frontier_aux.as<NodeBlock>();
+  uint2* const node_items =
+      want_aux ? reinterpret_cast<uint2*>(ctx->frontier_aux.as<char>() + o_items) : nullptr;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters, st));
   if (ctx->profiling >= 2)
     CSM_CUDA(cudaMemsetAsync(b->hist, 0, sizeof(unsigned long long) * CSM_MAX_DEPTH * 33, st));
@@ -1074,7 +1483,8 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   if (b->max_scans > 0) {
     const dim3 grid_sj(b->max_scans, nj);
     ++ctx->launches, k_discretize<<<grid_sj, 128, 0, st>>>(b->jobs, b->points, b->quats, b->xy, b->scans,
-                                          b->scan_best, 1);
+                                          b->scan_best, b->bucket_js, 1);
+    if (!tiles) CSM_CUDA(cudaMemsetAsync(b->bucket_cnt, 0, sizeof(unsigned int) * b->total_scans, st));
     ++ctx->launches, k_scan_prefix<<<nj, 256, 0, st>>>(b->jobs, b->scans, b->state, b->counters);
     mark();
     ++ctx->launches, k_score_top<<<grid_sj, kTopWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores,
@@ -1092,13 +1502,31 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
     for (int d = max_depth - 1; d >= 1; --d) {
       bool any = false;
       for (const JobDev& j : b->jobs_host) any = any || (j.depth - 1 == d && j.S > 0);
+      unsigned long long* const hist = ctx->profiling >= 2 ? b->hist : nullptr;
+      if (tiles) {
+        if (any)
+          ++ctx->launches, k_seed<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(
+              b->jobs, b->scans, b->top_scores, b->state, fbuf[d & 1], b->counters, d, fcap);
+        ++ctx->launches, k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(
+            b->jobs, b->xy, b->scans, b->top_scores, b->state, fbuf[d & 1], fbuf[(d - 1) & 1],
+            b->counters, d, d - 1, d, fcap, hist);
+        continue;
+      }
+      // Survivors of depth d (children of depth d + 1 and, for stacks whose top is d,
+      // the seeds) are gathered into bucket order, then expanded.
       if (any)
-        ++ctx->launches, k_seed<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
-                                        fbuf[d & 1], b->counters, d, fcap);
-      ++ctx->launches, k_expand<<<ctx->num_sms * 8, kExpandWarps * kWarp, 0, st>>>(b->jobs, b->xy, b->scans, b->top_scores, b->state,
-                                                 fbuf[d & 1], fbuf[(d - 1) & 1], b->counters, d,
-                                                 d - 1, d, fcap,
-                                                 ctx->profiling >= 2 ? b->hist : nullptr);
+        ++ctx->launches, k_seed_nodes<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(
+            b->jobs, b->scans, b->top_scores, b->state, node_tmp, node_blocks, b->bucket_cnt,
+            b->counters, d, node_cap, block_cap);
+      ++ctx->launches, k_bucket_prefix<<<1, 1024, 0, st>>>(
+          b->bucket_cnt, b->bucket_start, b->bucket_istart, b->counters, d,
+          static_cast<unsigned int>(nbuckets), node_cap, item_cap);
+      ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
+          node_tmp, node_blocks, b->bucket_start, b->bucket_istart, node_list, node_items,
+          b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap);
+      ++ctx->launches, k_expand_nodes<<<ctx->num_sms * 4, kExpandWarps * kWarp, 0, st>>>(
+          b->jobs, b->xy, b->scans, b->top_scores, b->state, b->bucket_js, node_list, node_items,
+          node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist);
     }
     mark();
     ++ctx->launches, k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
@@ -1194,7 +1622,7 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
       return CSM_ERR_CAPACITY;
     }
     // A work list overflowed: regrow it and replay the whole batch.
-    if (ov & 1u) b->frontier_want = std::max(b->frontier_want, ctx->frontier_cap) * 4ull;
+    if (ov & 1u) b->frontier_want *= 4ull;
     unsigned long long ccap = (ov & 4u) ? static_cast<unsigned long long>(counters[kCntContenders]) + 1024ull
                                         : b->contender_cap;
     if (ccap > 0xFFFFFFF0ull) ccap = 0xFFFFFFF0ull;
@@ -1315,7 +1743,8 @@ int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, i
   CSM_CUDA(cudaMemcpyAsync(d_job, &j, sizeof(j), cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_pts, job->points_xyz, sizeof(float) * 3 * j.n, cudaMemcpyHostToDevice, st));
   CSM_CUDA(cudaMemcpyAsync(d_quat, job->scan_quat, sizeof(float) * 2 * j.S, cudaMemcpyHostToDevice, st));
-  ++ctx->launches, k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, shrink);
+  ++ctx->launches, k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, nullptr,
+                                                              shrink);
   CSM_CUDA(cudaGetLastError());
   std::vector<ScanInfo> scans(j.S);
   CSM_CUDA(cudaMemcpyAsync(out_xy, d_xy, sizeof(int2) * static_cast<size_t>(j.S) * j.n,

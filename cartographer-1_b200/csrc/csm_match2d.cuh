@@ -145,6 +145,10 @@ struct csm_batch2d {
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
   unsigned long long* hist = nullptr;  // [depth][alive nodes per tile] tile counts (profiling)
+  unsigned int* bucket_js = nullptr;   // total_scans: job << 16 | scan of every bucket
+  unsigned int* bucket_cnt = nullptr;  // total_scans: survivors appended for the next level
+  unsigned int* bucket_start = nullptr;   // total_scans + 1: offsets into the sorted node list
+  unsigned int* bucket_istart = nullptr;  // total_scans + 1: offsets into the work items
   csm_ctx* owner = nullptr;            // context whose block pool backs arena / pinned
   void* arena = nullptr;               // single device block backing all of the above
   size_t arena_bytes = 0, arena_cap = 0;
