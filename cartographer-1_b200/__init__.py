@@ -51,7 +51,7 @@ ABI_SYMBOLS = [
     "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
     "csm_ctx_synchronize", "csm_ctx_stream", "csm_ctx_set_profiling", "csm_ctx_get_profile",
     "csm_ctx_get_tile_histogram", "csm_stack2d_build", "csm_stack2d_build_dev",
-    "csm_stack2d_rebuild_dev", "csm_stack2d_level", "csm_stack2d_depth",
+    "csm_stack2d_rebuild_dev", "csm_stack2d_level", "csm_stack2d_quad", "csm_stack2d_depth",
     "csm_stack2d_device_bytes", "csm_stack2d_destroy", "csm_match2d_batch",
     "csm_batch2d_upload", "csm_batch2d_run", "csm_batch2d_fetch", "csm_batch2d_destroy",
     "csm_discretize2d", "csm_rt_match2d_batch", "csm_ctx_launch_count", "csm_measure_gather_rate",
@@ -214,6 +214,21 @@ class Matcher:
         rc = host().csmh_matcher_level(self.ctx.h, self.h, i, out.ctypes.data_as(C.c_void_p),
                                        C.byref(wx), C.byref(wy))
         assert rc == 0, abi().csm_last_error()
+        return out
+
+    def quad(self, i):
+        """Quad-phase words of level i as a [2s, 2s, jn, in] uint32 array (pv, pu, j, i)."""
+        A = abi()
+        A.csm_stack2d_quad.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                       C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        stack = C.c_void_p(host().csmh_matcher_stack(self.h))
+        n_i, n_j = C.c_int(), C.c_int()
+        rc = A.csm_stack2d_quad(C.c_void_p(self.ctx.raw), stack, i, None, C.byref(n_i), C.byref(n_j))
+        assert rc == 0, A.csm_last_error()
+        out = np.empty((2 << i, 2 << i, n_j.value, n_i.value), dtype=np.uint32)
+        rc = A.csm_stack2d_quad(C.c_void_p(self.ctx.raw), stack, i, out.ctypes.data_as(C.c_void_p),
+                                C.byref(n_i), C.byref(n_j))
+        assert rc == 0, A.csm_last_error()
         return out
 
     def __del__(self):

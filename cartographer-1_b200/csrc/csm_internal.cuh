@@ -109,7 +109,8 @@ struct csm_ctx {
 namespace csm {
 // Device-resident description of one precomputation stack (what the kernels read).
 //
-// level[l]: the reference's PrecomputationGrid2D::cells_ of width 2^l, row-major bytes.
+// level[l]: the reference's PrecomputationGrid2D::cells_ of width 2^l, row-major bytes
+//           with rows pitched to 16 bytes (host side: csm_stack2d::level_pitch).
 // quad[l]:  the same level re-laid out for the matcher ("quad-phase" layout): one
 //           uint32 per window start (x, y), x in [-2s+1, num_x-1], s = 2^l, holding the
 //           four values a branch-and-bound parent needs for its children in generation
@@ -132,6 +133,7 @@ struct csm_stack2d {
   uint8_t* base = nullptr;                // one allocation: levels, quads, descriptor, LUT
   size_t base_cap = 0;                    // capacity of that block (pooled)
   size_t level_off[CSM_MAX_DEPTH] = {0};  // byte offset of level i inside base
+  int level_pitch[CSM_MAX_DEPTH] = {0};   // row pitch of level i in bytes (multiple of 16)
   size_t quad_off[CSM_MAX_DEPTH] = {0};   // byte offset of quad level i inside base
   csm::StackDev host_view;                // copy of *dev
   csm::StackDev* dev = nullptr;           // device-resident descriptor

@@ -52,7 +52,7 @@ constexpr int kWarp = 32;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kCntContenders = 32;
 constexpr int kCntOverflow = 33;
-constexpr int kNumCounters = 96;
+constexpr int kNumCounters = 112;
 
 // Tile shape: kTW x kTH parents, lane = lj * kTW + li.
 #ifndef CSM_LOG_TW
@@ -673,6 +673,8 @@ constexpr int kCntNodes = 0;     // + depth: nodes on the sorted list
 constexpr int kCntTmp = 48;      // + depth: scratch list fill
 constexpr int kCntBlocks = 64;   // + depth: blocks appended
 constexpr int kCntItems = 80;    // + depth: 32-node work items
+constexpr int kCntCursor = 96;   // + depth: next work item to hand out (k_expand_nodes)
+constexpr int kNodeBlocksPerSm = 4;  // resident k_expand_nodes blocks per SM (register bound)
 constexpr int kStagePoints = 128;
 
 struct NodeStage {
@@ -795,8 +797,8 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned int* buf = buf_all[warp];
   const unsigned int bucket = static_cast<unsigned int>(j.scan_off + scan);
-  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
-  const int tiles_x = (si.nx + kTW - 1) >> kLogTW, tiles_y = (si.ny + kTH - 1) >> kLogTH;
+  // Row by row (32 x 1 lanes): every listed run has consecutive ni at one nj.
+  const int tiles_x = (si.nx + kWarp - 1) / kWarp, tiles_y = si.ny;
   int held = 0;
   auto flush = [&]() {
     unsigned int src = 0u;
@@ -810,10 +812,10 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
     held = 0;
   };
   for (int t = warp; t < tiles_x * tiles_y; t += kSeedWarps) {
-    const int ti = t % tiles_x, tj = t / tiles_x;
-    const int ci = kTW * ti + li, cj = kTH * tj + lj;
+    const int ti = t % tiles_x, cj = t / tiles_x;
+    const int ci = kWarp * ti + lane;
     bool alive = false;
-    if (ci < si.nx && cj < si.ny)
+    if (ci < si.nx)
       alive = top_scores[j.cand_off + si.base + ci * si.ny + cj] > thr;
     const uint32_t m = __ballot_sync(kFull, alive);
     if (alive) buf[held + __popc(m & ((1u << lane) - 1u))] = static_cast<unsigned int>(ci | (cj << 16));
@@ -919,8 +921,12 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
   }
 }
 
-// 5'd. expand the nodes of depth d: one warp per work item, lane = alive node.
-__global__ void __launch_bounds__(kExpandWarps * kWarp)
+// 5'd. expand the nodes of depth d: one warp per work item, lane = alive node.  Work
+//      items are handed out in list order through a cursor (one atomic per item, the
+//      next one fetched while the current item is summed): an item costs between a few
+//      and several hundred loads per lane, so a static split leaves SMs idle at the end
+//      (ncu: l1tex busy 60 % of elapsed but 86 % of active cycles before this).
+__global__ void __launch_bounds__(kExpandWarps * kWarp, kNodeBlocksPerSm)
 k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
                const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
                JobState* __restrict__ state, const unsigned int* __restrict__ bucket_js,
@@ -935,12 +941,20 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
       static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[kCntItems + d]), item_cap));
   const int lane = threadIdx.x & 31;
   NodeStage* stage = &stage_all[threadIdx.x >> 5];
-  const unsigned int warps = gridDim.x * kExpandWarps;
   const int lvl = d - 1;
   const int two_s = 2 << lvl;
   int acc_job = -1;
   unsigned long long acc_scored = 0ull;
-  for (unsigned int it = blockIdx.x * kExpandWarps + (threadIdx.x >> 5); it < count; it += warps) {
+  auto next_item = [&]() -> unsigned int {
+    unsigned int v = 0u;
+    if (lane == 0) v = atomicAdd(&counters[kCntCursor + d], 1u);
+    return v;
+  };
+  unsigned int fetched = next_item();
+  for (;;) {
+    const unsigned int it = __shfl_sync(kFull, fetched, 0);
+    if (it >= count) break;
+    fetched = next_item();
     const uint2 item = items[it];
     const unsigned int bucket = item.y >> 5;
     const int cnt = static_cast<int>(item.y & 31u) + 1;
@@ -997,24 +1011,33 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
         if (key > cur) atomicMax(&st->best, key);
       }
     } else {
-      int pre = npass;  // inclusive scan over lanes
+      // Survivors are emitted as two ROW RUNS per work item: the even-row children
+      // (cj0) of every lane, then the odd-row ones (cj0 + 1), each in lane order.  A
+      // plane row is contiguous in the quad layout (index = P + nj * in + ni), so when
+      // the parents of an item lie along a row -- seeds are listed row by row, and by
+      // induction every later item is a row run -- the 32 nodes of a child item share
+      // their 32-byte sectors along ni instead of spreading over a 2-D Z-order block.
+      const int ne = (pass[0] ? 1 : 0) + (pass[2] ? 1 : 0), no = npass - ne;
+      int pre = ne | (no << 16);  // inclusive scan over lanes, both counts at once
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const int t = __shfl_up_sync(kFull, pre, o);
         if (lane >= o) pre += t;
       }
-      const int total = __shfl_sync(kFull, pre, 31);
+      const int totals = __shfl_sync(kFull, pre, 31);
+      const int total_e = totals & 0xFFFF, total = total_e + (totals >> 16);
       if (total > 0) {
         unsigned int src = 0u;
         if (lane == 0)
           src = open_block(counters, bucket_cnt, blocks, d - 1, bucket, total, cap, block_cap);
         src = __shfl_sync(kFull, src, 0);
         if (src != ~0u) {
-          unsigned int at = src + pre - npass;
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (pass[k])
-              tmp[at++] = static_cast<unsigned int>((ci0 + (k >> 1)) | ((cj0 + (k & 1)) << 16));
+          unsigned int at_e = src + (pre & 0xFFFF) - ne;
+          unsigned int at_o = src + total_e + (pre >> 16) - no;
+          if (pass[0]) tmp[at_e++] = static_cast<unsigned int>(ci0 | (cj0 << 16));
+          if (pass[2]) tmp[at_e] = static_cast<unsigned int>((ci0 + 1) | (cj0 << 16));
+          if (pass[1]) tmp[at_o++] = static_cast<unsigned int>(ci0 | ((cj0 + 1) << 16));
+          if (pass[3]) tmp[at_o] = static_cast<unsigned int>((ci0 + 1) | ((cj0 + 1) << 16));
         }
       }
     }
@@ -1524,7 +1547,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
           node_tmp, node_blocks, b->bucket_start, b->bucket_istart, node_list, node_items,
           b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap);
-      ++ctx->launches, k_expand_nodes<<<ctx->num_sms * 4, kExpandWarps * kWarp, 0, st>>>(
+      ++ctx->launches, k_expand_nodes<<<ctx->num_sms * kNodeBlocksPerSm, kExpandWarps * kWarp, 0, st>>>(
           b->jobs, b->xy, b->scans, b->top_scores, b->state, b->bucket_js, node_list, node_items,
           node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist);
     }

@@ -13,8 +13,10 @@
 // level i at offsets {0, 2^i}^2, which is what the kernels below evaluate.  Pure
 // integer work => bit-identical to the reference's cells_.
 //
-// Data layout in HBM: one allocation per stack; level i is a dense row-major
-// (num_x + 2^i - 1) x (num_y + 2^i - 1) byte image at a 256-byte aligned offset.
+// Data layout in HBM: one allocation per stack; level i is a row-major
+// (num_x + 2^i - 1) x (num_y + 2^i - 1) byte image at a 256-byte aligned offset whose
+// rows are PITCHED to a multiple of 16 bytes (pad bytes are zero), so every kernel
+// moves whole words; csm_stack2d_level() hands back the dense image.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -25,33 +27,43 @@ namespace {
 
 constexpr int kThreads = 256;
 
-// Level 0: out[i] = q_lut[cells[i]].  4 cells per thread, 8-byte loads / 4-byte stores.
+// Level 0: out(x, y) = q_lut[cells(x, y)], zero in the row padding.  Persistent blocks
+// (the 32 KB table is staged once per block); a thread makes 4 cells = one output word.
 __global__ void __launch_bounds__(kThreads)
 k_stack_level0(const uint16_t* __restrict__ cells, const uint8_t* __restrict__ q_lut,
-               uint8_t* __restrict__ out, size_t n) {
+               uint8_t* __restrict__ out, int num_x, int num_y, int pitch) {
   __shared__ uint8_t lut[65536 / 2];  // values 0..32767; the update marker bit is masked off
-  for (int i = threadIdx.x; i < 32768 / 4; i += kThreads)
-    reinterpret_cast<uint32_t*>(lut)[i] = reinterpret_cast<const uint32_t*>(q_lut)[i];
+  for (int i = threadIdx.x; i < 32768 / 16; i += kThreads)
+    reinterpret_cast<uint4*>(lut)[i] = __ldg(reinterpret_cast<const uint4*>(q_lut) + i);
   __syncthreads();
-  const size_t n4 = n / 4;
-  const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
-  for (size_t i = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x; i < n4; i += stride) {
-    const uint2 v = reinterpret_cast<const uint2*>(cells)[i];
-    const uint32_t b0 = lut[v.x & 0x7FFFu], b1 = lut[(v.x >> 16) & 0x7FFFu];
-    const uint32_t b2 = lut[v.y & 0x7FFFu], b3 = lut[(v.y >> 16) & 0x7FFFu];
-    reinterpret_cast<uint32_t*>(out)[i] = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
-  }
-  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-    const size_t i = n4 * 4 + threadIdx.x;
-    out[i] = lut[cells[i] & 0x7FFFu];
+  const int pw = pitch >> 2;
+  for (int y = blockIdx.x; y < num_y; y += gridDim.x) {
+    const size_t row = static_cast<size_t>(y) * num_x;
+    const uint16_t* __restrict__ crow = cells + row;
+    uint32_t* __restrict__ orow = reinterpret_cast<uint32_t*>(out + static_cast<size_t>(y) * pitch);
+    const bool aligned = (row & 3) == 0;
+    for (int k = threadIdx.x; k < pw; k += kThreads) {
+      const int x = 4 * k;
+      uint32_t w = 0u;
+      if (aligned && x + 3 < num_x) {
+        const uint2 v = __ldg(reinterpret_cast<const uint2*>(crow + x));
+        w = static_cast<uint32_t>(lut[v.x & 0x7FFFu]) | (static_cast<uint32_t>(lut[(v.x >> 16) & 0x7FFFu]) << 8) |
+            (static_cast<uint32_t>(lut[v.y & 0x7FFFu]) << 16) | (static_cast<uint32_t>(lut[(v.y >> 16) & 0x7FFFu]) << 24);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (x + b < num_x) w |= static_cast<uint32_t>(lut[__ldg(crow + x + b) & 0x7FFFu]) << (8 * b);
+      }
+      orow[k] = w;
+    }
   }
 }
 
 // Level i -> i+1 (h = 2^i): out(X, Y) = max of in at (X, Y), (X-h, Y), (X, Y-h),
 // (X-h, Y-h); taps outside the input image are 0.
 __global__ void __launch_bounds__(kThreads)
-k_stack_level_up(const uint8_t* __restrict__ in, int in_w, int in_h, uint8_t* __restrict__ out,
-                 int out_w, int out_h, int h) {
+k_stack_level_up(const uint8_t* __restrict__ in, int in_w, int in_h, int in_pitch,
+                 uint8_t* __restrict__ out, int out_w, int out_h, int out_pitch, int h) {
   const int X = blockIdx.x * blockDim.x + threadIdx.x;
   const int Y = blockIdx.y * blockDim.y + threadIdx.y;
   if (X >= out_w || Y >= out_h) return;
@@ -59,18 +71,18 @@ k_stack_level_up(const uint8_t* __restrict__ in, int in_w, int in_h, uint8_t* __
     if (static_cast<unsigned>(x) >= static_cast<unsigned>(in_w) ||
         static_cast<unsigned>(y) >= static_cast<unsigned>(in_h))
       return 0u;
-    return in[static_cast<size_t>(y) * in_w + x];
+    return in[static_cast<size_t>(y) * in_pitch + x];
   };
   const unsigned a = max(tap(X, Y), tap(X - h, Y));
   const unsigned b = max(tap(X, Y - h), tap(X - h, Y - h));
-  out[static_cast<size_t>(Y) * out_w + X] = static_cast<uint8_t>(max(a, b));
+  out[static_cast<size_t>(Y) * out_pitch + X] = static_cast<uint8_t>(max(a, b));
 }
 
 // Byte level -> quad-phase layout (see StackDev).  One thread per output word, so the
 // 4-byte stores are coalesced; the four byte taps are strided gathers served by L2.
 __global__ void __launch_bounds__(kThreads)
-k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, uint32_t* __restrict__ out,
-              int log2s, int in, int jn) {
+k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, int pitch,
+              uint32_t* __restrict__ out, int log2s, int in, int jn) {
   const int two_s = 2 << log2s, s = 1 << log2s;
   const size_t total = static_cast<size_t>(two_s) * two_s * in * jn;
   const size_t stride = static_cast<size_t>(gridDim.x) * kThreads;
@@ -87,7 +99,7 @@ k_stack_quads(const uint8_t* __restrict__ lvl, int wide_x, int wide_y, uint32_t*
       if (static_cast<unsigned>(x) >= static_cast<unsigned>(wide_x) ||
           static_cast<unsigned>(y) >= static_cast<unsigned>(wide_y))
         return 0u;
-      return lvl[static_cast<size_t>(y) * wide_x + x];
+      return lvl[static_cast<size_t>(y) * pitch + x];
     };
     out[idx] = tap(X, Y) | (tap(X, Y + s) << 8) | (tap(X + s, Y) << 16) | (tap(X + s, Y + s) << 24);
   }
@@ -134,7 +146,7 @@ __device__ __forceinline__ uint32_t max4_u8x4(uint32_t a, uint32_t b, uint32_t c
 struct QuadArgs {
   const uint8_t* level[CSM_MAX_DEPTH];
   uint32_t* quad[CSM_MAX_DEPTH];
-  int in[CSM_MAX_DEPTH], jn[CSM_MAX_DEPTH];
+  int in[CSM_MAX_DEPTH], jn[CSM_MAX_DEPTH], pitch[CSM_MAX_DEPTH];
   int num_x, num_y, depth;
 };
 
@@ -156,7 +168,7 @@ k_stack_quad_rows(const QuadArgs a) {
     const int Y = r == 0 ? v : v - s;
     uint8_t* dst = r == 0 ? cur : up;
     const bool row_ok = static_cast<unsigned>(Y) < static_cast<unsigned>(wide_y);
-    const uint8_t* src = lvl + static_cast<size_t>(row_ok ? Y : 0) * wide_x;
+    const uint8_t* src = lvl + static_cast<size_t>(row_ok ? Y : 0) * a.pitch[i];
     for (int x = threadIdx.x; x < pitch; x += kThreads) {
       const int X = x - s;
       dst[x] = (row_ok && static_cast<unsigned>(X) < static_cast<unsigned>(wide_x)) ? __ldg(src + X)
@@ -207,7 +219,7 @@ struct FusedArgs {
   const uint8_t* q_lut;
   uint8_t* level[kFusedMaxDepth];
   uint32_t* quad[kFusedMaxDepth];
-  int in[kFusedMaxDepth], jn[kFusedMaxDepth];
+  int in[kFusedMaxDepth], jn[kFusedMaxDepth], pitch[kFusedMaxDepth];
   int num_x, num_y, depth;
 };
 
@@ -267,7 +279,7 @@ k_stack_fused(const FusedArgs a) {
         const int lx = e & (kFusedTile - 1), ly = e >> kFusedLogTile;
         const int X = X0 + lx, Y = Y0 + ly;
         if (X < wide_x && Y < wide_y)
-          out[static_cast<size_t>(Y) * wide_x + X] = A8[(P + ly) * R + P + lx];
+          out[static_cast<size_t>(Y) * a.pitch[i] + X] = A8[(P + ly) * R + P + lx];
       }
     }
     // Tap words of level i for the word k of region row ry: c = (X, .), l = (X - h, .),
@@ -319,6 +331,7 @@ int launch_build_fused(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
     a.quad[i] = reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]);
     a.in[i] = s->host_view.in[i];
     a.jn[i] = s->host_view.jn[i];
+    a.pitch[i] = s->level_pitch[i];
   }
   // Tiles cover the widest byte level.
   const int ext_x = s->num_x + (1 << (s->depth - 1)) - 1, ext_y = s->num_y + (1 << (s->depth - 1)) - 1;
@@ -344,6 +357,7 @@ int launch_build_fused(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
       q.quad[i] = a.quad[i];
       q.in[i] = a.in[i];
       q.jn[i] = a.jn[i];
+      q.pitch[i] = a.pitch[i];
       max_v = std::max(max_v, a.jn[i] << (i + 1));
       max_pitch = std::max<size_t>(max_pitch, (static_cast<size_t>(a.in[i]) << (i + 1)) + (1 << i) + 4);
     }
@@ -356,33 +370,192 @@ int launch_build_fused(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
   return CSM_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Row build (default): one launch per level i makes BOTH the quad-phase words of level
+// i and the bytes of level i+1 from the bytes of level i -- they are the same four
+// taps: quad(X, Y) packs level i at {X - s, X} x {Y - s, Y} and level i+1 at (X, Y) is
+// their maximum.  A block owns one row Y: it stages rows Y and Y - s of level i in
+// shared memory with whole-word coalesced loads (rows are pitched; s zero bytes in
+// front stand for the taps left of the image), then
+//   (1) next-level bytes: lane = consecutive word, 4 cells per thread, one 4-byte
+//       coalesced store;
+//   (2) quad words: a thread takes 4 adjacent phases pu (one staged word and its tap
+//       s bytes to the left, rows Y and Y - s), transposes the 4 x 4 bytes into 4 quad
+//       words and stores them to 4 phase planes at column ii; lanes walk ii, so every
+//       store instruction writes contiguous runs of a plane row.
+// Lanes that walk ii read staged words 2s/4 apart: the staged rows carry one pad word
+// per 32 (index w + w/32), which makes every power-of-two stride conflict-free.
+// No halo is recomputed (the tile-fused kernel recomputes 4x at depth 7) and no byte
+// is moved one at a time; per level the kernel reads level i once (L2-resident) and
+// writes each output once.
+// ---------------------------------------------------------------------------
+struct RowsArgs {
+  const uint8_t* lvl;  // level i, pitched rows
+  uint8_t* next;       // level i + 1, pitched rows (nullptr on the last level)
+  uint32_t* quad;      // quad-phase words of level i
+  int pitch, next_pitch, wide_y, next_wide_y;
+  int in, jn, log2s;
+  unsigned int in_magic;  // ceil(2^32 / in): t / in == __umulhi(t, in_magic) for t < 2^16; 0 when in == 1
+};
+
+__device__ __forceinline__ int skew(int w) { return w + (w >> 5); }
+
+__global__ void __launch_bounds__(kThreads)
+k_stack_rows(const RowsArgs a) {
+  extern __shared__ uint32_t rows32[];
+  const int s = 1 << a.log2s, two_s = 2 << a.log2s, sh = a.log2s + 1;
+  const int v = blockIdx.x;  // window-end row Y of level i == row of level i + 1
+  const int padw = s >= 4 ? (s >> 2) : 1;           // zero words in front of X = 0
+  const int spanw = (a.in * two_s + 3) >> 2;        // staged words from X = 0
+  const int nw = padw + spanw;
+  uint32_t* cur = rows32;                 // Y = v
+  uint32_t* up = rows32 + skew(nw) + 1;   // Y = v - s
+  const int pw = a.pitch >> 2;
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int Y = r == 0 ? v : v - s;
+    uint32_t* dst = r == 0 ? cur : up;
+    const bool row_ok = static_cast<unsigned>(Y) < static_cast<unsigned>(a.wide_y);
+    const uint32_t* __restrict__ src =
+        reinterpret_cast<const uint32_t*>(a.lvl + static_cast<size_t>(row_ok ? Y : 0) * a.pitch);
+    for (int w = threadIdx.x; w < nw; w += kThreads) {
+      const int k = w - padw;
+      dst[skew(w)] = (row_ok && static_cast<unsigned>(k) < static_cast<unsigned>(pw)) ? __ldg(src + k) : 0u;
+    }
+  }
+  __syncthreads();
+  // The four tap words of the staged word xw: c = (X.., .), l = (X - s.., .).
+  auto taps = [&](int xw, uint32_t& c0, uint32_t& l0, uint32_t& c1, uint32_t& l1) {
+    const int ic = skew(xw);
+    c0 = cur[ic];
+    c1 = up[ic];
+    if (s >= 4) {
+      const int il = skew(xw - (s >> 2));
+      l0 = cur[il];
+      l1 = up[il];
+    } else {
+      const int il = skew(xw - 1);
+      l0 = __funnelshift_l(cur[il], c0, 8 * s);
+      l1 = __funnelshift_l(up[il], c1, 8 * s);
+    }
+  };
+  // (1) bytes of level i + 1, row v (pad words come out zero: their taps lie outside).
+  if (a.next != nullptr && v < a.next_wide_y) {
+    uint32_t* __restrict__ orow = reinterpret_cast<uint32_t*>(a.next + static_cast<size_t>(v) * a.next_pitch);
+    const int npw = a.next_pitch >> 2;
+    for (int k = threadIdx.x; k < npw; k += kThreads) {
+      uint32_t m = 0u;
+      if (k < spanw) {
+        uint32_t c0, l0, c1, l1;
+        taps(k + padw, c0, l0, c1, l1);
+        m = max4_u8x4(c0, l0, c1, l1);
+      }
+      orow[k] = m;
+    }
+  }
+  // (2) quad words of row v.  q_j = l1.b_j | l0.b_j << 8 | c1.b_j << 16 | c0.b_j << 24.
+  uint32_t* __restrict__ out = a.quad;
+  const size_t plane = static_cast<size_t>(a.in) * a.jn;
+  const size_t rowbase = (static_cast<size_t>((v & (two_s - 1)) << sh) * a.jn + (v >> sh)) * a.in;
+  if (a.log2s == 0) {
+    // 2 phases: the word X = 4k .. 4k + 3 holds (pu, ii) = (0, 2k), (1, 2k), (0, 2k + 1), (1, 2k + 1).
+    for (int k = threadIdx.x; 2 * k < a.in; k += kThreads) {
+      uint32_t c0, l0, c1, l1;
+      taps(k + padw, c0, l0, c1, l1);
+      const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+      const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+      uint32_t* o = out + rowbase + 2 * k;
+      o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+      o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+      if (2 * k + 1 < a.in) {
+        o[1] = __byte_perm(a_hi, b_hi, 0x5410);
+        o[plane + 1] = __byte_perm(a_hi, b_hi, 0x7632);
+      }
+    }
+  } else {
+    const int items = (two_s >> 2) * a.in;  // (group of 4 phases, ii)
+    for (int t = threadIdx.x; t < items; t += kThreads) {
+      const int pg = a.in_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(t), a.in_magic)) : t;
+      const int ii = t - pg * a.in;
+      uint32_t c0, l0, c1, l1;
+      taps(((ii << sh) >> 2) + pg + padw, c0, l0, c1, l1);
+      const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+      const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+      uint32_t* o = out + rowbase + static_cast<size_t>(pg << 2) * plane + ii;
+      o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+      o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+      o[2 * plane] = __byte_perm(a_hi, b_hi, 0x5410);
+      o[3 * plane] = __byte_perm(a_hi, b_hi, 0x7632);
+    }
+  }
+}
+
+int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  {
+    const int blocks = std::min(s->num_y, ctx->num_sms * 4);
+    ++ctx->launches, k_stack_level0<<<blocks, kThreads, 0, ctx->stream>>>(
+        cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
+  }
+  size_t max_smem = 0;
+  for (int i = 0; i < s->depth; ++i) {
+    const int padw = (1 << i) >= 4 ? (1 << i) >> 2 : 1;
+    const int nw = padw + ((s->host_view.in[i] * (2 << i) + 3) >> 2);
+    max_smem = std::max<size_t>(max_smem, 2 * static_cast<size_t>(nw + (nw >> 5) + 2) * 4);
+  }
+  if (max_smem > 48 * 1024)
+    CSM_CUDA(cudaFuncSetAttribute(k_stack_rows, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(max_smem)));
+  for (int i = 0; i < s->depth; ++i) {
+    RowsArgs a;
+    a.lvl = s->base + s->level_off[i];
+    a.next = i + 1 < s->depth ? s->base + s->level_off[i + 1] : nullptr;
+    a.quad = reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]);
+    a.pitch = s->level_pitch[i];
+    a.next_pitch = i + 1 < s->depth ? s->level_pitch[i + 1] : 0;
+    a.wide_y = s->num_y + (1 << i) - 1;
+    a.next_wide_y = s->num_y + (2 << i) - 1;
+    a.in = s->host_view.in[i];
+    a.jn = s->host_view.jn[i];
+    a.log2s = i;
+    a.in_magic = a.in > 1 ? static_cast<unsigned int>((0x100000000ull + a.in - 1) / a.in) : 0u;
+    const int padw = (1 << i) >= 4 ? (1 << i) >> 2 : 1;
+    const int nw = padw + ((a.in * (2 << i) + 3) >> 2);
+    const size_t smem = 2 * static_cast<size_t>(nw + (nw >> 5) + 2) * 4;
+    ++ctx->launches, k_stack_rows<<<a.jn << (i + 1), kThreads, smem, ctx->stream>>>(a);
+  }
+  CSM_CUDA(cudaGetLastError());
+  return CSM_OK;
+}
+
 int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev);
 
 int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
-  // Deep stacks (2^depth halo does not fit shared memory) and CSM_STACK_BUILD=levelwise
-  // take the one-launch-per-level path.
-  static const bool force_levelwise = [] {
+  // CSM_STACK_BUILD selects the path: "rows" (default, one launch per level),
+  // "fused" (tile-fused byte levels + quad re-layout, depth <= 7) or "levelwise" (the
+  // plain gather kernels, kept as a second opinion for the parity tests).
+  static const int mode = [] {
     const char* e = getenv("CSM_STACK_BUILD");
-    return e != nullptr && strcmp(e, "levelwise") == 0;
+    if (e != nullptr && strcmp(e, "levelwise") == 0) return 2;
+    if (e != nullptr && strcmp(e, "fused") == 0) return 1;
+    return 0;
   }();
-  if (s->depth <= kFusedMaxDepth && !force_levelwise) return launch_build_fused(ctx, s, cells_dev);
-  return launch_build_levelwise(ctx, s, cells_dev);
+  if (mode == 1 && s->depth <= kFusedMaxDepth) return launch_build_fused(ctx, s, cells_dev);
+  if (mode == 2) return launch_build_levelwise(ctx, s, cells_dev);
+  return launch_build_rows(ctx, s, cells_dev);
 }
 
 int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
-  const size_t n = static_cast<size_t>(s->num_x) * s->num_y;
-  int blocks = static_cast<int>(std::min<size_t>((n / 4 + kThreads - 1) / kThreads + 1,
-                                                 static_cast<size_t>(ctx->num_sms) * 8));
-  ++ctx->launches, k_stack_level0<<<blocks, kThreads, 0, ctx->stream>>>(cells_dev, s->q_lut_dev,
-                                                       s->base + s->level_off[0], n);
+  ++ctx->launches, k_stack_level0<<<std::min(s->num_y, ctx->num_sms * 4), kThreads, 0, ctx->stream>>>(
+      cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
   for (int i = 0; i + 1 < s->depth; ++i) {
     const int h = 1 << i;
     const int in_w = s->num_x + h - 1, in_h = s->num_y + h - 1;
     const int out_w = s->num_x + 2 * h - 1, out_h = s->num_y + 2 * h - 1;
     dim3 block(64, 4);
     dim3 grid((out_w + block.x - 1) / block.x, (out_h + block.y - 1) / block.y);
-    ++ctx->launches, k_stack_level_up<<<grid, block, 0, ctx->stream>>>(s->base + s->level_off[i], in_w, in_h,
-                                                      s->base + s->level_off[i + 1], out_w, out_h, h);
+    ++ctx->launches, k_stack_level_up<<<grid, block, 0, ctx->stream>>>(
+        s->base + s->level_off[i], in_w, in_h, s->level_pitch[i], s->base + s->level_off[i + 1], out_w,
+        out_h, s->level_pitch[i + 1], h);
   }
   for (int i = 0; i < s->depth; ++i) {
     const int w = s->num_x + (1 << i) - 1, hgt = s->num_y + (1 << i) - 1;
@@ -391,8 +564,8 @@ int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_d
     const int qblocks = static_cast<int>(
         std::min<size_t>((total + kThreads - 1) / kThreads, static_cast<size_t>(ctx->num_sms) * 16));
     ++ctx->launches, k_stack_quads<<<qblocks, kThreads, 0, ctx->stream>>>(
-        s->base + s->level_off[i], w, hgt, reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]), i,
-        in, jn);
+        s->base + s->level_off[i], w, hgt, s->level_pitch[i],
+        reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]), i, in, jn);
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
@@ -415,8 +588,10 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
   for (int i = 0; i < depth; ++i) {
     const size_t w = static_cast<size_t>(num_x) + (1u << i) - 1;
     const size_t hgt = static_cast<size_t>(num_y) + (1u << i) - 1;
+    const size_t pitch = (w + 15) & ~static_cast<size_t>(15);
     s->level_off[i] = off;
-    off += (w * hgt + 255) & ~static_cast<size_t>(255);
+    s->level_pitch[i] = static_cast<int>(pitch);
+    off += (pitch * hgt + 255) & ~static_cast<size_t>(255);
   }
   memset(&s->host_view, 0, sizeof(s->host_view));
   for (int i = 0; i < depth; ++i) {
@@ -502,8 +677,24 @@ int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* s, int level, uint8_t* ou
   if (wide_y) *wide_y = h;
   if (out) {
     CSM_CUDA(cudaSetDevice(ctx->device));
-    CSM_CUDA(cudaMemcpyAsync(out, s->base + s->level_off[level], static_cast<size_t>(w) * h,
-                             cudaMemcpyDeviceToHost, ctx->stream));
+    CSM_CUDA(cudaMemcpy2DAsync(out, static_cast<size_t>(w), s->base + s->level_off[level],
+                               static_cast<size_t>(s->level_pitch[level]), static_cast<size_t>(w),
+                               static_cast<size_t>(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
+  return CSM_OK;
+}
+
+int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* s, int level, uint32_t* out, int* in, int* jn) {
+  CSM_REQUIRE(ctx != nullptr && s != nullptr, "NULL argument");
+  CSM_REQUIRE(level >= 0 && level < s->depth, "level out of range");
+  if (in) *in = s->host_view.in[level];
+  if (jn) *jn = s->host_view.jn[level];
+  if (out) {
+    const size_t words = (static_cast<size_t>(4) << (2 * level)) * s->host_view.in[level] * s->host_view.jn[level];
+    CSM_CUDA(cudaSetDevice(ctx->device));
+    CSM_CUDA(cudaMemcpyAsync(out, s->base + s->quad_off[level], words * 4, cudaMemcpyDeviceToHost,
+                             ctx->stream));
     CSM_CUDA(cudaStreamSynchronize(ctx->stream));
   }
   return CSM_OK;

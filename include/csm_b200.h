@@ -99,6 +99,12 @@ int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* ce
 /* Copies level `level` to `out` (may be NULL to query the size only). */
 int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* stack, int level, uint8_t* out,
                       int* wide_x, int* wide_y);
+/* Copies the matcher's re-layout of level `level` (the quad-phase words, DESIGN.md §2;
+ * the reference has no counterpart, its PrecomputationGrid2D::GetValue reads cells_
+ * directly, fast_correlative_scan_matcher_2d.h:56-70) to `out`: 4 * s * s * in * jn
+ * words, s = 1 << level.  `out` may be NULL to query in / jn only.  Test support. */
+int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* stack, int level, uint32_t* out, int* in,
+                     int* jn);
 int csm_stack2d_depth(const csm_stack2d* stack);
 size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
 /* `ctx` may be NULL or a context that no longer exists: the stack's device block goes

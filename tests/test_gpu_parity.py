@@ -29,6 +29,31 @@ def test_stack_bytes_identical(csm, gpu_ctx, nx, ny, depth):
         assert np.array_equal(a, b), "level %d differs" % lvl
 
 
+@pytest.mark.parametrize("nx,ny,depth", [(250, 250, 4), (4, 4, 8), (1, 1, 3), (37, 5, 7), (3, 2, 2),
+                                         (400, 400, 7), (129, 257, 6), (1000, 1000, 7)])
+def test_stack_quad_words_identical(csm, gpu_ctx, nx, ny, depth):
+    """Every word of the matcher's quad-phase layout against the oracle's byte levels:
+    word(u, v) = L(u-s, v-s) | L(u-s, v) << 8 | L(u, v-s) << 16 | L(u, v) << 24 in
+    window-end coordinates (0 outside the level), stored at [v % 2s, u % 2s, v / 2s, u / 2s]."""
+    cells = _tiny_grid(nx * 1000 + ny + 7, nx, ny)
+    og = ob.OracleGrid(cells, 0.05, 1.0, 1.0)
+    om = ob.OracleFCSM2D(og, 1.0, 0.1, depth)
+    m = csm.Matcher(gpu_ctx, csm.Grid(cells, 0.05, 1.0, 1.0), 1.0, 0.1, depth)
+    for lvl in range(depth):
+        s = 1 << lvl
+        L = om.level(lvl).astype(np.uint32)
+        got = m.quad(lvl)
+        two_s, jn, n_i = got.shape[0], got.shape[2], got.shape[3]
+        U, V = n_i * two_s, jn * two_s
+        big = np.zeros((V + s, U + s), dtype=np.uint32)  # big[v + s, u + s] = L(u, v)
+        big[s:s + L.shape[0], s:s + L.shape[1]] = L[:V, :U]
+        assert L.shape[0] <= V and L.shape[1] <= U
+        want = (big[0:V, 0:U] | (big[s:V + s, 0:U] << 8) | (big[0:V, s:U + s] << 16) |
+                (big[s:V + s, s:U + s] << 24))
+        want = want.reshape(jn, two_s, n_i, two_s).transpose(1, 3, 0, 2)
+        assert np.array_equal(want, got), "quad level %d differs" % lvl
+
+
 def _compare(r_o, r_g):
     assert r_g.found == r_o.found
     if r_o.found:
