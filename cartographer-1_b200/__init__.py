@@ -105,6 +105,9 @@ def host():
     L.csmh_grid_create.restype = C.c_void_p
     L.csmh_grid_create.argtypes = [u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
     L.csmh_grid_destroy.argtypes = [C.c_void_p]
+    L.csmh_tsdf_create.restype = C.c_void_p
+    L.csmh_tsdf_create.argtypes = [u16p, u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                   C.c_float, C.c_float]
     L.csmh_quantization_table.argtypes = [C.c_void_p, u8p]
     L.csmh_matcher_create.restype = C.c_void_p
     L.csmh_matcher_create.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int]
@@ -192,6 +195,24 @@ class Grid:
         out = np.empty(65536, dtype=np.uint8)
         host().csmh_quantization_table(self.h, out)
         return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            host().csmh_grid_destroy(self.h)
+            self.h = None
+
+
+class TsdfGrid:
+    """A TSDF2D (truncated signed distance + weight cells); RealTimeCorrelativeScanMatcher2D
+    scores it with the reference's weighted TSD score (RT2D.cc:38-59)."""
+
+    def __init__(self, tsd_cells, weight_cells, res, max_x, max_y, truncation_distance, max_weight):
+        tsd_cells = np.ascontiguousarray(tsd_cells, dtype=np.uint16)
+        weight_cells = np.ascontiguousarray(weight_cells, dtype=np.uint16)
+        assert tsd_cells.shape == weight_cells.shape
+        self.ny, self.nx = tsd_cells.shape
+        self.h = host().csmh_tsdf_create(tsd_cells, weight_cells, self.nx, self.ny, res, max_x, max_y,
+                                         truncation_distance, max_weight)
 
     def __del__(self):
         if getattr(self, "h", None):

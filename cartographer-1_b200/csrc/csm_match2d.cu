@@ -344,68 +344,6 @@ k_scan_prefix(const JobDev* __restrict__ jobs, ScanInfo* __restrict__ scans,
   }
 }
 
-// ---------------------------------------------------------------------------
-// 3. lowest-resolution candidates (FCSM2D.cc:264-333).  grid = (max_scans, jobs).
-//    The candidates of a scan form an nx x ny lattice with step 2^(depth-1); they are
-//    scored as the children of virtual parents with step 2^depth, one tile per warp.
-//    Scores are stored in generation order (x outer, y inner).
-// ---------------------------------------------------------------------------
-constexpr int kTopWarps = 4;
-__global__ void __launch_bounds__(kTopWarps * kWarp)
-k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
-            const ScanInfo* __restrict__ scans, float* __restrict__ top_scores,
-            JobState* __restrict__ state, unsigned long long* __restrict__ scan_best) {
-  __shared__ int2 stage_all[kTopWarps][kWarp];
-  const JobDev& j = jobs[blockIdx.y];
-  const int scan = blockIdx.x;
-  if (scan >= j.S) return;
-  const ScanInfo si = scans[j.scan_off + scan];
-  const int count = si.nx * si.ny;
-  if (count == 0) return;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int2* stage = stage_all[warp];
-  const int li = lane & (kTW - 1), lj = lane >> kLogTW;
-  const int lvl = j.depth - 1;
-  const int two_s = 2 << lvl;
-  const int nvx = (si.nx + 1) >> 1, nvy = (si.ny + 1) >> 1;  // virtual parents
-  const int tiles_x = (nvx + kTW - 1) >> kLogTW, tiles_y = (nvy + kTH - 1) >> kLogTH;
-  const int2* pts = xy + j.xy_off + static_cast<long long>(scan) * j.n;
-  const StackDev& sd = *j.sd;
-  unsigned long long local_best = 0ull;
-  for (int t = warp; t < tiles_x * tiles_y; t += kTopWarps) {
-    const int ti = t % tiles_x, tj = t / tiles_x;
-    const int pi = kTW * ti + li, pj = kTH * tj + lj;
-    const bool alive = pi < nvx && pj < nvy;
-    int sum[4];
-    tile_sums(sd, pts, j.n, lvl, si.min_x + (two_s - 1) + two_s * kTW * ti,
-              si.min_y + (two_s - 1) + two_s * kTH * tj, __ballot_sync(kFull, alive), lane, stage,
-              sum);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int ci = 2 * pi + (k >> 1), cj = 2 * pj + (k & 1);
-      if (alive && ci < si.nx && cj < si.ny) {
-        const float score = to_score(j, sum[k]);
-        const unsigned int cand = static_cast<unsigned int>(si.base + ci * si.ny + cj);
-        top_scores[j.cand_off + cand] = score;
-        const unsigned long long key =
-            (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
-        local_best = max(local_best, key);
-      }
-    }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1)
-    local_best = max(local_best, __shfl_xor_sync(kFull, local_best, o));
-  if (lane == 0 && local_best != 0ull) {
-    atomicMax(&state[blockIdx.y].top_best, local_best);
-    atomicMax(&scan_best[j.scan_off + scan], local_best);
-  }
-  if (threadIdx.x == 0) {
-    atomicAdd(&state[blockIdx.y].scored, static_cast<unsigned long long>(count));
-    atomicAdd(&state[blockIdx.y].scored_phase[0], static_cast<unsigned long long>(count));
-  }
-}
-
 // Decodes a generation index into (scan, x, y) by binary search over the bases.
 __device__ inline void decode_candidate(const JobDev& j, const ScanInfo* __restrict__ scans,
                                         unsigned int cand, int& scan, int& x, int& y) {
@@ -753,6 +691,68 @@ __device__ __forceinline__ void node_sums(const StackDev& sd, const int2* __rest
   sum[1] = s1;
   sum[2] = s2;
   sum[3] = s3;
+}
+
+// ---------------------------------------------------------------------------
+// 3. lowest-resolution candidates (FCSM2D.cc:264-333).  grid = (max_scans, jobs).
+//    The candidates of a scan form an nx x ny lattice with step 2^(depth-1); they are
+//    scored as the children of virtual parents with step 2^depth.  The parents are
+//    taken row by row, 32 per warp (lane = parent, node_sums): the lattice is small
+//    (C3: about 10 x 10 parents per scan), so fixed 8 x 4 tiles left half the lanes idle.
+//    Scores are stored in generation order (x outer, y inner).
+// ---------------------------------------------------------------------------
+constexpr int kTopWarps = 4;
+__global__ void __launch_bounds__(kTopWarps * kWarp)
+k_score_top(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
+            const ScanInfo* __restrict__ scans, float* __restrict__ top_scores,
+            JobState* __restrict__ state, unsigned long long* __restrict__ scan_best) {
+  __shared__ NodeStage stage_all[kTopWarps];
+  const JobDev& j = jobs[blockIdx.y];
+  const int scan = blockIdx.x;
+  if (scan >= j.S) return;
+  const ScanInfo si = scans[j.scan_off + scan];
+  const int count = si.nx * si.ny;
+  if (count == 0) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  NodeStage* stage = &stage_all[warp];
+  const int lvl = j.depth - 1;
+  const int two_s = 2 << lvl;
+  const int nvx = (si.nx + 1) >> 1, nvy = (si.ny + 1) >> 1;  // virtual parents
+  const int parents = nvx * nvy;
+  const int2* pts = xy + j.xy_off + static_cast<long long>(scan) * j.n;
+  const StackDev& sd = *j.sd;
+  unsigned long long local_best = 0ull;
+  for (int f0 = warp * kWarp; f0 < parents; f0 += kTopWarps * kWarp) {
+    const bool alive = f0 + lane < parents;
+    const int f = alive ? f0 + lane : f0;  // idle lanes copy the item's first parent
+    const int pj = f / nvx, pi = f - pj * nvx;
+    int sum[4];
+    node_sums(sd, pts, j.n, lvl, si.min_x + (two_s - 1), si.min_y + (two_s - 1), pi, pj, lane, stage,
+              sum);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int ci = 2 * pi + (k >> 1), cj = 2 * pj + (k & 1);
+      if (alive && ci < si.nx && cj < si.ny) {
+        const float score = to_score(j, sum[k]);
+        const unsigned int cand = static_cast<unsigned int>(si.base + ci * si.ny + cj);
+        top_scores[j.cand_off + cand] = score;
+        const unsigned long long key =
+            (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
+        local_best = max(local_best, key);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    local_best = max(local_best, __shfl_xor_sync(kFull, local_best, o));
+  if (lane == 0 && local_best != 0ull) {
+    atomicMax(&state[blockIdx.y].top_best, local_best);
+    atomicMax(&scan_best[j.scan_off + scan], local_best);
+  }
+  if (threadIdx.x == 0) {
+    atomicAdd(&state[blockIdx.y].scored, static_cast<unsigned long long>(count));
+    atomicAdd(&state[blockIdx.y].scored_phase[0], static_cast<unsigned long long>(count));
+  }
 }
 
 // Appends `count` nodes of one bucket as a block: scratch range, bucket-relative offset

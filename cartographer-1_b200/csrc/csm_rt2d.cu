@@ -3,7 +3,8 @@
 //
 // Replaces /root/reference/cartographer/mapping/internal/2d/scan_matching/
 // real_time_correlative_scan_matcher_2d.cc:61-75 (ComputeCandidateScore on a
-// ProbabilityGrid), :83-115 (GenerateExhaustiveSearchCandidates), :117-176 (Match,
+// ProbabilityGrid), :38-59 (the same on a TSDF2D: weighted mean of the normalised
+// truncated distance, two cell arrays and two tables), :83-115 (GenerateExhaustiveSearchCandidates), :117-176 (Match,
 // ScoreCandidates).  One block per (job, scan): the scan is rotated and discretised
 // into shared memory once, then every thread scores whole candidates, summing the
 // probabilities in point order with sequential fp32 adds exactly like the CPU loop
@@ -20,12 +21,15 @@ namespace csm {
 struct RtJobDev {
   const uint16_t* cells;
   const float* cost_table;
+  const uint16_t* weight_cells;  // TSDF only (nullptr selects the probability score)
+  const float* weight_table;
   const double* penalty;
   int num_x, num_y, n, S, lin;
   long long pts_off, quat_off;
   float q0w, q0s, tx, ty;
   double max_x, max_y, res;
   float oob;
+  float max_cc, oob_tsd;  // TSDF: truncation distance, TSD outside the grid
 };
 
 // One warp per (job, scan); a block carries kRtWarps scans of one job.  The scan is
@@ -60,26 +64,58 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
   unsigned long long local = 0ull;
   for (int c = lane; c < count; c += 32) {
     const int x = c / side - j.lin, y = c % side - j.lin;  // x outer, y inner (RT2D.cc:100-112)
-    float sum = 0.f;
-    for (int p0 = 0; p0 < j.n; p0 += 8) {
-      float prob[8];
+    float score;
+    if (j.weight_cells == nullptr) {
+      float sum = 0.f;
+      for (int p0 = 0; p0 < j.n; p0 += 8) {
+        float prob[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        prob[k] = j.oob;
-        if (p0 + k < j.n) {
-          const int px = cell[p0 + k].x + x, py = cell[p0 + k].y + y;
-          if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
-              static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
-            const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
-            prob[k] = __fsub_rn(1.f, __ldg(j.cost_table + v));
+        for (int k = 0; k < 8; ++k) {
+          prob[k] = j.oob;
+          if (p0 + k < j.n) {
+            const int px = cell[p0 + k].x + x, py = cell[p0 + k].y + y;
+            if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
+                static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
+              const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
+              prob[k] = __fsub_rn(1.f, __ldg(j.cost_table + v));
+            }
           }
         }
-      }
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (p0 + k < j.n) sum = __fadd_rn(sum, prob[k]);
+        for (int k = 0; k < 8; ++k)
+          if (p0 + k < j.n) sum = __fadd_rn(sum, prob[k]);
+      }
+      score = __fdiv_rn(sum, n_float);
+    } else {
+      // TSDF2D (RT2D.cc:38-59): per point, in order, score += ((max_cc - |tsd|) / max_cc) * w
+      // and summed_weight += w, all fp32 without contraction.
+      float sum = 0.f, wsum = 0.f;
+      for (int p0 = 0; p0 < j.n; p0 += 8) {
+        float tsd[8], wt[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          tsd[k] = j.oob_tsd;
+          wt[k] = 0.f;
+          if (p0 + k < j.n) {
+            const int px = cell[p0 + k].x + x, py = cell[p0 + k].y + y;
+            if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
+                static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
+              const size_t flat = static_cast<size_t>(py) * j.num_x + px;
+              tsd[k] = __ldg(j.cost_table + __ldg(j.cells + flat));
+              wt[k] = __ldg(j.weight_table + __ldg(j.weight_cells + flat));
+            }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (p0 + k < j.n) {
+            const float norm = __fdiv_rn(__fsub_rn(j.max_cc, fabsf(tsd[k])), j.max_cc);
+            sum = __fadd_rn(sum, __fmul_rn(norm, wt[k]));
+            wsum = __fadd_rn(wsum, wt[k]);
+          }
+      }
+      score = wsum == 0.f ? 0.f : __fdiv_rn(sum, wsum);
     }
-    float score = __fdiv_rn(sum, n_float);
     const unsigned int cand = static_cast<unsigned int>(scan) * count + c;
     score = __double2float_rn(__dmul_rn(static_cast<double>(score), j.penalty[cand]));
     const unsigned long long key =
@@ -123,6 +159,18 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
       table_at[in.cost_table] = table_bytes;
       table_bytes += up(sizeof(float) * 65536);
     }
+    if (in.weight_cells != nullptr) {
+      CSM_REQUIRE(in.weight_table != nullptr && in.max_correspondence_cost > 0.f,
+                  "TSDF rt job needs a weight table and a positive truncation distance");
+      if (!grid_at.count(in.weight_cells)) {
+        grid_at[in.weight_cells] = grid_bytes;
+        grid_bytes += up(sizeof(uint16_t) * static_cast<size_t>(in.num_x) * in.num_y);
+      }
+      if (!table_at.count(in.weight_table)) {
+        table_at[in.weight_table] = table_bytes;
+        table_bytes += up(sizeof(float) * 65536);
+      }
+    }
     RtJobDev& j = dev[i];
     j.num_x = in.num_x;
     j.num_y = in.num_y;
@@ -139,6 +187,8 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     j.max_y = in.max_y;
     j.res = in.resolution;
     j.oob = in.out_of_bounds_probability;
+    j.max_cc = in.max_correspondence_cost;
+    j.oob_tsd = in.out_of_bounds_tsd;
     n_pts += in.num_points;
     n_scans += in.num_scans;
     n_pen += side * side * in.num_scans;
@@ -172,11 +222,17 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     j.penalty = reinterpret_cast<const double*>(base + o_pen) + pen_at;
     j.cells = reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
     j.cost_table = reinterpret_cast<const float*>(base + o_tab + table_at[in.cost_table]);
+    j.weight_cells = in.weight_cells
+                         ? reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.weight_cells])
+                         : nullptr;
+    j.weight_table = in.weight_cells
+                         ? reinterpret_cast<const float*>(base + o_tab + table_at[in.weight_table])
+                         : nullptr;
     pen_at += pen_n;
   }
   for (const auto& kv : grid_at) {
     for (int i = 0; i < num_jobs; ++i)
-      if (jobs[i].cells == kv.first) {
+      if (jobs[i].cells == kv.first || jobs[i].weight_cells == kv.first) {
         memcpy(pin + o_grid + kv.second, kv.first,
                sizeof(uint16_t) * static_cast<size_t>(jobs[i].num_x) * jobs[i].num_y);
         break;

@@ -91,7 +91,6 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
   for (size_t i = 0; i != n; ++i) {
     const Query& q = queries[i];
     CSM_CHECK(q.point_cloud != nullptr && q.grid != nullptr);
-    CSM_CHECK(q.grid->GetGridType() == GridType::PROBABILITY_GRID);
     CSM_CHECK(!q.point_cloud->empty());
     const MapLimits& limits = q.grid->limits();
     const float yaw = static_cast<float>(q.initial_pose_estimate.rotation().angle());
@@ -162,6 +161,14 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
     job.linear_bound = sp.linear_bounds[0].max_x;
     job.penalty = penalty[i].data();
     job.out_of_bounds_probability = kMinProbability;  // probability_grid.cc:78-82
+    if (q.grid->GetGridType() == GridType::TSDF) {  // reference :38-59, :163-168
+      const TSDF2D& tsdf = static_cast<const TSDF2D&>(*q.grid);
+      job.cost_table = tsdf.value_converter().value_to_tsd_table().data();
+      job.weight_cells = tsdf.weight_cells().data();
+      job.weight_table = tsdf.value_converter().value_to_weight_table().data();
+      job.max_correspondence_cost = tsdf.GetMaxCorrespondenceCost();
+      job.out_of_bounds_tsd = tsdf.value_converter().getMinTSD();  // tsdf_2d.cc:96-97
+    }
   }
   std::vector<csm_result2d> results(n);
   CheckOk(csm_rt_match2d_batch(ctx->get(), jobs.data(), static_cast<int>(n), results.data()),

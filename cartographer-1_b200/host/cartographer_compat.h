@@ -268,6 +268,70 @@ class ProbabilityGrid : public Grid2D {
   GridType GetGridType() const override { return GridType::PROBABILITY_GRID; }
 };
 
+// mapping/internal/2d/tsd_value_converter.{h,cc}
+class TSDValueConverter {
+ public:
+  TSDValueConverter(float max_tsd, float max_weight, ValueConversionTables* conversion_tables)
+      : max_tsd_(max_tsd),
+        min_tsd_(-max_tsd),
+        max_weight_(max_weight),
+        tsd_resolution_(32766.f / (max_tsd_ - min_tsd_)),
+        weight_resolution_(32766.f / (max_weight_ - min_weight_)),
+        value_to_tsd_(conversion_tables->GetConversionTable(min_tsd_, min_tsd_, max_tsd_)),
+        value_to_weight_(conversion_tables->GetConversionTable(min_weight_, min_weight_, max_weight)) {}
+  uint16 TSDToValue(const float tsd) const {
+    return static_cast<uint16>(
+        std::lround((std::min(std::max(tsd, min_tsd_), max_tsd_) - min_tsd_) * tsd_resolution_) + 1);
+  }
+  uint16 WeightToValue(const float weight) const {
+    return static_cast<uint16>(
+        std::lround((std::min(std::max(weight, min_weight_), max_weight_) - min_weight_) * weight_resolution_) + 1);
+  }
+  float ValueToTSD(const uint16 value) const { return (*value_to_tsd_)[value]; }
+  float ValueToWeight(const uint16 value) const { return (*value_to_weight_)[value]; }
+  static uint16 getUnknownTSDValue() { return 0; }
+  static uint16 getUnknownWeightValue() { return 0; }
+  static uint16 getUpdateMarker() { return 1u << 15; }
+  float getMaxTSD() const { return max_tsd_; }
+  float getMinTSD() const { return min_tsd_; }
+  float getMaxWeight() const { return max_weight_; }
+  float getMinWeight() const { return min_weight_; }
+  const std::vector<float>& value_to_tsd_table() const { return *value_to_tsd_; }
+  const std::vector<float>& value_to_weight_table() const { return *value_to_weight_; }
+
+ private:
+  float max_tsd_, min_tsd_, max_weight_, tsd_resolution_, weight_resolution_;
+  static constexpr float min_weight_ = 0.f;
+  const std::vector<float>* value_to_tsd_;
+  const std::vector<float>* value_to_weight_;
+};
+
+// mapping/internal/2d/tsdf_2d.{h,cc}: the parts the real-time matcher reads plus SetCell.
+class TSDF2D : public Grid2D {
+ public:
+  TSDF2D(const MapLimits& limits, float truncation_distance, float max_weight,
+         ValueConversionTables* conversion_tables)
+      : Grid2D(limits, -truncation_distance, truncation_distance, conversion_tables),
+        value_converter_(truncation_distance, max_weight, conversion_tables),
+        weight_cells_(static_cast<size_t>(limits.cell_limits().num_x_cells) *
+                          limits.cell_limits().num_y_cells,
+                      TSDValueConverter::getUnknownWeightValue()) {}
+  GridType GetGridType() const override { return GridType::TSDF; }
+  // tsdf_2d.cc:51-68 (the update marker is dropped at once: no FinishUpdate here)
+  void SetCell(int x, int y, float tsd, float weight) {
+    const size_t flat = static_cast<size_t>(limits().cell_limits().num_x_cells) * y + x;
+    (*mutable_correspondence_cost_cells())[flat] = value_converter_.TSDToValue(tsd);
+    weight_cells_[flat] = value_converter_.WeightToValue(weight);
+  }
+  const std::vector<uint16>& weight_cells() const { return weight_cells_; }
+  std::vector<uint16>* mutable_weight_cells() { return &weight_cells_; }
+  const TSDValueConverter& value_converter() const { return value_converter_; }
+
+ private:
+  TSDValueConverter value_converter_;
+  std::vector<uint16> weight_cells_;
+};
+
 // mapping/id.h:42-95
 struct NodeId {
   NodeId(int trajectory_id, int node_index) : trajectory_id(trajectory_id), node_index(node_index) {}

@@ -36,7 +36,7 @@ void* csmh_context_raw(void* c) { return static_cast<DeviceContext*>(c)->get(); 
 
 struct GridHolder {
   mapping::ValueConversionTables tables;
-  std::unique_ptr<mapping::ProbabilityGrid> grid;
+  std::unique_ptr<mapping::Grid2D> grid;
 };
 
 void* csmh_grid_create(const uint16_t* cells, int nx, int ny, double res, double max_x,
@@ -47,6 +47,20 @@ void* csmh_grid_create(const uint16_t* cells, int nx, int ny, double res, double
       &h->tables));
   std::memcpy(h->grid->mutable_correspondence_cost_cells()->data(), cells,
               sizeof(uint16_t) * static_cast<size_t>(nx) * ny);
+  return h;
+}
+// A TSDF2D from its two cell arrays (tsdf_2d.h): only the real-time matcher takes it.
+void* csmh_tsdf_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, int nx, int ny,
+                       double res, double max_x, double max_y, float truncation_distance,
+                       float max_weight) {
+  GridHolder* h = new GridHolder;
+  mapping::TSDF2D* tsdf = new mapping::TSDF2D(
+      mapping::MapLimits(res, transform::Vector2d(max_x, max_y), mapping::CellLimits(nx, ny)),
+      truncation_distance, max_weight, &h->tables);
+  h->grid.reset(tsdf);
+  const size_t bytes = sizeof(uint16_t) * static_cast<size_t>(nx) * ny;
+  std::memcpy(tsdf->mutable_correspondence_cost_cells()->data(), tsd_cells, bytes);
+  std::memcpy(tsdf->mutable_weight_cells()->data(), weight_cells, bytes);
   return h;
 }
 void csmh_grid_destroy(void* g) { delete static_cast<GridHolder*>(g); }

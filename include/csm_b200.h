@@ -188,6 +188,14 @@ typedef struct {
   const double* penalty;
   float out_of_bounds_probability; /* kMinProbability for a ProbabilityGrid            */
                                    /* (cartographer/mapping/2d/probability_grid.cc:78-82)*/
+  /* TSDF2D grids (RT2D.cc:38-59, mapping/internal/2d/tsdf_2d.cc:88-98): a non-NULL
+   * weight_cells selects the TSDF score sum(w * (max_cc - |tsd|) / max_cc) / sum(w),
+   * 0 when sum(w) == 0.  `cells` / `cost_table` are then the TSD cells and the
+   * value-to-TSD table; a cell outside the grid reads (out_of_bounds_tsd, weight 0). */
+  const uint16_t* weight_cells;    /* NULL for a ProbabilityGrid                       */
+  const float* weight_table;       /* 65536 floats, value-to-weight                    */
+  float max_correspondence_cost;   /* the truncation distance (tsdf_2d.cc:26)          */
+  float out_of_bounds_tsd;         /* TSDValueConverter::getMinTSD()                   */
 } csm_rt_job2d;
 
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,

@@ -306,6 +306,73 @@ class ProbabilityGrid {
 };
 
 // ---------------------------------------------------------------------------
+// TSDF2D: the second Grid2D flavour the real-time matcher scores against
+// (mapping/internal/2d/tsdf_2d.{h,cc}, tsd_value_converter.{h,cc}).  Two uint16 arrays
+// (truncated signed distance, weight), each with its own value table.
+// ---------------------------------------------------------------------------
+class TSDF2D {
+ public:
+  // tsdf_2d.cc:24-33, tsd_value_converter.cc:22-32
+  TSDF2D(const MapLimits& limits, const float truncation_distance, const float max_weight)
+      : limits_(limits),
+        max_tsd_(truncation_distance),
+        min_tsd_(-truncation_distance),
+        max_weight_(max_weight),
+        tsd_resolution_(32766.f / (max_tsd_ - min_tsd_)),
+        weight_resolution_(32766.f / (max_weight_ - 0.f)),
+        tsd_cells_(static_cast<size_t>(limits.cell_limits.num_x_cells) * limits.cell_limits.num_y_cells,
+                   kUnknownValue),
+        weight_cells_(tsd_cells_.size(), kUnknownValue),
+        value_to_tsd_(MakeConversionTable(min_tsd_, min_tsd_, max_tsd_)),
+        value_to_weight_(MakeConversionTable(0.f, 0.f, max_weight_)) {}
+  // Adopts existing cell arrays (flat = num_x_cells * y + x).
+  TSDF2D(const MapLimits& limits, const float truncation_distance, const float max_weight,
+         const uint16_t* tsd_cells, const uint16_t* weight_cells)
+      : TSDF2D(limits, truncation_distance, max_weight) {
+    tsd_cells_.assign(tsd_cells, tsd_cells + tsd_cells_.size());
+    weight_cells_.assign(weight_cells, weight_cells + weight_cells_.size());
+  }
+
+  const MapLimits& limits() const { return limits_; }
+  const std::vector<uint16_t>& tsd_cells() const { return tsd_cells_; }
+  const std::vector<uint16_t>& weight_cells() const { return weight_cells_; }
+  const std::vector<float>& value_to_tsd() const { return value_to_tsd_; }
+  const std::vector<float>& value_to_weight() const { return value_to_weight_; }
+  // Grid2D's max_correspondence_cost_ of a TSDF2D is the truncation distance (tsdf_2d.cc:26).
+  float GetMaxCorrespondenceCost() const { return max_tsd_; }
+  float GetMinTSD() const { return min_tsd_; }
+
+  // tsd_value_converter.h:38-56
+  uint16_t TSDToValue(const float tsd) const {
+    return static_cast<uint16_t>(RoundToInt((Clamp(tsd, min_tsd_, max_tsd_) - min_tsd_) * tsd_resolution_) + 1);
+  }
+  uint16_t WeightToValue(const float weight) const {
+    return static_cast<uint16_t>(RoundToInt((Clamp(weight, 0.f, max_weight_) - 0.f) * weight_resolution_) + 1);
+  }
+  // tsdf_2d.cc:51-68 without the update marker (cells are painted once, then "finished").
+  void SetCell(const Array2i& c, const float tsd, const float weight) {
+    ORACLE_CHECK(limits_.Contains(c));
+    const int flat = limits_.cell_limits.num_x_cells * c.y + c.x;
+    tsd_cells_[flat] = TSDToValue(tsd);
+    weight_cells_[flat] = WeightToValue(weight);
+  }
+  // tsdf_2d.cc:88-98
+  std::pair<float, float> GetTSDAndWeight(const Array2i& c) const {
+    if (limits_.Contains(c)) {
+      const int flat = limits_.cell_limits.num_x_cells * c.y + c.x;
+      return std::make_pair(value_to_tsd_[tsd_cells_[flat]], value_to_weight_[weight_cells_[flat]]);
+    }
+    return std::make_pair(min_tsd_, 0.f);
+  }
+
+ private:
+  MapLimits limits_;
+  float max_tsd_, min_tsd_, max_weight_, tsd_resolution_, weight_resolution_;
+  std::vector<uint16_t> tsd_cells_, weight_cells_;
+  std::vector<float> value_to_tsd_, value_to_weight_;
+};
+
+// ---------------------------------------------------------------------------
 // Range-data insertion: only needed to build the fixtures of the reference's
 // FastCorrelativeScanMatcherTest (mapping/2d/probability_grid_range_data_inserter_2d.cc:30-143,
 // mapping/internal/2d/ray_to_pixel_mask.cc:25-170).
@@ -873,21 +940,50 @@ class RealTimeCorrelativeScanMatcher2D {
     return cands;
   }
 
-  // real_time_correlative_scan_matcher_2d.cc:61-75,151-176 (probability grid)
-  void ScoreCandidates(const ProbabilityGrid& grid, const std::vector<DiscreteScan2D>& discrete,
+  // real_time_correlative_scan_matcher_2d.cc:61-75 (probability grid)
+  static float ComputeCandidateScore(const ProbabilityGrid& grid, const DiscreteScan2D& scan,
+                                     const int x_index_offset, const int y_index_offset) {
+    float s = 0.f;
+    for (const Array2i& xy : scan) {
+      Array2i p;
+      p.x = xy.x + x_index_offset;
+      p.y = xy.y + y_index_offset;
+      s += grid.GetProbability(p);
+    }
+    s /= static_cast<float>(scan.size());
+    ORACLE_CHECK(s > 0.f);
+    return s;
+  }
+  // real_time_correlative_scan_matcher_2d.cc:38-59 (TSDF)
+  static float ComputeCandidateScore(const TSDF2D& tsdf, const DiscreteScan2D& scan,
+                                     const int x_index_offset, const int y_index_offset) {
+    float candidate_score = 0.f;
+    float summed_weight = 0.f;
+    for (const Array2i& xy : scan) {
+      Array2i p;
+      p.x = xy.x + x_index_offset;
+      p.y = xy.y + y_index_offset;
+      const std::pair<float, float> tsd_and_weight = tsdf.GetTSDAndWeight(p);
+      const float normalized_tsd_score =
+          (tsdf.GetMaxCorrespondenceCost() - std::abs(tsd_and_weight.first)) /
+          tsdf.GetMaxCorrespondenceCost();
+      const float weight = tsd_and_weight.second;
+      candidate_score += normalized_tsd_score * weight;
+      summed_weight += weight;
+    }
+    if (summed_weight == 0.f) return 0.f;
+    candidate_score /= summed_weight;
+    ORACLE_CHECK(candidate_score >= 0.f);
+    return candidate_score;
+  }
+
+  // real_time_correlative_scan_matcher_2d.cc:151-176
+  template <typename Grid>
+  void ScoreCandidates(const Grid& grid, const std::vector<DiscreteScan2D>& discrete,
                        const SearchParameters& sp, std::vector<Candidate2D>* cands) const {
     (void)sp;
     for (Candidate2D& c : *cands) {
-      float s = 0.f;
-      for (const Array2i& xy : discrete[c.scan_index]) {
-        Array2i p;
-        p.x = xy.x + c.x_index_offset;
-        p.y = xy.y + c.y_index_offset;
-        s += grid.GetProbability(p);
-      }
-      s /= static_cast<float>(discrete[c.scan_index].size());
-      ORACLE_CHECK(s > 0.f);
-      c.score = s;
+      c.score = ComputeCandidateScore(grid, discrete[c.scan_index], c.x_index_offset, c.y_index_offset);
       const double t = std::hypot(c.x, c.y) * options_.translation_delta_cost_weight +
                        std::abs(c.orientation) * options_.rotation_delta_cost_weight;
       c.score *= std::exp(-(t * t));  // float *= double
@@ -895,7 +991,8 @@ class RealTimeCorrelativeScanMatcher2D {
   }
 
   // real_time_correlative_scan_matcher_2d.cc:117-149
-  double Match(const Rigid2d& initial, const PointCloud& cloud, const ProbabilityGrid& grid,
+  template <typename Grid>
+  double Match(const Rigid2d& initial, const PointCloud& cloud, const Grid& grid,
                Rigid2d* pose, FastCorrelativeScanMatcher2D::Winner* winner = nullptr) const {
     ORACLE_CHECK(pose != nullptr);
     const double initial_rotation = initial.angle;

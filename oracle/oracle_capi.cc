@@ -171,6 +171,59 @@ double oracle_rt_match2d(void* grid, double linear_window, double angular_window
   return score;
 }
 
+// --- TSDF grid + real-time matcher on it ----------------------------------------
+void* oracle_tsdf2d_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, int nx, int ny,
+                           double res, double max_x, double max_y, float truncation_distance,
+                           float max_weight) {
+  return new TSDF2D(MakeLimits(res, max_x, max_y, nx, ny), truncation_distance, max_weight, tsd_cells,
+                    weight_cells);
+}
+void oracle_tsdf2d_destroy(void* g) { delete static_cast<TSDF2D*>(g); }
+// TSDValueConverter::TSDToValue / WeightToValue of n floats (for painting fixtures).
+void oracle_tsdf2d_values(float truncation_distance, float max_weight, const float* tsd,
+                          const float* weight, int n, uint16_t* tsd_values, uint16_t* weight_values) {
+  const TSDF2D g(MakeLimits(1., 0., 0., 1, 1), truncation_distance, max_weight);
+  for (int i = 0; i < n; ++i) {
+    tsd_values[i] = g.TSDToValue(tsd[i]);
+    weight_values[i] = g.WeightToValue(weight[i]);
+  }
+}
+double oracle_rt_match2d_tsdf(void* grid, double linear_window, double angular_window,
+                              double translation_delta_cost_weight, double rotation_delta_cost_weight,
+                              double init_x, double init_y, double init_theta, const float* xyz, int n,
+                              oracle_result2d* out) {
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.linear_search_window = linear_window;
+  o.angular_search_window = angular_window;
+  o.translation_delta_cost_weight = translation_delta_cost_weight;
+  o.rotation_delta_cost_weight = rotation_delta_cost_weight;
+  const RealTimeCorrelativeScanMatcher2D matcher(o);
+  Rigid2d init, pose;
+  init.tx = init_x;
+  init.ty = init_y;
+  init.angle = init_theta;
+  FastCorrelativeScanMatcher2D::Winner w;
+  const double score = matcher.Match(init, ToCloud(xyz, n), *static_cast<TSDF2D*>(grid), &pose, &w);
+  MatchStats st;
+  Fill(out, true, w, static_cast<float>(score), pose, st);
+  return score;
+}
+// ScoreCandidates of ONE candidate at zero rotation (the shape of the reference's
+// real_time_correlative_scan_matcher_2d_test.cc:143-201).
+float oracle_rt_score_candidate_tsdf(void* grid, const float* xyz, int n, int x_offset, int y_offset) {
+  const TSDF2D& g = *static_cast<TSDF2D*>(grid);
+  const SearchParameters sp(0, 0, 0., 0.);
+  const std::vector<PointCloud> scans = GenerateRotatedScans(ToCloud(xyz, n), sp);
+  const std::vector<DiscreteScan2D> discrete = DiscretizeScans(g.limits(), scans, 0.f, 0.f);
+  RealTimeCorrelativeScanMatcherOptions o;
+  o.translation_delta_cost_weight = 0.;
+  o.rotation_delta_cost_weight = 0.;
+  std::vector<Candidate2D> cands;
+  cands.emplace_back(0, x_offset, y_offset, sp);
+  RealTimeCorrelativeScanMatcher2D(o).ScoreCandidates(g, discrete, sp, &cands);
+  return cands[0].score;
+}
+
 // --- thread-pooled constraint builder (timed CPU baseline) ---------------------
 // grids[num_submaps], submap_pose[num_submaps*3]; searches: submap index, node id,
 // full flag, relative pose [3], cloud given by offsets into xyz (offsets has

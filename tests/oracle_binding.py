@@ -90,6 +90,15 @@ def lib():
                                     C.c_double, C.c_double, C.c_double, f32p, C.c_int,
                                     C.POINTER(OracleResult2D)]
     L.oracle_rt_match2d.restype = C.c_double
+    L.oracle_tsdf2d_create.argtypes = [u16p, u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                       C.c_float, C.c_float]
+    L.oracle_tsdf2d_create.restype = C.c_void_p
+    L.oracle_tsdf2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_tsdf2d_values.argtypes = [C.c_float, C.c_float, f32p, f32p, C.c_int, u16p, u16p]
+    L.oracle_rt_match2d_tsdf.argtypes = L.oracle_rt_match2d.argtypes
+    L.oracle_rt_match2d_tsdf.restype = C.c_double
+    L.oracle_rt_score_candidate_tsdf.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int]
+    L.oracle_rt_score_candidate_tsdf.restype = C.c_float
     L.oracle_constraint_batch.argtypes = [
         C.c_int, C.POINTER(C.c_void_p), f64p, C.c_int, C.c_int, i32p, i32p, f64p, f32p, i64p,
         C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
@@ -130,6 +139,39 @@ class OracleGrid:
         if getattr(self, "h", None):
             lib().oracle_grid2d_destroy(self.h)
             self.h = None
+
+
+class OracleTsdf:
+    """TSDF2D restatement (tsd cells, weight cells, truncation distance, max weight)."""
+
+    def __init__(self, tsd_cells, weight_cells, res, max_x, max_y, truncation_distance, max_weight):
+        self.tsd_cells = np.ascontiguousarray(tsd_cells, dtype=np.uint16)
+        self.weight_cells = np.ascontiguousarray(weight_cells, dtype=np.uint16)
+        self.ny, self.nx = self.tsd_cells.shape
+        self.res, self.max_x, self.max_y = res, max_x, max_y
+        self.truncation_distance, self.max_weight = truncation_distance, max_weight
+        self.h = lib().oracle_tsdf2d_create(self.tsd_cells, self.weight_cells, self.nx, self.ny, res,
+                                            max_x, max_y, truncation_distance, max_weight)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_tsdf2d_destroy(self.h)
+            self.h = None
+
+    def score_candidate(self, pts, x_offset, y_offset):
+        pts = np.ascontiguousarray(pts, dtype=np.float32)
+        return float(lib().oracle_rt_score_candidate_tsdf(self.h, pts, len(pts), x_offset, y_offset))
+
+
+def tsdf_values(truncation_distance, max_weight, tsd, weight):
+    """TSDValueConverter::TSDToValue / WeightToValue, elementwise."""
+    tsd = np.ascontiguousarray(tsd, dtype=np.float32)
+    weight = np.ascontiguousarray(weight, dtype=np.float32)
+    tv = np.empty(tsd.size, dtype=np.uint16)
+    wv = np.empty(tsd.size, dtype=np.uint16)
+    lib().oracle_tsdf2d_values(truncation_distance, max_weight, tsd.reshape(-1), weight.reshape(-1),
+                               tsd.size, tv, wv)
+    return tv.reshape(tsd.shape), wv.reshape(tsd.shape)
 
 
 class OracleFCSM2D:
