@@ -27,36 +27,34 @@ namespace {
 
 constexpr int kThreads = 256;
 
-// Level 0: out(x, y) = q_lut[cells(x, y)], zero in the row padding.  Persistent blocks
-// (the 32 KB table is staged once per block); a thread makes 4 cells = one output word.
+// Level 0: out(x, y) = q_lut[cells(x, y)], zero in the row padding.  A thread makes 4
+// cells = one output word; the table (32 K useful entries, one byte each) is read
+// through L1 -- staging it per block cost more than the rows a block converts.
+// blockDim = (words per pass, rows per block); grid = (passes, row groups).
 __global__ void __launch_bounds__(kThreads)
 k_stack_level0(const uint16_t* __restrict__ cells, const uint8_t* __restrict__ q_lut,
                uint8_t* __restrict__ out, int num_x, int num_y, int pitch) {
-  __shared__ uint8_t lut[65536 / 2];  // values 0..32767; the update marker bit is masked off
-  for (int i = threadIdx.x; i < 32768 / 16; i += kThreads)
-    reinterpret_cast<uint4*>(lut)[i] = __ldg(reinterpret_cast<const uint4*>(q_lut) + i);
-  __syncthreads();
-  const int pw = pitch >> 2;
-  for (int y = blockIdx.x; y < num_y; y += gridDim.x) {
-    const size_t row = static_cast<size_t>(y) * num_x;
-    const uint16_t* __restrict__ crow = cells + row;
-    uint32_t* __restrict__ orow = reinterpret_cast<uint32_t*>(out + static_cast<size_t>(y) * pitch);
-    const bool aligned = (row & 3) == 0;
-    for (int k = threadIdx.x; k < pw; k += kThreads) {
-      const int x = 4 * k;
-      uint32_t w = 0u;
-      if (aligned && x + 3 < num_x) {
-        const uint2 v = __ldg(reinterpret_cast<const uint2*>(crow + x));
-        w = static_cast<uint32_t>(lut[v.x & 0x7FFFu]) | (static_cast<uint32_t>(lut[(v.x >> 16) & 0x7FFFu]) << 8) |
-            (static_cast<uint32_t>(lut[v.y & 0x7FFFu]) << 16) | (static_cast<uint32_t>(lut[(v.y >> 16) & 0x7FFFu]) << 24);
-      } else {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (y >= num_y || k >= (pitch >> 2)) return;
+  const size_t row = static_cast<size_t>(y) * num_x;
+  const uint16_t* __restrict__ crow = cells + row;
+  const int x = 4 * k;
+  uint32_t w = 0u;
+  if ((row & 3) == 0 && x + 3 < num_x) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(crow + x));
+    const uint32_t b0 = __ldg(q_lut + (v.x & 0x7FFFu)), b1 = __ldg(q_lut + ((v.x >> 16) & 0x7FFFu));
+    const uint32_t b2 = __ldg(q_lut + (v.y & 0x7FFFu)), b3 = __ldg(q_lut + ((v.y >> 16) & 0x7FFFu));
+    w = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+  } else {
+    uint32_t c[4];
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
-          if (x + b < num_x) w |= static_cast<uint32_t>(lut[__ldg(crow + x + b) & 0x7FFFu]) << (8 * b);
-      }
-      orow[k] = w;
-    }
+    for (int b = 0; b < 4; ++b) c[b] = x + b < num_x ? (__ldg(crow + x + b) & 0x7FFFu) : 0x10000u;
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+      if (c[b] != 0x10000u) w |= static_cast<uint32_t>(__ldg(q_lut + c[b])) << (8 * b);
   }
+  reinterpret_cast<uint32_t*>(out + static_cast<size_t>(y) * pitch)[k] = w;
 }
 
 // Level i -> i+1 (h = 2^i): out(X, Y) = max of in at (X, Y), (X-h, Y), (X, Y-h),
@@ -405,6 +403,7 @@ k_stack_rows(const RowsArgs a) {
   extern __shared__ uint32_t rows32[];
   const int s = 1 << a.log2s, two_s = 2 << a.log2s, sh = a.log2s + 1;
   const int v = blockIdx.x;  // window-end row Y of level i == row of level i + 1
+  const int nthr = blockDim.x;  // sized by the launcher so that a row's words fill whole passes
   const int padw = s >= 4 ? (s >> 2) : 1;           // zero words in front of X = 0
   const int spanw = (a.in * two_s + 3) >> 2;        // staged words from X = 0
   const int nw = padw + spanw;
@@ -418,7 +417,7 @@ k_stack_rows(const RowsArgs a) {
     const bool row_ok = static_cast<unsigned>(Y) < static_cast<unsigned>(a.wide_y);
     const uint32_t* __restrict__ src =
         reinterpret_cast<const uint32_t*>(a.lvl + static_cast<size_t>(row_ok ? Y : 0) * a.pitch);
-    for (int w = threadIdx.x; w < nw; w += kThreads) {
+    for (int w = threadIdx.x; w < nw; w += nthr) {
       const int k = w - padw;
       dst[skew(w)] = (row_ok && static_cast<unsigned>(k) < static_cast<unsigned>(pw)) ? __ldg(src + k) : 0u;
     }
@@ -443,7 +442,7 @@ k_stack_rows(const RowsArgs a) {
   if (a.next != nullptr && v < a.next_wide_y) {
     uint32_t* __restrict__ orow = reinterpret_cast<uint32_t*>(a.next + static_cast<size_t>(v) * a.next_pitch);
     const int npw = a.next_pitch >> 2;
-    for (int k = threadIdx.x; k < npw; k += kThreads) {
+    for (int k = threadIdx.x; k < npw; k += nthr) {
       uint32_t m = 0u;
       if (k < spanw) {
         uint32_t c0, l0, c1, l1;
@@ -459,7 +458,7 @@ k_stack_rows(const RowsArgs a) {
   const size_t rowbase = (static_cast<size_t>((v & (two_s - 1)) << sh) * a.jn + (v >> sh)) * a.in;
   if (a.log2s == 0) {
     // 2 phases: the word X = 4k .. 4k + 3 holds (pu, ii) = (0, 2k), (1, 2k), (0, 2k + 1), (1, 2k + 1).
-    for (int k = threadIdx.x; 2 * k < a.in; k += kThreads) {
+    for (int k = threadIdx.x; 2 * k < a.in; k += nthr) {
       uint32_t c0, l0, c1, l1;
       taps(k + padw, c0, l0, c1, l1);
       const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
@@ -474,7 +473,7 @@ k_stack_rows(const RowsArgs a) {
     }
   } else {
     const int items = (two_s >> 2) * a.in;  // (group of 4 phases, ii)
-    for (int t = threadIdx.x; t < items; t += kThreads) {
+    for (int t = threadIdx.x; t < items; t += nthr) {
       const int pg = a.in_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(t), a.in_magic)) : t;
       const int ii = t - pg * a.in;
       uint32_t c0, l0, c1, l1;
@@ -490,12 +489,18 @@ k_stack_rows(const RowsArgs a) {
   }
 }
 
+void launch_level0(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  const int pw = s->level_pitch[0] >> 2;
+  const int passes = (pw + kThreads - 1) / kThreads;
+  const int bx = std::min(kThreads, (((pw + passes - 1) / passes) + 31) & ~31);
+  const int by = std::max(1, kThreads / bx);
+  const dim3 grid((pw + bx - 1) / bx, (s->num_y + by - 1) / by);
+  ++ctx->launches, k_stack_level0<<<grid, dim3(bx, by), 0, ctx->stream>>>(
+      cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
+}
+
 int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
-  {
-    const int blocks = std::min(s->num_y, ctx->num_sms * 4);
-    ++ctx->launches, k_stack_level0<<<blocks, kThreads, 0, ctx->stream>>>(
-        cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
-  }
+  launch_level0(ctx, s, cells_dev);
   size_t max_smem = 0;
   for (int i = 0; i < s->depth; ++i) {
     const int padw = (1 << i) >= 4 ? (1 << i) >> 2 : 1;
@@ -521,7 +526,12 @@ int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     const int padw = (1 << i) >= 4 ? (1 << i) >> 2 : 1;
     const int nw = padw + ((a.in * (2 << i) + 3) >> 2);
     const size_t smem = 2 * static_cast<size_t>(nw + (nw >> 5) + 2) * 4;
-    ++ctx->launches, k_stack_rows<<<a.jn << (i + 1), kThreads, smem, ctx->stream>>>(a);
+    // A row is ~nw words; 256 threads would run ceil(nw / 256) passes with the last one
+    // mostly empty (1000 cells: 283 words = 2 passes at 55 %).  Keep the pass count, shrink
+    // the block to the warps that fill it.
+    const int passes = (nw + kThreads - 1) / kThreads;
+    const int threads = std::min(kThreads, (((nw + passes - 1) / passes) + 31) & ~31);
+    ++ctx->launches, k_stack_rows<<<a.jn << (i + 1), threads, smem, ctx->stream>>>(a);
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
@@ -545,8 +555,7 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
 }
 
 int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
-  ++ctx->launches, k_stack_level0<<<std::min(s->num_y, ctx->num_sms * 4), kThreads, 0, ctx->stream>>>(
-      cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
+  launch_level0(ctx, s, cells_dev);
   for (int i = 0; i + 1 < s->depth; ++i) {
     const int h = 1 << i;
     const int in_w = s->num_x + h - 1, in_h = s->num_y + h - 1;

@@ -229,6 +229,16 @@ def rt_match(grid, opts, init, pts):
     return r
 
 
+def rt_match_tsdf(grid, opts, init, pts):
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    r = OracleResult2D()
+    lib().oracle_rt_match2d_tsdf(grid.h, opts["linear_search_window"], opts["angular_search_window"],
+                                 opts["translation_delta_cost_weight"],
+                                 opts["rotation_delta_cost_weight"], init[0], init[1], init[2], pts,
+                                 len(pts), C.byref(r))
+    return r
+
+
 def constraint_batch(num_threads, grids, submap_poses, search_submap, search_full, rel_poses, clouds,
                      sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
                      global_min_score=0.6, linear_window=7.0, angular_window=np.deg2rad(30.0),

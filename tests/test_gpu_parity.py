@@ -190,6 +190,60 @@ def test_real_time_matcher_edge_cases(csm, gpu_ctx):
         assert (r_g.pose_x, r_g.pose_y, r_g.pose_theta) == (r_o.pose_x, r_o.pose_y, r_o.pose_theta)
 
 
+def test_real_time_matcher_tsdf_bit_exact(csm, gpu_ctx):
+    """TSDF2D branch (RT2D.cc:38-59): winner and score bits against the oracle, on the
+    reference fixture's seven-point L, on a painted office world with random weights, with a
+    scan partly outside the grid, and on a never-observed grid (every score 0)."""
+    import tsdf_util
+    from test_tsdf_cpu import POINTS
+    cases = []
+    tv, wv = tsdf_util.paint_from_points(20, 20, 0.05, 0.3, 0.5, POINTS[:, :2], (0.5, -0.5), 0.3, 1.0)
+    fix = (tv, wv, 0.05, 0.3, 0.5, 0.3, 1.0)
+    zero = (np.zeros_like(tv), np.zeros_like(wv), 0.05, 0.3, 0.5, 0.3, 1.0)
+    o_small = {"linear_search_window": 0.1, "angular_search_window": 0.1,
+               "translation_delta_cost_weight": 0.0, "rotation_delta_cost_weight": 0.0}
+    cases.append((fix, o_small, (0.05, -0.05, 0.02), POINTS))
+    cases.append((fix, dict(o_small, translation_delta_cost_weight=0.3, rotation_delta_cost_weight=0.7),
+                  (0.0, 0.05, -0.05), POINTS))
+    cases.append((zero, o_small, (0.0, 0.0, 0.0), POINTS))
+    w = synth.World(300, 260, seed=31)
+    tv, wv = tsdf_util.from_world(w, 0.3, 10.0, seed=5)
+    world = (tv, wv, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    o_c2 = {"linear_search_window": 0.1, "angular_search_window": float(np.deg2rad(20.0)),
+            "translation_delta_cost_weight": 0.1, "rotation_delta_cost_weight": 0.1}
+    rng = np.random.default_rng(17)
+    for i in range(8):
+        pose, pts = synth.make_scan(w, 500 + i, max_range=6.0)
+        pts = np.ascontiguousarray(pts[::max(1, len(pts) // 250)])
+        init = (pose[0] + rng.uniform(-0.08, 0.08), pose[1] + rng.uniform(-0.08, 0.08),
+                pose[2] + rng.uniform(-0.26, 0.26))
+        if i == 7:
+            init = (pose[0] + 4.0, pose[1] - 3.0, pose[2])  # partly outside the grid
+        cases.append((world, o_c2, init, pts))
+    grids = {}
+    for args, opts, init, pts in cases:
+        key = id(args)
+        if key not in grids:
+            grids[key] = (csm.TsdfGrid(*args), ob.OracleTsdf(*args))
+        g, og = grids[key]
+        r_g = csm.rt_match_batch(gpu_ctx, [g], [np.ascontiguousarray(pts)], [init], **opts)[0]
+        r_o = ob.rt_match_tsdf(og, opts, init, pts)
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
+        assert (r_g.pose_x, r_g.pose_y, r_g.pose_theta) == (r_o.pose_x, r_o.pose_y, r_o.pose_theta)
+    # one mixed batch: a ProbabilityGrid job next to TSDF jobs
+    pg, opg = csm.Grid(w.cells, w.res, w.max_x, w.max_y), ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    g, og = grids[id(world)]
+    _, _, init, pts = cases[4]
+    res = csm.rt_match_batch(gpu_ctx, [g, pg, g], [pts, pts, pts], [init, init, init], **o_c2)
+    for r_g, r_o in zip(res, [ob.rt_match_tsdf(og, o_c2, init, pts), ob.rt_match(opg, o_c2, init, pts),
+                              ob.rt_match_tsdf(og, o_c2, init, pts)]):
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
+
+
 def _builder_case(seed, n_sub=3, n_search=24, size=240):
     rng = np.random.default_rng(seed)
     worlds = [synth.World(size, size, seed=seed * 10 + k) for k in range(n_sub)]

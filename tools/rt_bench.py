@@ -49,6 +49,22 @@ def main():
         assert (r.scan_index, r.x_index_offset, r.y_index_offset) == \
             (res[i].scan_index, res[i].x_index_offset, res[i].y_index_offset)
     out["cpu_port_1_thread"] = {"scans_per_s": n / (time.perf_counter() - t0), "sample": n}
+    # The same scans against a TSDF2D of the same world (RT2D.cc:38-59).
+    import tsdf_util
+    tv, wv = tsdf_util.from_world(w, 0.3, 10.0, seed=3)
+    tg = pkg.TsdfGrid(tv, wv, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    otg = ob.OracleTsdf(tv, wv, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    pkg.rt_match_batch(ctx, [tg] * 64, clouds[:64], inits[:64])
+    t0 = time.perf_counter()
+    for _ in range(20):
+        tres = pkg.rt_match_batch(ctx, [tg] * 64, clouds[:64], inits[:64])
+    out["tsdf_batch_64"] = {"scans_per_s": 64 * 20 / (time.perf_counter() - t0)}
+    t0 = time.perf_counter()
+    for i in range(32):
+        r = ob.rt_match_tsdf(otg, opts, inits[i], clouds[i])
+        assert (r.scan_index, r.x_index_offset, r.y_index_offset) == \
+            (tres[i].scan_index, tres[i].x_index_offset, tres[i].y_index_offset)
+    out["tsdf_cpu_port_1_thread"] = {"scans_per_s": 32 / (time.perf_counter() - t0), "sample": 32}
     print(json.dumps(out))
 
 
