@@ -148,6 +148,8 @@ int csm_ctx_create(int device, csm_ctx** out) {
   {
     const char* sweep = getenv("CSM_SWEEP");  // diagnostic: "tiles" selects the tile sweep
     c->sweep_tiles = sweep != nullptr && strcmp(sweep, "tiles") == 0;
+    const char* ld = getenv("CSM_EXPAND_LOAD");  // experiment: "noalloc" = L1::no_allocate loads
+    c->expand_noalloc = ld != nullptr && strcmp(ld, "noalloc") == 0;
   }
   CSM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CSM_CUDA(cudaEventCreate(&c->ev0));

@@ -95,6 +95,7 @@ struct csm_ctx {
   csm::DevBuf frontier[2];
   csm::DevBuf frontier_aux;             // 2D node sweep: block descriptors | work items
   bool sweep_tiles = false;             // CSM_SWEEP=tiles: the tile sweep instead of node lists
+  bool expand_noalloc = false;          // CSM_EXPAND_LOAD=noalloc: L1::no_allocate loads in the sweep
   unsigned long long frontier_cap = 0;  // unused (capacities come from the buffers)
   // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
   static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2

@@ -620,8 +620,23 @@ struct NodeStage {
   int4 mix[kStagePoints];        // (P, ca0, ra0, -) of points that need the bounds check
 };
 
+// Read-only 32-bit load that does not allocate an L1 line (CSM_EXPAND_LOAD=noalloc): the
+// sweep re-uses almost nothing from L1 (ncu: 20-25 % sector hits, all of them inside one
+// request), so the fills only compete with the loads for the L1 data pipe.
+template <bool kNoAlloc>
+__device__ __forceinline__ uint32_t ldg_w(const uint32_t* p) {
+  if constexpr (kNoAlloc) {
+    uint32_t w;
+    asm("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(p));
+    return w;
+  } else {
+    return __ldg(p);
+  }
+}
+
 // Sums of the four child values over all scan points for this lane's node (ni, nj).
 // Lanes beyond the chunk's node count carry a copy of lane 0's node.
+template <bool kNoAlloc = false>
 __device__ __forceinline__ void node_sums(const StackDev& sd, const int2* __restrict__ pts, int n,
                                           int lvl, int x0, int y0, int ni, int nj, int lane,
                                           NodeStage* __restrict__ stage, int (&sum)[4]) {
@@ -662,9 +677,9 @@ __device__ __forceinline__ void node_sums(const StackDev& sd, const int2* __rest
     for (; k + 8 <= cin; k += 8) {
       const int4 a = *reinterpret_cast<const int4*>(&stage->in_p[k]);
       const int4 b = *reinterpret_cast<const int4*>(&stage->in_p[k + 4]);
-      const uint32_t w0 = __ldg(qb + a.x), w1 = __ldg(qb + a.y), w2 = __ldg(qb + a.z),
-                     w3 = __ldg(qb + a.w), w4 = __ldg(qb + b.x), w5 = __ldg(qb + b.y),
-                     w6 = __ldg(qb + b.z), w7 = __ldg(qb + b.w);
+      const uint32_t w0 = ldg_w<kNoAlloc>(qb + a.x), w1 = ldg_w<kNoAlloc>(qb + a.y), w2 = ldg_w<kNoAlloc>(qb + a.z),
+                     w3 = ldg_w<kNoAlloc>(qb + a.w), w4 = ldg_w<kNoAlloc>(qb + b.x), w5 = ldg_w<kNoAlloc>(qb + b.y),
+                     w6 = ldg_w<kNoAlloc>(qb + b.z), w7 = ldg_w<kNoAlloc>(qb + b.w);
       lo += (w0 & 0x00FF00FFu) + (w1 & 0x00FF00FFu) + (w2 & 0x00FF00FFu) + (w3 & 0x00FF00FFu) +
             (w4 & 0x00FF00FFu) + (w5 & 0x00FF00FFu) + (w6 & 0x00FF00FFu) + (w7 & 0x00FF00FFu);
       hi += __byte_perm(w0, 0u, 0x4341) + __byte_perm(w1, 0u, 0x4341) +
@@ -673,7 +688,7 @@ __device__ __forceinline__ void node_sums(const StackDev& sd, const int2* __rest
             __byte_perm(w6, 0u, 0x4341) + __byte_perm(w7, 0u, 0x4341);
     }
     for (; k < cin; ++k) {
-      const uint32_t w = __ldg(qb + stage->in_p[k]);
+      const uint32_t w = ldg_w<kNoAlloc>(qb + stage->in_p[k]);
       lo += w & 0x00FF00FFu;
       hi += __byte_perm(w, 0u, 0x4341);
     }
@@ -926,6 +941,7 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
 //      next one fetched while the current item is summed): an item costs between a few
 //      and several hundred loads per lane, so a static split leaves SMs idle at the end
 //      (ncu: l1tex busy 60 % of elapsed but 86 % of active cycles before this).
+template <bool kNoAlloc>
 __global__ void __launch_bounds__(kExpandWarps * kWarp, kNodeBlocksPerSm)
 k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
                const ScanInfo* __restrict__ scans, const float* __restrict__ top_scores,
@@ -970,7 +986,7 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
     const int ni = node & 0xFFFF, nj = node >> 16;
     if (hist != nullptr && lane == 0) atomicAdd(&hist[d * 33 + cnt], 1ull);
     int sum[4];
-    node_sums(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
+    node_sums<kNoAlloc>(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
               si.min_x + (two_s - 1), si.min_y + (two_s - 1), ni, nj, lane, stage, sum);
     // Children lattice of this scan on level lvl (FCSM2D.cc:353-367: a child beyond
     // max_x / max_y is not generated).
@@ -1547,7 +1563,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
           node_tmp, node_blocks, b->bucket_start, b->bucket_istart, node_list, node_items,
           b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap);
-      ++ctx->launches, k_expand_nodes<<<ctx->num_sms * kNodeBlocksPerSm, kExpandWarps * kWarp, 0, st>>>(
+      ++ctx->launches, (ctx->expand_noalloc ? k_expand_nodes<true> : k_expand_nodes<false>)<<<ctx->num_sms * kNodeBlocksPerSm, kExpandWarps * kWarp, 0, st>>>(
           b->jobs, b->xy, b->scans, b->top_scores, b->state, b->bucket_js, node_list, node_items,
           node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist);
     }
