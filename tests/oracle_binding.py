@@ -90,6 +90,11 @@ def lib():
                                     C.c_double, C.c_double, C.c_double, f32p, C.c_int,
                                     C.POINTER(OracleResult2D)]
     L.oracle_rt_match2d.restype = C.c_double
+    L.oracle_ceres_match2d.argtypes = [C.c_void_p, f64p, f64p, f64p, f32p, C.c_int, f64p, f64p]
+    L.oracle_ceres_match2d.restype = None
+    L.oracle_ceres_evaluate2d.argtypes = [C.c_void_p, f64p, f64p, C.c_double, f64p, f32p, C.c_int,
+                                          f64p, f64p]
+    L.oracle_ceres_evaluate2d.restype = None
     L.oracle_tsdf2d_create.argtypes = [u16p, u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                        C.c_float, C.c_float]
     L.oracle_tsdf2d_create.restype = C.c_void_p
@@ -227,6 +232,36 @@ def rt_match(grid, opts, init, pts):
                             opts["translation_delta_cost_weight"], opts["rotation_delta_cost_weight"],
                             init[0], init[1], init[2], pts, len(pts), C.byref(r))
     return r
+
+
+CERES_DEFAULTS = {"occupied_space_weight": 1.0, "translation_weight": 10.0, "rotation_weight": 40.0,
+                  "use_nonmonotonic_steps": False, "max_num_iterations": 20}
+
+
+def _ceres_options(opts):
+    o = dict(CERES_DEFAULTS)
+    o.update(opts or {})
+    return np.array([o["occupied_space_weight"], o["translation_weight"], o["rotation_weight"],
+                     1.0 if o["use_nonmonotonic_steps"] else 0.0, o["max_num_iterations"]], np.float64)
+
+
+def ceres_match(grid, opts, target, init, pts):
+    """CeresScanMatcher2D::Match restatement: (pose[3], summary dict)."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    pose, summ = np.zeros(3), np.zeros(6)
+    lib().oracle_ceres_match2d(grid.h, _ceres_options(opts), np.asarray(target, np.float64),
+                               np.asarray(init, np.float64), pts, len(pts), pose, summ)
+    return pose, {"initial_cost": summ[0], "final_cost": summ[1], "iterations": int(summ[2]),
+                  "num_successful_steps": int(summ[3]), "num_unsuccessful_steps": int(summ[4]),
+                  "termination": int(summ[5])}
+
+
+def ceres_evaluate(grid, opts, target, initial_angle, pose, pts):
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    r, j = np.zeros(len(pts) + 3), np.zeros((len(pts) + 3, 3))
+    lib().oracle_ceres_evaluate2d(grid.h, _ceres_options(opts), np.asarray(target, np.float64),
+                                  float(initial_angle), np.asarray(pose, np.float64), pts, len(pts), r, j)
+    return r, j
 
 
 def rt_match_tsdf(grid, opts, init, pts):
