@@ -58,7 +58,7 @@ ABI_SYMBOLS = [
     "csm_stack3d_build", "csm_stack3d_level", "csm_stack3d_depth", "csm_stack3d_device_bytes",
     "csm_stack3d_destroy", "csm_grid3d_build", "csm_grid3d_destroy", "csm_match3d_batch",
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
-    "csm_discretize3d", "csm_rt_match3d_batch",
+    "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch",
 ]
 
 _abi = None
@@ -304,6 +304,36 @@ def rt_match_batch(ctx, grids, clouds, initial, linear_search_window=0.1,
     rc = host().csmh_rt_match_batch(ctx.h, n, handles, opts, init, xyz, offsets, out)
     assert rc == 0
     return out
+
+
+def ceres_match_batch(ctx, grids, clouds, targets, initial, occupied_space_weight=1.0,
+                      translation_weight=10.0, rotation_weight=40.0, use_nonmonotonic_steps=False,
+                      max_num_iterations=20):
+    """CeresScanMatcher2D::Match for every (grid, cloud, target translation, initial pose):
+    returns (poses [n, 3], summaries [n, 6] = initial_cost, final_cost, iterations, successful,
+    unsuccessful steps, termination type)."""
+    n = len(clouds)
+    L = host()
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    L.csmh_ceres_match_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), f64p, f64p, f64p,
+                                         f32p, i64p, f64p, f64p]
+    handles = (C.c_void_p * n)(*[g.h for g in grids])
+    opts = np.array([occupied_space_weight, translation_weight, rotation_weight,
+                     1.0 if use_nonmonotonic_steps else 0.0, max_num_iterations], dtype=np.float64)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, c in enumerate(clouds):
+        offsets[i + 1] = offsets[i] + len(c)
+    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
+                                               for c in clouds], axis=0), dtype=np.float32)
+    poses, summaries = np.zeros((n, 3)), np.zeros((n, 6))
+    rc = L.csmh_ceres_match_batch(ctx.h, n, handles, opts,
+                                  np.ascontiguousarray(targets, np.float64).reshape(-1),
+                                  np.ascontiguousarray(initial, np.float64).reshape(-1), xyz, offsets,
+                                  poses.reshape(-1), summaries.reshape(-1))
+    assert rc == 0
+    return poses, summaries
 
 
 def discretize(ctx, res, max_x, max_y, nx, ny, pts, init, linear_window, angular_window,

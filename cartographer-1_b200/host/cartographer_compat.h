@@ -20,6 +20,7 @@
 #include <cstdlib>
 #include <map>
 #include <memory>
+#include <string>
 #include <tuple>
 #include <vector>
 
@@ -407,8 +408,69 @@ namespace metrics {
 class FamilyFactory;
 }  // namespace metrics
 
+}  // namespace mapping
+namespace common {
+namespace proto {
+// common/proto/ceres_solver_options.proto (fields 1-3)
+class CeresSolverOptions {
+ public:
+  bool use_nonmonotonic_steps() const { return use_nonmonotonic_steps_; }
+  int max_num_iterations() const { return max_num_iterations_; }
+  int num_threads() const { return num_threads_; }
+  void set_use_nonmonotonic_steps(bool v) { use_nonmonotonic_steps_ = v; }
+  void set_max_num_iterations(int v) { max_num_iterations_ = v; }
+  void set_num_threads(int v) { num_threads_ = v; }
+
+ private:
+  bool use_nonmonotonic_steps_ = false;
+  int max_num_iterations_ = 0;
+  int num_threads_ = 1;
+};
+}  // namespace proto
+}  // namespace common
+}  // namespace cartographer
+
+// The fields of ceres::Solver::Summary a Cartographer caller reads (ceres/solver.h); the
+// solve itself runs on the device (csm_ceres_match2d_batch).
+namespace ceres {
+enum TerminationType { CONVERGENCE, NO_CONVERGENCE, FAILURE };
+struct Solver {
+  struct Summary {
+    double initial_cost = 0., final_cost = 0.;
+    int num_successful_steps = 0, num_unsuccessful_steps = 0;
+    int num_iterations = 0;  // iterations after the initial evaluation
+    TerminationType termination_type = NO_CONVERGENCE;
+    std::string message;
+    std::string BriefReport() const {
+      return "B200 LM: iterations " + std::to_string(num_iterations) + ", initial_cost " +
+             std::to_string(initial_cost) + ", final_cost " + std::to_string(final_cost) + ", " + message;
+    }
+    std::string FullReport() const { return BriefReport(); }
+    bool IsSolutionUsable() const { return termination_type != FAILURE; }
+  };
+};
+}  // namespace ceres
+
+namespace cartographer {
+namespace mapping {
 namespace scan_matching {
 namespace proto {
+// mapping/proto/scan_matching/ceres_scan_matcher_options_2d.proto (fields 1, 2, 3, 9)
+class CeresScanMatcherOptions2D {
+ public:
+  double occupied_space_weight() const { return occupied_space_weight_; }
+  double translation_weight() const { return translation_weight_; }
+  double rotation_weight() const { return rotation_weight_; }
+  const common::proto::CeresSolverOptions& ceres_solver_options() const { return ceres_solver_options_; }
+  common::proto::CeresSolverOptions* mutable_ceres_solver_options() { return &ceres_solver_options_; }
+  void set_occupied_space_weight(double v) { occupied_space_weight_ = v; }
+  void set_translation_weight(double v) { translation_weight_ = v; }
+  void set_rotation_weight(double v) { rotation_weight_ = v; }
+
+ private:
+  double occupied_space_weight_ = 0., translation_weight_ = 0., rotation_weight_ = 0.;
+  common::proto::CeresSolverOptions ceres_solver_options_;
+};
 // fast_correlative_scan_matcher_options_2d.proto
 class FastCorrelativeScanMatcherOptions2D {
  public:

@@ -9,6 +9,7 @@
 #include <mutex>
 
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/constraints/constraint_builder_2d.h"
 
@@ -158,6 +159,48 @@ int csmh_matcher_rebuild_dev(void* ctx, void* m, const uint16_t* cells_dev) {
   return csm_stack2d_rebuild_dev(
       static_cast<DeviceContext*>(ctx)->get(),
       const_cast<csm_stack2d*>(static_cast<FastCorrelativeScanMatcher2D*>(m)->stack()), cells_dev);
+}
+
+// CeresScanMatcher2D::MatchBatch.  options5 = occupied_space_weight, translation_weight,
+// rotation_weight, use_nonmonotonic_steps, max_num_iterations; target[2i..], init_pose[3i..];
+// out_pose[3i..]; out_summary[6i..] = initial_cost, final_cost, iterations, successful,
+// unsuccessful steps, termination type (0 convergence, 1 no convergence, 2 failure).
+int csmh_ceres_match_batch(void* ctx, int n, void* const* grids, const double* options5,
+                           const double* target, const double* init_pose, const float* xyz,
+                           const int64_t* offsets, double* out_pose, double* out_summary) {
+  using mapping::scan_matching::CeresScanMatcher2D;
+  mapping::scan_matching::proto::CeresScanMatcherOptions2D o;
+  o.set_occupied_space_weight(options5[0]);
+  o.set_translation_weight(options5[1]);
+  o.set_rotation_weight(options5[2]);
+  o.mutable_ceres_solver_options()->set_use_nonmonotonic_steps(options5[3] != 0.);
+  o.mutable_ceres_solver_options()->set_max_num_iterations(static_cast<int>(options5[4]));
+  const CeresScanMatcher2D matcher(o, static_cast<DeviceContext*>(ctx));
+  std::vector<sensor::PointCloud> clouds(n);
+  std::vector<CeresScanMatcher2D::Query> q(n);
+  for (int i = 0; i < n; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    q[i].point_cloud = &clouds[i];
+    q[i].grid = static_cast<GridHolder*>(grids[i])->grid.get();
+    q[i].target_translation = transform::Vector2d(target[2 * i], target[2 * i + 1]);
+    q[i].initial_pose_estimate = transform::Rigid2d(
+        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
+  }
+  const auto answers = matcher.MatchBatch(q);
+  for (int i = 0; i < n; ++i) {
+    const auto& a = answers[i];
+    out_pose[3 * i] = a.pose_estimate.translation().x();
+    out_pose[3 * i + 1] = a.pose_estimate.translation().y();
+    out_pose[3 * i + 2] = a.pose_estimate.rotation().angle();
+    out_summary[6 * i] = a.summary.initial_cost;
+    out_summary[6 * i + 1] = a.summary.final_cost;
+    out_summary[6 * i + 2] = a.summary.num_iterations;
+    out_summary[6 * i + 3] = a.summary.num_successful_steps;
+    out_summary[6 * i + 4] = a.summary.num_unsuccessful_steps;
+    out_summary[6 * i + 5] = static_cast<int>(a.summary.termination_type);
+  }
+  return 0;
 }
 
 // RealTimeCorrelativeScanMatcher2D::Match for n scans in one device batch.

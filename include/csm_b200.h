@@ -201,6 +201,43 @@ typedef struct {
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
                          csm_result2d* results);
 
+/* ---- CeresScanMatcher2D::Match, batched ------------------------
+ * Replaces cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.cc:64-110
+ * (with occupied_space_cost_function_2d.cc:30-96 and the translation / rotation delta
+ * functors) for ProbabilityGrid: minimises over (x, y, theta)
+ *   sum_i [w_occ / sqrt(N) * C(T p_i)]^2 + [w_t (x - tx)]^2 + [w_t (y - ty)]^2 + [w_r (theta - theta0)]^2
+ * with C the bicubic interpolation of the correspondence-cost grid (kMaxCorrespondenceCost
+ * outside), by the trust-region Levenberg-Marquardt iteration ceres::Solve runs for
+ * Cartographer's options (Jacobi scaling, Ceres' default radii and tolerances).  One warp per
+ * problem, fp64.  Results agree with the CPU restatement to ~1e-9 on typical problems; the
+ * parity tests allow 1e-6 on the pose (normal equations here, QR there).
+ * termination: 0 gradient tolerance, 1 parameter tolerance, 2 function tolerance,
+ *              3 max_num_iterations, 4 minimum trust-region radius, 5 failure.
+ */
+typedef struct {
+  const uint16_t* cells;      /* grid cells, host                                    */
+  int32_t num_x, num_y;
+  const float* cost_table;    /* 65536 floats, value-to-correspondence-cost          */
+  const float* points_xyz;
+  int32_t num_points;
+  int32_t max_num_iterations;       /* ceres_solver_options.max_num_iterations        */
+  int32_t use_nonmonotonic_steps;   /* ceres_solver_options.use_nonmonotonic_steps    */
+  int32_t pad;
+  double max_x, max_y, resolution;
+  double initial_pose[3];           /* x, y, theta                                    */
+  double target_translation[2];
+  double occupied_space_weight, translation_weight, rotation_weight;
+} csm_ceres_job2d;
+
+typedef struct {
+  double pose[3];
+  double initial_cost, final_cost;  /* ceres::Solver::Summary                         */
+  int32_t iterations, num_successful_steps, num_unsuccessful_steps, termination;
+} csm_ceres_result2d;
+
+int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs, int num_jobs,
+                            csm_ceres_result2d* results);
+
 /* ==== 3D path ======================================================================
  * Citations relative to cartographer/mapping/internal/3d/scan_matching/:
  *   FCSM3D = fast_correlative_scan_matcher_3d.{h,cc}
