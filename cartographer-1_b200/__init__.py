@@ -359,15 +359,18 @@ def constraint_builder_run(grids, submap_poses, search_submap, search_full, rel_
                            sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
                            global_min_score=0.6, linear_window=7.0,
                            angular_window=float(np.deg2rad(30.0)), translation_weight=1.1e4,
-                           rotation_weight=1e5):
+                           rotation_weight=1e5, ceres=None):
     """Drives ConstraintBuilder2D (MaybeAdd*Constraint / NotifyEndOfNode / WhenDone) over the
     given searches; returns (seconds, found[int32 n], transform[n, 3], stats[4])."""
     n = len(clouds)
     handles = (C.c_void_p * len(grids))(*[g.h for g in grids])
     dev = np.ascontiguousarray(devices, dtype=np.int32)
+    c = ceres or {}  # ceres_scan_matcher options; None = no refinement
     opts = np.array([sampling_ratio, max_constraint_distance, min_score, global_min_score,
-                     linear_window, angular_window, translation_weight, rotation_weight],
-                    dtype=np.float64)
+                     linear_window, angular_window, translation_weight, rotation_weight,
+                     c.get("occupied_space_weight", 0.0), c.get("translation_weight", 0.0),
+                     c.get("rotation_weight", 0.0), 1.0 if c.get("use_nonmonotonic_steps") else 0.0,
+                     c.get("max_num_iterations", 0)], dtype=np.float64)
     offsets = np.zeros(n + 1, dtype=np.int64)
     for i, c in enumerate(clouds):
         offsets[i + 1] = offsets[i] + len(c)

@@ -1,5 +1,7 @@
 #include "cartographer/mapping/internal/constraints/constraint_builder_2d.h"
 
+#include "cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.h"
+
 #include <cmath>
 #include <cstdio>
 #include <thread>
@@ -177,6 +179,28 @@ void ConstraintBuilder2D::RunFlush(const std::vector<PendingSearch>& searches,
     if (queries.empty()) return;
     const auto shard_answers = FastCorrelativeScanMatcher2D::MatchBatch(ctx, queries);
     for (size_t k = 0; k != shard[slot].size(); ++k) answers[shard[slot][k]] = shard_answers[k];
+    // Refinement of every found pose, one more device batch on the same context
+    // (reference .cc:245-249: "Use the CSM estimate as both the initial and previous pose").
+    if (options_.ceres_scan_matcher_options().occupied_space_weight() > 0.) {
+      std::vector<scan_matching::CeresScanMatcher2D::Query> refine;
+      std::vector<size_t> which;
+      for (const size_t i : shard[slot]) {
+        if (!answers[i].found) continue;
+        scan_matching::CeresScanMatcher2D::Query q;
+        q.target_translation = answers[i].pose_estimate.translation();
+        q.initial_pose_estimate = answers[i].pose_estimate;
+        q.point_cloud = &searches[i].constant_data->filtered_gravity_aligned_point_cloud;
+        q.grid = matcher_of[i].grid;
+        refine.push_back(q);
+        which.push_back(i);
+      }
+      if (!refine.empty()) {
+        const scan_matching::CeresScanMatcher2D ceres_scan_matcher(options_.ceres_scan_matcher_options(),
+                                                                   ctx);
+        const auto refined = ceres_scan_matcher.MatchBatch(refine);
+        for (size_t k = 0; k != which.size(); ++k) answers[which[k]].pose_estimate = refined[k].pose_estimate;
+      }
+    }
   };
   std::vector<std::thread> workers;
   for (int slot = 1; slot < num_devices; ++slot)
@@ -191,9 +215,7 @@ void ConstraintBuilder2D::RunFlush(const std::vector<PendingSearch>& searches,
     scored += a.candidates_scored;
     if (!a.found) continue;  // below-threshold searches leave a null slot (.cc:225-241)
     ++found;
-    // [Ceres hook] In a full Cartographer tree the reference's refinement goes here:
-    // ceres_scan_matcher_.Match(pose.translation(), pose, cloud, *grid, &pose, &summary)
-    // (reference .cc:245-249).  Ceres is outside this path and absent from this image.
+    // a.pose_estimate is already refined (run_shard) when the Ceres options are set.
     // constraint_transform = ComputeSubmapPose(*submap).inverse() * pose_estimate
     const transform::Rigid2d constraint_transform =
         ComputeSubmapPose(*s.submap).inverse() * a.pose_estimate;

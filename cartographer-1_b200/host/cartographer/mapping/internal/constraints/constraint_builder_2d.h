@@ -11,8 +11,9 @@
 // submap go to the GPU that holds its precomputation stack), runs one
 // FastCorrelativeScanMatcher2D::Batch per GPU concurrently, and fills the result
 // slots.  There is no collective on the data path; results are gathered on the
-// host.  Ceres refinement (reference :245-249) is not part of this path: the
-// constraint carries the correlative scan matcher's pose estimate.
+// host.  Ceres refinement (reference :245-249) runs as one more device batch per flush
+// (CeresScanMatcher2D::MatchBatch) when options.ceres_scan_matcher_options() is filled in;
+// with an empty message the constraint carries the correlative scan matcher's pose estimate.
 #ifndef CARTOGRAPHER_MAPPING_INTERNAL_CONSTRAINTS_CONSTRAINT_BUILDER_2D_H_
 #define CARTOGRAPHER_MAPPING_INTERNAL_CONSTRAINTS_CONSTRAINT_BUILDER_2D_H_
 

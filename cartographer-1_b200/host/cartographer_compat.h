@@ -555,6 +555,13 @@ class ConstraintBuilderOptions {
   mutable_fast_correlative_scan_matcher_options_3d() {
     return &fast_correlative_scan_matcher_options_3d_;
   }
+  // field 11; an occupied_space_weight of 0 (message not filled in) disables the refinement
+  const scan_matching::proto::CeresScanMatcherOptions2D& ceres_scan_matcher_options() const {
+    return ceres_scan_matcher_options_;
+  }
+  scan_matching::proto::CeresScanMatcherOptions2D* mutable_ceres_scan_matcher_options() {
+    return &ceres_scan_matcher_options_;
+  }
   void set_sampling_ratio(double v) { sampling_ratio_ = v; }
   void set_max_constraint_distance(double v) { max_constraint_distance_ = v; }
   void set_min_score(double v) { min_score_ = v; }
@@ -570,6 +577,7 @@ class ConstraintBuilderOptions {
   bool log_matches_ = false;
   scan_matching::proto::FastCorrelativeScanMatcherOptions2D fast_correlative_scan_matcher_options_;
   scan_matching::proto::FastCorrelativeScanMatcherOptions3D fast_correlative_scan_matcher_options_3d_;
+  scan_matching::proto::CeresScanMatcherOptions2D ceres_scan_matcher_options_;
 };
 }  // namespace proto
 }  // namespace constraints

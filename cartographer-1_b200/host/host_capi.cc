@@ -270,6 +270,14 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
   o.mutable_fast_correlative_scan_matcher_options()->set_branch_and_bound_depth(depth);
   o.set_loop_closure_translation_weight(options8[6]);
   o.set_loop_closure_rotation_weight(options8[7]);
+  // options8[8..12]: ceres_scan_matcher_options (occupied_space_weight 0 = no refinement)
+  o.mutable_ceres_scan_matcher_options()->set_occupied_space_weight(options8[8]);
+  o.mutable_ceres_scan_matcher_options()->set_translation_weight(options8[9]);
+  o.mutable_ceres_scan_matcher_options()->set_rotation_weight(options8[10]);
+  o.mutable_ceres_scan_matcher_options()->mutable_ceres_solver_options()->set_use_nonmonotonic_steps(
+      options8[11] != 0.);
+  o.mutable_ceres_scan_matcher_options()->mutable_ceres_solver_options()->set_max_num_iterations(
+      static_cast<int>(options8[12]));
   std::vector<mapping::Submap2D> submaps;
   for (int i = 0; i < num_submaps; ++i) {
     submaps.emplace_back(

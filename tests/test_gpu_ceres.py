@@ -61,3 +61,42 @@ def test_batch_matches_oracle(csm, gpu_ctx, opts):
         assert summ[i][1] <= summ[i][0]
         same_iterations += int(summ[i][2]) == ws["iterations"]
     assert same_iterations >= len(clouds) - 2
+
+
+def _compose(a, b):
+    c, s = np.cos(a[2]), np.sin(a[2])
+    return np.array([a[0] + c * b[0] - s * b[1], a[1] + s * b[0] + c * b[1], a[2] + b[2]])
+
+
+def _inverse(a):
+    c, s = np.cos(a[2]), np.sin(a[2])
+    return np.array([-(c * a[0] + s * a[1]), -(-s * a[0] + c * a[1]), -a[2]])
+
+
+def test_constraint_builder_refines_found_poses(csm):
+    """ConstraintBuilder2D with ceres_scan_matcher_options set (constraint_builder_2d.cc:245-249):
+    every found constraint equals submap^-1 * CeresMatch(CSM pose) of the CPU restatement."""
+    from test_gpu_parity import _builder_case
+    worlds, poses, sub, full, rel, clouds = _builder_case(6)
+    ograds = [ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    grids = [csm.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    kw = dict(sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.45, global_min_score=0.5,
+              linear_window=3.0, angular_window=0.5, depth=5)
+    _, o_out, _ = ob.constraint_batch(4, ograds, poses, sub, full, rel, clouds, **kw)
+    _, found, tf, _ = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, ceres=POSE_GRAPH, **kw)
+    _, found0, tf0, _ = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, **kw)
+    assert found.sum() > 0 and np.array_equal(found, found0)
+    moved = 0
+    for i in range(len(clouds)):
+        assert found[i] == o_out[i].found
+        if not found[i]:
+            continue
+        s = sub[i]
+        csm_pose = _compose(poses[s], (o_out[i].pose_x, o_out[i].pose_y, o_out[i].pose_theta))
+        refined, _ = ob.ceres_match(ograds[s], POSE_GRAPH, csm_pose[:2], csm_pose, clouds[i])
+        want = _compose(_inverse(poses[s]), refined)
+        assert abs(tf[i][0] - want[0]) < 1e-6 and abs(tf[i][1] - want[1]) < 1e-6
+        d = (tf[i][2] - want[2] + np.pi) % (2 * np.pi) - np.pi
+        assert abs(d) < 1e-6
+        moved += np.hypot(tf[i][0] - tf0[i][0], tf[i][1] - tf0[i][1]) > 1e-4
+    assert moved > 0
