@@ -840,7 +840,10 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
   if (held > 0) flush();
 }
 
-// 5'b. bucket counters -> list offsets and work-item offsets of depth `slot`; one block.
+// 5'b. bucket counters -> list offsets and work-item offsets of depth `slot`; one block,
+//      kPrefixPer consecutive buckets per thread and pass (a C3 step has 126 k buckets:
+//      16 passes instead of 123 with one bucket per thread).
+constexpr int kPrefixPer = 8;
 __global__ void __launch_bounds__(1024)
 k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ bucket_start,
                 unsigned int* __restrict__ bucket_istart, unsigned int* __restrict__ counters,
@@ -851,21 +854,27 @@ k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict_
   if (threadIdx.x == 0) carry[0] = carry[1] = 0u;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (unsigned int b0 = 0; b0 < num_buckets; b0 += 1024) {
-    const unsigned int b = b0 + threadIdx.x;
-    unsigned int c = 0u;
-    if (b < num_buckets) {
-      c = bucket_cnt[b];
-      bucket_cnt[b] = 0u;  // ready for the next level
+  for (unsigned int b0 = 0; b0 < num_buckets; b0 += 1024 * kPrefixPer) {
+    const unsigned int first = b0 + threadIdx.x * kPrefixPer;
+    unsigned int c[kPrefixPer];
+    unsigned int tc = 0u, ti = 0u;  // this thread's totals
+#pragma unroll
+    for (int k = 0; k < kPrefixPer; ++k) {
+      c[k] = 0u;
+      if (first + k < num_buckets) {
+        c[k] = bucket_cnt[first + k];
+        bucket_cnt[first + k] = 0u;  // ready for the next level
+      }
+      tc += c[k];
+      ti += (c[k] + kWarp - 1) / kWarp;
     }
-    const unsigned int it = (c + kWarp - 1) / kWarp;
-    unsigned int pc = c, pi = it;
+    unsigned int pc = tc, pi = ti;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const unsigned int tc = __shfl_up_sync(kFull, pc, o), tI = __shfl_up_sync(kFull, pi, o);
+      const unsigned int uc = __shfl_up_sync(kFull, pc, o), ui = __shfl_up_sync(kFull, pi, o);
       if (lane >= o) {
-        pc += tc;
-        pi += tI;
+        pc += uc;
+        pi += ui;
       }
     }
     if (lane == 31) {
@@ -877,21 +886,26 @@ k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict_
       unsigned int a = wsum[0][lane], i2 = wsum[1][lane];
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int ta = __shfl_up_sync(kFull, a, o), ti = __shfl_up_sync(kFull, i2, o);
+        const unsigned int ta = __shfl_up_sync(kFull, a, o), tb = __shfl_up_sync(kFull, i2, o);
         if (lane >= o) {
           a += ta;
-          i2 += ti;
+          i2 += tb;
         }
       }
       wsum[0][lane] = a;
       wsum[1][lane] = i2;
     }
     __syncthreads();
-    const unsigned int base_c = carry[0] + (warp ? wsum[0][warp - 1] : 0u);
-    const unsigned int base_i = carry[1] + (warp ? wsum[1][warp - 1] : 0u);
-    if (b < num_buckets) {
-      bucket_start[b] = base_c + pc - c;
-      bucket_istart[b] = base_i + pi - it;
+    unsigned int at_c = carry[0] + (warp ? wsum[0][warp - 1] : 0u) + pc - tc;
+    unsigned int at_i = carry[1] + (warp ? wsum[1][warp - 1] : 0u) + pi - ti;
+#pragma unroll
+    for (int k = 0; k < kPrefixPer; ++k) {
+      if (first + k < num_buckets) {
+        bucket_start[first + k] = at_c;
+        bucket_istart[first + k] = at_i;
+      }
+      at_c += c[k];
+      at_i += (c[k] + kWarp - 1) / kWarp;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
