@@ -58,7 +58,8 @@ ABI_SYMBOLS = [
     "csm_stack3d_build", "csm_stack3d_level", "csm_stack3d_depth", "csm_stack3d_device_bytes",
     "csm_stack3d_destroy", "csm_grid3d_build", "csm_grid3d_destroy", "csm_match3d_batch",
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
-    "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch",
+    "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch", "csm_grid2d_create", "csm_grid2d_insert",
+    "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
 ]
 
 _abi = None
@@ -304,6 +305,50 @@ def rt_match_batch(ctx, grids, clouds, initial, linear_search_window=0.1,
     rc = host().csmh_rt_match_batch(ctx.h, n, handles, opts, init, xyz, offsets, out)
     assert rc == 0
     return out
+
+
+def grid_insert(ctx, grid, origins, returns, misses=None, hit_probability=0.55, miss_probability=0.49,
+                insert_free_space=True, resident=False):
+    """ProbabilityGridRangeDataInserter2D::Insert of every scan into `grid` (a Grid; it may grow).
+    Returns (cells [ny, nx] uint16, max_x, max_y) of the grid afterwards."""
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    L.csmh_grid_insert.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int,
+                                   f32p, f32p, i64p, f32p, i64p]
+    L.csmh_grid_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                 C.POINTER(C.c_double)]
+    L.csmh_grid_info.restype = None
+    L.csmh_grid_cells.argtypes = [C.c_void_p, u16p]
+    L.csmh_grid_cells.restype = None
+    n = len(origins)
+    misses = misses if misses is not None else [np.zeros((0, 3), np.float32)] * n
+
+    def pack(clouds):
+        off = np.zeros(n + 1, dtype=np.int64)
+        arrs = []
+        for i, c in enumerate(clouds):
+            a = np.asarray(c, np.float32).reshape(-1, 3)
+            arrs.append(a)
+            off[i + 1] = off[i] + len(a)
+        flat = np.concatenate(arrs, axis=0) if arrs else np.zeros((0, 3), np.float32)
+        if len(flat) == 0:
+            flat = np.zeros((1, 3), np.float32)
+        return np.ascontiguousarray(flat, dtype=np.float32), off
+
+    r, roff = pack(returns)
+    m, moff = pack(misses)
+    rc = L.csmh_grid_insert(ctx.h, grid.h, hit_probability, miss_probability, 1 if insert_free_space else 0,
+                            1 if resident else 0, n,
+                            np.ascontiguousarray(np.asarray(origins, np.float32)[:, :2]).reshape(-1), r, roff, m, moff)
+    assert rc == 0
+    nx, ny = C.c_int(), C.c_int()
+    mx, my = C.c_double(), C.c_double()
+    L.csmh_grid_info(grid.h, C.byref(nx), C.byref(ny), C.byref(mx), C.byref(my))
+    cells = np.empty((ny.value, nx.value), dtype=np.uint16)
+    L.csmh_grid_cells(grid.h, cells)
+    return cells, mx.value, my.value
 
 
 def ceres_match_batch(ctx, grids, clouds, targets, initial, occupied_space_weight=1.0,

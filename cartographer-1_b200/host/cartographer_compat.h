@@ -171,6 +171,12 @@ class PointCloud {
  private:
   std::vector<RangefinderPoint> points_;
 };
+// sensor/range_data.h:32-36
+struct RangeData {
+  Vector3f origin;
+  PointCloud returns;
+  PointCloud misses;
+};
 }  // namespace sensor
 
 namespace mapping {
@@ -204,6 +210,17 @@ constexpr float kMinProbability = 0.1f;
 constexpr float kMaxProbability = 1.f - kMinProbability;
 constexpr float kMinCorrespondenceCost = 1.f - kMaxProbability;
 constexpr float kMaxCorrespondenceCost = 1.f - kMinProbability;
+
+// probability_values.h:32-46, :85-88, :32-41 of the .cc (fp32, as the reference)
+inline uint16 BoundedFloatToValue(const float value, const float lower_bound, const float upper_bound) {
+  const float clamped = std::min(std::max(value, lower_bound), upper_bound);
+  return static_cast<uint16>(std::lround((clamped - lower_bound) * (32766.f / (upper_bound - lower_bound))) + 1);
+}
+inline uint16 CorrespondenceCostToValue(const float correspondence_cost) {
+  return BoundedFloatToValue(correspondence_cost, kMinCorrespondenceCost, kMaxCorrespondenceCost);
+}
+inline float Odds(float probability) { return probability / (1.f - probability); }
+inline float ProbabilityFromOdds(const float odds) { return odds / (odds + 1.f); }
 
 // value_conversion_tables.cc:29-67
 class ValueConversionTables {
@@ -252,6 +269,30 @@ class Grid2D {
   std::vector<uint16>* mutable_correspondence_cost_cells() { return &correspondence_cost_cells_; }
   const std::vector<float>& value_to_correspondence_cost_table() const {
     return *value_to_correspondence_cost_table_;
+  }
+  // grid_2d.cc:131-166: doubles the grid around its centre until it contains `point`.
+  virtual void GrowLimits(const float px, const float py) {
+    auto contains = [this](const float x, const float y) {
+      const long cx = std::lround((limits_.max().y() - y) / limits_.resolution() - 0.5);
+      const long cy = std::lround((limits_.max().x() - x) / limits_.resolution() - 0.5);
+      return cx >= 0 && cy >= 0 && cx < limits_.cell_limits().num_x_cells &&
+             cy < limits_.cell_limits().num_y_cells;
+    };
+    while (!contains(px, py)) {
+      const int nx = limits_.cell_limits().num_x_cells, ny = limits_.cell_limits().num_y_cells;
+      const int x_offset = nx / 2, y_offset = ny / 2;
+      const MapLimits grown(limits_.resolution(),
+                            transform::Vector2d(limits_.max().x() + limits_.resolution() * y_offset,
+                                                limits_.max().y() + limits_.resolution() * x_offset),
+                            CellLimits(2 * nx, 2 * ny));
+      const int stride = 2 * nx;
+      std::vector<uint16> cells(static_cast<size_t>(4) * nx * ny, 0);
+      for (int i = 0; i < ny; ++i)
+        for (int j = 0; j < nx; ++j)
+          cells[x_offset + stride * y_offset + j + i * stride] = correspondence_cost_cells_[j + i * nx];
+      correspondence_cost_cells_.swap(cells);
+      limits_ = grown;
+    }
   }
 
  private:
@@ -332,6 +373,23 @@ class TSDF2D : public Grid2D {
   TSDValueConverter value_converter_;
   std::vector<uint16> weight_cells_;
 };
+
+namespace proto {
+// mapping/proto/2d/probability_grid_range_data_inserter_options_2d.proto (fields 1-3)
+class ProbabilityGridRangeDataInserterOptions2D {
+ public:
+  double hit_probability() const { return hit_probability_; }
+  double miss_probability() const { return miss_probability_; }
+  bool insert_free_space() const { return insert_free_space_; }
+  void set_hit_probability(double v) { hit_probability_ = v; }
+  void set_miss_probability(double v) { miss_probability_ = v; }
+  void set_insert_free_space(bool v) { insert_free_space_ = v; }
+
+ private:
+  double hit_probability_ = 0., miss_probability_ = 0.;
+  bool insert_free_space_ = false;
+};
+}  // namespace proto
 
 // mapping/id.h:42-95
 struct NodeId {

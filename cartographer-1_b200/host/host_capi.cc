@@ -9,6 +9,7 @@
 #include <mutex>
 
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/2d/probability_grid_range_data_inserter_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/constraints/constraint_builder_2d.h"
@@ -159,6 +160,56 @@ int csmh_matcher_rebuild_dev(void* ctx, void* m, const uint16_t* cells_dev) {
   return csm_stack2d_rebuild_dev(
       static_cast<DeviceContext*>(ctx)->get(),
       const_cast<csm_stack2d*>(static_cast<FastCorrelativeScanMatcher2D*>(m)->stack()), cells_dev);
+}
+
+// ProbabilityGridRangeDataInserter2D over a grid holder.  The scans (origin_xy[2i..],
+// returns / misses given by offsets in points) are inserted one after the other.
+// resident = 0: the reference-signature Insert per scan (the grid grows as needed);
+// resident = 1: the grid is grown for all scans first, uploaded once, every scan inserted on
+// the device, and downloaded once.  Query the (possibly grown) grid with csmh_grid_info /
+// csmh_grid_cells.
+int csmh_grid_insert(void* ctx, void* grid, double hit_probability, double miss_probability,
+                     int insert_free_space, int resident, int num_scans, const float* origin_xy,
+                     const float* returns_xyz, const int64_t* return_offsets, const float* misses_xyz,
+                     const int64_t* miss_offsets) {
+  mapping::proto::ProbabilityGridRangeDataInserterOptions2D o;
+  o.set_hit_probability(hit_probability);
+  o.set_miss_probability(miss_probability);
+  o.set_insert_free_space(insert_free_space != 0);
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  const mapping::ProbabilityGridRangeDataInserter2D inserter(o, context);
+  mapping::Grid2D* g = static_cast<GridHolder*>(grid)->grid.get();
+  std::vector<sensor::RangeData> scans(num_scans);
+  for (int i = 0; i < num_scans; ++i) {
+    scans[i].origin = sensor::Vector3f(origin_xy[2 * i], origin_xy[2 * i + 1], 0.f);
+    for (int64_t p = return_offsets[i]; p < return_offsets[i + 1]; ++p)
+      scans[i].returns.push_back({sensor::Vector3f(returns_xyz[3 * p], returns_xyz[3 * p + 1], returns_xyz[3 * p + 2])});
+    for (int64_t p = miss_offsets[i]; p < miss_offsets[i + 1]; ++p)
+      scans[i].misses.push_back({sensor::Vector3f(misses_xyz[3 * p], misses_xyz[3 * p + 1], misses_xyz[3 * p + 2])});
+  }
+  if (!resident) {
+    for (const sensor::RangeData& rd : scans) inserter.Insert(rd, g);
+    return 0;
+  }
+  for (const sensor::RangeData& rd : scans)  // GrowAsNeeded of every scan, up front
+    mapping::ProbabilityGridRangeDataInserter2D::GrowAsNeeded(rd, g);
+  mapping::ProbabilityGridRangeDataInserter2D::DeviceGrid device_grid(context, *g);
+  std::vector<const sensor::RangeData*> ptrs;
+  for (const sensor::RangeData& rd : scans) ptrs.push_back(&rd);
+  inserter.Insert(ptrs, &device_grid);
+  device_grid.Download(g);
+  return 0;
+}
+void csmh_grid_info(void* grid, int* nx, int* ny, double* max_x, double* max_y) {
+  const mapping::MapLimits& l = static_cast<GridHolder*>(grid)->grid->limits();
+  *nx = l.cell_limits().num_x_cells;
+  *ny = l.cell_limits().num_y_cells;
+  *max_x = l.max().x();
+  *max_y = l.max().y();
+}
+void csmh_grid_cells(void* grid, uint16_t* out) {
+  const std::vector<uint16_t>& c = static_cast<GridHolder*>(grid)->grid->correspondence_cost_cells();
+  std::memcpy(out, c.data(), sizeof(uint16_t) * c.size());
 }
 
 // CeresScanMatcher2D::MatchBatch.  options5 = occupied_space_weight, translation_weight,

@@ -238,6 +238,36 @@ typedef struct {
 int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs, int num_jobs,
                             csm_ceres_result2d* results);
 
+/* ---- ProbabilityGridRangeDataInserter2D::Insert on a device-resident grid
+ * Replaces cartographer/mapping/2d/probability_grid_range_data_inserter_2d.cc:47-100 (CastRays)
+ * with mapping/internal/2d/ray_to_pixel_mask.cc:25-170 and Grid2D::FinishUpdate
+ * (mapping/2d/grid_2d.cc:98-106).  GrowLimits (:30-45, grid_2d.cc:131-166) is the caller's:
+ * the grid handle has a fixed size and every ray must lie inside it.  A csm_grid2d keeps the
+ * uint16 cells of a live submap in HBM: scans are inserted as they arrive and the finished
+ * submap's stack is built from csm_grid2d_cells_dev() with csm_stack2d_build_dev -- the cells
+ * never cross PCIe.  Cells are bit-identical to the reference's after every insertion. */
+typedef struct csm_grid2d csm_grid2d;
+typedef struct {
+  double max_x, max_y, resolution;  /* MapLimits of the grid                              */
+  float origin_x, origin_y;         /* range_data.origin                                  */
+  const float* returns_xy;          /* num_returns x (x, y)                               */
+  int32_t num_returns;
+  int32_t num_misses;
+  const float* misses_xy;           /* num_misses x (x, y)                                */
+  const uint16_t* hit_table;        /* ComputeLookupTableToApplyCorrespondenceCostOdds    */
+  const uint16_t* miss_table;       /* (probability_values.cc:89-105), 32768 entries each */
+  int32_t insert_free_space;
+  int32_t pad;
+} csm_range_data2d;
+
+/* cells may be NULL: every cell unknown (0). */
+int csm_grid2d_create(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y, csm_grid2d** out);
+/* Inserts the scans one after the other (each is one reference Insert + FinishUpdate). */
+int csm_grid2d_insert(csm_ctx* ctx, csm_grid2d* grid, const csm_range_data2d* scans, int num_scans);
+int csm_grid2d_download(csm_ctx* ctx, const csm_grid2d* grid, uint16_t* cells_out);
+const uint16_t* csm_grid2d_cells_dev(const csm_grid2d* grid);
+void csm_grid2d_destroy(csm_ctx* ctx, csm_grid2d* grid);
+
 /* ==== 3D path ======================================================================
  * Citations relative to cartographer/mapping/internal/3d/scan_matching/:
  *   FCSM3D = fast_correlative_scan_matcher_3d.{h,cc}

@@ -172,6 +172,38 @@ double oracle_rt_match2d(void* grid, double linear_window, double angular_window
   return score;
 }
 
+// --- ProbabilityGridRangeDataInserter2D -----------------------
+// Inserts one range data into the grid handle (GrowLimits included, so the grid may
+// change size: query it with oracle_grid2d_info / oracle_grid2d_cells afterwards).
+void oracle_grid2d_insert(void* grid, double hit_probability, double miss_probability,
+                          int insert_free_space, const float* origin_xy, const float* returns_xyz,
+                          int num_returns, const float* misses_xyz, int num_misses) {
+  RangeData rd;
+  rd.origin = Vec3f{origin_xy[0], origin_xy[1], 0.f};
+  rd.returns = ToCloud(returns_xyz, num_returns);
+  rd.misses = ToCloud(misses_xyz, num_misses);
+  ProbabilityGridRangeDataInserter2D(hit_probability, miss_probability, insert_free_space != 0)
+      .Insert(rd, static_cast<ProbabilityGrid*>(grid));
+}
+void oracle_grid2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
+  const MapLimits& l = static_cast<ProbabilityGrid*>(grid)->limits();
+  *nx = l.cell_limits.num_x_cells;
+  *ny = l.cell_limits.num_y_cells;
+  *max_x = l.max_x;
+  *max_y = l.max_y;
+  *res = l.resolution;
+}
+void oracle_grid2d_cells(void* grid, uint16_t* out) {
+  const std::vector<uint16_t>& c = static_cast<ProbabilityGrid*>(grid)->cells();
+  std::memcpy(out, c.data(), sizeof(uint16_t) * c.size());
+}
+// ComputeLookupTableToApplyCorrespondenceCostOdds(Odds(p)), 32768 entries.
+void oracle_apply_odds_table(double probability, uint16_t* out32768) {
+  const std::vector<uint16_t> t =
+      ComputeLookupTableToApplyCorrespondenceCostOdds(Odds(static_cast<float>(probability)));
+  std::memcpy(out32768, t.data(), sizeof(uint16_t) * t.size());
+}
+
 // --- TSDF grid + real-time matcher on it ----------------------------------------
 void* oracle_tsdf2d_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, int nx, int ny,
                            double res, double max_x, double max_y, float truncation_distance,

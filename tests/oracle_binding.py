@@ -90,6 +90,16 @@ def lib():
                                     C.c_double, C.c_double, C.c_double, f32p, C.c_int,
                                     C.POINTER(OracleResult2D)]
     L.oracle_rt_match2d.restype = C.c_double
+    L.oracle_grid2d_insert.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int, f32p, f32p, C.c_int,
+                                       f32p, C.c_int]
+    L.oracle_grid2d_insert.restype = None
+    L.oracle_grid2d_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.oracle_grid2d_info.restype = None
+    L.oracle_grid2d_cells.argtypes = [C.c_void_p, u16p]
+    L.oracle_grid2d_cells.restype = None
+    L.oracle_apply_odds_table.argtypes = [C.c_double, u16p]
+    L.oracle_apply_odds_table.restype = None
     L.oracle_ceres_match2d.argtypes = [C.c_void_p, f64p, f64p, f64p, f32p, C.c_int, f64p, f64p]
     L.oracle_ceres_match2d.restype = None
     L.oracle_ceres_evaluate2d.argtypes = [C.c_void_p, f64p, f64p, C.c_double, f64p, f32p, C.c_int,
@@ -144,6 +154,34 @@ class OracleGrid:
         if getattr(self, "h", None):
             lib().oracle_grid2d_destroy(self.h)
             self.h = None
+
+
+def _xyz(points):
+    a = np.asarray(points, dtype=np.float32).reshape(-1, 3) if len(points) else np.zeros((0, 3), np.float32)
+    return np.ascontiguousarray(a)
+
+
+def grid_insert(grid, origin, returns, misses=(), hit_probability=0.55, miss_probability=0.49,
+                insert_free_space=True):
+    """ProbabilityGridRangeDataInserter2D::Insert on an OracleGrid (it may grow); refreshes
+    grid.cells / nx / ny / max_x / max_y."""
+    r, m = _xyz(returns), _xyz(misses)
+    lib().oracle_grid2d_insert(grid.h, hit_probability, miss_probability, 1 if insert_free_space else 0,
+                               np.asarray(origin, np.float32)[:2].copy(), r, len(r), m, len(m))
+    nx, ny = C.c_int(), C.c_int()
+    mx, my, res = C.c_double(), C.c_double(), C.c_double()
+    lib().oracle_grid2d_info(grid.h, C.byref(nx), C.byref(ny), C.byref(mx), C.byref(my), C.byref(res))
+    grid.nx, grid.ny, grid.max_x, grid.max_y = nx.value, ny.value, mx.value, my.value
+    cells = np.empty((grid.ny, grid.nx), dtype=np.uint16)
+    lib().oracle_grid2d_cells(grid.h, cells)
+    grid.cells = cells
+    return grid
+
+
+def apply_odds_table(probability):
+    t = np.empty(32768, dtype=np.uint16)
+    lib().oracle_apply_odds_table(probability, t)
+    return t
 
 
 class OracleTsdf:
