@@ -109,23 +109,24 @@ __device__ __forceinline__ Children score_children(const JobDev& j, const int2* 
   int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
   uint32_t lo = 0, hi = 0;
   int since = 0;
-  // Four points per lane and pass: the four dependent load pairs (cell, then quad word) are
-  // issued together, so a single-path visit waits for one L2 round trip per pass instead of
-  // four (these visits are latency-bound: one warp follows one path).
-  for (int p0 = lane; p0 < j.n; p0 += 4 * kWarp) {
-    int2 c[4];
+  // kPathPts points per lane and pass: the dependent load pairs (cell, then quad word) of a
+  // pass are issued together, so a single-path visit waits for one L2 round trip per pass
+  // instead of one per point (these visits are latency-bound: one warp follows one path).
+  constexpr int kPathPts = 4;  // 8 was slower (phase 2 3.9 vs 2.9 ms: registers)
+  for (int p0 = lane; p0 < j.n; p0 += kPathPts * kWarp) {
+    int2 c[kPathPts];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) c[k] = p0 + k * kWarp < j.n ? pts[p0 + k * kWarp] : make_int2(0, 0);
-    uint32_t w[4];
+    for (int k = 0; k < kPathPts; ++k) c[k] = p0 + k * kWarp < j.n ? pts[p0 + k * kWarp] : make_int2(0, 0);
+    uint32_t w[kPathPts];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < kPathPts; ++k)
       w[k] = p0 + k * kWarp < j.n ? quad_at(sd, lvl, c[k].x + x, c[k].y + y) : 0u;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < kPathPts; ++k) {
       lo += w[k] & 0x00FF00FFu;
       hi += (w[k] >> 8) & 0x00FF00FFu;
     }
-    since += 4;
+    since += kPathPts;
     if (since >= 252) {  // flush before a 16-bit field can overflow (255 * 256 < 65536)
       s0 += lo & 0xFFFF; s2 += lo >> 16; s1 += hi & 0xFFFF; s3 += hi >> 16;
       lo = hi = 0;

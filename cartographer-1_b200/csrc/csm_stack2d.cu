@@ -401,6 +401,9 @@ __device__ __forceinline__ int skew(int w) { return w + (w >> 5); }
 __global__ void __launch_bounds__(kThreads)
 k_stack_rows(const RowsArgs a) {
   extern __shared__ uint32_t rows32[];
+  // Programmatic dependent launch: this grid may be scheduled while the kernel that makes
+  // level i is still draining; nothing of level i is read before the dependency resolves.
+  cudaGridDependencySynchronize();
   const int s = 1 << a.log2s, two_s = 2 << a.log2s, sh = a.log2s + 1;
   const int v = blockIdx.x;  // window-end row Y of level i == row of level i + 1
   const int nthr = blockDim.x;  // sized by the launcher so that a row's words fill whole passes
@@ -531,7 +534,20 @@ int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     // the block to the warps that fill it.
     const int passes = (nw + kThreads - 1) / kThreads;
     const int threads = std::min(kThreads, (((nw + passes - 1) / passes) + 31) & ~31);
-    ++ctx->launches, k_stack_rows<<<a.jn << (i + 1), threads, smem, ctx->stream>>>(a);
+    // Launched with programmatic stream serialization: the launch latency of level i + 1
+    // overlaps the tail of level i (the kernel waits in cudaGridDependencySynchronize).
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.jn << (i + 1));
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ++ctx->launches;
+    CSM_CUDA(cudaLaunchKernelEx(&cfg, k_stack_rows, a));
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
