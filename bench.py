@@ -375,21 +375,28 @@ def run_b200(args):
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": {"k_expand": "k_expand_nodes"}.get(names[dom], names[dom]),
+                     "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic.get(names[dom]),
                      "peak_source": peak_src,
                      "launch_ms": phase_ms[dom] / launches_of_dom,
                      "algorithmic_bytes_per_launch": dom_bytes / launches_of_dom,
                      "note": "algorithmic bytes = 1 B per (candidate, point) lookup; the stack is "
-                             "L2-resident, so the HBM peak is a loose bound and the L2 gather "
-                             "rate below is the one that binds (DESIGN.md)"},
+                             "L2-resident (97-99 % L2 hits, traffic = DRAM bytes of the largest "
+                             "launch), so the HBM peak is a loose bound: the unit that saturates "
+                             "is the L1 data pipe, 85-88 % of its peak under ncu "
+                             "(profiles/r01_v8_summary.md, DESIGN.md section 3)"},
         "gather_roofline": {"g_l2_lookups_per_s": g_l2.value,
                             "achieved_lookups_per_s": lookups_per_step / (search_ms * 1e-3),
                             "frac": lookups_per_step / (search_ms * 1e-3) / g_l2.value,
                             "searches_per_s_at_g_l2": g_l2.value / (lookups_per_step / n_search),
                             "how": "csm_measure_gather_rate: %d-byte table, %d-point scan, 2^21 "
-                                   "candidates x 3" % (stack_bytes, len(pts_xy))},
+                                   "candidates x 3" % (stack_bytes, len(pts_xy)),
+                            "note": "G_L2 is the rate of the reference's naive pattern (one byte per "
+                                    "candidate and point, SURVEY 8(d)); the quad-phase layout serves 4 "
+                                    "lookups per 4-byte load from neighbouring words, so frac > 1 is a "
+                                    "speed-up over that pattern, not a fraction of a ceiling"},
         "phase_ms_per_step": {n: phase_ms[i] / args.steps for i, n in enumerate(names)},
         "phase_candidates_per_step": {n: phase_scored[i] / args.steps for i, n in enumerate(names)},
         "stack_build": {"ms_per_step": build, "submaps": len(matchers),
