@@ -625,6 +625,7 @@ constexpr int kCntTmp = 48;      // + depth: scratch list fill
 constexpr int kCntBlocks = 64;   // + depth: blocks appended
 constexpr int kCntItems = 80;    // + depth: 32-node work items
 constexpr int kCntCursor = 96;   // + depth: next work item to hand out (k_expand_nodes)
+constexpr int kCntDfsCursor = 96;  // depth 0 is never swept: next contender (k_ordered_dfs)
 constexpr int kNodeBlocksPerSm = 4;  // resident k_expand_nodes blocks per SM (register bound)
 constexpr int kStagePoints = 128;
 
@@ -1137,12 +1138,16 @@ k_collect(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans,
 __global__ void __launch_bounds__(128)
 k_ordered_dfs(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
               const ScanInfo* __restrict__ scans, JobState* __restrict__ state,
-              Contender* __restrict__ list, const unsigned int* __restrict__ counters,
+              Contender* __restrict__ list, unsigned int* __restrict__ counters,
               unsigned int cap) {
   const unsigned int count = min(counters[kCntContenders], cap);
   const int lane = threadIdx.x & 31;
-  const unsigned int warps = gridDim.x * (blockDim.x >> 5);
-  for (unsigned int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < count; i += warps) {
+  // Contenders are handed out through a cursor: most die after one visit, a few walk deep.
+  for (;;) {
+    unsigned int i = 0u;
+    if (lane == 0) i = atomicAdd(&counters[kCntDfsCursor], 1u);
+    i = __shfl_sync(kFull, i, 0);
+    if (i >= count) break;
     Contender ct = list[i];
     const JobDev& j = jobs[ct.job];
     const ScanInfo si = scans[j.scan_off + ct.scan];
