@@ -17,6 +17,8 @@
 // pass over the grid applies the tables, drops the marker and clears the flags.  Integer
 // work end to end: cells are bit-identical to the reference's.
 #include <algorithm>
+#include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "csm_internal.cuh"
@@ -122,12 +124,13 @@ k_insert_mark(const InsertArgs a, const float* __restrict__ ends_xy, uint32_t* _
 }
 
 // cell = table[cell] - kUpdateMarker for every flagged cell (ApplyLookupTable + FinishUpdate);
-// flags are cleared for the next insertion.  4 cells per thread.
+// flags are cleared for the next insertion.  4 cells per thread, over the flag words
+// [word0, word1) of the rows the scan can have touched.
 __global__ void __launch_bounds__(256)
 k_insert_apply(uint16_t* __restrict__ cells, uint32_t* __restrict__ flags,
-               const uint16_t* __restrict__ tables, size_t num_cells) {
-  const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (4 * w >= num_cells) return;
+               const uint16_t* __restrict__ tables, size_t num_cells, size_t word0, size_t word1) {
+  const size_t w = word0 + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (w >= word1 || 4 * w >= num_cells) return;
   const uint32_t f = flags[w];
   if (f == 0u) return;
   flags[w] = 0u;
@@ -209,37 +212,54 @@ int csm_grid2d_insert(csm_ctx* ctx, csm_grid2d* g, const csm_range_data2d* scans
   CSM_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   const size_t n = static_cast<size_t>(g->num_x) * g->num_y;
-  const uint16_t* loaded_hit = nullptr;
-  const uint16_t* loaded_miss = nullptr;
+  size_t total_rays = 0;
   for (int s = 0; s < num_scans; ++s) {
     const csm_range_data2d& in = scans[s];
     CSM_REQUIRE(in.hit_table != nullptr && in.miss_table != nullptr, "lookup tables must not be NULL");
     CSM_REQUIRE(in.num_returns >= 0 && in.num_misses >= 0 && in.resolution > 0., "range data sizes");
     CSM_REQUIRE((in.num_returns == 0 || in.returns_xy) && (in.num_misses == 0 || in.misses_xy),
                 "range data arrays must not be NULL");
+    total_rays += static_cast<size_t>(in.num_returns) + in.num_misses;
+  }
+  if (total_rays == 0) return CSM_OK;
+  // The end points of every scan go up in ONE copy from pinned memory; the kernels of the
+  // scans then run back to back on the stream (scan s + 1 must see the cells scan s left).
+  if (g->points_cap < total_rays) {
+    CSM_CUDA(cudaStreamSynchronize(st));
+    cudaFree(g->points);
+    g->points = nullptr;
+    g->points_cap = 0;
+    CSM_CUDA(cudaMalloc(&g->points, sizeof(float) * 2 * (total_rays + 4096)));
+    g->points_cap = total_rays + 4096;
+  }
+  int rc = ctx->pin0.reserve(sizeof(float) * 2 * total_rays);
+  if (rc != CSM_OK) return rc;
+  float* pin = ctx->pin0.as<float>();
+  {
+    size_t at = 0;
+    for (int s = 0; s < num_scans; ++s) {
+      const csm_range_data2d& in = scans[s];
+      if (in.num_returns) memcpy(pin + 2 * at, in.returns_xy, sizeof(float) * 2 * in.num_returns);
+      at += in.num_returns;
+      if (in.num_misses) memcpy(pin + 2 * at, in.misses_xy, sizeof(float) * 2 * in.num_misses);
+      at += in.num_misses;
+    }
+  }
+  CSM_CUDA(cudaMemcpyAsync(g->points, pin, sizeof(float) * 2 * total_rays, cudaMemcpyHostToDevice, st));
+  const uint16_t* loaded_hit = nullptr;
+  const uint16_t* loaded_miss = nullptr;
+  size_t at = 0;
+  for (int s = 0; s < num_scans; ++s) {
+    const csm_range_data2d& in = scans[s];
     const int rays = in.num_returns + in.num_misses;
     if (rays == 0) continue;
-    if (in.hit_table != loaded_hit || in.miss_table != loaded_miss) {  // pageable copies are synchronous
+    if (in.hit_table != loaded_hit || in.miss_table != loaded_miss) {  // pageable: synchronous copies
       CSM_CUDA(cudaMemcpyAsync(g->tables, in.hit_table, sizeof(uint16_t) * 32768, cudaMemcpyHostToDevice, st));
       CSM_CUDA(cudaMemcpyAsync(g->tables + 32768, in.miss_table, sizeof(uint16_t) * 32768,
                                cudaMemcpyHostToDevice, st));
       loaded_hit = in.hit_table;
       loaded_miss = in.miss_table;
     }
-    if (g->points_cap < static_cast<size_t>(rays)) {
-      CSM_CUDA(cudaStreamSynchronize(st));
-      cudaFree(g->points);
-      g->points = nullptr;
-      g->points_cap = 0;
-      CSM_CUDA(cudaMalloc(&g->points, sizeof(float) * 2 * (static_cast<size_t>(rays) + 1024)));
-      g->points_cap = static_cast<size_t>(rays) + 1024;
-    }
-    if (in.num_returns)
-      CSM_CUDA(cudaMemcpyAsync(g->points, in.returns_xy, sizeof(float) * 2 * in.num_returns,
-                               cudaMemcpyHostToDevice, st));
-    if (in.num_misses)
-      CSM_CUDA(cudaMemcpyAsync(g->points + 2 * static_cast<size_t>(in.num_returns), in.misses_xy,
-                               sizeof(float) * 2 * in.num_misses, cudaMemcpyHostToDevice, st));
     InsertArgs a;
     a.max_x = in.max_x;
     a.max_y = in.max_y;
@@ -251,10 +271,26 @@ int csm_grid2d_insert(csm_ctx* ctx, csm_grid2d* g, const csm_range_data2d* scans
     a.num_returns = in.num_returns;
     a.num_rays = rays;
     a.insert_free_space = in.insert_free_space;
-    ++ctx->launches, k_insert_mark<<<(rays + 127) / 128, 128, 0, st>>>(a, g->points, g->flags);
-    const size_t words = (n + 3) / 4;
-    ++ctx->launches, k_insert_apply<<<static_cast<unsigned int>((words + 255) / 256), 256, 0, st>>>(
-        g->cells, g->flags, g->tables, n);
+    // Rows the rays can touch: between the rows of the origin and of every end point (the
+    // cell row comes from the world x, map_limits.h:69-76), one row of margin.
+    double lo_x = in.origin_x, hi_x = in.origin_x;
+    const float* ends = pin + 2 * at;
+    for (int r = 0; r < rays; ++r) {
+      lo_x = std::min<double>(lo_x, ends[2 * r]);
+      hi_x = std::max<double>(hi_x, ends[2 * r]);
+    }
+    long long row0 = static_cast<long long>(std::floor((in.max_x - hi_x) / in.resolution)) - 2;
+    long long row1 = static_cast<long long>(std::floor((in.max_x - lo_x) / in.resolution)) + 2;
+    row0 = std::max<long long>(row0, 0);
+    row1 = std::min<long long>(row1, g->num_y - 1);
+    ++ctx->launches, k_insert_mark<<<(rays + 127) / 128, 128, 0, st>>>(a, g->points + 2 * at, g->flags);
+    if (row1 >= row0) {
+      const size_t w0 = static_cast<size_t>(row0) * g->num_x / 4;
+      const size_t w1 = (static_cast<size_t>(row1 + 1) * g->num_x + 3) / 4;  // exclusive
+      ++ctx->launches, k_insert_apply<<<static_cast<unsigned int>((w1 - w0 + 255) / 256), 256, 0, st>>>(
+          g->cells, g->flags, g->tables, n, w0, w1);
+    }
+    at += rays;
   }
   CSM_CUDA(cudaGetLastError());
   CSM_CUDA(cudaStreamSynchronize(st));
