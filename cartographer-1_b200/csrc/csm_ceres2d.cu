@@ -35,6 +35,9 @@ constexpr int kCeresWarps = 4;
 struct CeresJobDev {
   const uint16_t* cells;
   const float* cost_table;
+  const uint16_t* weight_cells;  // TSDF only (nullptr: probability grid)
+  const float* weight_table;
+  float max_cc;                  // TSDF: truncation distance
   long long pts_off;
   int num_x, num_y, n;
   double max_x, max_y, res;
@@ -145,6 +148,149 @@ __device__ void evaluate(const CeresJobDev& j, const float* __restrict__ pts, co
   *out = s;
 }
 
+// ---- TSDF2D: interpolated_tsdf_2d.h:35-131, tsdf_match_cost_function_2d.cc:28-75 ----------
+// MapLimits::GetCellIndex (map_limits.h:69-76), lround.
+__device__ __forceinline__ int2 cell_of(const CeresJobDev& j, float px, float py) {
+  int2 c;
+  c.x = static_cast<int>(llround(__dsub_rn(__ddiv_rn(__dsub_rn(j.max_y, static_cast<double>(py)), j.res), 0.5)));
+  c.y = static_cast<int>(llround(__dsub_rn(__ddiv_rn(__dsub_rn(j.max_x, static_cast<double>(px)), j.res), 0.5)));
+  return c;
+}
+__device__ __forceinline__ float tsdf_weight(const CeresJobDev& j, int x, int y) {
+  if (static_cast<unsigned>(x) >= static_cast<unsigned>(j.num_x) ||
+      static_cast<unsigned>(y) >= static_cast<unsigned>(j.num_y))
+    return 0.f;
+  return __ldg(j.weight_table + __ldg(j.weight_cells + static_cast<size_t>(y) * j.num_x + x));
+}
+__device__ __forceinline__ float tsdf_cost(const CeresJobDev& j, int x, int y) {
+  if (static_cast<unsigned>(x) >= static_cast<unsigned>(j.num_x) ||
+      static_cast<unsigned>(y) >= static_cast<unsigned>(j.num_y))
+    return j.max_cc;
+  const uint16_t v = __ldg(j.cells + static_cast<size_t>(y) * j.num_x + x);
+  return (v & 0x7FFF) == 0 ? j.max_cc : __ldg(j.cost_table + v);  // unknown reads +truncation (grid_2d.h:53-57)
+}
+__device__ __forceinline__ void bilinear(float x1, float y1, float x2, float y2, double x, double y, float q11,
+                                         float q12, float q21, float q22, double* f, double* dfdx,
+                                         double* dfdy) {
+  const double wx = static_cast<double>(__fsub_rn(x2, x1)), wy = static_cast<double>(__fsub_rn(y2, y1));
+  const double nx = __ddiv_rn(__dsub_rn(x, static_cast<double>(x1)), wx);
+  const double ny = __ddiv_rn(__dsub_rn(y, static_cast<double>(y1)), wy);
+  const double d1 = static_cast<double>(__fsub_rn(q12, q11)), d2 = static_cast<double>(__fsub_rn(q22, q21));
+  const double q1 = __dadd_rn(__dmul_rn(d1, ny), static_cast<double>(q11));
+  const double q2 = __dadd_rn(__dmul_rn(d2, ny), static_cast<double>(q21));
+  *f = __dadd_rn(__dmul_rn(__dsub_rn(q2, q1), nx), q1);
+  *dfdx = (q2 - q1) / wx;
+  *dfdy = ((d2 - d1) * nx + d1) / wy;
+}
+// Cost and weight at the world point (x, y) with their partials.
+__device__ void tsdf_sample(const CeresJobDev& j, double x, double y, double* c, double* dcdx, double* dcdy,
+                            double* w, double* dwdx, double* dwdy) {
+  const int2 cell = cell_of(j, static_cast<float>(x), static_cast<float>(y));
+  // GetCellCenter (map_limits.h:79-82) narrowed to float, then the next lower pixel centre
+  float cx = static_cast<float>(__dsub_rn(j.max_x, __dmul_rn(j.res, cell.y + 0.5)));
+  float cy = static_cast<float>(__dsub_rn(j.max_y, __dmul_rn(j.res, cell.x + 0.5)));
+  if (static_cast<double>(cx) > x) cx = static_cast<float>(__dsub_rn(static_cast<double>(cx), j.res));
+  if (static_cast<double>(cy) > y) cy = static_cast<float>(__dsub_rn(static_cast<double>(cy), j.res));
+  const float x2 = __fadd_rn(cx, static_cast<float>(j.res)), y2 = __fadd_rn(cy, static_cast<float>(j.res));
+  const int2 i1 = cell_of(j, cx, cy);
+  const float w11 = tsdf_weight(j, i1.x, i1.y), w12 = tsdf_weight(j, i1.x - 1, i1.y);
+  const float w21 = tsdf_weight(j, i1.x, i1.y - 1), w22 = tsdf_weight(j, i1.x - 1, i1.y - 1);
+  if (w11 == 0.f || w12 == 0.f || w21 == 0.f || w22 == 0.f) {
+    *c = static_cast<double>(j.max_cc);
+    *dcdx = *dcdy = 0.;
+  } else {
+    bilinear(cx, cy, x2, y2, x, y, tsdf_cost(j, i1.x, i1.y), tsdf_cost(j, i1.x - 1, i1.y),
+             tsdf_cost(j, i1.x, i1.y - 1), tsdf_cost(j, i1.x - 1, i1.y - 1), c, dcdx, dcdy);
+  }
+  bilinear(cx, cy, x2, y2, x, y, w11, w12, w21, w22, w, dwdx, dwdy);
+}
+
+// Two passes: the summed weight W and its gradient couple every residual,
+// r_i = N s c_i w_i / W,  dr_i = N s ((dc_i w_i + c_i dw_i) / W - c_i w_i dW / W^2).
+// Returns false (every lane alike) when W == 0.
+__device__ bool evaluate_tsdf(const CeresJobDev& j, const float* __restrict__ pts, const double pose[3],
+                              bool with_jacobian, int lane, Sums* out) {
+  const double scaling = j.w_occ / sqrt(static_cast<double>(j.n));
+  double sn, cs;
+  sincos(pose[2], &sn, &cs);
+  double W = 0., dW[3] = {0., 0., 0.};
+  for (int p = lane; p < j.n; p += 32) {
+    const double px = static_cast<double>(pts[3 * p]), py = static_cast<double>(pts[3 * p + 1]);
+    const double wx = __dadd_rn(__dadd_rn(__dmul_rn(cs, px), __dmul_rn(-sn, py)), pose[0]);
+    const double wy = __dadd_rn(__dadd_rn(__dmul_rn(sn, px), __dmul_rn(cs, py)), pose[1]);
+    double c, dcdx, dcdy, w, dwdx, dwdy;
+    tsdf_sample(j, wx, wy, &c, &dcdx, &dcdy, &w, &dwdx, &dwdy);
+    W += w;
+    dW[0] += dwdx;
+    dW[1] += dwdy;
+    dW[2] += dwdx * (-sn * px - cs * py) + dwdy * (cs * px - sn * py);
+  }
+  W = warp_sum_d(W);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) dW[k] = warp_sum_d(dW[k]);
+  if (W == 0.) return false;
+  Sums s;
+  s.rr = 0.;
+  s.g[0] = s.g[1] = s.g[2] = 0.;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) s.h[k] = 0.;
+  const double ns = static_cast<double>(j.n) * scaling;
+  for (int p = lane; p < j.n; p += 32) {
+    const double px = static_cast<double>(pts[3 * p]), py = static_cast<double>(pts[3 * p + 1]);
+    const double wx = __dadd_rn(__dadd_rn(__dmul_rn(cs, px), __dmul_rn(-sn, py)), pose[0]);
+    const double wy = __dadd_rn(__dadd_rn(__dmul_rn(sn, px), __dmul_rn(cs, py)), pose[1]);
+    double c, dcdx, dcdy, w, dwdx, dwdy;
+    tsdf_sample(j, wx, wy, &c, &dcdx, &dcdy, &w, &dwdx, &dwdy);
+    const double num = ns * c * w;
+    const double res_i = num / W;
+    s.rr += res_i * res_i;
+    if (with_jacobian) {
+      const double tx = -sn * px - cs * py, ty = cs * px - sn * py;
+      const double dc[3] = {dcdx, dcdy, dcdx * tx + dcdy * ty};
+      const double dw[3] = {dwdx, dwdy, dwdx * tx + dwdy * ty};
+      double jr[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) jr[k] = ns * (dc[k] * w + c * dw[k]) / W - num * dW[k] / (W * W);
+      s.g[0] += jr[0] * res_i;
+      s.g[1] += jr[1] * res_i;
+      s.g[2] += jr[2] * res_i;
+      s.h[0] += jr[0] * jr[0];
+      s.h[1] += jr[0] * jr[1];
+      s.h[2] += jr[0] * jr[2];
+      s.h[3] += jr[1] * jr[1];
+      s.h[4] += jr[1] * jr[2];
+      s.h[5] += jr[2] * jr[2];
+    }
+  }
+  s.rr = warp_sum_d(s.rr);
+  if (with_jacobian) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s.g[k] = warp_sum_d(s.g[k]);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s.h[k] = warp_sum_d(s.h[k]);
+  }
+  const double r0 = j.w_t * (pose[0] - j.target[0]), r1 = j.w_t * (pose[1] - j.target[1]);
+  const double r2 = j.w_r * (pose[2] - j.init[2]);
+  s.rr += r0 * r0 + r1 * r1 + r2 * r2;
+  if (with_jacobian) {
+    s.g[0] += j.w_t * r0;
+    s.g[1] += j.w_t * r1;
+    s.g[2] += j.w_r * r2;
+    s.h[0] += j.w_t * j.w_t;
+    s.h[3] += j.w_t * j.w_t;
+    s.h[5] += j.w_r * j.w_r;
+  }
+  *out = s;
+  return true;
+}
+
+__device__ __forceinline__ bool evaluate_any(const CeresJobDev& j, const float* __restrict__ pts,
+                                             const double pose[3], int lane, Sums* out) {
+  if (j.weight_cells != nullptr) return evaluate_tsdf(j, pts, pose, true, lane, out);
+  evaluate(j, pts, pose, true, lane, out);
+  return true;
+}
+
 // Solves the symmetric positive definite 3 x 3 system A s = b (A: 00 01 02 11 12 22) by Cholesky.
 __device__ __forceinline__ bool solve_spd3(const double a[6], const double b[3], double s[3]) {
   const double l00 = sqrt(a[0]);
@@ -181,7 +327,17 @@ k_ceres_lm(const CeresJobDev* __restrict__ jobs, const float* __restrict__ point
   double x[3] = {j.init[0], j.init[1], j.init[2]};
   double x_min[3] = {x[0], x[1], x[2]};
   Sums cur;
-  evaluate(j, pts, x, true, lane, &cur);
+  if (!evaluate_any(j, pts, x, lane, &cur)) {  // "Residual and Jacobian evaluation failed": x untouched
+    if (lane == 0) {
+      csm_ceres_result2d r;
+      r.pose[0] = x[0], r.pose[1] = x[1], r.pose[2] = x[2];
+      r.initial_cost = r.final_cost = 0.;
+      r.iterations = r.num_successful_steps = r.num_unsuccessful_steps = 0;
+      r.termination = 5;
+      results[job] = r;
+    }
+    return;
+  }
   double x_cost = 0.5 * cur.rr;
   // Jacobi scaling from the first Jacobian: 1 / (1 + column norm)
   const double scale[3] = {1. / (1. + sqrt(cur.h[0])), 1. / (1. + sqrt(cur.h[3])),
@@ -247,13 +403,15 @@ k_ceres_lm(const CeresJobDev* __restrict__ jobs, const float* __restrict__ point
     const double delta[3] = {step[0] * scale[0], step[1] * scale[1], step[2] * scale[2]};
     const double cand[3] = {x[0] + delta[0], x[1] + delta[1], x[2] + delta[2]};
     Sums cs;
-    evaluate(j, pts, cand, true, lane, &cs);  // the Jacobian sums are kept if the step is accepted
-    const double cand_cost = 0.5 * cs.rr;
+    // the Jacobian sums are kept if the step is accepted; a failed evaluation makes the
+    // candidate infinitely expensive (the step is rejected)
+    const bool cand_ok = evaluate_any(j, pts, cand, lane, &cs);
+    const double cand_cost = cand_ok ? 0.5 * cs.rr : 1.7976931348623157e308;
     if (norm3(delta) <= 1e-8 * (x_norm + 1e-8)) { termination = 1; break; }
     if (fabs(x_cost - cand_cost) <= 1e-6 * x_cost) { termination = 2; break; }
     const double relative_decrease = (ev_current - cand_cost) / model_cost_change;
     const double historical = (ev_reference - cand_cost) / (acc_reference + model_cost_change);
-    const double quality = fmax(relative_decrease, historical);
+    const double quality = cand_ok ? fmax(relative_decrease, historical) : -1.7976931348623157e308;
     if (quality > 1e-3) {
       x[0] = cand[0], x[1] = cand[1], x[2] = cand[2];
       x_norm = norm3(x);
@@ -333,6 +491,19 @@ extern "C" int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs
       table_at[in.cost_table] = table_bytes;
       table_bytes += up(sizeof(float) * 65536);
     }
+    if (in.weight_cells != nullptr) {
+      CSM_REQUIRE(in.weight_table != nullptr && in.truncation_distance > 0.,
+                  "TSDF ceres job needs a weight table and a positive truncation distance");
+      if (!grid_at.count(in.weight_cells)) {
+        grid_at[in.weight_cells] = grid_bytes;
+        grid_size[in.weight_cells] = sizeof(uint16_t) * static_cast<size_t>(in.num_x) * in.num_y;
+        grid_bytes += up(grid_size[in.weight_cells]);
+      }
+      if (!table_at.count(in.weight_table)) {
+        table_at[in.weight_table] = table_bytes;
+        table_bytes += up(sizeof(float) * 65536);
+      }
+    }
     CeresJobDev& j = dev[i];
     j.pts_off = static_cast<long long>(n_pts);
     j.num_x = in.num_x;
@@ -368,6 +539,13 @@ extern "C" int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs
     memcpy(pin + o_pts + sizeof(float) * 3 * j.pts_off, in.points_xyz, sizeof(float) * 3 * j.n);
     j.cells = reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
     j.cost_table = reinterpret_cast<const float*>(base + o_tab + table_at[in.cost_table]);
+    j.weight_cells = in.weight_cells
+                         ? reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.weight_cells])
+                         : nullptr;
+    j.weight_table = in.weight_cells
+                         ? reinterpret_cast<const float*>(base + o_tab + table_at[in.weight_table])
+                         : nullptr;
+    j.max_cc = static_cast<float>(in.truncation_distance);
   }
   for (const auto& kv : grid_at) memcpy(pin + o_grid + kv.second, kv.first, grid_size[kv.first]);
   for (const auto& kv : table_at) memcpy(pin + o_tab + kv.second, kv.first, sizeof(float) * 65536);

@@ -48,7 +48,6 @@ std::vector<CeresScanMatcher2D::Answer> CeresScanMatcher2D::MatchBatch(
   for (size_t i = 0; i != n; ++i) {
     const Query& q = queries[i];
     CSM_CHECK(q.point_cloud != nullptr && q.grid != nullptr);
-    CSM_CHECK(q.grid->GetGridType() == GridType::PROBABILITY_GRID);
     CSM_CHECK(!q.point_cloud->empty());
     const MapLimits& limits = q.grid->limits();
     xyz[i].resize(3 * q.point_cloud->size());
@@ -79,6 +78,13 @@ std::vector<CeresScanMatcher2D::Answer> CeresScanMatcher2D::MatchBatch(
     job.occupied_space_weight = options_.occupied_space_weight();
     job.translation_weight = options_.translation_weight();
     job.rotation_weight = options_.rotation_weight();
+    if (q.grid->GetGridType() == GridType::TSDF) {  // reference :84-91
+      const TSDF2D& tsdf = static_cast<const TSDF2D&>(*q.grid);
+      job.cost_table = tsdf.value_converter().value_to_tsd_table().data();
+      job.weight_cells = tsdf.weight_cells().data();
+      job.weight_table = tsdf.value_converter().value_to_weight_table().data();
+      job.truncation_distance = tsdf.GetMaxCorrespondenceCost();
+    }
   }
   std::vector<csm_ceres_result2d> results(n);
   if (csm_ceres_match2d_batch(ctx->get(), jobs.data(), static_cast<int>(n), results.data()) != CSM_OK) {

@@ -7,8 +7,9 @@
 // Levenberg-Marquardt iteration ceres::Solve runs for these options, executed on the
 // device (csm_ceres_match2d_batch, one warp per problem, fp64).  MatchBatch refines many
 // poses in one launch -- what ConstraintBuilder2D needs right after a batch of
-// branch-and-bound searches (constraint_builder_2d.cc:245-249).  TSDF grids
-// (tsdf_match_cost_function_2d.cc) are not supported yet: CHECK.  No CPU fallback.
+// branch-and-bound searches (constraint_builder_2d.cc:245-249).  ProbabilityGrid
+// (occupied_space_cost_function_2d.cc) and TSDF2D (tsdf_match_cost_function_2d.cc) grids.
+// No CPU fallback.
 #ifndef CARTOGRAPHER_MAPPING_INTERNAL_2D_SCAN_MATCHING_CERES_SCAN_MATCHER_2D_H_
 #define CARTOGRAPHER_MAPPING_INTERNAL_2D_SCAN_MATCHING_CERES_SCAN_MATCHER_2D_H_
 

@@ -227,6 +227,15 @@ typedef struct {
   double initial_pose[3];           /* x, y, theta                                    */
   double target_translation[2];
   double occupied_space_weight, translation_weight, rotation_weight;
+  /* TSDF2D grids (tsdf_match_cost_function_2d.cc:28-75 on interpolated_tsdf_2d.h:35-131): a
+   * non-NULL weight_cells selects residual_i = N * w_occ / sqrt(N) * tsd(T p_i) * weight(T p_i) /
+   * sum_j weight(T p_j) with bilinear interpolation; `cells` / `cost_table` are then the TSD
+   * cells and the value-to-TSD table.  A pose whose points see no weight at all fails the
+   * evaluation like the reference's functor (termination 5 at the initial pose, a rejected
+   * step later). */
+  const uint16_t* weight_cells;
+  const float* weight_table;        /* 65536 floats                                   */
+  double truncation_distance;       /* Grid2D::GetMaxCorrespondenceCost of a TSDF2D   */
 } csm_ceres_job2d;
 
 typedef struct {

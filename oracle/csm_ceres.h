@@ -102,7 +102,7 @@ class CeresScanMatcher2D {
   // All N + 3 residuals and, optionally, the (N + 3) x 3 row-major Jacobian at `pose`:
   // what the three AutoDiffCostFunctions evaluate (Jet derivatives of the interpolator are
   // its analytic partials, cubic_interpolation.h BiCubicInterpolator::Evaluate<JetT>).
-  void Evaluate(const double pose[3], const double target[2], const double initial_angle,
+  bool Evaluate(const double pose[3], const double target[2], const double initial_angle,
                 const PointCloud& cloud, const ProbabilityGrid& grid, std::vector<double>* residuals,
                 std::vector<double>* jacobian) const {
     const size_t n = cloud.size();
@@ -137,11 +137,122 @@ class CeresScanMatcher2D {
       (*jacobian)[3 * (n + 1) + 1] = options_.translation_weight;
       (*jacobian)[3 * (n + 2) + 2] = options_.rotation_weight;
     }
+    return true;
+  }
+
+  // --- TSDF2D grids: tsdf_match_cost_function_2d.cc:28-75 on interpolated_tsdf_2d.h:35-131 ----
+  // Grid2D::GetCorrespondenceCost of a TSDF2D (grid_2d.h:53-57): the TSD itself, read through
+  // the table GetConversionTable(max, min, max) -- unknown cells and cells outside the grid
+  // read +truncation_distance.
+  static float TsdfCost(const TSDF2D& g, const Array2i& c) {
+    if (!g.limits().Contains(c)) return g.GetMaxCorrespondenceCost();
+    const uint16_t v = g.tsd_cells()[g.limits().cell_limits.num_x_cells * c.y + c.x];
+    return (v & 0x7FFF) == 0 ? g.GetMaxCorrespondenceCost() : g.value_to_tsd()[v];
+  }
+  static float TsdfWeight(const TSDF2D& g, const Array2i& c) { return g.GetTSDAndWeight(c).second; }
+
+  struct Bilinear {
+    float x1, y1, x2, y2;
+    Array2i index1;
+  };
+  // ComputeInterpolationDataPoints / CenterOfLowerPixel (interpolated_tsdf_2d.h:85-93,110-124)
+  static Bilinear LowerPixel(const TSDF2D& g, const double x, const double y) {
+    const MapLimits& l = g.limits();
+    const Array2i c = l.GetCellIndex(static_cast<float>(x), static_cast<float>(y));
+    float cx = static_cast<float>(l.max_x - l.resolution * (c.y + 0.5));  // GetCellCenter, map_limits.h:79-82
+    float cy = static_cast<float>(l.max_y - l.resolution * (c.x + 0.5));
+    if (cx > x) cx = static_cast<float>(cx - l.resolution);
+    if (cy > y) cy = static_cast<float>(cy - l.resolution);
+    Bilinear b;
+    b.x1 = cx;
+    b.y1 = cy;
+    b.x2 = cx + static_cast<float>(l.resolution);
+    b.y2 = cy + static_cast<float>(l.resolution);
+    b.index1 = l.GetCellIndex(b.x1, b.y1);
+    return b;
+  }
+  // InterpolateBilinear (:95-104) and its partials (what the Jets carry).
+  static void InterpolateBilinear(const Bilinear& b, const double x, const double y, const float q11,
+                                  const float q12, const float q21, const float q22, double* f,
+                                  double* dfdx, double* dfdy) {
+    const double wx = static_cast<double>(b.x2 - b.x1), wy = static_cast<double>(b.y2 - b.y1);
+    const double nx = (x - static_cast<double>(b.x1)) / wx;
+    const double ny = (y - static_cast<double>(b.y1)) / wy;
+    const double d1 = static_cast<double>(q12 - q11), d2 = static_cast<double>(q22 - q21);
+    const double q1 = d1 * ny + static_cast<double>(q11);
+    const double q2 = d2 * ny + static_cast<double>(q21);
+    *f = (q2 - q1) * nx + q1;
+    *dfdx = (q2 - q1) / wx;
+    *dfdy = ((d2 - d1) * nx + d1) / wy;
+  }
+  // GetCorrespondenceCost(x, y) and GetWeight(x, y) with partials (:41-83).
+  static void TsdfSample(const TSDF2D& g, const double x, const double y, double* cost, double* dcdx,
+                         double* dcdy, double* weight, double* dwdx, double* dwdy) {
+    const Bilinear b = LowerPixel(g, x, y);
+    Array2i i12 = b.index1, i21 = b.index1, i22 = b.index1;
+    i12.x -= 1;
+    i21.y -= 1;
+    i22.x -= 1;
+    i22.y -= 1;
+    const float w11 = TsdfWeight(g, b.index1), w12 = TsdfWeight(g, i12), w21 = TsdfWeight(g, i21),
+                w22 = TsdfWeight(g, i22);
+    if (w11 == 0.0 || w12 == 0.0 || w21 == 0.0 || w22 == 0.0) {
+      *cost = static_cast<double>(g.GetMaxCorrespondenceCost());
+      *dcdx = *dcdy = 0.;
+    } else {
+      InterpolateBilinear(b, x, y, TsdfCost(g, b.index1), TsdfCost(g, i12), TsdfCost(g, i21),
+                          TsdfCost(g, i22), cost, dcdx, dcdy);
+    }
+    InterpolateBilinear(b, x, y, w11, w12, w21, w22, weight, dwdx, dwdy);
+  }
+
+  bool Evaluate(const double pose[3], const double target[2], const double initial_angle,
+                const PointCloud& cloud, const TSDF2D& grid, std::vector<double>* residuals,
+                std::vector<double>* jacobian) const {
+    const size_t n = cloud.size();
+    residuals->assign(n + 3, 0.);
+    if (jacobian) jacobian->assign(3 * (n + 3), 0.);
+    const double scaling = options_.occupied_space_weight / std::sqrt(static_cast<double>(n));
+    const double cs = std::cos(pose[2]), sn = std::sin(pose[2]);
+    std::vector<double> c(n), w(n), dc(3 * n), dw(3 * n);
+    double summed = 0., dsummed[3] = {0., 0., 0.};
+    for (size_t i = 0; i < n; ++i) {
+      const double px = static_cast<double>(cloud[i].x), py = static_cast<double>(cloud[i].y);
+      const double wx = cs * px + (-sn) * py + pose[0] * 1.;
+      const double wy = sn * px + cs * py + pose[1] * 1.;
+      double dcdx, dcdy, dwdx, dwdy;
+      TsdfSample(grid, wx, wy, &c[i], &dcdx, &dcdy, &w[i], &dwdx, &dwdy);
+      const double dwx_dth = -sn * px - cs * py, dwy_dth = cs * px - sn * py;
+      dc[3 * i] = dcdx, dc[3 * i + 1] = dcdy, dc[3 * i + 2] = dcdx * dwx_dth + dcdy * dwy_dth;
+      dw[3 * i] = dwdx, dw[3 * i + 1] = dwdy, dw[3 * i + 2] = dwdx * dwx_dth + dwdy * dwy_dth;
+      summed += w[i];
+      for (int k = 0; k < 3; ++k) dsummed[k] += dw[3 * i + k];
+    }
+    if (summed == 0.) return false;  // tsdf_match_cost_function_2d.cc:62
+    const double ns = static_cast<double>(n) * scaling;
+    for (size_t i = 0; i < n; ++i) {
+      const double num = ns * c[i] * w[i];
+      (*residuals)[i] = num / summed;
+      if (jacobian)
+        for (int k = 0; k < 3; ++k)
+          (*jacobian)[3 * i + k] = ns * (dc[3 * i + k] * w[i] + c[i] * dw[3 * i + k]) / summed -
+                                   num * dsummed[k] / (summed * summed);
+    }
+    (*residuals)[n + 0] = options_.translation_weight * (pose[0] - target[0]);
+    (*residuals)[n + 1] = options_.translation_weight * (pose[1] - target[1]);
+    (*residuals)[n + 2] = options_.rotation_weight * (pose[2] - initial_angle);
+    if (jacobian) {
+      (*jacobian)[3 * (n + 0) + 0] = options_.translation_weight;
+      (*jacobian)[3 * (n + 1) + 1] = options_.translation_weight;
+      (*jacobian)[3 * (n + 2) + 2] = options_.rotation_weight;
+    }
+    return true;
   }
 
   // ceres_scan_matcher_2d.cc:64-110 + ceres::Solve (trust region, Levenberg-Marquardt, DENSE_QR).
+  template <typename Grid>
   void Match(const double target_x, const double target_y, const Rigid2d& initial,
-             const PointCloud& cloud, const ProbabilityGrid& grid, Rigid2d* pose_estimate,
+             const PointCloud& cloud, const Grid& grid, Rigid2d* pose_estimate,
              CeresSummary* summary) const {
     ORACLE_CHECK(!cloud.empty());
     const double target[2] = {target_x, target_y};
@@ -151,7 +262,14 @@ class CeresScanMatcher2D {
     double x_min[3] = {x[0], x[1], x[2]};
     std::vector<double> res, jac, cand_res;
     // --- Init: evaluate, Jacobi scaling from the first Jacobian ------------------------------
-    Evaluate(x, target, angle0, cloud, grid, &res, &jac);
+    if (!Evaluate(x, target, angle0, cloud, grid, &res, &jac)) {
+      // TrustRegionMinimizer::Init: "Residual and Jacobian evaluation failed" -> FAILURE, x untouched
+      CeresSummary failed;
+      failed.termination = 5;
+      *pose_estimate = initial;
+      if (summary) *summary = failed;
+      return;
+    }
     double x_cost = Cost(res);
     double gradient[3];
     Gradient(res, jac, gradient);
@@ -225,8 +343,9 @@ class CeresScanMatcher2D {
       num_invalid = 0;
       const double delta[3] = {step[0] * scale[0], step[1] * scale[1], step[2] * scale[2]};
       const double cand[3] = {x[0] + delta[0], x[1] + delta[1], x[2] + delta[2]};
-      Evaluate(cand, target, angle0, cloud, grid, &cand_res, nullptr);
-      const double cand_cost = Cost(cand_res);
+      // A failed evaluation makes the candidate infinitely expensive: the step is rejected.
+      const bool cand_ok = Evaluate(cand, target, angle0, cloud, grid, &cand_res, nullptr);
+      const double cand_cost = cand_ok ? Cost(cand_res) : std::numeric_limits<double>::max();
       // ParameterToleranceReached / FunctionToleranceReached (before the step is judged)
       const double step_norm = Norm3(delta);
       if (step_norm <= 1e-8 * (x_norm + 1e-8)) { sum.termination = 1; break; }
@@ -234,7 +353,8 @@ class CeresScanMatcher2D {
       // TrustRegionStepEvaluator::StepQuality
       const double relative_decrease = (ev_current - cand_cost) / model_cost_change;
       const double historical = (ev_reference - cand_cost) / (acc_reference + model_cost_change);
-      const double quality = std::max(relative_decrease, historical);
+      const double quality =
+          cand_ok ? std::max(relative_decrease, historical) : std::numeric_limits<double>::lowest();
       if (quality > 1e-3) {  // HandleSuccessfulStep
         x[0] = cand[0], x[1] = cand[1], x[2] = cand[2];
         x_norm = Norm3(x);

@@ -287,6 +287,48 @@ void oracle_ceres_match2d(void* grid, const double* options5, const double* targ
   summary6[4] = s.num_unsuccessful_steps;
   summary6[5] = s.termination;
 }
+// The same on a TSDF2D handle (oracle_tsdf2d_create).
+void oracle_ceres_match2d_tsdf(void* grid, const double* options5, const double* target2,
+                               const double* init3, const float* xyz, int n, double* pose3,
+                               double* summary6) {
+  CeresScanMatcherOptions2D o;
+  o.occupied_space_weight = options5[0];
+  o.translation_weight = options5[1];
+  o.rotation_weight = options5[2];
+  o.use_nonmonotonic_steps = options5[3] != 0.;
+  o.max_num_iterations = static_cast<int>(options5[4]);
+  Rigid2d init, pose;
+  init.tx = init3[0];
+  init.ty = init3[1];
+  init.angle = init3[2];
+  CeresSummary s;
+  CeresScanMatcher2D(o).Match(target2[0], target2[1], init, ToCloud(xyz, n), *static_cast<TSDF2D*>(grid),
+                              &pose, &s);
+  pose3[0] = pose.tx;
+  pose3[1] = pose.ty;
+  pose3[2] = pose.angle;
+  summary6[0] = s.initial_cost;
+  summary6[1] = s.final_cost;
+  summary6[2] = s.iterations;
+  summary6[3] = s.num_successful_steps;
+  summary6[4] = s.num_unsuccessful_steps;
+  summary6[5] = s.termination;
+}
+int oracle_ceres_evaluate2d_tsdf(void* grid, const double* options5, const double* target2,
+                                 double initial_angle, const double* pose3, const float* xyz, int n,
+                                 double* residuals, double* jacobian) {
+  CeresScanMatcherOptions2D o;
+  o.occupied_space_weight = options5[0];
+  o.translation_weight = options5[1];
+  o.rotation_weight = options5[2];
+  std::vector<double> r, j;
+  if (!CeresScanMatcher2D(o).Evaluate(pose3, target2, initial_angle, ToCloud(xyz, n),
+                                      *static_cast<TSDF2D*>(grid), &r, &j))
+    return 0;
+  std::memcpy(residuals, r.data(), sizeof(double) * r.size());
+  std::memcpy(jacobian, j.data(), sizeof(double) * j.size());
+  return 1;
+}
 // Residuals (n + 3) and row-major Jacobian ((n + 3) x 3) at a pose, for derivative checks.
 void oracle_ceres_evaluate2d(void* grid, const double* options5, const double* target2,
                              double initial_angle, const double* pose3, const float* xyz, int n,

@@ -105,6 +105,10 @@ def lib():
     L.oracle_ceres_evaluate2d.argtypes = [C.c_void_p, f64p, f64p, C.c_double, f64p, f32p, C.c_int,
                                           f64p, f64p]
     L.oracle_ceres_evaluate2d.restype = None
+    L.oracle_ceres_match2d_tsdf.argtypes = L.oracle_ceres_match2d.argtypes
+    L.oracle_ceres_match2d_tsdf.restype = None
+    L.oracle_ceres_evaluate2d_tsdf.argtypes = L.oracle_ceres_evaluate2d.argtypes
+    L.oracle_ceres_evaluate2d_tsdf.restype = C.c_int
     L.oracle_tsdf2d_create.argtypes = [u16p, u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                        C.c_float, C.c_float]
     L.oracle_tsdf2d_create.restype = C.c_void_p
@@ -292,6 +296,27 @@ def ceres_match(grid, opts, target, init, pts):
     return pose, {"initial_cost": summ[0], "final_cost": summ[1], "iterations": int(summ[2]),
                   "num_successful_steps": int(summ[3]), "num_unsuccessful_steps": int(summ[4]),
                   "termination": int(summ[5])}
+
+
+def ceres_match_tsdf(grid, opts, target, init, pts):
+    """CeresScanMatcher2D::Match restatement on an OracleTsdf: (pose[3], summary dict)."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    pose, summ = np.zeros(3), np.zeros(6)
+    lib().oracle_ceres_match2d_tsdf(grid.h, _ceres_options(opts), np.asarray(target, np.float64),
+                                    np.asarray(init, np.float64), pts, len(pts), pose, summ)
+    return pose, {"initial_cost": summ[0], "final_cost": summ[1], "iterations": int(summ[2]),
+                  "num_successful_steps": int(summ[3]), "num_unsuccessful_steps": int(summ[4]),
+                  "termination": int(summ[5])}
+
+
+def ceres_evaluate_tsdf(grid, opts, target, initial_angle, pose, pts):
+    """(valid, residuals, jacobian) of the TSDF cost function + the two delta functors."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    r, j = np.zeros(len(pts) + 3), np.zeros((len(pts) + 3, 3))
+    ok = lib().oracle_ceres_evaluate2d_tsdf(grid.h, _ceres_options(opts), np.asarray(target, np.float64),
+                                            float(initial_angle), np.asarray(pose, np.float64), pts,
+                                            len(pts), r, j)
+    return bool(ok), r, j
 
 
 def ceres_evaluate(grid, opts, target, initial_angle, pose, pts):

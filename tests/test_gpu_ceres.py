@@ -100,3 +100,37 @@ def test_constraint_builder_refines_found_poses(csm):
         assert abs(d) < 1e-6
         moved += np.hypot(tf[i][0] - tf0[i][0], tf[i][1] - tf0[i][1]) > 1e-4
     assert moved > 0
+
+
+def test_tsdf_grids_match_oracle(csm, gpu_ctx):
+    """TSDFMatchCostFunction2D branch: pose within 1e-6 of the CPU restatement on a painted office
+    world with random weights; a never-observed TSDF fails the first evaluation and leaves the
+    pose untouched (tsdf_match_cost_function_2d.cc:62, termination FAILURE)."""
+    import tsdf_util
+    w = synth.World(300, 300, seed=93)
+    tv, wv = tsdf_util.from_world(w, 0.3, 10.0, seed=8)
+    args = (tv, wv, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    g, og = csm.TsdfGrid(*args), ob.OracleTsdf(*args)
+    rng = np.random.default_rng(5)
+    clouds, inits, targets = [], [], []
+    for i in range(16):
+        truth, pts = synth.make_scan(w, 900 + i, max_range=8.0)
+        init = (truth[0] + rng.uniform(-0.04, 0.04), truth[1] + rng.uniform(-0.04, 0.04),
+                truth[2] + rng.uniform(-0.02, 0.02))
+        clouds.append(np.ascontiguousarray(pts))
+        inits.append(init)
+        targets.append((init[0], init[1]))
+    for opts in (POSE_GRAPH, LOCAL_SLAM):
+        poses, summ = csm.ceres_match_batch(gpu_ctx, [g] * 16, clouds, targets, inits, **opts)
+        same = 0
+        for i in range(16):
+            want, ws = ob.ceres_match_tsdf(og, opts, targets[i], inits[i], clouds[i])
+            assert np.allclose(poses[i], want, atol=1e-6), (i, poses[i], want)
+            assert abs(summ[i][0] - ws["initial_cost"]) <= 1e-9 * max(1.0, ws["initial_cost"])
+            assert abs(summ[i][1] - ws["final_cost"]) <= 1e-7 * max(1.0, ws["final_cost"])
+            same += int(summ[i][2]) == ws["iterations"]
+        assert same >= 14
+    z = np.zeros_like(tv)
+    empty = csm.TsdfGrid(z, z, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    poses, summ = csm.ceres_match_batch(gpu_ctx, [empty], clouds[:1], targets[:1], inits[:1], **POSE_GRAPH)
+    assert np.array_equal(poses[0], np.asarray(inits[0])) and int(summ[0][5]) == 2  # ceres::FAILURE
