@@ -854,22 +854,35 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
   if (held > 0) flush();
 }
 
-// 5'b. bucket counters -> list offsets and work-item offsets of depth `slot`; one block,
-//      kPrefixPer consecutive buckets per thread and pass (a C3 step has 126 k buckets:
-//      16 passes instead of 123 with one bucket per thread).
+// 5'b. bucket counters -> list offsets and work-item offsets of depth `slot`.  Block q scans
+//      the kPrefixChunk buckets [q * kPrefixChunk, ...) (kPrefixPer consecutive buckets per
+//      thread) and leaves chunk-local offsets in bucket_start / bucket_istart plus its totals
+//      in the tail of those arrays ([num_buckets + 1 + q]); the last block to finish turns
+//      the totals into chunk bases in place.  Readers add the base of a bucket's chunk
+//      (bucket_base).  A C3 step has 126 k buckets: one block needed 137 us per level.
 constexpr int kPrefixPer = 8;
+constexpr int kLogPrefixChunk = 13;  // 1024 threads x kPrefixPer buckets
+constexpr int kPrefixChunk = 1 << kLogPrefixChunk;
+constexpr int kCntTicket = 34;  // blocks of k_bucket_prefix that have finished
+static_assert(kPrefixChunk == 1024 * kPrefixPer, "one pass per block");
+
+__device__ __forceinline__ unsigned int bucket_base(const unsigned int* __restrict__ starts,
+                                                    unsigned int num_buckets, unsigned int b) {
+  // absolute offset of bucket b (b == num_buckets: the total)
+  return b == num_buckets ? starts[num_buckets]
+                          : starts[b] + starts[num_buckets + 1 + (b >> kLogPrefixChunk)];
+}
+
 __global__ void __launch_bounds__(1024)
 k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ bucket_start,
                 unsigned int* __restrict__ bucket_istart, unsigned int* __restrict__ counters,
                 int slot, unsigned int num_buckets, unsigned long long cap,
                 unsigned long long item_cap) {
   __shared__ unsigned int wsum[2][32];
-  __shared__ unsigned int carry[2];
-  if (threadIdx.x == 0) carry[0] = carry[1] = 0u;
-  __syncthreads();
+  __shared__ bool s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (unsigned int b0 = 0; b0 < num_buckets; b0 += 1024 * kPrefixPer) {
-    const unsigned int first = b0 + threadIdx.x * kPrefixPer;
+  {
+    const unsigned int first = blockIdx.x * kPrefixChunk + threadIdx.x * kPrefixPer;
     unsigned int c[kPrefixPer];
     unsigned int tc = 0u, ti = 0u;  // this thread's totals
 #pragma unroll
@@ -910,8 +923,8 @@ k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict_
       wsum[1][lane] = i2;
     }
     __syncthreads();
-    unsigned int at_c = carry[0] + (warp ? wsum[0][warp - 1] : 0u) + pc - tc;
-    unsigned int at_i = carry[1] + (warp ? wsum[1][warp - 1] : 0u) + pi - ti;
+    unsigned int at_c = (warp ? wsum[0][warp - 1] : 0u) + pc - tc;
+    unsigned int at_i = (warp ? wsum[1][warp - 1] : 0u) + pi - ti;
 #pragma unroll
     for (int k = 0; k < kPrefixPer; ++k) {
       if (first + k < num_buckets) {
@@ -921,19 +934,33 @@ k_bucket_prefix(unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict_
       at_c += c[k];
       at_i += (c[k] + kWarp - 1) / kWarp;
     }
-    __syncthreads();
     if (threadIdx.x == 0) {
-      carry[0] += wsum[0][31];
-      carry[1] += wsum[1][31];
+      bucket_start[num_buckets + 1 + blockIdx.x] = wsum[0][31];   // chunk totals for now
+      bucket_istart[num_buckets + 1 + blockIdx.x] = wsum[1][31];
     }
-    __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    bucket_start[num_buckets] = carry[0];
-    bucket_istart[num_buckets] = carry[1];
-    counters[kCntNodes + slot] = carry[0];
-    counters[kCntItems + slot] = carry[1];
-    if (carry[0] > cap || carry[1] > item_cap) atomicOr(&counters[kCntOverflow], 1u);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&counters[kCntTicket], 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    volatile unsigned int* vc = bucket_start + num_buckets + 1;
+    volatile unsigned int* vi = bucket_istart + num_buckets + 1;
+    unsigned int run_c = 0u, run_i = 0u;
+    for (unsigned int q = 0; q < gridDim.x; ++q) {  // totals -> chunk bases, in place
+      const unsigned int tcq = vc[q], tiq = vi[q];
+      vc[q] = run_c;
+      vi[q] = run_i;
+      run_c += tcq;
+      run_i += tiq;
+    }
+    bucket_start[num_buckets] = run_c;
+    bucket_istart[num_buckets] = run_i;
+    counters[kCntNodes + slot] = run_c;
+    counters[kCntItems + slot] = run_i;
+    counters[kCntTicket] = 0u;
+    if (run_c > cap || run_i > item_cap) atomicOr(&counters[kCntOverflow], 1u);
   }
 }
 
@@ -953,12 +980,13 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
       static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[kCntBlocks + slot]), block_cap));
   for (unsigned int q = warp; q < nblocks; q += warps) {
     const NodeBlock nb = blocks[q];
-    const unsigned int dst = bucket_start[nb.bucket] + nb.rel;
+    const unsigned int dst = bucket_base(bucket_start, num_buckets, nb.bucket) + nb.rel;
     for (unsigned int t = lane; t < nb.count; t += kWarp) nodes[dst + t] = tmp[nb.src + t];
   }
   for (unsigned int b = warp; b < num_buckets; b += warps) {
-    const unsigned int first = bucket_start[b], c = bucket_start[b + 1] - first;
-    const unsigned int ibase = bucket_istart[b];
+    const unsigned int first = bucket_base(bucket_start, num_buckets, b);
+    const unsigned int c = bucket_base(bucket_start, num_buckets, b + 1) - first;
+    const unsigned int ibase = bucket_base(bucket_istart, num_buckets, b);
     for (unsigned int t = lane; t * kWarp < c; t += kWarp)
       items[ibase + t] = make_uint2(first + t * kWarp, b * kWarp + (min(c - t * kWarp, 32u) - 1u));
   }
@@ -1309,8 +1337,10 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   // per bucket (= scan of a job): owner, counter, list offset, work-item offset
   const size_t o_bjs = take(sizeof(unsigned int) * b->total_scans);
   const size_t o_bcnt = take(sizeof(unsigned int) * b->total_scans);
-  const size_t o_bstart = take(sizeof(unsigned int) * (b->total_scans + 1));
-  const size_t o_bistart = take(sizeof(unsigned int) * (b->total_scans + 1));
+  // offsets | total | one base per k_bucket_prefix chunk
+  const size_t prefix_len = static_cast<size_t>(b->total_scans) + 1 + b->total_scans / 8192 + 2;
+  const size_t o_bstart = take(sizeof(unsigned int) * prefix_len);
+  const size_t o_bistart = take(sizeof(unsigned int) * prefix_len);
   if (b->owner->pool.take(false, off, &b->arena, &b->arena_cap) != CSM_OK) {
     b->arena = nullptr;
     set_error("allocation of a %zu-byte batch arena failed: %s", off, cudaGetErrorString(cudaGetLastError()));
@@ -1589,7 +1619,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
         ++ctx->launches, k_seed_nodes<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(
             b->jobs, b->scans, b->top_scores, b->state, node_tmp, node_blocks, b->bucket_cnt,
             b->counters, d, node_cap, block_cap);
-      ++ctx->launches, k_bucket_prefix<<<1, 1024, 0, st>>>(
+      ++ctx->launches, k_bucket_prefix<<<static_cast<unsigned int>((nbuckets + kPrefixChunk - 1) / kPrefixChunk), 1024, 0, st>>>(
           b->bucket_cnt, b->bucket_start, b->bucket_istart, b->counters, d,
           static_cast<unsigned int>(nbuckets), node_cap, item_cap);
       ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
