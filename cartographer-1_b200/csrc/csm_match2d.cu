@@ -983,11 +983,15 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
     const unsigned int dst = bucket_base(bucket_start, num_buckets, nb.bucket) + nb.rel;
     for (unsigned int t = lane; t < nb.count; t += kWarp) nodes[dst + t] = tmp[nb.src + t];
   }
-  for (unsigned int b = warp; b < num_buckets; b += warps) {
+  // Work items: one THREAD per bucket (most of the 126 k buckets of a C3 step are empty or
+  // hold a handful of items; a warp per bucket spent its time on the empty ones).
+  const unsigned int threads = gridDim.x * blockDim.x;
+  for (unsigned int b = blockIdx.x * blockDim.x + threadIdx.x; b < num_buckets; b += threads) {
     const unsigned int first = bucket_base(bucket_start, num_buckets, b);
     const unsigned int c = bucket_base(bucket_start, num_buckets, b + 1) - first;
+    if (c == 0u) continue;
     const unsigned int ibase = bucket_base(bucket_istart, num_buckets, b);
-    for (unsigned int t = lane; t * kWarp < c; t += kWarp)
+    for (unsigned int t = 0; t * kWarp < c; ++t)
       items[ibase + t] = make_uint2(first + t * kWarp, b * kWarp + (min(c - t * kWarp, 32u) - 1u));
   }
 }
