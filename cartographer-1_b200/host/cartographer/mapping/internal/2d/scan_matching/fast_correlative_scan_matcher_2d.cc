@@ -194,7 +194,7 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
     lattice_estimate[i] = sp.num_scans * (wx / step + 1.) * (wy / step + 1.);
   });
   // Split into device batches of bounded footprint.
-  constexpr double kLatticeBudget = 48e6;
+  constexpr double kLatticeBudget = 128e6;  // lowest-resolution candidates per device batch (4 B each)
   constexpr size_t kMaxJobs = 4096;
   size_t begin = 0;
   while (begin < n) {
