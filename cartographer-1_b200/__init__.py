@@ -642,6 +642,49 @@ def rt_match3d(resolution, xyz, values, options4, initial_pose7, points):
     return score, pose
 
 
+class DeviceGrid3D:
+    """A HybridGrid (voxel list) resident on the device for RealTimeCorrelativeScanMatcher3D."""
+
+    def __init__(self, ctx, resolution, xyz, values):
+        L = host()
+        L.csmh_device_grid3d_create.restype = C.c_void_p
+        L.csmh_device_grid3d_create.argtypes = [C.c_void_p, C.c_float,
+                                                np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS"),
+                                                np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS"), C.c_int]
+        L.csmh_device_grid3d_destroy.argtypes = [C.c_void_p]
+        self.ctx = ctx
+        xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)
+        values = np.ascontiguousarray(values, np.uint16)
+        self.h = L.csmh_device_grid3d_create(ctx.h, resolution, xyz, values, len(values))
+
+    def match(self, options4, initial_poses7, clouds):
+        """(scores, poses[n, 7], best_index, num_candidates) for every cloud against this grid."""
+        L = host()
+        f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+        f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+        i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+        i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+        L.csmh_rt_match3d_resident.argtypes = [C.c_void_p, C.c_void_p, f64p, C.c_int, f64p, f32p, i64p, f32p,
+                                               f64p, i32p, i32p]
+        n = len(clouds)
+        offsets = np.zeros(n + 1, np.int64)
+        offsets[1:] = np.cumsum([len(c) for c in clouds])
+        pts = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in clouds]))
+        scores = np.zeros(n, np.float32)
+        poses = np.zeros((n, 7), np.float64)
+        best = np.zeros(n, np.int32)
+        num = np.zeros(n, np.int32)
+        L.csmh_rt_match3d_resident(self.ctx.h, self.h, np.ascontiguousarray(options4, np.float64), n,
+                                   np.ascontiguousarray(initial_poses7, np.float64).reshape(-1),
+                                   pts.reshape(-1), offsets, scores, poses.reshape(-1), best, num)
+        return scores, poses, best, num
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            host().csmh_device_grid3d_destroy(self.h)
+            self.h = None
+
+
 def rt_match3d_batch(ctx, resolution, xyz, values, options4, initial_poses7, clouds):
     """Several clouds against one grid state: (scores, poses[n, 7], best_index, num_candidates)."""
     xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)

@@ -372,4 +372,48 @@ int csmh_rt_match3d_batch(void* ctx, float resolution, const int32_t* xyz, const
   return num;
 }
 
+// A HybridGrid kept on the device between calls (local SLAM matches every new scan against
+// the same live submap): create once, match many clouds, destroy.
+void* csmh_device_grid3d_create(void* ctx, float resolution, const int32_t* xyz, const uint16_t* values,
+                                int n_voxels) {
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n_voxels; ++i)
+    *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  return new mapping::scan_matching::DeviceHybridGrid(static_cast<DeviceContext*>(ctx), grid);
+}
+void csmh_device_grid3d_destroy(void* g) { delete static_cast<mapping::scan_matching::DeviceHybridGrid*>(g); }
+
+int csmh_rt_match3d_resident(void* ctx, void* device_grid, const double* options4, int num,
+                             const double* initial_poses7, const float* pts, const int64_t* offsets,
+                             float* scores, double* poses7_out, int32_t* best_index,
+                             int32_t* num_candidates) {
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  mapping::scan_matching::proto::RealTimeCorrelativeScanMatcherOptions o;
+  o.set_linear_search_window(options4[0]);
+  o.set_angular_search_window(options4[1]);
+  o.set_translation_delta_cost_weight(options4[2]);
+  o.set_rotation_delta_cost_weight(options4[3]);
+  const mapping::scan_matching::RealTimeCorrelativeScanMatcher3D matcher(o);
+  std::vector<sensor::PointCloud> clouds(num);
+  std::vector<mapping::scan_matching::RealTimeCorrelativeScanMatcher3D::Query> queries(num);
+  for (int i = 0; i < num; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2])});
+    queries[i].initial_pose_estimate = Pose7(initial_poses7 + 7 * i);
+    queries[i].point_cloud = &clouds[i];
+    queries[i].grid = static_cast<mapping::scan_matching::DeviceHybridGrid*>(device_grid);
+  }
+  const auto answers = matcher.MatchBatch(context, queries);
+  for (int i = 0; i < num; ++i) {
+    scores[i] = answers[i].score;
+    best_index[i] = answers[i].best_index;
+    num_candidates[i] = answers[i].num_candidates;
+    const transform::Rigid3d& p = answers[i].pose_estimate;
+    const double v[7] = {p.translation().x(), p.translation().y(), p.translation().z(), p.rotation().w(),
+                         p.rotation().x(),    p.rotation().y(),    p.rotation().z()};
+    for (int k = 0; k < 7; ++k) poses7_out[7 * i + k] = v[k];
+  }
+  return num;
+}
+
 }  // extern "C"

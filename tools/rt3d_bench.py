@@ -46,6 +46,17 @@ def main():
         out["batch_%d" % b] = {"scans_per_s": b / dt, "ms_per_call": 1e3 * dt,
                                "candidates_per_scan": int(num[0]),
                                "note": "includes the upload of the voxel list and the dense-box build every call"}
+    dg = pkg.DeviceGrid3D(ctx, 0.1, xyz, val)
+    for b in (1, 16):
+        reps = {1: 20, 16: 5}[b]
+        dg.match(opt, np.array(inits[:b]), clouds[:b])
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            s2, p2, b2, n2 = dg.match(opt, np.array(inits[:b]), clouds[:b])
+        dt = (time.perf_counter() - t0) / reps
+        out["resident_batch_%d" % b] = {"scans_per_s": b / dt, "ms_per_call": 1e3 * dt,
+                                        "note": "grid resident on the device (DeviceHybridGrid)"}
+    assert np.array_equal(b2, best) and np.array_equal(s2, scores)
     og = ob.OracleGrid3D(0.1, xyz, val)
     t0 = time.perf_counter()
     n = 2
