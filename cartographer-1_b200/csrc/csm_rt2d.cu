@@ -23,6 +23,11 @@ struct RtJobDev {
   const float* cost_table;
   const uint16_t* weight_cells;  // TSDF only (nullptr selects the probability score)
   const float* weight_table;
+  // The grid decoded once per batch (k_rt_decode): probability 1 - cost_table[cell] for a
+  // ProbabilityGrid, cost_table[cell] (the TSD) and weight_table[weight cell] for a TSDF2D.
+  // Same fp32 values as the two dependent lookups per point they replace.
+  const float* dec;
+  const float* wdec;
   const double* penalty;
   int num_x, num_y, n, S, lin;
   long long pts_off, quat_off;
@@ -37,6 +42,15 @@ struct RtJobDev {
 // scores candidates (lane, lane + 32, ...).  The fp32 sum runs in point order exactly
 // like the CPU loop; the loads of 8 points are issued together ahead of their adds so
 // that the two dependent reads (cell, then table) are pipelined, not serialised.
+__global__ void __launch_bounds__(256)
+k_rt_decode(const uint16_t* __restrict__ cells, const float* __restrict__ table, float* __restrict__ out,
+            size_t n, int one_minus) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float t = __ldg(table + __ldg(cells + i));
+  out[i] = one_minus ? __fsub_rn(1.f, t) : t;
+}
+
 constexpr int kRtWarps = 8;
 __global__ void __launch_bounds__(kRtWarps * 32)
 k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
@@ -76,8 +90,7 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
             const int px = cell[p0 + k].x + x, py = cell[p0 + k].y + y;
             if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
                 static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
-              const uint16_t v = __ldg(j.cells + static_cast<size_t>(py) * j.num_x + px);
-              prob[k] = __fsub_rn(1.f, __ldg(j.cost_table + v));
+              prob[k] = __ldg(j.dec + static_cast<size_t>(py) * j.num_x + px);
             }
           }
         }
@@ -101,8 +114,8 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
             if (static_cast<unsigned>(px) < static_cast<unsigned>(j.num_x) &&
                 static_cast<unsigned>(py) < static_cast<unsigned>(j.num_y)) {
               const size_t flat = static_cast<size_t>(py) * j.num_x + px;
-              tsd[k] = __ldg(j.cost_table + __ldg(j.cells + flat));
-              wt[k] = __ldg(j.weight_table + __ldg(j.weight_cells + flat));
+              tsd[k] = __ldg(j.dec + flat);
+              wt[k] = __ldg(j.wdec + flat);
             }
           }
         }
@@ -205,7 +218,32 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   const size_t o_grid = o_tab + table_bytes;
   const size_t o_best = o_grid + grid_bytes;
   const size_t total = o_best + up(sizeof(unsigned long long) * num_jobs);
-  int rc = ctx->tmp2.reserve(total);
+  // Device only, behind the uploaded blob: one decoded float image per distinct (cells, table).
+  struct Decoded {
+    const void* cells;
+    const void* table;
+    size_t cells_at, table_at, out_at, n;
+    int one_minus;
+  };
+  std::vector<Decoded> decoded;
+  size_t dec_bytes = 0;
+  auto decoded_at = [&](const void* cells, const void* table, size_t n, int one_minus) -> size_t {
+    for (const Decoded& d : decoded)
+      if (d.cells == cells && d.table == table && d.one_minus == one_minus) return d.out_at;
+    Decoded d{cells, table, grid_at[cells], table_at[table], dec_bytes, n, one_minus};
+    decoded.push_back(d);
+    dec_bytes += up(sizeof(float) * n);
+    return d.out_at;
+  };
+  std::vector<size_t> dec_of(num_jobs), wdec_of(num_jobs, 0);
+  for (int i = 0; i < num_jobs; ++i) {
+    const csm_rt_job2d& in = jobs[i];
+    const size_t n = static_cast<size_t>(in.num_x) * in.num_y;
+    dec_of[i] = decoded_at(in.cells, in.cost_table, n, in.weight_cells ? 0 : 1);
+    if (in.weight_cells) wdec_of[i] = decoded_at(in.weight_cells, in.weight_table, n, 0);
+  }
+  const size_t o_dec = total;
+  int rc = ctx->tmp2.reserve(total + dec_bytes);
   if (rc == CSM_OK) rc = ctx->pin0.reserve(total);
   if (rc != CSM_OK) return rc;
   char* pin = ctx->pin0.as<char>();
@@ -228,6 +266,8 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     j.weight_table = in.weight_cells
                          ? reinterpret_cast<const float*>(base + o_tab + table_at[in.weight_table])
                          : nullptr;
+    j.dec = reinterpret_cast<const float*>(base + o_dec + dec_of[i]);
+    j.wdec = in.weight_cells ? reinterpret_cast<const float*>(base + o_dec + wdec_of[i]) : nullptr;
     pen_at += pen_n;
   }
   for (const auto& kv : grid_at) {
@@ -243,6 +283,11 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   memset(pin + o_best, 0, sizeof(unsigned long long) * num_jobs);
   cudaStream_t st = ctx->stream;
   CSM_CUDA(cudaMemcpyAsync(base, pin, total, cudaMemcpyHostToDevice, st));
+  for (const Decoded& d : decoded)
+    ++ctx->launches, k_rt_decode<<<static_cast<unsigned int>((d.n + 255) / 256), 256, 0, st>>>(
+        reinterpret_cast<const uint16_t*>(base + o_grid + d.cells_at),
+        reinterpret_cast<const float*>(base + o_tab + d.table_at),
+        reinterpret_cast<float*>(base + o_dec + d.out_at), d.n, d.one_minus);
   CSM_CUDA(cudaFuncSetAttribute(k_rt_score, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(std::max<size_t>(smem, 1024))));
   ++ctx->launches, k_rt_score<<<dim3((max_scans + kRtWarps - 1) / kRtWarps, num_jobs), kRtWarps * 32, smem, st>>>(
