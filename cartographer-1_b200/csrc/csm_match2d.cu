@@ -341,6 +341,11 @@ k_scan_prefix(const JobDev* __restrict__ jobs, ScanInfo* __restrict__ scans,
     if (threadIdx.x == 255) carry += part[255];
     __syncthreads();
   }
+  // A lattice larger than the host's bound would make k_score_top write past this job's
+  // slice of top_scores: empty the job instead (the overflow flag fails the fetch).
+  const bool too_big = static_cast<long long>(carry) > j.cand_cap;
+  if (too_big)
+    for (int s = threadIdx.x; s < j.S; s += blockDim.x) scans[j.scan_off + s].nx = scans[j.scan_off + s].ny = 0;
   if (threadIdx.x == 0) {
     JobState st;
     st.best = 0ull;
@@ -348,7 +353,7 @@ k_scan_prefix(const JobDev* __restrict__ jobs, ScanInfo* __restrict__ scans,
     st.win = ~0ull;
     st.group_best = 0u;
     st.tie_count = 0u;
-    st.total = static_cast<unsigned int>(carry);
+    st.total = too_big ? 0u : static_cast<unsigned int>(carry);
     st.pad = 0u;
     st.scored = 0ull;
     for (int k = 0; k < 4; ++k) st.scored_phase[k] = 0ull;
@@ -1484,8 +1489,18 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
     }
     const long long ext = 2 * static_cast<long long>(std::ceil(std::sqrt(r2) / in.resolution)) + 4;
     const long long step = 1ll << (s->depth - 1);
-    const long long wx = std::min<long long>(2ll * j.lin, s->num_x - 1 + ext);
-    const long long wy = std::min<long long>(2ll * j.lin, s->num_y - 1 + ext);
+    // ShrinkToFit seeds its bounds at 0 (CSM2D.cc:78-79): the window of a scan whose cells span
+    // [a, b] is max(0, W - 1 - a) + max(0, b), clamped by the linear bound.  With the scan
+    // centred on cell c (the initial translation) and reaching e cells, a >= c - e and
+    // b <= c + e -- which also covers a scan that lies wholly outside the grid.
+    const double e = 0.5 * static_cast<double>(ext) + 2.;
+    const double cx = (in.max_y - static_cast<double>(in.init_ty)) / in.resolution;
+    const double cy = (in.max_x - static_cast<double>(in.init_tx)) / in.resolution;
+    auto window = [&](double c, int cells) {
+      const double w = std::max(0., cells - 1 - c + e) + std::max(0., c + e);
+      return static_cast<long long>(std::min(2. * j.lin, std::ceil(w)));
+    };
+    const long long wx = window(cx, s->num_x), wy = window(cy, s->num_y);
     const long long nx = wx / step + 1, ny = wy / step + 1;
     if (std::max(wx, wy) + ext > 32000) {
       set_error("job %d: search window of %lld cells exceeds the 16-bit offset range", i,

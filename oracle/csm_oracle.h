@@ -324,7 +324,8 @@ class TSDF2D {
                    kUnknownValue),
         weight_cells_(tsd_cells_.size(), kUnknownValue),
         value_to_tsd_(MakeConversionTable(min_tsd_, min_tsd_, max_tsd_)),
-        value_to_weight_(MakeConversionTable(0.f, 0.f, max_weight_)) {}
+        value_to_weight_(MakeConversionTable(0.f, 0.f, max_weight_)),
+        value_to_cost_(MakeConversionTable(max_tsd_, min_tsd_, max_tsd_)) {}
   // Adopts existing cell arrays (flat = num_x_cells * y + x).
   TSDF2D(const MapLimits& limits, const float truncation_distance, const float max_weight,
          const uint16_t* tsd_cells, const uint16_t* weight_cells)
@@ -340,7 +341,16 @@ class TSDF2D {
   const std::vector<float>& value_to_weight() const { return value_to_weight_; }
   // Grid2D's max_correspondence_cost_ of a TSDF2D is the truncation distance (tsdf_2d.cc:26).
   float GetMaxCorrespondenceCost() const { return max_tsd_; }
+  // Grid2D(limits, -truncation_distance, truncation_distance, tables) (tsdf_2d.cc:23-27).
+  float GetMinCorrespondenceCost() const { return min_tsd_; }
   float GetMinTSD() const { return min_tsd_; }
+  // Grid2D::GetCorrespondenceCost (grid_2d.h:53-57) of a TSDF2D: the base class's own table is
+  // GetConversionTable(max_cost, min_cost, max_cost) (grid_2d.cc:66-68), i.e. unknown reads
+  // +truncation_distance -- not TSDValueConverter's table, where unknown reads min_tsd.
+  float GetCorrespondenceCost(const Array2i& c) const {
+    if (!limits_.Contains(c)) return max_tsd_;
+    return value_to_cost_[tsd_cells_[limits_.cell_limits.num_x_cells * c.y + c.x]];
+  }
 
   // tsd_value_converter.h:38-56
   uint16_t TSDToValue(const float tsd) const {
@@ -369,7 +379,7 @@ class TSDF2D {
   MapLimits limits_;
   float max_tsd_, min_tsd_, max_weight_, tsd_resolution_, weight_resolution_;
   std::vector<uint16_t> tsd_cells_, weight_cells_;
-  std::vector<float> value_to_tsd_, value_to_weight_;
+  std::vector<float> value_to_tsd_, value_to_weight_, value_to_cost_;
 };
 
 // ---------------------------------------------------------------------------
@@ -645,7 +655,10 @@ class SlidingWindowMaximum {
 class PrecomputationGrid2D {
  public:
   // fast_correlative_scan_matcher_2d.cc:91-161
-  PrecomputationGrid2D(const ProbabilityGrid& grid, const CellLimits& limits, const int width,
+  // `Grid` is any Grid2D flavour (ProbabilityGrid or TSDF2D): the reference takes the base class
+  // and only calls GetCorrespondenceCost / GetMin- / GetMaxCorrespondenceCost on it.
+  template <typename Grid>
+  PrecomputationGrid2D(const Grid& grid, const CellLimits& limits, const int width,
                        std::vector<float>* scratch)
       : offset_x_(-width + 1),
         offset_y_(-width + 1),
@@ -738,7 +751,8 @@ class PrecomputationGrid2D {
 // fast_correlative_scan_matcher_2d.cc:171-186
 class PrecomputationGridStack2D {
  public:
-  PrecomputationGridStack2D(const ProbabilityGrid& grid, const int branch_and_bound_depth) {
+  template <typename Grid>
+  PrecomputationGridStack2D(const Grid& grid, const int branch_and_bound_depth) {
     ORACLE_CHECK(branch_and_bound_depth >= 1);
     std::vector<float> scratch;
     const CellLimits limits = grid.limits().cell_limits;
@@ -771,7 +785,8 @@ struct MatchStats {
 
 class FastCorrelativeScanMatcher2D {
  public:
-  FastCorrelativeScanMatcher2D(const ProbabilityGrid& grid,
+  template <typename Grid>
+  FastCorrelativeScanMatcher2D(const Grid& grid,
                                const FastCorrelativeScanMatcherOptions2D& options)
       : options_(options), limits_(grid.limits()), stack_(grid, options.branch_and_bound_depth) {}
 

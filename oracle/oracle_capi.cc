@@ -59,6 +59,15 @@ void* oracle_fcsm2d_create(void* grid, double linear_window, double angular_wind
   o.branch_and_bound_depth = depth;
   return new FastCorrelativeScanMatcher2D(*static_cast<ProbabilityGrid*>(grid), o);
 }
+// FastCorrelativeScanMatcher2D over a TSDF2D handle (oracle_tsdf2d_create): the reference takes
+// any Grid2D (fast_correlative_scan_matcher_2d.cc:91-113 uses 1.f - |GetCorrespondenceCost|).
+void* oracle_fcsm2d_create_tsdf(void* grid, double linear_window, double angular_window, int depth) {
+  FastCorrelativeScanMatcherOptions2D o;
+  o.linear_search_window = linear_window;
+  o.angular_search_window = angular_window;
+  o.branch_and_bound_depth = depth;
+  return new FastCorrelativeScanMatcher2D(*static_cast<TSDF2D*>(grid), o);
+}
 void oracle_fcsm2d_destroy(void* m) { delete static_cast<FastCorrelativeScanMatcher2D*>(m); }
 
 // Copies precomputation level `level` (wide_x * wide_y bytes) if out != NULL.

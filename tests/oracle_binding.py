@@ -75,6 +75,8 @@ def lib():
     L.oracle_grid2d_destroy.argtypes = [C.c_void_p]
     L.oracle_fcsm2d_create.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
     L.oracle_fcsm2d_create.restype = C.c_void_p
+    L.oracle_fcsm2d_create_tsdf.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    L.oracle_fcsm2d_create_tsdf.restype = C.c_void_p
     L.oracle_fcsm2d_destroy.argtypes = [C.c_void_p]
     L.oracle_fcsm2d_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int),
                                       C.POINTER(C.c_int)]
@@ -225,7 +227,8 @@ class OracleFCSM2D:
     def __init__(self, grid, linear_window, angular_window, depth):
         self.grid = grid
         self.depth = depth
-        self.h = lib().oracle_fcsm2d_create(grid.h, linear_window, angular_window, depth)
+        create = lib().oracle_fcsm2d_create_tsdf if isinstance(grid, OracleTsdf) else lib().oracle_fcsm2d_create
+        self.h = create(grid.h, linear_window, angular_window, depth)
 
     def __del__(self):
         if getattr(self, "h", None):

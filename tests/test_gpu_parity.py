@@ -286,3 +286,55 @@ def test_constraint_builder_matches_reference_semantics(csm, sampling_ratio, flu
             d = (tf[i][2] - o_out[i].pose_theta + np.pi) % (2 * np.pi) - np.pi
             assert abs(d) <= 1e-9
     assert stats[1] == found.sum()
+
+
+def test_fast_matcher_on_tsdf_grid_bit_exact(csm, gpu_ctx):
+    """FastCorrelativeScanMatcher2D takes any Grid2D: over a TSDF2D its stack is built from
+    1.f - |GetCorrespondenceCost| with the base class's table (FCSM2D.cc:97-113, grid_2d.cc:59-70;
+    unknown and out-of-grid cells read +truncation_distance).  Stack bytes, full-submap and
+    local searches against the oracle on a painted office world."""
+    import tsdf_util
+    w = synth.World(300, 260, seed=31)
+    tv, wv = tsdf_util.from_world(w, 0.3, 10.0, seed=5)
+    args = (tv, wv, w.res, w.max_x, w.max_y, 0.3, 10.0)
+    og, g = ob.OracleTsdf(*args), csm.TsdfGrid(*args)
+    depth = 6
+    om = ob.OracleFCSM2D(og, 3.0, 0.6, depth)
+    m = csm.Matcher(gpu_ctx, g, 3.0, 0.6, depth)
+    for lvl in range(depth):
+        assert np.array_equal(om.level(lvl), m.level(lvl)), "level %d differs" % lvl
+    assert len(np.unique(m.level(0))) > 10  # a real TSD profile, not two values
+    rng = np.random.default_rng(6)
+    clouds, inits = [], []
+    for i in range(6):
+        pose, pts = synth.make_scan(w, 700 + i, max_range=6.0)
+        clouds.append(pts)
+        inits.append(None if i < 3 else (pose[0] + rng.uniform(-1, 1), pose[1] + rng.uniform(-1, 1),
+                                         pose[2] + rng.uniform(-0.3, 0.3)))
+    # TSDF scores live in [1 - d, 1 + d]: a wall cell scores ~1, unknown space 1 - d = 0.7
+    res = csm.match_batch(gpu_ctx, [m] * 6, clouds, [0.8] * 6, initial=inits)
+    found = 0
+    for pts, init, r_g in zip(clouds, inits, res):
+        r_o = om.match(pts, 0.8, initial=init)
+        _compare(r_o, r_g)
+        found += r_o.found
+    assert found >= 3
+
+
+def test_scan_wholly_outside_a_small_grid(csm, gpu_ctx):
+    """ShrinkToFit seeds its bounds at 0 (CSM2D.cc:78-79), so a short-range scan placed far
+    outside a small grid keeps a window of up to linear_bound cells towards the grid: the
+    lowest-resolution lattice is larger than (grid + scan extent) / step.  The reference
+    reports no match; so must the device (no capacity error, no abort)."""
+    w = synth.World(100, 100, seed=8)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    om = ob.OracleFCSM2D(og, 7.0, 0.3, 5)
+    m = csm.Matcher(gpu_ctx, g, 7.0, 0.3, 5)
+    ang = np.linspace(0, 2 * np.pi, 40, endpoint=False)
+    pts = np.stack([0.5 * np.cos(ang), 0.5 * np.sin(ang), np.zeros(40)], 1).astype(np.float32)
+    inits = [(20.0, 0.0, 0.0), (0.0, -20.0, 0.3), (-9.0, 9.0, 0.0), (3.2, 0.0, 0.0)]
+    res = csm.match_batch(gpu_ctx, [m] * len(inits), [pts] * len(inits), [0.3] * len(inits), initial=inits)
+    for init, r_g in zip(inits, res):
+        _compare(om.match(pts, 0.3, initial=init), r_g)
+    assert res[0].found == 0 and res[1].found == 0
