@@ -1,24 +1,31 @@
 #!/usr/bin/env python
 """bench.py -- MatchFullSubmap constraint searches / s on B200 (BASELINE.json metric).
 
-Workload (config C3 of BASELINE.json / SURVEY.md 8(d)): global loop closure,
-independent (node, submap) MatchFullSubmap searches on 1000x1000-cell (50 m) synthetic
-submaps, ~360-point scans, branch_and_bound_depth 7, min_score 0.6, 30 % of the scans
-drawn inside the target submap.  The 10k-search job is sharded over the ranks with no
-data-path collective (weak scaling: every rank runs the same number of searches per
-step against its own submaps).  One step = every rank builds the precomputation stacks
-of its `--submaps` submaps and runs `--submaps x --nodes` searches against them.
+Workload = config C3 of BASELINE.json / SURVEY.md 8(d): ONE global loop-closure job of
+`--submaps` x `--nodes` (default 100 x 100 = 10 000) independent (node, submap)
+MatchFullSubmap searches on 1000x1000-cell (50 m) synthetic submaps, ~360-beam scans,
+branch_and_bound_depth 7, min_score 0.6, 30 % of a submap's scans drawn inside it.
 
-  value : searches/s over all ranks with inputs (cells, points, tables) resident in
-          HBM when the timed region starts; CUDA-event time on the context's stream,
-          max over ranks; L2 flushed (untimed) between steps.
-  e2e   : the same through the public host API from HOST buffers (grid upload, stack
-          build, search, results back on the host) every step.
+One step = the whole job.  With N ranks (one process per GPU) the job is PARTITIONED:
+`sharding.partition_searches` assigns the searches to ranks by submap affinity (greedy LPT
+on an estimated cost, a hot submap's node list split and the submap replicated), every rank
+builds the stacks of its submaps and runs its shard through the host API, rank 0 gathers the
+results in submission order.  No data-path collective; strong scaling (the job is fixed).
+
+  value : searches/s of the whole job, inputs (cells, points, tables) resident in HBM
+          when the timed region starts; CUDA events on each context's stream, MAX over
+          ranks; L2 flushed (untimed) before every step.
+  e2e   : the same from HOST buffers through the public host API every step: grid H2D,
+          stack builds, job upload, searches, results D2H and the gather of every rank's
+          results on rank 0.
+  result_sha1 : hash of the gathered result array in submission order -- identical at
+          every N (1-GPU and N-GPU runs return the same array).
   --impl reference : the reference algorithm (oracle restatement, thread-pooled like
           ConstraintBuilder2D) on the host cores, bounded sample per step.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -30,6 +37,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 sys.path.insert(0, ROOT)
 
 MIN_SCORE = 0.6
@@ -38,42 +46,85 @@ LINEAR = 7.0
 ANGULAR = float(np.deg2rad(30.0))
 
 
-def parse():
+def parse(argv=None):
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--grid", type=int, default=1000, help="submap cells per side")
-    p.add_argument("--submaps", type=int, default=4, help="submaps per rank per step")
-    p.add_argument("--nodes", type=int, default=25, help="searches per submap per step")
+    p.add_argument("--submaps", type=int, default=100, help="submaps of the job")
+    p.add_argument("--nodes", type=int, default=100, help="searches per submap")
     p.add_argument("--cpu-searches", type=int, default=0, help="CPU sample size (0 = auto)")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    return p.parse_args()
+    p.add_argument("--no-extras", action="store_true",
+                   help="skip the C1 / C2 / C4 / C5 sub-records (they run at N = 1 only)")
+    return p.parse_args(argv)
 
 
-def make_workload(args, rank):
-    """Deterministic synthetic submaps and scans (seed = 1000 * config + index).
-    Weak scaling: every rank runs a shard of the same size AND the same content (the
-    generator ignores the rank), so that value(N) / value(1) measures the machine and not
-    the luck of which scans landed on which rank; ranks never exchange data."""
-    rank = 0
+# ---------------------------------------------------------------------------------------
+# The C3 job.  Deterministic (seed = 1000 * config + index).  Every submap s has
+# 3 * ceil(nodes / 10) scans ray-cast inside it; node k of submap s is one of them when
+# k % 10 < 3 (30 % true positives) and otherwise a scan drawn inside ANOTHER submap (a
+# negative that must return "no match").
+# ---------------------------------------------------------------------------------------
+def _gen_submap(task):
     import synth
-    worlds, clouds, target = [], [], []
-    n_sub = args.submaps
-    for s in range(n_sub):
-        worlds.append(synth.World(args.grid, args.grid, seed=3000 + rank * 1000 + s))
-    decoy = synth.World(args.grid, args.grid, seed=3000 + rank * 1000 + 999)
-    for s in range(n_sub):
-        for k in range(args.nodes):
-            inside = (k % 10) < 3  # 30 % true positives
-            src = worlds[s] if inside else (worlds[(s + 1 + k) % n_sub] if n_sub > 1 and k % 2 else decoy)
-            _, pts = synth.make_scan(src, 100000 * rank + 1000 * s + k)
-            if len(pts) < 8:
-                _, pts = synth.make_scan(src, 100000 * rank + 1000 * s + k + 500)
-            clouds.append(pts)
-            target.append(s)
-    return worlds, clouds, target
+    s, grid, n_pos = task
+    w = synth.World(grid, grid, seed=3000 + s)
+    scans = []
+    for k in range(n_pos):
+        _, pts = synth.make_scan(w, 1000 * s + k)
+        if len(pts) < 8:
+            _, pts = synth.make_scan(w, 1000 * s + k + 500)
+        scans.append(pts)
+    return s, w.cells, (w.res, w.max_x, w.max_y), scans
+
+
+class Job:
+    """cells[s], limits[s]; per search (submission order, submap-major): submap[i], cloud[i]."""
+
+    def __init__(self, args, limit_submaps=None):
+        n_sub, n_nodes, grid = args.submaps, args.nodes, args.grid
+        n_pos = 3 * ((n_nodes + 9) // 10)
+        tasks = [(s, grid, n_pos) for s in range(n_sub)]
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        procs = max(1, min(len(tasks), (os.cpu_count() or 1) // max(1, world)))
+        if procs > 1:
+            import multiprocessing as mp
+            with mp.get_context("fork").Pool(procs) as pool:  # before any CUDA initialisation
+                made = pool.map(_gen_submap, tasks, chunksize=1)
+        else:
+            made = [_gen_submap(t) for t in tasks]
+        self.cells = [m[1] for m in made]
+        self.limits = [m[2] for m in made]
+        pos = [m[3] for m in made]
+        self.submap, self.clouds, self.inside = [], [], []
+        for s in range(n_sub):
+            for k in range(n_nodes):
+                inside = (k % 10) < 3
+                if inside or n_sub == 1:
+                    src, which = s, ((k // 10) * 3 + k % 10) % n_pos
+                else:
+                    src, which = (s + 1 + k % (n_sub - 1)) % n_sub, (7 * k + s) % n_pos
+                self.submap.append(s)
+                self.clouds.append(pos[src][which])
+                self.inside.append(bool(inside))
+        self.submap = np.asarray(self.submap, dtype=np.int64)
+        self.num_submaps, self.grid, self.res = n_sub, grid, self.limits[0][0]
+        self.points = np.array([len(c) for c in self.clouds], dtype=np.int64)
+        self.scans = np.array([num_scans_of(c, self.res) for c in self.clouds], dtype=np.int64)
+
+    def __len__(self):
+        return len(self.clouds)
+
+
+def num_scans_of(cloud, res):
+    """SearchParameters::num_scans for a full-submap search (CSM2D.cc:27-55)."""
+    r = max(3.0 * res, float(np.sqrt((cloud[:, 0].astype(np.float64) ** 2 +
+                                      cloud[:, 1].astype(np.float64) ** 2).max())))
+    step = (1.0 - 1e-3) * np.arccos(1.0 - res * res / (2.0 * r * r))
+    return 2 * int(np.ceil(np.pi / step)) + 1
 
 
 class ClockSampler:
@@ -131,53 +182,65 @@ class ClockSampler:
                 "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons)}
 
 
-def cpu_reference_run(args, worlds, clouds, target, n_searches, threads):
-    """Times the thread-pooled reference restatement on `n_searches` searches of the
-    workload (stack construction included, as one pool task per submap)."""
+def cpu_reference_run(job, idx, threads):
+    """Times the thread-pooled reference restatement on the searches `idx` of the job
+    (stack construction included, as one pool task per submap)."""
     import oracle_binding as ob
-    idx = list(range(min(n_searches, len(clouds))))
-    used = sorted(set(target[i] for i in idx))
+    used = sorted(set(int(job.submap[i]) for i in idx))
     remap = {s: k for k, s in enumerate(used)}
-    grids = [ob.OracleGrid(worlds[s].cells, worlds[s].res, worlds[s].max_x, worlds[s].max_y)
-             for s in used]
+    grids = [ob.OracleGrid(job.cells[s], *job.limits[s]) for s in used]
     n = len(idx)
     secs, out, stats = ob.constraint_batch(
-        threads, grids, np.zeros((len(grids), 3)), [remap[target[i]] for i in idx], [1] * n,
-        np.zeros((n, 3)), [clouds[i] for i in idx], sampling_ratio=1.0,
+        threads, grids, np.zeros((len(grids), 3)), [remap[int(job.submap[i])] for i in idx], [1] * n,
+        np.zeros((n, 3)), [job.clouds[i] for i in idx], sampling_ratio=1.0,
         global_min_score=MIN_SCORE, min_score=MIN_SCORE, linear_window=LINEAR,
         angular_window=ANGULAR, depth=DEPTH)
-    return secs, out, stats, n
+    return secs, out, stats
 
 
+def cpu_sample(job, n):
+    """`n` searches spread over the job: whole groups of 8 nodes from evenly spaced submaps, so
+    that the sample keeps the job's 30 % positives and its stack-build share."""
+    per = 8
+    subs = max(1, (n + per - 1) // per)
+    chosen = np.unique(np.linspace(0, job.num_submaps - 1, min(subs, job.num_submaps)).astype(int))
+    idx = []
+    for s in chosen:
+        idx.extend(np.nonzero(job.submap == s)[0][:max(per, (n + len(chosen) - 1) // len(chosen))].tolist())
+    return idx[:max(n, 1)]
 
 
-def workload_config(args, world, n_search, n_pts):
-    return {"workload": "C3 2D global loop closure: MatchFullSubmap on %dx%d submaps, depth %d, "
-                        "min_score %.2f, 30%% true positives" % (args.grid, args.grid, DEPTH, MIN_SCORE),
-            "submaps_per_rank_per_step": args.submaps, "searches_per_rank_per_step": n_search,
+def workload_config(args, world, job, n_pts):
+    return {"workload": "C3 2D global loop closure: one job of %d (node, submap) MatchFullSubmap searches "
+                        "on %d submaps of %dx%d cells (50 m), depth %d, min_score %.2f, 30%% true positives"
+                        % (len(job), args.submaps, args.grid, args.grid, DEPTH, MIN_SCORE),
+            "searches_per_step": len(job), "submaps": args.submaps,
             "mean_points_per_scan": n_pts,
-            "l2": "flushed between steps (256 MiB write, untimed); stacks + work lists of a step "
-                  "exceed L2",
-            "parallelism": "independent searches sharded over %d ranks by submap (identical synthetic "
-                           "shard per rank), no collective" % world}
+            "l2": "flushed before every step (256 MiB write, untimed); the %d stacks of a step (36 MB "
+                  "each with their quad words) exceed L2" % args.submaps,
+            "parallelism": "one job partitioned over %d ranks by submap affinity (LPT on estimated cost, "
+                           "hot submaps replicated), results gathered on rank 0 in submission order; no "
+                           "data-path collective" % world}
 
 
 def run_reference(args):
     """The reference algorithm on the host cores: thread-pooled oracle restatement driven
     like ConstraintBuilder2D (one pool task per stack build, one per search).  The
     reference's own sources cannot be built here (Eigen, glog, abseil, protobuf, Lua,
-    Ceres absent), so kind = "port".  Each step is a bounded sample of the workload."""
+    Ceres absent), so kind = "port".  Each step is a bounded sample of the job."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    worlds, clouds, target = make_workload(args, 0)
-    n = args.cpu_searches or max(4, min(len(clouds), 2 * threads))
+    # the sample touches few submaps: generate only those
+    n = args.cpu_searches or max(8, 2 * threads)
+    job = Job(args)
+    idx = cpu_sample(job, n)
     times, total_scored = [], 0.0
     steps, warmup = args.steps, args.warmup
     it = 0
     while it < warmup + steps:
-        secs, out, stats, n_done = cpu_reference_run(args, worlds, clouds, target, n, threads)
+        secs, out, stats = cpu_reference_run(job, idx, threads)
         if it >= warmup:
             times.append(secs)
             total_scored += stats[0] + stats[1]
@@ -186,43 +249,80 @@ def run_reference(args):
             steps = max(1, min(steps, int(200 / secs) - warmup))
         it += 1
     total = sum(times)
-    value = n_done * len(times) / total
-    n_pts = float(np.mean([len(c) for c in clouds]))
+    value = len(idx) * len(times) / total
+    n_pts = float(job.points.mean())
     line = {
         "impl": "reference", "metric": "MatchFullSubmap constraint searches/sec",
         "value": value, "unit": "searches/s", "n_gpus": args.gpus, "steps": len(times),
         "warmup": warmup, "ms_per_step": 1000.0 * total / len(times),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": workload_config(args, max(1, args.gpus), len(clouds), n_pts),
+        "config": workload_config(args, max(1, args.gpus), job, n_pts),
         "candidate_scores_per_s": total_scored / total,
         "cpu_baseline": {"value": value, "unit": "searches/s", "cores": threads, "kind": "port",
-                         "sample": "%d searches per step over %d submaps (stack builds included), "
-                                   "thread-pooled oracle restatement of ConstraintBuilder2D; the "
-                                   "reference sources are unbuildable here" %
-                                   (n_done, len(set(target[:n_done])))},
+                         "sample": "%d searches of the job per step over %d submaps (stack builds included), "
+                                   "thread-pooled oracle restatement of ConstraintBuilder2D on %d host "
+                                   "threads; the reference sources are unbuildable here" %
+                                   (len(idx), len(set(int(job.submap[i]) for i in idx)), threads)},
         "e2e": {"value": value, "unit": "searches/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
     }
     emit(line)
 
 
-def num_scans_of(cloud, res):
-    """SearchParameters::num_scans for a full-submap search (CSM2D.cc:27-55), for byte counts."""
-    r = max(3.0 * res, float(np.sqrt((cloud[:, 0].astype(np.float64) ** 2 +
-                                      cloud[:, 1].astype(np.float64) ** 2).max())))
-    step = (1.0 - 1e-3) * np.arccos(1.0 - res * res / (2.0 * r * r))
-    return 2 * int(np.ceil(np.pi / step)) + 1
+def _load_sharding():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "csm_sharding", os.path.join(ROOT, "cartographer-1_b200", "sharding.py"))
+    sh = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sh)
+    return sh
+
+
+def time_grid_broadcast(torch, dist, world, local, sizes=(2000000, 8000000), reps=10):
+    """A new submap's uint16 grid reaching every replica: NCCL broadcast over NVLink from the
+    owner's HBM against the alternative of each replica copying it from pinned host memory
+    ("measure both").  Device-timed, max over ranks, microseconds."""
+    out = {}
+    for nbytes in sizes:
+        dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        res = {}
+        for name in (("nccl_broadcast", "h2d_copy") if world > 1 else ("h2d_copy",)):
+            for it in range(3 + reps):
+                if it == 3:
+                    if world > 1:
+                        dist.barrier()
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                if name == "nccl_broadcast":
+                    dist.broadcast(dev, src=0)
+                else:
+                    dev.copy_(host, non_blocking=True)
+            e1.record()
+            e1.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res[name + "_us"] = 1e3 * float(t[0])
+        res["gbs"] = {k[:-3]: nbytes / (v * 1e-6) / 1e9 for k, v in res.items()}
+        out["%d_bytes" % nbytes] = res
+    return out
 
 
 def run_b200(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    t_gen = time.time()
+    job = Job(args)  # forks worker processes: must precede CUDA initialisation
+    t_gen = time.time() - t_gen
     import torch
     import torch.distributed as dist
     from __graft_entry__ import _load_package
     pkg = _load_package()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    sh = _load_sharding()
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the scan matcher has no CPU fallback")
     torch.cuda.set_device(local)
@@ -234,27 +334,42 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    worlds, clouds, target = make_workload(args, rank)
-    n_search = len(clouds)
+    # ---- partition of the job (identical on every rank: deterministic inputs) ----------
+    n_total = len(job)
+    cost = sh.search_costs(job.points, job.scans)
+    owner = sh.partition_searches(job.submap, cost, job.num_submaps, world)
+    shard_sizes = np.bincount(owner, minlength=world)
+    idx = np.nonzero(owner == rank)[0]
+    my_submaps = sorted(set(int(s) for s in job.submap[idx]))
+    slot = {s: k for k, s in enumerate(my_submaps)}
+    replicated = sum(1 for r in sh.replicas(job.submap, owner, job.num_submaps) if len(r) > 1)
+    clouds = [job.clouds[i] for i in idx]
+    target = [slot[int(job.submap[i])] for i in idx]
+    n_search = len(idx)
+
     ctx = pkg.Context(local)
     raw = C.c_void_p(ctx.raw)
-    grids = [pkg.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    grids = [pkg.Grid(job.cells[s], *job.limits[s]) for s in my_submaps]
     matchers = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
-    cells_dev = [torch.from_numpy(w.cells.view(np.int16)).cuda() for w in worlds]
+    cells_dev = [torch.from_numpy(job.cells[s].view(np.int16)).cuda() for s in my_submaps]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     batch = pkg.PreparedBatch(ctx, [matchers[t] for t in target], clouds, [MIN_SCORE] * n_search)
     abi = pkg.abi()
     stream = torch.cuda.ExternalStream(abi.csm_ctx_stream(raw))
 
-    def timed(fn):
-        """One step: L2 flush (untimed), then `fn` bracketed by CUDA events on the
-        context's stream.  Returns (result, milliseconds)."""
+    def timed(fn, end_on_current_stream=False):
+        """One step: L2 flush (untimed), then `fn` bracketed by CUDA events; the first on the
+        context's stream, the second there too or (e2e: the gather runs on torch's stream
+        after the results reached the host) on the current stream.  (result, ms)."""
         flush.fill_(1)  # 256 MiB write > 126 MB L2
-        torch.cuda.synchronize()
+        barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         out = fn()
-        e1.record(stream)
+        if end_on_current_stream:
+            e1.record()
+        else:
+            e1.record(stream)
         e1.synchronize()
         return out, e0.elapsed_time(e1)
 
@@ -274,9 +389,14 @@ def run_b200(args):
         return res
 
     def e2e_step():
-        # host buffers in, host results out: grid H2D + stack build + upload + search + D2H
+        # host buffers in, gathered host results out: grid H2D + stack builds + upload +
+        # searches + D2H + gather of every rank's results on rank 0 (one collective)
         ms = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
-        return pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
+        res = pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
+        packed = sh.pack_results(idx, res)
+        if world > 1:
+            return sh.gather_packed(packed, shard_sizes, n_total, device=torch.device("cuda", local))
+        return packed
 
     # ---- device-resident arm ---------------------------------------------------------
     sampler = ClockSampler(local)
@@ -299,128 +419,121 @@ def run_b200(args):
     phase_scored = (C.c_double * 5)()
     runs = C.c_int()
     abi.csm_ctx_get_profile(raw, phase_ms, phase_scored, C.byref(runs))
+    import roofline2d
+    timed_profile = roofline2d.depth_profile(abi, raw)
     abi.csm_ctx_set_profiling(raw, 0)
     build = sum(a.elapsed_time(b) for a, b in build_ms) / max(1, len(build_ms))
-    scored_per_step = sum(r.candidates_scored for r in res)
+    scored_per_step = float(sum(r.candidates_scored for r in res))
     lookups_per_step = float(sum(r.candidates_scored * len(c) for r, c in zip(res, clouds)))
     found = sum(1 for r in res if r.found)
     ties = sum(1 for r in res if r.tie_resolution)
 
     # ---- end-to-end arm ----------------------------------------------------------------
-    for _ in range(min(args.warmup, 3)):
-        timed(e2e_step)
+    for _ in range(min(args.warmup, 2)):
+        timed(e2e_step, True)
     barrier()
     ms_e2e = 0.0
     for _ in range(args.steps):
-        out, ms = timed(e2e_step)
+        gathered, ms = timed(e2e_step, True)
         ms_e2e += ms
     barrier()
-    for a, b in zip(out, res):
-        assert (a.found, a.scan_index, a.x_index_offset, a.y_index_offset) == \
-               (b.found, b.scan_index, b.x_index_offset, b.y_index_offset)
+    mine = sh.pack_results(idx, res)
+    assert np.array_equal(gathered[idx] if world > 1 else gathered, mine), \
+        "the end-to-end results differ from the resident ones"
+    result_sha1 = hashlib.sha1(np.ascontiguousarray(gathered[:, 1:]).tobytes()).hexdigest()
 
-    times = torch.tensor([ms_resident, ms_e2e], dtype=torch.float64, device="cuda")
+    # ---- whole-job totals over ranks -----------------------------------------------------
+    tot = torch.tensor([scored_per_step, lookups_per_step, float(found), float(ties), float(launches),
+                        float(replicated if rank == 0 else 0)], dtype=torch.float64, device="cuda")
+    mx = torch.tensor([ms_resident, ms_e2e, build] + [phase_ms[k] for k in range(5)],
+                      dtype=torch.float64, device="cuda")
+    per_rank = torch.zeros(world, dtype=torch.float64, device="cuda")
+    per_rank[rank] = ms_resident / args.steps
     if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms_resident, ms_e2e = float(times[0]), float(times[1])
-    total_searches = world * n_search * args.steps
-    value = total_searches / (ms_resident * 1e-3)
-    e2e_value = total_searches / (ms_e2e * 1e-3)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(per_rank, op=dist.ReduceOp.SUM)
+        mx_all = mx.clone()
+        dist.all_reduce(mx_all, op=dist.ReduceOp.MAX)
+        ms_resident, ms_e2e = float(mx_all[0]), float(mx_all[1])
+    scored_job, lookups_job, found_job, ties_job, launches_job = (float(tot[k]) for k in range(5))
+    value = n_total * args.steps / (ms_resident * 1e-3)
+    e2e_value = n_total * args.steps / (ms_e2e * 1e-3)
+    broadcast = time_grid_broadcast(torch, dist, world, local)
 
-    n_pts = float(np.mean([len(c) for c in clouds]))
-    res0 = worlds[0].res
-    h2d = sum(w.cells.nbytes + 65536 for w in worlds) + sum(
-        c.nbytes + 8 * num_scans_of(c, res0) + 160 for c in clouds)
-    d2h = n_search * 40
+    n_pts = float(job.points.mean())
+    res0 = job.res
+    h2d = sum(job.cells[s].nbytes + 65536 for s in range(job.num_submaps)) + sum(
+        c.nbytes + 8 * int(k) + 160 for c, k in zip(job.clouds, job.scans))
+    d2h = n_total * 40
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured"
     else:
         peak, peak_src = 6650.0, "fallback"
-    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
-    traffic = json.load(open(traffic_path)) if os.path.exists(traffic_path) else {}
 
-    # Dominant kernel: k_expand, the level-synchronous tile expansion (6 launches per
-    # batch).  Algorithmic bytes = 1 B per (candidate, point) lookup.
-    steps = max(1, runs.value)  # profiled batch runs (a step may split into several)
-    names = ["k_discretize", "k_score_top", "k_dive", "k_expand", "phase2"]
-    dom = int(np.argmax(list(phase_ms)))
-    launches_of_dom = {"k_expand": DEPTH - 1}.get(names[dom], 1) * steps
-    dom_bytes = phase_scored[dom] * n_pts
-    dom_s = phase_ms[dom] / 1000.0
-    achieved = dom_bytes / dom_s / 1e9 if dom_s > 0 else 0.0
-
-    # Gather roofline G_L2: naive 1-byte gathers, warp per candidate,
-    # lane per point, L2-resident table of the stack's size, this workload's scan shape.
-    xy, _ = pkg.discretize(ctx, res0, worlds[0].max_x, worlds[0].max_y, args.grid, args.grid,
-                           clouds[0], (0.0, 0.0, 0.3), 1.0, 0.0, shrink=False)
-    pts_xy = np.ascontiguousarray(xy[0], dtype=np.int32)
-    stack_bytes = sum((args.grid + 2 ** i - 1) ** 2 for i in range(DEPTH))
-    g_l2 = C.c_double()
-    rc = abi.csm_measure_gather_rate(raw, C.c_size_t(stack_bytes), args.grid + 63,
-                                     pts_xy.ctypes.data_as(C.c_void_p), len(pts_xy), 1 << 21, 3,
-                                     C.byref(g_l2))
-    assert rc == 0, abi.csm_last_error()
-    search_ms = sum(phase_ms) / steps
     line = {
         "metric": "MatchFullSubmap constraint searches/sec", "value": value, "unit": "searches/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_resident / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": ms_resident / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": workload_config(args, world, n_search, n_pts),
-        "candidate_scores_per_s": world * scored_per_step * args.steps / (ms_resident * 1e-3),
-        "candidates_scored_per_search": scored_per_step / n_search,
-        "found": found, "host_tie_replays": ties,
+        "config": workload_config(args, world, job, n_pts),
+        "candidate_scores_per_s": scored_job * args.steps / (ms_resident * 1e-3),
+        "candidates_scored_per_search": scored_job / n_total,
+        "found": int(found_job), "host_tie_replays": int(ties_job),
+        "result_sha1": result_sha1,
         "e2e": {"value": e2e_value, "unit": "searches/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": int(launches),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+                "includes": "grid H2D, stack builds, job upload, searches, results D2H, gather on rank 0"},
+        "gpu_launches": int(launches_job),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": {"k_expand": "k_expand_nodes"}.get(names[dom], names[dom]),
-                     "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic.get(names[dom]),
-                     "peak_source": peak_src,
-                     "launch_ms": phase_ms[dom] / launches_of_dom,
-                     "algorithmic_bytes_per_launch": dom_bytes / launches_of_dom,
-                     "note": "algorithmic bytes = 1 B per (candidate, point) lookup; the stack is "
-                             "L2-resident (97-99 % L2 hits, traffic = DRAM bytes of the largest "
-                             "launch), so the HBM peak is a loose bound: the unit that saturates "
-                             "is the L1 data pipe, 85-88 % of its peak under ncu "
-                             "(profiles/r01_v8_summary.md, DESIGN.md section 3)"},
-        "gather_roofline": {"g_l2_lookups_per_s": g_l2.value,
-                            "achieved_lookups_per_s": lookups_per_step / (search_ms * 1e-3),
-                            "frac": lookups_per_step / (search_ms * 1e-3) / g_l2.value,
-                            "searches_per_s_at_g_l2": g_l2.value / (lookups_per_step / n_search),
-                            "how": "csm_measure_gather_rate: %d-byte table, %d-point scan, 2^21 "
-                                   "candidates x 3" % (stack_bytes, len(pts_xy)),
-                            "note": "G_L2 is the rate of the reference's naive pattern (one byte per "
-                                    "candidate and point, SURVEY 8(d)); the quad-phase layout serves 4 "
-                                    "lookups per 4-byte load from neighbouring words, so frac > 1 is a "
-                                    "speed-up over that pattern, not a fraction of a ceiling"},
-        "phase_ms_per_step": {n: phase_ms[i] / args.steps for i, n in enumerate(names)},
-        "phase_candidates_per_step": {n: phase_scored[i] / args.steps for i, n in enumerate(names)},
-        "stack_build": {"ms_per_step": build, "submaps": len(matchers),
-                        "algorithmic_gbs": (len(matchers) * (2 * args.grid ** 2 + stack_bytes)) /
-                        (build * 1e6) if build > 0 else None},
+        "partition": {"searches_per_rank": [int(x) for x in shard_sizes],
+                      "replicated_submaps": int(tot[5]),
+                      "resident_ms_per_step_per_rank": [float(x) for x in per_rank.cpu()],
+                      "idle_fraction_of_slowest": [float(1.0 - x / max(1e-9, float(per_rank.max())))
+                                                   for x in per_rank.cpu()],
+                      "estimated_cost_imbalance": float(np.bincount(owner, weights=cost, minlength=world).max() /
+                                                        (cost.sum() / world))},
+        "grid_broadcast_us": broadcast,
+        "workload_generation_s": t_gen,
     }
+    names = ["k_discretize", "k_score_top", "k_dive", "k_expand", "phase2"]
+    line["phase_ms_per_step"] = {n: phase_ms[i] / args.steps for i, n in enumerate(names)}
+    line["phase_candidates_per_step"] = {n: phase_scored[i] / args.steps for i, n in enumerate(names)}
+    if rank == 0:  # rank 0's shard: per-depth times of its own launches against the measured ceiling
+        xy, _ = pkg.discretize(ctx, res0, job.limits[my_submaps[0]][1], job.limits[my_submaps[0]][2],
+                               args.grid, args.grid, clouds[0], (0.0, 0.0, 0.3), 1.0, 0.0, shrink=False)
+        line.update(roofline2d.measure(
+            pkg, abi, raw, timed_profile, max(1, runs.value) // max(1, args.steps), list(phase_ms),
+            list(phase_scored), args.steps, float(np.mean([len(c) for c in clouds])), args.grid, DEPTH,
+            peak, peak_src, resident_step, np.ascontiguousarray(xy[0], dtype=np.int32)))
+    line["stack_build"] = {"ms_per_step": build, "submaps": len(matchers),
+                           "algorithmic_gbs": (len(matchers) * (2 * args.grid ** 2 + sum(
+                               (args.grid + 2 ** i - 1) ** 2 for i in range(DEPTH)))) / (build * 1e6)
+                           if build > 0 else None}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        n = args.cpu_searches or max(4, min(n_search, 4 * threads))
-        secs, cpu_out, stats, n_done = cpu_reference_run(args, worlds, clouds, target, n, threads)
-        for i in range(n_done):  # the oracle doubles as a full-size parity check
-            a, b = cpu_out[i], res[i]
+        n = args.cpu_searches or max(8, min(n_total, 4 * threads))
+        sample = cpu_sample(job, n)
+        secs, cpu_out, stats = cpu_reference_run(job, sample, threads)
+        for k, i in enumerate(sample):  # the oracle doubles as a full-size parity check
+            a, b = cpu_out[k], res[i]
             assert a.found == b.found and (not a.found or (
                 a.scan_index, a.x_index_offset, a.y_index_offset, a.score) == (
                 b.scan_index, b.x_index_offset, b.y_index_offset, b.score)), "parity broke at %d" % i
         line["cpu_baseline"] = {
-            "value": n_done / secs, "unit": "searches/s", "cores": threads, "kind": "port",
-            "sample": "first %d searches of the step, thread-pooled oracle restatement "
-                      "(ConstraintBuilder2D shape, stack builds included), %.1f s; results "
-                      "identical to the GPU's" % (n_done, secs),
+            "value": len(sample) / secs, "unit": "searches/s", "cores": threads, "kind": "port",
+            "sample": "%d searches of the job over %d submaps, thread-pooled oracle restatement "
+                      "(ConstraintBuilder2D shape, stack builds included) on %d host threads, %.1f s; "
+                      "results identical to the GPU's" %
+                      (len(sample), len(set(int(job.submap[i]) for i in sample)), threads, secs),
             "candidate_scores_per_s": (stats[0] + stats[1]) / secs}
+    if rank == 0 and world == 1 and not args.no_extras:
+        import extra_configs
+        line["extra"] = {"configs": extra_configs.measure_all(pkg, ctx, torch, peak)}
     if rank == 0:
         emit(line)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -60,6 +60,7 @@ ABI_SYMBOLS = [
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
     "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch", "csm_grid2d_create", "csm_grid2d_insert",
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
+    "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile",
 ]
 
 _abi = None
@@ -81,6 +82,9 @@ def abi():
         _abi.csm_ctx_launch_count.argtypes = [C.c_void_p]
         _abi.csm_measure_gather_rate.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int,
                                                  C.c_uint, C.c_int, C.POINTER(C.c_double)]
+        _abi.csm_measure_gather_ceiling.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_uint, C.c_int, C.c_int,
+                                                    C.POINTER(C.c_double)]
+        _abi.csm_ctx_get_depth_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     return _abi
 
 
@@ -135,6 +139,8 @@ def host():
     L.csmh_constraint_builder_run.argtypes = [
         C.c_int, i32p, C.c_int, C.c_int, C.c_int, f64p, C.c_int, C.POINTER(C.c_void_p), f64p,
         C.c_int, i32p, i32p, f64p, f32p, i64p, i32p, f64p, f64p]
+    L.csmh_constraint_builder_run2.restype = C.c_double
+    L.csmh_constraint_builder_run2.argtypes = L.csmh_constraint_builder_run.argtypes + [C.c_int, C.c_int, f64p]
     L.csmh_fcsm3d_create.restype = C.c_void_p
     L.csmh_fcsm3d_create.argtypes = [C.c_void_p, C.c_float, i32p, u16p, C.c_int, C.c_float, i32p, u16p,
                                      C.c_int, f32p, C.c_int, f64p]
@@ -404,9 +410,11 @@ def constraint_builder_run(grids, submap_poses, search_submap, search_full, rel_
                            sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
                            global_min_score=0.6, linear_window=7.0,
                            angular_window=float(np.deg2rad(30.0)), translation_weight=1.1e4,
-                           rotation_weight=1e5, ceres=None):
+                           rotation_weight=1e5, ceres=None, burst=0, extended=False):
     """Drives ConstraintBuilder2D (MaybeAdd*Constraint / NotifyEndOfNode / WhenDone) over the
-    given searches; returns (seconds, found[int32 n], transform[n, 3], stats[4])."""
+    given searches; returns (seconds, found[int32 n], transform[n, 3], stats[4]).  burst > 0:
+    the searches enter through MaybeAddConstraints in bursts of that many requests.  extended:
+    stats is the 32-double record of csmh_constraint_builder_run2 (metrics, per-device counts)."""
     n = len(clouds)
     handles = (C.c_void_p * len(grids))(*[g.h for g in grids])
     dev = np.ascontiguousarray(devices, dtype=np.int32)
@@ -424,14 +432,15 @@ def constraint_builder_run(grids, submap_poses, search_submap, search_full, rel_
     found = np.zeros(n, dtype=np.int32)
     transform = np.zeros((n, 3), dtype=np.float64)
     stats = np.zeros(4, dtype=np.float64)
-    secs = host().csmh_constraint_builder_run(
+    ext = np.zeros(32, dtype=np.float64)
+    secs = host().csmh_constraint_builder_run2(
         len(dev), dev, pool_threads, flush_threshold, depth, opts, len(grids), handles,
         np.ascontiguousarray(submap_poses, dtype=np.float64).reshape(-1), n,
         np.ascontiguousarray(search_submap, dtype=np.int32),
         np.ascontiguousarray(search_full, dtype=np.int32),
         np.ascontiguousarray(rel_poses, dtype=np.float64).reshape(-1), xyz, offsets, found,
-        transform.reshape(-1), stats)
-    return secs, found, transform, stats
+        transform.reshape(-1), stats, 1 if burst > 0 else 0, int(burst), ext)
+    return secs, found, transform, (ext if extended else stats)
 
 
 class PreparedBatch:

@@ -97,6 +97,10 @@ struct csm_ctx {
   bool sweep_tiles = false;             // CSM_SWEEP=tiles: the tile sweep instead of node lists
   bool expand_noalloc = false;          // CSM_EXPAND_LOAD=noalloc: L1::no_allocate loads in the sweep
   unsigned long long frontier_cap = 0;  // unused (capacities come from the buffers)
+  // Work-list sizes learned from earlier batches on this context, per lowest-resolution
+  // candidate: a batch that overflowed a list (and was replayed) makes the next ones ask for
+  // enough up front.
+  double frontier_per_candidate = 0.5, contenders_per_candidate = 0.;
   // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
   static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2
   int profiling = 0;  // 0 off, 1 phase events, 2 + tile histogram
@@ -105,6 +109,12 @@ struct csm_ctx {
   int profiled_runs = 0;
   unsigned long long launches = 0;  // kernels launched through this context so far
   double tile_hist[CSM_MAX_DEPTH * 33] = {0};  // expanded tiles by [depth][alive nodes]
+  // Per-depth profile of the 2D node sweep (csm_ctx_get_depth_profile): kDepthFields doubles
+  // per depth = expand kernel ms, list bookkeeping ms (seed / prefix / place), and -- with
+  // profiling 2 -- work items, warp load requests, lane loads, 32-byte sectors and 128-byte
+  // lines those requests touch, nodes.
+  static constexpr int kDepthFields = 8;
+  double depth_profile[CSM_MAX_DEPTH * kDepthFields] = {0};
 };
 
 namespace csm {

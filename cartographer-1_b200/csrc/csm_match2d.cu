@@ -1129,6 +1129,56 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
   }
 }
 
+// Profiling only (csm_ctx_set_profiling(ctx, 2)): what the work items of depth d ask of the
+// memory system.  One warp per item; per item and scan point the sweep issues ONE warp-wide
+// 4-byte load whose lanes read quad[P + nj * in + ni].  The 32-byte sectors (128-byte lines)
+// that request touches are the distinct (nj, (ni + a) >> 3) ((ni + a) >> 5) over the alive
+// lanes, a = the point's alignment inside a sector (line): averaged over all alignments.
+// stats[d * 6 ..] += items, requests (points; the few points the sweep drops at the plane's
+// border are counted too), lane loads, sectors, lines, nodes.
+__global__ void __launch_bounds__(256)
+k_item_stats(const JobDev* __restrict__ jobs, const unsigned int* __restrict__ bucket_js,
+             const unsigned int* __restrict__ nodes, const uint2* __restrict__ items,
+             const unsigned int* __restrict__ counters, int d, unsigned long long item_cap,
+             double* __restrict__ stats) {
+  const unsigned int count =
+      static_cast<unsigned int>(min(static_cast<unsigned long long>(counters[kCntItems + d]), item_cap));
+  const int lane = threadIdx.x & 31;
+  const unsigned int warps = gridDim.x * (blockDim.x >> 5);
+  double acc[6] = {0., 0., 0., 0., 0., 0.};
+  for (unsigned int it = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); it < count; it += warps) {
+    const uint2 item = items[it];
+    const int cnt = static_cast<int>(item.y & 31u) + 1;
+    const unsigned int js = bucket_js[item.y >> 5];
+    const int n = jobs[js >> 16].n;
+    const bool alive = lane < cnt;
+    const unsigned int mask = __ballot_sync(kFull, alive);
+    int sectors = 0, lines = 0;
+    if (alive) {
+      const unsigned int node = nodes[item.x + lane];
+      const unsigned int ni = node & 0xFFFFu, nj = node >> 16;
+      for (unsigned int a = 0; a < 8; ++a) {
+        const unsigned int m = __match_any_sync(mask, (nj << 16) | ((ni + a) >> 3));
+        sectors += __popc(__ballot_sync(mask, lane == __ffs(m) - 1));
+      }
+      for (unsigned int a = 0; a < 32; a += 8) {
+        const unsigned int m = __match_any_sync(mask, (nj << 16) | ((ni + a) >> 5));
+        lines += __popc(__ballot_sync(mask, lane == __ffs(m) - 1));
+      }
+    }
+    sectors = __shfl_sync(kFull, sectors, 0);
+    lines = __shfl_sync(kFull, lines, 0);
+    acc[0] += 1.;
+    acc[1] += n;
+    acc[2] += static_cast<double>(cnt) * n;
+    acc[3] += n * (sectors / 8.);
+    acc[4] += n * (lines / 4.);
+    acc[5] += cnt;
+  }
+  if (lane == 0 && acc[0] > 0.)
+    for (int k = 0; k < 6; ++k) atomicAdd(&stats[d * 6 + k], acc[k]);
+}
+
 // ---------------------------------------------------------------------------
 // 6. phase 2: which leaf attaining S* does the reference's DFS reach first?
 // ---------------------------------------------------------------------------
@@ -1343,6 +1393,7 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   const size_t o_cnt = take(sizeof(unsigned int) * kNumCounters);
   const size_t o_res = take(sizeof(csm_result2d) * b->num_jobs);
   const size_t o_hist = take(sizeof(unsigned long long) * CSM_MAX_DEPTH * 33);
+  const size_t o_dstats = take(sizeof(double) * CSM_MAX_DEPTH * 6);
   // per bucket (= scan of a job): owner, counter, list offset, work-item offset
   const size_t o_bjs = take(sizeof(unsigned int) * b->total_scans);
   const size_t o_bcnt = take(sizeof(unsigned int) * b->total_scans);
@@ -1369,11 +1420,24 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   b->counters = reinterpret_cast<unsigned int*>(base + o_cnt);
   b->results_dev = reinterpret_cast<csm_result2d*>(base + o_res);
   b->hist = reinterpret_cast<unsigned long long*>(base + o_hist);
+  b->depth_stats = reinterpret_cast<double*>(base + o_dstats);
   b->bucket_js = reinterpret_cast<unsigned int*>(base + o_bjs);
   b->bucket_cnt = reinterpret_cast<unsigned int*>(base + o_bcnt);
   b->bucket_start = reinterpret_cast<unsigned int*>(base + o_bstart);
   b->bucket_istart = reinterpret_cast<unsigned int*>(base + o_bistart);
   return CSM_OK;
+}
+
+// The batch's pinned block: [jobs | points | quats | results | counters].
+csm_result2d* pinned_results(const csm_batch2d* b) {
+  const size_t s_jobs = align_up(sizeof(JobDev) * b->num_jobs);
+  const size_t s_pts = align_up(sizeof(float) * 3 * b->total_pts);
+  const size_t s_quat = align_up(sizeof(float) * 2 * b->total_scans);
+  return reinterpret_cast<csm_result2d*>(static_cast<char*>(b->pinned) + s_jobs + s_pts + s_quat);
+}
+unsigned int* pinned_counters(const csm_batch2d* b) {
+  return reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(pinned_results(b)) +
+                                         align_up(sizeof(csm_result2d) * b->num_jobs));
 }
 
 // Host -> device copy of job descriptors, points and quaternion tables through the
@@ -1401,7 +1465,14 @@ int csm_ctx_set_profiling(csm_ctx* ctx, int enabled) {
   ctx->profiling = enabled;
   for (int k = 0; k < csm_ctx::kPhases; ++k) ctx->phase_ms[k] = ctx->phase_scored[k] = 0.;
   for (double& v : ctx->tile_hist) v = 0.;
+  for (double& v : ctx->depth_profile) v = 0.;
   ctx->profiled_runs = 0;
+  return CSM_OK;
+}
+
+int csm_ctx_get_depth_profile(csm_ctx* ctx, double* out) {
+  CSM_REQUIRE(ctx != nullptr && out != nullptr, "NULL argument");
+  for (int k = 0; k < CSM_MAX_DEPTH * csm_ctx::kDepthFields; ++k) out[k] = ctx->depth_profile[k];
   return CSM_OK;
 }
 
@@ -1425,10 +1496,14 @@ void csm_batch2d_destroy(csm_ctx* ctx, csm_batch2d* b) {
   if (!b) return;
   if (ctx) {
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    // A batch that was fetched after its last run has nothing in flight: its blocks can go
+    // back to the pool while later batches are still queued on the stream.
+    if (!b->idle) cudaStreamSynchronize(ctx->stream);
   }
   free_batch_device(b);
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
+  for (cudaEvent_t e : b->depth_events) cudaEventDestroy(e);
+  if (b->done) cudaEventDestroy(b->done);
   if (b->pinned) {
     if (b->owner) b->owner->pool.give(true, b->pinned, b->pinned_cap);
     else cudaFreeHost(b->pinned);
@@ -1525,7 +1600,7 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
   const size_t s_pts = align_up(sizeof(float) * 3 * b->total_pts);
   const size_t s_quat = align_up(sizeof(float) * 2 * b->total_scans);
   const size_t s_res = align_up(sizeof(csm_result2d) * num_jobs);
-  b->pinned_bytes = s_jobs + s_pts + s_quat + s_res;
+  b->pinned_bytes = s_jobs + s_pts + s_quat + s_res + align_up(sizeof(unsigned int) * kNumCounters);
   b->owner = ctx;
   if (ctx->pool.take(true, b->pinned_bytes, &b->pinned, &b->pinned_cap) != CSM_OK) {
     set_error("pinned allocation of %zu bytes failed: %s", b->pinned_bytes,
@@ -1543,8 +1618,10 @@ int csm_batch2d_upload(csm_ctx* ctx, const csm_job2d* jobs, int num_jobs, csm_ba
     if (j.S > 0) memcpy(pquat + 2 * j.quat_off, jobs[i].scan_quat, sizeof(float) * 2 * j.S);
   }
   // Tiles per frontier buffer; an overflow regrows it and replays the batch (fetch).
-  b->frontier_want = static_cast<unsigned long long>(b->total_cand) / 2ull + (1ull << 20);
-  int rc = allocate_batch(b, 1u << 20);
+  b->frontier_want = static_cast<unsigned long long>(ctx->frontier_per_candidate * static_cast<double>(b->total_cand)) +
+                     (1ull << 20);
+  const double want_contenders = ctx->contenders_per_candidate * static_cast<double>(b->total_cand);
+  int rc = allocate_batch(b, static_cast<unsigned int>(std::min(4.0e9, std::max(1048576., want_contenders))));
   if (rc == CSM_OK) rc = copy_inputs(ctx, b);
   if (rc != CSM_OK) {
     csm_batch2d_destroy(nullptr, b);
@@ -1587,8 +1664,21 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   uint2* const node_items =
       want_aux ? reinterpret_cast<uint2*>(ctx->frontier_aux.as<char>() + o_items) : nullptr;
   CSM_CUDA(cudaMemsetAsync(b->counters, 0, sizeof(unsigned int) * kNumCounters, st));
-  if (ctx->profiling >= 2)
+  if (ctx->profiling >= 2) {
     CSM_CUDA(cudaMemsetAsync(b->hist, 0, sizeof(unsigned long long) * CSM_MAX_DEPTH * 33, st));
+    CSM_CUDA(cudaMemsetAsync(b->depth_stats, 0, sizeof(double) * CSM_MAX_DEPTH * 6, st));
+  }
+  for (cudaEvent_t e : b->depth_events) cudaEventDestroy(e);
+  b->depth_events.clear();
+  b->depth_of_events.clear();
+  auto mark_depth = [&](int d, bool first) {
+    if (!ctx->profiling) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    b->depth_events.push_back(e);
+    if (first) b->depth_of_events.push_back(d);
+  };
   const int nj = b->num_jobs;
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   b->prof_events.clear();
@@ -1634,6 +1724,7 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       }
       // Survivors of depth d (children of depth d + 1 and, for stacks whose top is d,
       // the seeds) are gathered into bucket order, then expanded.
+      mark_depth(d, true);
       if (any)
         ++ctx->launches, k_seed_nodes<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(
             b->jobs, b->scans, b->top_scores, b->state, node_tmp, node_blocks, b->bucket_cnt,
@@ -1644,9 +1735,14 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
           node_tmp, node_blocks, b->bucket_start, b->bucket_istart, node_list, node_items,
           b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap);
+      mark_depth(d, false);
       ++ctx->launches, (ctx->expand_noalloc ? k_expand_nodes<true> : k_expand_nodes<false>)<<<ctx->num_sms * kNodeBlocksPerSm, kExpandWarps * kWarp, 0, st>>>(
           b->jobs, b->xy, b->scans, b->top_scores, b->state, b->bucket_js, node_list, node_items,
           node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist);
+      mark_depth(d, false);
+      if (ctx->profiling >= 2)
+        ++ctx->launches, k_item_stats<<<ctx->num_sms * 4, 256, 0, st>>>(
+            b->jobs, b->bucket_js, node_list, node_items, b->counters, d, item_cap, b->depth_stats);
     }
     mark();
     ++ctx->launches, k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
@@ -1662,7 +1758,16 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   ++ctx->launches, k_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
   mark();
   CSM_CUDA(cudaGetLastError());
+  // Results and counters follow the kernels into the pinned block; fetch() waits for this
+  // batch's own event only, so a caller can keep later batches queued behind it.
+  CSM_CUDA(cudaMemcpyAsync(pinned_results(b), b->results_dev, sizeof(csm_result2d) * b->num_jobs,
+                           cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaMemcpyAsync(pinned_counters(b), b->counters, sizeof(unsigned int) * kNumCounters,
+                           cudaMemcpyDeviceToHost, st));
+  if (!b->done) CSM_CUDA(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+  CSM_CUDA(cudaEventRecord(b->done, st));
   b->ran = true;
+  b->idle = false;
   return CSM_OK;
 }
 
@@ -1723,18 +1828,10 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
   CSM_REQUIRE(ctx != nullptr && b != nullptr && results != nullptr, "NULL argument");
   CSM_REQUIRE(b->ran, "batch was not run");
   CSM_CUDA(cudaSetDevice(ctx->device));
-  const size_t s_jobs = align_up(sizeof(JobDev) * b->num_jobs);
-  const size_t s_pts = align_up(sizeof(float) * 3 * b->total_pts);
-  const size_t s_quat = align_up(sizeof(float) * 2 * b->total_scans);
-  csm_result2d* pin_res =
-      reinterpret_cast<csm_result2d*>(static_cast<char*>(b->pinned) + s_jobs + s_pts + s_quat);
-  unsigned int counters[kNumCounters];
+  csm_result2d* pin_res = pinned_results(b);
+  const unsigned int* counters = pinned_counters(b);
   for (int attempt = 0;; ++attempt) {
-    CSM_CUDA(cudaMemcpyAsync(pin_res, b->results_dev, sizeof(csm_result2d) * b->num_jobs,
-                             cudaMemcpyDeviceToHost, ctx->stream));
-    CSM_CUDA(cudaMemcpyAsync(counters, b->counters, sizeof(counters), cudaMemcpyDeviceToHost,
-                             ctx->stream));
-    CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+    CSM_CUDA(cudaEventSynchronize(b->done));
     const unsigned int ov = counters[kCntOverflow];
     if (ov == 0) break;
     if ((ov & 2u) || attempt >= 4) {
@@ -1742,9 +1839,16 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
       return CSM_ERR_CAPACITY;
     }
     // A work list overflowed: regrow it and replay the whole batch.
-    if (ov & 1u) b->frontier_want *= 4ull;
+    if (ov & 1u) {
+      b->frontier_want *= 4ull;
+      ctx->frontier_per_candidate = std::max(
+          ctx->frontier_per_candidate, static_cast<double>(b->frontier_want) / std::max<double>(1., b->total_cand));
+    }
     unsigned long long ccap = (ov & 4u) ? static_cast<unsigned long long>(counters[kCntContenders]) + 1024ull
                                         : b->contender_cap;
+    if (ov & 4u)
+      ctx->contenders_per_candidate = std::max(
+          ctx->contenders_per_candidate, 1.5 * static_cast<double>(ccap) / std::max<double>(1., b->total_cand));
     if (ccap > 0xFFFFFFF0ull) ccap = 0xFFFFFFF0ull;
     int rc = allocate_batch(b, static_cast<unsigned int>(ccap));
     if (rc == CSM_OK) rc = copy_inputs(ctx, b);
@@ -1768,6 +1872,22 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
         ctx->phase_scored[3] += static_cast<double>(s.scored_phase[2]);
         ctx->phase_scored[4] += static_cast<double>(s.scored_phase[3]);
       }
+      for (size_t k = 0; k < b->depth_of_events.size() && 3 * k + 2 < b->depth_events.size(); ++k) {
+        const int d = b->depth_of_events[k];
+        float book = 0.f, expand = 0.f;
+        cudaEventElapsedTime(&book, b->depth_events[3 * k], b->depth_events[3 * k + 1]);
+        cudaEventElapsedTime(&expand, b->depth_events[3 * k + 1], b->depth_events[3 * k + 2]);
+        ctx->depth_profile[d * csm_ctx::kDepthFields + 0] += expand;
+        ctx->depth_profile[d * csm_ctx::kDepthFields + 1] += book;
+      }
+      if (ctx->profiling >= 2) {
+        std::vector<double> dstats(CSM_MAX_DEPTH * 6);
+        CSM_CUDA(cudaMemcpyAsync(dstats.data(), b->depth_stats, sizeof(double) * dstats.size(),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+        CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int d = 0; d < CSM_MAX_DEPTH; ++d)
+          for (int k = 0; k < 6; ++k) ctx->depth_profile[d * csm_ctx::kDepthFields + 2 + k] += dstats[d * 6 + k];
+      }
       if (ctx->profiling >= 2) {
         std::vector<unsigned long long> hist(CSM_MAX_DEPTH * 33);
         CSM_CUDA(cudaMemcpyAsync(hist.data(), b->hist, sizeof(unsigned long long) * hist.size(),
@@ -1779,6 +1899,9 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
     }
     for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
     b->prof_events.clear();
+    for (cudaEvent_t e : b->depth_events) cudaEventDestroy(e);
+    b->depth_events.clear();
+    b->depth_of_events.clear();
   }
   std::vector<Contender> list;
   bool have_list = false;
@@ -1804,6 +1927,7 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
     }
     results[i] = r;
   }
+  b->idle = true;
   return CSM_OK;
 }
 

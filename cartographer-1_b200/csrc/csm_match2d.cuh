@@ -156,7 +156,12 @@ struct csm_batch2d {
   void* pinned = nullptr;              // staging for uploads / results
   size_t pinned_bytes = 0;
   bool uploaded = false, ran = false;
+  cudaEvent_t done = nullptr;            // recorded by run() after the results reached the pinned block
+  bool idle = false;                     // fetched since the last run: nothing of it is in flight
   std::vector<cudaEvent_t> prof_events;  // kPhases + 1 events of the last profiled run
+  std::vector<cudaEvent_t> depth_events;  // 3 per swept depth: lists, expand start, expand end
+  std::vector<int> depth_of_events;       // the depth of every such triple
+  double* depth_stats = nullptr;          // CSM_MAX_DEPTH x 6 (k_item_stats, profiling 2)
 };
 
 #endif  // CSM_MATCH2D_CUH_

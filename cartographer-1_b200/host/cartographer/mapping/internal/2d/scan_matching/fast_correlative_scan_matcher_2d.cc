@@ -122,17 +122,20 @@ bool FastCorrelativeScanMatcher2D::MatchFullSubmap(const sensor::PointCloud& poi
 std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::MatchBatch(
     DeviceContext* context, const QueryList& queries) {
   if (queries.empty()) return {};
-  Batch batch(context, queries);
-  batch.Run();
-  return batch.Fetch();
+  Batch batch(context, queries, /*resident=*/false);
+  return batch.RunStreaming();
 }
 
-FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryList& queries)
+FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryList& queries,
+                                           const bool resident)
     : context_(context) {
   const size_t n = queries.size();
   initial_.resize(n);
-  std::vector<std::vector<float>> xyz(n), quats(n);
-  std::vector<csm_job2d> jobs(n);
+  xyz_.resize(n);
+  quats_.resize(n);
+  jobs_.resize(n);
+  std::vector<std::vector<float>>&xyz = xyz_, &quats = quats_;
+  std::vector<csm_job2d>& jobs = jobs_;
   std::vector<double> lattice_estimate(n);
   params_.assign(n, SearchParameters(0, 0, 0., 0.));
   // Host side of every search (search parameters, angle tables: libm): independent.
@@ -204,12 +207,14 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
       sum += lattice_estimate[end];
       ++end;
     }
-    csm_batch2d* device_batch = nullptr;
-    CheckOk(csm_batch2d_upload(context_->get(), jobs.data() + begin, static_cast<int>(end - begin),
-                               &device_batch),
-            "csm_batch2d_upload");
     chunks_.emplace_back(begin, end);
-    device_batches_.push_back(device_batch);
+    if (resident) {
+      csm_batch2d* device_batch = nullptr;
+      CheckOk(csm_batch2d_upload(context_->get(), jobs.data() + begin, static_cast<int>(end - begin),
+                                 &device_batch),
+              "csm_batch2d_upload");
+      device_batches_.push_back(device_batch);
+    }
     begin = end;
   }
 }
@@ -225,9 +230,43 @@ void FastCorrelativeScanMatcher2D::Batch::Run() {
 std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::Fetch() {
   const size_t n = initial_.size();
   std::vector<csm_result2d> results(n);
+  CSM_CHECK(device_batches_.size() == chunks_.size());  // resident form
   for (size_t c = 0; c != chunks_.size(); ++c)
     CheckOk(csm_batch2d_fetch(context_->get(), device_batches_[c], results.data() + chunks_[c].first),
             "csm_batch2d_fetch");
+  return Convert(results);
+}
+
+std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::RunStreaming() {
+  // Device batch k+1 is uploaded and its kernels queued while k runs; a batch is fetched (its
+  // own event, not the stream) and its blocks go back to the context's pool once kInFlight
+  // are queued.
+  constexpr size_t kInFlight = 3;
+  std::vector<csm_result2d> results(initial_.size());
+  std::vector<std::pair<size_t, csm_batch2d*>> live;
+  auto retire = [&]() {
+    const size_t c = live.front().first;
+    CheckOk(csm_batch2d_fetch(context_->get(), live.front().second, results.data() + chunks_[c].first),
+            "csm_batch2d_fetch");
+    csm_batch2d_destroy(context_->get(), live.front().second);
+    live.erase(live.begin());
+  };
+  for (size_t c = 0; c != chunks_.size(); ++c) {
+    csm_batch2d* device_batch = nullptr;
+    CheckOk(csm_batch2d_upload(context_->get(), jobs_.data() + chunks_[c].first,
+                               static_cast<int>(chunks_[c].second - chunks_[c].first), &device_batch),
+            "csm_batch2d_upload");
+    CheckOk(csm_batch2d_run(context_->get(), device_batch), "csm_batch2d_run");
+    live.emplace_back(c, device_batch);
+    if (live.size() >= kInFlight) retire();
+  }
+  while (!live.empty()) retire();
+  return Convert(results);
+}
+
+std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::Convert(
+    const std::vector<csm_result2d>& results) const {
+  const size_t n = initial_.size();
   std::vector<Answer> answers(n);
   for (size_t i = 0; i != n; ++i) {
     const csm_result2d& r = results[i];

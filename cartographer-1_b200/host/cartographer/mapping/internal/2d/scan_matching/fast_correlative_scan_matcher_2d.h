@@ -90,22 +90,33 @@ class FastCorrelativeScanMatcher2D {
   // parameters (libm) and uploads; Run() enqueues every kernel on the context's
   // stream without waiting; Fetch() waits, copies the results back and converts the
   // winning candidates to poses.  Run() may be repeated.
+  //
+  // A large batch is cut into device batches of bounded footprint.  With `resident` false
+  // nothing is uploaded by the constructor and RunStreaming() moves the device batches
+  // through the device a few at a time -- upload k+1 and its kernels are queued while k runs,
+  // results are collected as each finishes -- so the device footprint stays at a few device
+  // batches however large the job is (MatchBatch does this).
   class Batch {
    public:
-    Batch(DeviceContext* context, const QueryList& queries);
+    Batch(DeviceContext* context, const QueryList& queries, bool resident = true);
     ~Batch();
     Batch(const Batch&) = delete;
     Batch& operator=(const Batch&) = delete;
     void Run();
     std::vector<Answer> Fetch();
+    std::vector<Answer> RunStreaming();
     size_t size() const { return initial_.size(); }
 
    private:
+    std::vector<Answer> Convert(const std::vector<csm_result2d>& results) const;
+
     DeviceContext* context_;
     std::vector<SearchParameters> params_;
     std::vector<transform::Rigid2d> initial_;
+    std::vector<std::vector<float>> xyz_, quats_;    // host copies the job descriptors point into
+    std::vector<csm_job2d> jobs_;
     std::vector<std::pair<size_t, size_t>> chunks_;  // [begin, end) job ranges
-    std::vector<csm_batch2d*> device_batches_;
+    std::vector<csm_batch2d*> device_batches_;       // resident form only
   };
 
   const csm_stack2d* stack() const { return stack_; }

@@ -8,10 +8,12 @@
 // depth-first branch-and-bound on a CPU core.  Here the searches are queued and
 // flushed in batches: each flush is ONE thread-pool task that shards the queued
 // searches over the configured GPUs by submap affinity (all searches against a
-// submap go to the GPU that holds its precomputation stack), runs one
-// FastCorrelativeScanMatcher2D::Batch per GPU concurrently, and fills the result
-// slots.  There is no collective on the data path; results are gathered on the
-// host.  Ceres refinement (reference :245-249) runs as one more device batch per flush
+// submap go to a GPU that holds its precomputation stack; greedy longest-processing-time
+// on an estimated cost, and a submap whose searches would unbalance the GPUs -- the
+// "new submap x all old nodes" burst of pose_graph_2d.cc:383-393 -- is replicated and
+// its node list split), runs one FastCorrelativeScanMatcher2D::MatchBatch per GPU
+// concurrently, and fills the result slots.  There is no collective on the data path;
+// results are gathered on the host.  Ceres refinement (reference :245-249) runs as one more device batch per flush
 // (CeresScanMatcher2D::MatchBatch) when options.ceres_scan_matcher_options() is filled in;
 // with an empty message the constraint carries the correlative scan matcher's pose estimate.
 #ifndef CARTOGRAPHER_MAPPING_INTERNAL_CONSTRAINTS_CONSTRAINT_BUILDER_2D_H_
@@ -25,7 +27,9 @@
 #include <vector>
 
 #include "cartographer/common/fixed_ratio_sampler.h"
+#include "cartographer/common/histogram.h"
 #include "cartographer/common/thread_pool.h"
+#include "cartographer/metrics/family_factory.h"
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 #include "cartographer_compat.h"
 
@@ -81,20 +85,49 @@ class ConstraintBuilder2D {
   static void RegisterMetrics(metrics::FamilyFactory* family_factory);
 
   // --- additions of the B200 path (not in the reference) ---
+  // Whole-node / whole-submap batches.  The reference's caller emits
+  // one MaybeAdd*Constraint call at a time, each taking the builder's mutex
+  // (PoseGraph2D::ComputeConstraintsForNode, pose_graph_2d.cc:312-402: a node against every
+  // finished submap, and at :383-393 a newly finished submap against all old nodes).  One call
+  // here carries the whole burst: same per-request semantics as MaybeAddConstraint
+  // (match_full_submap false: distance gate, then the submap's sampler) and
+  // MaybeAddGlobalConstraint (true), in order, under ONE lock and with ONE flush decision.
+  // NotifyEndOfNode stays the caller's.
+  struct ConstraintRequest {
+    SubmapId submap_id{0, 0};
+    const Submap2D* submap = nullptr;
+    NodeId node_id{0, 0};
+    const TrajectoryNode::Data* constant_data = nullptr;
+    bool match_full_submap = false;
+    transform::Rigid2d initial_relative_pose;  // ignored for full-submap requests
+  };
+  void MaybeAddConstraints(const std::vector<ConstraintRequest>& requests);
+
   // Searches queued before a flush is scheduled from NotifyEndOfNode (WhenDone always
   // flushes the rest).  Default 256.
   void set_flush_threshold(int searches) { flush_threshold_ = searches; }
-  // Totals since construction.
+  // Totals since construction (what the reference reports through its metrics families,
+  // constraint_builder_2d.cc:46-53, plus the sharding of the flushes over the devices).
   struct Stats {
     uint64_t searches = 0, found = 0, candidates_scored = 0, flushes = 0;
+    uint64_t local_searched = 0, local_found = 0, global_searched = 0, global_found = 0;
+    uint64_t queue_length = 0;         // result slots not yet handed to a WhenDone callback
+    uint64_t num_submap_scan_matchers = 0;
+    uint64_t replicated_stacks = 0;    // stacks built on a second (third, ...) device
+    std::vector<uint64_t> searches_per_device;
+    std::vector<double> cost_per_device;  // estimated cost assigned (the LPT quantity)
   };
   Stats stats();
+  // common::Histogram::ToString of the scores of the constraints found (the reference logs it
+  // from RunWhenDoneCallback when log_matches is set, .cc:289-293).
+  std::string ScoreHistogram(int buckets = 10);
 
  private:
   struct SubmapScanMatcher {
     const Grid2D* grid = nullptr;
-    int device_slot = 0;  // index into devices_
-    std::shared_ptr<scan_matching::FastCorrelativeScanMatcher2D> fast_correlative_scan_matcher;
+    // One stack per device that has searched this submap so far (index = slot in devices_;
+    // nullptr = not built there).  Searches prefer a device that holds the stack.
+    std::vector<std::shared_ptr<scan_matching::FastCorrelativeScanMatcher2D>> per_device;
   };
   struct PendingSearch {
     SubmapId submap_id;
@@ -111,6 +144,11 @@ class ConstraintBuilder2D {
                const transform::Rigid2d& initial_relative_pose);  // mutex_ held
   std::weak_ptr<common::Task> ScheduleFlush();                     // mutex_ held
   void RunFlush(const std::vector<PendingSearch>& searches, int finished_nodes_after);
+  // Estimated cost of a search (points x angular slices x lowest-resolution lattice): what the
+  // device assignment balances.
+  double EstimateCost(const PendingSearch& search) const;
+  // device slot of every search of a flush (mutex_ held).
+  std::vector<int> AssignDevices(const std::vector<PendingSearch>& searches, std::vector<double>* cost);
   void RunWhenDoneCallback();
 
   const proto::ConstraintBuilderOptions options_;
@@ -131,8 +169,8 @@ class ConstraintBuilder2D {
   std::vector<std::unique_ptr<scan_matching::DeviceContext>> devices_;
   std::map<SubmapId, SubmapScanMatcher> submap_scan_matchers_;
   std::map<SubmapId, common::FixedRatioSampler> per_submap_sampler_;
-  int next_device_slot_ = 0;
   Stats stats_;
+  common::Histogram score_histogram_;
 };
 
 }  // namespace constraints

@@ -462,11 +462,10 @@ class PoseGraphInterface {
   };
 };
 
-namespace metrics {
-class FamilyFactory;
-}  // namespace metrics
-
 }  // namespace mapping
+namespace metrics {
+class FamilyFactory;  // cartographer/metrics/family_factory.h
+}  // namespace metrics
 namespace common {
 namespace proto {
 // common/proto/ceres_solver_options.proto (fields 1-3)

@@ -147,10 +147,21 @@ int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* ful
                      const double* init_pose, const float* xyz, const int64_t* offsets,
                      const float* min_score, csmh_result2d* out) {
   if (n == 0) return 0;
-  void* b = csmh_batch_create(ctx, n, matchers, full, init_pose, xyz, offsets, min_score);
-  csmh_batch_run(b);
-  csmh_batch_fetch(b, out);
-  csmh_batch_destroy(b);
+  // The public one-call path: FastCorrelativeScanMatcher2D::MatchBatch streams the device
+  // batches of a large job through the device instead of uploading all of them first.
+  std::vector<sensor::PointCloud> clouds(n);
+  FastCorrelativeScanMatcher2D::QueryList q(n);
+  for (int i = 0; i < n; ++i) {
+    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
+      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
+    q[i].first = static_cast<const FastCorrelativeScanMatcher2D*>(matchers[i]);
+    q[i].second.point_cloud = &clouds[i];
+    q[i].second.full_submap = full[i] != 0;
+    q[i].second.initial_pose_estimate = transform::Rigid2d(
+        transform::Vector2d(init_pose[3 * i], init_pose[3 * i + 1]), init_pose[3 * i + 2]);
+    q[i].second.min_score = min_score[i];
+  }
+  Convert(FastCorrelativeScanMatcher2D::MatchBatch(static_cast<DeviceContext*>(ctx), q), out);
   return 0;
 }
 
@@ -303,6 +314,22 @@ int csmh_rt_match_batch(void* ctx, int n, void* const* grids, const double* opti
 // the constraint transform submap <- node as (x, y, yaw) in transform3[3i..].
 // stats4 = {searches run, constraints found, candidates scored, flushes}.
 // Returns wall seconds from the first MaybeAdd* call to the WhenDone callback.
+// csmh_constraint_builder_run2 adds: entry_mode 0 = one MaybeAdd*Constraint + NotifyEndOfNode per
+// search (the reference's caller), 1 = MaybeAddConstraints bursts of `burst` requests (whole-node
+// batches) followed by the NotifyEndOfNode calls; an InMemoryFamilyFactory registered through
+// RegisterMetrics; stats_ext (32 doubles): [0..3] as stats4, [4] local searched, [5] local found,
+// [6] global searched, [7] global found, [8] replicated stacks, [9..12] the same four counts read
+// back from the metrics families, [13] queue-length gauge after the callback, [14] observations in
+// the two score histograms, [15] scores in common::Histogram, [16 + d] searches run on device d.
+double csmh_constraint_builder_run2(int num_devices, const int* devices, int num_pool_threads,
+                                    int flush_threshold, int depth, const double* options8,
+                                    int num_submaps, void* const* grids, const double* submap_pose,
+                                    int num_searches, const int32_t* search_submap,
+                                    const int32_t* search_full, const double* search_rel_pose,
+                                    const float* xyz, const int64_t* offsets, int32_t* found,
+                                    double* transform3, double* stats4, int entry_mode, int burst,
+                                    double* stats_ext);
+
 double csmh_constraint_builder_run(int num_devices, const int* devices, int num_pool_threads,
                                    int flush_threshold, int depth, const double* options8,
                                    int num_submaps, void* const* grids, const double* submap_pose,
@@ -310,6 +337,19 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
                                    const int32_t* search_full, const double* search_rel_pose,
                                    const float* xyz, const int64_t* offsets, int32_t* found,
                                    double* transform3, double* stats4) {
+  return csmh_constraint_builder_run2(num_devices, devices, num_pool_threads, flush_threshold, depth, options8,
+                                      num_submaps, grids, submap_pose, num_searches, search_submap, search_full,
+                                      search_rel_pose, xyz, offsets, found, transform3, stats4, 0, 0, nullptr);
+}
+
+double csmh_constraint_builder_run2(int num_devices, const int* devices, int num_pool_threads,
+                                    int flush_threshold, int depth, const double* options8,
+                                    int num_submaps, void* const* grids, const double* submap_pose,
+                                    int num_searches, const int32_t* search_submap,
+                                    const int32_t* search_full, const double* search_rel_pose,
+                                    const float* xyz, const int64_t* offsets, int32_t* found,
+                                    double* transform3, double* stats4, int entry_mode, int burst,
+                                    double* stats_ext) {
   using mapping::constraints::ConstraintBuilder2D;
   mapping::constraints::proto::ConstraintBuilderOptions o;
   o.set_sampling_ratio(options8[0]);
@@ -344,6 +384,25 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
     found[i] = 0;
   }
   double seconds = 0.;
+  static metrics::InMemoryFamilyFactory metric_factory;  // the metric handles are process-wide statics
+  static bool registered = false;
+  if (!registered) {
+    ConstraintBuilder2D::RegisterMetrics(&metric_factory);
+    registered = true;
+  }
+  const std::string kCounts = "mapping_constraints_constraint_builder_2d_constraints";
+  const std::string kScores = "mapping_constraints_constraint_builder_2d_scores";
+  auto metric_snapshot = [&](double* v) {
+    v[0] = metric_factory.Value(kCounts + "{matcher=searched,search_region=local}");
+    v[1] = metric_factory.Value(kCounts + "{matcher=found,search_region=local}");
+    v[2] = metric_factory.Value(kCounts + "{matcher=searched,search_region=global}");
+    v[3] = metric_factory.Value(kCounts + "{matcher=found,search_region=global}");
+    v[4] = 0.;
+    for (const char* region : {"local", "global"})
+      for (const double c : metric_factory.BucketCounts(kScores + "{search_region=" + region + "}")) v[4] += c;
+  };
+  double before[5];
+  metric_snapshot(before);
   {
     common::ThreadPool pool(num_pool_threads);
     ConstraintBuilder2D builder(o, &pool, std::vector<int>(devices, devices + num_devices));
@@ -353,18 +412,38 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
     bool done = false;
     ConstraintBuilder2D::Result result;
     const auto t0 = std::chrono::steady_clock::now();
-    for (int i = 0; i < num_searches; ++i) {
-      const int s = search_submap[i];
-      if (search_full[i]) {
-        builder.MaybeAddGlobalConstraint(mapping::SubmapId{0, s}, &submaps[s],
-                                         mapping::NodeId{0, i}, &nodes[i]);
-      } else {
-        builder.MaybeAddConstraint(
-            mapping::SubmapId{0, s}, &submaps[s], mapping::NodeId{0, i}, &nodes[i],
-            transform::Rigid2d(transform::Vector2d(search_rel_pose[3 * i], search_rel_pose[3 * i + 1]),
-                               search_rel_pose[3 * i + 2]));
+    if (entry_mode == 1) {
+      for (int begin = 0; begin < num_searches; begin += std::max(1, burst)) {
+        const int end = std::min(num_searches, begin + std::max(1, burst));
+        std::vector<ConstraintBuilder2D::ConstraintRequest> requests;
+        for (int i = begin; i < end; ++i) {
+          ConstraintBuilder2D::ConstraintRequest r;
+          r.submap_id = mapping::SubmapId{0, search_submap[i]};
+          r.submap = &submaps[search_submap[i]];
+          r.node_id = mapping::NodeId{0, i};
+          r.constant_data = &nodes[i];
+          r.match_full_submap = search_full[i] != 0;
+          r.initial_relative_pose = transform::Rigid2d(
+              transform::Vector2d(search_rel_pose[3 * i], search_rel_pose[3 * i + 1]), search_rel_pose[3 * i + 2]);
+          requests.push_back(r);
+        }
+        builder.MaybeAddConstraints(requests);
+        for (int i = begin; i < end; ++i) builder.NotifyEndOfNode();
       }
-      builder.NotifyEndOfNode();
+    } else {
+      for (int i = 0; i < num_searches; ++i) {
+        const int s = search_submap[i];
+        if (search_full[i]) {
+          builder.MaybeAddGlobalConstraint(mapping::SubmapId{0, s}, &submaps[s],
+                                           mapping::NodeId{0, i}, &nodes[i]);
+        } else {
+          builder.MaybeAddConstraint(
+              mapping::SubmapId{0, s}, &submaps[s], mapping::NodeId{0, i}, &nodes[i],
+              transform::Rigid2d(transform::Vector2d(search_rel_pose[3 * i], search_rel_pose[3 * i + 1]),
+                                 search_rel_pose[3 * i + 2]));
+        }
+        builder.NotifyEndOfNode();
+      }
     }
     builder.WhenDone([&](const ConstraintBuilder2D::Result& r) {
       std::lock_guard<std::mutex> l(m);
@@ -393,6 +472,27 @@ double csmh_constraint_builder_run(int num_devices, const int* devices, int num_
       stats4[1] = static_cast<double>(st.found);
       stats4[2] = static_cast<double>(st.candidates_scored);
       stats4[3] = static_cast<double>(st.flushes);
+    }
+    if (stats_ext) {
+      double after[5];
+      metric_snapshot(after);
+      for (int k = 0; k < 32; ++k) stats_ext[k] = 0.;
+      stats_ext[0] = static_cast<double>(st.searches);
+      stats_ext[1] = static_cast<double>(st.found);
+      stats_ext[2] = static_cast<double>(st.candidates_scored);
+      stats_ext[3] = static_cast<double>(st.flushes);
+      stats_ext[4] = static_cast<double>(st.local_searched);
+      stats_ext[5] = static_cast<double>(st.local_found);
+      stats_ext[6] = static_cast<double>(st.global_searched);
+      stats_ext[7] = static_cast<double>(st.global_found);
+      stats_ext[8] = static_cast<double>(st.replicated_stacks);
+      for (int k = 0; k < 4; ++k) stats_ext[9 + k] = after[k] - before[k];
+      stats_ext[13] = metric_factory.Value("mapping_constraints_constraint_builder_2d_queue_length{}");
+      stats_ext[14] = after[4] - before[4];
+      const std::string hist = builder.ScoreHistogram(10);
+      stats_ext[15] = std::atof(hist.c_str() + 7);  // "Count: N ..."
+      for (size_t d = 0; d < st.searches_per_device.size() && d < 16; ++d)
+        stats_ext[16 + d] = static_cast<double>(st.searches_per_device[d]);
     }
     CSM_CHECK(builder.GetNumFinishedNodes() == num_searches);
     for (int s = 0; s < num_submaps; ++s) builder.DeleteScanMatcher(mapping::SubmapId{0, s});

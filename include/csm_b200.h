@@ -404,6 +404,22 @@ int csm_rt_match3d_batch(csm_ctx* ctx, const csm_rt_job3d* jobs, int num_jobs, c
  * sustained rate in lookups per second.
  */
 unsigned long long csm_ctx_launch_count(csm_ctx* ctx);
+/* csm_measure_gather_ceiling: the ceiling of the ACCESS SHAPE of the 2D branch-and-bound sweep
+ * (k_expand_nodes): per (work item, scan point) one warp-wide 4-byte read-only load from an
+ * L2-resident table, base broadcast from shared memory, lanes spread evenly over
+ * `sectors_per_request` consecutive 32-byte sectors (4 = perfectly coalesced, 32 = one sector
+ * per lane), the packed accumulate, and nothing else.  Writes warp load requests per second.
+ * bench.py evaluates it at the sectors / request the run's own work items have
+ * (csm_ctx_get_depth_profile) -- the roofline denominator of the dominant kernel. */
+int csm_measure_gather_ceiling(csm_ctx* ctx, size_t table_bytes, int sectors_per_request,
+                               unsigned int num_items, int points_per_item, int repeats,
+                               double* requests_per_second);
+/* Per-depth profile of the 2D sweep since profiling was switched on: CSM_MAX_DEPTH x 8 doubles,
+ * per depth d (the depth of the PARENTS a launch expands): [0] k_expand_nodes milliseconds,
+ * [1] list bookkeeping milliseconds (seed, bucket prefix, placement), and -- profiling level 2
+ * only -- [2] work items, [3] warp load requests (items x points), [4] lane loads, [5] 32-byte
+ * sectors and [6] 128-byte lines those requests touch, [7] nodes. */
+int csm_ctx_get_depth_profile(csm_ctx* ctx, double* out);
 int csm_measure_gather_rate(csm_ctx* ctx, size_t table_bytes, int row_pitch, const int32_t* point_xy,
                             int num_points, unsigned int num_candidates, int repeats,
                             double* lookups_per_second);

@@ -338,3 +338,58 @@ def test_scan_wholly_outside_a_small_grid(csm, gpu_ctx):
     for init, r_g in zip(inits, res):
         _compare(om.match(pts, 0.3, initial=init), r_g)
     assert res[0].found == 0 and res[1].found == 0
+
+
+def test_constraint_builder_batch_entry_and_metrics(csm):
+    """MaybeAddConstraints (whole-node bursts) returns what one
+    MaybeAdd*Constraint call per search returns -- same gate, same sampler sequence, same
+    submission order -- and the builder reports what the reference reports: searched / found
+    counters per search region, the score histograms and the queue length
+    (constraint_builder_2d.cc:46-53,205-240,289-293,318-343)."""
+    worlds, poses, sub, full, rel, clouds = _builder_case(7)
+    ograds = [ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    grids = [csm.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    kw = dict(sampling_ratio=0.5, max_constraint_distance=15.0, min_score=0.45,
+              global_min_score=0.5, linear_window=3.0, angular_window=0.5, depth=5)
+    _, o_out, _ = ob.constraint_batch(4, ograds, poses, sub, full, rel, clouds, **kw)
+    _, f1, t1, s1 = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, flush_threshold=6,
+                                               extended=True, **kw)
+    _, f2, t2, s2 = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, flush_threshold=6,
+                                               burst=5, extended=True, **kw)
+    assert np.array_equal(f1, f2) and np.array_equal(t1, t2)
+    assert np.array_equal(f1, np.array([o.found for o in o_out], np.int32))
+    for s in (s1, s2):
+        searched, found = s[0], s[1]
+        assert found == f1.sum() and found > 0
+        assert s[4] + s[6] == searched and s[5] + s[7] == found          # local + global
+        assert list(s[9:13]) == list(s[4:8])                            # the metrics families agree
+        assert s[13] == 0 and s[14] == found and s[15] == found         # queue drained, scores observed
+        assert s[16] == searched                                        # one device ran everything
+    assert s1[0] == s2[0] < len(clouds)  # the sampler and the distance gate dropped some, identically
+
+
+def _device_count(csm):
+    return csm.abi().csm_device_count()
+
+
+def test_constraint_builder_two_devices_partition_and_hot_submap(csm):
+    """ConstraintBuilder2D(options, pool, {0, 1}): a flush is sharded by submap affinity and cost,
+    both devices run their shard concurrently, results come back in submission order and equal the
+    one-device run bit for bit; a burst against ONE submap is split and the submap replicated."""
+    if _device_count(csm) < 2:
+        pytest.skip("needs two CUDA devices")
+    worlds, poses, sub, full, rel, clouds = _builder_case(9, n_sub=4, n_search=40)
+    grids = [csm.Grid(w.cells, w.res, w.max_x, w.max_y) for w in worlds]
+    kw = dict(sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.45,
+              global_min_score=0.5, linear_window=3.0, angular_window=0.5, depth=5, extended=True)
+    _, f1, t1, s1 = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, devices=(0,), **kw)
+    _, f2, t2, s2 = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, devices=(0, 1), **kw)
+    assert np.array_equal(f1, f2) and np.array_equal(t1, t2) and f1.sum() > 0
+    assert s2[16] > 0 and s2[17] > 0 and s2[16] + s2[17] == s2[0]
+    assert abs(s2[16] - s2[17]) <= 0.4 * s2[0]
+    # hot submap: every search against submap 0
+    hot = [0] * len(clouds)
+    _, f3, t3, s3 = csm.constraint_builder_run(grids, poses, hot, full, rel, clouds, devices=(0,), **kw)
+    _, f4, t4, s4 = csm.constraint_builder_run(grids, poses, hot, full, rel, clouds, devices=(0, 1), **kw)
+    assert np.array_equal(f3, f4) and np.array_equal(t3, t4)
+    assert s4[8] >= 1 and s4[16] > 0 and s4[17] > 0   # the stack was replicated, the node list split
