@@ -686,6 +686,58 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
   return CSM_OK;
 }
 
+// PrecomputationGrid2D of ANY width (the public class takes one, FCSM2D.h:49-54; the stack only
+// uses powers of two): the window maximum over `width` cells is the maximum of two windows of
+// p = the largest power of two <= width cells, `width - p` apart, so the levels are doubled up
+// to p (k_stack_level_up with h = 1, 2, 4, ...) and one more pass with h = width - p finishes.
+int csm_precomputation_grid2d(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
+                              const uint8_t* q_lut, int width, uint8_t* out) {
+  CSM_REQUIRE(ctx != nullptr && cells != nullptr && q_lut != nullptr && out != nullptr, "NULL argument");
+  CSM_REQUIRE(num_x >= 1 && num_y >= 1 && num_x <= 30000 && num_y <= 30000, "cell limits out of range");
+  CSM_REQUIRE(width >= 1 && width <= 30000, "width out of range");
+  CSM_CUDA(cudaSetDevice(ctx->device));
+  const size_t wide_x = static_cast<size_t>(num_x) + width - 1, wide_y = static_cast<size_t>(num_y) + width - 1;
+  const size_t pitch = (wide_x + 15) & ~static_cast<size_t>(15);
+  const size_t image = pitch * wide_y;
+  const size_t cell_bytes = sizeof(uint16_t) * static_cast<size_t>(num_x) * num_y;
+  const size_t lut_at = (cell_bytes + 255) & ~static_cast<size_t>(255);
+  int rc = ctx->tmp0.reserve(lut_at + 65536 + 256);
+  if (rc == CSM_OK) rc = ctx->tmp1.reserve(image);
+  if (rc == CSM_OK) rc = ctx->tmp2.reserve(image);
+  if (rc != CSM_OK) return rc;
+  cudaStream_t st = ctx->stream;
+  uint16_t* d_cells = ctx->tmp0.as<uint16_t>();
+  uint8_t* d_lut = ctx->tmp0.as<uint8_t>() + lut_at;
+  CSM_CUDA(cudaMemcpyAsync(d_cells, cells, cell_bytes, cudaMemcpyHostToDevice, st));
+  CSM_CUDA(cudaMemcpyAsync(d_lut, q_lut, 65536, cudaMemcpyHostToDevice, st));
+  uint8_t* buf[2] = {ctx->tmp1.as<uint8_t>(), ctx->tmp2.as<uint8_t>()};
+  {  // level 0 into buf[0] at the final pitch (rows beyond num_y stay zero)
+    const int pw = static_cast<int>(pitch >> 2);
+    CSM_CUDA(cudaMemsetAsync(buf[0], 0, image, st));
+    const int bx = std::min(kThreads, (pw + 31) & ~31), by = std::max(1, kThreads / bx);
+    const dim3 grid((pw + bx - 1) / bx, (num_y + by - 1) / by);
+    ++ctx->launches, k_stack_level0<<<grid, dim3(bx, by), 0, st>>>(d_cells, d_lut, buf[0], num_x, num_y,
+                                                                   static_cast<int>(pitch));
+  }
+  int have = 1, cur = 0;  // window width of buf[cur]
+  auto widen = [&](int h) {  // width `have` -> `have + h` (h <= have)
+    const int in_w = num_x + have - 1, in_h = num_y + have - 1;
+    const int out_w = in_w + h, out_h = in_h + h;
+    dim3 block(64, 4);
+    dim3 grid((out_w + block.x - 1) / block.x, (out_h + block.y - 1) / block.y);
+    ++ctx->launches, k_stack_level_up<<<grid, block, 0, st>>>(buf[cur], in_w, in_h, static_cast<int>(pitch),
+                                                            buf[cur ^ 1], out_w, out_h, static_cast<int>(pitch), h);
+    cur ^= 1;
+    have += h;
+  };
+  while (2 * have <= width) widen(have);
+  if (have < width) widen(width - have);
+  CSM_CUDA(cudaGetLastError());
+  CSM_CUDA(cudaMemcpy2DAsync(out, wide_x, buf[cur], pitch, wide_x, wide_y, cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaStreamSynchronize(st));
+  return CSM_OK;
+}
+
 int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* cells_dev) {
   CSM_REQUIRE(ctx != nullptr && stack != nullptr && cells_dev != nullptr, "NULL argument");
   CSM_REQUIRE(stack->device == ctx->device, "stack lives on another device");

@@ -112,6 +112,13 @@ size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
  * device (the next build reuses it without a cudaMalloc), and is freed otherwise. */
 void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* stack);
 
+/* ---- PrecomputationGrid2D of any width (the public class of FCSM2D.h:49-92; ctor FCSM2D.cc:91-161)
+ * out: (num_x + width - 1) x (num_y + width - 1) bytes, dense, byte-identical to the reference's
+ * cells_ (wide index (x0 + width - 1, y0 + width - 1) = maximum over the width x width cells from
+ * (x0, y0), 0 outside the grid).  Used by the host class PrecomputationGrid2D::GetValue. */
+int csm_precomputation_grid2d(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
+                              const uint8_t* q_lut, int width, uint8_t* out);
+
 /* ---- FastCorrelativeScanMatcher2D::MatchWithSearchParameters (FCSM2D.cc:227-262)
  * One job = one (node, submap) search.  The host supplies the search parameters it
  * computed with libm; the device does GenerateRotatedScans, DiscretizeScans,
@@ -166,6 +173,17 @@ void csm_batch2d_destroy(csm_ctx* ctx, csm_batch2d* batch);
 int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, int shrink,
                      int32_t* out_xy, int32_t* out_bounds);
 
+/* ---- the free functions of CSM2D.h:63-72 (the matchers fuse them; the reference's tests and
+ * any other caller reach them here).
+ * csm_rotate_scans2d: GenerateRotatedScans (CSM2D.cc:93-109): out_xyz = num_scans x num_points x 3,
+ *   scan s = the cloud rotated about z by the angle whose half-angle (cosf, sinf) is scan_quat[2s..].
+ * csm_discretize_points2d: DiscretizeScans for num_points points of any number of scans laid end
+ *   to end (CSM2D.cc:111-127): out_xy[2i..] = GetCellIndex(Translation2f(tx, ty) * p_i.head<2>()). */
+int csm_rotate_scans2d(csm_ctx* ctx, const float* points_xyz, int num_points, const float* scan_quat,
+                       int num_scans, float* out_xyz);
+int csm_discretize_points2d(csm_ctx* ctx, const float* points_xyz, long long num_points, float tx, float ty,
+                            double max_x, double max_y, double resolution, int32_t* out_xy);
+
 /* ---- RealTimeCorrelativeScanMatcher2D::Match (RT2D.cc:117-176) -----------------
  * Exhaustive search directly on the live uint16 grid (no precomputation).
  * cost_table: the grid's 65536-entry value-to-correspondence-cost table.
@@ -200,6 +218,14 @@ typedef struct {
 
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,
                          csm_result2d* results);
+/* RealTimeCorrelativeScanMatcher2D::ScoreCandidates on a caller-supplied list ("visible for
+ * testing", RT2D.h:75-79; RT2D.cc:151-176 up to the motion penalty, which the host applies in
+ * double): out_scores[c] = ComputeCandidateScore(grid, discrete_scans[scan_c], x_c, y_c).
+ * `grid` supplies cells / tables / limits / num_points (its point, scan-table and penalty fields are
+ * not read); discrete_xy = num_scans x num_points x 2 int32; candidates = num_candidates x
+ * (scan_index, x_index_offset, y_index_offset). */
+int csm_rt_score_candidates2d(csm_ctx* ctx, const csm_rt_job2d* grid, const int32_t* discrete_xy,
+                              int num_scans, const int32_t* candidates, int num_candidates, float* out_scores);
 
 /* ---- CeresScanMatcher2D::Match, batched ------------------------
  * Replaces cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.cc:64-110
