@@ -44,6 +44,21 @@ struct SearchParameters {
   std::vector<LinearBounds> linear_bounds;  // per rotated scan, before ShrinkToFit
 };
 
+typedef std::vector<Eigen::Array2i> DiscreteScan2D;  // reference :33
+
+// Generates a collection of rotated scans (reference :62-65, .cc:93-109).  Runs on the calling
+// thread's default device context (csm_rotate_scans2d); the matchers do not call it -- their
+// kernels rotate, discretise and score in one pass -- it exists for callers and tests that use
+// the reference's public helper.
+std::vector<sensor::PointCloud> GenerateRotatedScans(const sensor::PointCloud& point_cloud,
+                                                     const SearchParameters& search_parameters);
+
+// Translates and discretizes the rotated scans into a vector of integer indices (reference
+// :67-72, .cc:111-127; csm_discretize_points2d).
+std::vector<DiscreteScan2D> DiscretizeScans(const MapLimits& map_limits,
+                                            const std::vector<sensor::PointCloud>& scans,
+                                            const Eigen::Translation2f& initial_translation);
+
 // A possible solution (reference: correlative_scan_matcher_2d.h:74-103).
 struct Candidate2D {
   Candidate2D(const int init_scan_index, const int init_x_index_offset,

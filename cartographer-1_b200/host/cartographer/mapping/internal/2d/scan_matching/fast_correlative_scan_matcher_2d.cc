@@ -48,6 +48,75 @@ std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid) {
   return table;
 }
 
+proto::FastCorrelativeScanMatcherOptions2D CreateFastCorrelativeScanMatcherOptions2D(
+    common::LuaParameterDictionary* const parameter_dictionary) {
+  proto::FastCorrelativeScanMatcherOptions2D options;
+  options.set_linear_search_window(parameter_dictionary->GetDouble("linear_search_window"));
+  options.set_angular_search_window(parameter_dictionary->GetDouble("angular_search_window"));
+  options.set_branch_and_bound_depth(parameter_dictionary->GetInt("branch_and_bound_depth"));
+  return options;
+}
+
+PrecomputationGrid2D::PrecomputationGrid2D(const Grid2D& grid, const CellLimits& limits, const int width,
+                                           std::vector<float>* /*reusable_intermediate_grid*/)
+    : offset_(-width + 1, -width + 1),
+      wide_limits_(limits.num_x_cells + width - 1, limits.num_y_cells + width - 1),
+      min_score_(1.f - grid.GetMaxCorrespondenceCost()),
+      max_score_(1.f - grid.GetMinCorrespondenceCost()),
+      cells_(static_cast<size_t>(wide_limits_.num_x_cells) * wide_limits_.num_y_cells) {
+  CSM_CHECK(width >= 1);
+  CSM_CHECK(limits.num_x_cells >= 1);
+  CSM_CHECK(limits.num_y_cells >= 1);
+  // The reference reads the grid through GetCorrespondenceCost(), i.e. cells outside the grid's own
+  // limits count as unknown; `limits` is the grid's cell limits at every call site.
+  CSM_CHECK(limits.num_x_cells == grid.limits().cell_limits().num_x_cells);
+  CSM_CHECK(limits.num_y_cells == grid.limits().cell_limits().num_y_cells);
+  const std::vector<uint8> q = ComputeQuantizationTable(grid);
+  CheckOk(csm_precomputation_grid2d(DeviceContext::ThreadDefault()->get(), grid.correspondence_cost_cells().data(),
+                                    limits.num_x_cells, limits.num_y_cells, q.data(), width, cells_.data()),
+          "csm_precomputation_grid2d");
+}
+
+PrecomputationGrid2D::PrecomputationGrid2D(const CellLimits& limits, const int width, const float min_score,
+                                           const float max_score, std::vector<uint8> cells)
+    : offset_(-width + 1, -width + 1),
+      wide_limits_(limits.num_x_cells + width - 1, limits.num_y_cells + width - 1),
+      min_score_(min_score),
+      max_score_(max_score),
+      cells_(std::move(cells)) {
+  CSM_CHECK(cells_.size() == static_cast<size_t>(wide_limits_.num_x_cells) * wide_limits_.num_y_cells);
+}
+
+PrecomputationGridStack2D::PrecomputationGridStack2D(const Grid2D& grid,
+                                                     const proto::FastCorrelativeScanMatcherOptions2D& options)
+    : limits_(grid.limits().cell_limits()),
+      min_score_(1.f - grid.GetMaxCorrespondenceCost()),
+      max_score_(1.f - grid.GetMinCorrespondenceCost()) {
+  CSM_CHECK(options.branch_and_bound_depth() >= 1);
+  const std::vector<uint8> q = ComputeQuantizationTable(grid);
+  build_context_ = DeviceContext::ThreadDefault()->get();
+  CheckOk(csm_stack2d_build(build_context_, grid.correspondence_cost_cells().data(), limits_.num_x_cells,
+                            limits_.num_y_cells, q.data(), options.branch_and_bound_depth(), &stack_),
+          "csm_stack2d_build");
+  precomputation_grids_.resize(options.branch_and_bound_depth());
+}
+
+PrecomputationGridStack2D::~PrecomputationGridStack2D() { csm_stack2d_destroy(build_context_, stack_); }
+
+const PrecomputationGrid2D& PrecomputationGridStack2D::Get(const int index) {
+  CSM_CHECK(index >= 0 && index <= max_depth());
+  if (!precomputation_grids_[index]) {
+    int wide_x = 0, wide_y = 0;
+    csm_ctx* ctx = DeviceContext::ThreadDefault()->get();
+    CheckOk(csm_stack2d_level(ctx, stack_, index, nullptr, &wide_x, &wide_y), "csm_stack2d_level");
+    std::vector<uint8> cells(static_cast<size_t>(wide_x) * wide_y);
+    CheckOk(csm_stack2d_level(ctx, stack_, index, cells.data(), &wide_x, &wide_y), "csm_stack2d_level");
+    precomputation_grids_[index].reset(
+        new PrecomputationGrid2D(limits_, 1 << index, min_score_, max_score_, std::move(cells)));
+  }
+  return *precomputation_grids_[index];
+}
+
 FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
     const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options)
     : options_(options), limits_(grid.limits()), context_(DeviceContext::ThreadDefault()) {

@@ -13,6 +13,7 @@
 #include <memory>
 #include <vector>
 
+#include "cartographer/common/lua_parameter_dictionary.h"
 #include "cartographer/mapping/internal/2d/scan_matching/correlative_scan_matcher_2d.h"
 #include "cartographer_compat.h"
 #include "csm_b200.h"
@@ -44,6 +45,65 @@ class DeviceContext {
 // ComputeCellValue(1.f - |GetCorrespondenceCost|) for every possible cell value
 // (fast_correlative_scan_matcher_2d.cc:97-98,112-113,163-169).
 std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid);
+
+// Reference :42-44, .cc:76-89.
+proto::FastCorrelativeScanMatcherOptions2D CreateFastCorrelativeScanMatcherOptions2D(
+    common::LuaParameterDictionary* parameter_dictionary);
+
+// A precomputed grid that contains in each cell (x0, y0) the maximum probability in the
+// width x width area x0 <= x < x0 + width, y0 <= y < y0 + width (reference :49-92, .cc:91-169).
+// Built on the device for ANY width (csm_precomputation_grid2d); the bytes are kept on the host
+// so that GetValue is the reference's inline lookup.  `reusable_intermediate_grid` is accepted
+// for signature compatibility and left untouched: the device build has no float intermediate.
+class PrecomputationGrid2D {
+ public:
+  PrecomputationGrid2D(const Grid2D& grid, const CellLimits& limits, int width,
+                       std::vector<float>* reusable_intermediate_grid);
+  // Adopts bytes that are already on the host (PrecomputationGridStack2D downloads its levels).
+  PrecomputationGrid2D(const CellLimits& limits, int width, float min_score, float max_score,
+                       std::vector<uint8> cells);
+
+  // Returns a value between 0 and 255 to represent probabilities between min_score and max_score.
+  int GetValue(const Eigen::Array2i& xy_index) const {
+    const Eigen::Array2i local_xy_index = xy_index - offset_;
+    if (static_cast<unsigned>(local_xy_index.x()) >= static_cast<unsigned>(wide_limits_.num_x_cells) ||
+        static_cast<unsigned>(local_xy_index.y()) >= static_cast<unsigned>(wide_limits_.num_y_cells)) {
+      return 0;
+    }
+    const int stride = wide_limits_.num_x_cells;
+    return cells_[local_xy_index.x() + local_xy_index.y() * stride];
+  }
+
+  // Maps values from [0, 255] to [min_score, max_score].
+  float ToScore(float value) const { return min_score_ + value * ((max_score_ - min_score_) / 255.f); }
+
+ private:
+  Eigen::Array2i offset_;
+  CellLimits wide_limits_;
+  float min_score_;
+  float max_score_;
+  std::vector<uint8> cells_;
+};
+
+// Reference :94-109, .cc:171-186: levels of width 1 << i.  One device build (the matcher's own
+// csm_stack2d_build); a level is downloaded the first time Get() asks for it.
+class PrecomputationGridStack2D {
+ public:
+  PrecomputationGridStack2D(const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options);
+  ~PrecomputationGridStack2D();
+  PrecomputationGridStack2D(const PrecomputationGridStack2D&) = delete;
+  PrecomputationGridStack2D& operator=(const PrecomputationGridStack2D&) = delete;
+
+  const PrecomputationGrid2D& Get(int index);
+  int max_depth() const { return static_cast<int>(precomputation_grids_.size()) - 1; }
+
+ private:
+  CellLimits limits_;
+  float min_score_ = 0.f, max_score_ = 0.f;  // the grid is borrowed during construction only
+  csm_ctx* build_context_ = nullptr;
+  csm_stack2d* stack_ = nullptr;
+  std::vector<std::unique_ptr<PrecomputationGrid2D>> precomputation_grids_;
+};
 
 class FastCorrelativeScanMatcher2D {
  public:

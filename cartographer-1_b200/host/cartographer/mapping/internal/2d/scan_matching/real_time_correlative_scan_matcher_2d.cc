@@ -63,6 +63,65 @@ std::vector<Candidate2D> RealTimeCorrelativeScanMatcher2D::GenerateExhaustiveSea
   return candidates;
 }
 
+void RealTimeCorrelativeScanMatcher2D::ScoreCandidates(const Grid2D& grid,
+                                                       const std::vector<DiscreteScan2D>& discrete_scans,
+                                                       const SearchParameters& search_parameters,
+                                                       std::vector<Candidate2D>* const candidates) const {
+  CSM_CHECK(candidates != nullptr);
+  if (candidates->empty()) return;
+  CSM_CHECK(!discrete_scans.empty());
+  const size_t n = discrete_scans[0].size();
+  CSM_CHECK(n > 0);
+  std::vector<int32_t> xy(2 * n * discrete_scans.size());
+  for (size_t s = 0; s != discrete_scans.size(); ++s) {
+    CSM_CHECK(discrete_scans[s].size() == n);  // rotated copies of one cloud
+    for (size_t p = 0; p != n; ++p) {
+      xy[2 * (s * n + p)] = discrete_scans[s][p].x();
+      xy[2 * (s * n + p) + 1] = discrete_scans[s][p].y();
+    }
+  }
+  std::vector<int32_t> list(3 * candidates->size());
+  for (size_t c = 0; c != candidates->size(); ++c) {
+    list[3 * c] = (*candidates)[c].scan_index;
+    list[3 * c + 1] = (*candidates)[c].x_index_offset;
+    list[3 * c + 2] = (*candidates)[c].y_index_offset;
+  }
+  const MapLimits& limits = grid.limits();
+  csm_rt_job2d job;
+  std::memset(&job, 0, sizeof(job));
+  job.cells = grid.correspondence_cost_cells().data();
+  job.num_x = limits.cell_limits().num_x_cells;
+  job.num_y = limits.cell_limits().num_y_cells;
+  job.cost_table = grid.value_to_correspondence_cost_table().data();
+  job.num_points = static_cast<int32_t>(n);
+  job.max_x = limits.max().x();
+  job.max_y = limits.max().y();
+  job.resolution = limits.resolution();
+  job.out_of_bounds_probability = kMinProbability;
+  if (grid.GetGridType() == GridType::TSDF) {
+    const TSDF2D& tsdf = static_cast<const TSDF2D&>(grid);
+    job.cost_table = tsdf.value_converter().value_to_tsd_table().data();
+    job.weight_cells = tsdf.weight_cells().data();
+    job.weight_table = tsdf.value_converter().value_to_weight_table().data();
+    job.max_correspondence_cost = tsdf.GetMaxCorrespondenceCost();
+    job.out_of_bounds_tsd = tsdf.value_converter().getMinTSD();
+  }
+  std::vector<float> scores(candidates->size());
+  DeviceContext* ctx = context_ != nullptr ? context_ : DeviceContext::ThreadDefault();
+  CheckOk(csm_rt_score_candidates2d(ctx->get(), &job, xy.data(), static_cast<int>(discrete_scans.size()),
+                                    list.data(), static_cast<int>(list.size() / 3), scores.data()),
+          "csm_rt_score_candidates2d");
+  (void)search_parameters;  // the reference does not read it either
+  for (size_t c = 0; c != candidates->size(); ++c) {
+    Candidate2D& candidate = (*candidates)[c];
+    candidate.score = scores[c];
+    // reference :170-174: float *= double, evaluated in double and narrowed
+    const double t = std::hypot(candidate.x, candidate.y) * options_.translation_delta_cost_weight() +
+                     std::abs(candidate.orientation) * options_.rotation_delta_cost_weight();
+    candidate.score = static_cast<float>(candidate.score * std::exp(-(t * t)));
+  }
+}
+
 double RealTimeCorrelativeScanMatcher2D::Match(const transform::Rigid2d& initial_pose_estimate,
                                                const sensor::PointCloud& point_cloud,
                                                const Grid2D& grid,

@@ -41,8 +41,16 @@ class RealTimeCorrelativeScanMatcher2D {
                const sensor::PointCloud& point_cloud, const Grid2D& grid,
                transform::Rigid2d* pose_estimate) const;
 
-  // Generation order scan -> x -> y of the exhaustive window (reference :83-115);
-  // kept for tests and for the penalty table.
+  // Computes the score for each Candidate2D in a collection.  The cost is computed as the sum of
+  // probabilities or normalized TSD values, different from the Ceres CostFunctions:
+  // http://ceres-solver.org/modeling.html  Visible for testing (reference :68-79, .cc:151-176).
+  // The per-candidate sums run on the device (csm_rt_score_candidates2d), the motion penalty is
+  // applied here in double like the reference does.
+  void ScoreCandidates(const Grid2D& grid, const std::vector<DiscreteScan2D>& discrete_scans,
+                       const SearchParameters& search_parameters,
+                       std::vector<Candidate2D>* candidates) const;
+
+  // Generation order scan -> x -> y of the exhaustive window (reference :81-83, .cc:83-115).
   std::vector<Candidate2D> GenerateExhaustiveSearchCandidates(
       const SearchParameters& search_parameters) const;
 

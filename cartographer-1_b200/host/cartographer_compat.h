@@ -32,6 +32,37 @@
     }                                                                                 \
   } while (0)
 
+// The subset of Eigen the public helpers of the replaced headers name in their signatures
+// (Array2i cell indices, Translation2f).  In a full Cartographer tree the real Eigen provides them.
+namespace Eigen {
+struct Array2b {
+  bool v[2];
+  bool all() const { return v[0] && v[1]; }
+  bool any() const { return v[0] || v[1]; }
+};
+struct Array2i {
+  int v[2] = {0, 0};
+  Array2i() = default;
+  Array2i(int x, int y) : v{x, y} {}
+  static Array2i Zero() { return Array2i(0, 0); }
+  int x() const { return v[0]; }
+  int y() const { return v[1]; }
+  int& x() { return v[0]; }
+  int& y() { return v[1]; }
+  Array2i operator+(const Array2i& o) const { return Array2i(v[0] + o.v[0], v[1] + o.v[1]); }
+  Array2i operator-(const Array2i& o) const { return Array2i(v[0] - o.v[0], v[1] - o.v[1]); }
+  Array2b operator==(const Array2i& o) const { return Array2b{{v[0] == o.v[0], v[1] == o.v[1]}}; }
+};
+struct Translation2f {
+  float v[2] = {0.f, 0.f};
+  Translation2f() = default;
+  Translation2f(float x, float y) : v{x, y} {}
+  static Translation2f Identity() { return Translation2f(); }
+  float x() const { return v[0]; }
+  float y() const { return v[1]; }
+};
+}  // namespace Eigen
+
 namespace cartographer {
 
 using uint8 = uint8_t;
@@ -149,6 +180,7 @@ struct Vector3f {
   float v[3] = {0.f, 0.f, 0.f};
   Vector3f() = default;
   Vector3f(float x, float y, float z) : v{x, y, z} {}
+  static Vector3f Zero() { return Vector3f(); }
   float x() const { return v[0]; }
   float y() const { return v[1]; }
   float z() const { return v[2]; }
@@ -188,6 +220,37 @@ struct CellLimits {
   int num_y_cells = 0;
 };
 
+// mapping/2d/xy_index.h:49-110: row-major walk over a range of cell indices (x fastest).
+class XYIndexRangeIterator {
+ public:
+  XYIndexRangeIterator(const Eigen::Array2i& min_xy_index, const Eigen::Array2i& max_xy_index)
+      : min_xy_index_(min_xy_index), max_xy_index_(max_xy_index), xy_index_(min_xy_index) {}
+  explicit XYIndexRangeIterator(const CellLimits& cell_limits)
+      : XYIndexRangeIterator(Eigen::Array2i::Zero(),
+                             Eigen::Array2i(cell_limits.num_x_cells - 1, cell_limits.num_y_cells - 1)) {}
+  XYIndexRangeIterator& operator++() {
+    if (xy_index_.x() < max_xy_index_.x()) {
+      ++xy_index_.x();
+    } else {
+      xy_index_.x() = min_xy_index_.x();
+      ++xy_index_.y();
+    }
+    return *this;
+  }
+  Eigen::Array2i& operator*() { return xy_index_; }
+  bool operator==(const XYIndexRangeIterator& other) const { return (xy_index_ == other.xy_index_).all(); }
+  bool operator!=(const XYIndexRangeIterator& other) const { return !operator==(other); }
+  XYIndexRangeIterator begin() { return XYIndexRangeIterator(min_xy_index_, max_xy_index_); }
+  XYIndexRangeIterator end() {
+    XYIndexRangeIterator it = begin();
+    it.xy_index_ = Eigen::Array2i(min_xy_index_.x(), max_xy_index_.y() + 1);
+    return it;
+  }
+
+ private:
+  Eigen::Array2i min_xy_index_, max_xy_index_, xy_index_;
+};
+
 class MapLimits {
  public:
   MapLimits(double resolution, const transform::Vector2d& max, const CellLimits& cell_limits)
@@ -199,6 +262,11 @@ class MapLimits {
   double resolution() const { return resolution_; }
   const transform::Vector2d& max() const { return max_; }
   const CellLimits& cell_limits() const { return cell_limits_; }
+  // map_limits.h:84-90
+  bool Contains(const Eigen::Array2i& cell_index) const {
+    return cell_index.x() >= 0 && cell_index.y() >= 0 && cell_index.x() < cell_limits_.num_x_cells &&
+           cell_index.y() < cell_limits_.num_y_cells;
+  }
 
  private:
   double resolution_;
@@ -308,6 +376,20 @@ class ProbabilityGrid : public Grid2D {
   ProbabilityGrid(const MapLimits& limits, ValueConversionTables* conversion_tables)
       : Grid2D(limits, kMinCorrespondenceCost, kMaxCorrespondenceCost, conversion_tables) {}
   GridType GetGridType() const override { return GridType::PROBABILITY_GRID; }
+  // probability_grid.cc:40-48: sets the probability of a cell that was unknown so far.
+  void SetProbability(const Eigen::Array2i& cell_index, const float probability) {
+    CSM_CHECK(limits().Contains(cell_index));
+    uint16& cell = (*mutable_correspondence_cost_cells())[
+        static_cast<size_t>(limits().cell_limits().num_x_cells) * cell_index.y() + cell_index.x()];
+    CSM_CHECK(cell == 0);
+    cell = CorrespondenceCostToValue(1.f - probability);
+  }
+  // probability_grid.cc:78-82
+  float GetProbability(const Eigen::Array2i& cell_index) const {
+    if (!limits().Contains(cell_index)) return kMinProbability;
+    return 1.f - value_to_correspondence_cost_table()[correspondence_cost_cells()[
+        static_cast<size_t>(limits().cell_limits().num_x_cells) * cell_index.y() + cell_index.x()]];
+  }
 };
 
 // mapping/internal/2d/tsd_value_converter.{h,cc}
