@@ -52,6 +52,45 @@ std::vector<uint8> ComputeQuantizationTable3D() {
   return table;
 }
 
+proto::FastCorrelativeScanMatcherOptions3D CreateFastCorrelativeScanMatcherOptions3D(
+    common::LuaParameterDictionary* const parameter_dictionary) {
+  proto::FastCorrelativeScanMatcherOptions3D options;
+  options.set_branch_and_bound_depth(parameter_dictionary->GetInt("branch_and_bound_depth"));
+  options.set_full_resolution_depth(parameter_dictionary->GetInt("full_resolution_depth"));
+  options.set_min_rotational_score(parameter_dictionary->GetDouble("min_rotational_score"));
+  options.set_min_low_resolution_score(parameter_dictionary->GetDouble("min_low_resolution_score"));
+  options.set_linear_xy_search_window(parameter_dictionary->GetDouble("linear_xy_search_window"));
+  options.set_linear_z_search_window(parameter_dictionary->GetDouble("linear_z_search_window"));
+  options.set_angular_search_window(parameter_dictionary->GetDouble("angular_search_window"));
+  return options;
+}
+
+PrecomputationGridStack3D::PrecomputationGridStack3D(const HybridGrid& hybrid_grid,
+                                                     const proto::FastCorrelativeScanMatcherOptions3D& options) {
+  CSM_CHECK(options.branch_and_bound_depth() >= 1);  // reference :60
+  CSM_CHECK(options.full_resolution_depth() >= 1);   // reference :61
+  std::vector<int32_t> xyz;
+  std::vector<uint16> values;
+  hybrid_grid.Export(&xyz, &values);
+  const std::vector<uint8> q = ComputeQuantizationTable3D();
+  csm_ctx* ctx = DeviceContext::ThreadDefault()->get();
+  csm_stack3d* stack = nullptr;
+  CheckOk(csm_stack3d_build(ctx, xyz.data(), values.data(), static_cast<int>(values.size()), q.data(),
+                            options.branch_and_bound_depth(), options.full_resolution_depth(), &stack),
+          "csm_stack3d_build");
+  // Every level reports the source grid's resolution(), half-resolution levels included
+  // (PrecomputeGrid constructs its result with grid.resolution(), precomputation_grid_3d.cc:66).
+  const float resolution = hybrid_grid.resolution();
+  for (int depth = 0; depth != options.branch_and_bound_depth(); ++depth) {
+    int32_t lo[3] = {0, 0, 0}, dims[3] = {0, 0, 0};
+    CheckOk(csm_stack3d_level(ctx, stack, depth, nullptr, lo, dims), "csm_stack3d_level");
+    std::vector<uint8> bytes(static_cast<size_t>(dims[0]) * dims[1] * dims[2]);
+    if (!bytes.empty()) CheckOk(csm_stack3d_level(ctx, stack, depth, bytes.data(), lo, dims), "csm_stack3d_level");
+    precomputation_grids_.emplace_back(resolution, lo, dims, std::move(bytes));
+  }
+  csm_stack3d_destroy(ctx, stack);
+}
+
 FastCorrelativeScanMatcher3D::FastCorrelativeScanMatcher3D(
     const HybridGrid& hybrid_grid, const HybridGrid* const low_resolution_hybrid_grid,
     const Eigen::VectorXf* const rotational_scan_matcher_histogram,

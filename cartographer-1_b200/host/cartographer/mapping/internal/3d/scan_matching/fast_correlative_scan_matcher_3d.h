@@ -29,6 +29,52 @@ namespace scan_matching {
 std::vector<uint8> ComputeQuantizationTable3D();
 const std::vector<float>& ValueToProbabilityTable();
 
+// Reference :41-43, .cc:36-56.
+proto::FastCorrelativeScanMatcherOptions3D CreateFastCorrelativeScanMatcherOptions3D(
+    common::LuaParameterDictionary* parameter_dictionary);
+
+// One level of the 3D precomputation stack as the reference's callers read it
+// (precomputation_grid_3d.h:27-38: a HybridGridBase<uint8> with value() and ToProbability()).
+// Here a dense byte box downloaded from the device; outside the box a voxel reads the sparse
+// grid's default, 0.
+class PrecomputationGrid3D {
+ public:
+  PrecomputationGrid3D(float resolution, const int32_t lo[3], const int32_t dims[3], std::vector<uint8> bytes)
+      : resolution_(resolution), lo_{lo[0], lo[1], lo[2]}, dims_{dims[0], dims[1], dims[2]}, bytes_(std::move(bytes)) {}
+  float resolution() const { return resolution_; }
+  uint8 value(const Eigen::Array3i& index) const {
+    const int x = index.x() - lo_[0], y = index.y() - lo_[1], z = index.z() - lo_[2];
+    if (static_cast<unsigned>(x) >= static_cast<unsigned>(dims_[0]) ||
+        static_cast<unsigned>(y) >= static_cast<unsigned>(dims_[1]) ||
+        static_cast<unsigned>(z) >= static_cast<unsigned>(dims_[2]))
+      return 0;
+    return bytes_[(static_cast<size_t>(z) * dims_[1] + y) * dims_[0] + x];
+  }
+  // Maps values from [0, 255] to [kMinProbability, kMaxProbability].
+  static float ToProbability(float value) {
+    return kMinProbability + value * ((kMaxProbability - kMinProbability) / 255.f);
+  }
+
+ private:
+  float resolution_;
+  int32_t lo_[3], dims_[3];
+  std::vector<uint8> bytes_;
+};
+
+// Reference :45-64, .cc:57-77.  One device build (csm_stack3d_build); every level is downloaded at
+// construction (Get() is const in the reference).  Levels at or beyond full_resolution_depth hold
+// half-resolution indices, like the reference's.
+class PrecomputationGridStack3D {
+ public:
+  PrecomputationGridStack3D(const HybridGrid& hybrid_grid,
+                            const proto::FastCorrelativeScanMatcherOptions3D& options);
+  const PrecomputationGrid3D& Get(int depth) const { return precomputation_grids_.at(depth); }
+  int max_depth() const { return static_cast<int>(precomputation_grids_.size()) - 1; }
+
+ private:
+  std::vector<PrecomputationGrid3D> precomputation_grids_;
+};
+
 class FastCorrelativeScanMatcher3D {
  public:
   struct Result {
