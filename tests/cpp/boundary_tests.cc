@@ -186,10 +186,21 @@ static Pose2f Inverse(const Pose2f& a) {
   const float c = std::cos(-a.angle), s = std::sin(-a.angle);
   return Pose2f{-(c * a.x - s * a.y), -(s * a.x + c * a.y), -a.angle};
 }
+// transform::IsNearly (transform/rigid_transform_test_helpers.h:31-46): Eigen's isApprox on the 3x3
+// affine matrices, |a - b|_F^2 <= tol^2 * min(|a|_F^2, |b|_F^2), in fp32 like the reference test.
 static bool IsNearly(const Pose2f& want, const transform::Rigid2d& got, const float tol) {
-  const double d = std::remainder(got.rotation().angle() - want.angle, 2. * M_PI);
-  return std::abs(got.translation().x() - want.x) <= tol && std::abs(got.translation().y() - want.y) <= tol &&
-         std::abs(d) <= tol;
+  const float ga = static_cast<float>(got.rotation().angle());
+  const float m0[9] = {std::cos(want.angle), -std::sin(want.angle), want.x, std::sin(want.angle),
+                       std::cos(want.angle), want.y, 0.f, 0.f, 1.f};
+  const float m1[9] = {std::cos(ga), -std::sin(ga), static_cast<float>(got.translation().x()), std::sin(ga),
+                       std::cos(ga), static_cast<float>(got.translation().y()), 0.f, 0.f, 1.f};
+  float d2 = 0.f, n0 = 0.f, n1 = 0.f;
+  for (int i = 0; i < 9; ++i) {
+    d2 += (m0[i] - m1[i]) * (m0[i] - m1[i]);
+    n0 += m0[i] * m0[i];
+    n1 += m1[i] * m1[i];
+  }
+  return d2 <= tol * tol * std::min(n0, n1);
 }
 
 static void TestCorrectPose() {
