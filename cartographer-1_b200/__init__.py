@@ -62,6 +62,7 @@ ABI_SYMBOLS = [
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
     "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile", "csm_precomputation_grid2d",
     "csm_rotate_scans2d", "csm_discretize_points2d", "csm_rt_score_candidates2d",
+    "csm_discretize2d_noalloc",
 ]
 
 _abi = None

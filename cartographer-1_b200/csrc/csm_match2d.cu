@@ -2005,3 +2005,109 @@ int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, i
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// csm_discretize2d_noalloc: csm_discretize2d for callers that must not allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  Same kernel (k_discretize), but its
+// scratch -- job descriptor, points, scan table, discrete scans, per-scan windows -- lives in
+// ONE file-scope device array of fixed size instead of the context's growable buffer:
+//   num_points <= 4096, num_scans <= 4096, num_scans * num_points <= 524 288
+// (a C3 full-submap search is 1259 x 360 = 453 240).  Every GPU that loads the library holds the
+// array (about 4.2 MiB) until exit.  All calls share it: nothing in it has to start at zero (the
+// kernel writes every element it later copies out), but two calls that overlap on the GPU --
+// different contexts, streams or host threads -- race.  The entry point calls no cudaMalloc,
+// cudaFree, cudaHostAlloc or any other allocating routine, and allocates nothing on the host.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr int kNoAllocMaxPoints = 4096;
+constexpr int kNoAllocMaxScans = 4096;
+constexpr long long kNoAllocMaxCells = 1ll << 19;  // num_scans * num_points
+constexpr size_t kNaJob = 256;                                                   // JobDev
+constexpr size_t kNaPts = sizeof(float) * 3 * kNoAllocMaxPoints;                 // 48 KiB
+constexpr size_t kNaQuat = sizeof(float) * 2 * kNoAllocMaxScans;                 // 32 KiB
+constexpr size_t kNaXy = sizeof(int2) * static_cast<size_t>(kNoAllocMaxCells);   // 4 MiB
+constexpr size_t kNaScan = sizeof(csm::ScanInfo) * kNoAllocMaxScans;             // 128 KiB
+constexpr size_t kNaBytes = kNaJob + kNaPts + kNaQuat + kNaXy + kNaScan;
+static_assert(sizeof(csm::JobDev) <= kNaJob, "job descriptor outgrew its slot");
+static_assert(kNaJob % 256 == 0 && kNaPts % 256 == 0 && kNaQuat % 256 == 0 && kNaXy % 256 == 0, "slots stay aligned");
+
+// In host code this name is a host-side stand-in, NOT a device address: the address the kernel
+// gets comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+std::mutex g_noalloc_mu;
+
+// Device address of the scratch array on `device` (which must be the current device).
+int noalloc_scratch(int device, unsigned char** out) {
+  CSM_REQUIRE(device >= 0 && device < kNoAllocMaxDevices, "device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[device] == nullptr) {
+    void* p = nullptr;
+    CSM_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (p == nullptr) {
+      set_error("cudaGetSymbolAddress returned a null scratch address on device %d", device);
+      return CSM_ERR_CUDA;
+    }
+    g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return CSM_OK;
+}
+
+}  // namespace
+
+extern "C" int csm_discretize2d_noalloc(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, int shrink,
+                                        int32_t* out_xy, int32_t* out_bounds) {
+  CSM_REQUIRE(ctx != nullptr && job != nullptr && out_xy != nullptr && out_bounds != nullptr, "NULL argument");
+  CSM_REQUIRE(job->num_points >= 1 && job->num_scans >= 1 && job->points_xyz && job->scan_quat,
+              "job needs points and a scan table");
+  if (job->num_points > kNoAllocMaxPoints || job->num_scans > kNoAllocMaxScans ||
+      static_cast<long long>(job->num_points) * job->num_scans > kNoAllocMaxCells) {
+    set_error("csm_discretize2d_noalloc: %d points x %d scans exceed the fixed scratch (at most %d points, %d "
+              "scans, %lld points x scans); use csm_discretize2d",
+              job->num_points, job->num_scans, kNoAllocMaxPoints, kNoAllocMaxScans, kNoAllocMaxCells);
+    return CSM_ERR_ARG;
+  }
+  CSM_CUDA(cudaSetDevice(ctx->device));
+  unsigned char* base = nullptr;
+  const int rc = noalloc_scratch(ctx->device, &base);
+  if (rc != CSM_OK) return rc;
+  JobDev j;
+  memset(&j, 0, sizeof(j));
+  j.num_x = num_x;
+  j.num_y = num_y;
+  j.depth = 1;
+  j.n = job->num_points;
+  j.S = job->num_scans;
+  j.lin = job->linear_bound;
+  j.q0w = job->init_quat_w;
+  j.q0s = job->init_quat_s;
+  j.tx = job->init_tx;
+  j.ty = job->init_ty;
+  j.max_x = job->max_x;
+  j.max_y = job->max_y;
+  j.res = job->resolution;
+  JobDev* d_job = reinterpret_cast<JobDev*>(base);
+  float* d_pts = reinterpret_cast<float*>(base + kNaJob);
+  float* d_quat = reinterpret_cast<float*>(base + kNaJob + kNaPts);
+  int2* d_xy = reinterpret_cast<int2*>(base + kNaJob + kNaPts + kNaQuat);
+  ScanInfo* d_scan = reinterpret_cast<ScanInfo*>(base + kNaJob + kNaPts + kNaQuat + kNaXy);
+  cudaStream_t st = ctx->stream;
+  // `j` is on this frame: the copy must have left it before we return (the stream is synchronised below).
+  CSM_CUDA(cudaMemcpyAsync(d_job, &j, sizeof(j), cudaMemcpyHostToDevice, st));
+  CSM_CUDA(cudaMemcpyAsync(d_pts, job->points_xyz, sizeof(float) * 3 * j.n, cudaMemcpyHostToDevice, st));
+  CSM_CUDA(cudaMemcpyAsync(d_quat, job->scan_quat, sizeof(float) * 2 * j.S, cudaMemcpyHostToDevice, st));
+  ++ctx->launches, k_discretize<<<dim3(j.S, 1), 128, 0, st>>>(d_job, d_pts, d_quat, d_xy, d_scan, nullptr, nullptr,
+                                                              shrink);
+  CSM_CUDA(cudaGetLastError());
+  CSM_CUDA(cudaMemcpyAsync(out_xy, d_xy, sizeof(int2) * static_cast<size_t>(j.S) * j.n, cudaMemcpyDeviceToHost, st));
+  // ScanInfo starts with (min_x, max_x, min_y, max_y): a strided copy drops the other four ints.
+  CSM_CUDA(cudaMemcpy2DAsync(out_bounds, 4 * sizeof(int32_t), d_scan, sizeof(ScanInfo), 4 * sizeof(int32_t), j.S,
+                             cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaStreamSynchronize(st));
+  return CSM_OK;
+}

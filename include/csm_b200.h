@@ -173,6 +173,20 @@ void csm_batch2d_destroy(csm_ctx* ctx, csm_batch2d* batch);
 int csm_discretize2d(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, int shrink,
                      int32_t* out_xy, int32_t* out_bounds);
 
+/* csm_discretize2d for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses
+ * that forbid cudaMalloc.  Same kernel, same arguments and outputs as csm_discretize2d, but the scratch
+ * (job descriptor, points, scan table, discrete scans, per-scan windows) is one fixed device array
+ * inside the library instead of the context's growable buffer, and the call makes no cudaMalloc /
+ * cudaFree / cudaHostAlloc and no host allocation.
+ * Limits: num_points <= 4096, num_scans <= 4096, num_scans * num_points <= 524288; larger inputs
+ * are rejected with CSM_ERR_ARG and a message naming the limits (use csm_discretize2d then).
+ * Every GPU that loads the library holds the array (about 4.2 MiB) until exit.  All calls share it
+ * and it keeps the last call's contents (the kernel overwrites every element it copies out, nothing
+ * has to be cleared): calls that overlap on the GPU -- other contexts, streams or threads -- race. */
+int csm_discretize2d_noalloc(csm_ctx* ctx, const csm_job2d* job, int num_x, int num_y, int shrink,
+                             int32_t* out_xy, int32_t* out_bounds);
+
 /* ---- the free functions of CSM2D.h:63-72 (the matchers fuse them; the reference's tests and
  * any other caller reach them here).
  * csm_rotate_scans2d: GenerateRotatedScans (CSM2D.cc:93-109): out_xyz = num_scans x num_points x 3,
