@@ -150,6 +150,8 @@ int csm_ctx_create(int device, csm_ctx** out) {
     c->sweep_tiles = sweep != nullptr && strcmp(sweep, "tiles") == 0;
     const char* ld = getenv("CSM_EXPAND_LOAD");  // experiment: "noalloc" = L1::no_allocate loads
     c->expand_noalloc = ld != nullptr && strcmp(ld, "noalloc") == 0;
+    const char* p2 = getenv("CSM_PHASE2");  // second opinion: "dfs" = the ordered walk of round 1
+    c->phase2_dfs = p2 != nullptr && strcmp(p2, "dfs") == 0;
   }
   CSM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CSM_CUDA(cudaEventCreate(&c->ev0));

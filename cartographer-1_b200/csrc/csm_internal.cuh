@@ -96,6 +96,8 @@ struct csm_ctx {
   csm::DevBuf frontier_aux;             // 2D node sweep: block descriptors | work items
   bool sweep_tiles = false;             // CSM_SWEEP=tiles: the tile sweep instead of node lists
   bool expand_noalloc = false;          // CSM_EXPAND_LOAD=noalloc: L1::no_allocate loads in the sweep
+  bool phase2_dfs = false;              // CSM_PHASE2=dfs: the ordered walk over top-level contenders
+                                        // instead of sibling-rank paths carried through the sweep
   unsigned long long frontier_cap = 0;  // unused (capacities come from the buffers)
   // Work-list sizes learned from earlier batches on this context, per lowest-resolution
   // candidate: a batch that overflowed a list (and was replayed) makes the next ones ask for

@@ -52,6 +52,9 @@ constexpr int kWarp = 32;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kCntContenders = 32;
 constexpr int kCntOverflow = 33;
+constexpr int kCntLeaves = 35;        // path mode: leaves recorded
+constexpr int kCntDeferred = 36;      // path mode: nodes set aside (bound == incumbent)
+constexpr int kCntDeferCursor = 37;   // path mode: next deferred node to walk
 constexpr int kNumCounters = 112;
 
 // Tile shape: kTW x kTH parents, lane = lj * kTW + li.
@@ -354,7 +357,7 @@ k_scan_prefix(const JobDev* __restrict__ jobs, ScanInfo* __restrict__ scans,
     st.group_best = 0u;
     st.tie_count = 0u;
     st.total = too_big ? 0u : static_cast<unsigned int>(carry);
-    st.pad = 0u;
+    st.cand_max = 0u;
     st.scored = 0ull;
     for (int k = 0; k < 4; ++k) st.scored_phase[k] = 0ull;
     state[blockIdx.x] = st;
@@ -395,6 +398,22 @@ __device__ __forceinline__ float threshold(const JobDev& j, const JobState* st) 
   const unsigned int hi = static_cast<unsigned int>(b >> 32);
   if (hi == 0u) return j.min_score;
   return fmaxf(j.min_score, ordered_to_float(hi));
+}
+
+// Snapshot of a job's incumbent: the best real leaf score so far (has == false: none yet).
+__device__ __forceinline__ float incumbent(const JobState* st, bool& has) {
+  const unsigned long long b = *reinterpret_cast<const volatile unsigned long long*>(&st->best);
+  const unsigned int hi = static_cast<unsigned int>(b >> 32);
+  has = hi != 0u;
+  return has ? ordered_to_float(hi) : 0.f;
+}
+
+// Path mode: appends one record to a bounded list (rare events: plain atomics).
+template <typename T>
+__device__ __forceinline__ void push_record(T* __restrict__ list, unsigned int* __restrict__ counter,
+                                            unsigned int cap, unsigned int* __restrict__ overflow, const T& rec) {
+  const unsigned int slot = atomicAdd(counter, 1u);
+  if (slot < cap) list[slot] = rec; else atomicOr(overflow, 4u);
 }
 
 // ---------------------------------------------------------------------------
@@ -820,7 +839,8 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
              const float* __restrict__ top_scores, const JobState* __restrict__ state,
              unsigned int* __restrict__ tmp, NodeBlock* __restrict__ blocks,
              unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ counters, int slot,
-             unsigned long long cap, unsigned long long block_cap) {
+             unsigned long long cap, unsigned long long block_cap, unsigned int* __restrict__ tmp_path,
+             Deferred2* __restrict__ deferred, unsigned int record_cap) {
   __shared__ unsigned int buf_all[kSeedWarps][128];
   const JobDev& j = jobs[blockIdx.y];
   const int scan = blockIdx.x;
@@ -841,16 +861,35 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
     src = __shfl_sync(kFull, src, 0);
     __syncwarp();
     if (src != ~0u)
-      for (int t = lane; t < held; t += kWarp) tmp[src + t] = buf[t];
+      for (int t = lane; t < held; t += kWarp) {
+        tmp[src + t] = buf[t];
+        if (tmp_path != nullptr) tmp_path[src + t] = 0u;  // a top-level candidate: empty path
+      }
     __syncwarp();
     held = 0;
   };
+  bool has_inc = false;
+  const float inc = incumbent(&state[blockIdx.y], has_inc);
   for (int t = warp; t < tiles_x * tiles_y; t += kSeedWarps) {
     const int ti = t % tiles_x, cj = t / tiles_x;
     const int ci = kWarp * ti + lane;
     bool alive = false;
-    if (ci < si.nx)
-      alive = top_scores[j.cand_off + si.base + ci * si.ny + cj] > thr;
+    if (ci < si.nx) {
+      const float top = top_scores[j.cand_off + si.base + ci * si.ny + cj];
+      alive = top > thr;
+      if (deferred != nullptr && !alive && has_inc && top == inc) {  // bound == incumbent: set aside
+        Deferred2 d;
+        d.job = blockIdx.y;
+        d.scan = scan;
+        d.x = si.min_x + (ci << slot);
+        d.y = si.min_y + (cj << slot);
+        d.depth = slot;
+        d.cand = static_cast<unsigned int>(si.base + ci * si.ny + cj);
+        d.path = 0u;
+        d.score = top;
+        push_record(deferred, &counters[kCntDeferred], record_cap, &counters[kCntOverflow], d);
+      }
+    }
     const uint32_t m = __ballot_sync(kFull, alive);
     if (alive) buf[held + __popc(m & ((1u << lane) - 1u))] = static_cast<unsigned int>(ci | (cj << 16));
     held += __popc(m);
@@ -976,7 +1015,8 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
         const unsigned int* __restrict__ bucket_start, const unsigned int* __restrict__ bucket_istart,
         unsigned int* __restrict__ nodes, uint2* __restrict__ items,
         const unsigned int* __restrict__ counters, int slot, unsigned int num_buckets,
-        unsigned long long cap, unsigned long long block_cap, unsigned long long item_cap) {
+        unsigned long long cap, unsigned long long block_cap, unsigned long long item_cap,
+        const unsigned int* __restrict__ tmp_path, unsigned int* __restrict__ node_path) {
   if (counters[kCntOverflow] & 1u) return;  // the batch is replayed with larger lists
   const int lane = threadIdx.x & 31;
   const unsigned int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -987,6 +1027,8 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
     const NodeBlock nb = blocks[q];
     const unsigned int dst = bucket_base(bucket_start, num_buckets, nb.bucket) + nb.rel;
     for (unsigned int t = lane; t < nb.count; t += kWarp) nodes[dst + t] = tmp[nb.src + t];
+    if (tmp_path != nullptr)
+      for (unsigned int t = lane; t < nb.count; t += kWarp) node_path[dst + t] = tmp_path[nb.src + t];
   }
   // Work items: one THREAD per bucket (most of the 126 k buckets of a C3 step are empty or
   // hold a handful of items; a warp per bucket spent its time on the empty ones).
@@ -1015,7 +1057,9 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
                unsigned int* __restrict__ tmp, NodeBlock* __restrict__ blocks,
                unsigned int* __restrict__ bucket_cnt, unsigned int* __restrict__ counters, int d,
                unsigned long long cap, unsigned long long block_cap, unsigned long long item_cap,
-               unsigned long long* __restrict__ hist) {
+               unsigned long long* __restrict__ hist, const unsigned int* __restrict__ node_path,
+               unsigned int* __restrict__ tmp_path, Leaf2* __restrict__ leaves,
+               Deferred2* __restrict__ deferred, unsigned int record_cap) {
   __shared__ NodeStage stage_all[kExpandWarps];
   if (counters[kCntOverflow] & 1u) return;
   const unsigned int count =
@@ -1043,30 +1087,74 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
     const int job = js >> 16, scan = js & 0xFFFF;
     const JobDev& j = jobs[job];
     JobState* st = &state[job];
-    float thr = threshold(j, st);
-    thr = __shfl_sync(kFull, thr, 0);
     const ScanInfo si = scans[j.scan_off + scan];
     const bool alive = lane < cnt;
     const unsigned int node = nodes[item.x + (alive ? lane : 0)];
     const int ni = node & 0xFFFF, nj = node >> 16;
+    const bool paths = node_path != nullptr;
     if (hist != nullptr && lane == 0) atomicAdd(&hist[d * 33 + cnt], 1ull);
     int sum[4];
     node_sums<kNoAlloc>(*j.sd, xy + j.xy_off + static_cast<long long>(scan) * j.n, j.n, lvl,
               si.min_x + (two_s - 1), si.min_y + (two_s - 1), ni, nj, lane, stage, sum);
+    // One snapshot of the incumbent per item, warp-uniform (it moves under concurrent atomics),
+    // taken after the sums: fresher, and nothing of it is live across the summing loop.
+    unsigned long long snap = *reinterpret_cast<const volatile unsigned long long*>(&st->best);
+    snap = __shfl_sync(kFull, snap, 0);
+    const bool has_inc = (snap >> 32) != 0ull;
+    const float inc = has_inc ? ordered_to_float(static_cast<unsigned int>(snap >> 32)) : 0.f;
+    const float thr = has_inc ? fmaxf(j.min_score, inc) : j.min_score;
+    const unsigned int ppath = paths ? node_path[item.x + (alive ? lane : 0)] : 0u;
     // Children lattice of this scan on level lvl (FCSM2D.cc:353-367: a child beyond
     // max_x / max_y is not generated).
     const int nxl = ((si.max_x - si.min_x) >> lvl) + 1, nyl = ((si.max_y - si.min_y) >> lvl) + 1;
     const int ci0 = 2 * ni, cj0 = 2 * nj;
-    bool pass[4];
+    bool pass[4], valid[4];
     float sc[4];
     int nvalid = 0, npass = 0;
+    bool any_tie = false;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const bool valid = alive && ci0 + (k >> 1) < nxl && cj0 + (k & 1) < nyl;
+      valid[k] = alive && ci0 + (k >> 1) < nxl && cj0 + (k & 1) < nyl;
       sc[k] = to_score(j, sum[k]);
-      pass[k] = valid && sc[k] > thr;
-      nvalid += valid ? 1 : 0;
+      pass[k] = valid[k] && sc[k] > thr;
+      any_tie = any_tie || (valid[k] && has_inc && sc[k] == inc);
+      nvalid += valid[k] ? 1 : 0;
       npass += pass[k] ? 1 : 0;
+    }
+    // Path mode: rank of every child among its sorted siblings (score descending, generation
+    // order among equals), packed two bits each.  A bound that EQUALS the incumbent is neither
+    // expanded nor forgotten: it is set aside (interior node) or recorded (leaf).
+    unsigned int ranks = 0u;
+    if (paths && (npass != 0 || any_tie)) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        unsigned int r = 0u;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          r += (q != k && valid[q] && (sc[q] > sc[k] || (sc[q] == sc[k] && q < k))) ? 1u : 0u;
+        ranks |= r << (2 * k);
+      }
+    }
+    if (paths && any_tie) {
+      const int top_shift = j.depth - 1 - lvl;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (!(valid[k] && has_inc && sc[k] == inc)) continue;
+        const int ci = ci0 + (k >> 1), cj = cj0 + (k & 1);
+        const unsigned int cand = static_cast<unsigned int>(si.base + (ci >> top_shift) * si.ny + (cj >> top_shift));
+        const unsigned int path = (ppath << 2) | ((ranks >> (2 * k)) & 3u);
+        if (lvl == 0) {
+          Leaf2 lf;
+          lf.job = job; lf.scan = scan; lf.x = si.min_x + ci; lf.y = si.min_y + cj;
+          lf.cand = cand; lf.path = path; lf.score = sc[k]; lf.pad = 0;
+          push_record(leaves, &counters[kCntLeaves], record_cap, &counters[kCntOverflow], lf);
+        } else {
+          Deferred2 df;
+          df.job = job; df.scan = scan; df.x = si.min_x + (ci << lvl); df.y = si.min_y + (cj << lvl);
+          df.depth = lvl; df.cand = cand; df.path = path; df.score = sc[k];
+          push_record(deferred, &counters[kCntDeferred], record_cap, &counters[kCntOverflow], df);
+        }
+      }
     }
     const int tot = __reduce_add_sync(kFull, nvalid);
     if (job != acc_job) {
@@ -1090,6 +1178,13 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
         const unsigned long long cur =
             *reinterpret_cast<const volatile unsigned long long*>(&st->best);
         if (key > cur) atomicMax(&st->best, key);
+        if (paths) {
+          Leaf2 lf;
+          lf.job = job; lf.scan = scan; lf.x = si.min_x + ci; lf.y = si.min_y + cj;
+          lf.cand = static_cast<unsigned int>(si.base + ix * si.ny + iy);
+          lf.path = (ppath << 2) | ((ranks >> (2 * k)) & 3u); lf.score = sc[k]; lf.pad = 0;
+          push_record(leaves, &counters[kCntLeaves], record_cap, &counters[kCntOverflow], lf);
+        }
       }
     } else {
       // Survivors are emitted as two ROW RUNS per work item: the even-row children
@@ -1115,6 +1210,14 @@ k_expand_nodes(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
         if (src != ~0u) {
           unsigned int at_e = src + (pre & 0xFFFF) - ne;
           unsigned int at_o = src + total_e + (pre >> 16) - no;
+          if (paths) {
+            const unsigned int pp = ppath << 2;
+            unsigned int pe = at_e, po = at_o;
+            if (pass[0]) tmp_path[pe++] = pp | (ranks & 3u);
+            if (pass[2]) tmp_path[pe] = pp | ((ranks >> 4) & 3u);
+            if (pass[1]) tmp_path[po++] = pp | ((ranks >> 2) & 3u);
+            if (pass[3]) tmp_path[po] = pp | ((ranks >> 6) & 3u);
+          }
           if (pass[0]) tmp[at_e++] = static_cast<unsigned int>(ci0 | (cj0 << 16));
           if (pass[2]) tmp[at_e] = static_cast<unsigned int>((ci0 + 1) | (cj0 << 16));
           if (pass[1]) tmp[at_o++] = static_cast<unsigned int>(ci0 | ((cj0 + 1) << 16));
@@ -1324,6 +1427,182 @@ k_pick(JobState* __restrict__ state, const Contender* __restrict__ list,
   atomicMin(&st->win, (static_cast<unsigned long long>(ct.cand) << 32) | i);
 }
 
+// ---------------------------------------------------------------------------
+// 6'. path mode: the winner from the leaves the sweep recorded.
+// ---------------------------------------------------------------------------
+// One warp per set-aside node whose bound equals the final S*: depth-first in the reference's
+// sibling order over nodes with bound >= S*; the first leaf reached attains S* and is the first
+// S*-leaf of that subtree.  Its path continues the node's.  Few nodes qualify (exact ties of a
+// bound with the best leaf), so single-path latency does not matter here.
+__global__ void __launch_bounds__(128)
+k_deferred_dfs(const JobDev* __restrict__ jobs, const int2* __restrict__ xy,
+               const ScanInfo* __restrict__ scans, JobState* __restrict__ state,
+               const Deferred2* __restrict__ list, Leaf2* __restrict__ leaves,
+               unsigned int* __restrict__ counters, unsigned int cap) {
+  const unsigned int count = min(counters[kCntDeferred], cap);
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    unsigned int i = 0u;
+    if (lane == 0) i = atomicAdd(&counters[kCntDeferCursor], 1u);
+    i = __shfl_sync(kFull, i, 0);
+    if (i >= count) break;
+    const Deferred2 df = list[i];
+    const JobDev& j = jobs[df.job];
+    const float s_star = ordered_to_float(static_cast<unsigned int>(state[df.job].best >> 32));
+    if (!(df.score == s_star)) continue;  // its bound stayed below the best leaf: nothing to find
+    const ScanInfo si = scans[j.scan_off + df.scan];
+    int fx[CSM_MAX_DEPTH], fy[CSM_MAX_DEPTH];
+    unsigned int forder[CSM_MAX_DEPTH], fpath[CSM_MAX_DEPTH];
+    int fcount[CSM_MAX_DEPTH], fnext[CSM_MAX_DEPTH];
+    int lv = 0;
+    fx[0] = df.x;
+    fy[0] = df.y;
+    fpath[0] = df.path;
+    fcount[0] = -1;
+    bool found = false;
+    int leaf_x = 0, leaf_y = 0;
+    unsigned int leaf_path = 0u;
+    unsigned long long scored = 0;
+    while (lv >= 0 && !found) {
+      const int d = df.depth - lv;
+      const int half = 1 << (d - 1);
+      if (fcount[lv] < 0) {
+        const Children c = score_children(j, xy, si, df.scan, fx[lv], fy[lv], d, lane);
+        int idx[4], n = 0;
+        for (int k = 0; k < 4; ++k) {
+          scored += c.valid[k] ? 1 : 0;
+          if (!(c.valid[k] && c.score[k] >= s_star && c.score[k] > j.min_score)) continue;
+          int pos = n++;
+          while (pos > 0 && c.score[idx[pos - 1]] < c.score[k]) {  // stable insertion
+            idx[pos] = idx[pos - 1];
+            --pos;
+          }
+          idx[pos] = k;
+        }
+        if (d == 1) {
+          if (n > 0) {  // leaves cannot exceed S*: the first survivor attains it, with rank 0
+            found = true;
+            leaf_x = fx[lv] + ((idx[0] & 2) ? half : 0);
+            leaf_y = fy[lv] + ((idx[0] & 1) ? half : 0);
+            leaf_path = fpath[lv] << 2;
+          } else {
+            --lv;
+          }
+          continue;
+        }
+        unsigned int packed = 0;
+        for (int k = 0; k < n; ++k) packed |= static_cast<unsigned int>(idx[k]) << (2 * k);
+        forder[lv] = packed;
+        fcount[lv] = n;
+        fnext[lv] = 0;
+      }
+      if (fnext[lv] < fcount[lv]) {
+        // survivors (bound >= S*) precede every other sibling in sorted order, so the position
+        // among them IS the rank among all siblings
+        const int k = (forder[lv] >> (2 * fnext[lv])) & 3;
+        fpath[lv + 1] = (fpath[lv] << 2) | static_cast<unsigned int>(fnext[lv]);
+        ++fnext[lv];
+        fx[lv + 1] = fx[lv] + ((k & 2) ? half : 0);
+        fy[lv + 1] = fy[lv] + ((k & 1) ? half : 0);
+        fcount[lv + 1] = -1;
+        ++lv;
+      } else {
+        --lv;
+      }
+    }
+    if (lane == 0) {
+      if (found) {
+        Leaf2 lf;
+        lf.job = df.job; lf.scan = df.scan; lf.x = leaf_x; lf.y = leaf_y;
+        lf.cand = df.cand; lf.path = leaf_path; lf.score = s_star; lf.pad = 0;
+        push_record(leaves, &counters[kCntLeaves], cap, &counters[kCntOverflow], lf);
+      }
+      atomicAdd(&state[df.job].scored, scored);
+      atomicAdd(&state[df.job].scored_phase[3], scored);
+    }
+  }
+}
+
+// Depth-1 stacks are not swept: their lowest-resolution candidates ARE the leaves, and k_dive has
+// offered the best of every scan.  Every candidate that attains S* is recorded.
+__global__ void __launch_bounds__(256)
+k_leaves_depth1(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans,
+                const float* __restrict__ top_scores, const JobState* __restrict__ state,
+                Leaf2* __restrict__ leaves, unsigned int* __restrict__ counters, unsigned int cap) {
+  const JobDev& j = jobs[blockIdx.y];
+  const int scan = blockIdx.x;
+  if (scan >= j.S || j.depth != 1) return;
+  const unsigned long long best = state[blockIdx.y].best;
+  if ((best >> 32) == 0ull) return;
+  const float s_star = ordered_to_float(static_cast<unsigned int>(best >> 32));
+  const ScanInfo si = scans[j.scan_off + scan];
+  const int count = si.nx * si.ny;
+  for (int c = threadIdx.x; c < count; c += blockDim.x) {
+    const float score = top_scores[j.cand_off + si.base + c];
+    if (!(score == s_star)) continue;
+    const int ix = c / si.ny, iy = c - ix * si.ny;
+    Leaf2 lf;
+    lf.job = blockIdx.y; lf.scan = scan; lf.x = si.min_x + ix; lf.y = si.min_y + iy;
+    lf.cand = static_cast<unsigned int>(si.base + c); lf.path = 0u; lf.score = score; lf.pad = 0;
+    push_record(leaves, &counters[kCntLeaves], cap, &counters[kCntOverflow], lf);
+  }
+}
+
+// stage 0: best top-level score among the ancestors of S*-leaves; stage 1: smallest (ancestor,
+// path) inside that group, and the largest ancestor (more than one ancestor: the host ranks them
+// with the reference's std::sort); stage 2: the winning leaf writes its offsets.
+__global__ void __launch_bounds__(256)
+k_pick_leaf(const JobDev* __restrict__ jobs, const float* __restrict__ top_scores,
+            JobState* __restrict__ state, const Leaf2* __restrict__ leaves,
+            const unsigned int* __restrict__ counters, unsigned int cap, int stage,
+            csm_result2d* __restrict__ results) {
+  const unsigned int count = min(counters[kCntLeaves], cap);
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    const Leaf2 lf = leaves[i];
+    JobState* st = &state[lf.job];
+    if (float_to_ordered(lf.score) != static_cast<unsigned int>(st->best >> 32)) continue;
+    const unsigned int top = float_to_ordered(top_scores[jobs[lf.job].cand_off + lf.cand]);
+    if (stage == 0) {
+      atomicMax(&st->group_best, top);
+      continue;
+    }
+    if (top != st->group_best) continue;
+    const unsigned long long key = (static_cast<unsigned long long>(lf.cand) << 32) | lf.path;
+    if (stage == 1) {
+      atomicMin(&st->win, key);
+      atomicMax(&st->cand_max, lf.cand);
+    } else if (key == st->win) {
+      results[lf.job].scan_index = lf.scan;
+      results[lf.job].x_index_offset = lf.x;
+      results[lf.job].y_index_offset = lf.y;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+k_finalize_paths(const JobDev* __restrict__ jobs, const JobState* __restrict__ state,
+                 csm_result2d* __restrict__ results, int num_jobs) {
+  const int job = blockIdx.x * blockDim.x + threadIdx.x;
+  if (job >= num_jobs) return;
+  const JobState st = state[job];
+  csm_result2d r;
+  r.found = 0;
+  r.scan_index = r.x_index_offset = r.y_index_offset = 0;  // Candidate2D(0, 0, 0) (FCSM2D.cc:345)
+  r.score = jobs[job].min_score;
+  r.tie_resolution = 0;
+  r.candidates_scored = st.scored;
+  if ((st.best >> 32) != 0ull) {
+    r.score = ordered_to_float(static_cast<unsigned int>(st.best >> 32));
+    if (st.win == ~0ull) {
+      r.found = -1;  // internal inconsistency: no recorded leaf attains the best score
+    } else {
+      r.found = 1;
+      r.tie_resolution = st.cand_max != static_cast<unsigned int>(st.win >> 32) ? 2 : 1;  // 2: host replay
+    }
+  }
+  results[job] = r;
+}
+
 __global__ void __launch_bounds__(128)
 k_finalize(const JobDev* __restrict__ jobs, const JobState* __restrict__ state,
            const Contender* __restrict__ list, csm_result2d* __restrict__ results, int num_jobs) {
@@ -1389,7 +1668,10 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   const size_t o_sbest = take(sizeof(unsigned long long) * b->total_scans);
   const size_t o_top = take(sizeof(float) * b->total_cand);
   const size_t o_state = take(sizeof(JobState) * b->num_jobs);
-  const size_t o_cont = take(sizeof(Contender) * contender_cap);
+  const bool dfs = b->owner->phase2_dfs;
+  const size_t o_cont = take(dfs ? sizeof(Contender) * contender_cap : 0);
+  const size_t o_leaf = take(dfs ? 0 : sizeof(Leaf2) * contender_cap);
+  const size_t o_defer = take(dfs ? 0 : sizeof(Deferred2) * contender_cap);
   const size_t o_cnt = take(sizeof(unsigned int) * kNumCounters);
   const size_t o_res = take(sizeof(csm_result2d) * b->num_jobs);
   const size_t o_hist = take(sizeof(unsigned long long) * CSM_MAX_DEPTH * 33);
@@ -1417,6 +1699,8 @@ int allocate_batch(csm_batch2d* b, unsigned int contender_cap) {
   b->top_scores = reinterpret_cast<float*>(base + o_top);
   b->state = reinterpret_cast<JobState*>(base + o_state);
   b->contenders = reinterpret_cast<Contender*>(base + o_cont);
+  b->leaves = reinterpret_cast<Leaf2*>(base + o_leaf);
+  b->deferred = reinterpret_cast<Deferred2*>(base + o_defer);
   b->counters = reinterpret_cast<unsigned int*>(base + o_cnt);
   b->results_dev = reinterpret_cast<csm_result2d*>(base + o_res);
   b->hist = reinterpret_cast<unsigned long long*>(base + o_hist);
@@ -1645,7 +1929,9 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   const unsigned long long node_cap = 2ull * b->frontier_want;
   const unsigned long long block_cap = node_cap / 16ull + 8ull * nbuckets + 4096ull;
   const unsigned long long item_cap = node_cap / 16ull + nbuckets + 4096ull;
-  const size_t want_list = tiles ? sizeof(Tile) * b->frontier_want : sizeof(unsigned int) * node_cap;
+  const bool paths = !tiles && !ctx->phase2_dfs;  // every node carries its sibling-rank path
+  const size_t want_list =
+      tiles ? sizeof(Tile) * b->frontier_want : sizeof(unsigned int) * node_cap * (paths ? 2 : 1);
   const size_t o_items = align_up(sizeof(NodeBlock) * block_cap);
   const size_t want_aux = tiles ? 0 : o_items + sizeof(uint2) * item_cap;
   if (ctx->frontier[0].cap < want_list || ctx->frontier[1].cap < want_list ||
@@ -1660,6 +1946,11 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
   const unsigned long long fcap = b->frontier_want;
   unsigned int* const node_list = ctx->frontier[0].as<unsigned int>();
   unsigned int* const node_tmp = ctx->frontier[1].as<unsigned int>();
+  unsigned int* const node_path = paths ? node_list + node_cap : nullptr;
+  unsigned int* const tmp_path = paths ? node_tmp + node_cap : nullptr;
+  Leaf2* const leaves = paths ? b->leaves : nullptr;
+  Deferred2* const deferred = paths ? b->deferred : nullptr;
+  const unsigned int record_cap = b->contender_cap;
   NodeBlock* const node_blocks = ctx->frontier_aux.as<NodeBlock>();
   uint2* const node_items =
       want_aux ? reinterpret_cast<uint2*>(ctx->frontier_aux.as<char>() + o_items) : nullptr;
@@ -1728,34 +2019,59 @@ int csm_batch2d_run(csm_ctx* ctx, csm_batch2d* b) {
       if (any)
         ++ctx->launches, k_seed_nodes<<<grid_sj, kSeedWarps * kWarp, 0, st>>>(
             b->jobs, b->scans, b->top_scores, b->state, node_tmp, node_blocks, b->bucket_cnt,
-            b->counters, d, node_cap, block_cap);
+            b->counters, d, node_cap, block_cap, tmp_path, deferred, record_cap);
       ++ctx->launches, k_bucket_prefix<<<static_cast<unsigned int>((nbuckets + kPrefixChunk - 1) / kPrefixChunk), 1024, 0, st>>>(
           b->bucket_cnt, b->bucket_start, b->bucket_istart, b->counters, d,
           static_cast<unsigned int>(nbuckets), node_cap, item_cap);
       ++ctx->launches, k_place<<<ctx->num_sms * 4, 256, 0, st>>>(
           node_tmp, node_blocks, b->bucket_start, b->bucket_istart, node_list, node_items,
-          b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap);
+          b->counters, d, static_cast<unsigned int>(nbuckets), node_cap, block_cap, item_cap, tmp_path, node_path);
       mark_depth(d, false);
       ++ctx->launches, (ctx->expand_noalloc ? k_expand_nodes<true> : k_expand_nodes<false>)<<<ctx->num_sms * kNodeBlocksPerSm, kExpandWarps * kWarp, 0, st>>>(
           b->jobs, b->xy, b->scans, b->top_scores, b->state, b->bucket_js, node_list, node_items,
-          node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist);
+          node_tmp, node_blocks, b->bucket_cnt, b->counters, d, node_cap, block_cap, item_cap, hist, node_path,
+          tmp_path, leaves, deferred, record_cap);
       mark_depth(d, false);
       if (ctx->profiling >= 2)
         ++ctx->launches, k_item_stats<<<ctx->num_sms * 4, 256, 0, st>>>(
             b->jobs, b->bucket_js, node_list, node_items, b->counters, d, item_cap, b->depth_stats);
     }
     mark();
-    ++ctx->launches, k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
-                                       b->counters, b->contender_cap);
-    ++ctx->launches, k_ordered_dfs<<<ctx->num_sms * 8, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->state,
-                                                    b->contenders, b->counters, b->contender_cap);
-    ++ctx->launches, k_pick<<<(b->contender_cap + 255) / 256, 256, 0, st>>>(b->state, b->contenders, b->counters,
-                                                           b->contender_cap);
+    if (paths) {
+      bool any_depth1 = false;
+      for (const JobDev& j : b->jobs_host) any_depth1 = any_depth1 || (j.depth == 1 && j.S > 0);
+      ++ctx->launches, k_deferred_dfs<<<ctx->num_sms * 4, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->state,
+                                                                    b->deferred, b->leaves, b->counters, record_cap);
+      if (any_depth1)
+        ++ctx->launches, k_leaves_depth1<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state,
+                                                                b->leaves, b->counters, record_cap);
+    } else {
+      ++ctx->launches, k_collect<<<grid_sj, 256, 0, st>>>(b->jobs, b->scans, b->top_scores, b->state, b->contenders,
+                                         b->counters, b->contender_cap);
+      ++ctx->launches, k_ordered_dfs<<<ctx->num_sms * 8, 128, 0, st>>>(b->jobs, b->xy, b->scans, b->state,
+                                                      b->contenders, b->counters, b->contender_cap);
+      ++ctx->launches, k_pick<<<(b->contender_cap + 255) / 256, 256, 0, st>>>(b->state, b->contenders, b->counters,
+                                                             b->contender_cap);
+    }
   } else {
     CSM_CUDA(cudaMemsetAsync(b->state, 0, sizeof(JobState) * nj, st));
     for (int k = 0; k < 4; ++k) mark();
   }
-  ++ctx->launches, k_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
+  if (paths) {
+    // The number of recorded leaves is known on the device only; the grids cover a modest count
+    // and the rest is strided over (ties of whole worlds are the rare case).
+    const bool ran = b->max_scans > 0;
+    const unsigned int leaf_blocks = std::min(record_cap, 1u << 18) / 256 + 1;
+    for (int stage = 0; ran && stage < 2; ++stage)
+      ++ctx->launches, k_pick_leaf<<<leaf_blocks, 256, 0, st>>>(b->jobs, b->top_scores, b->state, b->leaves,
+                                                              b->counters, record_cap, stage, b->results_dev);
+    ++ctx->launches, k_finalize_paths<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->results_dev, nj);
+    if (ran)
+      ++ctx->launches, k_pick_leaf<<<leaf_blocks, 256, 0, st>>>(b->jobs, b->top_scores, b->state, b->leaves,
+                                                              b->counters, record_cap, 2, b->results_dev);
+  } else {
+    ++ctx->launches, k_finalize<<<(nj + 127) / 128, 128, 0, st>>>(b->jobs, b->state, b->contenders, b->results_dev, nj);
+  }
   mark();
   CSM_CUDA(cudaGetLastError());
   // Results and counters follow the kernels into the pinned block; fetch() waits for this
@@ -1790,7 +2106,7 @@ struct ScoreIdx {
 };
 
 int resolve_tie(csm_ctx* ctx, csm_batch2d* b, int job, const std::vector<Contender>& list,
-                csm_result2d* r) {
+                const std::vector<Leaf2>& leaves, csm_result2d* r) {
   const JobDev& j = b->jobs_host[job];
   JobState st;
   CSM_CUDA(cudaMemcpyAsync(&st, b->state + job, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1804,6 +2120,26 @@ int resolve_tie(csm_ctx* ctx, csm_batch2d* b, int job, const std::vector<Contend
   std::sort(v.begin(), v.end(), std::greater<ScoreIdx>());
   std::vector<unsigned int> rank(st.total);
   for (unsigned int i = 0; i < st.total; ++i) rank[v[i].idx] = i;
+  if (!ctx->phase2_dfs) {
+    // Path mode: among the leaves attaining S* whose ancestor has the group's top-level score, the
+    // reference reaches first the one whose ancestor sorts first, then the smallest path.
+    const Leaf2* win = nullptr;
+    for (const Leaf2& lf : leaves) {
+      if (lf.job != job || float_to_ordered(lf.score) != float_to_ordered(r->score) ||
+          float_to_ordered(scores[lf.cand]) != st.group_best)
+        continue;
+      if (!win || rank[lf.cand] < rank[win->cand] || (lf.cand == win->cand && lf.path < win->path)) win = &lf;
+    }
+    if (!win) {
+      set_error("tie replay found no leaf for job %d", job);
+      return CSM_ERR_CUDA;
+    }
+    r->scan_index = win->scan;
+    r->x_index_offset = win->x;
+    r->y_index_offset = win->y;
+    r->tie_resolution = 1;
+    return CSM_OK;
+  }
   const Contender* best = nullptr;
   for (const Contender& c : list) {
     if (c.job != job || !c.has_leaf || float_to_ordered(c.score) != st.group_best) continue;
@@ -1844,8 +2180,9 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
       ctx->frontier_per_candidate = std::max(
           ctx->frontier_per_candidate, static_cast<double>(b->frontier_want) / std::max<double>(1., b->total_cand));
     }
-    unsigned long long ccap = (ov & 4u) ? static_cast<unsigned long long>(counters[kCntContenders]) + 1024ull
-                                        : b->contender_cap;
+    const unsigned int records = ctx->phase2_dfs ? counters[kCntContenders]
+                                                 : std::max(counters[kCntLeaves], counters[kCntDeferred]);
+    unsigned long long ccap = (ov & 4u) ? static_cast<unsigned long long>(records) + 1024ull : b->contender_cap;
     if (ov & 4u)
       ctx->contenders_per_candidate = std::max(
           ctx->contenders_per_candidate, 1.5 * static_cast<double>(ccap) / std::max<double>(1., b->total_cand));
@@ -1904,6 +2241,7 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
     b->depth_of_events.clear();
   }
   std::vector<Contender> list;
+  std::vector<Leaf2> leaf_list;
   bool have_list = false;
   for (int i = 0; i < b->num_jobs; ++i) {
     csm_result2d r = pin_res[i];
@@ -1912,7 +2250,7 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
       return CSM_ERR_CUDA;
     }
     if (r.found == 1 && r.tie_resolution > 1) {
-      if (!have_list) {
+      if (!have_list && ctx->phase2_dfs) {
         const unsigned int n = std::min(counters[kCntContenders], b->contender_cap);
         list.resize(n);
         CSM_CUDA(cudaMemcpyAsync(list.data(), b->contenders, sizeof(Contender) * n,
@@ -1920,7 +2258,15 @@ int csm_batch2d_fetch(csm_ctx* ctx, csm_batch2d* b, csm_result2d* results) {
         CSM_CUDA(cudaStreamSynchronize(ctx->stream));
         have_list = true;
       }
-      const int rc = resolve_tie(ctx, b, i, list, &r);
+      if (!have_list && !ctx->phase2_dfs) {
+        const unsigned int n = std::min(counters[kCntLeaves], b->contender_cap);
+        leaf_list.resize(n);
+        CSM_CUDA(cudaMemcpyAsync(leaf_list.data(), b->leaves, sizeof(Leaf2) * n, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+        CSM_CUDA(cudaStreamSynchronize(ctx->stream));
+        have_list = true;
+      }
+      const int rc = resolve_tie(ctx, b, i, list, leaf_list, &r);
       if (rc != CSM_OK) return rc;
     } else {
       r.tie_resolution = 0;

@@ -45,7 +45,7 @@ struct JobState {
   unsigned int group_best;      // phase 2: ordered top score of the winning group
   unsigned int tie_count;       // phase 2: contenders in the winning group that hold an S*-leaf
   unsigned int total;           // top-level candidates of this job
-  unsigned int pad;
+  unsigned int cand_max;        // path mode: largest ancestor index in the winning group (!= win >> 32: tie)
   unsigned long long scored;    // candidate scores evaluated (all phases)
   unsigned long long scored_phase[4];  // score_top, dive, expand, phase 2
 };
@@ -70,6 +70,34 @@ struct Contender {
   int leaf_x, leaf_y;   // first S*-leaf in reference DFS order, valid if has_leaf
   int has_leaf;
   int pad[3];
+};
+
+// Traversal order without a second walk (node sweep).  The reference returns the FIRST leaf
+// attaining the best score S* in its depth-first order: top-level candidates by descending score,
+// then at every level the <= 4 siblings by descending score, generation order among equals
+// (std::sort of <= 16 elements is an insertion sort, i.e. stable).  Every node of the sweep carries
+// its `path`: two bits per level below the top = its rank among its sorted siblings, most
+// significant first.  Among the leaves that attain S*, the winner is the one with the best-ranked
+// top-level ancestor and then the smallest path.
+//   Leaf2:     a leaf whose score was >= the incumbent when it was scored.
+//   Deferred2: a node whose bound EQUALLED the incumbent: the reference prunes it only if the
+//              incumbent was found earlier in ITS order, so it is set aside and, if its bound turns
+//              out to equal S*, walked depth-first in sibling order for its first S*-leaf.
+struct Leaf2 {
+  int job, scan;
+  int x, y;            // index offsets of the leaf (Candidate2D::x_index_offset / y_index_offset)
+  unsigned int cand;   // generation index of its top-level ancestor inside the job
+  unsigned int path;
+  float score;
+  int pad;
+};
+struct Deferred2 {
+  int job, scan;
+  int x, y;            // index offsets of the node
+  int depth;           // its depth (children live on level depth - 1)
+  unsigned int cand;   // top-level ancestor
+  unsigned int path;   // ranks from the top down to this node
+  float score;         // its bound
 };
 
 // Order-preserving map float -> uint32 (works for negative values too).
@@ -141,7 +169,9 @@ struct csm_batch2d {
   csm::JobState* state = nullptr;      // num_jobs
   unsigned long long frontier_want = 0;  // nodes per frontier buffer this batch asks for
   csm::Contender* contenders = nullptr;
-  unsigned int contender_cap = 0;
+  unsigned int contender_cap = 0;        // also the capacity of `leaves` and `deferred`
+  csm::Leaf2* leaves = nullptr;          // path mode
+  csm::Deferred2* deferred = nullptr;    // path mode
   unsigned int* counters = nullptr;    // [0..CSM_MAX_DEPTH]: frontier sizes, [32]: contenders, [33]: overflow
   csm_result2d* results_dev = nullptr;
   unsigned long long* hist = nullptr;  // [depth][alive nodes per tile] tile counts (profiling)
