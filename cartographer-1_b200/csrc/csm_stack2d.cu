@@ -492,6 +492,142 @@ k_stack_rows(const RowsArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Row build, pipelined ("rows2"): the same per-level work as k_stack_rows, but a block owns
+// GROUPS of kGroupRows consecutive rows, walks them with a stride of the grid, and brings the rows of
+// its NEXT group into a second shared-memory buffer with cp.async while it works on the current
+// one -- one row per block left the SMs waiting on a load -> barrier -> store chain (2000 x 2000:
+// 11 us per level for 21 MB).  4-byte cp.async lets every word land at its skewed position.
+// ---------------------------------------------------------------------------
+#ifndef CSM_GROUP_ROWS
+#define CSM_GROUP_ROWS 1
+#endif
+constexpr int kGroupRows = CSM_GROUP_ROWS;
+
+struct Rows2Args {
+  RowsArgs r;
+  int rows_total;             // jn << (log2s + 1): rows of the quad planes (>= wide_y)
+  int nw, rw;                 // staged words per row, row pitch in shared memory (words)
+  int npw, items;             // words of a next-level row, quad work items of a row
+  unsigned int npw_magic, items_magic;  // ceil(2^32 / x): t / x == __umulhi(t, magic) for t < 2^16
+};
+
+__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gsrc) {
+  const unsigned int d = static_cast<unsigned int>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_stack_rows2(const Rows2Args p) {
+  extern __shared__ uint32_t rows32[];
+  cudaGridDependencySynchronize();
+  const RowsArgs& a = p.r;
+  const int s = 1 << a.log2s, two_s = 2 << a.log2s, sh = a.log2s + 1;
+  const int padw = s >= 4 ? (s >> 2) : 1;
+  const int pw = a.pitch >> 2;
+  const int buf_words = 2 * kGroupRows * p.rw;
+  const int groups = (p.rows_total + kGroupRows - 1) / kGroupRows;
+  // rows 0 .. R-1 of a buffer: Y = v0 + r; rows R .. 2R-1: Y = v0 + r - s
+  auto issue = [&](int g, uint32_t* buf) {
+    const int v0 = g * kGroupRows;
+    for (int t = threadIdx.x; t < 2 * kGroupRows * p.nw; t += kThreads) {
+      const int row = t / p.nw, w = t - row * p.nw;
+      const int Y = row < kGroupRows ? v0 + row : v0 + row - kGroupRows - s;
+      const int k = w - padw;
+      uint32_t* dst = buf + row * p.rw + skew(w);
+      if (static_cast<unsigned>(Y) < static_cast<unsigned>(a.wide_y) && static_cast<unsigned>(k) < static_cast<unsigned>(pw))
+        cp_async4(dst, reinterpret_cast<const uint32_t*>(a.lvl + static_cast<size_t>(Y) * a.pitch) + k);
+      else
+        *dst = 0u;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int g = blockIdx.x;
+  if (g >= groups) return;
+  issue(g, rows32);
+  int which = 0;
+  uint32_t* __restrict__ out = a.quad;
+  const size_t plane = static_cast<size_t>(a.in) * a.jn;
+  for (; g < groups; g += gridDim.x, which ^= 1) {
+    uint32_t* buf = rows32 + which * buf_words;
+    const int gn = g + gridDim.x;
+    if (gn < groups) {
+      issue(gn, rows32 + (which ^ 1) * buf_words);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const int v0 = g * kGroupRows;
+    auto taps = [&](const uint32_t* cur, const uint32_t* up, int xw, uint32_t& c0, uint32_t& l0, uint32_t& c1,
+                    uint32_t& l1) {
+      const int ic = skew(xw);
+      c0 = cur[ic];
+      c1 = up[ic];
+      if (s >= 4) {
+        const int il = skew(xw - (s >> 2));
+        l0 = cur[il];
+        l1 = up[il];
+      } else {
+        const int il = skew(xw - 1);
+        l0 = __funnelshift_l(cur[il], c0, 8 * s);
+        l1 = __funnelshift_l(up[il], c1, 8 * s);
+      }
+    };
+    // (1) bytes of level i + 1
+    if (a.next != nullptr) {
+      const int spanw = p.nw - padw;
+      for (int t = threadIdx.x; t < kGroupRows * p.npw; t += kThreads) {
+        const int row = static_cast<int>(__umulhi(static_cast<unsigned int>(t), p.npw_magic));
+        const int k = t - row * p.npw, v = v0 + row;
+        if (v >= a.next_wide_y) continue;
+        uint32_t m = 0u;
+        if (k < spanw) {
+          uint32_t c0, l0, c1, l1;
+          taps(buf + row * p.rw, buf + (kGroupRows + row) * p.rw, k + padw, c0, l0, c1, l1);
+          m = max4_u8x4(c0, l0, c1, l1);
+        }
+        reinterpret_cast<uint32_t*>(a.next + static_cast<size_t>(v) * a.next_pitch)[k] = m;
+      }
+    }
+    // (2) quad words
+    for (int t = threadIdx.x; t < kGroupRows * p.items; t += kThreads) {
+      const int row = static_cast<int>(__umulhi(static_cast<unsigned int>(t), p.items_magic));
+      const int e = t - row * p.items, v = v0 + row;
+      if (v >= p.rows_total) continue;
+      const uint32_t* cur = buf + row * p.rw;
+      const uint32_t* up = buf + (kGroupRows + row) * p.rw;
+      const size_t rowbase = (static_cast<size_t>((v & (two_s - 1)) << sh) * a.jn + (v >> sh)) * a.in;
+      uint32_t c0, l0, c1, l1;
+      if (a.log2s == 0) {
+        if (2 * e >= a.in) continue;
+        taps(cur, up, e + padw, c0, l0, c1, l1);
+        const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+        const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+        uint32_t* o = out + rowbase + 2 * e;
+        o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+        o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+        if (2 * e + 1 < a.in) {
+          o[1] = __byte_perm(a_hi, b_hi, 0x5410);
+          o[plane + 1] = __byte_perm(a_hi, b_hi, 0x7632);
+        }
+      } else {
+        const int pg = a.in_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(e), a.in_magic)) : e;
+        const int ii = e - pg * a.in;
+        taps(cur, up, ((ii << sh) >> 2) + pg + padw, c0, l0, c1, l1);
+        const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+        const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+        uint32_t* o = out + rowbase + static_cast<size_t>(pg << 2) * plane + ii;
+        o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+        o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+        o[2 * plane] = __byte_perm(a_hi, b_hi, 0x5410);
+        o[3 * plane] = __byte_perm(a_hi, b_hi, 0x7632);
+      }
+    }
+    __syncthreads();  // the buffer is refilled two iterations from now, by the next issue()
+  }
+}
+
 void launch_level0(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const int pw = s->level_pitch[0] >> 2;
   const int passes = (pw + kThreads - 1) / kThreads;
@@ -553,6 +689,65 @@ int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   return CSM_OK;
 }
 
+int launch_build_rows2(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  launch_level0(ctx, s, cells_dev);
+  auto magic = [](int x) { return x > 1 ? static_cast<unsigned int>((0x100000000ull + x - 1) / x) : 0u; };
+  size_t max_smem = 0;
+  std::vector<Rows2Args> args(s->depth);
+  for (int i = 0; i < s->depth; ++i) {
+    Rows2Args& p = args[i];
+    RowsArgs& a = p.r;
+    a.lvl = s->base + s->level_off[i];
+    a.next = i + 1 < s->depth ? s->base + s->level_off[i + 1] : nullptr;
+    a.quad = reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]);
+    a.pitch = s->level_pitch[i];
+    a.next_pitch = i + 1 < s->depth ? s->level_pitch[i + 1] : 0;
+    a.wide_y = s->num_y + (1 << i) - 1;
+    a.next_wide_y = s->num_y + (2 << i) - 1;
+    a.in = s->host_view.in[i];
+    a.jn = s->host_view.jn[i];
+    a.log2s = i;
+    a.in_magic = magic(a.in);
+    const int padw = (1 << i) >= 4 ? (1 << i) >> 2 : 1;
+    p.nw = padw + ((a.in * (2 << i) + 3) >> 2);
+    p.rw = p.nw + (p.nw >> 5) + 2;
+    p.rows_total = a.jn << (i + 1);
+    p.npw = std::max(1, a.next_pitch >> 2);
+    p.items = i == 0 ? (a.in + 1) / 2 : ((2 << i) >> 2) * a.in;
+    p.npw_magic = p.npw > 1 ? magic(p.npw) : 0u;
+    p.items_magic = p.items > 1 ? magic(p.items) : 0u;
+    max_smem = std::max<size_t>(max_smem, static_cast<size_t>(4) * kGroupRows * p.rw * 4);
+  }
+  // t / x via __umulhi needs t < 2^16; one-word rows (x == 1) divide by themselves
+  for (const Rows2Args& p : args)
+    if (kGroupRows * std::max(p.npw, p.items) >= 65536 || p.npw == 1 || p.items == 1)
+      return launch_build_rows(ctx, s, cells_dev);
+  if (max_smem > 200 * 1024) return launch_build_rows(ctx, s, cells_dev);
+  if (max_smem > 48 * 1024)
+    CSM_CUDA(cudaFuncSetAttribute(k_stack_rows2, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(max_smem)));
+  for (int i = 0; i < s->depth; ++i) {
+    const Rows2Args& p = args[i];
+    const size_t smem = static_cast<size_t>(4) * kGroupRows * p.rw * 4;
+    const int groups = (p.rows_total + kGroupRows - 1) / kGroupRows;
+    const int per_sm = static_cast<int>(std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / smem)));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(std::min(groups, ctx->num_sms * per_sm));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ++ctx->launches;
+    CSM_CUDA(cudaLaunchKernelEx(&cfg, k_stack_rows2, p));
+  }
+  CSM_CUDA(cudaGetLastError());
+  return CSM_OK;
+}
+
 int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev);
 
 int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
@@ -563,8 +758,10 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     const char* e = getenv("CSM_STACK_BUILD");
     if (e != nullptr && strcmp(e, "levelwise") == 0) return 2;
     if (e != nullptr && strcmp(e, "fused") == 0) return 1;
+    if (e != nullptr && strcmp(e, "rows2") == 0) return 3;
     return 0;
   }();
+  if (mode == 3) return launch_build_rows2(ctx, s, cells_dev);
   if (mode == 1 && s->depth <= kFusedMaxDepth) return launch_build_fused(ctx, s, cells_dev);
   if (mode == 2) return launch_build_levelwise(ctx, s, cells_dev);
   return launch_build_rows(ctx, s, cells_dev);
