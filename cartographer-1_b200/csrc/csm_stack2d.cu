@@ -628,6 +628,173 @@ k_stack_rows2(const Rows2Args p) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Row build, lean ("rows3", the default).  ncu on k_stack_rows (profiles/r02_ncu): one level of a
+// 2000 x 2000 build issues 7.06 M warp instructions -- ~30 per staged word, ~70 per next-level
+// word, ~50 per quad item -- and the issue slots, not memory, bound it.  Same work, fewer
+// instructions:
+//   * rows are staged with 16-byte loads into TWO copies: a linear one (16-byte aligned, for the
+//     vector taps of the next level) and a word-skewed one (conflict-free for the strided reads of
+//     the quad words);
+//   * the next level is computed four words per thread from 16-byte shared-memory loads and
+//     stored with one 16-byte store;
+//   * the quad loop keeps its shape (4 adjacent phases per thread, lanes walk ii) with the
+//     address arithmetic hoisted.
+// PAD zero words in front of X = 0 stand for the taps left of the image: s / 4 for s >= 16, else 4
+// (a multiple of four keeps the data 16-byte aligned).
+// ---------------------------------------------------------------------------
+struct Rows3Args {
+  RowsArgs r;
+  int pad, spanw, nw4;        // zero words in front, data words, staged 16-byte chunks per row
+  int lin_pitch, skw_pitch;   // words per staged row (linear / skewed copy)
+  int npw4, items;            // 16-byte chunks of a next-level row, quad work items of a row
+  int rows_total, rows_per_block;  // a block builds rows_per_block consecutive rows
+};
+
+__device__ __forceinline__ uint4 max4_u8x16(const uint4& a, const uint4& b, const uint4& c, const uint4& d) {
+  return make_uint4(max4_u8x4(a.x, b.x, c.x, d.x), max4_u8x4(a.y, b.y, c.y, d.y), max4_u8x4(a.z, b.z, c.z, d.z),
+                    max4_u8x4(a.w, b.w, c.w, d.w));
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_stack_rows3(const Rows3Args p) {
+  extern __shared__ uint4 rows128[];
+  cudaGridDependencySynchronize();
+  const RowsArgs& a = p.r;
+  const int s = 1 << a.log2s, two_s = 2 << a.log2s, sh = a.log2s + 1;
+  const int nthr = blockDim.x;
+  uint32_t* const lin_cur = reinterpret_cast<uint32_t*>(rows128);
+  uint32_t* const lin_up = lin_cur + p.lin_pitch;
+  uint32_t* const skw_cur = lin_up + p.lin_pitch;
+  uint32_t* const skw_up = skw_cur + p.skw_pitch;
+  const int pw = a.pitch >> 2;
+  const size_t plane = static_cast<size_t>(a.in) * a.jn;
+  // quad work items (pg, ii) = (t / in, t % in) of this thread: one division here, then the
+  // loop over t += nthr advances them with a carry
+  const int pg_first = a.in_magic ? static_cast<int>(__umulhi(threadIdx.x, a.in_magic)) : static_cast<int>(threadIdx.x);
+  const int ii_first = static_cast<int>(threadIdx.x) - pg_first * a.in;
+  const int dpg = a.in_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(nthr), a.in_magic)) : nthr;
+  const int dii = nthr - dpg * a.in;
+  const int v_end = min(p.rows_total, (static_cast<int>(blockIdx.x) + 1) * p.rows_per_block);
+  for (int v = blockIdx.x * p.rows_per_block; v < v_end; ++v) {
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int Y = r == 0 ? v : v - s;
+    uint32_t* const lin = r == 0 ? lin_cur : lin_up;
+    uint32_t* const skw = r == 0 ? skw_cur : skw_up;
+    const bool row_ok = static_cast<unsigned>(Y) < static_cast<unsigned>(a.wide_y);
+    const uint4* __restrict__ src =
+        reinterpret_cast<const uint4*>(a.lvl + static_cast<size_t>(row_ok ? Y : 0) * a.pitch);
+    for (int q = threadIdx.x; q < p.nw4; q += nthr) {
+      const int w0 = 4 * q, k0 = w0 - p.pad;  // k0 is a multiple of 4; pw too: a chunk is all in or all out
+      uint4 x = make_uint4(0u, 0u, 0u, 0u);
+      if (row_ok && k0 >= 0 && k0 < pw) x = __ldg(src + (k0 >> 2));
+      reinterpret_cast<uint4*>(lin)[q] = x;
+      const int sk = skew(w0);  // w0 % 4 == 0: the four words stay inside one 32-word run
+      skw[sk] = x.x;
+      skw[sk + 1] = x.y;
+      skw[sk + 2] = x.z;
+      skw[sk + 3] = x.w;
+    }
+  }
+  __syncthreads();
+  // (1) bytes of level i + 1, row v: four words per thread.
+  if (a.next != nullptr && v < a.next_wide_y) {
+    uint4* __restrict__ orow = reinterpret_cast<uint4*>(a.next + static_cast<size_t>(v) * a.next_pitch);
+    const uint4* c4 = reinterpret_cast<const uint4*>(lin_cur);
+    const uint4* u4 = reinterpret_cast<const uint4*>(lin_up);
+    const int padq = p.pad >> 2, shiftq = s >> 4;  // left tap in 16-byte chunks when s >= 16
+    for (int q = threadIdx.x; q < p.npw4; q += nthr) {
+      const int k0 = 4 * q;
+      uint4 m = make_uint4(0u, 0u, 0u, 0u);
+      if (k0 < p.spanw) {
+        const uint4 C0 = c4[q + padq], C1 = u4[q + padq];
+        uint4 L0, L1;
+        if (s >= 16) {
+          L0 = c4[q + padq - shiftq];
+          L1 = u4[q + padq - shiftq];
+        } else {
+          const uint4 P0 = c4[q + padq - 1], P1 = u4[q + padq - 1];
+          if (s == 8) {
+            L0 = make_uint4(P0.z, P0.w, C0.x, C0.y);
+            L1 = make_uint4(P1.z, P1.w, C1.x, C1.y);
+          } else if (s == 4) {
+            L0 = make_uint4(P0.w, C0.x, C0.y, C0.z);
+            L1 = make_uint4(P1.w, C1.x, C1.y, C1.z);
+          } else {  // the tap is s bytes to the left: shift across neighbouring words
+            const int b = 8 * s;
+            L0 = make_uint4(__funnelshift_l(P0.w, C0.x, b), __funnelshift_l(C0.x, C0.y, b),
+                            __funnelshift_l(C0.y, C0.z, b), __funnelshift_l(C0.z, C0.w, b));
+            L1 = make_uint4(__funnelshift_l(P1.w, C1.x, b), __funnelshift_l(C1.x, C1.y, b),
+                            __funnelshift_l(C1.y, C1.z, b), __funnelshift_l(C1.z, C1.w, b));
+          }
+        }
+        m = max4_u8x16(C0, L0, C1, L1);
+        // words at and beyond spanw are row padding of the next level: zero
+        if (k0 + 1 >= p.spanw) m.y = 0u;
+        if (k0 + 2 >= p.spanw) m.z = 0u;
+        if (k0 + 3 >= p.spanw) m.w = 0u;
+      }
+      orow[q] = m;
+    }
+  }
+  // (2) quad words of row v.  q_j = l1.b_j | l0.b_j << 8 | c1.b_j << 16 | c0.b_j << 24.
+  auto taps = [&](int xw, uint32_t& c0, uint32_t& l0, uint32_t& c1, uint32_t& l1) {
+    const int ic = skew(xw);
+    c0 = skw_cur[ic];
+    c1 = skw_up[ic];
+    if (s >= 4) {
+      const int il = skew(xw - (s >> 2));
+      l0 = skw_cur[il];
+      l1 = skw_up[il];
+    } else {
+      const int il = skew(xw - 1);
+      l0 = __funnelshift_l(skw_cur[il], c0, 8 * s);
+      l1 = __funnelshift_l(skw_up[il], c1, 8 * s);
+    }
+  };
+  uint32_t* __restrict__ const orow =
+      a.quad + (static_cast<size_t>((v & (two_s - 1)) << sh) * a.jn + (v >> sh)) * a.in;
+  if (a.log2s == 0) {
+    for (int k = threadIdx.x; 2 * k < a.in; k += nthr) {
+      uint32_t c0, l0, c1, l1;
+      taps(k + p.pad, c0, l0, c1, l1);
+      const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+      const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+      uint32_t* o = orow + 2 * k;
+      o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+      o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+      if (2 * k + 1 < a.in) {
+        o[1] = __byte_perm(a_hi, b_hi, 0x5410);
+        o[plane + 1] = __byte_perm(a_hi, b_hi, 0x7632);
+      }
+    }
+  } else {
+    const int step_words = two_s >> 2;  // staged words between consecutive ii
+    const int groups = two_s >> 2;      // groups of 4 phases
+    int pg = pg_first, ii = ii_first;
+    while (pg < groups) {
+      uint32_t c0, l0, c1, l1;
+      taps(ii * step_words + pg + p.pad, c0, l0, c1, l1);
+      const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+      const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+      uint32_t* o = orow + static_cast<size_t>(pg << 2) * plane + ii;
+      o[0] = __byte_perm(a_lo, b_lo, 0x5410);
+      o[plane] = __byte_perm(a_lo, b_lo, 0x7632);
+      o[2 * plane] = __byte_perm(a_hi, b_hi, 0x5410);
+      o[3 * plane] = __byte_perm(a_hi, b_hi, 0x7632);
+      pg += dpg;
+      ii += dii;
+      if (ii >= a.in) {
+        ii -= a.in;
+        ++pg;
+      }
+    }
+  }
+  __syncthreads();  // the staged rows are overwritten by the next row of this block
+  }
+}
+
 void launch_level0(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const int pw = s->level_pitch[0] >> 2;
   const int passes = (pw + kThreads - 1) / kThreads;
@@ -684,6 +851,68 @@ int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     cfg.numAttrs = 1;
     ++ctx->launches;
     CSM_CUDA(cudaLaunchKernelEx(&cfg, k_stack_rows, a));
+  }
+  CSM_CUDA(cudaGetLastError());
+  return CSM_OK;
+}
+
+int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+  launch_level0(ctx, s, cells_dev);
+  std::vector<Rows3Args> args(s->depth);
+  size_t max_smem = 0;
+  for (int i = 0; i < s->depth; ++i) {
+    Rows3Args& p = args[i];
+    RowsArgs& a = p.r;
+    a.lvl = s->base + s->level_off[i];
+    a.next = i + 1 < s->depth ? s->base + s->level_off[i + 1] : nullptr;
+    a.quad = reinterpret_cast<uint32_t*>(s->base + s->quad_off[i]);
+    a.pitch = s->level_pitch[i];
+    a.next_pitch = i + 1 < s->depth ? s->level_pitch[i + 1] : 0;
+    a.wide_y = s->num_y + (1 << i) - 1;
+    a.next_wide_y = s->num_y + (2 << i) - 1;
+    a.in = s->host_view.in[i];
+    a.jn = s->host_view.jn[i];
+    a.log2s = i;
+    a.in_magic = a.in > 1 ? static_cast<unsigned int>((0x100000000ull + a.in - 1) / a.in) : 0u;
+    const int sw = 1 << i;
+    p.pad = sw >= 16 ? sw >> 2 : 4;
+    p.spanw = (a.in * (2 << i) + 3) >> 2;
+    p.nw4 = (p.pad + p.spanw + 3) >> 2;
+    p.lin_pitch = 4 * p.nw4;
+    const int nw = 4 * p.nw4;
+    p.skw_pitch = ((nw + (nw >> 5) + 2) + 3) & ~3;
+    p.npw4 = a.next_pitch >> 4;
+    p.items = i == 0 ? (a.in + 1) / 2 : ((2 << i) >> 2) * a.in;
+    p.rows_total = a.jn << (i + 1);
+    // one wave: as many rows per block as it takes to fit the grid into the resident block slots
+    p.rows_per_block = std::max(1, (p.rows_total + ctx->num_sms * 8 - 1) / (ctx->num_sms * 8));
+    max_smem = std::max<size_t>(max_smem, (2 * static_cast<size_t>(p.lin_pitch) + 2 * p.skw_pitch) * 4);
+  }
+  for (const Rows3Args& p : args)  // t / in via __umulhi needs t < 2^16
+    if (p.items >= 65536) return launch_build_rows(ctx, s, cells_dev);
+  if (max_smem > 200 * 1024) return launch_build_rows(ctx, s, cells_dev);
+  if (max_smem > 48 * 1024)
+    CSM_CUDA(cudaFuncSetAttribute(k_stack_rows3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(max_smem)));
+  for (int i = 0; i < s->depth; ++i) {
+    const Rows3Args& p = args[i];
+    const size_t smem = (2 * static_cast<size_t>(p.lin_pitch) + 2 * p.skw_pitch) * 4;
+    // the widest loop is the quad loop (items); size the block so that its passes are full
+    const int widest = std::max(p.items, std::max(p.nw4, p.npw4));
+    const int passes = (widest + kThreads - 1) / kThreads;
+    const int threads = std::min(kThreads, (((widest + passes - 1) / passes) + 31) & ~31);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((p.rows_total + p.rows_per_block - 1) / p.rows_per_block);
+    cfg.blockDim = dim3(std::max(32, threads));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ++ctx->launches;
+    CSM_CUDA(cudaLaunchKernelEx(&cfg, k_stack_rows3, p));
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
@@ -759,9 +988,11 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     if (e != nullptr && strcmp(e, "levelwise") == 0) return 2;
     if (e != nullptr && strcmp(e, "fused") == 0) return 1;
     if (e != nullptr && strcmp(e, "rows2") == 0) return 3;
+    if (e != nullptr && strcmp(e, "rows1") == 0) return 4;  // round 1's row kernel
     return 0;
   }();
   if (mode == 3) return launch_build_rows2(ctx, s, cells_dev);
+  if (mode == 0) return launch_build_rows3(ctx, s, cells_dev);
   if (mode == 1 && s->depth <= kFusedMaxDepth) return launch_build_fused(ctx, s, cells_dev);
   if (mode == 2) return launch_build_levelwise(ctx, s, cells_dev);
   return launch_build_rows(ctx, s, cells_dev);
