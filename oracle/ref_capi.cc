@@ -1,0 +1,401 @@
+// TEST INFRASTRUCTURE ONLY.  Flat C entry points over the REFERENCE'S OWN scan-matcher classes,
+// compiled unmodified from /root/reference by `make ref` (oracle/Makefile) into
+// oracle/_ref/libref.so.  The entry points carry the same names and argument lists as the
+// ones oracle_capi.cc puts over the restatement (csm_oracle.h), so tests/oracle_binding.py can
+// bind either library and tests/test_oracle_vs_ref.py can hold one to the other bit for bit.
+//
+// What is the reference here and what is not: every line of the matchers, the grids, the
+// value tables and the point-cloud transform is the reference's; Eigen, glog, abseil, protobuf,
+// Lua, Ceres and boost are absent from this image and are replaced by the stand-in headers
+// under oracle/ref_shim/ (see Eigen/Core there for the arithmetic they carry).  This file adds
+// the C surface and the link stubs for LuaParameterDictionary's out-of-line members (the
+// Create*Options functions reference them; nothing calls them here).
+#include <atomic>
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+#include <future>
+#include <map>
+#include <memory>
+#include <thread>
+#include <vector>
+
+#include "cartographer/common/lua_parameter_dictionary.h"
+#include "cartographer/mapping/2d/probability_grid.h"
+#include "cartographer/mapping/internal/2d/scan_matching/correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
+#include "cartographer/mapping/internal/2d/tsdf_2d.h"
+#include "cartographer/mapping/probability_values.h"
+#include "cartographer/sensor/point_cloud.h"
+#include "cartographer/transform/transform.h"
+
+namespace carto = ::cartographer;
+using carto::mapping::scan_matching::DiscreteScan2D;
+using carto::mapping::scan_matching::FastCorrelativeScanMatcher2D;
+using carto::mapping::scan_matching::PrecomputationGrid2D;
+using carto::mapping::scan_matching::PrecomputationGridStack2D;
+using carto::mapping::scan_matching::RealTimeCorrelativeScanMatcher2D;
+using carto::mapping::scan_matching::SearchParameters;
+
+// ---- link stubs ---------------------------------------------------------------------------
+namespace cartographer {
+namespace common {
+[[noreturn]] static void NoLua() {
+  LOG(FATAL) << "LuaParameterDictionary is not available in oracle/_ref";
+  std::abort();
+}
+std::string LuaParameterDictionary::GetString(const std::string&) { NoLua(); }
+double LuaParameterDictionary::GetDouble(const std::string&) { NoLua(); }
+int LuaParameterDictionary::GetInt(const std::string&) { NoLua(); }
+bool LuaParameterDictionary::GetBool(const std::string&) { NoLua(); }
+int LuaParameterDictionary::GetNonNegativeInt(const std::string&) { NoLua(); }
+}  // namespace common
+}  // namespace cartographer
+
+namespace {
+
+struct GridHolder {
+  carto::mapping::ValueConversionTables tables;
+  std::unique_ptr<carto::mapping::Grid2D> grid;
+};
+
+struct MatcherHolder {
+  carto::mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions2D options;
+  std::unique_ptr<FastCorrelativeScanMatcher2D> matcher;
+  std::unique_ptr<PrecomputationGridStack2D> stack;  // the same construction, for level read-back
+  int nx = 0, ny = 0;
+};
+
+carto::sensor::PointCloud ToCloud(const float* xyz, int n) {
+  carto::sensor::PointCloud cloud;
+  for (int i = 0; i < n; ++i) {
+    cloud.push_back({Eigen::Vector3f(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])});
+  }
+  return cloud;
+}
+
+carto::mapping::proto::Grid2D GridProto(const uint16_t* cells, int nx, int ny, double res, double max_x,
+                                        double max_y, float min_cost, float max_cost) {
+  carto::mapping::proto::Grid2D proto;
+  auto* limits = proto.mutable_limits();
+  limits->set_resolution(res);
+  limits->mutable_max()->set_x(max_x);
+  limits->mutable_max()->set_y(max_y);
+  limits->mutable_cell_limits()->set_num_x_cells(nx);
+  limits->mutable_cell_limits()->set_num_y_cells(ny);
+  proto.mutable_cells()->assign(cells, cells + static_cast<size_t>(nx) * ny);
+  proto.set_min_correspondence_cost(min_cost);
+  proto.set_max_correspondence_cost(max_cost);
+  return proto;
+}
+
+carto::mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions2D FastOptions(double linear_window,
+                                                                                    double angular_window,
+                                                                                    int depth) {
+  carto::mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions2D o;
+  o.set_linear_search_window(linear_window);
+  o.set_angular_search_window(angular_window);
+  o.set_branch_and_bound_depth(depth);
+  return o;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Same layout as oracle_capi.cc's.  The reference's Match() returns score and pose only, so the
+// winner's indices are reported as INT32_MIN and the counters as 0.
+struct oracle_result2d {
+  int32_t found;
+  int32_t scan_index, x_index_offset, y_index_offset;
+  float score;
+  int32_t num_scans;
+  double pose_x, pose_y, pose_theta;
+  uint64_t scored_top, scored_lower;
+};
+
+int oracle_is_reference() { return 1; }
+
+void oracle_correspondence_cost_table(float* out65536) {
+  carto::mapping::ValueConversionTables tables;
+  const std::vector<float>* table = tables.GetConversionTable(
+      carto::mapping::kMaxCorrespondenceCost, carto::mapping::kMinCorrespondenceCost,
+      carto::mapping::kMaxCorrespondenceCost);
+  std::memcpy(out65536, table->data(), 65536 * sizeof(float));
+}
+uint16_t oracle_probability_to_cost_value(float probability) {
+  return carto::mapping::CorrespondenceCostToValue(carto::mapping::ProbabilityToCorrespondenceCost(probability));
+}
+
+void* oracle_grid2d_create(const uint16_t* cells, int nx, int ny, double res, double max_x, double max_y) {
+  auto* h = new GridHolder;
+  carto::mapping::proto::Grid2D proto = GridProto(cells, nx, ny, res, max_x, max_y,
+                                                  carto::mapping::kMinCorrespondenceCost,
+                                                  carto::mapping::kMaxCorrespondenceCost);
+  proto.mutable_probability_grid_2d();
+  h->grid = std::make_unique<carto::mapping::ProbabilityGrid>(proto, &h->tables);
+  return h;
+}
+void oracle_grid2d_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+
+void* oracle_tsdf2d_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, int nx, int ny, double res,
+                           double max_x, double max_y, float truncation_distance, float max_weight) {
+  auto* h = new GridHolder;
+  carto::mapping::proto::Grid2D proto =
+      GridProto(tsd_cells, nx, ny, res, max_x, max_y, -truncation_distance, truncation_distance);
+  auto* tsdf = proto.mutable_tsdf_2d();
+  tsdf->set_truncation_distance(truncation_distance);
+  tsdf->set_max_weight(max_weight);
+  tsdf->mutable_weight_cells()->assign(weight_cells, weight_cells + static_cast<size_t>(nx) * ny);
+  h->grid = std::make_unique<carto::mapping::TSDF2D>(proto, &h->tables);
+  return h;
+}
+void oracle_tsdf2d_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+
+void* oracle_fcsm2d_create(void* grid, double linear_window, double angular_window, int depth) {
+  const carto::mapping::Grid2D& g = *static_cast<GridHolder*>(grid)->grid;
+  auto* h = new MatcherHolder;
+  h->options = FastOptions(linear_window, angular_window, depth);
+  h->matcher = std::make_unique<FastCorrelativeScanMatcher2D>(g, h->options);
+  h->stack = std::make_unique<PrecomputationGridStack2D>(g, h->options);
+  h->nx = g.limits().cell_limits().num_x_cells;
+  h->ny = g.limits().cell_limits().num_y_cells;
+  return h;
+}
+void* oracle_fcsm2d_create_tsdf(void* grid, double linear_window, double angular_window, int depth) {
+  return oracle_fcsm2d_create(grid, linear_window, angular_window, depth);
+}
+void oracle_fcsm2d_destroy(void* m) { delete static_cast<MatcherHolder*>(m); }
+
+// Level `level` read back through PrecomputationGrid2D::GetValue over its whole stored range
+// (offset (-width + 1, -width + 1), fast_correlative_scan_matcher_2d.cc:95-99).
+int oracle_fcsm2d_level(void* m, int level, uint8_t* out, int* wide_x, int* wide_y) {
+  const auto* h = static_cast<MatcherHolder*>(m);
+  if (level < 0 || level > h->stack->max_depth()) return -1;
+  const int width = 1 << level;
+  *wide_x = h->nx + width - 1;
+  *wide_y = h->ny + width - 1;
+  if (out) {
+    const PrecomputationGrid2D& pg = h->stack->Get(level);
+    for (int y = 0; y < *wide_y; ++y) {
+      for (int x = 0; x < *wide_x; ++x) {
+        out[static_cast<size_t>(y) * *wide_x + x] =
+            static_cast<uint8_t>(pg.GetValue(Eigen::Array2i(x - width + 1, y - width + 1)));
+      }
+    }
+  }
+  return 0;
+}
+
+int oracle_fcsm2d_match(void* m, int full_submap, double init_x, double init_y, double init_theta,
+                        const float* xyz, int n, float min_score, oracle_result2d* out) {
+  const auto* h = static_cast<MatcherHolder*>(m);
+  const carto::sensor::PointCloud cloud = ToCloud(xyz, n);
+  float score = 0.f;
+  carto::transform::Rigid2d pose = carto::transform::Rigid2d::Identity();
+  bool ok;
+  if (full_submap) {
+    ok = h->matcher->MatchFullSubmap(cloud, min_score, &score, &pose);
+  } else {
+    ok = h->matcher->Match(carto::transform::Rigid2d({init_x, init_y}, init_theta), cloud, min_score, &score,
+                           &pose);
+  }
+  std::memset(out, 0, sizeof(*out));
+  out->found = ok ? 1 : 0;
+  out->scan_index = out->x_index_offset = out->y_index_offset = INT32_MIN;
+  out->score = score;
+  out->pose_x = pose.translation().x();
+  out->pose_y = pose.translation().y();
+  out->pose_theta = pose.rotation().angle();
+  return 0;
+}
+
+int oracle_search_parameters2d(double linear_window, double angular_window, const float* xyz, int n, double res,
+                               int* num_angular_perturbations, double* step, int* num_scans,
+                               int* num_linear_perturbations) {
+  const SearchParameters sp(linear_window, angular_window, ToCloud(xyz, n), res);
+  *num_angular_perturbations = sp.num_angular_perturbations;
+  *step = sp.angular_perturbation_step_size;
+  *num_scans = sp.num_scans;
+  *num_linear_perturbations = sp.linear_bounds.empty() ? 0 : sp.linear_bounds[0].max_x;
+  return 0;
+}
+
+// The steps of MatchWithSearchParameters up to the discrete scans
+// (fast_correlative_scan_matcher_2d.cc:234-246), through the reference's own free functions.
+int oracle_discretize2d(double res, double max_x, double max_y, int nx, int ny, const float* xyz, int n,
+                        double init_x, double init_y, double init_theta, int num_linear_perturbations,
+                        int num_angular_perturbations, double step, int shrink, int32_t* out_xy,
+                        int32_t* out_bounds) {
+  const carto::mapping::MapLimits limits(res, Eigen::Vector2d(max_x, max_y), carto::mapping::CellLimits(nx, ny));
+  SearchParameters sp(num_linear_perturbations, num_angular_perturbations, step, res);
+  const Eigen::Rotation2Dd initial_rotation(init_theta);
+  const carto::sensor::PointCloud rotated = carto::sensor::TransformPointCloud(
+      ToCloud(xyz, n), carto::transform::Rigid3f::Rotation(Eigen::AngleAxisf(
+                           initial_rotation.cast<float>().angle(), Eigen::Vector3f::UnitZ())));
+  const std::vector<carto::sensor::PointCloud> scans =
+      carto::mapping::scan_matching::GenerateRotatedScans(rotated, sp);
+  const std::vector<DiscreteScan2D> d = carto::mapping::scan_matching::DiscretizeScans(
+      limits, scans, Eigen::Translation2f(init_x, init_y));
+  if (shrink) sp.ShrinkToFit(d, limits.cell_limits());
+  for (int s = 0; s < sp.num_scans; ++s) {
+    for (int i = 0; i < n; ++i) {
+      out_xy[(static_cast<size_t>(s) * n + i) * 2 + 0] = d[s][i].x();
+      out_xy[(static_cast<size_t>(s) * n + i) * 2 + 1] = d[s][i].y();
+    }
+    out_bounds[4 * s + 0] = sp.linear_bounds[s].min_x;
+    out_bounds[4 * s + 1] = sp.linear_bounds[s].max_x;
+    out_bounds[4 * s + 2] = sp.linear_bounds[s].min_y;
+    out_bounds[4 * s + 3] = sp.linear_bounds[s].max_y;
+  }
+  return 0;
+}
+
+static double RtMatch(void* grid, double linear_window, double angular_window,
+                      double translation_delta_cost_weight, double rotation_delta_cost_weight, double init_x,
+                      double init_y, double init_theta, const float* xyz, int n, oracle_result2d* out) {
+  carto::mapping::scan_matching::proto::RealTimeCorrelativeScanMatcherOptions o;
+  o.set_linear_search_window(linear_window);
+  o.set_angular_search_window(angular_window);
+  o.set_translation_delta_cost_weight(translation_delta_cost_weight);
+  o.set_rotation_delta_cost_weight(rotation_delta_cost_weight);
+  const RealTimeCorrelativeScanMatcher2D matcher(o);
+  carto::transform::Rigid2d pose = carto::transform::Rigid2d::Identity();
+  const double score = matcher.Match(carto::transform::Rigid2d({init_x, init_y}, init_theta), ToCloud(xyz, n),
+                                     *static_cast<GridHolder*>(grid)->grid, &pose);
+  std::memset(out, 0, sizeof(*out));
+  out->found = 1;
+  out->scan_index = out->x_index_offset = out->y_index_offset = INT32_MIN;
+  out->score = static_cast<float>(score);
+  out->pose_x = pose.translation().x();
+  out->pose_y = pose.translation().y();
+  out->pose_theta = pose.rotation().angle();
+  return score;
+}
+double oracle_rt_match2d(void* grid, double linear_window, double angular_window,
+                         double translation_delta_cost_weight, double rotation_delta_cost_weight, double init_x,
+                         double init_y, double init_theta, const float* xyz, int n, oracle_result2d* out) {
+  return RtMatch(grid, linear_window, angular_window, translation_delta_cost_weight, rotation_delta_cost_weight,
+                 init_x, init_y, init_theta, xyz, n, out);
+}
+double oracle_rt_match2d_tsdf(void* grid, double linear_window, double angular_window,
+                              double translation_delta_cost_weight, double rotation_delta_cost_weight,
+                              double init_x, double init_y, double init_theta, const float* xyz, int n,
+                              oracle_result2d* out) {
+  return RtMatch(grid, linear_window, angular_window, translation_delta_cost_weight, rotation_delta_cost_weight,
+                 init_x, init_y, init_theta, xyz, n, out);
+}
+
+void oracle_grid2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
+  const carto::mapping::MapLimits& l = static_cast<GridHolder*>(grid)->grid->limits();
+  *nx = l.cell_limits().num_x_cells;
+  *ny = l.cell_limits().num_y_cells;
+  *max_x = l.max().x();
+  *max_y = l.max().y();
+  *res = l.resolution();
+}
+void oracle_grid2d_cells(void* grid, uint16_t* out) {
+  const carto::mapping::proto::Grid2D proto = static_cast<GridHolder*>(grid)->grid->ToProto();
+  for (int i = 0; i < proto.cells_size(); ++i) out[i] = static_cast<uint16_t>(proto.cells(i));
+}
+void oracle_apply_odds_table(double probability, uint16_t* out32768) {
+  const std::vector<uint16_t> t = carto::mapping::ComputeLookupTableToApplyCorrespondenceCostOdds(
+      carto::mapping::Odds(static_cast<float>(probability)));
+  std::memcpy(out32768, t.data(), sizeof(uint16_t) * t.size());
+}
+
+// The constraint search of ConstraintBuilder2D on `num_threads` host threads with the reference's
+// matchers: one task per submap that constructs its FastCorrelativeScanMatcher2D (the stack
+// build, constraint_builder_2d.cc:165-186), one task per search that waits for it and runs
+// MatchFullSubmap / Match (:188-236), tasks taken in submission order.  The reference's own
+// thread pool and builder need abseil's synchronisation and Ceres, so this driver is ours; the
+// Ceres refinement that follows each found match in the reference (:238-248) is not run
+// (neither arm of the bench runs it).  found == 0 rows are the reference's null constraint
+// slots; pose = ComputeSubmapPose(submap)^-1 * pose_estimate (:250-258).  Returns wall seconds
+// from the first task until the last has finished.  out_stats4 is zeroed: the reference does
+// not count the candidates it scores.
+double oracle_constraint_batch(int num_threads, void* const* grids, const double* submap_pose, int num_submaps,
+                               int num_searches, const int32_t* search_submap, const int32_t* search_full,
+                               const double* search_rel_pose, const float* xyz, const int64_t* offsets,
+                               double sampling_ratio, double max_constraint_distance, double min_score,
+                               double global_min_score, double linear_window, double angular_window, int depth,
+                               oracle_result2d* out, double* out_stats4) {
+  (void)sampling_ratio;  // 1.0 in every caller: every search is kept
+  const auto options = FastOptions(linear_window, angular_window, depth);
+  std::vector<carto::sensor::PointCloud> clouds(num_searches);
+  for (int i = 0; i < num_searches; ++i) {
+    clouds[i] = ToCloud(xyz + 3 * offsets[i], static_cast<int>(offsets[i + 1] - offsets[i]));
+    std::memset(&out[i], 0, sizeof(out[i]));
+  }
+  struct Task {
+    int submap, search;  // search < 0: construct the submap's matcher
+  };
+  std::vector<Task> tasks;
+  std::vector<std::unique_ptr<FastCorrelativeScanMatcher2D>> matchers(num_submaps);
+  std::vector<std::promise<void>> built(num_submaps);
+  std::vector<std::shared_future<void>> ready(num_submaps);
+  std::vector<char> seen(num_submaps, 0);
+  for (int s = 0; s < num_submaps; ++s) ready[s] = built[s].get_future().share();
+  for (int i = 0; i < num_searches; ++i) {
+    const int s = search_submap[i];
+    if (!search_full[i]) {
+      const double tx = search_rel_pose[3 * i], ty = search_rel_pose[3 * i + 1];
+      if (Eigen::Vector2d(tx, ty).norm() > max_constraint_distance) continue;
+    }
+    if (!seen[s]) {
+      seen[s] = 1;
+      tasks.push_back({s, -1});
+    }
+    tasks.push_back({s, i});
+  }
+  std::atomic<size_t> next(0);
+  auto worker = [&] {
+    for (;;) {
+      const size_t k = next.fetch_add(1);
+      if (k >= tasks.size()) return;
+      const Task t = tasks[k];
+      const carto::mapping::Grid2D& grid = *static_cast<GridHolder*>(grids[t.submap])->grid;
+      if (t.search < 0) {
+        matchers[t.submap] = std::make_unique<FastCorrelativeScanMatcher2D>(grid, options);
+        built[t.submap].set_value();
+        continue;
+      }
+      ready[t.submap].wait();
+      const int i = t.search;
+      const carto::transform::Rigid2d submap_local_pose({submap_pose[3 * t.submap], submap_pose[3 * t.submap + 1]},
+                                                       submap_pose[3 * t.submap + 2]);
+      float score = 0.f;
+      carto::transform::Rigid2d pose_estimate = carto::transform::Rigid2d::Identity();
+      bool ok;
+      if (search_full[i]) {
+        ok = matchers[t.submap]->MatchFullSubmap(clouds[i], static_cast<float>(global_min_score), &score,
+                                                 &pose_estimate);
+      } else {
+        const carto::transform::Rigid2d initial_pose =
+            submap_local_pose * carto::transform::Rigid2d({search_rel_pose[3 * i], search_rel_pose[3 * i + 1]},
+                                                          search_rel_pose[3 * i + 2]);
+        ok = matchers[t.submap]->Match(initial_pose, clouds[i], static_cast<float>(min_score), &score,
+                                       &pose_estimate);
+      }
+      if (!ok) continue;
+      const carto::transform::Rigid2d constraint_transform = submap_local_pose.inverse() * pose_estimate;
+      oracle_result2d& r = out[i];
+      r.found = 1;
+      r.scan_index = r.x_index_offset = r.y_index_offset = INT32_MIN;
+      r.score = score;
+      r.pose_x = constraint_transform.translation().x();
+      r.pose_y = constraint_transform.translation().y();
+      r.pose_theta = constraint_transform.rotation().angle();
+    }
+  };
+  const auto t0 = std::chrono::steady_clock::now();
+  std::vector<std::thread> threads;
+  for (int i = 0; i < std::max(1, num_threads); ++i) threads.emplace_back(worker);
+  for (std::thread& t : threads) t.join();
+  const auto t1 = std::chrono::steady_clock::now();
+  if (out_stats4) std::memset(out_stats4, 0, 4 * sizeof(double));
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+}  // extern "C"

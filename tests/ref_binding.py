@@ -1,0 +1,206 @@
+"""ctypes binding of oracle/_ref/libref.so (TEST INFRASTRUCTURE ONLY): the reference's own 2D
+scan-matcher sources compiled unmodified by `make -C oracle ref` (see oracle/ref_capi.cc).
+
+The library only exists where it was built: in the container that has /root/reference, and
+on the GPU box as a prebuilt file that travelled with the snapshot.  available() says which.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from oracle_binding import OracleResult2D
+
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_ORACLE_DIR = os.path.join(_ROOT, "oracle")
+_LIB_PATH = os.path.join(_ORACLE_DIR, "_ref", "libref.so")
+_REFERENCE = "/root/reference"
+
+_lib = None
+
+
+def available():
+    return os.path.exists(_LIB_PATH) or os.path.isdir(os.path.join(_REFERENCE, "cartographer"))
+
+
+def build_ref():
+    """Builds oracle/_ref/libref.so from the sources under /root/reference, where they exist."""
+    if os.path.isdir(os.path.join(_REFERENCE, "cartographer")):
+        subprocess.check_call(["make", "-s", "-C", _ORACLE_DIR, "-j8", "ref"], stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    build_ref()
+    L = C.CDLL(_LIB_PATH)
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    assert L.oracle_is_reference() == 1
+    L.oracle_correspondence_cost_table.argtypes = [f32p]
+    L.oracle_probability_to_cost_value.argtypes = [C.c_float]
+    L.oracle_probability_to_cost_value.restype = C.c_uint16
+    L.oracle_grid2d_create.argtypes = [u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    L.oracle_grid2d_create.restype = C.c_void_p
+    L.oracle_grid2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_tsdf2d_create.argtypes = [u16p, u16p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                       C.c_float, C.c_float]
+    L.oracle_tsdf2d_create.restype = C.c_void_p
+    L.oracle_tsdf2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_fcsm2d_create.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    L.oracle_fcsm2d_create.restype = C.c_void_p
+    L.oracle_fcsm2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_fcsm2d_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.oracle_fcsm2d_match.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, f32p, C.c_int,
+                                      C.c_float, C.POINTER(OracleResult2D)]
+    L.oracle_search_parameters2d.argtypes = [C.c_double, C.c_double, f32p, C.c_int, C.c_double,
+                                             C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int),
+                                             C.POINTER(C.c_int)]
+    L.oracle_discretize2d.argtypes = [C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, f32p, C.c_int,
+                                      C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_double, C.c_int,
+                                      i32p, i32p]
+    L.oracle_rt_match2d.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                    C.c_double, C.c_double, f32p, C.c_int, C.POINTER(OracleResult2D)]
+    L.oracle_rt_match2d.restype = C.c_double
+    L.oracle_grid2d_cells.argtypes = [C.c_void_p, u16p]
+    L.oracle_grid2d_cells.restype = None
+    L.oracle_apply_odds_table.argtypes = [C.c_double, u16p]
+    L.oracle_apply_odds_table.restype = None
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    L.oracle_constraint_batch.argtypes = [
+        C.c_int, C.POINTER(C.c_void_p), f64p, C.c_int, C.c_int, i32p, i32p, f64p, f32p, i64p,
+        C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
+        C.POINTER(OracleResult2D), f64p]
+    L.oracle_constraint_batch.restype = C.c_double
+    _lib = L
+    return L
+
+
+class RefGrid:
+    """cartographer::mapping::ProbabilityGrid holding the given uint16 cells."""
+
+    def __init__(self, cells, res, max_x, max_y):
+        cells = np.ascontiguousarray(cells, dtype=np.uint16)
+        self.ny, self.nx = cells.shape
+        self.h = lib().oracle_grid2d_create(cells, self.nx, self.ny, res, max_x, max_y)
+
+    def cells(self):
+        out = np.empty((self.ny, self.nx), dtype=np.uint16)
+        lib().oracle_grid2d_cells(self.h, out)
+        return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_grid2d_destroy(self.h)
+            self.h = None
+
+
+class RefTsdf:
+    """cartographer::mapping::TSDF2D holding the given tsd / weight cells."""
+
+    def __init__(self, tsd_cells, weight_cells, res, max_x, max_y, truncation_distance, max_weight):
+        tsd_cells = np.ascontiguousarray(tsd_cells, dtype=np.uint16)
+        weight_cells = np.ascontiguousarray(weight_cells, dtype=np.uint16)
+        self.ny, self.nx = tsd_cells.shape
+        self.h = lib().oracle_tsdf2d_create(tsd_cells, weight_cells, self.nx, self.ny, res, max_x, max_y,
+                                            truncation_distance, max_weight)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_tsdf2d_destroy(self.h)
+            self.h = None
+
+
+class RefFCSM2D:
+    """cartographer::mapping::scan_matching::FastCorrelativeScanMatcher2D on a RefGrid / RefTsdf."""
+
+    def __init__(self, grid, linear_window, angular_window, depth):
+        self.grid = grid
+        self.h = lib().oracle_fcsm2d_create(grid.h, linear_window, angular_window, depth)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_fcsm2d_destroy(self.h)
+            self.h = None
+
+    def level(self, i):
+        wx, wy = C.c_int(), C.c_int()
+        assert lib().oracle_fcsm2d_level(self.h, i, None, C.byref(wx), C.byref(wy)) == 0
+        out = np.empty((wy.value, wx.value), dtype=np.uint8)
+        lib().oracle_fcsm2d_level(self.h, i, out.ctypes.data_as(C.c_void_p), C.byref(wx), C.byref(wy))
+        return out
+
+    def match(self, pts, min_score, initial=None):
+        pts = np.ascontiguousarray(pts, dtype=np.float32)
+        r = OracleResult2D()
+        full = initial is None
+        ix, iy, it = (0.0, 0.0, 0.0) if full else initial
+        lib().oracle_fcsm2d_match(self.h, 1 if full else 0, ix, iy, it, pts, len(pts), C.c_float(min_score),
+                                  C.byref(r))
+        return r
+
+
+def search_parameters(linear_window, angular_window, pts, res):
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    nap, step, ns, nlin = C.c_int(), C.c_double(), C.c_int(), C.c_int()
+    lib().oracle_search_parameters2d(linear_window, angular_window, pts, len(pts), res, C.byref(nap),
+                                     C.byref(step), C.byref(ns), C.byref(nlin))
+    return nap.value, step.value, ns.value, nlin.value
+
+
+def discretize(res, max_x, max_y, nx, ny, pts, init, nlin, nap, step, shrink=True):
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    s = 2 * nap + 1
+    xy = np.empty((s, len(pts), 2), dtype=np.int32)
+    bounds = np.empty((s, 4), dtype=np.int32)
+    lib().oracle_discretize2d(res, max_x, max_y, nx, ny, pts, len(pts), init[0], init[1], init[2], nlin, nap,
+                              step, 1 if shrink else 0, xy, bounds)
+    return xy, bounds
+
+
+def rt_match(grid, opts, init, pts):
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    r = OracleResult2D()
+    lib().oracle_rt_match2d(grid.h, opts["linear_search_window"], opts["angular_search_window"],
+                            opts["translation_delta_cost_weight"], opts["rotation_delta_cost_weight"],
+                            init[0], init[1], init[2], pts, len(pts), C.byref(r))
+    return r
+
+
+def correspondence_cost_table():
+    t = np.empty(65536, dtype=np.float32)
+    lib().oracle_correspondence_cost_table(t)
+    return t
+
+
+def apply_odds_table(probability):
+    t = np.empty(32768, dtype=np.uint16)
+    lib().oracle_apply_odds_table(probability, t)
+    return t
+
+
+def constraint_batch(num_threads, grids, submap_poses, search_submap, search_full, rel_poses, clouds,
+                     sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55, global_min_score=0.6,
+                     linear_window=7.0, angular_window=np.deg2rad(30.0), depth=7):
+    """The constraint searches of ConstraintBuilder2D on the reference's own matchers, thread-pooled
+    (same arguments and return as oracle_binding.constraint_batch; stats are zeros)."""
+    n = len(clouds)
+    handles = (C.c_void_p * len(grids))(*[g.h for g in grids])
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, c in enumerate(clouds):
+        offsets[i + 1] = offsets[i] + len(c)
+    xyz = np.ascontiguousarray(np.concatenate(clouds, axis=0), dtype=np.float32) if n else \
+        np.zeros((0, 3), np.float32)
+    out = (OracleResult2D * n)()
+    stats = np.zeros(4, dtype=np.float64)
+    secs = lib().oracle_constraint_batch(
+        num_threads, handles, np.ascontiguousarray(submap_poses, dtype=np.float64).reshape(-1), len(grids), n,
+        np.ascontiguousarray(search_submap, dtype=np.int32), np.ascontiguousarray(search_full, dtype=np.int32),
+        np.ascontiguousarray(rel_poses, dtype=np.float64).reshape(-1), xyz, offsets, sampling_ratio,
+        max_constraint_distance, min_score, global_min_score, linear_window, angular_window, depth, out, stats)
+    return secs, out, stats
