@@ -22,6 +22,7 @@
 
 #include "cartographer/common/lua_parameter_dictionary.h"
 #include "cartographer/mapping/2d/probability_grid.h"
+#include "cartographer/mapping/2d/probability_grid_range_data_inserter_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
@@ -50,6 +51,7 @@ double LuaParameterDictionary::GetDouble(const std::string&) { NoLua(); }
 int LuaParameterDictionary::GetInt(const std::string&) { NoLua(); }
 bool LuaParameterDictionary::GetBool(const std::string&) { NoLua(); }
 int LuaParameterDictionary::GetNonNegativeInt(const std::string&) { NoLua(); }
+bool LuaParameterDictionary::HasKey(const std::string&) const { NoLua(); }
 }  // namespace common
 }  // namespace cartographer
 
@@ -287,6 +289,20 @@ double oracle_rt_match2d_tsdf(void* grid, double linear_window, double angular_w
                  init_x, init_y, init_theta, xyz, n, out);
 }
 
+// ProbabilityGridRangeDataInserter2D::Insert on the grid handle (GrowLimits included).
+void oracle_grid2d_insert(void* grid, double hit_probability, double miss_probability, int insert_free_space,
+                          const float* origin_xy, const float* returns_xyz, int num_returns,
+                          const float* misses_xyz, int num_misses) {
+  carto::mapping::proto::ProbabilityGridRangeDataInserterOptions2D o;
+  o.set_hit_probability(hit_probability);
+  o.set_miss_probability(miss_probability);
+  o.set_insert_free_space(insert_free_space != 0);
+  carto::sensor::RangeData rd;
+  rd.origin = Eigen::Vector3f(origin_xy[0], origin_xy[1], 0.f);
+  rd.returns = ToCloud(returns_xyz, num_returns);
+  rd.misses = ToCloud(misses_xyz, num_misses);
+  carto::mapping::ProbabilityGridRangeDataInserter2D(o).Insert(rd, static_cast<GridHolder*>(grid)->grid.get());
+}
 void oracle_grid2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
   const carto::mapping::MapLimits& l = static_cast<GridHolder*>(grid)->grid->limits();
   *nx = l.cell_limits().num_x_cells;

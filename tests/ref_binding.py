@@ -66,6 +66,12 @@ def lib():
     L.oracle_rt_match2d.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
                                     C.c_double, C.c_double, f32p, C.c_int, C.POINTER(OracleResult2D)]
     L.oracle_rt_match2d.restype = C.c_double
+    L.oracle_grid2d_insert.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int, f32p, f32p, C.c_int, f32p,
+                                       C.c_int]
+    L.oracle_grid2d_insert.restype = None
+    L.oracle_grid2d_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.oracle_grid2d_info.restype = None
     L.oracle_grid2d_cells.argtypes = [C.c_void_p, u16p]
     L.oracle_grid2d_cells.restype = None
     L.oracle_apply_odds_table.argtypes = [C.c_double, u16p]
@@ -93,6 +99,21 @@ class RefGrid:
         out = np.empty((self.ny, self.nx), dtype=np.uint16)
         lib().oracle_grid2d_cells(self.h, out)
         return out
+
+    def insert(self, origin, returns, misses=(), hit_probability=0.55, miss_probability=0.49,
+               insert_free_space=True):
+        """ProbabilityGridRangeDataInserter2D::Insert (the grid may grow); returns (cells, max_x, max_y)."""
+        def xyz(points):
+            a = np.asarray(points, dtype=np.float32).reshape(-1, 3) if len(points) else np.zeros((0, 3), np.float32)
+            return np.ascontiguousarray(a)
+        r, m = xyz(returns), xyz(misses)
+        lib().oracle_grid2d_insert(self.h, hit_probability, miss_probability, 1 if insert_free_space else 0,
+                                   np.asarray(origin, np.float32)[:2].copy(), r, len(r), m, len(m))
+        nx, ny = C.c_int(), C.c_int()
+        mx, my, res = C.c_double(), C.c_double(), C.c_double()
+        lib().oracle_grid2d_info(self.h, C.byref(nx), C.byref(ny), C.byref(mx), C.byref(my), C.byref(res))
+        self.nx, self.ny = nx.value, ny.value
+        return self.cells(), mx.value, my.value
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -179,3 +179,23 @@ def test_reference_reproduces_fullsize_golden():
         if r.found:
             assert gu.score_bits(r.score) == want["score_bits"]
             assert [r.pose_x, r.pose_y, r.pose_theta] == want["pose"]
+
+
+def test_range_data_inserter_of_the_oracle_equals_the_reference():
+    """ProbabilityGridRangeDataInserter2D: three successive scans into a small grid
+    that has to grow, hits and misses, free space on and off; cells and limits after every insert."""
+    rng = np.random.default_rng(5)
+    for free_space in (True, False):
+        og = ob.OracleGrid(np.zeros((20, 24), np.uint16), 0.05, 0.6, 0.5)
+        rg = rb.RefGrid(np.zeros((20, 24), np.uint16), 0.05, 0.6, 0.5)
+        for k in range(3):
+            origin = rng.uniform(-0.5, 0.5, 2).astype(np.float32)
+            ang = rng.uniform(-np.pi, np.pi, 120)
+            rad = rng.uniform(0.3, 6.0, 120)
+            pts = np.stack([origin[0] + rad * np.cos(ang), origin[1] + rad * np.sin(ang), np.zeros(120)], 1)
+            returns, misses = pts[:100].astype(np.float32), pts[100:].astype(np.float32)
+            ob.grid_insert(og, origin, returns, misses, 0.55 + 0.05 * k, 0.49 - 0.03 * k, free_space)
+            cells, max_x, max_y = rg.insert(origin, returns, misses, 0.55 + 0.05 * k, 0.49 - 0.03 * k, free_space)
+            assert (og.nx, og.ny, og.max_x, og.max_y) == (rg.nx, rg.ny, max_x, max_y)
+            assert og.cells.tobytes() == cells.tobytes()
+        assert (og.cells > 0).sum() > (1000 if free_space else 250)
