@@ -254,7 +254,7 @@ def run_reference(args):
         return
     threads = os.cpu_count() or 1
     # the sample touches few submaps: generate only those
-    n = args.cpu_searches or max(8, 2 * threads)
+    n = args.cpu_searches or max(8, 4 * threads)
     job = Job(args)
     idx = cpu_sample(job, n)
     times, total_scored = [], 0.0
