@@ -129,6 +129,39 @@ def test_tie_cases_follow_reference_order(csm, gpu_ctx):
     _compare(om.match(pts, 0.3), r_g[0])
 
 
+def test_ordered_walk_and_path_keys_agree(csm, gpu_ctx, monkeypatch):
+    """The two implementations of the reference's tie order — path keys carried through the sweep
+    (default) and round 1's ordered depth-first walk (CSM_PHASE2=dfs, read when a context is
+    created) — return the same winners on tie-heavy and ordinary searches."""
+    monkeypatch.setenv("CSM_PHASE2", "dfs")
+    dfs_ctx = csm.Context(0)
+    monkeypatch.delenv("CSM_PHASE2")
+    try:
+        cases = []
+        cells = np.zeros((110, 100), dtype=np.uint16)
+        cases.append((cells, 1.0, 2.0, 3.0, np.array([[0.1, 0.2, 0.3]], dtype=np.float32), 0.0, 5))
+        cells = np.zeros((200, 200), dtype=np.uint16)
+        wall = synth.probability_to_value(np.float32(0.8))
+        cells[60:62, :] = wall
+        cells[140:142, :] = wall
+        ys = np.linspace(-3, 3, 40, dtype=np.float32)
+        pts = np.concatenate([np.stack([np.full(40, 2.0, np.float32), ys, np.zeros(40, np.float32)], 1),
+                              np.stack([np.full(40, -2.0, np.float32), ys, np.zeros(40, np.float32)], 1)])
+        cases.append((cells, 0.05, 5.0, 5.0, pts, 0.3, 6))
+        w = synth.World(300, 300, seed=31)
+        for k in range(3):
+            cases.append((w.cells, w.res, w.max_x, w.max_y, synth.make_scan(w, 60 + k, max_range=8.0)[1], 0.4, 6))
+        for cells, res, max_x, max_y, pts, min_score, depth in cases:
+            g = csm.Grid(cells, res, max_x, max_y)
+            a = csm.match_batch(gpu_ctx, [csm.Matcher(gpu_ctx, g, 7.0, np.deg2rad(30.0), depth)], [pts], [min_score])[0]
+            b = csm.match_batch(dfs_ctx, [csm.Matcher(dfs_ctx, g, 7.0, np.deg2rad(30.0), depth)], [pts], [min_score])[0]
+            assert (a.found, a.scan_index, a.x_index_offset, a.y_index_offset) == \
+                   (b.found, b.scan_index, b.x_index_offset, b.y_index_offset)
+            assert np.float32(a.score).tobytes() == np.float32(b.score).tobytes()
+    finally:
+        dfs_ctx.close()
+
+
 def test_empty_cloud_is_not_found(csm, gpu_ctx):
     w = synth.World(100, 100, seed=3)
     g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
