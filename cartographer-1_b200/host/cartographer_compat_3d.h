@@ -127,10 +127,12 @@ inline Rigid3f CastToFloat(const Rigid3d& t) {
                           static_cast<float>(t.translation().z())),
                  CastToFloat(t.rotation()));
 }
-// transform.h:57-61 with T = float
+// transform.h:41-47 with T = float.  The reference's unqualified atan2(float, float) resolves to the
+// C library's double atan2 (its translation units include <cmath>, not <math.h>), so the yaw is
+// computed in double and narrowed; atan2f would differ in the last bit for ~16 % of inputs.
 inline float GetYaw(const Quaternionf& q) {
   const Vector3f d = q * Vector3f(1.f, 0.f, 0.f);
-  return std::atan2(d.y(), d.x());
+  return static_cast<float>(std::atan2(static_cast<double>(d.y()), static_cast<double>(d.x())));
 }
 // transform.h:94-108 with T = float; the literals 2. and 1e-8 are doubles.
 inline Quaternionf AngleAxisVectorToRotationQuaternion(const Vector3f& a) {

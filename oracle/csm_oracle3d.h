@@ -88,10 +88,16 @@ inline Rigid3f Mul(const Rigid3f& l, const Rigid3f& r) {
   return o;
 }
 inline Vec3f Apply(const Rigid3f& a, const Vec3f& p) { return Add(QuatRotate4(a.q, p), a.t); }
-// transform.h:57-61
+// transform.h:41-47 with T = float.  The reference writes an UNQUALIFIED atan2(direction.y(),
+// direction.x()): from namespace cartographer::transform, with <cmath> but not <math.h> in the
+// translation unit, that resolves to the C library's ::atan2(double, double), so the yaw is
+// computed in double and narrowed (it differs from atan2f in the last bit for ~16 % of inputs).
+// This is what the reference's own sources do when compiled here (oracle/_ref; see
+// tests/test_oracle_vs_ref3d.py); a build whose headers drag in libstdc++'s <math.h> wrapper would
+// pick the float overload instead.
 inline float GetYaw(const Quat4f& q) {
   const Vec3f d = QuatRotate4(q, Vec3f{1.f, 0.f, 0.f});
-  return std::atan2(d.y, d.x);
+  return static_cast<float>(std::atan2(static_cast<double>(d.y), static_cast<double>(d.x)));
 }
 // transform.h:94-108 with T = float (the 2. literals promote to double)
 inline Quat4f AngleAxisVectorToRotationQuaternion(const Vec3f& aa) {

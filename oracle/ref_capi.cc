@@ -170,6 +170,17 @@ void* oracle_fcsm2d_create_tsdf(void* grid, double linear_window, double angular
 }
 void oracle_fcsm2d_destroy(void* m) { delete static_cast<MatcherHolder*>(m); }
 
+// Wall seconds of ONE PrecomputationGridStack2D construction (fast_correlative_scan_matcher_2d.cc:
+// 171-186), for the C4 CPU baseline.
+double oracle_stack2d_build_seconds(void* grid, int depth) {
+  const carto::mapping::Grid2D& g = *static_cast<GridHolder*>(grid)->grid;
+  const auto options = FastOptions(7.0, 0.5, depth);
+  const auto t0 = std::chrono::steady_clock::now();
+  const PrecomputationGridStack2D stack(g, options);
+  const auto t1 = std::chrono::steady_clock::now();
+  return stack.max_depth() == depth - 1 ? std::chrono::duration<double>(t1 - t0).count() : -1.;
+}
+
 // Level `level` read back through PrecomputationGrid2D::GetValue over its whole stored range
 // (offset (-width + 1, -width + 1), fast_correlative_scan_matcher_2d.cc:95-99).
 int oracle_fcsm2d_level(void* m, int level, uint8_t* out, int* wide_x, int* wide_y) {

@@ -4,6 +4,7 @@
 #define ORACLE_REF_SHIM_GLOG_LOGGING_H_
 
 #include <cstdlib>
+#include <functional>
 #include <iostream>
 #include <map>
 #include <memory>

@@ -10,7 +10,7 @@ import subprocess
 
 import numpy as np
 
-from oracle_binding import OracleResult2D
+from oracle_binding import IDENTITY_POSE7, OracleResult2D, OracleResult3D
 
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _ORACLE_DIR = os.path.join(_ROOT, "oracle")
@@ -54,6 +54,8 @@ def lib():
     L.oracle_fcsm2d_create.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
     L.oracle_fcsm2d_create.restype = C.c_void_p
     L.oracle_fcsm2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_stack2d_build_seconds.argtypes = [C.c_void_p, C.c_int]
+    L.oracle_stack2d_build_seconds.restype = C.c_double
     L.oracle_fcsm2d_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.oracle_fcsm2d_match.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, f32p, C.c_int,
                                       C.c_float, C.POINTER(OracleResult2D)]
@@ -83,6 +85,21 @@ def lib():
         C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
         C.POINTER(OracleResult2D), f64p]
     L.oracle_constraint_batch.restype = C.c_double
+    L.oracle_grid3d_create.argtypes = [C.c_float, i32p, u16p, C.c_int]
+    L.oracle_grid3d_create.restype = C.c_void_p
+    L.oracle_grid3d_destroy.argtypes = [C.c_void_p]
+    L.oracle_grid3d_size.argtypes = [C.c_void_p]
+    L.oracle_grid3d_cells.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_fcsm3d_create.argtypes = [C.c_void_p, C.c_void_p, f32p, C.c_int, f64p]
+    L.oracle_fcsm3d_create.restype = C.c_void_p
+    L.oracle_fcsm3d_destroy.argtypes = [C.c_void_p]
+    L.oracle_fcsm3d_level.argtypes = [C.c_void_p, C.c_int, i32p, i32p, C.c_void_p]
+    L.oracle_fcsm3d_match.argtypes = [C.c_void_p, C.c_int, f32p, f32p, f32p, C.c_int, f32p, C.c_int, f32p, C.c_int,
+                                      f64p, C.c_float, C.POINTER(OracleResult3D)]
+    L.oracle_rt_match3d.restype = C.c_float
+    L.oracle_rt_match3d.argtypes = [C.c_void_p, f64p, f32p, f32p, C.c_int, f32p, C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int)]
+    L.oracle_rotational_match.argtypes = [f32p, f32p, C.c_int, C.c_float, f32p, C.c_int, f32p]
     _lib = L
     return L
 
@@ -166,6 +183,11 @@ class RefFCSM2D:
         return r
 
 
+def stack_build_seconds(grid, depth):
+    """Wall seconds of one PrecomputationGridStack2D construction on a RefGrid."""
+    return lib().oracle_stack2d_build_seconds(grid.h, depth)
+
+
 def search_parameters(linear_window, angular_window, pts, res):
     pts = np.ascontiguousarray(pts, dtype=np.float32)
     nap, step, ns, nlin = C.c_int(), C.c_double(), C.c_int(), C.c_int()
@@ -225,3 +247,87 @@ def constraint_batch(num_threads, grids, submap_poses, search_submap, search_ful
         np.ascontiguousarray(rel_poses, dtype=np.float64).reshape(-1), xyz, offsets, sampling_ratio,
         max_constraint_distance, min_score, global_min_score, linear_window, angular_window, depth, out, stats)
     return secs, out, stats
+
+
+# ---- 3D ---------------------------------------------------------------------------
+class RefGrid3D:
+    """cartographer::mapping::HybridGrid holding the given uint16 values."""
+
+    def __init__(self, resolution, xyz=None, values=None):
+        xyz = np.zeros((0, 3), np.int32) if xyz is None else np.ascontiguousarray(xyz, np.int32)
+        values = np.zeros(0, np.uint16) if values is None else np.ascontiguousarray(values, np.uint16)
+        self.resolution = float(np.float32(resolution))
+        self.h = lib().oracle_grid3d_create(resolution, xyz.reshape(-1), values, len(values))
+
+    def cells(self):
+        n = lib().oracle_grid3d_cells(self.h, None, None)
+        xyz = np.zeros((n, 3), np.int32)
+        values = np.zeros(n, np.uint16)
+        if n:
+            lib().oracle_grid3d_cells(self.h, xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
+        order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
+        return xyz[order], values[order]
+
+    @property
+    def grid_size(self):
+        return lib().oracle_grid3d_size(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_grid3d_destroy(self.h)
+            self.h = None
+
+
+class RefFCSM3D:
+    """cartographer::mapping::scan_matching::FastCorrelativeScanMatcher3D."""
+
+    def __init__(self, grid, low_grid, histogram, options):
+        self.grid, self.low_grid = grid, low_grid
+        self.options = np.ascontiguousarray(options, np.float64)
+        self.histogram = np.ascontiguousarray(histogram, np.float32)
+        self.h = lib().oracle_fcsm3d_create(grid.h, low_grid.h, self.histogram, len(self.histogram), self.options)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_fcsm3d_destroy(self.h)
+            self.h = None
+
+    def level(self, i):
+        lo, hi = np.zeros(3, np.int32), np.zeros(3, np.int32)
+        lib().oracle_fcsm3d_level(self.h, i, lo, hi, None)
+        shape = tuple(int(v) for v in (hi - lo + 1)[::-1])
+        out = np.zeros(shape, np.uint8)
+        lib().oracle_fcsm3d_level(self.h, i, lo, hi, out.ctypes.data_as(C.c_void_p))
+        return lo, out
+
+    def match(self, hi_pts, lo_pts, histogram, min_score, node_pose7=IDENTITY_POSE7, submap_pose7=IDENTITY_POSE7,
+              gravity=(1., 0., 0., 0.), full=False):
+        hi_pts = np.ascontiguousarray(hi_pts, np.float32)
+        lo_pts = np.ascontiguousarray(lo_pts, np.float32)
+        histogram = np.ascontiguousarray(histogram, np.float32)
+        r = OracleResult3D()
+        lib().oracle_fcsm3d_match(self.h, 1 if full else 0, np.ascontiguousarray(node_pose7, np.float32),
+                                  np.ascontiguousarray(submap_pose7, np.float32), hi_pts.reshape(-1), len(hi_pts),
+                                  lo_pts.reshape(-1), len(lo_pts), histogram, len(histogram),
+                                  np.ascontiguousarray(gravity, np.float64), min_score, C.byref(r))
+        return r
+
+
+def rotational_match(submap_hist, hist, initial_angle, angles):
+    submap_hist = np.ascontiguousarray(submap_hist, np.float32)
+    hist = np.ascontiguousarray(hist, np.float32)
+    angles = np.ascontiguousarray(angles, np.float32)
+    out = np.zeros(len(angles), np.float32)
+    lib().oracle_rotational_match(submap_hist, hist, len(hist), initial_angle, angles, len(angles), out)
+    return out
+
+
+def rt_match3d(grid, options4, initial_pose7, points):
+    """RealTimeCorrelativeScanMatcher3D::Match: (score, pose7 float32)."""
+    pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+    pose = np.zeros(7, np.float32)
+    best, num = C.c_int(), C.c_int()
+    score = lib().oracle_rt_match3d(grid.h, np.ascontiguousarray(options4, np.float64),
+                                    np.ascontiguousarray(initial_pose7, np.float32), pts.reshape(-1), len(pts), pose,
+                                    C.byref(best), C.byref(num))
+    return score, pose

@@ -34,9 +34,25 @@ def _event_ms(torch, stream, fn, flush=None):
     return out, e0.elapsed_time(e1)
 
 
+def _cpu_kind():
+    """"reference": oracle/_ref/libref.so (the reference's own sources, DESIGN.md section 4) exists;
+    "port": only the oracle restatement does."""
+    return "reference" if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref.so")) and \
+        os.environ.get("CSM_CPU_BASELINE") != "port" else "port"
+
+
+_CPU_TEXT = {"reference": "the reference's own sources (oracle/_ref)", "port": "oracle restatement"}
+
+
 def c1(pkg, ctx, torch):
-    import oracle_binding as ob
     import synth
+    kind = _cpu_kind()
+    if kind == "reference":
+        import ref_binding as ob
+        make_grid = ob.RefGrid
+    else:
+        import oracle_binding as ob
+        make_grid = ob.OracleGrid
     grid, depth, lin, ang = 400, 7, 7.0, float(np.deg2rad(30.0))
     n_sub, n_nodes = 8, 16
     worlds = [synth.World(grid, grid, seed=1000 + s) for s in range(n_sub)]
@@ -71,15 +87,17 @@ def c1(pkg, ctx, torch):
     idx = list(range(0, len(clouds), max(1, len(clouds) // (2 * cores))))[:2 * cores]
     used = sorted(set(target[i] for i in idx))
     remap = {s: k for k, s in enumerate(used)}
-    ogrids = [ob.OracleGrid(worlds[s].cells, worlds[s].res, worlds[s].max_x, worlds[s].max_y) for s in used]
+    ogrids = [make_grid(worlds[s].cells, worlds[s].res, worlds[s].max_x, worlds[s].max_y) for s in used]
     secs, out, _ = ob.constraint_batch(
         cores, ogrids, np.zeros((len(ogrids), 3)), [remap[target[i]] for i in idx], [1] * len(idx),
         np.zeros((len(idx), 3)), [clouds[i] for i in idx], sampling_ratio=1.0, global_min_score=0.6,
         min_score=0.6, linear_window=lin, angular_window=ang, depth=depth)
     for k, i in enumerate(idx):
         a, b = out[k], res[i]
-        assert a.found == b.found and (not a.found or (a.scan_index, a.x_index_offset, a.y_index_offset, a.score) == (
-            b.scan_index, b.x_index_offset, b.y_index_offset, b.score)), "C1 parity broke at %d" % i
+        assert a.found == b.found and (not a.found or a.score == b.score), "C1 parity broke at %d" % i
+        if a.found and kind == "port":  # the reference's Match() does not return the winner's indices
+            assert (a.scan_index, a.x_index_offset, a.y_index_offset) == (
+                b.scan_index, b.x_index_offset, b.y_index_offset), "C1 parity broke at %d" % i
     return {
         "workload": "C1 MatchFullSubmap 400x400 @5 cm, depth 7, min_score 0.6, %d searches on %d submaps"
                     % (len(clouds), n_sub),
@@ -89,14 +107,20 @@ def c1(pkg, ctx, torch):
         "found": int(sum(r.found for r in res)),
         "candidates_scored_per_search": float(np.mean([r.candidates_scored for r in res])),
         "bound": "the sweep's gather ceiling (see roofline) plus per-call latency at this size",
-        "cpu_baseline": {"value": len(idx) / secs, "unit": "searches/s", "cores": cores, "kind": "port",
-                         "sample": "%d of the searches, thread-pooled oracle restatement, %.1f s; results "
-                                   "identical to the GPU's" % (len(idx), secs)}}
+        "cpu_baseline": {"value": len(idx) / secs, "unit": "searches/s", "cores": cores, "kind": kind,
+                         "sample": "%d of the searches, thread-pooled, %s, %.1f s; found flags and scores "
+                                   "identical to the GPU's" % (len(idx), _CPU_TEXT[kind], secs)}}
 
 
 def c2(pkg, ctx, torch):
-    import oracle_binding as ob
     import synth
+    kind = _cpu_kind()
+    if kind == "reference":
+        import ref_binding as ob
+        make_grid = ob.RefGrid
+    else:
+        import oracle_binding as ob
+        make_grid = ob.OracleGrid
     w = synth.World(400, 400, seed=2000)
     g = pkg.Grid(w.cells, w.res, w.max_x, w.max_y)
     rng = np.random.default_rng(2)
@@ -122,7 +146,7 @@ def c2(pkg, ctx, torch):
         dt = (time.perf_counter() - t0) / reps
         out["batch_%d" % b] = {"scans_per_s": b / dt, "ms_per_call": 1e3 * dt}
     out["value"] = max(out["batch_%d" % b]["scans_per_s"] for b in (1, 64, 1024))
-    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    og = make_grid(w.cells, w.res, w.max_x, w.max_y)
     opts = {"linear_search_window": 0.1, "angular_search_window": float(np.deg2rad(20.0)),
             "translation_delta_cost_weight": 0.1, "rotation_delta_cost_weight": 0.1}
     n = 48
@@ -136,13 +160,16 @@ def c2(pkg, ctx, torch):
         cpu = list(ex.map(one, range(n)))
     secs = time.perf_counter() - t0
     for i, r in enumerate(cpu):
-        assert (r.scan_index, r.x_index_offset, r.y_index_offset) == \
-            (res[i].scan_index, res[i].x_index_offset, res[i].y_index_offset), "C2 parity broke at %d" % i
-        assert np.float32(r.score).tobytes() == np.float32(res[i].score).tobytes()
+        if kind == "port":  # the reference's Match() does not return the winner's indices
+            assert (r.scan_index, r.x_index_offset, r.y_index_offset) == \
+                (res[i].scan_index, res[i].x_index_offset, res[i].y_index_offset), "C2 parity broke at %d" % i
+        assert np.float32(r.score).tobytes() == np.float32(res[i].score).tobytes(), "C2 parity broke at %d" % i
+        assert (r.pose_x, r.pose_y, r.pose_theta) == (res[i].pose_x, res[i].pose_y, res[i].pose_theta), \
+            "C2 pose parity broke at %d" % i
     out["bound"] = "host-side preparation (penalty tables, packing) at large batches; k_rt_score itself is L1-latency bound"
-    out["cpu_baseline"] = {"value": n / secs, "unit": "scans/s", "cores": cores, "kind": "port",
-                           "sample": "%d scans, one oracle call per pool thread, %.2f s; winners and score bits "
-                                     "identical to the GPU's" % (n, secs)}
+    out["cpu_baseline"] = {"value": n / secs, "unit": "scans/s", "cores": cores, "kind": kind,
+                           "sample": "%d scans, one Match call per pool thread, %s, %.2f s; score bits and poses "
+                                     "identical to the GPU's" % (n, _CPU_TEXT[kind], secs)}
     return out
 
 
@@ -183,14 +210,22 @@ def c4(pkg, ctx, torch, hbm_peak):
                                "frac": alg / (cold * 1e6) / hbm_peak,
                                "note": "algorithmic bytes = 2*W*H + sum of level bytes (SURVEY.md 8(d)); the build "
                                        "also writes the matcher's quad-phase words"}
-            og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
-            t0 = time.perf_counter()
-            om = ob.OracleFCSM2D(og, 7.0, 0.5, depth)
-            secs = time.perf_counter() - t0
+            kind = _cpu_kind()
+            if kind == "reference":
+                import ref_binding as rb
+                rg = rb.RefGrid(w.cells, w.res, w.max_x, w.max_y)
+                secs = rb.stack_build_seconds(rg, depth)
+                om = rb.RefFCSM2D(rg, 7.0, 0.5, depth)
+            else:
+                og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+                t0 = time.perf_counter()
+                om = ob.OracleFCSM2D(og, 7.0, 0.5, depth)
+                secs = time.perf_counter() - t0
             assert np.array_equal(om.level(depth - 1), m.level(depth - 1)), "C4 parity broke"
-            out["cpu_baseline"] = {"value": alg / secs / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
-                                   "sample": "one 2000x2000 depth-7 stack, oracle restatement "
-                                             "(SlidingWindowMaximum), %.2f s; coarsest level identical" % secs}
+            out["cpu_baseline"] = {"value": alg / secs / 1e9, "unit": "GB/s", "cores": 1, "kind": kind,
+                                   "sample": "one 2000x2000 depth-7 PrecomputationGridStack2D, %s "
+                                             "(SlidingWindowMaximum), one thread, %.2f s; coarsest level "
+                                             "identical" % (_CPU_TEXT[kind], secs)}
     return out
 
 
@@ -242,10 +277,19 @@ def c5(pkg, ctx, torch):
         _, ms = _event_ms(torch, stream,
                           lambda: pkg.match3d_batch(ctx, [matcher] * n, objs, mins, inits, None, full), flush)
         ms_e2e += ms
-    om = ob.OracleFCSM3D(ob.OracleGrid3D(0.1, hi_xyz, hi_val), ob.OracleGrid3D(0.45, lo_xyz, lo_val), hist,
-                         np.array(fc.C5_OPT))
+    # CPU leg: the reference's own FastCorrelativeScanMatcher3D on its own HybridGrid where oracle/_ref
+    # was built (kind "reference"), else the oracle restatement, whose HybridGrid is a hash map (kind "port").
+    kind = "reference" if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref.so")) and \
+        os.environ.get("CSM_CPU_BASELINE") != "port" else "port"
+    if kind == "reference":
+        import ref_binding as rb
+        om = rb.RefFCSM3D(rb.RefGrid3D(0.1, hi_xyz, hi_val), rb.RefGrid3D(0.45, lo_xyz, lo_val), hist,
+                          np.array(fc.C5_OPT))
+    else:
+        om = ob.OracleFCSM3D(ob.OracleGrid3D(0.1, hi_xyz, hi_val), ob.OracleGrid3D(0.45, lo_xyz, lo_val), hist,
+                             np.array(fc.C5_OPT))
     cores = os.cpu_count() or 1
-    k = min(n_match, cores)
+    k = min(n_match, 2 * cores if kind == "reference" else cores)
 
     def one(i):
         hi, lo, h_, g, init, _ = nodes[i]
@@ -257,9 +301,13 @@ def c5(pkg, ctx, torch):
     secs = time.perf_counter() - t0
     for i, r in enumerate(cpu):
         g = res[i]
-        assert bool(r.found) == bool(g.found) and (not r.found or (
-            r.scan_index, tuple(r.offset), np.float32(r.score).tobytes()) == (
-            g.scan_index, tuple(g.offset), np.float32(g.score).tobytes())), "C5 parity broke at %d" % i
+        assert bool(r.found) == bool(g.found) and (not r.found or np.float32(r.score).tobytes() ==
+                                                   np.float32(g.score).tobytes()), "C5 parity broke at %d" % i
+        if r.found and kind == "port":  # the reference's Result does not carry the winner's indices
+            assert (r.scan_index, tuple(r.offset)) == (g.scan_index, tuple(g.offset)), "C5 parity broke at %d" % i
+        if r.found and kind == "reference":
+            assert np.array(list(r.pose), np.float32).tobytes() == np.array(list(g.pose), np.float32).tobytes(), \
+                "C5 pose parity broke at %d" % i
     scored = float(sum(r.candidates_scored for r in res))
     return {
         "workload": "C5 FastCorrelativeScanMatcher3D: 40x40x6 m room @0.1/0.45 m, %d Match + %d MatchFullSubmap "
@@ -269,10 +317,14 @@ def c5(pkg, ctx, torch):
         "found": int(sum(1 for r in res if r.found)),
         "candidate_scores_per_s": scored * steps / (ms_res * 1e-3),
         "bound": "L1/L2 sector throughput of the 8-child pack gather (k3_expand), profiles/r01_3d_summary.md",
-        "cpu_baseline": {"value": k / secs, "unit": "searches/s", "cores": cores, "kind": "port",
-                         "sample": "%d Match searches on a thread pool of the oracle restatement (its HybridGrid is a "
-                                   "hash map, slower per lookup than the reference's brick tree), %.1f s; results "
-                                   "identical to the GPU's" % (k, secs)}}
+        "cpu_baseline": {"value": k / secs, "unit": "searches/s", "cores": cores, "kind": kind,
+                         "sample": "%d Match searches on %d host threads, %s, %.1f s; found flags, scores%s identical "
+                                   "to the GPU's" % (k, cores,
+                                                     "the reference's own FastCorrelativeScanMatcher3D on its own "
+                                                     "HybridGrid (oracle/_ref)" if kind == "reference" else
+                                                     "the oracle restatement (its HybridGrid is a hash map, slower per "
+                                                     "lookup than the reference's brick tree)", secs,
+                                                     " and poses" if kind == "reference" else " and winners")}}
 
 
 def measure_all(pkg, ctx, torch, hbm_peak):
