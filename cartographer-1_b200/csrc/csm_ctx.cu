@@ -66,6 +66,7 @@ bool ctx_alive_on(const csm_ctx* ctx, int device) {
 int BlockPool::take(bool pin, size_t bytes, void** out, size_t* cap) {
   std::lock_guard<std::mutex> l(mu);
   std::vector<Block>& list = pin ? pinned : device;
+  size_t& held = pin ? pinned_bytes : device_bytes;
   int best = -1;
   for (size_t i = 0; i != list.size(); ++i)
     if (list[i].cap >= bytes && list[i].cap <= 4 * bytes + (1u << 20) &&
@@ -74,15 +75,23 @@ int BlockPool::take(bool pin, size_t bytes, void** out, size_t* cap) {
   if (best >= 0) {
     *out = list[best].p;
     *cap = list[best].cap;
+    held -= list[best].cap;
     list.erase(list.begin() + best);
     return CSM_OK;
   }
   const size_t want = bytes + bytes / 8 + 4096;
-  if (pin) {
-    CSM_CUDA(cudaHostAlloc(out, want, cudaHostAllocDefault));
-  } else {
-    CSM_CUDA(cudaMalloc(out, want));
+  cudaError_t e = pin ? cudaHostAlloc(out, want, cudaHostAllocDefault) : cudaMalloc(out, want);
+  if (e != cudaSuccess && !list.empty()) {
+    // Out of memory with blocks parked in the pool: release them and try once more.
+    cudaGetLastError();
+    for (Block& b : list) {
+      if (pin) cudaFreeHost(b.p); else cudaFree(b.p);
+    }
+    list.clear();
+    held = 0;
+    e = pin ? cudaHostAlloc(out, want, cudaHostAllocDefault) : cudaMalloc(out, want);
   }
+  CSM_CUDA(e);
   *cap = want;
   return CSM_OK;
 }
@@ -90,12 +99,16 @@ void BlockPool::give(bool pin, void* p, size_t cap) {
   if (!p) return;
   std::lock_guard<std::mutex> l(mu);
   std::vector<Block>& list = pin ? pinned : device;
+  size_t& held = pin ? pinned_bytes : device_bytes;
+  const size_t budget = pin ? pinned_budget : device_budget;
   list.push_back(Block{p, cap});
-  if (list.size() > kMaxBlocks) {  // drop the smallest
+  held += cap;
+  while (!list.empty() && (list.size() > kMaxBlocks || held > budget)) {  // drop the smallest
     size_t k = 0;
     for (size_t i = 1; i != list.size(); ++i)
       if (list[i].cap < list[k].cap) k = i;
     if (pin) cudaFreeHost(list[k].p); else cudaFree(list[k].p);
+    held -= list[k].cap;
     list.erase(list.begin() + k);
   }
 }
@@ -105,6 +118,7 @@ void BlockPool::release() {
   for (Block& b : pinned) cudaFreeHost(b.p);
   device.clear();
   pinned.clear();
+  device_bytes = pinned_bytes = 0;
 }
 
 }  // namespace csm
@@ -150,6 +164,8 @@ int csm_ctx_create(int device, csm_ctx** out) {
     c->sweep_tiles = sweep != nullptr && strcmp(sweep, "tiles") == 0;
     const char* ld = getenv("CSM_EXPAND_LOAD");  // experiment: "noalloc" = L1::no_allocate loads
     c->expand_noalloc = ld != nullptr && strcmp(ld, "noalloc") == 0;
+    if (const char* mb = getenv("CSM_POOL_DEVICE_MB")) c->pool.device_budget = static_cast<size_t>(atoll(mb)) << 20;
+    if (const char* mb = getenv("CSM_POOL_PINNED_MB")) c->pool.pinned_budget = static_cast<size_t>(atoll(mb)) << 20;
     const char* p2 = getenv("CSM_PHASE2");  // second opinion: "dfs" = the ordered walk of round 1
     c->phase2_dfs = p2 != nullptr && strcmp(p2, "dfs") == 0;
   }

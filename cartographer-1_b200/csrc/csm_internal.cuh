@@ -57,17 +57,24 @@ struct PinBuf {
   }
 };
 
-// Free lists of device / pinned blocks a context keeps between batches: a batch's arena
-// and staging buffer are a cudaMalloc + cudaHostAlloc + two frees otherwise (several
-// milliseconds per batch end to end).  Blocks are reused when at most 4x oversized; at
-// most kMaxBlocks are kept per kind.  take/give are internally locked: an object built on
-// a context may be destroyed from another thread than the one driving it.
+// Free lists of device / pinned blocks a context keeps between batches and stacks: a batch's
+// arena and staging buffer are a cudaMalloc + cudaHostAlloc + two frees otherwise (several
+// milliseconds per batch end to end), and a loop-closure job that rebuilds the stacks of 100
+// submaps per flush would free and re-allocate 3.6 GB every time (cudaFree synchronises the
+// device: 77 - 640 ms per 100 stacks were measured before the pool kept them).  Blocks are reused
+// when at most 4x oversized.  The pool keeps up to `device_budget` / `pinned_budget` bytes and
+// kMaxBlocks blocks per kind (CSM_POOL_DEVICE_MB / CSM_POOL_PINNED_MB override the budgets: 16 GiB
+// and 1 GiB by default, of 180 GB of HBM); beyond that the smallest block is released.  take/give
+// are internally locked: an object built on a context may be destroyed from another thread than
+// the one driving it.
 struct BlockPool {
   struct Block {
     void* p;
     size_t cap;
   };
-  static constexpr size_t kMaxBlocks = 6;
+  static constexpr size_t kMaxBlocks = 1024;
+  size_t device_budget = size_t(16) << 30, pinned_budget = size_t(1) << 30;
+  size_t device_bytes = 0, pinned_bytes = 0;
   std::vector<Block> device, pinned;
   std::mutex mu;
   int take(bool pin, size_t bytes, void** out, size_t* cap);
