@@ -60,6 +60,7 @@ ABI_SYMBOLS = [
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
     "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch", "csm_grid2d_create", "csm_grid2d_insert",
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
+    "csm_hgrid3d_create", "csm_hgrid3d_insert", "csm_hgrid3d_export", "csm_hgrid3d_box", "csm_hgrid3d_destroy",
     "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile", "csm_precomputation_grid2d",
     "csm_rotate_scans2d", "csm_discretize_points2d", "csm_rt_score_candidates2d",
     "csm_discretize2d_noalloc",
@@ -713,3 +714,48 @@ def rt_match3d_batch(ctx, resolution, xyz, values, options4, initial_poses7, clo
                                  np.ascontiguousarray(initial_poses7, np.float64).reshape(-1), pts.reshape(-1),
                                  offsets, scores, poses.reshape(-1), best, num)
     return scores, poses, best, num
+
+
+def grid3d_insert(ctx, resolution, xyz, values, origins, returns, hit_probability=0.55, miss_probability=0.49,
+                  num_free_space_voxels=2, resident=False):
+    """RangeDataInserter3D::Insert of every scan (origins[i], returns[i]) into the HybridGrid given by
+    its non-default voxels.  resident=False: the reference-signature call per scan; True: one
+    device-resident grid for all scans.  Returns (xyz [n, 3] int32, values [n] uint16, grid_size),
+    voxels sorted by (z, y, x)."""
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    L.csmh_grid3d_insert.argtypes = [C.c_void_p, C.c_float, i32p, u16p, C.c_int, f64p, C.c_int, f32p, f32p, i64p,
+                                     C.c_int]
+    L.csmh_grid3d_insert.restype = C.c_void_p
+    L.csmh_grid3d_result_size.argtypes = [C.c_void_p]
+    L.csmh_grid3d_result_grid_size.argtypes = [C.c_void_p]
+    L.csmh_grid3d_result_copy.argtypes = [C.c_void_p, i32p, u16p]
+    L.csmh_grid3d_result_copy.restype = None
+    L.csmh_grid3d_result_destroy.argtypes = [C.c_void_p]
+    L.csmh_grid3d_result_destroy.restype = None
+    xyz = np.ascontiguousarray(np.asarray(xyz, np.int32).reshape(-1, 3))
+    values = np.ascontiguousarray(values, np.uint16)
+    n = len(origins)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, r in enumerate(returns):
+        offsets[i + 1] = offsets[i] + len(r)
+    pts = np.ascontiguousarray(np.concatenate([np.asarray(r, np.float32).reshape(-1, 3) for r in returns], axis=0)
+                               if n else np.zeros((0, 3), np.float32), dtype=np.float32)
+    h = L.csmh_grid3d_insert(ctx.h, resolution, xyz.reshape(-1), values, len(values),
+                             np.array([hit_probability, miss_probability, num_free_space_voxels], np.float64), n,
+                             np.ascontiguousarray(origins, np.float32).reshape(-1), pts.reshape(-1), offsets,
+                             1 if resident else 0)
+    assert h
+    m = L.csmh_grid3d_result_size(h)
+    out_xyz = np.zeros((m, 3), np.int32)
+    out_val = np.zeros(m, np.uint16)
+    if m:
+        L.csmh_grid3d_result_copy(h, out_xyz.reshape(-1), out_val)
+    size = L.csmh_grid3d_result_grid_size(h)
+    L.csmh_grid3d_result_destroy(h)
+    order = np.lexsort((out_xyz[:, 0], out_xyz[:, 1], out_xyz[:, 2]))
+    return out_xyz[order], out_val[order], size

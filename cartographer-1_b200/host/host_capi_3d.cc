@@ -7,6 +7,7 @@
 #include <memory>
 #include <mutex>
 
+#include "cartographer/mapping/3d/range_data_inserter_3d.h"
 #include "cartographer/mapping/internal/3d/scan_matching/fast_correlative_scan_matcher_3d.h"
 #include "cartographer/mapping/internal/3d/scan_matching/real_time_correlative_scan_matcher_3d.h"
 #include "cartographer/mapping/internal/constraints/constraint_builder_3d.h"
@@ -415,5 +416,57 @@ int csmh_rt_match3d_resident(void* ctx, void* device_grid, const double* options
   }
   return num;
 }
+
+
+// RangeDataInserter3D.  scans: origins[3 * num], returns given by offsets (num + 1 entries, in
+// points) into returns_xyz.  options3 = {hit_probability, miss_probability, num_free_space_voxels}.
+// resident == 0: one reference-signature Insert(range_data, HybridGrid*) per scan (grid up and down
+// every call); resident != 0: one DeviceGrid, every scan inserted, exported once.  The grid's
+// non-default voxels come back through csmh_grid3d_result_* (the handle owns them).
+struct Grid3DResult {
+  std::vector<int32_t> xyz;
+  std::vector<uint16> values;
+  int grid_size = 0;
+};
+void* csmh_grid3d_insert(void* ctx, float resolution, const int32_t* xyz, const uint16_t* values, int n_voxels,
+                         const double* options3, int num, const float* origins, const float* returns_xyz,
+                         const int64_t* offsets, int resident) {
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n_voxels; ++i)
+    *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  mapping::proto::RangeDataInserterOptions3D o;
+  o.set_hit_probability(options3[0]);
+  o.set_miss_probability(options3[1]);
+  o.set_num_free_space_voxels(static_cast<int>(options3[2]));
+  const mapping::RangeDataInserter3D inserter(o, context);
+  std::vector<sensor::RangeData> scans(num);
+  for (int s = 0; s < num; ++s) {
+    scans[s].origin = sensor::Vector3f(origins[3 * s], origins[3 * s + 1], origins[3 * s + 2]);
+    for (int64_t i = offsets[s]; i < offsets[s + 1]; ++i)
+      scans[s].returns.push_back({sensor::Vector3f(returns_xyz[3 * i], returns_xyz[3 * i + 1], returns_xyz[3 * i + 2])});
+  }
+  Grid3DResult* out = new Grid3DResult;
+  if (resident) {
+    mapping::RangeDataInserter3D::DeviceGrid device_grid(context, grid);
+    std::vector<const sensor::RangeData*> list;
+    for (const sensor::RangeData& rd : scans) list.push_back(&rd);
+    inserter.Insert(list, &device_grid);
+    device_grid.Download(&grid);
+  } else {
+    for (const sensor::RangeData& rd : scans) inserter.Insert(rd, &grid);
+  }
+  grid.Export(&out->xyz, &out->values);
+  out->grid_size = grid.grid_size();
+  return out;
+}
+int csmh_grid3d_result_size(void* r) { return static_cast<int>(static_cast<Grid3DResult*>(r)->values.size()); }
+int csmh_grid3d_result_grid_size(void* r) { return static_cast<Grid3DResult*>(r)->grid_size; }
+void csmh_grid3d_result_copy(void* r, int32_t* xyz, uint16_t* values) {
+  const Grid3DResult* g = static_cast<Grid3DResult*>(r);
+  std::memcpy(xyz, g->xyz.data(), sizeof(int32_t) * g->xyz.size());
+  std::memcpy(values, g->values.data(), sizeof(uint16_t) * g->values.size());
+}
+void csmh_grid3d_result_destroy(void* r) { delete static_cast<Grid3DResult*>(r); }
 
 }  // extern "C"

@@ -434,6 +434,39 @@ typedef struct {
 
 int csm_rt_match3d_batch(csm_ctx* ctx, const csm_rt_job3d* jobs, int num_jobs, csm_rt_result3d* results);
 
+/* ---- RangeDataInserter3D::Insert on a device-resident HybridGrid (SURVEY 8(f) rank 3, 3D half)
+ * Replaces cartographer/mapping/3d/range_data_inserter_3d.cc:44-76 (InsertMissesIntoGrid) and
+ * :112-131 (Insert) with HybridGrid::GetCellIndex / ApplyLookupTable / FinishUpdate
+ * (mapping/3d/hybrid_grid.h:428-434,492-518).  A csm_hgrid3d keeps a live submap's uint16 voxels in
+ * HBM as a dense box [z][y][x] that grows when a range data reaches outside it (the reference's
+ * sparse grid has no box; its hard limit of +-8192 cells per axis is kept).  What the path
+ * observes -- the set of non-default voxels the reference's HybridGrid::Iterator visits, with their
+ * values -- is bit-identical after every insertion; csm_hgrid3d_export returns it (unordered) and
+ * is what csm_stack3d_build / csm_grid3d_build take.  The intensity grid of this fork
+ * (range_data_inserter_3d.cc:78-92) is not carried. */
+typedef struct csm_hgrid3d csm_hgrid3d;
+typedef struct {
+  float origin[3];                 /* range_data.origin                                   */
+  int32_t num_returns;
+  const float* returns_xyz;        /* num_returns x (x, y, z)                             */
+  const uint16_t* hit_table;       /* ComputeLookupTableToApplyOdds(Odds(p)),             */
+  const uint16_t* miss_table;      /* probability_values.cc:72-87, 32768 entries each     */
+  int32_t num_free_space_voxels;   /* RangeDataInserterOptions3D                          */
+  int32_t pad;
+} csm_range_data3d;
+
+/* A grid holding the given voxels (num_voxels may be 0: an empty grid). */
+int csm_hgrid3d_create(csm_ctx* ctx, float resolution, const int32_t* voxel_xyz, const uint16_t* voxel_values,
+                       int num_voxels, csm_hgrid3d** out);
+/* Inserts the scans one after the other (each is one reference Insert incl. FinishUpdate). */
+int csm_hgrid3d_insert(csm_ctx* ctx, csm_hgrid3d* grid, const csm_range_data3d* scans, int num_scans);
+/* Non-default voxels.  capacity == 0: count only.  *num_voxels is the total even if it exceeds
+ * capacity (then only `capacity` voxels were written). */
+int csm_hgrid3d_export(csm_ctx* ctx, const csm_hgrid3d* grid, int32_t* voxel_xyz, uint16_t* voxel_values,
+                       int capacity, int* num_voxels);
+int csm_hgrid3d_box(const csm_hgrid3d* grid, int32_t* lo3, int32_t* dims3);
+void csm_hgrid3d_destroy(csm_ctx* ctx, csm_hgrid3d* grid);
+
 /* ---- measurement aids (bench.py) ------------------------------------------------
  * csm_ctx_launch_count: kernels launched through `ctx` since it was created.
  * csm_measure_gather_rate: the L2 gather roofline G_L2 of the scoring loop

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "cartographer/mapping/3d/hybrid_grid.h"
+#include "cartographer/mapping/3d/range_data_inserter_3d.h"
 #include "cartographer/mapping/internal/3d/scan_matching/fast_correlative_scan_matcher_3d.h"
 #include "cartographer/mapping/internal/3d/scan_matching/precomputation_grid_3d.h"
 #include "cartographer/mapping/internal/3d/scan_matching/real_time_correlative_scan_matcher_3d.h"
@@ -101,6 +102,20 @@ int oracle_grid3d_cells(void* g, int32_t* xyz, uint16_t* values) {
     ++n;
   }
   return n;
+}
+
+// RangeDataInserter3D::Insert of one range data (no intensity grid).  The fork's debugging
+// printout (hgrid_info, range_data_inserter_3d.cc:26-43) goes to stdout as in the reference.
+void oracle_grid3d_insert(void* g, const float* origin3, const float* returns, int n, float hit_probability,
+                          float miss_probability, int num_free_space_voxels) {
+  carto::mapping::proto::RangeDataInserterOptions3D o;
+  o.set_hit_probability(hit_probability);
+  o.set_miss_probability(miss_probability);
+  o.set_num_free_space_voxels(num_free_space_voxels);
+  carto::sensor::RangeData rd;
+  rd.origin = Eigen::Vector3f(origin3[0], origin3[1], origin3[2]);
+  rd.returns = ToCloud3(returns, n);
+  carto::mapping::RangeDataInserter3D(o).Insert(rd, static_cast<HybridGrid*>(g), nullptr);
 }
 
 void* oracle_fcsm3d_create(void* grid, void* low_grid, const float* hist, int n_hist, const double* o7) {

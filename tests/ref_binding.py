@@ -90,6 +90,8 @@ def lib():
     L.oracle_grid3d_destroy.argtypes = [C.c_void_p]
     L.oracle_grid3d_size.argtypes = [C.c_void_p]
     L.oracle_grid3d_cells.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_grid3d_insert.argtypes = [C.c_void_p, f32p, f32p, C.c_int, C.c_float, C.c_float, C.c_int]
+    L.oracle_grid3d_insert.restype = None
     L.oracle_fcsm3d_create.argtypes = [C.c_void_p, C.c_void_p, f32p, C.c_int, f64p]
     L.oracle_fcsm3d_create.restype = C.c_void_p
     L.oracle_fcsm3d_destroy.argtypes = [C.c_void_p]
@@ -267,6 +269,11 @@ class RefGrid3D:
             lib().oracle_grid3d_cells(self.h, xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
         order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
         return xyz[order], values[order]
+
+    def insert(self, origin, returns, hit_probability=0.7, miss_probability=0.4, num_free_space_voxels=5):
+        returns = np.ascontiguousarray(returns, np.float32)
+        lib().oracle_grid3d_insert(self.h, np.ascontiguousarray(origin, np.float32), returns.reshape(-1),
+                                   len(returns), hit_probability, miss_probability, num_free_space_voxels)
 
     @property
     def grid_size(self):

@@ -122,3 +122,27 @@ def test_reference_reproduces_fullsize_c5_golden():
             assert gu.score_bits(r.low_resolution_score) == want["low_resolution_score_bits"]
             assert gu.score_bits(r.rotational_score) == want["rotational_score_bits"]
             assert [float(x) for x in r.pose] == want["pose"]
+
+
+def test_range_data_inserter3d_of_the_oracle_equals_the_reference():
+    """RangeDataInserter3D: scans into an empty grid and into a filled one that has
+    to grow, 0 / 2 / 5 free-space voxels; the non-default voxels, their values and grid_size()."""
+    import synth3d
+    w = synth3d.World3D(5, size_xy=8.0)
+    rng = np.random.default_rng(5)
+    for free in (0, 2, 5):
+        for start in ("empty", "filled"):
+            xyz, val = (None, None) if start == "empty" else w.voxels(0.2)
+            res = 0.1 if start == "empty" else 0.2
+            og, rg = ob.OracleGrid3D(res, xyz, val), rb.RefGrid3D(res, xyz, val)
+            for k in range(4):
+                o = np.array([rng.uniform(-2, 2), rng.uniform(-2, 2), rng.uniform(0.2, 1.5)], np.float32)
+                pts = w.points[rng.choice(len(w.points), 300, replace=False)].astype(np.float32)
+                if k == 3:
+                    pts = np.concatenate([pts, np.array([[30.0, -25.0, 2.0]], np.float32)])  # grows the grid
+                og.insert(o, pts, 0.6, 0.45, free)
+                rg.insert(o, pts, 0.6, 0.45, free)
+                (oxyz, oval), (rxyz, rval) = og.cells(), rg.cells()
+                assert oxyz.tobytes() == rxyz.tobytes() and oval.tobytes() == rval.tobytes()
+                assert og.grid_size == rg.grid_size
+            assert og.grid_size > 128 and len(oval) > 500
