@@ -759,3 +759,61 @@ def grid3d_insert(ctx, resolution, xyz, values, origins, returns, hit_probabilit
     L.csmh_grid3d_result_destroy(h)
     order = np.lexsort((out_xyz[:, 0], out_xyz[:, 1], out_xyz[:, 2]))
     return out_xyz[order], out_val[order], size
+
+
+class ProtoGrid:
+    """A grid handle made from a serialized proto::Grid2D message (io/grid_proto_reader.h): usable
+    wherever a Grid / TsdfGrid is (Matcher, rt_match_batch, ...)."""
+
+    def __init__(self, serialized):
+        L = host()
+        L.csmh_grid_from_proto.argtypes = [C.c_char_p, C.c_int64, C.POINTER(C.c_double)]
+        L.csmh_grid_from_proto.restype = C.c_void_p
+        info = (C.c_double * 6)()
+        self.h = L.csmh_grid_from_proto(serialized, len(serialized), info)
+        self.nx, self.ny = int(info[0]), int(info[1])
+        self.res, self.max_x, self.max_y = info[2], info[3], info[4]
+        self.is_tsdf = bool(info[5])
+
+    def cells(self):
+        u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+        host().csmh_grid_cells.argtypes = [C.c_void_p, u16p]
+        host().csmh_grid_cells.restype = None
+        out = np.empty((self.ny, self.nx), np.uint16)
+        host().csmh_grid_cells(self.h, out)
+        return out
+
+    def weight_cells(self):
+        u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+        host().csmh_grid_weight_cells.argtypes = [C.c_void_p, u16p]
+        host().csmh_grid_weight_cells.restype = None
+        out = np.empty((self.ny, self.nx), np.uint16)
+        host().csmh_grid_weight_cells(self.h, out)
+        return out
+
+    def quantization_table(self):
+        out = np.empty(65536, dtype=np.uint8)
+        host().csmh_quantization_table(self.h, out)
+        return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            host().csmh_grid_destroy(self.h)
+            self.h = None
+
+
+def hybrid_grid_from_proto(serialized):
+    """(resolution, grid_size, xyz [n, 3] int32 sorted by (z, y, x), values [n] uint16) of a serialized
+    proto::HybridGrid."""
+    L = host()
+    L.csmh_hybrid_grid_from_proto.argtypes = [C.c_char_p, C.c_int64, C.POINTER(C.c_float), C.POINTER(C.c_int),
+                                              C.c_void_p, C.c_void_p]
+    res, size = C.c_float(), C.c_int()
+    n = L.csmh_hybrid_grid_from_proto(serialized, len(serialized), C.byref(res), C.byref(size), None, None)
+    xyz = np.zeros((n, 3), np.int32)
+    values = np.zeros(n, np.uint16)
+    if n:
+        L.csmh_hybrid_grid_from_proto(serialized, len(serialized), C.byref(res), C.byref(size),
+                                      xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
+    order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
+    return res.value, size.value, xyz[order], values[order]

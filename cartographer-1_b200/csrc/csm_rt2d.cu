@@ -29,6 +29,7 @@ struct RtJobDev {
   const float* dec;
   const float* wdec;
   const double* penalty;
+  int compact_nap;  // >= 0: `penalty` is the compact table indexed by (|scan - nap|, |x|, |y|)
   int num_x, num_y, n, S, lin;
   long long pts_off, quat_off;
   float q0w, q0s, tx, ty;
@@ -130,7 +131,10 @@ k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
       score = wsum == 0.f ? 0.f : __fdiv_rn(sum, wsum);
     }
     const unsigned int cand = static_cast<unsigned int>(scan) * count + c;
-    score = __double2float_rn(__dmul_rn(static_cast<double>(score), j.penalty[cand]));
+    const double factor = j.compact_nap >= 0
+                              ? j.penalty[(abs(scan - j.compact_nap) * (j.lin + 1) + abs(x)) * (j.lin + 1) + abs(y)]
+                              : j.penalty[cand];
+    score = __double2float_rn(__dmul_rn(static_cast<double>(score), factor));
     const unsigned long long key =
         (static_cast<unsigned long long>(float_to_ordered(score)) << 32) | (0xFFFFFFFFu - cand);
     local = max(local, key);
@@ -157,8 +161,11 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   int max_scans = 0, max_n = 0;
   for (int i = 0; i < num_jobs; ++i) {
     const csm_rt_job2d& in = jobs[i];
-    CSM_REQUIRE(in.cells && in.cost_table && in.points_xyz && in.scan_quat && in.penalty,
+    CSM_REQUIRE(in.cells && in.cost_table && in.points_xyz && in.scan_quat && (in.penalty || in.penalty_table),
                 "rt job has a NULL array");
+    CSM_REQUIRE(in.penalty_table == nullptr ||
+                    (in.num_angular_perturbations >= 0 && in.num_scans == 2 * in.num_angular_perturbations + 1),
+                "compact penalty table needs num_scans == 2 * num_angular_perturbations + 1");
     CSM_REQUIRE(in.num_points >= 1 && in.num_scans >= 1 && in.num_x >= 1 && in.num_y >= 1 &&
                     in.linear_bound >= 0 && in.linear_bound <= 1024 && in.resolution > 0.,
                 "rt job sizes out of range");
@@ -204,7 +211,9 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     j.oob_tsd = in.out_of_bounds_tsd;
     n_pts += in.num_points;
     n_scans += in.num_scans;
-    n_pen += side * side * in.num_scans;
+    n_pen += in.penalty_table ? static_cast<size_t>(in.num_angular_perturbations + 1) * (in.linear_bound + 1) *
+                                    (in.linear_bound + 1)
+                              : side * side * in.num_scans;
     max_scans = std::max(max_scans, in.num_scans);
     max_n = std::max(max_n, in.num_points);
   }
@@ -253,10 +262,14 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     const csm_rt_job2d& in = jobs[i];
     RtJobDev& j = dev[i];
     const size_t side = 2 * static_cast<size_t>(in.linear_bound) + 1;
-    const size_t pen_n = side * side * in.num_scans;
+    const size_t pen_n = in.penalty_table ? static_cast<size_t>(in.num_angular_perturbations + 1) *
+                                                (in.linear_bound + 1) * (in.linear_bound + 1)
+                                          : side * side * in.num_scans;
     memcpy(pin + o_pts + sizeof(float) * 3 * j.pts_off, in.points_xyz, sizeof(float) * 3 * j.n);
     memcpy(pin + o_quat + sizeof(float) * 2 * j.quat_off, in.scan_quat, sizeof(float) * 2 * j.S);
-    memcpy(pin + o_pen + sizeof(double) * pen_at, in.penalty, sizeof(double) * pen_n);
+    memcpy(pin + o_pen + sizeof(double) * pen_at, in.penalty_table ? in.penalty_table : in.penalty,
+           sizeof(double) * pen_n);
+    j.compact_nap = in.penalty_table ? in.num_angular_perturbations : -1;
     j.penalty = reinterpret_cast<const double*>(base + o_pen) + pen_at;
     j.cells = reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
     j.cost_table = reinterpret_cast<const float*>(base + o_tab + table_at[in.cost_table]);

@@ -176,7 +176,6 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
     // triple with exactly the reference's operations and copied to the mirror images.
     {
       const int lin = sp.linear_bounds[0].max_x;
-      const int side = 2 * lin + 1;
       const int nap = sp.num_angular_perturbations;
       std::vector<double> reach(static_cast<size_t>(lin + 1) * (lin + 1));
       for (int ax = 0; ax <= lin; ++ax)
@@ -184,7 +183,9 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
           const Candidate2D c(nap, ax, ay, sp);
           reach[ax * (lin + 1) + ay] = std::hypot(c.x, c.y) * options_.translation_delta_cost_weight();
         }
-      std::vector<double> table(static_cast<size_t>(nap + 1) * reach.size());
+      // (|scan - nap|, |x|, |y|) -> factor; the device indexes it per candidate (csm_rt_job2d::penalty_table).
+      std::vector<double>& table = penalty[i];
+      table.resize(static_cast<size_t>(nap + 1) * reach.size());
       for (int a = 0; a <= nap; ++a) {
         const Candidate2D c(nap + a, 0, 0, sp);
         const double turn = std::abs(c.orientation) * options_.rotation_delta_cost_weight();
@@ -192,14 +193,6 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
           const double t = reach[k] + turn;
           table[a * reach.size() + k] = std::exp(-(t * t));
         }
-      }
-      penalty[i].resize(static_cast<size_t>(sp.num_scans) * side * side);
-      size_t at = 0;
-      for (int scan = 0; scan != sp.num_scans; ++scan) {
-        const double* row = table.data() + static_cast<size_t>(std::abs(scan - nap)) * reach.size();
-        for (int x = -lin; x <= lin; ++x)
-          for (int y = -lin; y <= lin; ++y)
-            penalty[i][at++] = row[std::abs(x) * (lin + 1) + std::abs(y)];
       }
     }
     csm_rt_job2d& job = jobs[i];
@@ -221,7 +214,9 @@ std::vector<RealTimeCorrelativeScanMatcher2D::Answer> RealTimeCorrelativeScanMat
     job.max_y = limits.max().y();
     job.resolution = limits.resolution();
     job.linear_bound = sp.linear_bounds[0].max_x;
-    job.penalty = penalty[i].data();
+    job.penalty = nullptr;
+    job.penalty_table = penalty[i].data();
+    job.num_angular_perturbations = sp.num_angular_perturbations;
     job.out_of_bounds_probability = kMinProbability;  // probability_grid.cc:78-82
     if (q.grid->GetGridType() == GridType::TSDF) {  // reference :38-59, :163-168
       const TSDF2D& tsdf = static_cast<const TSDF2D&>(*q.grid);

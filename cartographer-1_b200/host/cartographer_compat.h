@@ -375,6 +375,11 @@ class ProbabilityGrid : public Grid2D {
  public:
   ProbabilityGrid(const MapLimits& limits, ValueConversionTables* conversion_tables)
       : Grid2D(limits, kMinCorrespondenceCost, kMaxCorrespondenceCost, conversion_tables) {}
+  // What ProbabilityGrid(const proto::Grid2D&, ...) builds (probability_grid.cc:33-37): the
+  // correspondence-cost bounds come from the message (io/grid_proto_reader.h).
+  ProbabilityGrid(const MapLimits& limits, float min_correspondence_cost, float max_correspondence_cost,
+                  ValueConversionTables* conversion_tables)
+      : Grid2D(limits, min_correspondence_cost, max_correspondence_cost, conversion_tables) {}
   GridType GetGridType() const override { return GridType::PROBABILITY_GRID; }
   // probability_grid.cc:40-48: sets the probability of a cell that was unknown so far.
   void SetProbability(const Eigen::Array2i& cell_index, const float probability) {
@@ -436,6 +441,15 @@ class TSDF2D : public Grid2D {
   TSDF2D(const MapLimits& limits, float truncation_distance, float max_weight,
          ValueConversionTables* conversion_tables)
       : Grid2D(limits, -truncation_distance, truncation_distance, conversion_tables),
+        value_converter_(truncation_distance, max_weight, conversion_tables),
+        weight_cells_(static_cast<size_t>(limits.cell_limits().num_x_cells) *
+                          limits.cell_limits().num_y_cells,
+                      TSDValueConverter::getUnknownWeightValue()) {}
+  // What TSDF2D(const proto::Grid2D&, ...) builds (tsdf_2d.cc:35-47): bounds from the message,
+  // converter from its tsdf_2d field (io/grid_proto_reader.h).
+  TSDF2D(const MapLimits& limits, float min_correspondence_cost, float max_correspondence_cost,
+         float truncation_distance, float max_weight, ValueConversionTables* conversion_tables)
+      : Grid2D(limits, min_correspondence_cost, max_correspondence_cost, conversion_tables),
         value_converter_(truncation_distance, max_weight, conversion_tables),
         weight_cells_(static_cast<size_t>(limits.cell_limits().num_x_cells) *
                           limits.cell_limits().num_y_cells,

@@ -8,6 +8,7 @@
 #include <memory>
 #include <mutex>
 
+#include "cartographer/io/grid_proto_reader.h"
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/2d/probability_grid_range_data_inserter_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/ceres_scan_matcher_2d.h"
@@ -66,6 +67,42 @@ void* csmh_tsdf_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, 
   return h;
 }
 void csmh_grid_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+
+// Grid ingestion: a serialized proto::Grid2D message -> a grid handle (ProbabilityGrid or TSDF2D,
+// whichever the message holds) every matcher entry point takes.  info6 = {num_x, num_y,
+// resolution, max_x, max_y, is_tsdf}.
+void* csmh_grid_from_proto(const uint8_t* bytes, int64_t size, double* info6) {
+  GridHolder* h = new GridHolder;
+  h->grid = io::ReadGrid2DProto(bytes, static_cast<size_t>(size), &h->tables);
+  const mapping::MapLimits& l = h->grid->limits();
+  info6[0] = l.cell_limits().num_x_cells;
+  info6[1] = l.cell_limits().num_y_cells;
+  info6[2] = l.resolution();
+  info6[3] = l.max().x();
+  info6[4] = l.max().y();
+  info6[5] = h->grid->GetGridType() == mapping::GridType::TSDF ? 1. : 0.;
+  return h;
+}
+void csmh_grid_weight_cells(void* grid, uint16_t* out) {
+  const mapping::TSDF2D& t = static_cast<const mapping::TSDF2D&>(*static_cast<GridHolder*>(grid)->grid);
+  std::memcpy(out, t.weight_cells().data(), sizeof(uint16_t) * t.weight_cells().size());
+}
+// A serialized proto::HybridGrid -> its non-default voxels (xyz / values may be NULL to count);
+// *resolution and *grid_size are always filled.
+int csmh_hybrid_grid_from_proto(const uint8_t* bytes, int64_t size, float* resolution, int* grid_size,
+                                int32_t* xyz, uint16_t* values) {
+  const std::unique_ptr<mapping::HybridGrid> grid = io::ReadHybridGridProto(bytes, static_cast<size_t>(size));
+  *resolution = grid->resolution();
+  *grid_size = grid->grid_size();
+  std::vector<int32_t> cells;
+  std::vector<uint16_t> vals;
+  grid->Export(&cells, &vals);
+  if (xyz != nullptr) {
+    std::memcpy(xyz, cells.data(), sizeof(int32_t) * cells.size());
+    std::memcpy(values, vals.data(), sizeof(uint16_t) * vals.size());
+  }
+  return static_cast<int>(vals.size());
+}
 
 void csmh_quantization_table(void* g, uint8_t* out65536) {
   const std::vector<uint8_t> t =

@@ -228,6 +228,14 @@ typedef struct {
   const float* weight_table;       /* 65536 floats, value-to-weight                    */
   float max_correspondence_cost;   /* the truncation distance (tsdf_2d.cc:26)          */
   float out_of_bounds_tsd;         /* TSDValueConverter::getMinTSD()                   */
+  /* Compact form of `penalty` (then `penalty` may be NULL): the factor depends only on
+   * (|scan - num_angular_perturbations|, |x offset|, |y offset|), so
+   * penalty_table[(a * (linear_bound + 1) + |x|) * (linear_bound + 1) + |y|], a = 0 ..
+   * num_angular_perturbations, holds every distinct value once (5 KB instead of 28 KB per scan at
+   * the default options) and the device indexes it per candidate. */
+  const double* penalty_table;     /* NULL: use `penalty`                              */
+  int32_t num_angular_perturbations;
+  int32_t pad;
 } csm_rt_job2d;
 
 int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int num_jobs,

@@ -426,3 +426,19 @@ def test_constraint_builder_two_devices_partition_and_hot_submap(csm):
     _, f4, t4, s4 = csm.constraint_builder_run(grids, poses, hot, full, rel, clouds, devices=(0, 1), **kw)
     assert np.array_equal(f3, f4) and np.array_equal(t3, t4)
     assert s4[8] >= 1 and s4[16] > 0 and s4[17] > 0   # the stack was replicated, the node list split
+
+
+def test_matcher_on_a_grid_read_from_a_proto_message(csm, gpu_ctx):
+    """Grid ingestion end to end: serialized proto::Grid2D -> grid handle -> stack -> search, identical
+    to the same search on the grid built directly."""
+    import proto_fixtures as pf
+    w = synth.World(220, 200, seed=91)
+    direct = csm.Matcher(gpu_ctx, csm.Grid(w.cells, w.res, w.max_x, w.max_y), 7.0, np.deg2rad(30.0), 5)
+    loaded = csm.Matcher(gpu_ctx, csm.ProtoGrid(pf.grid2d_bytes(w.cells, w.res, w.max_x, w.max_y)), 7.0,
+                         np.deg2rad(30.0), 5)
+    for lvl in range(5):
+        assert np.array_equal(direct.level(lvl), loaded.level(lvl))
+    _, pts = synth.make_scan(w, 17, max_range=8.0)
+    a, b = csm.match_batch(gpu_ctx, [direct, loaded], [pts, pts], [0.4, 0.4])
+    assert a.found and (a.found, a.scan_index, a.x_index_offset, a.y_index_offset, a.score) == \
+        (b.found, b.scan_index, b.x_index_offset, b.y_index_offset, b.score)
