@@ -60,6 +60,7 @@ ABI_SYMBOLS = [
     "csm_batch3d_upload", "csm_batch3d_run", "csm_batch3d_fetch", "csm_batch3d_destroy",
     "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch", "csm_grid2d_create", "csm_grid2d_insert",
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
+    "csm_grid2d_broadcast_dev", "csm_stack2d_broadcast",
     "csm_hgrid3d_create", "csm_hgrid3d_insert", "csm_hgrid3d_export", "csm_hgrid3d_box", "csm_hgrid3d_destroy",
     "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile", "csm_precomputation_grid2d",
     "csm_rotate_scans2d", "csm_discretize_points2d", "csm_rt_score_candidates2d",

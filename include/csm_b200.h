@@ -93,6 +93,18 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
 /* Same, with `cells_dev` already resident in device memory (benchmark path). */
 int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, int num_y,
                           const uint8_t* q_lut, int depth, csm_stack2d** out);
+/* ---- A new submap's grid to every replica (no counterpart in the reference,
+ * whose submaps live in one address space: constraint_builder_2d.cc:165-186 builds the matcher
+ * from the Grid2D it is handed).  One process per GPU: the owner of a finished submap broadcasts
+ * its uint16 cells over NCCL (NVLink) and every rank builds its own stack from its copy.
+ * nccl_comm is the caller's ncclComm_t (one rank per process); NCCL is reached through dlsym on the
+ * libnccl.so.2 the process already loaded, so this header and the library carry no NCCL dependency.
+ * Collective: every rank of the communicator calls it with the same root, sizes and depth.
+ * csm_grid2d_broadcast_dev: in place on a device buffer, asynchronous on the context's stream.
+ * csm_stack2d_broadcast: root passes is_root != 0 and its host cells (others may pass NULL). */
+int csm_grid2d_broadcast_dev(csm_ctx* ctx, void* nccl_comm, int root, uint16_t* cells_dev, size_t num_cells);
+int csm_stack2d_broadcast(csm_ctx* ctx, void* nccl_comm, int root, int is_root, const uint16_t* cells_host,
+                          int num_x, int num_y, const uint8_t* q_lut, int depth, csm_stack2d** out);
 /* Rebuilds an existing stack in place from device-resident cells; asynchronous on
  * the context's stream (used to time the build kernels alone). */
 int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* cells_dev);
