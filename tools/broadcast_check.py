@@ -44,12 +44,15 @@ def main():
     uid = UniqueId()
     if rank == 0:
         assert nccl.ncclGetUniqueId(C.byref(uid)) == 0
-    box = [bytes(uid.internal)] if rank == 0 else [None]
+    box = [C.string_at(C.byref(uid), 128)] if rank == 0 else [None]  # all 128 bytes (the id contains NULs)
     dist.broadcast_object_list(box, src=0)
+    assert len(box[0]) == 128
     C.memmove(C.byref(uid), box[0], 128)
     comm = C.c_void_p()
     nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
-    assert nccl.ncclCommInitRank(C.byref(comm), world, uid, rank) == 0
+    torch.zeros(1, device="cuda")  # a CUDA context on this rank's device before NCCL starts
+    rc = nccl.ncclCommInitRank(C.byref(comm), world, uid, rank)
+    assert rc == 0, "ncclCommInitRank -> %d" % rc
 
     pkg = _load_package()
     abi = pkg.abi()
