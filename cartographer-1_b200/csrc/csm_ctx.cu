@@ -57,6 +57,16 @@ std::mutex g_live_mu;
 std::set<const csm_ctx*> g_live;
 }  // namespace
 
+// Returns the block to `ctx`'s pool if `ctx` is a live context on `device`; the registry lock is
+// held across the hand-over so that a concurrent csm_ctx_destroy cannot free the pool in between.
+bool give_if_alive(::csm_ctx* ctx, int device, void* p, size_t cap) {
+  if (ctx == nullptr || p == nullptr) return false;
+  std::lock_guard<std::mutex> l(g_live_mu);
+  if (g_live.count(ctx) == 0 || ctx->device != device) return false;
+  ctx->pool.give(false, p, cap);
+  return true;
+}
+
 bool ctx_alive_on(const csm_ctx* ctx, int device) {
   if (ctx == nullptr) return false;
   std::lock_guard<std::mutex> l(g_live_mu);

@@ -85,6 +85,9 @@ struct BlockPool {
 // True while `ctx` is a live context on `device` (registry of csm_ctx_create/destroy):
 // destroy entry points use it to decide whether a block can go back to a pool.
 bool ctx_alive_on(const csm_ctx* ctx, int device);
+// Hands a device block back to the pool of `ctx` if it is a live context on `device` (under the
+// registry lock); false: the caller frees the block.
+bool give_if_alive(::csm_ctx* ctx, int device, void* p, size_t cap);
 
 }  // namespace csm
 

@@ -55,13 +55,18 @@ k_rt_decode(const uint16_t* __restrict__ cells, const float* __restrict__ table,
 constexpr int kRtWarps = 8;
 __global__ void __launch_bounds__(kRtWarps * 32)
 k_rt_score(const RtJobDev* __restrict__ jobs, const float* __restrict__ points,
-           const float* __restrict__ quats, unsigned long long* __restrict__ best, int max_n) {
+           const float* __restrict__ quats, unsigned long long* __restrict__ best, int max_n,
+           int2* __restrict__ spill) {
   extern __shared__ int2 cell_all[];
   const RtJobDev& j = jobs[blockIdx.y];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int scan = blockIdx.x * kRtWarps + warp;
   if (scan >= j.S) return;
-  int2* cell = cell_all + static_cast<size_t>(warp) * max_n;
+  // The discrete scan of a warp lives in shared memory; clouds too large for that (more than
+  // 3200 points) keep it in a global scratch slice per (job, scan) instead -- the reference has
+  // no limit on the cloud's size.
+  int2* cell = spill != nullptr ? spill + static_cast<size_t>(j.quat_off + scan) * max_n
+                                : cell_all + static_cast<size_t>(warp) * max_n;
   const float qw = quats[2 * (j.quat_off + scan)], qs = quats[2 * (j.quat_off + scan) + 1];
   for (int p = lane; p < j.n; p += 32) {
     float vx = points[3 * (j.pts_off + p)], vy = points[3 * (j.pts_off + p) + 1];
@@ -217,8 +222,10 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     max_scans = std::max(max_scans, in.num_scans);
     max_n = std::max(max_n, in.num_points);
   }
-  const size_t smem = sizeof(int2) * static_cast<size_t>(max_n) * kRtWarps;
-  CSM_REQUIRE(smem <= 200 * 1024, "point cloud too large for the real-time matcher (3200 points)");
+  size_t smem = sizeof(int2) * static_cast<size_t>(max_n) * kRtWarps;
+  const bool use_spill = smem > 200 * 1024;
+  const size_t spill_bytes = use_spill ? up(sizeof(int2) * n_scans * static_cast<size_t>(max_n)) : 0;
+  if (use_spill) smem = 0;
   const size_t o_jobs = 0;
   const size_t o_pts = o_jobs + up(sizeof(RtJobDev) * num_jobs);
   const size_t o_quat = o_pts + up(sizeof(float) * 3 * n_pts);
@@ -252,7 +259,7 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
     if (in.weight_cells) wdec_of[i] = decoded_at(in.weight_cells, in.weight_table, n, 0);
   }
   const size_t o_dec = total;
-  int rc = ctx->tmp2.reserve(total + dec_bytes);
+  int rc = ctx->tmp2.reserve(total + dec_bytes + spill_bytes);
   if (rc == CSM_OK) rc = ctx->pin0.reserve(total);
   if (rc != CSM_OK) return rc;
   char* pin = ctx->pin0.as<char>();
@@ -306,7 +313,8 @@ extern "C" int csm_rt_match2d_batch(csm_ctx* ctx, const csm_rt_job2d* jobs, int 
   ++ctx->launches, k_rt_score<<<dim3((max_scans + kRtWarps - 1) / kRtWarps, num_jobs), kRtWarps * 32, smem, st>>>(
       reinterpret_cast<const RtJobDev*>(base + o_jobs), reinterpret_cast<const float*>(base + o_pts),
       reinterpret_cast<const float*>(base + o_quat),
-      reinterpret_cast<unsigned long long*>(base + o_best), max_n);
+      reinterpret_cast<unsigned long long*>(base + o_best), max_n,
+      use_spill ? reinterpret_cast<int2*>(base + o_dec + dec_bytes) : nullptr);
   CSM_CUDA(cudaGetLastError());
   unsigned long long* best = reinterpret_cast<unsigned long long*>(pin + o_best);
   CSM_CUDA(cudaMemcpyAsync(best, base + o_best, sizeof(unsigned long long) * num_jobs,

@@ -1094,9 +1094,15 @@ int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, in
   int rc = create_stack(ctx, num_x, num_y, q_lut, depth, out);
   if (rc != CSM_OK) return rc;
   rc = launch_build(ctx, *out, cells_dev);
-  if (rc != CSM_OK) return rc;
-  CSM_CUDA(cudaStreamSynchronize(ctx->stream));
-  return CSM_OK;
+  if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+    csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = CSM_ERR_CUDA;
+  }
+  if (rc != CSM_OK) {  // no half-built stack escapes
+    csm_stack2d_destroy(ctx, *out);
+    *out = nullptr;
+  }
+  return rc;
 }
 
 int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
@@ -1106,12 +1112,21 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
   if (rc != CSM_OK) return rc;
   const size_t bytes = static_cast<size_t>(num_x) * num_y * sizeof(uint16_t);
   rc = ctx->tmp0.reserve(bytes + 16);
-  if (rc != CSM_OK) return rc;
-  CSM_CUDA(cudaMemcpyAsync(ctx->tmp0.p, cells, bytes, cudaMemcpyHostToDevice, ctx->stream));
-  rc = launch_build(ctx, *out, ctx->tmp0.as<uint16_t>());
-  if (rc != CSM_OK) return rc;
-  CSM_CUDA(cudaStreamSynchronize(ctx->stream));
-  return CSM_OK;
+  if (rc == CSM_OK &&
+      cudaMemcpyAsync(ctx->tmp0.p, cells, bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
+    csm::set_error("grid upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = CSM_ERR_CUDA;
+  }
+  if (rc == CSM_OK) rc = launch_build(ctx, *out, ctx->tmp0.as<uint16_t>());
+  if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+    csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = CSM_ERR_CUDA;
+  }
+  if (rc != CSM_OK) {  // no half-built stack escapes
+    csm_stack2d_destroy(ctx, *out);
+    *out = nullptr;
+  }
+  return rc;
 }
 
 // PrecomputationGrid2D of ANY width (the public class takes one, FCSM2D.h:49-54; the stack only
@@ -1213,13 +1228,10 @@ void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* s) {
   cudaSetDevice(s->device);
   // `ctx` may be stale (a matcher can outlive the context it was built on): only a
   // live context of the stack's device gets the block back into its pool.
-  if (csm::ctx_alive_on(ctx, s->device)) {
-    cudaStreamSynchronize(ctx->stream);
-    ctx->pool.give(false, s->base, s->base_cap);
-  } else {
-    cudaDeviceSynchronize();
-    if (s->base) cudaFree(s->base);
-  }
+  // A stack may be searched from any context of its device (csm_b200.h), so the whole device is
+  // drained, not only the building context's stream, before the block can be handed out again.
+  cudaDeviceSynchronize();
+  if (!csm::give_if_alive(ctx, s->device, s->base, s->base_cap) && s->base) cudaFree(s->base);
   delete s;
 }
 

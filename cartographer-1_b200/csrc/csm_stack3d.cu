@@ -332,12 +332,8 @@ size_t csm_stack3d_device_bytes(const csm_stack3d* s) { return s ? s->bytes : 0;
 void csm_stack3d_destroy(csm_ctx* ctx, csm_stack3d* s) {
   if (!s) return;
   cudaSetDevice(s->device);
-  if (ctx_alive_on(ctx, s->device)) {  // see csm_stack2d_destroy
-    cudaStreamSynchronize(ctx->stream);
-    ctx->pool.give(false, s->base, s->cap);
-  } else if (s->base) {
-    cudaFree(s->base);
-  }
+  cudaDeviceSynchronize();  // see csm_stack2d_destroy
+  if (!give_if_alive(ctx, s->device, s->base, s->cap) && s->base) cudaFree(s->base);
   delete s;
 }
 
@@ -406,12 +402,8 @@ int csm_grid3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vox
 void csm_grid3d_destroy(csm_ctx* ctx, csm_grid3d* g) {
   if (!g) return;
   cudaSetDevice(g->device);
-  if (ctx_alive_on(ctx, g->device)) {
-    cudaStreamSynchronize(ctx->stream);
-    ctx->pool.give(false, g->data, g->cap);
-  } else if (g->data) {
-    cudaFree(g->data);
-  }
+  cudaDeviceSynchronize();  // see csm_stack2d_destroy
+  if (!give_if_alive(ctx, g->device, g->data, g->cap) && g->data) cudaFree(g->data);
   delete g;
 }
 

@@ -4,6 +4,9 @@
 #include <cmath>
 #include <cstring>
 
+#include <map>
+#include <memory>
+
 #include "parallel_for.h"
 
 namespace cartographer {
@@ -22,9 +25,13 @@ void CheckOk(int status, const char* what) {
 
 }  // namespace
 
-DeviceContext* DeviceContext::ThreadDefault() {
-  thread_local DeviceContext context(0);
-  return &context;
+DeviceContext* DeviceContext::ThreadDefault() { return ThreadLocal(0); }
+
+DeviceContext* DeviceContext::ThreadLocal(const int device) {
+  thread_local std::map<int, std::unique_ptr<DeviceContext>> contexts;
+  std::unique_ptr<DeviceContext>& slot = contexts[device];
+  if (!slot) slot.reset(new DeviceContext(device));
+  return slot.get();
 }
 
 DeviceContext::DeviceContext(int device) : device_(device) {
@@ -137,6 +144,7 @@ void FastCorrelativeScanMatcher2D::Build(const Grid2D& grid) {
   const std::vector<uint8> q = ComputeQuantizationTable(grid);
   const CellLimits& cells = limits_.cell_limits();
   build_context_ = context_->get();
+  device_ = context_->device();
   CheckOk(csm_stack2d_build(build_context_, grid.correspondence_cost_cells().data(),
                             cells.num_x_cells, cells.num_y_cells, q.data(),
                             options_.branch_and_bound_depth(), &stack_),
@@ -160,9 +168,9 @@ bool FastCorrelativeScanMatcher2D::Match(const transform::Rigid2d& initial_pose_
   q.full_submap = false;
   q.initial_pose_estimate = initial_pose_estimate;
   q.min_score = min_score;
-  // A matcher built on another thread's context still runs on the caller's own one.
-  DeviceContext* ctx = DeviceContext::ThreadDefault();
-  if (ctx->device() != context_->device()) ctx = context_;
+  // Whatever context the matcher was built on, a call runs on the calling thread's own context
+  // for the stack's device (a csm_ctx is single-threaded; Match is const and called concurrently).
+  DeviceContext* ctx = DeviceContext::ThreadLocal(device_);
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return false;
   *score = a.score;
@@ -179,8 +187,7 @@ bool FastCorrelativeScanMatcher2D::MatchFullSubmap(const sensor::PointCloud& poi
   q.point_cloud = &point_cloud;
   q.full_submap = true;
   q.min_score = min_score;
-  DeviceContext* ctx = DeviceContext::ThreadDefault();
-  if (ctx->device() != context_->device()) ctx = context_;
+  DeviceContext* ctx = DeviceContext::ThreadLocal(device_);
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return false;
   *score = a.score;

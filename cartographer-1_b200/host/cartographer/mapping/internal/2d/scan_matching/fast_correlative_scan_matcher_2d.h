@@ -34,6 +34,9 @@ class DeviceContext {
   // One lazily created context on device 0 per calling thread (the reference's
   // Match* are called concurrently from pool threads; a csm_ctx is single-threaded).
   static DeviceContext* ThreadDefault();
+  // One lazily created context per (calling thread, device): what the const, concurrently
+  // callable Match / MatchFullSubmap of a matcher living on `device` run on.
+  static DeviceContext* ThreadLocal(int device);
   int device() const { return device_; }
 
  private:
@@ -193,6 +196,7 @@ class FastCorrelativeScanMatcher2D {
   DeviceContext* context_ = nullptr;
   csm_stack2d* stack_ = nullptr;
   csm_ctx* build_context_ = nullptr;  // raw handle: DeviceContext may be deleted before us
+  int device_ = 0;                    // where the stack lives (context_ may dangle once its thread exits)
 };
 
 }  // namespace scan_matching

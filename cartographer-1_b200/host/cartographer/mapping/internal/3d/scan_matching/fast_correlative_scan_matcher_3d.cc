@@ -121,6 +121,7 @@ void FastCorrelativeScanMatcher3D::Build(const HybridGrid& hybrid_grid) {
   hybrid_grid.Export(&xyz, &values);
   const std::vector<uint8> q = ComputeQuantizationTable3D();
   build_context_ = context_->get();
+  device_ = context_->device();
   CheckOk(csm_stack3d_build(build_context_, xyz.data(), values.data(), static_cast<int>(values.size()),
                             q.data(), options_.branch_and_bound_depth(),
                             options_.full_resolution_depth(), &stack_),
@@ -146,8 +147,7 @@ std::unique_ptr<FastCorrelativeScanMatcher3D::Result> FastCorrelativeScanMatcher
   q.global_node_pose = global_node_pose;
   q.global_submap_pose = global_submap_pose;
   q.min_score = min_score;
-  DeviceContext* ctx = DeviceContext::ThreadDefault();
-  if (ctx->device() != context_->device()) ctx = context_;
+  DeviceContext* ctx = DeviceContext::ThreadLocal(device_);
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return nullptr;
   return std::unique_ptr<Result>(new Result(a.result));
@@ -162,8 +162,7 @@ std::unique_ptr<FastCorrelativeScanMatcher3D::Result> FastCorrelativeScanMatcher
   q.global_node_pose = transform::Rigid3d(transform::Vector3d(), global_node_rotation);
   q.global_submap_pose = transform::Rigid3d(transform::Vector3d(), global_submap_rotation);
   q.min_score = min_score;
-  DeviceContext* ctx = DeviceContext::ThreadDefault();
-  if (ctx->device() != context_->device()) ctx = context_;
+  DeviceContext* ctx = DeviceContext::ThreadLocal(device_);
   const Answer a = MatchBatch(ctx, {{this, q}})[0];
   if (!a.found) return nullptr;
   return std::unique_ptr<Result>(new Result(a.result));

@@ -189,6 +189,7 @@ class FastCorrelativeScanMatcher3D {
   csm_stack3d* stack_ = nullptr;
   csm_grid3d* low_grid_ = nullptr;
   csm_ctx* build_context_ = nullptr;  // raw handle the device blocks go back to
+  int device_ = 0;                    // where the stack lives
 };
 
 }  // namespace scan_matching

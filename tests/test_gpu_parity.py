@@ -442,3 +442,26 @@ def test_matcher_on_a_grid_read_from_a_proto_message(csm, gpu_ctx):
     a, b = csm.match_batch(gpu_ctx, [direct, loaded], [pts, pts], [0.4, 0.4])
     assert a.found and (a.found, a.scan_index, a.x_index_offset, a.y_index_offset, a.score) == \
         (b.found, b.scan_index, b.x_index_offset, b.y_index_offset, b.score)
+
+
+def test_real_time_matcher_takes_clouds_of_any_size(csm, gpu_ctx):
+    """clouds of more than 3200 points used to be rejected (the discrete scan of a warp
+    did not fit shared memory); they now go through a global scratch slice.  One batch mixes a
+    5000-point cloud with an ordinary one."""
+    w = synth.World(300, 300, seed=23)
+    og = ob.OracleGrid(w.cells, w.res, w.max_x, w.max_y)
+    g = csm.Grid(w.cells, w.res, w.max_x, w.max_y)
+    opts = {"linear_search_window": 0.1, "angular_search_window": float(np.deg2rad(10.0)),
+            "translation_delta_cost_weight": 0.1, "rotation_delta_cost_weight": 0.1}
+    rng = np.random.default_rng(4)
+    pose, pts = synth.make_scan(w, 77)
+    big = np.ascontiguousarray(np.concatenate([pts + rng.normal(0, 0.02, pts.shape).astype(np.float32) * [1, 1, 0]
+                                               for _ in range(5000 // len(pts) + 1)])[:5000].astype(np.float32))
+    clouds = [big, np.ascontiguousarray(pts)]
+    inits = [(pose[0] + 0.04, pose[1] - 0.03, pose[2] + 0.05)] * 2
+    res = csm.rt_match_batch(gpu_ctx, [g, g], clouds, inits, **opts)
+    for c, init, r_g in zip(clouds, inits, res):
+        r_o = ob.rt_match(og, opts, init, c)
+        assert (r_g.scan_index, r_g.x_index_offset, r_g.y_index_offset) == \
+               (r_o.scan_index, r_o.x_index_offset, r_o.y_index_offset)
+        assert np.float32(r_g.score).tobytes() == np.float32(r_o.score).tobytes()
