@@ -62,6 +62,7 @@ ABI_SYMBOLS = [
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
     "csm_grid2d_broadcast_dev", "csm_stack2d_broadcast",
     "csm_hgrid3d_create", "csm_hgrid3d_insert", "csm_hgrid3d_export", "csm_hgrid3d_box", "csm_hgrid3d_destroy",
+    "csm_stack3d_build_from_hgrid",
     "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile", "csm_precomputation_grid2d",
     "csm_rotate_scans2d", "csm_discretize_points2d", "csm_rt_score_candidates2d",
     "csm_discretize2d_noalloc",
@@ -818,3 +819,30 @@ def hybrid_grid_from_proto(serialized):
                                       xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
     order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
     return res.value, size.value, xyz[order], values[order]
+
+
+def grid3d_resident_stack_check(ctx, resolution, xyz, values, origins, returns, depth, full_resolution_depth,
+                                hit_probability=0.55, miss_probability=0.49, num_free_space_voxels=2):
+    """Inserts the scans into a device-resident HybridGrid, builds the matcher's stack straight from it and
+    from its exported voxel list; returns the number of differing level bytes (0 = identical)."""
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    L.csmh_grid3d_resident_stack_check.argtypes = [C.c_void_p, C.c_float, i32p, u16p, C.c_int, f64p, C.c_int, f32p,
+                                                   f32p, i64p, C.c_int, C.c_int]
+    L.csmh_grid3d_resident_stack_check.restype = C.c_int64
+    xyz = np.ascontiguousarray(np.asarray(xyz, np.int32).reshape(-1, 3))
+    values = np.ascontiguousarray(values, np.uint16)
+    n = len(origins)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, r in enumerate(returns):
+        offsets[i + 1] = offsets[i] + len(r)
+    pts = np.ascontiguousarray(np.concatenate([np.asarray(r, np.float32).reshape(-1, 3) for r in returns], axis=0),
+                               dtype=np.float32)
+    return L.csmh_grid3d_resident_stack_check(
+        ctx.h, resolution, xyz.reshape(-1), values, len(values),
+        np.array([hit_probability, miss_probability, num_free_space_voxels], np.float64), n,
+        np.ascontiguousarray(origins, np.float32).reshape(-1), pts.reshape(-1), offsets, depth, full_resolution_depth)

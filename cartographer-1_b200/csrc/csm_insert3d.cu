@@ -161,6 +161,27 @@ __global__ void k_export(const uint16_t* __restrict__ cells, Box3 box, size_t n,
   values[at] = v;
 }
 
+// lo/hi of the n exported voxels: out6 = {min x, y, z, max x, y, z}, pre-set to +-INT_MAX.
+__global__ void k_voxel_box(const int* __restrict__ xyz, unsigned int n, int* out6) {
+  const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int v[3] = {0, 0, 0};
+  const bool have = i < n;
+  if (have) {
+    v[0] = xyz[3 * i];
+    v[1] = xyz[3 * i + 1];
+    v[2] = xyz[3 * i + 2];
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const int mn = __reduce_min_sync(0xFFFFFFFFu, have ? v[a] : 0x7FFFFFFF);
+    const int mx = __reduce_max_sync(0xFFFFFFFFu, have ? v[a] : -0x7FFFFFFF);
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(out6 + a, mn);
+      atomicMax(out6 + 3 + a, mx);
+    }
+  }
+}
+
 Box3 box_of(const csm_hgrid3d* g) {
   Box3 b;
   for (int a = 0; a < 3; ++a) {
@@ -229,6 +250,45 @@ int ensure_box(csm_ctx* ctx, csm_hgrid3d* g, const int* lo, const int* hi) {
 }
 
 }  // namespace
+
+namespace csm {
+int hgrid3d_stage(::csm_ctx* ctx, const ::csm_hgrid3d* g, int* num_voxels, int* lo3, int* hi3) {
+  CSM_REQUIRE(g->device == ctx->device, "grid lives on another device");
+  CSM_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  *num_voxels = 0;
+  const size_t n = g->cells ? volume(g->dim) : 0;
+  if (n == 0) return CSM_OK;
+  // pass 1: count; pass 2: write (the order between blocks is arbitrary, a set is all the build needs)
+  unsigned int count = 0;
+  CSM_CUDA(cudaMemsetAsync(g->counter, 0, sizeof(unsigned int), st));
+  ++ctx->launches, k_export<<<static_cast<unsigned int>((n + 255) / 256), 256, 0, st>>>(g->cells, box_of(g), n, g->counter,
+                                                                                       nullptr, nullptr, 0u);
+  CSM_CUDA(cudaMemcpyAsync(&count, g->counter, sizeof(count), cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaStreamSynchronize(st));
+  if (count == 0) return CSM_OK;
+  int rc = ctx->tmp0.reserve(sizeof(int) * 3 * static_cast<size_t>(count) + 64);
+  if (rc == CSM_OK) rc = ctx->tmp1.reserve(sizeof(uint16_t) * static_cast<size_t>(count) + 64);
+  if (rc == CSM_OK) rc = ctx->tmp2.reserve(64);
+  if (rc != CSM_OK) return rc;
+  CSM_CUDA(cudaMemsetAsync(g->counter, 0, sizeof(unsigned int), st));
+  ++ctx->launches, k_export<<<static_cast<unsigned int>((n + 255) / 256), 256, 0, st>>>(
+      g->cells, box_of(g), n, g->counter, ctx->tmp0.as<int>(), ctx->tmp1.as<uint16_t>(), count);
+  const int init[6] = {0x7FFFFFFF, 0x7FFFFFFF, 0x7FFFFFFF, -0x7FFFFFFF, -0x7FFFFFFF, -0x7FFFFFFF};
+  int box[6];
+  CSM_CUDA(cudaMemcpyAsync(ctx->tmp2.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  ++ctx->launches, k_voxel_box<<<(count + 255) / 256, 256, 0, st>>>(ctx->tmp0.as<int>(), count, ctx->tmp2.as<int>());
+  CSM_CUDA(cudaMemcpyAsync(box, ctx->tmp2.p, sizeof(box), cudaMemcpyDeviceToHost, st));
+  CSM_CUDA(cudaStreamSynchronize(st));
+  CSM_CUDA(cudaGetLastError());
+  for (int a = 0; a < 3; ++a) {
+    lo3[a] = box[a];
+    hi3[a] = box[3 + a];
+  }
+  *num_voxels = static_cast<int>(count);
+  return CSM_OK;
+}
+}  // namespace csm
 
 extern "C" {
 

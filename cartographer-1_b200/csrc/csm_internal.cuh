@@ -85,6 +85,10 @@ struct BlockPool {
 // True while `ctx` is a live context on `device` (registry of csm_ctx_create/destroy):
 // destroy entry points use it to decide whether a block can go back to a pool.
 bool ctx_alive_on(const csm_ctx* ctx, int device);
+// csm_insert3d.cu: writes the non-default voxels of a device-resident HybridGrid into ctx->tmp0
+// (xyz, int32) / ctx->tmp1 (values, uint16) -- where csm_stack3d_build stages a host list -- and
+// returns their number and bounding box (inclusive).  Synchronises the context's stream.
+int hgrid3d_stage(::csm_ctx* ctx, const ::csm_hgrid3d* grid, int* num_voxels, int* lo3, int* hi3);
 // Hands a device block back to the pool of `ctx` if it is a live context on `device` (under the
 // registry lock); false: the caller frees the block.
 bool give_if_alive(::csm_ctx* ctx, int device, void* p, size_t cap);

@@ -165,12 +165,34 @@ using namespace csm;
 
 extern "C" {
 
+// staged_box != nullptr: the voxel list already sits in ctx->tmp0 / tmp1 on the device (put there by
+// hgrid3d_stage) and staged_box = {lo[3], hi[3]} is its bounding box; else it is taken from the host
+// arrays.
+static int build_stack3d(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* voxel_values, int num_voxels,
+                         const int* staged_box, const uint8_t* q_lut, int depth, int full_resolution_depth,
+                         csm_stack3d** out);
+
 int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* voxel_values,
                       int num_voxels, const uint8_t* q_lut, int depth, int full_resolution_depth,
                       csm_stack3d** out) {
-  CSM_REQUIRE(ctx != nullptr && out != nullptr && q_lut != nullptr, "NULL argument");
   CSM_REQUIRE(num_voxels >= 0 && (num_voxels == 0 || (voxel_xyz != nullptr && voxel_values != nullptr)),
               "voxel list");
+  return build_stack3d(ctx, voxel_xyz, voxel_values, num_voxels, nullptr, q_lut, depth, full_resolution_depth, out);
+}
+
+int csm_stack3d_build_from_hgrid(csm_ctx* ctx, const csm_hgrid3d* grid, const uint8_t* q_lut, int depth,
+                                 int full_resolution_depth, csm_stack3d** out) {
+  CSM_REQUIRE(ctx != nullptr && grid != nullptr, "NULL argument");
+  int n = 0, box[6] = {0, 0, 0, -1, -1, -1};
+  const int rc = hgrid3d_stage(ctx, grid, &n, box, box + 3);
+  if (rc != CSM_OK) return rc;
+  return build_stack3d(ctx, nullptr, nullptr, n, box, q_lut, depth, full_resolution_depth, out);
+}
+
+static int build_stack3d(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* voxel_values, int num_voxels,
+                         const int* staged_box, const uint8_t* q_lut, int depth, int full_resolution_depth,
+                         csm_stack3d** out) {
+  CSM_REQUIRE(ctx != nullptr && out != nullptr && q_lut != nullptr, "NULL argument");
   CSM_REQUIRE(depth >= 1 && depth <= CSM_MAX_DEPTH, "branch_and_bound_depth out of range");
   CSM_REQUIRE(full_resolution_depth >= 1, "full_resolution_depth must be >= 1");  // FCSM3D.cc:61
   CSM_CUDA(cudaSetDevice(ctx->device));
@@ -183,7 +205,16 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
   s->host_view.depth = depth;
   s->host_view.frd = full_resolution_depth;
   int lo[3] = {0, 0, 0}, hi[3] = {-1, -1, -1};
-  const bool any = voxel_box(voxel_xyz, voxel_values, num_voxels, true, lo, hi);
+  bool any;
+  if (staged_box != nullptr) {
+    any = num_voxels > 0;  // a staged list holds non-default voxels only
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = staged_box[a];
+      hi[a] = staged_box[3 + a];
+    }
+  } else {
+    any = voxel_box(voxel_xyz, voxel_values, num_voxels, true, lo, hi);
+  }
   // Boxes of all levels and the shift between them (FCSM3D.cc:63-76).
   int shifts[CSM_MAX_DEPTH] = {0};
   int halfs[CSM_MAX_DEPTH] = {0};
@@ -254,7 +285,7 @@ int csm_stack3d_build(csm_ctx* ctx, const int32_t* voxel_xyz, const uint16_t* vo
         k + 1 < depth ? reinterpret_cast<const uint2*>(s->base + s->pack_off[k]) : nullptr;
   }
   cudaStream_t st = ctx->stream;
-  int rc = upload_voxels(ctx, voxel_xyz, voxel_values, num_voxels);
+  int rc = staged_box != nullptr ? CSM_OK : upload_voxels(ctx, voxel_xyz, voxel_values, num_voxels);
   if (rc != CSM_OK) return fail(rc);
   if (cudaMemcpyAsync(lut_dev, q_lut, 65536, cudaMemcpyHostToDevice, st) != cudaSuccess ||
       cudaMemcpyAsync(s->dev, &s->host_view, sizeof(Stack3Dev), cudaMemcpyHostToDevice, st) != cudaSuccess ||

@@ -469,4 +469,63 @@ void csmh_grid3d_result_copy(void* r, int32_t* xyz, uint16_t* values) {
 }
 void csmh_grid3d_result_destroy(void* r) { delete static_cast<Grid3DResult*>(r); }
 
+
+// The resident 3D pipeline end to end: voxels -> DeviceGrid, every scan inserted, then the matcher's
+// stack built (a) straight from the device grid (csm_stack3d_build_from_hgrid) and (b) from the
+// exported voxel list (csm_stack3d_build).  Returns the number of level bytes that differ between
+// the two (0 = identical boxes and contents), -1 on differing boxes.
+int64_t csmh_grid3d_resident_stack_check(void* ctx, float resolution, const int32_t* xyz, const uint16_t* values,
+                                         int n_voxels, const double* options3, int num, const float* origins,
+                                         const float* returns_xyz, const int64_t* offsets, int depth,
+                                         int full_resolution_depth) {
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n_voxels; ++i)
+    *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  mapping::proto::RangeDataInserterOptions3D o;
+  o.set_hit_probability(options3[0]);
+  o.set_miss_probability(options3[1]);
+  o.set_num_free_space_voxels(static_cast<int>(options3[2]));
+  const mapping::RangeDataInserter3D inserter(o, context);
+  std::vector<sensor::RangeData> scans(num);
+  std::vector<const sensor::RangeData*> list;
+  for (int s = 0; s < num; ++s) {
+    scans[s].origin = sensor::Vector3f(origins[3 * s], origins[3 * s + 1], origins[3 * s + 2]);
+    for (int64_t i = offsets[s]; i < offsets[s + 1]; ++i)
+      scans[s].returns.push_back({sensor::Vector3f(returns_xyz[3 * i], returns_xyz[3 * i + 1], returns_xyz[3 * i + 2])});
+    list.push_back(&scans[s]);
+  }
+  mapping::RangeDataInserter3D::DeviceGrid device_grid(context, grid);
+  inserter.Insert(list, &device_grid);
+  const std::vector<uint8_t> q = mapping::scan_matching::ComputeQuantizationTable3D();
+  csm_stack3d *direct = nullptr, *listed = nullptr;
+  if (csm_stack3d_build_from_hgrid(context->get(), device_grid.get(), q.data(), depth, full_resolution_depth,
+                                   &direct) != CSM_OK)
+    return -2;
+  std::vector<int32_t> vx;
+  std::vector<uint16_t> vv;
+  device_grid.Export(&vx, &vv);
+  if (csm_stack3d_build(context->get(), vx.data(), vv.data(), static_cast<int>(vv.size()), q.data(), depth,
+                        full_resolution_depth, &listed) != CSM_OK)
+    return -3;
+  int64_t differing = 0;
+  for (int level = 0; level < depth && differing >= 0; ++level) {
+    int32_t lo_a[3], dim_a[3], lo_b[3], dim_b[3];
+    csm_stack3d_level(context->get(), direct, level, nullptr, lo_a, dim_a);
+    csm_stack3d_level(context->get(), listed, level, nullptr, lo_b, dim_b);
+    if (std::memcmp(lo_a, lo_b, sizeof(lo_a)) != 0 || std::memcmp(dim_a, dim_b, sizeof(dim_a)) != 0) {
+      differing = -1;
+      break;
+    }
+    const size_t bytes = static_cast<size_t>(dim_a[0]) * dim_a[1] * dim_a[2];
+    std::vector<uint8_t> a(bytes), b(bytes);
+    csm_stack3d_level(context->get(), direct, level, a.data(), lo_a, dim_a);
+    csm_stack3d_level(context->get(), listed, level, b.data(), lo_b, dim_b);
+    for (size_t i = 0; i != bytes; ++i) differing += a[i] != b[i];
+  }
+  csm_stack3d_destroy(context->get(), direct);
+  csm_stack3d_destroy(context->get(), listed);
+  return differing;
+}
+
 }  // extern "C"

@@ -485,6 +485,10 @@ int csm_hgrid3d_insert(csm_ctx* ctx, csm_hgrid3d* grid, const csm_range_data3d* 
 int csm_hgrid3d_export(csm_ctx* ctx, const csm_hgrid3d* grid, int32_t* voxel_xyz, uint16_t* voxel_values,
                        int capacity, int* num_voxels);
 int csm_hgrid3d_box(const csm_hgrid3d* grid, int32_t* lo3, int32_t* dims3);
+/* The matcher's stack straight from the device-resident grid (same result as csm_stack3d_build of
+ * csm_hgrid3d_export's list): the voxels never cross PCIe. */
+int csm_stack3d_build_from_hgrid(csm_ctx* ctx, const csm_hgrid3d* grid, const uint8_t* q_lut, int depth,
+                                 int full_resolution_depth, csm_stack3d** out);
 void csm_hgrid3d_destroy(csm_ctx* ctx, csm_hgrid3d* grid);
 
 /* ---- measurement aids (bench.py) ------------------------------------------------

@@ -74,3 +74,16 @@ def test_edge_cases(csm, gpu_ctx):
         got = csm.grid3d_insert(gpu_ctx, 0.1, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16), [o], [returns],
                                 resident=True, **kw)
         assert got[0].tobytes() == want[0].tobytes() and got[1].tobytes() == want[1].tobytes()
+
+
+@pytest.mark.parametrize("depth,frd", [(5, 3), (6, 1), (3, 5)])
+def test_stack_straight_from_the_device_grid(csm, gpu_ctx, depth, frd):
+    """csm_stack3d_build_from_hgrid: the precomputation stack built from the device-resident grid
+    (voxels never leave HBM) equals the one built from the exported voxel list, box by box and
+    byte by byte; the latter is what test_gpu_parity3d holds to the oracle."""
+    w = synth3d.World3D(13, size_xy=6.0)
+    xyz, val = w.voxels(0.1)
+    origins, returns = _scans(13, 3, max_range=4.0, n=300)
+    assert csm.grid3d_resident_stack_check(gpu_ctx, 0.1, xyz, val, origins, returns, depth, frd) == 0
+    assert csm.grid3d_resident_stack_check(gpu_ctx, 0.1, np.zeros((0, 3), np.int32), np.zeros(0, np.uint16),
+                                           origins, returns, depth, frd) == 0
