@@ -366,6 +366,51 @@ class TSDF2D {
     tsd_cells_[flat] = TSDToValue(tsd);
     weight_cells_[flat] = WeightToValue(weight);
   }
+  // tsdf_2d.cc:44-48, 51-68 with the update marker, and Grid2D::FinishUpdate (grid_2d.cc:98-106):
+  // what TSDFRangeDataInserter2D uses (csm_tsdf_inserter.h).
+  bool CellIsUpdated(const Array2i& c) const {
+    ORACLE_CHECK(limits_.Contains(c));
+    return tsd_cells_[limits_.cell_limits.num_x_cells * c.y + c.x] >= kUpdateMarker;
+  }
+  void SetCellMarked(const Array2i& c, const float tsd, const float weight) {
+    ORACLE_CHECK(limits_.Contains(c));
+    const int flat = limits_.cell_limits.num_x_cells * c.y + c.x;
+    if (tsd_cells_[flat] >= kUpdateMarker) return;
+    update_indices_.push_back(flat);
+    tsd_cells_[flat] = static_cast<uint16_t>(TSDToValue(tsd) + kUpdateMarker);
+    weight_cells_[flat] = WeightToValue(weight);
+  }
+  void FinishUpdate() {
+    while (!update_indices_.empty()) {
+      tsd_cells_[update_indices_.back()] -= kUpdateMarker;
+      update_indices_.pop_back();
+    }
+  }
+  // tsdf_2d.cc:100-105 on grid_2d.cc:131-166: both cell arrays, unknown value 0 for each.
+  void GrowLimits(const float px, const float py) {
+    ORACLE_CHECK(update_indices_.empty());
+    while (!limits_.Contains(limits_.GetCellIndex(px, py))) {
+      const int nx = limits_.cell_limits.num_x_cells, ny = limits_.cell_limits.num_y_cells;
+      const int x_offset = nx / 2, y_offset = ny / 2;
+      MapLimits grown;
+      grown.resolution = limits_.resolution;
+      grown.max_x = limits_.max_x + limits_.resolution * y_offset;
+      grown.max_y = limits_.max_y + limits_.resolution * x_offset;
+      grown.cell_limits.num_x_cells = 2 * nx;
+      grown.cell_limits.num_y_cells = 2 * ny;
+      const int stride = grown.cell_limits.num_x_cells;
+      for (std::vector<uint16_t>* grid : {&tsd_cells_, &weight_cells_}) {
+        std::vector<uint16_t> cells(static_cast<size_t>(4) * nx * ny, kUnknownValue);
+        for (int i = 0; i < ny; ++i)
+          for (int j = 0; j < nx; ++j) cells[x_offset + stride * y_offset + j + i * stride] = (*grid)[j + i * nx];
+        grid->swap(cells);
+      }
+      limits_ = grown;
+    }
+  }
+  float max_weight() const { return max_weight_; }
+  float truncation_distance() const { return max_tsd_; }
+
   // tsdf_2d.cc:88-98
   std::pair<float, float> GetTSDAndWeight(const Array2i& c) const {
     if (limits_.Contains(c)) {
@@ -379,6 +424,7 @@ class TSDF2D {
   MapLimits limits_;
   float max_tsd_, min_tsd_, max_weight_, tsd_resolution_, weight_resolution_;
   std::vector<uint16_t> tsd_cells_, weight_cells_;
+  std::vector<int> update_indices_;
   std::vector<float> value_to_tsd_, value_to_weight_, value_to_cost_;
 };
 

@@ -8,6 +8,7 @@
 #include "csm_oracle.h"
 #include "csm_ceres.h"
 #include "csm_oracle3d.h"
+#include "csm_tsdf_inserter.h"
 
 using namespace oracle;
 
@@ -221,6 +222,36 @@ void* oracle_tsdf2d_create(const uint16_t* tsd_cells, const uint16_t* weight_cel
                     weight_cells);
 }
 void oracle_tsdf2d_destroy(void* g) { delete static_cast<TSDF2D*>(g); }
+// TSDFRangeDataInserter2D::Insert on a TSDF2D handle (GrowLimits included); options9 as in
+// ref_capi.cc's entry of the same name.
+void oracle_tsdf2d_insert(void* grid, const double* options9, const float* origin_xy, const float* returns_xyz,
+                          int num_returns) {
+  TSDFRangeDataInserterOptions2D o;
+  o.truncation_distance = options9[0];
+  o.maximum_weight = options9[1];
+  o.update_free_space = options9[2] != 0.;
+  o.num_normal_samples = static_cast<int>(options9[3]);
+  o.sample_radius = static_cast<float>(options9[4]);
+  o.project_sdf_distance_to_scan_normal = options9[5] != 0.;
+  o.update_weight_range_exponent = static_cast<int>(options9[6]);
+  o.update_weight_angle_scan_normal_to_ray_kernel_bandwidth = options9[7];
+  o.update_weight_distance_cell_to_hit_kernel_bandwidth = options9[8];
+  TSDFRangeDataInserter2D(o).Insert(Vec3f{origin_xy[0], origin_xy[1], 0.f}, ToCloud(returns_xyz, num_returns),
+                                    static_cast<TSDF2D*>(grid));
+}
+void oracle_tsdf2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
+  const MapLimits& l = static_cast<TSDF2D*>(grid)->limits();
+  *nx = l.cell_limits.num_x_cells;
+  *ny = l.cell_limits.num_y_cells;
+  *max_x = l.max_x;
+  *max_y = l.max_y;
+  *res = l.resolution;
+}
+void oracle_tsdf2d_cells(void* grid, uint16_t* tsd_out, uint16_t* weight_out) {
+  const TSDF2D& t = *static_cast<TSDF2D*>(grid);
+  std::memcpy(tsd_out, t.tsd_cells().data(), sizeof(uint16_t) * t.tsd_cells().size());
+  std::memcpy(weight_out, t.weight_cells().data(), sizeof(uint16_t) * t.weight_cells().size());
+}
 // TSDValueConverter::TSDToValue / WeightToValue of n floats (for painting fixtures).
 void oracle_tsdf2d_values(float truncation_distance, float max_weight, const float* tsd,
                           const float* weight, int n, uint16_t* tsd_values, uint16_t* weight_values) {

@@ -27,6 +27,7 @@
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/2d/tsdf_2d.h"
+#include "cartographer/mapping/internal/2d/tsdf_range_data_inserter_2d.h"
 #include "cartographer/mapping/probability_values.h"
 #include "cartographer/sensor/point_cloud.h"
 #include "cartographer/transform/transform.h"
@@ -52,6 +53,8 @@ int LuaParameterDictionary::GetInt(const std::string&) { NoLua(); }
 bool LuaParameterDictionary::GetBool(const std::string&) { NoLua(); }
 int LuaParameterDictionary::GetNonNegativeInt(const std::string&) { NoLua(); }
 bool LuaParameterDictionary::HasKey(const std::string&) const { NoLua(); }
+std::unique_ptr<LuaParameterDictionary> LuaParameterDictionary::GetDictionary(const std::string&) { NoLua(); }
+LuaParameterDictionary::~LuaParameterDictionary() {}
 }  // namespace common
 }  // namespace cartographer
 
@@ -313,6 +316,40 @@ void oracle_grid2d_insert(void* grid, double hit_probability, double miss_probab
   rd.returns = ToCloud(returns_xyz, num_returns);
   rd.misses = ToCloud(misses_xyz, num_misses);
   carto::mapping::ProbabilityGridRangeDataInserter2D(o).Insert(rd, static_cast<GridHolder*>(grid)->grid.get());
+}
+// TSDFRangeDataInserter2D::Insert on a TSDF2D handle (GrowLimits included).  options9 =
+// {truncation_distance, maximum_weight, update_free_space, num_normal_samples, sample_radius,
+//  project_sdf_distance_to_scan_normal, update_weight_range_exponent,
+//  update_weight_angle_scan_normal_to_ray_kernel_bandwidth,
+//  update_weight_distance_cell_to_hit_kernel_bandwidth}.
+void oracle_tsdf2d_insert(void* grid, const double* options9, const float* origin_xy, const float* returns_xyz,
+                          int num_returns) {
+  carto::mapping::proto::TSDFRangeDataInserterOptions2D o;
+  o.set_truncation_distance(options9[0]);
+  o.set_maximum_weight(options9[1]);
+  o.set_update_free_space(options9[2] != 0.);
+  o.mutable_normal_estimation_options()->set_num_normal_samples(static_cast<int>(options9[3]));
+  o.mutable_normal_estimation_options()->set_sample_radius(static_cast<float>(options9[4]));
+  o.set_project_sdf_distance_to_scan_normal(options9[5] != 0.);
+  o.set_update_weight_range_exponent(static_cast<int>(options9[6]));
+  o.set_update_weight_angle_scan_normal_to_ray_kernel_bandwidth(options9[7]);
+  o.set_update_weight_distance_cell_to_hit_kernel_bandwidth(options9[8]);
+  carto::sensor::RangeData rd;
+  rd.origin = Eigen::Vector3f(origin_xy[0], origin_xy[1], 0.f);
+  rd.returns = ToCloud(returns_xyz, num_returns);
+  carto::mapping::TSDFRangeDataInserter2D(o).Insert(rd, static_cast<GridHolder*>(grid)->grid.get());
+}
+// TSD cells and weight cells of a TSDF2D handle (sizes from oracle_grid2d_info).
+void oracle_tsdf2d_cells(void* grid, uint16_t* tsd_out, uint16_t* weight_out) {
+  const carto::mapping::proto::Grid2D proto = static_cast<GridHolder*>(grid)->grid->ToProto();
+  for (int i = 0; i < proto.cells_size(); ++i) tsd_out[i] = static_cast<uint16_t>(proto.cells(i));
+  for (int i = 0; i < proto.tsdf_2d().weight_cells_size(); ++i) {
+    weight_out[i] = static_cast<uint16_t>(proto.tsdf_2d().weight_cells(i));
+  }
+}
+void oracle_grid2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res);
+void oracle_tsdf2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
+  oracle_grid2d_info(grid, nx, ny, max_x, max_y, res);
 }
 void oracle_grid2d_info(void* grid, int* nx, int* ny, double* max_x, double* max_y, double* res) {
   const carto::mapping::MapLimits& l = static_cast<GridHolder*>(grid)->grid->limits();

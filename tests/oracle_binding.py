@@ -115,6 +115,14 @@ def lib():
                                        C.c_float, C.c_float]
     L.oracle_tsdf2d_create.restype = C.c_void_p
     L.oracle_tsdf2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_tsdf2d_insert.argtypes = [C.c_void_p, np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS"), f32p, f32p,
+                                       C.c_int]
+    L.oracle_tsdf2d_insert.restype = None
+    L.oracle_tsdf2d_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.oracle_tsdf2d_info.restype = None
+    L.oracle_tsdf2d_cells.argtypes = [C.c_void_p, u16p, u16p]
+    L.oracle_tsdf2d_cells.restype = None
     L.oracle_tsdf2d_values.argtypes = [C.c_float, C.c_float, f32p, f32p, C.c_int, u16p, u16p]
     L.oracle_rt_match2d_tsdf.argtypes = L.oracle_rt_match2d.argtypes
     L.oracle_rt_match2d_tsdf.restype = C.c_double
@@ -477,3 +485,39 @@ def rt_match3d(grid, options4, initial_pose7, points):
                                     np.ascontiguousarray(initial_pose7, np.float32), pts.reshape(-1), len(pts),
                                     pose, C.byref(best), C.byref(num))
     return score, pose, best.value, num.value
+
+
+TSDF_INSERTER_DEFAULTS = {"truncation_distance": 0.3, "maximum_weight": 10.0, "update_free_space": False,
+                          "num_normal_samples": 4, "sample_radius": 0.5,
+                          "project_sdf_distance_to_scan_normal": True, "update_weight_range_exponent": 0,
+                          "update_weight_angle_scan_normal_to_ray_kernel_bandwidth": 0.5,
+                          "update_weight_distance_cell_to_hit_kernel_bandwidth": 0.5}
+
+
+def tsdf_inserter_options(opts=None):
+    """TSDFRangeDataInserterOptions2D (defaults of trajectory_builder_2d.lua:100-112) as 9 doubles."""
+    o = dict(TSDF_INSERTER_DEFAULTS)
+    o.update(opts or {})
+    return np.array([o["truncation_distance"], o["maximum_weight"], float(o["update_free_space"]),
+                     o["num_normal_samples"], o["sample_radius"], float(o["project_sdf_distance_to_scan_normal"]),
+                     o["update_weight_range_exponent"], o["update_weight_angle_scan_normal_to_ray_kernel_bandwidth"],
+                     o["update_weight_distance_cell_to_hit_kernel_bandwidth"]], np.float64)
+
+
+def _tsdf_insert(L, grid, origin, returns, opts):
+    r = np.ascontiguousarray(np.asarray(returns, np.float32).reshape(-1, 3))
+    L.oracle_tsdf2d_insert(grid.h, tsdf_inserter_options(opts), np.asarray(origin, np.float32)[:2].copy(), r, len(r))
+    nx, ny = C.c_int(), C.c_int()
+    mx, my, res = C.c_double(), C.c_double(), C.c_double()
+    L.oracle_tsdf2d_info(grid.h, C.byref(nx), C.byref(ny), C.byref(mx), C.byref(my), C.byref(res))
+    grid.nx, grid.ny, grid.max_x, grid.max_y = nx.value, ny.value, mx.value, my.value
+    tsd = np.empty((grid.ny, grid.nx), np.uint16)
+    weight = np.empty((grid.ny, grid.nx), np.uint16)
+    L.oracle_tsdf2d_cells(grid.h, tsd, weight)
+    grid.tsd_cells, grid.weight_cells = tsd, weight
+    return grid
+
+
+def tsdf_insert(grid, origin, returns, opts=None):
+    """TSDFRangeDataInserter2D::Insert on an OracleTsdf (it may grow); refreshes its cells and limits."""
+    return _tsdf_insert(lib(), grid, origin, returns, opts)

@@ -51,6 +51,14 @@ def lib():
                                        C.c_float, C.c_float]
     L.oracle_tsdf2d_create.restype = C.c_void_p
     L.oracle_tsdf2d_destroy.argtypes = [C.c_void_p]
+    L.oracle_tsdf2d_insert.argtypes = [C.c_void_p, np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS"), f32p, f32p,
+                                       C.c_int]
+    L.oracle_tsdf2d_insert.restype = None
+    L.oracle_tsdf2d_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.oracle_tsdf2d_info.restype = None
+    L.oracle_tsdf2d_cells.argtypes = [C.c_void_p, u16p, u16p]
+    L.oracle_tsdf2d_cells.restype = None
     L.oracle_fcsm2d_create.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
     L.oracle_fcsm2d_create.restype = C.c_void_p
     L.oracle_fcsm2d_destroy.argtypes = [C.c_void_p]
@@ -338,3 +346,9 @@ def rt_match3d(grid, options4, initial_pose7, points):
                                     np.ascontiguousarray(initial_pose7, np.float32), pts.reshape(-1), len(pts), pose,
                                     C.byref(best), C.byref(num))
     return score, pose
+
+
+def tsdf_insert(grid, origin, returns, opts=None):
+    """TSDFRangeDataInserter2D::Insert on a RefTsdf (it may grow); sets grid.tsd_cells / weight_cells / limits."""
+    import oracle_binding as ob
+    return ob._tsdf_insert(lib(), grid, origin, returns, opts)

@@ -199,3 +199,32 @@ def test_range_data_inserter_of_the_oracle_equals_the_reference():
             assert (og.nx, og.ny, og.max_x, og.max_y) == (rg.nx, rg.ny, max_x, max_y)
             assert og.cells.tobytes() == cells.tobytes()
         assert (og.cells > 0).sum() > (1000 if free_space else 250)
+
+
+@pytest.mark.parametrize("opts", [
+    {},                                                                # trajectory_builder_2d.lua defaults
+    {"update_free_space": True},
+    {"project_sdf_distance_to_scan_normal": False, "update_weight_angle_scan_normal_to_ray_kernel_bandwidth": 0.0},
+    {"update_weight_range_exponent": 2, "update_weight_distance_cell_to_hit_kernel_bandwidth": 0.0},
+    {"truncation_distance": 0.15, "maximum_weight": 3.0, "num_normal_samples": 8, "sample_radius": 0.2},
+])
+def test_tsdf_range_data_inserter_of_the_oracle_equals_the_reference(opts):
+    """TSDFRangeDataInserter2D with its normal estimation: five scans of a synthetic
+    office into a small TSDF2D that has to grow; TSD cells, weight cells and limits after every scan."""
+    w = synth.World(200, 180, seed=33)
+    trunc = opts.get("truncation_distance", 0.3)
+    maxw = opts.get("maximum_weight", 10.0)
+    zero = np.zeros((40, 40), np.uint16)
+    og = ob.OracleTsdf(zero, zero, 0.05, 1.0, 1.0, trunc, maxw)
+    rg = rb.RefTsdf(zero, zero, 0.05, 1.0, 1.0, trunc, maxw)
+    for k in range(5):
+        pose, pts = synth.make_scan(w, 400 + k, max_range=6.0)
+        c, s = np.cos(pose[2]), np.sin(pose[2])
+        world = np.stack([pose[0] + c * pts[:, 0] - s * pts[:, 1], pose[1] + s * pts[:, 0] + c * pts[:, 1],
+                          np.zeros(len(pts))], axis=1).astype(np.float32)
+        ob.tsdf_insert(og, pose[:2], world, opts)
+        rb.tsdf_insert(rg, pose[:2], world, opts)
+        assert (og.nx, og.ny, og.max_x, og.max_y) == (rg.nx, rg.ny, rg.max_x, rg.max_y)
+        assert og.tsd_cells.tobytes() == rg.tsd_cells.tobytes()
+        assert og.weight_cells.tobytes() == rg.weight_cells.tobytes()
+    assert (og.weight_cells > 0).sum() > 1500 and og.nx > 40
