@@ -61,6 +61,8 @@ ABI_SYMBOLS = [
     "csm_discretize3d", "csm_rt_match3d_batch", "csm_ceres_match2d_batch", "csm_grid2d_create", "csm_grid2d_insert",
     "csm_grid2d_download", "csm_grid2d_cells_dev", "csm_grid2d_destroy",
     "csm_grid2d_broadcast_dev", "csm_stack2d_broadcast",
+    "csm_tsdfgrid2d_create", "csm_tsdfgrid2d_insert", "csm_tsdfgrid2d_download", "csm_tsdfgrid2d_tsd_dev",
+    "csm_tsdfgrid2d_weight_dev", "csm_tsdfgrid2d_destroy",
     "csm_hgrid3d_create", "csm_hgrid3d_insert", "csm_hgrid3d_export", "csm_hgrid3d_box", "csm_hgrid3d_destroy",
     "csm_stack3d_build_from_hgrid",
     "csm_measure_gather_ceiling", "csm_ctx_get_depth_profile", "csm_precomputation_grid2d",
@@ -846,3 +848,41 @@ def grid3d_resident_stack_check(ctx, resolution, xyz, values, origins, returns, 
         ctx.h, resolution, xyz.reshape(-1), values, len(values),
         np.array([hit_probability, miss_probability, num_free_space_voxels], np.float64), n,
         np.ascontiguousarray(origins, np.float32).reshape(-1), pts.reshape(-1), offsets, depth, full_resolution_depth)
+
+
+def tsdf_insert(ctx, grid, origins, returns, options9, resident=False):
+    """TSDFRangeDataInserter2D::Insert of every scan (origins[i] = (x, y), returns[i] = [n, 3]) into a
+    TsdfGrid (it may grow).  options9: the 9 doubles of TSDFRangeDataInserterOptions2D (see
+    host_capi.cc).  Returns (tsd cells, weight cells) uint16 [ny, nx] and (max_x, max_y)."""
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    L.csmh_tsdf_insert.argtypes = [C.c_void_p, C.c_void_p, f64p, C.c_int, f32p, f32p, i64p, C.c_int]
+    L.csmh_grid_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                 C.POINTER(C.c_double)]
+    L.csmh_grid_info.restype = None
+    L.csmh_grid_cells.argtypes = [C.c_void_p, u16p]
+    L.csmh_grid_cells.restype = None
+    L.csmh_grid_weight_cells.argtypes = [C.c_void_p, u16p]
+    L.csmh_grid_weight_cells.restype = None
+    n = len(origins)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    for i, r in enumerate(returns):
+        offsets[i + 1] = offsets[i] + len(r)
+    pts = np.ascontiguousarray(np.concatenate([np.asarray(r, np.float32).reshape(-1, 3) for r in returns], axis=0),
+                               dtype=np.float32)
+    rc = L.csmh_tsdf_insert(ctx.h, grid.h, np.ascontiguousarray(options9, np.float64), n,
+                            np.ascontiguousarray(np.asarray(origins, np.float32)[:, :2]).reshape(-1), pts.reshape(-1),
+                            offsets, 1 if resident else 0)
+    assert rc == 0
+    nx, ny = C.c_int(), C.c_int()
+    mx, my = C.c_double(), C.c_double()
+    L.csmh_grid_info(grid.h, C.byref(nx), C.byref(ny), C.byref(mx), C.byref(my))
+    grid.nx, grid.ny = nx.value, ny.value
+    tsd = np.empty((grid.ny, grid.nx), np.uint16)
+    weight = np.empty((grid.ny, grid.nx), np.uint16)
+    L.csmh_grid_cells(grid.h, tsd)
+    L.csmh_grid_weight_cells(grid.h, weight)
+    return tsd, weight, (mx.value, my.value)

@@ -360,8 +360,14 @@ class Grid2D {
           cells[x_offset + stride * y_offset + j + i * stride] = correspondence_cost_cells_[j + i * nx];
       correspondence_cost_cells_.swap(cells);
       limits_ = grown;
+      Grown(nx, ny, x_offset, y_offset);
     }
   }
+
+ protected:
+  // Called after every doubling with the old size and the offset of the old cells in the new grid,
+  // for grids that carry a second cell array (TSDF2D::GrowLimits, tsdf_2d.cc:100-105).
+  virtual void Grown(int /*old_nx*/, int /*old_ny*/, int /*x_offset*/, int /*y_offset*/) {}
 
  private:
   MapLimits limits_;
@@ -464,6 +470,15 @@ class TSDF2D : public Grid2D {
   const std::vector<uint16>& weight_cells() const { return weight_cells_; }
   std::vector<uint16>* mutable_weight_cells() { return &weight_cells_; }
   const TSDValueConverter& value_converter() const { return value_converter_; }
+
+ protected:
+  void Grown(const int nx, const int ny, const int x_offset, const int y_offset) override {
+    const int stride = 2 * nx;
+    std::vector<uint16> cells(static_cast<size_t>(4) * nx * ny, TSDValueConverter::getUnknownWeightValue());
+    for (int i = 0; i < ny; ++i)
+      for (int j = 0; j < nx; ++j) cells[x_offset + stride * y_offset + j + i * stride] = weight_cells_[j + i * nx];
+    weight_cells_.swap(cells);
+  }
 
  private:
   TSDValueConverter value_converter_;

@@ -8,6 +8,7 @@
 #include <memory>
 #include <mutex>
 
+#include "cartographer/mapping/internal/2d/tsdf_range_data_inserter_2d.h"
 #include "cartographer/io/grid_proto_reader.h"
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/2d/probability_grid_range_data_inserter_2d.h"
@@ -67,6 +68,49 @@ void* csmh_tsdf_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, 
   return h;
 }
 void csmh_grid_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+
+// TSDFRangeDataInserter2D on a TSDF grid handle (csmh_tsdf_create / csmh_grid_from_proto); the grid
+// may grow.  options9 = {truncation_distance, maximum_weight, update_free_space, num_normal_samples,
+// sample_radius, project_sdf_distance_to_scan_normal, update_weight_range_exponent, angle kernel
+// bandwidth, distance kernel bandwidth}.  resident == 0: one reference-signature Insert per scan;
+// != 0: grown for every scan first, then one DeviceGrid, every scan inserted, downloaded once.
+int csmh_tsdf_insert(void* ctx, void* grid, const double* options9, int num, const float* origins_xy,
+                     const float* returns_xyz, const int64_t* offsets, int resident) {
+  DeviceContext* context = static_cast<DeviceContext*>(ctx);
+  mapping::Grid2D* g = static_cast<GridHolder*>(grid)->grid.get();
+  if (g->GetGridType() != mapping::GridType::TSDF) return -1;
+  mapping::TSDF2D* tsdf = static_cast<mapping::TSDF2D*>(g);
+  mapping::proto::TSDFRangeDataInserterOptions2D o;
+  o.set_truncation_distance(options9[0]);
+  o.set_maximum_weight(options9[1]);
+  o.set_update_free_space(options9[2] != 0.);
+  o.mutable_normal_estimation_options()->set_num_normal_samples(static_cast<int>(options9[3]));
+  o.mutable_normal_estimation_options()->set_sample_radius(static_cast<float>(options9[4]));
+  o.set_project_sdf_distance_to_scan_normal(options9[5] != 0.);
+  o.set_update_weight_range_exponent(static_cast<int>(options9[6]));
+  o.set_update_weight_angle_scan_normal_to_ray_kernel_bandwidth(options9[7]);
+  o.set_update_weight_distance_cell_to_hit_kernel_bandwidth(options9[8]);
+  const mapping::TSDFRangeDataInserter2D inserter(o, context);
+  std::vector<sensor::RangeData> scans(num);
+  for (int s = 0; s < num; ++s) {
+    scans[s].origin = sensor::Vector3f(origins_xy[2 * s], origins_xy[2 * s + 1], 0.f);
+    for (int64_t i = offsets[s]; i < offsets[s + 1]; ++i)
+      scans[s].returns.push_back({sensor::Vector3f(returns_xyz[3 * i], returns_xyz[3 * i + 1], returns_xyz[3 * i + 2])});
+  }
+  if (resident) {
+    std::vector<const sensor::RangeData*> list;
+    for (const sensor::RangeData& rd : scans) {
+      mapping::TSDFRangeDataInserter2D::GrowAsNeeded(rd, static_cast<float>(o.truncation_distance()), tsdf);
+      list.push_back(&rd);
+    }
+    mapping::TSDFRangeDataInserter2D::DeviceGrid device_grid(context, *tsdf);
+    inserter.Insert(list, *tsdf, &device_grid);
+    device_grid.Download(tsdf);
+  } else {
+    for (const sensor::RangeData& rd : scans) inserter.Insert(rd, tsdf);
+  }
+  return 0;
+}
 
 // Grid ingestion: a serialized proto::Grid2D message -> a grid handle (ProbabilityGrid or TSDF2D,
 // whichever the message holds) every matcher entry point takes.  info6 = {num_x, num_y,

@@ -337,6 +337,45 @@ int csm_grid2d_download(csm_ctx* ctx, const csm_grid2d* grid, uint16_t* cells_ou
 const uint16_t* csm_grid2d_cells_dev(const csm_grid2d* grid);
 void csm_grid2d_destroy(csm_ctx* ctx, csm_grid2d* grid);
 
+/* ---- TSDFRangeDataInserter2D::Insert on a device-resident TSDF2D ------
+ * Replaces cartographer/mapping/internal/2d/tsdf_range_data_inserter_2d.cc:167-239 (InsertHit,
+ * UpdateCell) with ray_to_pixel_mask.cc:25-170 and TSDF2D::SetCell / GetTSDAndWeight /
+ * CellIsUpdated / FinishUpdate (mapping/internal/2d/tsdf_2d.cc:44-98).  The host keeps what is per
+ * return and goes through libm -- the bearing sort (:71-90,146-150), EstimateNormals
+ * (normal_estimation_2d.cc), cosf / sinf of the normal, the range and angle weight factors
+ * (:189-203) -- and GrowAsNeeded (:33-48); the device owns every per-cell step: a cell is updated by
+ * the first return, in the given order, whose ray crosses it with a non-zero weight.  Cells are
+ * bit-identical to the reference's up to the per-cell double-precision exp of the distance kernel
+ * (see csrc/csm_insert_tsdf2d.cu). */
+typedef struct csm_tsdfgrid2d csm_tsdfgrid2d;
+typedef struct {
+  double max_x, max_y, resolution;   /* MapLimits of the grid                                  */
+  float origin_x, origin_y;          /* range_data.origin                                      */
+  int32_t num_returns;
+  int32_t update_free_space;         /* TSDFRangeDataInserterOptions2D                         */
+  const float* hits_xy;              /* num_returns x (x, y), in insertion order               */
+  const float* normal_cos_sin;       /* num_returns x (cosf(normal), sinf(normal)); may be NULL */
+                                     /* unless project_sdf_distance_to_scan_normal             */
+  const float* hit_weight;           /* weight_factor_range * weight_factor_angle_ray_normal   */
+  float truncation_distance, maximum_weight;
+  float distance_kernel_bandwidth;   /* update_weight_distance_cell_to_hit_kernel_bandwidth; 0: off */
+  int32_t project_sdf_distance_to_scan_normal;
+  float min_tsd, max_tsd, tsd_resolution;      /* TSDValueConverter (tsd_value_converter.h)     */
+  float max_weight_value, weight_resolution;   /* its max weight and 32766 / max weight          */
+  int32_t pad;
+} csm_tsdf_range_data2d;
+
+/* tsd_cells / weight_cells may be NULL (all unknown); the tables are the converter's 65536-entry
+ * value-to-TSD and value-to-weight tables. */
+int csm_tsdfgrid2d_create(csm_ctx* ctx, const uint16_t* tsd_cells, const uint16_t* weight_cells, int num_x,
+                          int num_y, const float* value_to_tsd, const float* value_to_weight,
+                          csm_tsdfgrid2d** out);
+int csm_tsdfgrid2d_insert(csm_ctx* ctx, csm_tsdfgrid2d* grid, const csm_tsdf_range_data2d* scans, int num_scans);
+int csm_tsdfgrid2d_download(csm_ctx* ctx, const csm_tsdfgrid2d* grid, uint16_t* tsd_out, uint16_t* weight_out);
+const uint16_t* csm_tsdfgrid2d_tsd_dev(const csm_tsdfgrid2d* grid);
+const uint16_t* csm_tsdfgrid2d_weight_dev(const csm_tsdfgrid2d* grid);
+void csm_tsdfgrid2d_destroy(csm_ctx* ctx, csm_tsdfgrid2d* grid);
+
 /* ==== 3D path ======================================================================
  * Citations relative to cartographer/mapping/internal/3d/scan_matching/:
  *   FCSM3D = fast_correlative_scan_matcher_3d.{h,cc}
