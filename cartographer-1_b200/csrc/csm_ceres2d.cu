@@ -476,13 +476,13 @@ extern "C" int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs
   size_t n_pts = 0, grid_bytes = 0, table_bytes = 0;
   for (int i = 0; i < num_jobs; ++i) {
     const csm_ceres_job2d& in = jobs[i];
-    CSM_REQUIRE(in.cells && in.cost_table && in.points_xyz, "ceres job has a NULL array");
+    CSM_REQUIRE((in.cells || in.cells_dev) && in.cost_table && in.points_xyz, "ceres job has a NULL array");
     CSM_REQUIRE(in.num_points >= 1 && in.num_x >= 1 && in.num_y >= 1 && in.resolution > 0.,
                 "ceres job sizes out of range");
     CSM_REQUIRE(in.occupied_space_weight > 0. && in.translation_weight > 0. && in.rotation_weight > 0.,
                 "ceres weights must be positive (ceres_scan_matcher_2d.cc:75,94,99)");
     CSM_REQUIRE(in.max_num_iterations >= 0, "max_num_iterations must not be negative");
-    if (!grid_at.count(in.cells)) {
+    if (in.cells_dev == nullptr && !grid_at.count(in.cells)) {
       grid_at[in.cells] = grid_bytes;
       grid_size[in.cells] = sizeof(uint16_t) * static_cast<size_t>(in.num_x) * in.num_y;
       grid_bytes += up(grid_size[in.cells]);
@@ -537,7 +537,8 @@ extern "C" int csm_ceres_match2d_batch(csm_ctx* ctx, const csm_ceres_job2d* jobs
     const csm_ceres_job2d& in = jobs[i];
     CeresJobDev& j = dev[i];
     memcpy(pin + o_pts + sizeof(float) * 3 * j.pts_off, in.points_xyz, sizeof(float) * 3 * j.n);
-    j.cells = reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
+    j.cells = in.cells_dev != nullptr ? in.cells_dev
+                                      : reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.cells]);
     j.cost_table = reinterpret_cast<const float*>(base + o_tab + table_at[in.cost_table]);
     j.weight_cells = in.weight_cells
                          ? reinterpret_cast<const uint16_t*>(base + o_grid + grid_at[in.weight_cells])

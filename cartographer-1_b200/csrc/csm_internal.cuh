@@ -166,6 +166,7 @@ struct csm_stack2d {
   csm::StackDev* dev = nullptr;           // device-resident descriptor
   size_t bytes = 0;
   uint8_t* q_lut_dev = nullptr;  // 65536 bytes
+  uint16_t* cells_dev = nullptr;  // the grid's uint16 cells as given to the build (csm_stack2d_cells_dev)
 };
 
 #endif  // CSM_INTERNAL_CUH_

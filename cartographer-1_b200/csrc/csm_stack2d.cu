@@ -1060,7 +1060,11 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
   // levels | quads | descriptor | quantisation table, one pooled block
   const size_t o_dev = off, o_lut = o_dev + ((sizeof(csm::StackDev) + 255) & ~static_cast<size_t>(255));
   void* block = nullptr;
-  if (ctx->pool.take(false, o_lut + 65536, &block, &s->base_cap) != CSM_OK) {
+  // ... | the grid's own uint16 cells: the refinement that follows a found match
+  // (CeresScanMatcher2D) interpolates them, and they are already here for the build.
+  const size_t o_cells = o_lut + 65536;
+  const size_t cells_bytes = (sizeof(uint16_t) * static_cast<size_t>(num_x) * num_y + 255) & ~static_cast<size_t>(255);
+  if (ctx->pool.take(false, o_cells + cells_bytes, &block, &s->base_cap) != CSM_OK) {
     csm::set_error("allocation of a %zu-byte stack failed: %s", s->bytes,
                    cudaGetErrorString(cudaGetLastError()));
     delete s;
@@ -1069,6 +1073,7 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
   s->base = static_cast<uint8_t*>(block);
   s->dev = reinterpret_cast<csm::StackDev*>(s->base + o_dev);
   s->q_lut_dev = s->base + o_lut;
+  s->cells_dev = reinterpret_cast<uint16_t*>(s->base + o_cells);
   s->host_view.num_x = num_x;
   s->host_view.num_y = num_y;
   s->host_view.depth = depth;
@@ -1094,6 +1099,11 @@ int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, in
   int rc = create_stack(ctx, num_x, num_y, q_lut, depth, out);
   if (rc != CSM_OK) return rc;
   rc = launch_build(ctx, *out, cells_dev);
+  if (rc == CSM_OK && cudaMemcpyAsync((*out)->cells_dev, cells_dev, sizeof(uint16_t) * static_cast<size_t>(num_x) * num_y,
+                                      cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess) {
+    csm::set_error("keeping the cells failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = CSM_ERR_CUDA;
+  }
   if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
     csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
     rc = CSM_ERR_CUDA;
@@ -1118,6 +1128,11 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
     rc = CSM_ERR_CUDA;
   }
   if (rc == CSM_OK) rc = launch_build(ctx, *out, ctx->tmp0.as<uint16_t>());
+  if (rc == CSM_OK && cudaMemcpyAsync((*out)->cells_dev, ctx->tmp0.p, bytes, cudaMemcpyDeviceToDevice, ctx->stream) !=
+                          cudaSuccess) {
+    csm::set_error("keeping the cells failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = CSM_ERR_CUDA;
+  }
   if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
     csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
     rc = CSM_ERR_CUDA;
@@ -1185,7 +1200,12 @@ int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* ce
   CSM_REQUIRE(ctx != nullptr && stack != nullptr && cells_dev != nullptr, "NULL argument");
   CSM_REQUIRE(stack->device == ctx->device, "stack lives on another device");
   CSM_CUDA(cudaSetDevice(ctx->device));
-  return launch_build(ctx, stack, cells_dev);
+  const int rc = launch_build(ctx, stack, cells_dev);
+  if (rc == CSM_OK && cells_dev != stack->cells_dev) {  // keep csm_stack2d_cells_dev in step with the levels
+    CSM_CUDA(cudaMemcpyAsync(stack->cells_dev, cells_dev, sizeof(uint16_t) * static_cast<size_t>(stack->num_x) * stack->num_y,
+                             cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  return rc;
 }
 
 int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* s, int level, uint8_t* out, int* wide_x,
@@ -1221,6 +1241,7 @@ int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* s, int level, uint32_t* ou
 }
 
 int csm_stack2d_depth(const csm_stack2d* s) { return s ? s->depth : 0; }
+const uint16_t* csm_stack2d_cells_dev(const csm_stack2d* s) { return s ? s->cells_dev : nullptr; }
 size_t csm_stack2d_device_bytes(const csm_stack2d* s) { return s ? s->bytes + 65536 : 0; }
 
 void csm_stack2d_destroy(csm_ctx* ctx, csm_stack2d* s) {

@@ -60,6 +60,7 @@ std::vector<CeresScanMatcher2D::Answer> CeresScanMatcher2D::MatchBatch(
     csm_ceres_job2d& job = jobs[i];
     std::memset(&job, 0, sizeof(job));
     job.cells = q.grid->correspondence_cost_cells().data();
+    job.cells_dev = q.device_cells;
     job.num_x = limits.cell_limits().num_x_cells;
     job.num_y = limits.cell_limits().num_y_cells;
     job.cost_table = q.grid->value_to_correspondence_cost_table().data();

@@ -45,6 +45,10 @@ class CeresScanMatcher2D {
     transform::Rigid2d initial_pose_estimate;
     const sensor::PointCloud* point_cloud = nullptr;
     const Grid2D* grid = nullptr;
+    // Optional: the grid's cells already resident on the matcher's device (the submap's
+    // precomputation stack keeps them, FastCorrelativeScanMatcher2D::device_cells()); then the
+    // batch uploads nothing for this grid.  `grid` still supplies limits and the value table.
+    const uint16* device_cells = nullptr;
   };
   struct Answer {
     transform::Rigid2d pose_estimate;

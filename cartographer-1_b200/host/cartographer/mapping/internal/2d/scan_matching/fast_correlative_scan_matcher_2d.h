@@ -183,6 +183,9 @@ class FastCorrelativeScanMatcher2D {
   };
 
   const csm_stack2d* stack() const { return stack_; }
+  // The grid's uint16 cells, resident on device() beside the stack (for CeresScanMatcher2D::Query).
+  const uint16* device_cells() const { return csm_stack2d_cells_dev(stack_); }
+  int device() const { return device_; }
   const MapLimits& limits() const { return limits_; }
   DeviceContext* context() const { return context_; }
 

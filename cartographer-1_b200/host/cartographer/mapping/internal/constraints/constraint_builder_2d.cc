@@ -345,6 +345,8 @@ void ConstraintBuilder2D::RunFlush(const std::vector<PendingSearch>& searches,
         q.initial_pose_estimate = answers[i].pose_estimate;
         q.point_cloud = &searches[i].constant_data->filtered_gravity_aligned_point_cloud;
         q.grid = grid_of[i];
+        // The submap's stack keeps the grid's cells on this device: the refinement reads them there.
+        if (matcher_of[i] && matcher_of[i]->device() == ctx->device()) q.device_cells = matcher_of[i]->device_cells();
         refine.push_back(q);
         which.push_back(i);
       }

@@ -118,6 +118,9 @@ int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* stack, int level, uint8_t
 int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* stack, int level, uint32_t* out, int* in,
                      int* jn);
 int csm_stack2d_depth(const csm_stack2d* stack);
+/* The grid's uint16 cells as given to the last build, resident beside the levels (what the
+ * refinement after a found match interpolates: csm_ceres_job2d::cells_dev). */
+const uint16_t* csm_stack2d_cells_dev(const csm_stack2d* stack);
 size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
 /* `ctx` may be NULL or a context that no longer exists: the stack's device block goes
  * back to the block pool of `ctx` when that is still a live context on the stack's
@@ -296,6 +299,10 @@ typedef struct {
   const uint16_t* weight_cells;
   const float* weight_table;        /* 65536 floats                                   */
   double truncation_distance;       /* Grid2D::GetMaxCorrespondenceCost of a TSDF2D   */
+  /* The same cells already resident on the context's device (csm_stack2d_cells_dev of the submap's
+   * stack, csm_grid2d_cells_dev of a live grid): then `cells` may be NULL and nothing is uploaded
+   * for the grid (2 MB per 1000 x 1000 submap and batch otherwise). */
+  const uint16_t* cells_dev;
 } csm_ceres_job2d;
 
 typedef struct {
