@@ -51,7 +51,7 @@ ABI_SYMBOLS = [
     "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
     "csm_ctx_synchronize", "csm_ctx_stream", "csm_ctx_set_profiling", "csm_ctx_get_profile",
     "csm_ctx_get_tile_histogram", "csm_stack2d_build", "csm_stack2d_build_dev",
-    "csm_stack2d_rebuild_dev", "csm_stack2d_cells_dev", "csm_stack2d_level", "csm_stack2d_quad", "csm_stack2d_depth",
+    "csm_stack2d_rebuild_dev", "csm_stack2d_cells_dev", "csm_ctx_set_keep_cells", "csm_stack2d_level", "csm_stack2d_quad", "csm_stack2d_depth",
     "csm_stack2d_device_bytes", "csm_stack2d_destroy", "csm_match2d_batch",
     "csm_batch2d_upload", "csm_batch2d_run", "csm_batch2d_fetch", "csm_batch2d_destroy",
     "csm_discretize2d", "csm_rt_match2d_batch", "csm_ctx_launch_count", "csm_measure_gather_rate",

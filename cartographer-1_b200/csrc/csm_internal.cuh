@@ -120,6 +120,7 @@ struct csm_ctx {
   // Optional per-phase CUDA-event timing of csm_batch2d_run (csm_ctx_set_profiling).
   static constexpr int kPhases = 5;  // discretize, score_top, dive, expand, phase2
   int profiling = 0;  // 0 off, 1 phase events, 2 + tile histogram
+  int keep_cells = 1;  // stack builds leave the grid's cells beside the levels (csm_ctx_set_keep_cells)
   double phase_ms[kPhases] = {0, 0, 0, 0, 0};
   double phase_scored[kPhases] = {0, 0, 0, 0, 0};  // candidate scores evaluated per phase
   int profiled_runs = 0;

@@ -33,7 +33,7 @@ constexpr int kThreads = 256;
 // blockDim = (words per pass, rows per block); grid = (passes, row groups).
 __global__ void __launch_bounds__(kThreads)
 k_stack_level0(const uint16_t* __restrict__ cells, const uint8_t* __restrict__ q_lut,
-               uint8_t* __restrict__ out, int num_x, int num_y, int pitch) {
+               uint8_t* __restrict__ out, int num_x, int num_y, int pitch, uint16_t* __restrict__ keep) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
   if (y >= num_y || k >= (pitch >> 2)) return;
@@ -43,13 +43,21 @@ k_stack_level0(const uint16_t* __restrict__ cells, const uint8_t* __restrict__ q
   uint32_t w = 0u;
   if ((row & 3) == 0 && x + 3 < num_x) {
     const uint2 v = __ldg(reinterpret_cast<const uint2*>(crow + x));
+    if (keep != nullptr) *reinterpret_cast<uint2*>(keep + row + x) = v;  // csm_stack2d_cells_dev
     const uint32_t b0 = __ldg(q_lut + (v.x & 0x7FFFu)), b1 = __ldg(q_lut + ((v.x >> 16) & 0x7FFFu));
     const uint32_t b2 = __ldg(q_lut + (v.y & 0x7FFFu)), b3 = __ldg(q_lut + ((v.y >> 16) & 0x7FFFu));
     w = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
   } else {
     uint32_t c[4];
 #pragma unroll
-    for (int b = 0; b < 4; ++b) c[b] = x + b < num_x ? (__ldg(crow + x + b) & 0x7FFFu) : 0x10000u;
+    for (int b = 0; b < 4; ++b) {
+      c[b] = 0x10000u;
+      if (x + b < num_x) {
+        const uint16_t raw = __ldg(crow + x + b);
+        if (keep != nullptr) keep[row + x + b] = raw;
+        c[b] = raw & 0x7FFFu;
+      }
+    }
 #pragma unroll
     for (int b = 0; b < 4; ++b)
       if (c[b] != 0x10000u) w |= static_cast<uint32_t>(__ldg(q_lut + c[b])) << (8 * b);
@@ -801,8 +809,10 @@ void launch_level0(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   const int bx = std::min(kThreads, (((pw + passes - 1) / passes) + 31) & ~31);
   const int by = std::max(1, kThreads / bx);
   const dim3 grid((pw + bx - 1) / bx, (s->num_y + by - 1) / by);
+  // The level-0 pass reads every cell anyway: it also leaves the copy the stack keeps.
   ++ctx->launches, k_stack_level0<<<grid, dim3(bx, by), 0, ctx->stream>>>(
-      cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0]);
+      cells_dev, s->q_lut_dev, s->base + s->level_off[0], s->num_x, s->num_y, s->level_pitch[0],
+      ctx->keep_cells && cells_dev != s->cells_dev ? s->cells_dev : nullptr);
 }
 
 int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
@@ -1099,11 +1109,6 @@ int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, in
   int rc = create_stack(ctx, num_x, num_y, q_lut, depth, out);
   if (rc != CSM_OK) return rc;
   rc = launch_build(ctx, *out, cells_dev);
-  if (rc == CSM_OK && cudaMemcpyAsync((*out)->cells_dev, cells_dev, sizeof(uint16_t) * static_cast<size_t>(num_x) * num_y,
-                                      cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess) {
-    csm::set_error("keeping the cells failed: %s", cudaGetErrorString(cudaGetLastError()));
-    rc = CSM_ERR_CUDA;
-  }
   if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
     csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
     rc = CSM_ERR_CUDA;
@@ -1128,11 +1133,6 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
     rc = CSM_ERR_CUDA;
   }
   if (rc == CSM_OK) rc = launch_build(ctx, *out, ctx->tmp0.as<uint16_t>());
-  if (rc == CSM_OK && cudaMemcpyAsync((*out)->cells_dev, ctx->tmp0.p, bytes, cudaMemcpyDeviceToDevice, ctx->stream) !=
-                          cudaSuccess) {
-    csm::set_error("keeping the cells failed: %s", cudaGetErrorString(cudaGetLastError()));
-    rc = CSM_ERR_CUDA;
-  }
   if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
     csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
     rc = CSM_ERR_CUDA;
@@ -1175,7 +1175,7 @@ int csm_precomputation_grid2d(csm_ctx* ctx, const uint16_t* cells, int num_x, in
     const int bx = std::min(kThreads, (pw + 31) & ~31), by = std::max(1, kThreads / bx);
     const dim3 grid((pw + bx - 1) / bx, (num_y + by - 1) / by);
     ++ctx->launches, k_stack_level0<<<grid, dim3(bx, by), 0, st>>>(d_cells, d_lut, buf[0], num_x, num_y,
-                                                                   static_cast<int>(pitch));
+                                                                   static_cast<int>(pitch), nullptr);
   }
   int have = 1, cur = 0;  // window width of buf[cur]
   auto widen = [&](int h) {  // width `have` -> `have + h` (h <= have)
@@ -1200,12 +1200,7 @@ int csm_stack2d_rebuild_dev(csm_ctx* ctx, csm_stack2d* stack, const uint16_t* ce
   CSM_REQUIRE(ctx != nullptr && stack != nullptr && cells_dev != nullptr, "NULL argument");
   CSM_REQUIRE(stack->device == ctx->device, "stack lives on another device");
   CSM_CUDA(cudaSetDevice(ctx->device));
-  const int rc = launch_build(ctx, stack, cells_dev);
-  if (rc == CSM_OK && cells_dev != stack->cells_dev) {  // keep csm_stack2d_cells_dev in step with the levels
-    CSM_CUDA(cudaMemcpyAsync(stack->cells_dev, cells_dev, sizeof(uint16_t) * static_cast<size_t>(stack->num_x) * stack->num_y,
-                             cudaMemcpyDeviceToDevice, ctx->stream));
-  }
-  return rc;
+  return launch_build(ctx, stack, cells_dev);  // level 0 refreshes csm_stack2d_cells_dev too
 }
 
 int csm_stack2d_level(csm_ctx* ctx, const csm_stack2d* s, int level, uint8_t* out, int* wide_x,
@@ -1237,6 +1232,12 @@ int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* s, int level, uint32_t* ou
                              ctx->stream));
     CSM_CUDA(cudaStreamSynchronize(ctx->stream));
   }
+  return CSM_OK;
+}
+
+int csm_ctx_set_keep_cells(csm_ctx* ctx, int enabled) {
+  CSM_REQUIRE(ctx != nullptr, "ctx must not be NULL");
+  ctx->keep_cells = enabled != 0;
   return CSM_OK;
 }
 

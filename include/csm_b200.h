@@ -121,6 +121,10 @@ int csm_stack2d_depth(const csm_stack2d* stack);
 /* The grid's uint16 cells as given to the last build, resident beside the levels (what the
  * refinement after a found match interpolates: csm_ceres_job2d::cells_dev). */
 const uint16_t* csm_stack2d_cells_dev(const csm_stack2d* stack);
+/* Stack builds on `ctx` write that copy from their level-0 pass (default on).  Off: builds do
+ * exactly the work of PrecomputationGridStack2D and csm_stack2d_cells_dev is stale or unset --
+ * what bench.py's C4 record times. */
+int csm_ctx_set_keep_cells(csm_ctx* ctx, int enabled);
 size_t csm_stack2d_device_bytes(const csm_stack2d* stack);
 /* `ctx` may be NULL or a context that no longer exists: the stack's device block goes
  * back to the block pool of `ctx` when that is still a live context on the stack's

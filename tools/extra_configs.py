@@ -181,6 +181,18 @@ def c4(pkg, ctx, torch, hbm_peak):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     depth = 7
     out = {"unit": "GB/s", "sizes": {}}
+    # C4 is the reference's PrecomputationGridStack2D build: the copy of the cells that builds
+    # otherwise leave for the refinement stage is switched off for this record.
+    abi.csm_ctx_set_keep_cells(C.c_void_p(ctx.raw), 0)
+    try:
+        return _c4_sizes(pkg, ctx, torch, hbm_peak, abi, stream, flush, depth, out)
+    finally:
+        abi.csm_ctx_set_keep_cells(C.c_void_p(ctx.raw), 1)
+
+
+def _c4_sizes(pkg, ctx, torch, hbm_peak, abi, stream, flush, depth, out):
+    import oracle_binding as ob
+    import synth
     for size in (400, 1000, 2000):
         w = synth.World(size, size, seed=4000 + size)
         g = pkg.Grid(w.cells, w.res, w.max_x, w.max_y)
