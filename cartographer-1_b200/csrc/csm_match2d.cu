@@ -1030,16 +1030,33 @@ k_place(const unsigned int* __restrict__ tmp, const NodeBlock* __restrict__ bloc
     if (tmp_path != nullptr)
       for (unsigned int t = lane; t < nb.count; t += kWarp) node_path[dst + t] = tmp_path[nb.src + t];
   }
-  // Work items: one THREAD per bucket (most of the 126 k buckets of a C3 step are empty or
-  // hold a handful of items; a warp per bucket spent its time on the empty ones).
+  // Work items.  A lane looks at one bucket: most of the 126 k buckets of a C3 step are empty or
+  // hold a handful of items, and a lane writes the first two of its bucket itself; a bucket with
+  // more (thousands at the dense depths, where one lane writing them all held its warp for the
+  // whole launch) is then written by the 32 lanes together.
+  const unsigned int group = blockIdx.x * blockDim.x + (threadIdx.x & ~31u);  // first bucket of this warp's pass
   const unsigned int threads = gridDim.x * blockDim.x;
-  for (unsigned int b = blockIdx.x * blockDim.x + threadIdx.x; b < num_buckets; b += threads) {
-    const unsigned int first = bucket_base(bucket_start, num_buckets, b);
-    const unsigned int c = bucket_base(bucket_start, num_buckets, b + 1) - first;
-    if (c == 0u) continue;
-    const unsigned int ibase = bucket_base(bucket_istart, num_buckets, b);
-    for (unsigned int t = 0; t * kWarp < c; ++t)
+  for (unsigned int b0 = group; b0 < num_buckets; b0 += threads) {
+    const unsigned int b = b0 + lane;
+    unsigned int first = 0, c = 0, ibase = 0;
+    if (b < num_buckets) {
+      first = bucket_base(bucket_start, num_buckets, b);
+      c = bucket_base(bucket_start, num_buckets, b + 1) - first;
+      if (c != 0u) ibase = bucket_base(bucket_istart, num_buckets, b);
+    }
+    const unsigned int n_items = (c + kWarp - 1) / kWarp;
+    for (unsigned int t = 0; t < min(n_items, 2u); ++t)
       items[ibase + t] = make_uint2(first + t * kWarp, b * kWarp + (min(c - t * kWarp, 32u) - 1u));
+    unsigned int big = __ballot_sync(kFull, n_items > 2u);
+    while (big != 0u) {
+      const int src = __ffs(big) - 1;
+      big &= big - 1u;
+      const unsigned int s_first = __shfl_sync(kFull, first, src), s_c = __shfl_sync(kFull, c, src);
+      const unsigned int s_ibase = __shfl_sync(kFull, ibase, src), s_items = __shfl_sync(kFull, n_items, src);
+      const unsigned int s_b = b0 + src;
+      for (unsigned int t = 2u + lane; t < s_items; t += kWarp)
+        items[s_ibase + t] = make_uint2(s_first + t * kWarp, s_b * kWarp + (min(s_c - t * kWarp, 32u) - 1u));
+    }
   }
 }
 
