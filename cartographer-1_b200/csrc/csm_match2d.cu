@@ -487,7 +487,6 @@ __device__ __forceinline__ void push_tile(Tile* __restrict__ out, unsigned int* 
 //     grid = (max_scans, jobs); only jobs whose top depth is `slot` take part.
 // ---------------------------------------------------------------------------
 constexpr int kSeedWarps = 4;
-constexpr int kSeedStage = 4096;  // top-level scores of one scan staged per block (k_seed_nodes)
 __global__ void __launch_bounds__(kSeedWarps * kWarp)
 k_seed(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans,
        const float* __restrict__ top_scores, const JobState* __restrict__ state,
@@ -852,17 +851,6 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned int* buf = buf_all[warp];
   const unsigned int bucket = static_cast<unsigned int>(j.scan_off + scan);
-  // The scores are stored x outer, y inner (generation order) and read below with the lanes along
-  // x: one sector per lane.  A scan's lattice is a few hundred candidates, contiguous in memory,
-  // so the block stages it with coalesced loads first.
-  __shared__ float tops[kSeedStage];
-  const int count = si.nx * si.ny;
-  const bool staged = count <= kSeedStage;
-  const float* __restrict__ scan_scores = top_scores + j.cand_off + si.base;
-  if (staged) {
-    for (int i = threadIdx.x; i < count; i += blockDim.x) tops[i] = scan_scores[i];
-    __syncthreads();
-  }
   // Row by row (32 x 1 lanes): every listed run has consecutive ni at one nj.
   const int tiles_x = (si.nx + kWarp - 1) / kWarp, tiles_y = si.ny;
   int held = 0;
@@ -887,7 +875,7 @@ k_seed_nodes(const JobDev* __restrict__ jobs, const ScanInfo* __restrict__ scans
     const int ci = kWarp * ti + lane;
     bool alive = false;
     if (ci < si.nx) {
-      const float top = staged ? tops[ci * si.ny + cj] : scan_scores[ci * si.ny + cj];
+      const float top = top_scores[j.cand_off + si.base + ci * si.ny + cj];
       alive = top > thr;
       if (deferred != nullptr && !alive && has_inc && top == inc) {  // bound == incumbent: set aside
         Deferred2 d;
