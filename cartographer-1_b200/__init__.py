@@ -886,3 +886,159 @@ def tsdf_insert(ctx, grid, origins, returns, options9, resident=False):
     L.csmh_grid_cells(grid.h, tsd)
     L.csmh_grid_weight_cells(grid.h, weight)
     return tsd, weight, (mx.value, my.value)
+
+
+# ---------------------------------------------------------------------------------------------
+# .pbstream ingestion (host/cartographer/io/proto_stream*.h)
+# ---------------------------------------------------------------------------------------------
+def _io():
+    L = host()
+    if getattr(L, "_io_bound", False):
+        return L
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    L.csmh_pbstream_write.argtypes = [C.c_char_p, C.c_int, u8p, i64p]
+    L.csmh_pbstream_read.argtypes = [C.c_char_p, u8p, C.c_int64, i64p, C.c_int]
+    L.csmh_pbstream_read.restype = C.c_int64
+    L.csmh_pbstream_count.argtypes = [C.c_char_p]
+    L.csmh_pbstream_count.restype = C.c_int64
+    L.csmh_state_load.argtypes = [C.c_char_p, C.c_int, i32p]
+    L.csmh_state_load.restype = C.c_void_p
+    L.csmh_state_destroy.argtypes = [C.c_void_p]
+    L.csmh_state_destroy.restype = None
+    L.csmh_state_submap.argtypes = [C.c_void_p, C.c_int, i32p, f64p]
+    L.csmh_state_submap.restype = None
+    L.csmh_state_submap_grid.argtypes = [C.c_void_p, C.c_int, f64p]
+    L.csmh_state_submap_grid.restype = C.c_void_p
+    L.csmh_state_submap_hybrid_grid.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float),
+                                                C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
+    L.csmh_state_submap_histogram.argtypes = [C.c_void_p, C.c_int, f32p]
+    L.csmh_state_submap_histogram.restype = None
+    L.csmh_state_node.argtypes = [C.c_void_p, C.c_int, i32p, C.POINTER(C.c_int64), f64p]
+    L.csmh_state_node.restype = None
+    L.csmh_state_node_cloud.argtypes = [C.c_void_p, C.c_int, C.c_int, f32p]
+    L.csmh_state_node_cloud.restype = None
+    L.csmh_state_node_histogram.argtypes = [C.c_void_p, C.c_int, f32p]
+    L.csmh_state_node_histogram.restype = None
+    L.csmh_state_constraints.argtypes = [C.c_void_p, i32p, f64p]
+    L.csmh_state_constraints.restype = None
+    L._io_bound = True
+    return L
+
+
+def pbstream_write(path, messages):
+    """io::ProtoStreamWriter: serialized messages (bytes) -> a .pbstream file."""
+    offsets = np.zeros(len(messages) + 1, dtype=np.int64)
+    for i, m in enumerate(messages):
+        offsets[i + 1] = offsets[i] + len(m)
+    blob = np.frombuffer(b"".join(messages) or b"\0", dtype=np.uint8).copy()
+    rc = _io().csmh_pbstream_write(os.fsencode(path), len(messages), blob, offsets)
+    if rc != 0:
+        raise IOError("could not write %s" % path)
+
+
+def pbstream_read(path):
+    """io::ProtoStreamReader: every message of a .pbstream file, decompressed."""
+    L = _io()
+    count = L.csmh_pbstream_count(os.fsencode(path))
+    if count < 0:
+        raise IOError("truncated proto stream %s" % path)
+    offsets = np.zeros(count + 1, dtype=np.int64)
+    need = L.csmh_pbstream_read(os.fsencode(path), np.zeros(1, np.uint8), 0, offsets, count)
+    size = -(need + 1) if need < 0 else 0
+    blob = np.zeros(max(1, size), dtype=np.uint8)
+    got = L.csmh_pbstream_read(os.fsencode(path), blob, size, offsets, count)
+    assert got == count
+    return [blob[offsets[i]:offsets[i + 1]].tobytes() for i in range(count)]
+
+
+class _StateGrid(ProtoGrid):
+    """The grid of a loaded 2D submap (a handle like ProtoGrid's)."""
+
+    def __init__(self, handle, info):
+        self.h = handle
+        self.nx, self.ny = int(info[0]), int(info[1])
+        self.res, self.max_x, self.max_y = info[2], info[3], info[4]
+        self.is_tsdf = bool(info[5])
+
+
+class MappingState:
+    """A saved mapping state (.pbstream) read through io::ProtoStreamDeserializer and the
+    kSubmap / kNode cases of MapBuilder::LoadState.  `submaps` and `nodes` are lists of dicts in
+    stream order; poses are (tx, ty, tz, qw, qx, qy, qz).  A 2D submap's "grid" is a grid handle
+    every matcher entry point takes; a 3D submap carries "high" / "low" = (resolution, grid_size,
+    xyz[n, 3] int32, values[n] uint16) sorted by voxel index, and its "histogram"."""
+
+    def __init__(self, path, expect_3d=False):
+        L = _io()
+        counts = np.zeros(4, dtype=np.int32)
+        self.h = L.csmh_state_load(os.fsencode(path), 1 if expect_3d else 0, counts)
+        self.format_version = int(counts[3])
+        self.submaps, self.nodes = [], []
+        for i in range(int(counts[0])):
+            ints, poses = np.zeros(8, np.int32), np.zeros(14, np.float64)
+            L.csmh_state_submap(self.h, i, ints, poses)
+            s = {"trajectory_id": int(ints[0]), "submap_index": int(ints[1]), "is_3d": bool(ints[3]),
+                 "num_range_data": int(ints[4]), "finished": bool(ints[5]),
+                 "local_pose": poses[:7].copy(), "global_pose": poses[7:].copy(), "grid": None}
+            if ints[2] and ints[6]:
+                info = np.zeros(6, np.float64)
+                s["grid"] = _StateGrid(L.csmh_state_submap_grid(self.h, i, info), info)
+            if ints[3]:
+                for which, key in ((0, "high"), (1, "low")):
+                    s[key] = self._hybrid(i, which) if ints[6] & (1 << which) else None
+                hist = np.zeros(int(ints[7]), np.float32)
+                if len(hist):
+                    L.csmh_state_submap_histogram(self.h, i, hist)
+                s["histogram"] = hist
+            self.submaps.append(s)
+        for i in range(int(counts[1])):
+            ints, doubles, stamp = np.zeros(8, np.int32), np.zeros(18, np.float64), C.c_int64()
+            L.csmh_state_node(self.h, i, ints, C.byref(stamp), doubles)
+            n = {"trajectory_id": int(ints[0]), "node_index": int(ints[1]), "timestamp": stamp.value,
+                 "gravity_alignment": doubles[:4].copy(), "local_pose": doubles[4:11].copy(),
+                 "global_pose": doubles[11:].copy()}
+            for which, key in ((0, "filtered_gravity_aligned_point_cloud"), (1, "high_resolution_point_cloud"),
+                               (2, "low_resolution_point_cloud")):
+                cloud = np.zeros((int(ints[2 + which]), 3), np.float32)
+                if len(cloud):
+                    L.csmh_state_node_cloud(self.h, i, which, cloud.reshape(-1))
+                n[key] = cloud
+            hist = np.zeros(int(ints[5]), np.float32)
+            if len(hist):
+                L.csmh_state_node_histogram(self.h, i, hist)
+            n["histogram"] = hist
+            self.nodes.append(n)
+        nc = int(counts[2])
+        ints, doubles = np.zeros(max(1, 5 * nc), np.int32), np.zeros(max(1, 9 * nc), np.float64)
+        if nc:
+            L.csmh_state_constraints(self.h, ints, doubles)
+        self.constraints = [{"submap_id": (int(ints[5 * c]), int(ints[5 * c + 1])),
+                             "node_id": (int(ints[5 * c + 2]), int(ints[5 * c + 3])),
+                             "tag": "INTER_SUBMAP" if ints[5 * c + 4] else "INTRA_SUBMAP",
+                             "relative_pose": doubles[9 * c:9 * c + 7].copy(),
+                             "translation_weight": float(doubles[9 * c + 7]),
+                             "rotation_weight": float(doubles[9 * c + 8])} for c in range(nc)]
+
+    def _hybrid(self, i, which):
+        L = _io()
+        res, size = C.c_float(), C.c_int()
+        n = L.csmh_state_submap_hybrid_grid(self.h, i, which, C.byref(res), C.byref(size), None, None)
+        xyz, values = np.zeros((max(1, n), 3), np.int32), np.zeros(max(1, n), np.uint16)
+        L.csmh_state_submap_hybrid_grid(self.h, i, which, C.byref(res), C.byref(size),
+                                        xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
+        xyz, values = xyz[:n], values[:n]
+        order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
+        return float(res.value), int(size.value), xyz[order], values[order]
+
+    def close(self):
+        if getattr(self, "h", None):
+            host().csmh_state_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()

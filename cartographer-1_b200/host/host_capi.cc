@@ -38,10 +38,7 @@ void* csmh_context_create(int device) {
 void csmh_context_destroy(void* c) { delete static_cast<DeviceContext*>(c); }
 void* csmh_context_raw(void* c) { return static_cast<DeviceContext*>(c)->get(); }
 
-struct GridHolder {
-  mapping::ValueConversionTables tables;
-  std::unique_ptr<mapping::Grid2D> grid;
-};
+#include "host_capi_holders.h"
 
 void* csmh_grid_create(const uint16_t* cells, int nx, int ny, double res, double max_x,
                        double max_y) {

@@ -352,3 +352,79 @@ def tsdf_insert(grid, origin, returns, opts=None):
     """TSDFRangeDataInserter2D::Insert on a RefTsdf (it may grow); sets grid.tsd_cells / weight_cells / limits."""
     import oracle_binding as ob
     return ob._tsdf_insert(lib(), grid, origin, returns, opts)
+
+
+# ---------------------------------------------------------------------------------------------
+# The reference's own .pbstream container and point-cloud compression (oracle/ref_capi_io.cc)
+# ---------------------------------------------------------------------------------------------
+def _io():
+    L = lib()
+    if getattr(L, "_io_bound", False):
+        return L
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    L.oracle_pbstream_write.argtypes = [C.c_char_p, C.c_int, u8p, i64p]
+    L.oracle_pbstream_read.argtypes = [C.c_char_p, u8p, C.c_int64, i64p, C.c_int]
+    L.oracle_pbstream_read.restype = C.c_int64
+    L.oracle_gzip.argtypes = [u8p, C.c_int64, C.c_int, u8p, C.c_int64]
+    L.oracle_gzip.restype = C.c_int64
+    L.oracle_compress_point_cloud.argtypes = [f32p, C.c_int, C.c_void_p, C.c_int64]
+    L.oracle_compress_point_cloud.restype = C.c_int64
+    L.oracle_decompress_point_cloud.argtypes = [np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS"), C.c_int64,
+                                                C.c_int, f32p]
+    L.oracle_decompress_point_cloud.restype = None
+    L._io_bound = True
+    return L
+
+
+def pbstream_write(path, messages):
+    """The reference's ProtoStreamWriter on serialized messages."""
+    offsets = np.zeros(len(messages) + 1, dtype=np.int64)
+    for i, m in enumerate(messages):
+        offsets[i + 1] = offsets[i] + len(m)
+    blob = np.frombuffer(b"".join(messages) or b"\0", dtype=np.uint8).copy()
+    assert _io().oracle_pbstream_write(os.fsencode(path), len(messages), blob, offsets) == 0
+
+
+def pbstream_read(path, max_messages=1 << 16):
+    """The reference's ProtoStreamReader: every message, decompressed."""
+    L = _io()
+    offsets = np.zeros(max_messages + 1, dtype=np.int64)
+    need = L.oracle_pbstream_read(os.fsencode(path), np.zeros(1, np.uint8), 0, offsets, max_messages)
+    size = -(need + 1) if need < 0 else 0
+    blob = np.zeros(max(1, size), dtype=np.uint8)
+    count = L.oracle_pbstream_read(os.fsencode(path), blob, size, offsets, max_messages)
+    assert count >= 0
+    return [blob[offsets[i]:offsets[i + 1]].tobytes() for i in range(count)]
+
+
+def gzip_string(data, decompress=False):
+    """common::FastGzipString / FastGunzipString."""
+    L = _io()
+    src = np.frombuffer(data or b"\0", dtype=np.uint8).copy()
+    need = L.oracle_gzip(src, len(data), 1 if decompress else 0, np.zeros(1, np.uint8), 0)
+    size = -(need + 1) if need < 0 else need
+    out = np.zeros(max(1, size), dtype=np.uint8)
+    got = L.oracle_gzip(src, len(data), 1 if decompress else 0, out, size)
+    assert got == size
+    return out[:size].tobytes()
+
+
+def compress_point_cloud(points):
+    """sensor::CompressedPointCloud(points).ToProto().point_data() as int32 words."""
+    L = _io()
+    pts = np.ascontiguousarray(np.asarray(points, np.float32).reshape(-1, 3))
+    n = L.oracle_compress_point_cloud(pts.reshape(-1), len(pts), None, 0)
+    words = np.zeros(max(1, n), dtype=np.int32)
+    L.oracle_compress_point_cloud(pts.reshape(-1), len(pts), words.ctypes.data_as(C.c_void_p), n)
+    return words[:n]
+
+
+def decompress_point_cloud(num_points, words):
+    out = np.zeros((max(1, num_points), 3), dtype=np.float32)
+    w = np.ascontiguousarray(words, dtype=np.int32)
+    if len(w) == 0:
+        w = np.zeros(1, np.int32)
+    _io().oracle_decompress_point_cloud(w, len(words), num_points, out.reshape(-1))
+    return out[:num_points]
