@@ -9,8 +9,8 @@
 // on the wire format itself (io/proto_wire.h), with the reference's CHECKs as aborts.  The bytes
 // are what `grid.ToProto().SerializeAsString()` produces in a Cartographer process, i.e. the
 // `grid` field of a proto::Submap2D / the `high_resolution_hybrid_grid` of a proto::Submap3D
-// inside a .pbstream; unpacking the stream container itself (gzip + length prefixes,
-// io/proto_stream.cc) stays with the caller.
+// inside a .pbstream; the stream container and the records around the grids are read by
+// io/proto_stream.h and io/proto_stream_deserializer.h.
 #ifndef CARTOGRAPHER_IO_GRID_PROTO_READER_H_
 #define CARTOGRAPHER_IO_GRID_PROTO_READER_H_
 
