@@ -409,14 +409,28 @@ def run_b200(args):
         build_ms.append((b0, b1))
         return res
 
+    # the searches' point clouds as the host buffers the C entry point takes (xyz + offsets)
+    host_clouds = pkg.PackedClouds(clouds)
+    e2e_host = {"matchers_h2d_and_stack_builds": 0.0, "match_batch": 0.0, "pack_and_gather": 0.0,
+                "matcher_teardown": 0.0}
+
     def e2e_step():
         # host buffers in, gathered host results out: grid H2D + stack builds + upload +
         # searches + D2H + gather of every rank's results on rank 0 (one collective)
+        t0 = time.perf_counter()
         ms = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
-        res = pkg.match_batch(ctx, [ms[t] for t in target], clouds, [MIN_SCORE] * n_search)
+        t1 = time.perf_counter()
+        res = pkg.match_batch(ctx, [ms[t] for t in target], host_clouds, [MIN_SCORE] * n_search)
+        t2 = time.perf_counter()
         packed = sh.pack_results(idx, res)
         if world > 1:
-            return sh.gather_packed(packed, shard_sizes, n_total, device=torch.device("cuda", local))
+            packed = sh.gather_packed(packed, shard_sizes, n_total, device=torch.device("cuda", local))
+        t3 = time.perf_counter()
+        del ms
+        e2e_host["matchers_h2d_and_stack_builds"] += t1 - t0  # host wall time: the builds are queued, not awaited
+        e2e_host["match_batch"] += t2 - t1
+        e2e_host["pack_and_gather"] += t3 - t2
+        e2e_host["matcher_teardown"] += time.perf_counter() - t3
         return packed
 
     # ---- device-resident arm ---------------------------------------------------------
@@ -454,6 +468,8 @@ def run_b200(args):
         timed(e2e_step, True)
     barrier()
     ms_e2e = 0.0
+    for k in e2e_host:
+        e2e_host[k] = 0.0
     for _ in range(args.steps):
         gathered, ms = timed(e2e_step, True)
         ms_e2e += ms
@@ -504,6 +520,7 @@ def run_b200(args):
         "result_sha1": result_sha1,
         "e2e": {"value": e2e_value, "unit": "searches/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+                "host_wall_ms_per_step": {k: 1e3 * v / args.steps for k, v in e2e_host.items()},
                 "includes": "grid H2D, stack builds, job upload, searches, results D2H, gather on rank 0"},
         "gpu_launches": int(launches_job),
         "clocks": clocks,

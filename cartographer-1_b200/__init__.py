@@ -272,21 +272,55 @@ class Matcher:
             self.h = None
 
 
+class PackedClouds:
+    """Point clouds already in the layout the C entry points take: xyz float32 [total, 3] and
+    offsets int64 [n + 1] (cloud i = xyz[offsets[i]:offsets[i + 1]]).  Behaves like a list of
+    clouds; match_batch passes the two arrays on without a copy."""
+
+    def __init__(self, clouds):
+        if isinstance(clouds, PackedClouds):
+            self.xyz, self.offsets = clouds.xyz, clouds.offsets
+            return
+        self.offsets = np.zeros(len(clouds) + 1, dtype=np.int64)
+        np.cumsum([len(c) for c in clouds], out=self.offsets[1:])
+        self.xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in clouds], axis=0),
+                                        dtype=np.float32) if len(clouds) else np.zeros((0, 3), np.float32)
+
+    def __len__(self):
+        return len(self.offsets) - 1
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(len(self)))]
+        return self.xyz[self.offsets[i]:self.offsets[i + 1]]
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
 def _pack(matchers, clouds, min_scores, initial):
     n = len(clouds)
     handles = (C.c_void_p * n)(*[m.h for m in matchers])
-    full = np.zeros(n, dtype=np.int32)
     init = np.zeros((n, 3), dtype=np.float64)
-    for i in range(n):
-        if initial is None or initial[i] is None:
-            full[i] = 1
-        else:
-            init[i] = initial[i]
+    if initial is None:
+        full = np.ones(n, dtype=np.int32)
+    else:
+        full = np.zeros(n, dtype=np.int32)
+        for i in range(n):
+            if initial[i] is None:
+                full[i] = 1
+            else:
+                init[i] = initial[i]
+    if isinstance(clouds, PackedClouds):
+        return n, handles, full, init.reshape(-1), clouds.xyz, clouds.offsets, \
+            np.ascontiguousarray(min_scores, dtype=np.float32)
     offsets = np.zeros(n + 1, dtype=np.int64)
-    for i, c in enumerate(clouds):
-        offsets[i + 1] = offsets[i] + len(c)
-    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
-                                               for c in clouds], axis=0), dtype=np.float32)
+    np.cumsum([len(c) for c in clouds], out=offsets[1:])
+    if n and all(isinstance(c, np.ndarray) and c.dtype == np.float32 and c.ndim == 2 and c.shape[1] == 3 for c in clouds):
+        xyz = np.concatenate(clouds, axis=0)  # already [k, 3] float32: one copy
+    else:
+        xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
+                                                   for c in clouds], axis=0), dtype=np.float32)
     return n, handles, full, init.reshape(-1), xyz, offsets, \
         np.ascontiguousarray(min_scores, dtype=np.float32)
 

@@ -1,5 +1,7 @@
 #include "cartographer/mapping/internal/2d/scan_matching/fast_correlative_scan_matcher_2d.h"
 
+#include <mutex>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -42,8 +44,26 @@ DeviceContext::~DeviceContext() { csm_ctx_destroy(ctx_); }
 std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid) {
   const float min_score = 1.f - grid.GetMaxCorrespondenceCost();
   const float max_score = 1.f - grid.GetMinCorrespondenceCost();
-  const float scale = 255.f / (max_score - min_score);
   const std::vector<float>& cost = grid.value_to_correspondence_cost_table();
+  CSM_CHECK(cost.size() == 65536);
+  // 65536 lround calls are 0.4 ms -- as long as the whole stack build of a 1000 x 1000 grid -- and
+  // the submaps of a map share one value table and one pair of bounds: the last few tables are
+  // kept, keyed by the bounds and the FULL contents of the value table (compared, not hashed).
+  struct Entry {
+    float min_score, max_score;
+    std::vector<float> cost;
+    std::vector<uint8> table;
+  };
+  static std::mutex mutex;
+  static std::vector<Entry> cache;
+  {
+    std::lock_guard<std::mutex> lock(mutex);
+    for (const Entry& e : cache)
+      if (e.min_score == min_score && e.max_score == max_score &&
+          std::memcmp(e.cost.data(), cost.data(), sizeof(float) * cost.size()) == 0)
+        return e.table;
+  }
+  const float scale = 255.f / (max_score - min_score);
   std::vector<uint8> table(65536);
   for (size_t v = 0; v != table.size(); ++v) {
     const float probability = 1.f - std::abs(cost[v]);
@@ -52,6 +72,9 @@ std::vector<uint8> ComputeQuantizationTable(const Grid2D& grid) {
     CSM_CHECK(q <= 255);
     table[v] = static_cast<uint8>(q);
   }
+  std::lock_guard<std::mutex> lock(mutex);
+  if (cache.size() >= 8) cache.erase(cache.begin());
+  cache.push_back(Entry{min_score, max_score, cost, table});
   return table;
 }
 
@@ -199,7 +222,7 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
     DeviceContext* context, const QueryList& queries) {
   if (queries.empty()) return {};
   Batch batch(context, queries, /*resident=*/false);
-  return batch.RunStreaming();
+  return batch.RunStreaming(queries);
 }
 
 FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryList& queries,
@@ -210,7 +233,6 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
   xyz_.resize(n);
   quats_.resize(n);
   jobs_.resize(n);
-  std::vector<std::vector<float>>&xyz = xyz_, &quats = quats_;
   std::vector<csm_job2d>& jobs = jobs_;
   std::vector<double> lattice_estimate(n);
   params_.assign(n, SearchParameters(0, 0, 0., 0.));
@@ -234,23 +256,16 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
       initial_[i] = q.initial_pose_estimate;
     }
     const SearchParameters& sp = params_[i];
-    xyz[i].resize(3 * q.point_cloud->size());
     double reach = 0.;
     for (size_t p = 0; p != q.point_cloud->size(); ++p) {
       const sensor::Vector3f& v = (*q.point_cloud)[p].position;
-      xyz[i][3 * p] = v.x();
-      xyz[i][3 * p + 1] = v.y();
-      xyz[i][3 * p + 2] = v.z();
       reach = std::max(reach, std::hypot(static_cast<double>(v.x()), static_cast<double>(v.y())));
     }
-    quats[i] = sp.ScanQuaternionTable();
     csm_job2d& job = jobs[i];
     std::memset(&job, 0, sizeof(job));
     job.stack = m.stack_;
-    job.points_xyz = xyz[i].data();
     job.num_points = static_cast<int32_t>(q.point_cloud->size());
-    job.num_scans = sp.num_scans;
-    job.scan_quat = quats[i].data();
+    job.num_scans = sp.num_scans;  // points_xyz and scan_quat: Prepare()
     // Rotation2Dd -> Rotation2Df -> AngleAxisf -> Quaternionf (reference :235-239)
     const float yaw = static_cast<float>(initial_[i].rotation().angle());
     const float half_yaw = 0.5f * yaw;
@@ -285,6 +300,7 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
     }
     chunks_.emplace_back(begin, end);
     if (resident) {
+      Prepare(queries, begin, end);
       csm_batch2d* device_batch = nullptr;
       CheckOk(csm_batch2d_upload(context_->get(), jobs.data() + begin, static_cast<int>(end - begin),
                                  &device_batch),
@@ -293,6 +309,23 @@ FastCorrelativeScanMatcher2D::Batch::Batch(DeviceContext* context, const QueryLi
     }
     begin = end;
   }
+}
+
+void FastCorrelativeScanMatcher2D::Batch::Prepare(const QueryList& queries, const size_t begin, const size_t end) {
+  common::ParallelFor(end - begin, [&](const size_t k) {
+    const size_t i = begin + k;
+    const sensor::PointCloud& cloud = *queries[i].second.point_cloud;
+    xyz_[i].resize(3 * cloud.size());
+    for (size_t p = 0; p != cloud.size(); ++p) {
+      const sensor::Vector3f& v = cloud[p].position;
+      xyz_[i][3 * p] = v.x();
+      xyz_[i][3 * p + 1] = v.y();
+      xyz_[i][3 * p + 2] = v.z();
+    }
+    quats_[i] = params_[i].ScanQuaternionTable();
+    jobs_[i].points_xyz = xyz_[i].data();
+    jobs_[i].scan_quat = quats_[i].data();
+  });
 }
 
 FastCorrelativeScanMatcher2D::Batch::~Batch() {
@@ -313,10 +346,12 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
   return Convert(results);
 }
 
-std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::RunStreaming() {
-  // Device batch k+1 is uploaded and its kernels queued while k runs; a batch is fetched (its
-  // own event, not the stream) and its blocks go back to the context's pool once kInFlight
-  // are queued.
+std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::Batch::RunStreaming(
+    const QueryList& queries) {
+  // Device batch k+1 is prepared on the host (angle tables: libm), uploaded and its kernels queued
+  // while k runs; a batch is fetched (its own event, not the stream) and its blocks go back to the
+  // context's pool once kInFlight are queued.  Only the first device batch's host preparation is
+  // not hidden behind device work.
   constexpr size_t kInFlight = 3;
   std::vector<csm_result2d> results(initial_.size());
   std::vector<std::pair<size_t, csm_batch2d*>> live;
@@ -327,6 +362,8 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
     csm_batch2d_destroy(context_->get(), live.front().second);
     live.erase(live.begin());
   };
+  CSM_CHECK(queries.size() == initial_.size());
+  if (!chunks_.empty()) Prepare(queries, chunks_[0].first, chunks_[0].second);
   for (size_t c = 0; c != chunks_.size(); ++c) {
     csm_batch2d* device_batch = nullptr;
     CheckOk(csm_batch2d_upload(context_->get(), jobs_.data() + chunks_[c].first,
@@ -334,6 +371,14 @@ std::vector<FastCorrelativeScanMatcher2D::Answer> FastCorrelativeScanMatcher2D::
             "csm_batch2d_upload");
     CheckOk(csm_batch2d_run(context_->get(), device_batch), "csm_batch2d_run");
     live.emplace_back(c, device_batch);
+    // the upload staged this batch's points and tables: the host copies are done with
+    for (size_t i = chunks_[c].first; i != chunks_[c].second; ++i) {
+      std::vector<float>().swap(xyz_[i]);
+      std::vector<float>().swap(quats_[i]);
+      jobs_[i].points_xyz = nullptr;
+      jobs_[i].scan_quat = nullptr;
+    }
+    if (c + 1 != chunks_.size()) Prepare(queries, chunks_[c + 1].first, chunks_[c + 1].second);
     if (live.size() >= kInFlight) retire();
   }
   while (!live.empty()) retire();

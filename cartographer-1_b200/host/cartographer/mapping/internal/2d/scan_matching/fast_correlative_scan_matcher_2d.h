@@ -167,11 +167,15 @@ class FastCorrelativeScanMatcher2D {
     Batch& operator=(const Batch&) = delete;
     void Run();
     std::vector<Answer> Fetch();
-    std::vector<Answer> RunStreaming();
+    // `queries`: the list the batch was constructed from (the streaming form reads the point
+    // clouds of device batch k+1 while k runs).
+    std::vector<Answer> RunStreaming(const QueryList& queries);
     size_t size() const { return initial_.size(); }
 
    private:
     std::vector<Answer> Convert(const std::vector<csm_result2d>& results) const;
+    // The heavy host half of jobs [begin, end): point copies and the scans' angle tables (libm).
+    void Prepare(const QueryList& queries, size_t begin, size_t end);
 
     DeviceContext* context_;
     std::vector<SearchParameters> params_;

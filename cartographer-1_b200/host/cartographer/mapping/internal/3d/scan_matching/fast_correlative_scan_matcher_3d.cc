@@ -40,16 +40,20 @@ const std::vector<float>& ValueToProbabilityTable() {
 
 // precomputation_grid_3d.cc:49-61
 std::vector<uint8> ComputeQuantizationTable3D() {
-  const std::vector<float>& probability = ValueToProbabilityTable();
-  std::vector<uint8> table(65536);
-  for (size_t v = 0; v != table.size(); ++v) {
-    const int cell_value = common::RoundToInt((probability[v] - kMinProbability) *
-                                              (255.f / (kMaxProbability - kMinProbability)));
-    CSM_CHECK(cell_value >= 0);
-    CSM_CHECK(cell_value <= 255);
-    table[v] = static_cast<uint8>(cell_value);
-  }
-  return table;
+  // no inputs: computed once per process (function-local static, thread-safe initialisation)
+  static const std::vector<uint8> kTable = [] {
+    const std::vector<float>& probability = ValueToProbabilityTable();
+    std::vector<uint8> table(65536);
+    for (size_t v = 0; v != table.size(); ++v) {
+      const int cell_value = common::RoundToInt((probability[v] - kMinProbability) *
+                                                (255.f / (kMaxProbability - kMinProbability)));
+      CSM_CHECK(cell_value >= 0);
+      CSM_CHECK(cell_value <= 255);
+      table[v] = static_cast<uint8>(cell_value);
+    }
+    return table;
+  }();
+  return kTable;
 }
 
 proto::FastCorrelativeScanMatcherOptions3D CreateFastCorrelativeScanMatcherOptions3D(

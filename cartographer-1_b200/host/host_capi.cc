@@ -16,6 +16,9 @@
 #include "cartographer/mapping/internal/2d/scan_matching/real_time_correlative_scan_matcher_2d.h"
 #include "cartographer/mapping/internal/constraints/constraint_builder_2d.h"
 
+#include "host_capi_holders.h"
+#include "parallel_for.h"
+
 using namespace cartographer;
 using mapping::scan_matching::DeviceContext;
 using mapping::scan_matching::FastCorrelativeScanMatcher2D;
@@ -38,7 +41,6 @@ void* csmh_context_create(int device) {
 void csmh_context_destroy(void* c) { delete static_cast<DeviceContext*>(c); }
 void* csmh_context_raw(void* c) { return static_cast<DeviceContext*>(c)->get(); }
 
-#include "host_capi_holders.h"
 
 void* csmh_grid_create(const uint16_t* cells, int nx, int ny, double res, double max_x,
                        double max_y) {
@@ -229,9 +231,14 @@ int csmh_match_batch(void* ctx, int n, void* const* matchers, const int32_t* ful
   // batches of a large job through the device instead of uploading all of them first.
   std::vector<sensor::PointCloud> clouds(n);
   FastCorrelativeScanMatcher2D::QueryList q(n);
+  common::ParallelFor(static_cast<size_t>(n), [&](const size_t i) {
+    std::vector<sensor::RangefinderPoint> points(static_cast<size_t>(offsets[i + 1] - offsets[i]));
+    const float* src = xyz + 3 * offsets[i];
+    for (size_t p = 0; p != points.size(); ++p)
+      points[p].position = sensor::Vector3f(src[3 * p], src[3 * p + 1], src[3 * p + 2]);
+    clouds[i] = sensor::PointCloud(std::move(points));
+  }, 64);
   for (int i = 0; i < n; ++i) {
-    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
-      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
     q[i].first = static_cast<const FastCorrelativeScanMatcher2D*>(matchers[i]);
     q[i].second.point_cloud = &clouds[i];
     q[i].second.full_submap = full[i] != 0;

@@ -18,6 +18,8 @@ from the rank that produced it to the ranks that replicate it; `torch.distribute
 carries it (NCCL over NVLink on GPUs, gloo in the CPU tests).  Nothing here computes
 scores.
 """
+import ctypes
+
 import numpy as np
 
 
@@ -135,6 +137,12 @@ def gather_in_submission_order(local_indices, local_results, num_searches, group
 # three float64 = 6 x int32).  Fixed size, so the gather is ONE collective on a device tensor.
 RESULT_WORDS = 12
 
+# csmh_result2d (host/host_capi.cc) as a numpy record: 48 bytes, naturally aligned
+RESULT2D_DTYPE = np.dtype([("found", np.int32), ("scan_index", np.int32), ("x_index_offset", np.int32),
+                           ("y_index_offset", np.int32), ("score", np.float32), ("tie_resolution", np.int32),
+                           ("pose_x", np.float64), ("pose_y", np.float64), ("pose_theta", np.float64),
+                           ("candidates_scored", np.uint64)])
+
 
 def pack_results(indices, results):
     """Result2D-like objects (found, scan_index, x/y_index_offset, score, pose_x/y/theta) ->
@@ -142,6 +150,14 @@ def pack_results(indices, results):
     n = len(indices)
     out = np.zeros((n, RESULT_WORDS), dtype=np.int32)
     out[:, 0] = np.asarray(indices, dtype=np.int32)
+    if isinstance(results, ctypes.Array) and ctypes.sizeof(results) == n * RESULT2D_DTYPE.itemsize:
+        # the array csmh_match_batch filled: one structured view, no per-result Python work
+        r = np.frombuffer(results, dtype=RESULT2D_DTYPE, count=n)
+        out[:, 1], out[:, 2], out[:, 3], out[:, 4] = r["found"], r["scan_index"], r["x_index_offset"], r["y_index_offset"]
+        out[:, 5] = r["score"].view(np.int32)
+        pose = np.stack([r["pose_x"], r["pose_y"], r["pose_theta"]], axis=1)
+        out[:, 6:12] = np.ascontiguousarray(pose).view(np.int32).reshape(n, 6)
+        return out
     pose = np.zeros((n, 3), dtype=np.float64)
     score = np.zeros(n, dtype=np.float32)
     for k, r in enumerate(results):
