@@ -283,8 +283,13 @@ class PackedClouds:
             return
         self.offsets = np.zeros(len(clouds) + 1, dtype=np.int64)
         np.cumsum([len(c) for c in clouds], out=self.offsets[1:])
-        self.xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in clouds], axis=0),
-                                        dtype=np.float32) if len(clouds) else np.zeros((0, 3), np.float32)
+        if len(clouds) == 0:
+            self.xyz = np.zeros((0, 3), np.float32)
+        elif all(isinstance(c, np.ndarray) and c.dtype == np.float32 and c.ndim == 2 and c.shape[1] == 3 for c in clouds):
+            self.xyz = np.concatenate(clouds, axis=0)  # one copy
+        else:
+            self.xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in clouds],
+                                                           axis=0), dtype=np.float32)
 
     def __len__(self):
         return len(self.offsets) - 1
@@ -343,11 +348,8 @@ def rt_match_batch(ctx, grids, clouds, initial, linear_search_window=0.1,
     opts = np.array([linear_search_window, angular_search_window, translation_delta_cost_weight,
                      rotation_delta_cost_weight], dtype=np.float64)
     init = np.ascontiguousarray(initial, dtype=np.float64).reshape(-1)
-    offsets = np.zeros(n + 1, dtype=np.int64)
-    for i, c in enumerate(clouds):
-        offsets[i + 1] = offsets[i] + len(c)
-    xyz = np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3)
-                                               for c in clouds], axis=0), dtype=np.float32)
+    packed = clouds if isinstance(clouds, PackedClouds) else PackedClouds(clouds)
+    xyz, offsets = packed.xyz, packed.offsets
     out = (Result2D * n)()
     rc = host().csmh_rt_match_batch(ctx.h, n, handles, opts, init, xyz, offsets, out)
     assert rc == 0

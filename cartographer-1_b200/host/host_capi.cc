@@ -366,9 +366,14 @@ int csmh_rt_match_batch(void* ctx, int n, void* const* grids, const double* opti
   const RealTimeCorrelativeScanMatcher2D matcher(o, static_cast<DeviceContext*>(ctx));
   std::vector<sensor::PointCloud> clouds(n);
   std::vector<RealTimeCorrelativeScanMatcher2D::Query> q(n);
+  common::ParallelFor(static_cast<size_t>(n), [&](const size_t i) {
+    std::vector<sensor::RangefinderPoint> points(static_cast<size_t>(offsets[i + 1] - offsets[i]));
+    const float* src = xyz + 3 * offsets[i];
+    for (size_t p = 0; p != points.size(); ++p)
+      points[p].position = sensor::Vector3f(src[3 * p], src[3 * p + 1], src[3 * p + 2]);
+    clouds[i] = sensor::PointCloud(std::move(points));
+  }, 64);
   for (int i = 0; i < n; ++i) {
-    for (int64_t p = offsets[i]; p < offsets[i + 1]; ++p)
-      clouds[i].push_back({sensor::Vector3f(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2])});
     q[i].point_cloud = &clouds[i];
     q[i].grid = static_cast<GridHolder*>(grids[i])->grid.get();
     q[i].initial_pose_estimate = transform::Rigid2d(
