@@ -84,3 +84,65 @@ def test_searches_over_a_saved_state_match_the_oracle(csm, tmp_path):
             d = (tf[i][2] - o_out[i].pose_theta + np.pi) % (2 * np.pi) - np.pi
             assert abs(d) <= 1e-9
     assert stats[1] == found.sum()
+
+
+def test_3d_state_searches_match_the_oracle(csm, gpu_ctx, tmp_path):
+    """The same for a 3D map: hybrid grids, histograms and the nodes' two point clouds travel through
+    the saved state; ConstraintBuilder3D on what the reader returns against the oracle's matcher on
+    the fixture's own data (clouds decoded with the reference's arithmetic in numpy)."""
+    import synth3d
+    worlds = [synth3d.World3D(61 + k, size_xy=8.0) for k in range(2)]
+    opt = ob.options3d(6, 3, 0.3, 0.4, 1.2, 0.4, np.radians(10))
+    rng = np.random.default_rng(8)
+    submaps, nodes, raw = [], [], []
+    for k, w in enumerate(worlds):
+        xyz, val = w.voxels(w.res)
+        lxyz, lval = w.voxels(w.low_res)
+        submaps.append({"id": (0, k), "high_bytes": pf.hybrid_grid_bytes(0.1, xyz, val),
+                        "low_bytes": pf.hybrid_grid_bytes(0.45, lxyz, lval), "histogram": w.submap_histogram(),
+                        "local_pose": (0, 0, 0, 1, 0, 0, 0), "global_pose": (0, 0, 0, 1, 0, 0, 0),
+                        "num_range_data": 160, "finished": True, "voxels": (xyz, val, lxyz, lval)})
+    for i in range(10):
+        s = i % 2
+        hi, lo, hist, grav, true = worlds[s].node(np.append(rng.uniform(-2, 2, 2), 0.2), rng.uniform(-1, 1),
+                                                  n_high=200, n_low=50, max_range=5.0)
+        init = true.copy()
+        init[:3] += rng.uniform(-0.4, 0.4, 3) * [1, 1, 0.3]
+        init = init.astype(np.float32).astype(np.float64)
+        nodes.append({"id": (0, i), "timestamp": 10 + i, "gravity_alignment": grav, "local_pose": init,
+                      "global_pose": init, "high": hi, "low": lo, "histogram": hist, "submap": s})
+    path = tmp_path / "map3d.pbstream"
+    path.write_bytes(pf.pbstream_bytes(pf.mapping_state_messages(submaps, nodes)))
+    state = csm.MappingState(str(path), expect_3d=True)
+    assert len(state.submaps) == 2 and len(state.nodes) == 10
+    gpu_m, oracle_m = [], []
+    for got, want in zip(state.submaps, submaps):
+        res, _, xyz, val = got["high"]
+        lres, _, lxyz, lval = got["low"]
+        gpu_m.append(csm.Matcher3D(gpu_ctx, res, xyz, val, lres, lxyz, lval, got["histogram"], opt))
+        wx, wv, wlx, wlv = want["voxels"]
+        oracle_m.append(ob.OracleFCSM3D(ob.OracleGrid3D(0.1, wx, wv), ob.OracleGrid3D(0.45, wlx, wlv),
+                                        np.asarray(want["histogram"], np.float32), opt))
+    gpu_nodes, node_poses, search_submap, search_full = [], [], [], []
+    for got, want in zip(state.nodes, nodes):
+        gpu_nodes.append(csm.Node3D(got["high_resolution_point_cloud"], got["low_resolution_point_cloud"],
+                                    got["histogram"], got["gravity_alignment"]))
+        node_poses.append(got["global_pose"])
+        search_submap.append(want["submap"])
+        search_full.append(0)
+        assert got["global_pose"].tolist() == [float(v) for v in want["global_pose"]]
+    ident = np.tile(ob.IDENTITY_POSE7.astype(np.float64), (len(nodes), 1))
+    found, transform, stats, _ = csm.constraint_builder3d_run(
+        gpu_m, search_submap, search_full, gpu_nodes, np.array(node_poses), ident, opt, min_score=0.45,
+        global_localization_min_score=0.5, pool_threads=3, flush_threshold=4)
+    assert stats["searches"] == len(nodes)
+    for i, want in enumerate(nodes):
+        hi = pf.decode_point_cloud_reference_math(*pf.compress_point_cloud(want["high"])[:2])
+        lo = pf.decode_point_cloud_reference_math(*pf.compress_point_cloud(want["low"])[:2])
+        r = oracle_m[want["submap"]].match(hi, lo, np.asarray(want["histogram"], np.float32), 0.45,
+                                           np.asarray(want["global_pose"], np.float32), ob.IDENTITY_POSE7,
+                                           np.asarray(want["gravity_alignment"], np.float64), False)
+        assert bool(found[i]) == bool(r.found), i
+        if r.found:
+            assert np.array_equal(transform[i].astype(np.float32), np.array(r.pose, np.float32))
+    assert found.sum() >= 5
