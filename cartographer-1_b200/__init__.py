@@ -656,8 +656,9 @@ def rotational_match(submap_hist, hist, initial_angle, angles):
 def constraint_builder3d_run(submap_matchers, search_submap, search_full, nodes, node_poses, submap_poses,
                              fcsm_options7, sampling_ratio=1.0, max_constraint_distance=15.0, min_score=0.55,
                              global_localization_min_score=0.6, devices=(0,), pool_threads=4,
-                             flush_threshold=256):
+                             flush_threshold=256, burst=0):
     """Drives ConstraintBuilder3D (MaybeAdd(Global)Constraint / NotifyEndOfNode / WhenDone).
+    burst > 0: the searches enter through MaybeAddConstraints in bursts of that many requests.
     Returns (found[n], transform[n, 7], stats dict, seconds)."""
     n = len(nodes)
     sm = (C.c_void_p * len(submap_matchers))(*[m.h for m in submap_matchers])
@@ -667,12 +668,15 @@ def constraint_builder3d_run(submap_matchers, search_submap, search_full, nodes,
     stats = np.zeros(4, np.float64)
     opts = np.array([sampling_ratio, max_constraint_distance, min_score, global_localization_min_score,
                      1.1e4, 1e5], np.float64)
-    secs = host().csmh_constraint_builder3d_run(
+    L = host()
+    L.csmh_constraint_builder3d_run2.restype = C.c_double
+    L.csmh_constraint_builder3d_run2.argtypes = L.csmh_constraint_builder3d_run.argtypes + [C.c_int]
+    secs = L.csmh_constraint_builder3d_run2(
         len(devices), np.ascontiguousarray(devices, np.int32), pool_threads, flush_threshold, opts,
         np.ascontiguousarray(fcsm_options7, np.float64), len(submap_matchers), sm, n,
         np.ascontiguousarray(search_submap, np.int32), np.ascontiguousarray(search_full, np.int32), nh,
         np.ascontiguousarray(node_poses, np.float64).reshape(-1),
-        np.ascontiguousarray(submap_poses, np.float64).reshape(-1), found, transform.reshape(-1), stats)
+        np.ascontiguousarray(submap_poses, np.float64).reshape(-1), found, transform.reshape(-1), stats, int(burst))
     return found, transform, dict(searches=int(stats[0]), found=int(stats[1]),
                                   candidates_scored=int(stats[2]), flushes=int(stats[3])), secs
 

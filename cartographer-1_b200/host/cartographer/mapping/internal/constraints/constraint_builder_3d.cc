@@ -93,6 +93,30 @@ void ConstraintBuilder3D::MaybeAddGlobalConstraint(const SubmapId& submap_id, co
           transform::Rigid3d(transform::Vector3d(), global_submap_rotation));
 }
 
+void ConstraintBuilder3D::MaybeAddConstraints(const std::vector<ConstraintRequest>& requests) {
+  std::lock_guard<std::mutex> locker(mutex_);
+  for (const ConstraintRequest& r : requests) {
+    if (r.match_full_submap) {
+      Enqueue(r.submap_id, r.submap, r.node_id, true, r.constant_data,
+              transform::Rigid3d(transform::Vector3d(), r.global_node_pose.rotation()),
+              transform::Rigid3d(transform::Vector3d(), r.global_submap_pose.rotation()));
+      continue;
+    }
+    const double dx = r.global_node_pose.translation().x() - r.global_submap_pose.translation().x();
+    const double dy = r.global_node_pose.translation().y() - r.global_submap_pose.translation().y();
+    const double dz = r.global_node_pose.translation().z() - r.global_submap_pose.translation().z();
+    if (std::sqrt(dx * dx + dy * dy + dz * dz) > options_.max_constraint_distance()) continue;
+    if (!per_submap_sampler_
+             .emplace(std::piecewise_construct, std::forward_as_tuple(r.submap_id),
+                      std::forward_as_tuple(options_.sampling_ratio()))
+             .first->second.Pulse()) {
+      continue;
+    }
+    Enqueue(r.submap_id, r.submap, r.node_id, false, r.constant_data, r.global_node_pose, r.global_submap_pose);
+  }
+  if (static_cast<int>(pending_.size()) >= flush_threshold_) ScheduleFlush();
+}
+
 std::weak_ptr<common::Task> ConstraintBuilder3D::ScheduleFlush() {
   auto searches = std::make_shared<std::vector<PendingSearch>>(std::move(pending_));
   pending_.clear();

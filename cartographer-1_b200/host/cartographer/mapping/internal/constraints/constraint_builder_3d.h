@@ -64,6 +64,22 @@ class ConstraintBuilder3D {
   static void RegisterMetrics(metrics::FamilyFactory* family_factory);
 
   // --- additions of the B200 path (not in the reference) ---
+  // Whole-node / whole-submap batches, as ConstraintBuilder2D's: the
+  // reference's caller (PoseGraph3D::ComputeConstraintsForNode, pose_graph_3d.cc) emits one
+  // MaybeAdd*Constraint call per (node, submap) pair, each taking the builder's mutex.  One call
+  // carries the burst: per request the semantics of MaybeAddConstraint (match_full_submap false:
+  // distance gate, then the submap's sampler) or MaybeAddGlobalConstraint (true: only the poses'
+  // rotations are used), in order, under ONE lock and with ONE flush decision.
+  struct ConstraintRequest {
+    SubmapId submap_id{0, 0};
+    const Submap3D* submap = nullptr;
+    NodeId node_id{0, 0};
+    const TrajectoryNode::Data* constant_data = nullptr;
+    bool match_full_submap = false;
+    transform::Rigid3d global_node_pose;
+    transform::Rigid3d global_submap_pose;
+  };
+  void MaybeAddConstraints(const std::vector<ConstraintRequest>& requests);
   void set_flush_threshold(int searches) { flush_threshold_ = searches; }
   struct Stats {
     uint64_t searches = 0, found = 0, candidates_scored = 0, flushes = 0;

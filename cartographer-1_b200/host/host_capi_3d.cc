@@ -223,6 +223,13 @@ int csmh_fcsm3d_discrete_scans(void* ctx, void* m, void* node, const double* nod
 // csmh_fcsm3d_create.  Per search i: found[i] and the constraint transform
 // submap <- node as 7 doubles.  Returns wall seconds from the first MaybeAdd* call to
 // the WhenDone callback.
+double csmh_constraint_builder3d_run2(int num_devices, const int* devices, int num_pool_threads,
+                                      int flush_threshold, const double* options6,
+                                      const double* fcsm_options7, int num_submaps, void* const* submap_holders,
+                                      int num_searches, const int32_t* search_submap,
+                                      const int32_t* search_full, void* const* nodes,
+                                      const double* node_poses, const double* submap_poses, int32_t* found,
+                                      double* transform7, double* stats4, int burst);
 double csmh_constraint_builder3d_run(int num_devices, const int* devices, int num_pool_threads,
                                      int flush_threshold, const double* options6,
                                      const double* fcsm_options7, int num_submaps, void* const* submap_holders,
@@ -230,6 +237,19 @@ double csmh_constraint_builder3d_run(int num_devices, const int* devices, int nu
                                      const int32_t* search_full, void* const* nodes,
                                      const double* node_poses, const double* submap_poses, int32_t* found,
                                      double* transform7, double* stats4) {
+  return csmh_constraint_builder3d_run2(num_devices, devices, num_pool_threads, flush_threshold, options6,
+                                        fcsm_options7, num_submaps, submap_holders, num_searches, search_submap,
+                                        search_full, nodes, node_poses, submap_poses, found, transform7, stats4, 0);
+}
+// burst > 0: the searches enter through MaybeAddConstraints in bursts of that many requests
+// (whole-node batches), followed by the burst's NotifyEndOfNode calls.
+double csmh_constraint_builder3d_run2(int num_devices, const int* devices, int num_pool_threads,
+                                      int flush_threshold, const double* options6,
+                                      const double* fcsm_options7, int num_submaps, void* const* submap_holders,
+                                      int num_searches, const int32_t* search_submap,
+                                      const int32_t* search_full, void* const* nodes,
+                                      const double* node_poses, const double* submap_poses, int32_t* found,
+                                      double* transform7, double* stats4, int burst) {
   using mapping::constraints::ConstraintBuilder3D;
   mapping::constraints::proto::ConstraintBuilderOptions o;
   o.set_sampling_ratio(options6[0]);
@@ -262,7 +282,24 @@ double csmh_constraint_builder3d_run(int num_devices, const int* devices, int nu
     bool done = false;
     ConstraintBuilder3D::Result result;
     const auto t0 = std::chrono::steady_clock::now();
-    for (int i = 0; i < num_searches; ++i) {
+    for (int begin = 0; burst > 0 && begin < num_searches; begin += burst) {
+      const int end = std::min(num_searches, begin + burst);
+      std::vector<ConstraintBuilder3D::ConstraintRequest> requests;
+      for (int i = begin; i < end; ++i) {
+        ConstraintBuilder3D::ConstraintRequest r;
+        r.submap_id = mapping::SubmapId{0, search_submap[i]};
+        r.submap = &submaps[search_submap[i]];
+        r.node_id = mapping::NodeId{0, i};
+        r.constant_data = &static_cast<Node3DHolder*>(nodes[i])->data;
+        r.match_full_submap = search_full[i] != 0;
+        r.global_node_pose = Pose7(node_poses + 7 * i);
+        r.global_submap_pose = Pose7(submap_poses + 7 * i);
+        requests.push_back(r);
+      }
+      builder.MaybeAddConstraints(requests);
+      for (int i = begin; i < end; ++i) builder.NotifyEndOfNode();
+    }
+    for (int i = 0; burst <= 0 && i < num_searches; ++i) {
       const int s = search_submap[i];
       const mapping::TrajectoryNode::Data* data = &static_cast<Node3DHolder*>(nodes[i])->data;
       const transform::Rigid3d np = Pose7(node_poses + 7 * i), sp = Pose7(submap_poses + 7 * i);

@@ -325,6 +325,12 @@ def test_constraint_builder3d_protocol_and_results(csm, gpu_ctx):
         if r.found:
             assert np.array_equal(transform[i].astype(np.float32), np.array(r.pose, np.float32))
     assert found.sum() == stats["found"] and found.sum() >= 6
+    # the same searches entering as whole-node bursts (MaybeAddConstraints): identical answers
+    found_b, transform_b, stats_b, _ = csm.constraint_builder3d_run(
+        gpu_m, search_submap, search_full, nodes, np.array(node_poses), ident, opt, min_score=0.45,
+        global_localization_min_score=0.5, pool_threads=3, flush_threshold=5, burst=4)
+    assert stats_b["searches"] == 11
+    assert np.array_equal(found, found_b) and transform.tobytes() == transform_b.tobytes()
 
 
 RT_CLOUD = np.array([[-3, 2, 0], [-4, 2, 0], [-5, 2, 0], [-6, 2, 0], [-6, 3, 1], [-6, 4, 2], [-7, 3, 1]],

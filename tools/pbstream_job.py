@@ -99,7 +99,9 @@ def main():
               angular_window=a.angular_window, depth=a.depth, max_constraint_distance=15.0)
     devices = tuple(int(d) for d in a.devices.split(","))
     csm.constraint_builder_run(grids, poses, sub[:8], full[:8], rel[:8], clouds[:8], devices=devices, **kw)  # warm-up
-    secs, found, tf, stats = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, devices=devices, **kw)
+    # a node's searches enter as one MaybeAddConstraints burst (whole-node batches)
+    secs, found, tf, stats = csm.constraint_builder_run(grids, poses, sub, full, rel, clouds, devices=devices,
+                                                        burst=max(1, len(grids)), **kw)
     out = {"pbstream": os.path.basename(a.pbstream), "submaps": len(grids), "nodes": len(state.nodes),
            "searches": int(stats[0]), "found": int(found.sum()), "seconds": secs,
            "searches_per_s": stats[0] / secs if secs > 0 else None, "candidates_scored": int(stats[2])}
