@@ -1082,3 +1082,32 @@ class MappingState:
 
     def __del__(self):
         self.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# Voxel filters of the node clouds (host/cartographer/sensor/internal/voxel_filter.h; host code)
+# ---------------------------------------------------------------------------------------------
+def _voxel_filter(which, points, a, b=0.0, c=0.0):
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    L.csmh_voxel_filter.argtypes = [C.c_int, f32p, C.c_int, C.c_float, C.c_float, C.c_float, f32p]
+    pts = np.ascontiguousarray(np.asarray(points, np.float32).reshape(-1, 3))
+    out = np.zeros((max(1, len(pts)), 3), np.float32)
+    n = L.csmh_voxel_filter(which, pts.reshape(-1) if len(pts) else np.zeros(3, np.float32), len(pts), a, b, c,
+                            out.reshape(-1))
+    return out[:n]
+
+
+def voxel_filter(points, resolution):
+    """sensor::VoxelFilter: one point per voxel of edge `resolution`, reservoir-sampled in point order."""
+    return _voxel_filter(0, points, resolution)
+
+
+def adaptive_voxel_filter(points, max_length, min_num_points, max_range):
+    """sensor::AdaptiveVoxelFilter."""
+    return _voxel_filter(1, points, max_length, min_num_points, max_range)
+
+
+def voxel_filter_edge(points, rad, voxeledgeratio):
+    """sensor::VoxelFilterEdge (this fork's addition)."""
+    return _voxel_filter(2, points, rad, voxeledgeratio)

@@ -47,6 +47,11 @@ class LuaParameterDictionary {
   bool HasKey(const std::string& key) const { return values_.count(key) != 0; }
   double GetDouble(const std::string& key) { return std::atof(Take(key).c_str()); }
   int GetInt(const std::string& key) { return std::atoi(Take(key).c_str()); }
+  int GetNonNegativeInt(const std::string& key) {  // lua_parameter_dictionary.cc: CHECK_GE(value, 0)
+    const int value = GetInt(key);
+    CSM_CHECK(value >= 0);
+    return value;
+  }
   bool GetBool(const std::string& key) { return Take(key) == "true"; }
 
  private:

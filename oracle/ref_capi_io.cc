@@ -111,3 +111,40 @@ void oracle_decompress_point_cloud(const int32_t* point_data, int64_t words, int
 }
 
 }  // extern "C"
+
+// ---- the reference's own voxel filters (cartographer/sensor/internal/voxel_filter.cc) ----
+#include "cartographer/sensor/internal/voxel_filter.h"
+
+namespace {
+cartographer::sensor::PointCloud MakeCloud(const float* xyz, int n) {
+  std::vector<cartographer::sensor::RangefinderPoint> points(n);
+  for (int i = 0; i < n; ++i) points[i].position = Eigen::Vector3f(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+  return cartographer::sensor::PointCloud(points);
+}
+int StoreCloud(const cartographer::sensor::PointCloud& cloud, float* out_xyz) {
+  for (size_t i = 0; i < cloud.size(); ++i) {
+    out_xyz[3 * i] = cloud[i].position.x();
+    out_xyz[3 * i + 1] = cloud[i].position.y();
+    out_xyz[3 * i + 2] = cloud[i].position.z();
+  }
+  return static_cast<int>(cloud.size());
+}
+}  // namespace
+
+extern "C" {
+// which: 0 VoxelFilter(cloud, a), 1 AdaptiveVoxelFilter(cloud, {max_length a, min_num_points b,
+// max_range c}), 2 VoxelFilterEdge(cloud, rad a, voxeledgeratio b).  out_xyz holds up to n points;
+// returns the number kept.
+int oracle_voxel_filter(int which, const float* xyz, int n, float a, float b, float c, float* out_xyz) {
+  const cartographer::sensor::PointCloud cloud = MakeCloud(xyz, n);
+  if (which == 0) return StoreCloud(cartographer::sensor::VoxelFilter(cloud, a), out_xyz);
+  if (which == 1) {
+    cartographer::sensor::proto::AdaptiveVoxelFilterOptions options;
+    options.set_max_length(a);
+    options.set_min_num_points(b);
+    options.set_max_range(c);
+    return StoreCloud(cartographer::sensor::AdaptiveVoxelFilter(cloud, options), out_xyz);
+  }
+  return StoreCloud(cartographer::sensor::VoxelFilterEdge(cloud, a, b), out_xyz);
+}
+}  // extern "C"

@@ -428,3 +428,15 @@ def decompress_point_cloud(num_points, words):
         w = np.zeros(1, np.int32)
     _io().oracle_decompress_point_cloud(w, len(words), num_points, out.reshape(-1))
     return out[:num_points]
+
+
+def voxel_filter(which, points, a, b=0.0, c=0.0):
+    """The reference's own VoxelFilter (which = 0), AdaptiveVoxelFilter (1), VoxelFilterEdge (2)."""
+    L = lib()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    L.oracle_voxel_filter.argtypes = [C.c_int, f32p, C.c_int, C.c_float, C.c_float, C.c_float, f32p]
+    pts = np.ascontiguousarray(np.asarray(points, np.float32).reshape(-1, 3))
+    out = np.zeros((max(1, len(pts)), 3), np.float32)
+    n = L.oracle_voxel_filter(which, pts.reshape(-1) if len(pts) else np.zeros(3, np.float32), len(pts), a, b, c,
+                              out.reshape(-1))
+    return out[:n]
