@@ -48,6 +48,7 @@ class Result3D(C.Structure):
 
 # Symbols include/csm_b200.h declares; tests check every one is exported.
 ABI_SYMBOLS = [
+    "csm_stack2d_build_many",
     "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
     "csm_ctx_synchronize", "csm_ctx_stream", "csm_ctx_set_profiling", "csm_ctx_get_profile",
     "csm_ctx_get_tile_histogram", "csm_stack2d_build", "csm_stack2d_build_dev",
@@ -270,6 +271,25 @@ class Matcher:
         if getattr(self, "h", None):
             host().csmh_matcher_destroy(self.h)
             self.h = None
+
+    @classmethod
+    def create_many(cls, ctx, grids, linear_window, angular_window, depth):
+        """FastCorrelativeScanMatcher2D::CreateMany: one matcher per grid, their stacks built in one
+        pipelined call (csm_stack2d_build_many)."""
+        L = host()
+        L.csmh_matchers_create.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_double, C.c_double,
+                                           C.c_int, C.POINTER(C.c_void_p)]
+        L.csmh_matchers_create.restype = None
+        n = len(grids)
+        handles = (C.c_void_p * n)(*[g.h for g in grids])
+        out = (C.c_void_p * n)()
+        L.csmh_matchers_create(ctx.h, n, handles, linear_window, angular_window, depth, out)
+        matchers = []
+        for i in range(n):
+            m = cls.__new__(cls)
+            m.ctx, m.grid, m.depth, m.h = ctx, grids[i], depth, out[i]
+            matchers.append(m)
+        return matchers
 
 
 class PackedClouds:

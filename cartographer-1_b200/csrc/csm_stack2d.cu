@@ -1034,8 +1034,10 @@ int launch_build_levelwise(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_d
   return CSM_OK;
 }
 
+// upload false: the descriptor and the table are left for the caller to copy (csm_stack2d_build_many
+// sends them with the cells in one transfer); o_dev_out receives the descriptor's offset in the block.
 int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int depth,
-                 csm_stack2d** out) {
+                 csm_stack2d** out, bool upload = true, size_t* o_dev_out = nullptr) {
   CSM_REQUIRE(ctx != nullptr && out != nullptr, "ctx/out must not be NULL");
   CSM_REQUIRE(q_lut != nullptr, "q_lut must not be NULL");
   CSM_REQUIRE(depth >= 1 && depth <= CSM_MAX_DEPTH, "branch_and_bound_depth out of range");
@@ -1091,10 +1093,13 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
     s->host_view.level[i] = s->base + s->level_off[i];
     s->host_view.quad[i] = reinterpret_cast<const uint32_t*>(s->base + s->quad_off[i]);
   }
-  CSM_CUDA(cudaMemcpyAsync(s->dev, &s->host_view, sizeof(csm::StackDev), cudaMemcpyHostToDevice,
-                           ctx->stream));
-  CSM_CUDA(cudaMemcpyAsync(s->q_lut_dev, q_lut, 65536, cudaMemcpyHostToDevice, ctx->stream));
-  CSM_CUDA(cudaStreamSynchronize(ctx->stream));  // host_view/q_lut are read from pageable memory
+  if (o_dev_out != nullptr) *o_dev_out = o_dev;
+  if (upload) {
+    CSM_CUDA(cudaMemcpyAsync(s->dev, &s->host_view, sizeof(csm::StackDev), cudaMemcpyHostToDevice,
+                             ctx->stream));
+    CSM_CUDA(cudaMemcpyAsync(s->q_lut_dev, q_lut, 65536, cudaMemcpyHostToDevice, ctx->stream));
+    CSM_CUDA(cudaStreamSynchronize(ctx->stream));  // host_view/q_lut are read from pageable memory
+  }
   *out = s;
   return CSM_OK;
 }
@@ -1120,26 +1125,88 @@ int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, in
   return rc;
 }
 
+int csm_stack2d_build_many(csm_ctx* ctx, int count, const uint16_t* const* cells, const int* num_x,
+                           const int* num_y, const uint8_t* const* q_lut, int depth, csm_stack2d** out);
+
 int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
                       const uint8_t* q_lut, int depth, csm_stack2d** out) {
   CSM_REQUIRE(cells != nullptr, "cells must not be NULL");
-  int rc = create_stack(ctx, num_x, num_y, q_lut, depth, out);
-  if (rc != CSM_OK) return rc;
-  const size_t bytes = static_cast<size_t>(num_x) * num_y * sizeof(uint16_t);
-  rc = ctx->tmp0.reserve(bytes + 16);
-  if (rc == CSM_OK &&
-      cudaMemcpyAsync(ctx->tmp0.p, cells, bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
-    csm::set_error("grid upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-    rc = CSM_ERR_CUDA;
+  CSM_REQUIRE(q_lut != nullptr, "q_lut must not be NULL");
+  CSM_REQUIRE(out != nullptr, "ctx/out must not be NULL");
+  return csm_stack2d_build_many(ctx, 1, &cells, &num_x, &num_y, &q_lut, depth, out);
+}
+
+// `count` stacks, pipelined: while the device builds stack k the host stages stack k + 1.  A
+// cudaMemcpyAsync from pageable memory first waits for the stream (CUDA's API synchronisation rules),
+// so the cells, the table and the descriptor of a stack are copied by the host into one of a few pinned
+// staging blocks laid out like the tail of the stack's device block (descriptor | table | cells) and
+// travel in ONE asynchronous transfer; the build reads the cells where they land (the copy the stack
+// keeps, csm_stack2d_cells_dev).  One synchronisation at the end; on failure no stack survives.
+int csm_stack2d_build_many(csm_ctx* ctx, int count, const uint16_t* const* cells, const int* num_x,
+                           const int* num_y, const uint8_t* const* q_lut, int depth, csm_stack2d** out) {
+  CSM_REQUIRE(ctx != nullptr && count >= 0, "ctx must not be NULL, count not negative");
+  if (count == 0) return CSM_OK;
+  CSM_REQUIRE(out != nullptr, "out must not be NULL");
+  for (int k = 0; k < count; ++k) out[k] = nullptr;
+  CSM_REQUIRE(cells != nullptr && num_x != nullptr && num_y != nullptr && q_lut != nullptr, "NULL argument");
+  for (int k = 0; k < count; ++k) CSM_REQUIRE(cells[k] != nullptr && q_lut[k] != nullptr, "cells / q_lut must not be NULL");
+  CSM_CUDA(cudaSetDevice(ctx->device));
+  constexpr int kSlots = 3;
+  const size_t head = ((sizeof(csm::StackDev) + 255) & ~static_cast<size_t>(255)) + 65536;  // descriptor | table
+  size_t slot_bytes = 0;
+  for (int k = 0; k < count; ++k) {
+    CSM_REQUIRE(num_x[k] >= 1 && num_y[k] >= 1 && num_x[k] <= 30000 && num_y[k] <= 30000, "cell limits out of range");
+    slot_bytes = std::max(slot_bytes, head + sizeof(uint16_t) * static_cast<size_t>(num_x[k]) * num_y[k]);
   }
-  if (rc == CSM_OK) rc = launch_build(ctx, *out, ctx->tmp0.as<uint16_t>());
+  const int slots = std::min(kSlots, count);
+  void* slot[kSlots] = {nullptr, nullptr, nullptr};
+  size_t slot_cap[kSlots] = {0, 0, 0};
+  cudaEvent_t slot_free[kSlots] = {nullptr, nullptr, nullptr};
+  int rc = CSM_OK;
+  for (int i = 0; i < slots && rc == CSM_OK; ++i) {
+    rc = ctx->pool.take(true, slot_bytes, &slot[i], &slot_cap[i]);
+    if (rc == CSM_OK && cudaEventCreateWithFlags(&slot_free[i], cudaEventDisableTiming) != cudaSuccess) rc = CSM_ERR_CUDA;
+  }
+  if (rc != CSM_OK) csm::set_error("staging for %d stack builds failed: %s", count, cudaGetErrorString(cudaGetLastError()));
+  for (int k = 0; k < count && rc == CSM_OK; ++k) {
+    size_t o_dev = 0;
+    rc = create_stack(ctx, num_x[k], num_y[k], q_lut[k], depth, &out[k], /*upload=*/false, &o_dev);
+    if (rc != CSM_OK) break;
+    csm_stack2d* s = out[k];
+    const int i = k % slots;
+    if (k >= slots && cudaEventSynchronize(slot_free[i]) != cudaSuccess) {  // the transfer that used the slot is done
+      csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = CSM_ERR_CUDA;
+      break;
+    }
+    uint8_t* stage = static_cast<uint8_t*>(slot[i]);
+    const size_t cell_bytes = sizeof(uint16_t) * static_cast<size_t>(num_x[k]) * num_y[k];
+    memcpy(stage, &s->host_view, sizeof(csm::StackDev));
+    memcpy(stage + head - 65536, q_lut[k], 65536);
+    memcpy(stage + head, cells[k], cell_bytes);
+    // descriptor, table and cells are contiguous in the stack's block, in this order (create_stack)
+    if (cudaMemcpyAsync(s->base + o_dev, stage, head + cell_bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+        cudaEventRecord(slot_free[i], ctx->stream) != cudaSuccess) {
+      csm::set_error("grid upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = CSM_ERR_CUDA;
+      break;
+    }
+    rc = launch_build(ctx, s, s->cells_dev);
+  }
   if (rc == CSM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
     csm::set_error("stack build failed: %s", cudaGetErrorString(cudaGetLastError()));
     rc = CSM_ERR_CUDA;
   }
+  if (rc != CSM_OK) cudaStreamSynchronize(ctx->stream);  // nothing may still read a staging block
+  for (int i = 0; i < slots; ++i) {
+    if (slot_free[i] != nullptr) cudaEventDestroy(slot_free[i]);
+    if (slot[i] != nullptr) ctx->pool.give(true, slot[i], slot_cap[i]);
+  }
   if (rc != CSM_OK) {  // no half-built stack escapes
-    csm_stack2d_destroy(ctx, *out);
-    *out = nullptr;
+    for (int k = 0; k < count; ++k) {
+      if (out[k] != nullptr) csm_stack2d_destroy(ctx, out[k]);
+      out[k] = nullptr;
+    }
   }
   return rc;
 }

@@ -160,6 +160,44 @@ FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
   Build(grid);
 }
 
+FastCorrelativeScanMatcher2D::FastCorrelativeScanMatcher2D(
+    const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options, DeviceContext* context,
+    Prebuilt)
+    : options_(options), limits_(grid.limits()), context_(context) {
+  CSM_CHECK(options_.branch_and_bound_depth() >= 1);
+  min_score_ = 1.f - grid.GetMaxCorrespondenceCost();
+  max_score_ = 1.f - grid.GetMinCorrespondenceCost();
+  build_context_ = context_->get();
+  device_ = context_->device();
+}
+
+std::vector<std::unique_ptr<FastCorrelativeScanMatcher2D>> FastCorrelativeScanMatcher2D::CreateMany(
+    const std::vector<const Grid2D*>& grids, const proto::FastCorrelativeScanMatcherOptions2D& options,
+    DeviceContext* context) {
+  const size_t n = grids.size();
+  std::vector<std::unique_ptr<FastCorrelativeScanMatcher2D>> matchers(n);
+  if (n == 0) return matchers;
+  std::vector<std::vector<uint8>> tables(n);
+  std::vector<const uint16_t*> cells(n);
+  std::vector<const uint8_t*> luts(n);
+  std::vector<int> num_x(n), num_y(n);
+  for (size_t i = 0; i != n; ++i) {
+    CSM_CHECK(grids[i] != nullptr);
+    matchers[i].reset(new FastCorrelativeScanMatcher2D(*grids[i], options, context, Prebuilt()));
+    tables[i] = ComputeQuantizationTable(*grids[i]);
+    cells[i] = grids[i]->correspondence_cost_cells().data();
+    luts[i] = tables[i].data();
+    num_x[i] = grids[i]->limits().cell_limits().num_x_cells;
+    num_y[i] = grids[i]->limits().cell_limits().num_y_cells;
+  }
+  std::vector<csm_stack2d*> stacks(n, nullptr);
+  CheckOk(csm_stack2d_build_many(context->get(), static_cast<int>(n), cells.data(), num_x.data(), num_y.data(),
+                                 luts.data(), options.branch_and_bound_depth(), stacks.data()),
+          "csm_stack2d_build_many");
+  for (size_t i = 0; i != n; ++i) matchers[i]->stack_ = stacks[i];
+  return matchers;
+}
+
 void FastCorrelativeScanMatcher2D::Build(const Grid2D& grid) {
   CSM_CHECK(options_.branch_and_bound_depth() >= 1);
   min_score_ = 1.f - grid.GetMaxCorrespondenceCost();

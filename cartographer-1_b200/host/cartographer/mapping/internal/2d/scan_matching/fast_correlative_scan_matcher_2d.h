@@ -118,6 +118,13 @@ class FastCorrelativeScanMatcher2D {
                                DeviceContext* context);
   ~FastCorrelativeScanMatcher2D();
 
+  // Several matchers at once (the submaps of a loaded map, a burst of finished submaps): the
+  // same matchers as constructing one per grid, in the order of `grids`; their stacks are built by
+  // csm_stack2d_build_many -- the host stages grid k + 1 while the device builds stack k.
+  static std::vector<std::unique_ptr<FastCorrelativeScanMatcher2D>> CreateMany(
+      const std::vector<const Grid2D*>& grids, const proto::FastCorrelativeScanMatcherOptions2D& options,
+      DeviceContext* context);
+
   FastCorrelativeScanMatcher2D(const FastCorrelativeScanMatcher2D&) = delete;
   FastCorrelativeScanMatcher2D& operator=(const FastCorrelativeScanMatcher2D&) = delete;
 
@@ -194,6 +201,9 @@ class FastCorrelativeScanMatcher2D {
   DeviceContext* context() const { return context_; }
 
  private:
+  struct Prebuilt {};  // CreateMany: every member but the stack
+  FastCorrelativeScanMatcher2D(const Grid2D& grid, const proto::FastCorrelativeScanMatcherOptions2D& options,
+                               DeviceContext* context, Prebuilt);
   void Build(const Grid2D& grid);
 
   const proto::FastCorrelativeScanMatcherOptions2D options_;

@@ -163,6 +163,18 @@ void* csmh_matcher_create(void* ctx, void* grid, double linear_window, double an
                                           static_cast<DeviceContext*>(ctx));
 }
 void csmh_matcher_destroy(void* m) { delete static_cast<FastCorrelativeScanMatcher2D*>(m); }
+// FastCorrelativeScanMatcher2D::CreateMany: `n` matchers (handles as csmh_matcher_create's) in out[].
+void csmh_matchers_create(void* ctx, int n, void* const* grids, double linear_window, double angular_window,
+                          int depth, void** out) {
+  mapping::scan_matching::proto::FastCorrelativeScanMatcherOptions2D o;
+  o.set_linear_search_window(linear_window);
+  o.set_angular_search_window(angular_window);
+  o.set_branch_and_bound_depth(depth);
+  std::vector<const mapping::Grid2D*> list(n);
+  for (int i = 0; i < n; ++i) list[i] = static_cast<GridHolder*>(grids[i])->grid.get();
+  auto matchers = FastCorrelativeScanMatcher2D::CreateMany(list, o, static_cast<DeviceContext*>(ctx));
+  for (int i = 0; i < n; ++i) out[i] = matchers[i].release();
+}
 const void* csmh_matcher_stack(void* m) {
   return static_cast<FastCorrelativeScanMatcher2D*>(m)->stack();
 }

@@ -90,6 +90,15 @@ int csm_ctx_get_tile_histogram(csm_ctx* ctx, double* hist);
  */
 int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
                       const uint8_t* q_lut, int depth, csm_stack2d** out);
+/* `count` stacks in one call, with the semantics of `count` csm_stack2d_build calls (cells[k] is
+ * num_x[k] x num_y[k], q_lut[k] its table; one depth): the reference builds one
+ * PrecomputationGridStack2D per FastCorrelativeScanMatcher2D constructor
+ * (fast_correlative_scan_matcher_2d.cc:171-186, 198-202); a caller that has several finished submaps at
+ * once (a loaded map, a burst of constraint searches) hands them over together and the host's staging of
+ * stack k + 1 overlaps the device's build of stack k.  Synchronises once, at the end; on failure every
+ * out[k] is NULL.  csm_stack2d_build is the count = 1 case. */
+int csm_stack2d_build_many(csm_ctx* ctx, int count, const uint16_t* const* cells, const int* num_x,
+                           const int* num_y, const uint8_t* const* q_lut, int depth, csm_stack2d** out);
 /* Same, with `cells_dev` already resident in device memory (benchmark path). */
 int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, int num_y,
                           const uint8_t* q_lut, int depth, csm_stack2d** out);

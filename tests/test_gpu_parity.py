@@ -29,6 +29,30 @@ def test_stack_bytes_identical(csm, gpu_ctx, nx, ny, depth):
         assert np.array_equal(a, b), "level %d differs" % lvl
 
 
+def test_matchers_created_together_equal_matchers_created_one_by_one(csm, gpu_ctx):
+    """FastCorrelativeScanMatcher2D::CreateMany / csm_stack2d_build_many: seven grids of mixed sizes
+    (more than the staging slots, so slots are reused) -> the byte levels, the quad words and the kept
+    uint16 cells of every stack equal those of a matcher constructed alone, and a search on each finds
+    the same winner."""
+    shapes = [(250, 250), (37, 5), (400, 400), (1, 1), (129, 257), (640, 480), (250, 250)]
+    depth = 6
+    cells = [_tiny_grid(900 + k, nx, ny) for k, (nx, ny) in enumerate(shapes)]
+    grids = [csm.Grid(c, 0.05, 1.0, 1.0) for c in cells]
+    many = csm.Matcher.create_many(gpu_ctx, grids, 1.0, 0.1, depth)
+    assert len(many) == len(grids)
+    pts = np.array([[0.3, 0.2, 0], [-0.4, 0.1, 0], [0.1, -0.35, 0], [0.5, 0.5, 0]], np.float32)
+    for k, g in enumerate(grids):
+        alone = csm.Matcher(gpu_ctx, g, 1.0, 0.1, depth)
+        for lvl in range(depth):
+            assert np.array_equal(alone.level(lvl), many[k].level(lvl)), (k, lvl)
+            assert np.array_equal(alone.quad(lvl), many[k].quad(lvl)), (k, lvl)
+        a = csm.match_batch(gpu_ctx, [alone], [pts], [0.0])[0]
+        b = csm.match_batch(gpu_ctx, [many[k]], [pts], [0.0])[0]
+        assert (a.found, a.scan_index, a.x_index_offset, a.y_index_offset, a.score) == \
+            (b.found, b.scan_index, b.x_index_offset, b.y_index_offset, b.score)
+    assert csm.Matcher.create_many(gpu_ctx, [], 1.0, 0.1, depth) == []
+
+
 @pytest.mark.parametrize("nx,ny,depth", [(250, 250, 4), (4, 4, 8), (1, 1, 3), (37, 5, 7), (3, 2, 2),
                                          (400, 400, 7), (129, 257, 6), (1000, 1000, 7)])
 def test_stack_quad_words_identical(csm, gpu_ctx, nx, ny, depth):
