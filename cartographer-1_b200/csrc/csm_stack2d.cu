@@ -657,6 +657,8 @@ struct Rows3Args {
   int lin_pitch, skw_pitch;   // words per staged row (linear / skewed copy)
   int npw4, items;            // 16-byte chunks of a next-level row, quad work items of a row
   int rows_total, rows_per_block;  // a block builds rows_per_block consecutive rows
+  int nq;                     // kVec: in / 4, groups of four consecutive ii
+  unsigned int nq_magic;      // ceil(2^32 / nq), 0 when nq == 1
 };
 
 __device__ __forceinline__ uint4 max4_u8x16(const uint4& a, const uint4& b, const uint4& c, const uint4& d) {
@@ -664,6 +666,11 @@ __device__ __forceinline__ uint4 max4_u8x16(const uint4& a, const uint4& b, cons
                     max4_u8x4(a.w, b.w, c.w, d.w));
 }
 
+// kVec: the quad words leave as uint4s -- a thread makes the words of four consecutive ii for four
+// adjacent phases (16 words from 16 staged taps) and stores one 16-byte run per phase plane, instead
+// of four 4-byte stores with their own 64-bit addresses (the quad loop was ~80 instructions per four
+// words: more than half of the kernel's issue slots).  Needs in % 4 == 0 (create_stack pads it).
+template <bool kVec>
 __global__ void __launch_bounds__(kThreads)
 k_stack_rows3(const Rows3Args p) {
   extern __shared__ uint4 rows128[];
@@ -763,7 +770,58 @@ k_stack_rows3(const Rows3Args p) {
   };
   uint32_t* __restrict__ const orow =
       a.quad + (static_cast<size_t>((v & (two_s - 1)) << sh) * a.jn + (v >> sh)) * a.in;
-  if (a.log2s == 0) {
+  auto quad4 = [](uint32_t c0, uint32_t l0, uint32_t c1, uint32_t l1, uint32_t (&q)[4]) {
+    const uint32_t a_lo = __byte_perm(l1, l0, 0x5140), a_hi = __byte_perm(l1, l0, 0x7362);
+    const uint32_t b_lo = __byte_perm(c1, c0, 0x5140), b_hi = __byte_perm(c1, c0, 0x7362);
+    q[0] = __byte_perm(a_lo, b_lo, 0x5410);
+    q[1] = __byte_perm(a_lo, b_lo, 0x7632);
+    q[2] = __byte_perm(a_hi, b_hi, 0x5410);
+    q[3] = __byte_perm(a_hi, b_hi, 0x7632);
+  };
+  if (kVec && a.log2s == 0) {
+    // 2 phases: staged words 2t and 2t + 1 hold X = 8t .. 8t + 7 = (pu, ii) = (0, 4t), (1, 4t), (0, 4t + 1), ...
+    for (int t = threadIdx.x; t < p.nq; t += nthr) {
+      const int xw = 2 * t + p.pad;
+      const uint32_t P0 = skw_cur[skew(xw - 1)], A0 = skw_cur[skew(xw)], B0 = skw_cur[skew(xw + 1)];
+      const uint32_t P1 = skw_up[skew(xw - 1)], A1 = skw_up[skew(xw)], B1 = skw_up[skew(xw + 1)];
+      uint32_t qa[4], qb[4];
+      quad4(A0, __funnelshift_l(P0, A0, 8), A1, __funnelshift_l(P1, A1, 8), qa);
+      quad4(B0, __funnelshift_l(A0, B0, 8), B1, __funnelshift_l(A1, B1, 8), qb);
+      uint32_t* o = orow + 4 * t;
+      *reinterpret_cast<uint4*>(o) = make_uint4(qa[0], qa[2], qb[0], qb[2]);
+      *reinterpret_cast<uint4*>(o + plane) = make_uint4(qa[1], qa[3], qb[1], qb[3]);
+    }
+  } else if (kVec) {
+    const int step_words = two_s >> 2, groups = two_s >> 2;
+    const int t0 = threadIdx.x;
+    int pg = p.nq_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(t0), p.nq_magic)) : t0;
+    int q = t0 - pg * p.nq;
+    const int dpg = p.nq_magic ? static_cast<int>(__umulhi(static_cast<unsigned int>(nthr), p.nq_magic)) : nthr;
+    const int dq = nthr - dpg * p.nq;
+    while (pg < groups) {
+      uint32_t w[4][4];  // [phase within the group][ii within the four]
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t c0, l0, c1, l1, qk[4];
+        taps((4 * q + k) * step_words + pg + p.pad, c0, l0, c1, l1);
+        quad4(c0, l0, c1, l1, qk);
+        w[0][k] = qk[0];
+        w[1][k] = qk[1];
+        w[2][k] = qk[2];
+        w[3][k] = qk[3];
+      }
+      uint32_t* o = orow + (static_cast<size_t>(pg << 2) * plane + 4 * q);
+#pragma unroll
+      for (int ph = 0; ph < 4; ++ph)
+        *reinterpret_cast<uint4*>(o + ph * plane) = make_uint4(w[ph][0], w[ph][1], w[ph][2], w[ph][3]);
+      pg += dpg;
+      q += dq;
+      if (q >= p.nq) {
+        q -= p.nq;
+        ++pg;
+      }
+    }
+  } else if (a.log2s == 0) {
     for (int k = threadIdx.x; 2 * k < a.in; k += nthr) {
       uint32_t c0, l0, c1, l1;
       taps(k + p.pad, c0, l0, c1, l1);
@@ -866,7 +924,7 @@ int launch_build_rows(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
   return CSM_OK;
 }
 
-int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
+int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev, bool vec = true) {
   launch_level0(ctx, s, cells_dev);
   std::vector<Rows3Args> args(s->depth);
   size_t max_smem = 0;
@@ -893,6 +951,9 @@ int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
     p.skw_pitch = ((nw + (nw >> 5) + 2) + 3) & ~3;
     p.npw4 = a.next_pitch >> 4;
     p.items = i == 0 ? (a.in + 1) / 2 : ((2 << i) >> 2) * a.in;
+    p.nq = a.in >> 2;
+    p.nq_magic = p.nq > 1 ? static_cast<unsigned int>((0x100000000ull + p.nq - 1) / p.nq) : 0u;
+    if (vec) p.items = i == 0 ? p.nq : ((2 << i) >> 2) * p.nq;
     p.rows_total = a.jn << (i + 1);
     // one wave: as many rows per block as it takes to fit the grid into the resident block slots
     p.rows_per_block = std::max(1, (p.rows_total + ctx->num_sms * 8 - 1) / (ctx->num_sms * 8));
@@ -902,8 +963,8 @@ int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
     if (p.items >= 65536) return launch_build_rows(ctx, s, cells_dev);
   if (max_smem > 200 * 1024) return launch_build_rows(ctx, s, cells_dev);
   if (max_smem > 48 * 1024)
-    CSM_CUDA(cudaFuncSetAttribute(k_stack_rows3, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(max_smem)));
+    CSM_CUDA(cudaFuncSetAttribute(vec ? k_stack_rows3<true> : k_stack_rows3<false>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(max_smem)));
   for (int i = 0; i < s->depth; ++i) {
     const Rows3Args& p = args[i];
     const size_t smem = (2 * static_cast<size_t>(p.lin_pitch) + 2 * p.skw_pitch) * 4;
@@ -922,7 +983,7 @@ int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) 
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     ++ctx->launches;
-    CSM_CUDA(cudaLaunchKernelEx(&cfg, k_stack_rows3, p));
+    CSM_CUDA(cudaLaunchKernelEx(&cfg, vec ? k_stack_rows3<true> : k_stack_rows3<false>, p));
   }
   CSM_CUDA(cudaGetLastError());
   return CSM_OK;
@@ -999,10 +1060,12 @@ int launch_build(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev) {
     if (e != nullptr && strcmp(e, "fused") == 0) return 1;
     if (e != nullptr && strcmp(e, "rows2") == 0) return 3;
     if (e != nullptr && strcmp(e, "rows1") == 0) return 4;  // round 1's row kernel
+    if (e != nullptr && strcmp(e, "rows3") == 0) return 5;  // 4-byte quad stores (before the uint4 ones)
     return 0;
   }();
   if (mode == 3) return launch_build_rows2(ctx, s, cells_dev);
-  if (mode == 0) return launch_build_rows3(ctx, s, cells_dev);
+  if (mode == 0) return launch_build_rows3(ctx, s, cells_dev, true);
+  if (mode == 5) return launch_build_rows3(ctx, s, cells_dev, false);
   if (mode == 1 && s->depth <= kFusedMaxDepth) return launch_build_fused(ctx, s, cells_dev);
   if (mode == 2) return launch_build_levelwise(ctx, s, cells_dev);
   return launch_build_rows(ctx, s, cells_dev);
@@ -1061,7 +1124,10 @@ int create_stack(csm_ctx* ctx, int num_x, int num_y, const uint8_t* q_lut, int d
   memset(&s->host_view, 0, sizeof(s->host_view));
   for (int i = 0; i < depth; ++i) {
     const int two_s = 2 << i;
-    const int in = (num_x + two_s - 1 + two_s - 1) / two_s;  // ceil((num_x + 2s - 1) / 2s)
+    // ceil((num_x + 2s - 1) / 2s), rounded up to a multiple of 4 words: every row of every phase plane
+    // starts on a 16-byte boundary, so the build stores whole uint4s (k_stack_rows3<true>); the
+    // extra words lie beyond the level and hold zeros like everything outside it.
+    const int in = (((num_x + two_s - 1 + two_s - 1) / two_s) + 3) & ~3;
     const int jn = (num_y + two_s - 1 + two_s - 1) / two_s;
     s->host_view.in[i] = in;
     s->host_view.jn[i] = jn;
