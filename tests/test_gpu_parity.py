@@ -16,7 +16,8 @@ def _tiny_grid(seed, nx, ny):
 
 
 @pytest.mark.parametrize("nx,ny,depth", [(250, 250, 4), (4, 4, 8), (1, 1, 3), (37, 5, 7),
-                                         (400, 400, 7), (129, 257, 6)])
+                                         (400, 400, 7), (129, 257, 6),
+                                         (1001, 777, 5), (2047, 300, 4)])  # odd widths: rows that start unaligned
 def test_stack_bytes_identical(csm, gpu_ctx, nx, ny, depth):
     cells = _tiny_grid(nx * 1000 + ny, nx, ny)
     og = ob.OracleGrid(cells, 0.05, 1.0, 1.0)
