@@ -671,7 +671,7 @@ __device__ __forceinline__ uint4 max4_u8x16(const uint4& a, const uint4& b, cons
 // of four 4-byte stores with their own 64-bit addresses (the quad loop was ~80 instructions per four
 // words: more than half of the kernel's issue slots).  Needs in % 4 == 0 (create_stack pads it).
 template <bool kVec>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 k_stack_rows3(const Rows3Args p) {
   extern __shared__ uint4 rows128[];
   cudaGridDependencySynchronize();
@@ -956,7 +956,9 @@ int launch_build_rows3(csm_ctx* ctx, csm_stack2d* s, const uint16_t* cells_dev, 
     if (vec) p.items = i == 0 ? p.nq : ((2 << i) >> 2) * p.nq;
     p.rows_total = a.jn << (i + 1);
     // one wave: as many rows per block as it takes to fit the grid into the resident block slots
-    p.rows_per_block = std::max(1, (p.rows_total + ctx->num_sms * 8 - 1) / (ctx->num_sms * 8));
+    // (k_stack_rows3 is held to 32 registers: 16 blocks of 128 threads per SM)
+    const int slots = ctx->num_sms * (vec ? 16 : 8);
+    p.rows_per_block = std::max(1, (p.rows_total + slots - 1) / slots);
     max_smem = std::max<size_t>(max_smem, (2 * static_cast<size_t>(p.lin_pitch) + 2 * p.skw_pitch) * 4);
   }
   for (const Rows3Args& p : args)  // t / in via __umulhi needs t < 2^16
