@@ -370,7 +370,8 @@ def run_b200(args):
 
     ctx = pkg.Context(local)
     raw = C.c_void_p(ctx.raw)
-    grids = [pkg.Grid(job.cells[s], *job.limits[s]) for s in my_submaps]
+    # the submaps' grids: host buffers, page-locked (the step copies them from pinned host memory)
+    grids = [pkg.Grid(job.cells[s], *job.limits[s]).pin() for s in my_submaps]
     matchers = [pkg.Matcher(ctx, g, LINEAR, ANGULAR, DEPTH) for g in grids]
     cells_dev = [torch.from_numpy(job.cells[s].view(np.int16)).cuda() for s in my_submaps]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")

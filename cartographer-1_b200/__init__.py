@@ -48,7 +48,7 @@ class Result3D(C.Structure):
 
 # Symbols include/csm_b200.h declares; tests check every one is exported.
 ABI_SYMBOLS = [
-    "csm_stack2d_build_many",
+    "csm_stack2d_build_many", "csm_host_register", "csm_host_unregister",
     "csm_last_error", "csm_device_count", "csm_ctx_create", "csm_ctx_destroy",
     "csm_ctx_synchronize", "csm_ctx_stream", "csm_ctx_set_profiling", "csm_ctx_get_profile",
     "csm_ctx_get_tile_histogram", "csm_stack2d_build", "csm_stack2d_build_dev",
@@ -210,6 +210,16 @@ class Grid:
         out = np.empty(65536, dtype=np.uint8)
         host().csmh_quantization_table(self.h, out)
         return out
+
+    def pin(self):
+        """Page-locks the cells where they are: Matcher.create_many then copies them to the device
+        with an asynchronous transfer instead of through a staging block."""
+        L = host()
+        L.csmh_grid_pin.argtypes = [C.c_void_p]
+        rc = L.csmh_grid_pin(self.h)
+        if rc != 0:
+            raise RuntimeError(abi().csm_last_error().decode())
+        return self
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -1251,9 +1251,16 @@ int csm_stack2d_build_many(csm_ctx* ctx, int count, const uint16_t* const* cells
     const size_t cell_bytes = sizeof(uint16_t) * static_cast<size_t>(num_x[k]) * num_y[k];
     memcpy(stage, &s->host_view, sizeof(csm::StackDev));
     memcpy(stage + head - 65536, q_lut[k], 65536);
-    memcpy(stage + head, cells[k], cell_bytes);
+    // cells the caller page-locked (csm_host_register, cudaHostAlloc) need no staging copy
+    cudaPointerAttributes where;
+    const bool locked = cudaPointerGetAttributes(&where, cells[k]) == cudaSuccess && where.type == cudaMemoryTypeHost;
+    cudaGetLastError();  // an unregistered pointer is reported as an error by older drivers
+    if (!locked) memcpy(stage + head, cells[k], cell_bytes);
     // descriptor, table and cells are contiguous in the stack's block, in this order (create_stack)
-    if (cudaMemcpyAsync(s->base + o_dev, stage, head + cell_bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+    if (cudaMemcpyAsync(s->base + o_dev, stage, locked ? head : head + cell_bytes, cudaMemcpyHostToDevice,
+                        ctx->stream) != cudaSuccess ||
+        (locked && cudaMemcpyAsync(s->cells_dev, cells[k], cell_bytes, cudaMemcpyHostToDevice, ctx->stream) !=
+                       cudaSuccess) ||
         cudaEventRecord(slot_free[i], ctx->stream) != cudaSuccess) {
       csm::set_error("grid upload failed: %s", cudaGetErrorString(cudaGetLastError()));
       rc = CSM_ERR_CUDA;
@@ -1367,6 +1374,17 @@ int csm_stack2d_quad(csm_ctx* ctx, const csm_stack2d* s, int level, uint32_t* ou
                              ctx->stream));
     CSM_CUDA(cudaStreamSynchronize(ctx->stream));
   }
+  return CSM_OK;
+}
+
+int csm_host_register(void* ptr, size_t bytes) {
+  CSM_REQUIRE(ptr != nullptr && bytes > 0, "nothing to register");
+  CSM_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+  return CSM_OK;
+}
+int csm_host_unregister(void* ptr) {
+  CSM_REQUIRE(ptr != nullptr, "nothing to unregister");
+  CSM_CUDA(cudaHostUnregister(ptr));
   return CSM_OK;
 }
 

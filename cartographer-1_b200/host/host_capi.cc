@@ -67,6 +67,17 @@ void* csmh_tsdf_create(const uint16_t* tsd_cells, const uint16_t* weight_cells, 
   return h;
 }
 void csmh_grid_destroy(void* g) { delete static_cast<GridHolder*>(g); }
+// Page-locks the grid's cells where they are (csm_host_register), so that stack builds copy them with
+// an asynchronous transfer; released when the handle is destroyed.  The grid must not grow afterwards.
+int csmh_grid_pin(void* g) {
+  GridHolder* h = static_cast<GridHolder*>(g);
+  if (h->locked != nullptr) return 0;
+  const std::vector<uint16_t>& cells = h->grid->correspondence_cost_cells();
+  if (cells.empty()) return 0;
+  const int rc = csm_host_register(const_cast<uint16_t*>(cells.data()), sizeof(uint16_t) * cells.size());
+  if (rc == 0) h->locked = cells.data();
+  return rc;
+}
 
 // TSDFRangeDataInserter2D on a TSDF grid handle (csmh_tsdf_create / csmh_grid_from_proto); the grid
 // may grow.  options9 = {truncation_distance, maximum_weight, update_free_space, num_normal_samples,

@@ -99,6 +99,11 @@ int csm_stack2d_build(csm_ctx* ctx, const uint16_t* cells, int num_x, int num_y,
  * out[k] is NULL.  csm_stack2d_build is the count = 1 case. */
 int csm_stack2d_build_many(csm_ctx* ctx, int count, const uint16_t* const* cells, const int* num_x,
                            const int* num_y, const uint8_t* const* q_lut, int depth, csm_stack2d** out);
+/* Page-locks (cudaHostRegister) / releases a host range the caller owns, e.g. a finished submap's
+ * cells: csm_stack2d_build_many then copies the cells straight from the caller's memory with an
+ * asynchronous transfer instead of through its staging blocks.  Plain pageable memory keeps working. */
+int csm_host_register(void* ptr, size_t bytes);
+int csm_host_unregister(void* ptr);
 /* Same, with `cells_dev` already resident in device memory (benchmark path). */
 int csm_stack2d_build_dev(csm_ctx* ctx, const uint16_t* cells_dev, int num_x, int num_y,
                           const uint8_t* q_lut, int depth, csm_stack2d** out);

@@ -39,6 +39,8 @@ def test_matchers_created_together_equal_matchers_created_one_by_one(csm, gpu_ct
     depth = 6
     cells = [_tiny_grid(900 + k, nx, ny) for k, (nx, ny) in enumerate(shapes)]
     grids = [csm.Grid(c, 0.05, 1.0, 1.0) for c in cells]
+    for g in grids[::2]:
+        g.pin()  # page-locked cells travel without the staging copy; the others through it
     many = csm.Matcher.create_many(gpu_ctx, grids, 1.0, 0.1, depth)
     assert len(many) == len(grids)
     pts = np.array([[0.3, 0.2, 0], [-0.4, 0.1, 0], [0.1, -0.35, 0], [0.5, 0.5, 0]], np.float32)
