@@ -237,3 +237,48 @@ def test_reader_refuses_what_the_reference_refuses(csm, tmp_path):
     orphan.submap.submap_id.submap_index = 9
     orphan.submap.submap_2d.finished = True
     assert load_aborts(pf.pbstream_bytes(good + [orphan.SerializeToString()]))
+
+
+def test_mutated_messages_never_crash_the_reader(csm, tmp_path):
+    """Truncated and bit-flipped records (inside valid gzip members, so the damage reaches the wire
+    reader): the loader either returns or stops on one of its checks (SIGABRT, as the reference's
+    CHECKs do) -- never a segmentation fault, a hang or a runaway allocation."""
+    import signal
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    rng = np.random.default_rng(11)
+    submaps, nodes, constraints = _state_2d(rng, num_submaps=2, nodes_per_submap=1)
+    good = pf.mapping_state_messages(submaps, nodes, constraints)
+    paths = []
+    for case in range(24):
+        msgs = list(good)
+        k = int(rng.integers(1, len(msgs)))  # not the header: the version check would stop everything
+        m = bytearray(msgs[k])
+        if case % 3 == 0 and len(m) > 2:
+            m = m[: int(rng.integers(1, len(m)))]                       # truncated record
+        elif case % 3 == 1:
+            for _ in range(int(rng.integers(1, 6))):
+                m[int(rng.integers(0, len(m)))] ^= 1 << int(rng.integers(0, 8))  # flipped bits
+        else:
+            at = int(rng.integers(0, len(m)))
+            m[at:at] = bytes(rng.integers(0, 256, int(rng.integers(1, 12)), dtype=np.uint8))  # inserted garbage
+        msgs[k] = bytes(m)
+        path = tmp_path / ("mutated_%d.pbstream" % case)
+        path.write_bytes(pf.pbstream_bytes(msgs))
+        paths.append(str(path))
+    code = ("import sys, os, resource; sys.path.insert(0, %r); import conftest; csm = conftest.load_package()\n"
+            "resource.setrlimit(resource.RLIMIT_AS, (8 << 30, 8 << 30))\n"
+            "for p in sys.argv[1:]:\n"
+            "    pid = os.fork()\n"
+            "    if pid == 0:\n"
+            "        s = csm.MappingState(p); os._exit(0)\n"
+            "    _, status = os.waitpid(pid, 0)\n"
+            "    print(p, os.WTERMSIG(status) if os.WIFSIGNALED(status) else 0, flush=True)\n"
+            % os.path.join(root, "tests"))
+    out = subprocess.run([sys.executable, "-c", code] + paths, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr[-2000:]
+    ends = [int(line.split()[-1]) for line in out.stdout.strip().splitlines()]
+    assert len(ends) == len(paths)
+    assert set(ends) <= {0, int(signal.SIGABRT)}, ends
+    assert int(signal.SIGABRT) in ends  # at least one mutation was caught by a check
