@@ -1141,3 +1141,17 @@ def adaptive_voxel_filter(points, max_length, min_num_points, max_range):
 def voxel_filter_edge(points, rad, voxeledgeratio):
     """sensor::VoxelFilterEdge (this fork's addition)."""
     return _voxel_filter(2, points, rad, voxeledgeratio)
+
+
+def compress_point_cloud(points):
+    """sensor::CompressedPointCloud(points): the int32 words of proto::CompressedPointCloud.point_data."""
+    L = host()
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    L.csmh_compress_point_cloud.argtypes = [f32p, C.c_int, C.c_void_p, C.c_int64]
+    L.csmh_compress_point_cloud.restype = C.c_int64
+    pts = np.ascontiguousarray(np.asarray(points, np.float32).reshape(-1, 3))
+    flat = pts.reshape(-1) if len(pts) else np.zeros(3, np.float32)
+    n = L.csmh_compress_point_cloud(flat, len(pts), None, 0)
+    words = np.zeros(max(1, n), dtype=np.int32)
+    L.csmh_compress_point_cloud(flat, len(pts), words.ctypes.data_as(C.c_void_p), n)
+    return words[:n]

@@ -1,7 +1,9 @@
 // Flat C entry points over the host-side point-cloud filters (cartographer/sensor/internal/
 // voxel_filter.h), for ctypes.  Product code: never touches oracle/.
+#include <cstdint>
 #include <vector>
 
+#include "cartographer/sensor/compressed_point_cloud.h"
 #include "cartographer/sensor/internal/voxel_filter.h"
 
 using namespace cartographer;
@@ -38,6 +40,18 @@ int csmh_voxel_filter(int which, const float* xyz, int n, float a, float b, floa
     return StoreCloud(sensor::AdaptiveVoxelFilter(cloud, options), out_xyz);
   }
   return StoreCloud(sensor::VoxelFilterEdge(cloud, a, b), out_xyz);
+}
+
+// sensor::CompressedPointCloud(cloud).point_data(): returns the number of int32 words (out may be
+// NULL to count; -1 when `cap` is too small).
+int64_t csmh_compress_point_cloud(const float* xyz, int n, int32_t* out, int64_t cap) {
+  const sensor::CompressedPointCloud compressed(MakeCloud(xyz, n));
+  const std::vector<int32_t>& words = compressed.point_data();
+  if (out != nullptr) {
+    if (static_cast<int64_t>(words.size()) > cap) return -1;
+    for (size_t i = 0; i < words.size(); ++i) out[i] = words[i];
+  }
+  return static_cast<int64_t>(words.size());
 }
 
 }  // extern "C"
