@@ -1155,3 +1155,69 @@ def compress_point_cloud(points):
     words = np.zeros(max(1, n), dtype=np.int32)
     L.csmh_compress_point_cloud(flat, len(pts), words.ctypes.data_as(C.c_void_p), n)
     return words[:n]
+
+
+# ---- writing grids and states back (host/cartographer/io/grid_proto_writer.h) ----
+def _sized_bytes(call):
+    n = call(None, 0)
+    if n < 0:
+        raise RuntimeError("serialization failed (%d)" % n)
+    buf = np.zeros(max(1, n), dtype=np.uint8)
+    got = call(buf.ctypes.data_as(C.c_void_p), n)
+    assert got == n
+    return buf[:n].tobytes()
+
+
+def grid_to_proto(grid):
+    """Grid2D::ToProto().SerializeAsString() of a grid handle (Grid, TsdfGrid, ProtoGrid, a state's grid)."""
+    L = host()
+    L.csmh_grid_to_proto.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+    L.csmh_grid_to_proto.restype = C.c_int64
+    return _sized_bytes(lambda out, cap: L.csmh_grid_to_proto(grid.h, out, cap))
+
+
+def hybrid_grid_to_proto(resolution, xyz, values):
+    """HybridGrid::ToProto().SerializeAsString() of the grid holding the given voxels."""
+    L = host()
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+    u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+    L.csmh_hybrid_grid_to_proto.argtypes = [C.c_float, i32p, u16p, C.c_int, C.c_void_p, C.c_int64]
+    L.csmh_hybrid_grid_to_proto.restype = C.c_int64
+    xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1)
+    values = np.ascontiguousarray(values, np.uint16)
+    if len(values) == 0:
+        xyz, values = np.zeros(3, np.int32), np.zeros(1, np.uint16)
+        n = 0
+    else:
+        n = len(values)
+    return _sized_bytes(lambda out, cap: L.csmh_hybrid_grid_to_proto(resolution, xyz, values, n, out, cap))
+
+
+def reencode_pose_graph(record):
+    """A serialized SerializedData{pose_graph} record parsed and written again."""
+    L = host()
+    L.csmh_reencode_pose_graph.argtypes = [C.c_char_p, C.c_int64, C.c_void_p, C.c_int64]
+    L.csmh_reencode_pose_graph.restype = C.c_int64
+    return _sized_bytes(lambda out, cap: L.csmh_reencode_pose_graph(record, len(record), out, cap))
+
+
+def _state_write(self, path):
+    """WriteStateToFile: submap and node records re-encoded from the state, the others as read."""
+    L = _io()
+    L.csmh_state_write.argtypes = [C.c_void_p, C.c_char_p]
+    L.csmh_state_write.restype = None
+    L.csmh_state_write(self.h, os.fsencode(path))
+
+
+def _state_set_submap_cells(self, i, cells):
+    """Replaces the cells of 2D submap i's grid (same limits), e.g. after insertions on the device."""
+    L = _io()
+    L.csmh_state_set_submap_cells.argtypes = [C.c_void_p, C.c_int, np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS"),
+                                              C.c_int64]
+    cells = np.ascontiguousarray(cells, np.uint16)
+    if L.csmh_state_set_submap_cells(self.h, i, cells.reshape(-1), cells.size) != 0:
+        raise ValueError("submap %d has no grid of %d cells" % (i, cells.size))
+
+
+MappingState.write = _state_write
+MappingState.set_submap_cells = _state_set_submap_cells

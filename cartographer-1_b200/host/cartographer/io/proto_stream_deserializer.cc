@@ -319,9 +319,9 @@ ProtoStreamDeserializer::ProtoStreamDeserializer(ProtoStreamReader* const reader
              format_version_ == static_cast<uint32_t>(kFormatVersionWithoutSubmapHistograms)) &&
             "Unsupported serialization format");
   // :56-70
-  CSM_CHECK(ReadNextSerializedData(&pose_graph_) && "Serialized stream misses PoseGraph.");
+  CSM_CHECK(ReadNextSerializedData(&pose_graph_, &raw_pose_graph_) && "Serialized stream misses PoseGraph.");
   CSM_CHECK(pose_graph_.has_pose_graph() && "Serialized stream order corrupt. Expecting `PoseGraph` after `SerializationHeader`");
-  CSM_CHECK(ReadNextSerializedData(&all_trajectory_builder_options_) &&
+  CSM_CHECK(ReadNextSerializedData(&all_trajectory_builder_options_, &raw_options_) &&
             "Serialized stream misses `AllTrajectoryBuilderOptions`.");
   CSM_CHECK(all_trajectory_builder_options_.has_all_trajectory_builder_options() &&
             "Serialized stream order corrupt. Expecting `AllTrajectoryBuilderOptions` after PoseGraph");
@@ -329,10 +329,11 @@ ProtoStreamDeserializer::ProtoStreamDeserializer(ProtoStreamReader* const reader
             all_trajectory_builder_options_.options_with_sensor_ids_size());
 }
 
-bool ProtoStreamDeserializer::ReadNextSerializedData(SerializedData* data) {
+bool ProtoStreamDeserializer::ReadNextSerializedData(SerializedData* data, std::string* raw) {
   std::string serialized;
   if (!reader_->Read(&serialized)) return false;
   ParseSerializedData(serialized, conversion_tables_, data);
+  if (raw != nullptr) raw->swap(serialized);
   return true;
 }
 
@@ -343,6 +344,8 @@ MappingState LoadState(ProtoStreamReader* const reader, const bool expect_3d) {
   state.format_version = deserializer.format_version();
   const PoseGraphProto& pose_graph = deserializer.pose_graph();
   state.constraints = pose_graph.constraint;
+  state.raw_pose_graph_record = deserializer.raw_pose_graph_record();
+  state.raw_options_record = deserializer.raw_options_record();
   // map_builder.cc:262-281 (trajectory ids are kept: there is one map builder state here, no remapping)
   std::map<mapping::SubmapId, transform::Rigid3d> submap_poses;
   std::map<mapping::NodeId, transform::Rigid3d> node_poses;
@@ -355,7 +358,10 @@ MappingState LoadState(ProtoStreamReader* const reader, const bool expect_3d) {
   // :290-296
   if (expect_3d) CSM_CHECK(state.format_version != static_cast<uint32_t>(kFormatVersionWithoutSubmapHistograms));
   SerializedData proto;
-  while (deserializer.ReadNextSerializedData(&proto)) {
+  std::string raw;
+  while (deserializer.ReadNextSerializedData(&proto, &raw)) {
+    MappingState::Record record;
+    record.data_case = proto.data_case();
     switch (proto.data_case()) {
       case SerializedData::kPoseGraph:
         std::fprintf(stderr, "Found multiple serialized `PoseGraph`. Serialized stream likely corrupt!.\n");
@@ -367,18 +373,22 @@ MappingState LoadState(ProtoStreamReader* const reader, const bool expect_3d) {
       case SerializedData::kSubmap: {
         const auto pose = submap_poses.find(proto.submap().submap_id);
         CSM_CHECK(pose != submap_poses.end());
+        record.index = static_cast<int>(state.submaps.size());
         state.submaps.push_back(MappingState::Submap{pose->second, std::move(*proto.mutable_submap())});
         break;
       }
       case SerializedData::kNode: {
         const auto pose = node_poses.find(proto.node().node_id);
         CSM_CHECK(pose != node_poses.end());
+        record.index = static_cast<int>(state.nodes.size());
         state.nodes.push_back(MappingState::Node{pose->second, std::move(*proto.mutable_node())});
         break;
       }
       default:
         break;
     }
+    if (record.index < 0) record.raw.swap(raw);  // everything but submaps and nodes is kept as read
+    state.records.push_back(std::move(record));
   }
   // map_builder.cc:393: CHECK(reader->eof())
   CSM_CHECK(reader->eof());

@@ -120,8 +120,11 @@ class ProtoStreamDeserializer {
   int options_with_sensor_ids_size() const {
     return all_trajectory_builder_options_.options_with_sensor_ids_size();
   }
-  // The next record; false at the end of the stream.
-  bool ReadNextSerializedData(SerializedData* data);
+  // The next record; false at the end of the stream.  `raw`, if given, receives its serialized bytes.
+  bool ReadNextSerializedData(SerializedData* data, std::string* raw = nullptr);
+  // The serialized PoseGraph and AllTrajectoryBuilderOptions records as read.
+  const std::string& raw_pose_graph_record() const { return raw_pose_graph_; }
+  const std::string& raw_options_record() const { return raw_options_; }
 
  private:
   ProtoStreamReader* reader_;
@@ -129,6 +132,7 @@ class ProtoStreamDeserializer {
   uint32_t format_version_ = 0;
   SerializedData pose_graph_;
   SerializedData all_trajectory_builder_options_;
+  std::string raw_pose_graph_, raw_options_;
 };
 
 // What the kSubmap / kNode cases of MapBuilder::LoadState hand to the pose graph
@@ -144,11 +148,21 @@ struct MappingState {
     transform::Rigid3d global_pose;
     NodeProto proto;
   };
+  // Every record after the builder options, in stream order: `index` points into submaps / nodes
+  // for those two kinds; `raw` holds the serialized record of every other kind (and of the first
+  // two records of the stream below), so that the state can be written back (grid_proto_writer.h).
+  struct Record {
+    SerializedData::DataCase data_case = SerializedData::DATA_NOT_SET;
+    int index = -1;
+    std::string raw;
+  };
   uint32_t format_version = 0;
   std::unique_ptr<mapping::ValueConversionTables> conversion_tables;  // the 2D grids borrow it
   std::vector<Submap> submaps;
   std::vector<Node> nodes;
   std::vector<mapping::PoseGraphInterface::Constraint> constraints;
+  std::vector<Record> records;
+  std::string raw_pose_graph_record, raw_options_record;
 };
 
 // `expect_3d` applies LoadState's refusal of format version 1 (submaps without rotational

@@ -1,4 +1,4 @@
-// A reader for the protocol-buffers wire format, enough to take serialized proto::Grid2D and
+// A reader (and, further down, a writer) for the protocol-buffers wire format, enough to take serialized proto::Grid2D and
 // proto::HybridGrid messages apart (libprotobuf and protoc are not in this image; inside a
 // Cartographer tree the generated classes do this).  Wire format (public specification,
 // protobuf.dev/programming-guides/encoding): a message is a sequence of (tag, value) records,
@@ -119,6 +119,81 @@ void RepeatedVarint(Reader* r, int wire_type, const F& fn) {
     r->Skip(-1);
   }
 }
+
+// The writing side, canonical as libprotobuf and upb emit it: the caller adds fields in field-number
+// order; a proto3 scalar that is zero is left out (floating point: all bits zero), a repeated scalar
+// travels packed and is left out when empty, a sub-message that is present is always written, even
+// when empty.  int32 / int64 / enum values are sign-extended to 64 bits before the varint.
+class Writer {
+ public:
+  const std::string& str() const { return out_; }
+  void Varint(uint64_t v) {
+    while (v >= 0x80) {
+      out_.push_back(static_cast<char>((v & 0x7F) | 0x80));
+      v >>= 7;
+    }
+    out_.push_back(static_cast<char>(v));
+  }
+  void Tag(const int field, const int wire_type) { Varint((static_cast<uint64_t>(field) << 3) | wire_type); }
+  void Int64(const int field, const int64_t v) {
+    if (v == 0) return;
+    Tag(field, 0);
+    Varint(static_cast<uint64_t>(v));
+  }
+  void Int32(const int field, const int32_t v) { Int64(field, static_cast<int64_t>(v)); }
+  void UInt32(const int field, const uint32_t v) { Int64(field, static_cast<int64_t>(v)); }
+  void Bool(const int field, const bool v) { Int64(field, v ? 1 : 0); }
+  void Float(const int field, const float v) {
+    uint32_t bits;
+    std::memcpy(&bits, &v, 4);
+    if (bits == 0) return;
+    Tag(field, 5);
+    out_.append(reinterpret_cast<const char*>(&bits), 4);  // little endian on the wire and on this machine
+  }
+  void Double(const int field, const double v) {
+    uint64_t bits;
+    std::memcpy(&bits, &v, 8);
+    if (bits == 0) return;
+    Tag(field, 1);
+    out_.append(reinterpret_cast<const char*>(&bits), 8);
+  }
+  void Message(const int field, const std::string& body) {
+    Tag(field, 2);
+    Varint(body.size());
+    out_.append(body);
+  }
+  // repeated int32 / sint32 / float, packed; `get(i)` returns element i
+  template <typename F>
+  void PackedInt32(const int field, const size_t n, const F& get) {
+    if (n == 0) return;
+    Writer payload;
+    for (size_t i = 0; i != n; ++i) payload.Varint(static_cast<uint64_t>(static_cast<int64_t>(static_cast<int32_t>(get(i)))));
+    Message(field, payload.str());
+  }
+  template <typename F>
+  void PackedSInt32(const int field, const size_t n, const F& get) {
+    if (n == 0) return;
+    Writer payload;
+    for (size_t i = 0; i != n; ++i) {
+      const int32_t v = static_cast<int32_t>(get(i));
+      payload.Varint(static_cast<uint32_t>((static_cast<uint32_t>(v) << 1) ^ static_cast<uint32_t>(v >> 31)));
+    }
+    Message(field, payload.str());
+  }
+  template <typename F>
+  void PackedFloat(const int field, const size_t n, const F& get) {
+    if (n == 0) return;
+    std::string payload(4 * n, '\0');
+    for (size_t i = 0; i != n; ++i) {
+      const float v = get(i);
+      std::memcpy(&payload[4 * i], &v, 4);
+    }
+    Message(field, payload);
+  }
+
+ private:
+  std::string out_;
+};
 
 }  // namespace wire
 }  // namespace io

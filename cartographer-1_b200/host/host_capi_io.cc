@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 
+#include "cartographer/io/grid_proto_writer.h"
 #include "cartographer/io/proto_stream.h"
 #include "cartographer/io/proto_stream_deserializer.h"
 #include "host_capi_holders.h"
@@ -191,6 +192,43 @@ void csmh_state_constraints(void* st, int32_t* ints5, double* doubles9) {
     doubles9[9 * c + 7] = cs[c].pose.translation_weight;
     doubles9[9 * c + 8] = cs[c].pose.rotation_weight;
   }
+}
+
+// ---- writing (cartographer/io/grid_proto_writer.h) ----
+static int64_t CopyOut(const std::string& bytes, uint8_t* out, int64_t cap) {
+  if (out != nullptr) {
+    if (static_cast<int64_t>(bytes.size()) > cap) return -1;
+    std::memcpy(out, bytes.data(), bytes.size());
+  }
+  return static_cast<int64_t>(bytes.size());
+}
+// A grid handle -> its serialized proto::Grid2D (out may be NULL to size).
+int64_t csmh_grid_to_proto(void* grid, uint8_t* out, int64_t cap) {
+  return CopyOut(io::WriteGrid2DProto(*static_cast<GridHolder*>(grid)->grid), out, cap);
+}
+// A voxel list -> the serialized proto::HybridGrid of the HybridGrid holding it.
+int64_t csmh_hybrid_grid_to_proto(float resolution, const int32_t* xyz, const uint16_t* values, int n, uint8_t* out,
+                                  int64_t cap) {
+  mapping::HybridGrid grid(resolution);
+  for (int i = 0; i < n; ++i) *grid.mutable_value(Eigen::Array3i(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])) = values[i];
+  return CopyOut(io::WriteHybridGridProto(grid), out, cap);
+}
+// A serialized SerializedData{pose_graph} -> parsed and written again (WritePoseGraphRecord).
+int64_t csmh_reencode_pose_graph(const uint8_t* bytes, int64_t size, uint8_t* out, int64_t cap) {
+  mapping::ValueConversionTables tables;
+  io::SerializedData data;
+  io::ParseSerializedData(std::string(reinterpret_cast<const char*>(bytes), static_cast<size_t>(size)), &tables, &data);
+  if (!data.has_pose_graph()) return -2;
+  return CopyOut(io::WritePoseGraphRecord(data.pose_graph()), out, cap);
+}
+// The loaded state back into a .pbstream (WriteStateToFile).
+void csmh_state_write(void* st, const char* filename) { io::WriteStateToFile(**static_cast<StateHandle*>(st), filename); }
+// Replaces the cells of 2D submap i's grid (same limits), e.g. with cells that were updated on the device.
+int csmh_state_set_submap_cells(void* st, int i, const uint16_t* cells, int64_t count) {
+  mapping::Grid2D* grid = (**static_cast<StateHandle*>(st)).submaps[i].proto.grid.get();
+  if (grid == nullptr || static_cast<int64_t>(grid->correspondence_cost_cells().size()) != count) return -1;
+  std::memcpy(grid->mutable_correspondence_cost_cells()->data(), cells, sizeof(uint16_t) * static_cast<size_t>(count));
+  return 0;
 }
 
 }  // extern "C"

@@ -269,12 +269,15 @@ class RefGrid3D:
         self.resolution = float(np.float32(resolution))
         self.h = lib().oracle_grid3d_create(resolution, xyz.reshape(-1), values, len(values))
 
-    def cells(self):
+    def cells(self, iteration_order=False):
+        """Non-default voxels, sorted by (z, y, x) or in the order the reference's own iterator visits them."""
         n = lib().oracle_grid3d_cells(self.h, None, None)
         xyz = np.zeros((n, 3), np.int32)
         values = np.zeros(n, np.uint16)
         if n:
             lib().oracle_grid3d_cells(self.h, xyz.ctypes.data_as(C.c_void_p), values.ctypes.data_as(C.c_void_p))
+        if iteration_order:
+            return xyz, values
         order = np.lexsort((xyz[:, 0], xyz[:, 1], xyz[:, 2]))
         return xyz[order], values[order]
 
