@@ -57,39 +57,38 @@ void FastGunzipString(const std::string& compressed, std::string* decompressed) 
 namespace io {
 namespace {
 
-// proto_stream.cc:27
-const uint64_t kMagic = 0x7b1d1f7b5bf501dbull;
+// proto_stream.cc:27: the eight bytes every stream starts with, and the unit of its framing: an
+// unsigned 64-bit integer, least significant byte first (proto_stream.cc:29-43).
+constexpr uint64_t kMagic = 0x7b1d1f7b5bf501dbull;
 
-// proto_stream.cc:29-34
-void WriteSizeAsLittleEndian(uint64_t size, std::ostream* out) {
-  for (int i = 0; i != 8; ++i) {
-    out->put(static_cast<char>(size & 0xff));
-    size >>= 8;
-  }
+void PutFrameWord(std::ofstream* file, const uint64_t value) {
+  char bytes[8];
+  for (int k = 0; k < 8; ++k) bytes[k] = static_cast<char>((value >> (8 * k)) & 0xffu);
+  file->write(bytes, sizeof(bytes));
 }
 
-// proto_stream.cc:36-43
-bool ReadSizeAsLittleEndian(std::istream* in, uint64_t* size) {
-  *size = 0;
-  for (int i = 0; i != 8; ++i) {
-    *size >>= 8;
-    *size += static_cast<uint64_t>(in->get()) << 56;
-  }
-  return !in->fail();
+bool GetFrameWord(std::ifstream* file, uint64_t* value) {
+  unsigned char bytes[8];
+  file->read(reinterpret_cast<char*>(bytes), sizeof(bytes));  // a short read sets failbit (and eofbit)
+  if (file->gcount() != static_cast<std::streamsize>(sizeof(bytes))) return false;
+  uint64_t v = 0;
+  for (int k = 7; k >= 0; --k) v = (v << 8) | bytes[k];
+  *value = v;
+  return true;
 }
 
 }  // namespace
 
-ProtoStreamWriter::ProtoStreamWriter(const std::string& filename)
-    : out_(filename, std::ios::out | std::ios::binary) {
-  WriteSizeAsLittleEndian(kMagic, &out_);
+ProtoStreamWriter::ProtoStreamWriter(const std::string& filename) : out_(filename, std::ios::binary | std::ios::out) {
+  PutFrameWord(&out_, kMagic);
 }
 
+// proto_stream.cc:52-57: one gzip member per message behind its compressed size.
 void ProtoStreamWriter::Write(const std::string& uncompressed_data) {
-  std::string compressed_data;
-  common::FastGzipString(uncompressed_data, &compressed_data);
-  WriteSizeAsLittleEndian(compressed_data.size(), &out_);
-  out_.write(compressed_data.data(), static_cast<std::streamsize>(compressed_data.size()));
+  std::string member;
+  common::FastGzipString(uncompressed_data, &member);
+  PutFrameWord(&out_, member.size());
+  out_.write(member.data(), static_cast<std::streamsize>(member.size()));
 }
 
 bool ProtoStreamWriter::Close() {
@@ -97,34 +96,32 @@ bool ProtoStreamWriter::Close() {
   return !out_.fail();
 }
 
-ProtoStreamReader::ProtoStreamReader(const std::string& filename)
-    : in_(filename, std::ios::in | std::ios::binary) {
-  uint64_t magic;
-  if (!ReadSizeAsLittleEndian(&in_, &magic) || magic != kMagic) in_.setstate(std::ios::failbit);
-  if (!in_.good()) {
+// proto_stream.cc:68-76: a file that cannot be opened or starts with anything but the magic is fatal.
+ProtoStreamReader::ProtoStreamReader(const std::string& filename) : in_(filename, std::ios::binary | std::ios::in) {
+  uint64_t first = 0;
+  if (!in_.is_open() || !GetFrameWord(&in_, &first) || first != kMagic) {
     std::fprintf(stderr, "Failed to open proto stream '%s'.\n", filename.c_str());
     std::abort();
   }
 }
 
+// proto_stream.cc:78-90
 bool ProtoStreamReader::Read(std::string* decompressed_data) {
-  uint64_t compressed_size;
-  if (!ReadSizeAsLittleEndian(&in_, &compressed_size)) return false;
-  // a size beyond the file is a truncated stream: fail the read instead of allocating it
-  const std::streampos here = in_.tellg();
+  uint64_t member_size = 0;
+  if (!GetFrameWord(&in_, &member_size)) return false;  // the regular end: eofbit is set now
+  // a size that points beyond the file is a truncated stream: fail the read instead of allocating it
+  const std::streampos at = in_.tellg();
   in_.seekg(0, std::ios::end);
-  const std::streampos end = in_.tellg();
-  in_.seekg(here);
-  if (here < 0 || compressed_size > static_cast<uint64_t>(end - here)) {
+  const std::streampos file_end = in_.tellg();
+  in_.seekg(at);
+  if (at < 0 || member_size > static_cast<uint64_t>(file_end - at)) {
     in_.setstate(std::ios::failbit);
     return false;
   }
-  std::string compressed_data(compressed_size, '\0');
-  if (compressed_size != 0 &&
-      !in_.read(&compressed_data.front(), static_cast<std::streamsize>(compressed_size)))
-    return false;
+  std::string member(static_cast<size_t>(member_size), '\0');
+  if (member_size != 0 && !in_.read(&member[0], static_cast<std::streamsize>(member_size))) return false;
   decompressed_data->clear();
-  common::FastGunzipString(compressed_data, decompressed_data);
+  common::FastGunzipString(member, decompressed_data);
   return true;
 }
 
