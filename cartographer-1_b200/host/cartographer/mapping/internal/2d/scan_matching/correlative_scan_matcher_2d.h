@@ -17,70 +17,65 @@ namespace cartographer {
 namespace mapping {
 namespace scan_matching {
 
-// Describes the search space (reference: correlative_scan_matcher_2d.h:35-60).
+// The search space of one matcher call (the reference's struct of the same name, :35-60): how many
+// rotated copies of the scan there are, how far apart in angle, and per copy the window of cell
+// offsets that is searched.
 struct SearchParameters {
   struct LinearBounds {
-    int min_x;
-    int max_x;
-    int min_y;
-    int max_y;
+    int min_x, max_x, min_y, max_y;  // inclusive cell offsets
   };
 
-  SearchParameters(double linear_search_window, double angular_search_window,
-                   const sensor::PointCloud& point_cloud, double resolution);
-  // For testing.
-  SearchParameters(int num_linear_perturbations, int num_angular_perturbations,
-                   double angular_perturbation_step_size, double resolution);
-
-  // (cosf(a/2), sinf(a/2)) of the fp32-narrowed rotation of every scan, with the
-  // double accumulation of delta_theta of GenerateRotatedScans
-  // (reference: correlative_scan_matcher_2d.cc:99-106).  2 * num_scans floats.
-  std::vector<float> ScanQuaternionTable() const;
-
+  // public data, as in the reference
   int num_angular_perturbations;
   double angular_perturbation_step_size;
   double resolution;
   int num_scans;
-  std::vector<LinearBounds> linear_bounds;  // per rotated scan, before ShrinkToFit
+  std::vector<LinearBounds> linear_bounds;  // one entry per rotated scan; ShrinkToFit runs on the device
+
+  // From the matcher options and the cloud (its farthest point sets the angular step, .cc:27-53).
+  SearchParameters(double linear_search_window, double angular_search_window,
+                   const sensor::PointCloud& point_cloud, double resolution);
+  // From explicit counts (the reference's test-only constructor, .cc:55-69).
+  SearchParameters(int num_linear_perturbations, int num_angular_perturbations,
+                   double angular_perturbation_step_size, double resolution);
+
+  // What the device needs of the rotations: (cosf(a / 2), sinf(a / 2)) of every scan's angle a,
+  // with a accumulated in double and narrowed to float exactly as GenerateRotatedScans does
+  // (.cc:99-106).  2 * num_scans floats.
+  std::vector<float> ScanQuaternionTable() const;
 };
 
-typedef std::vector<Eigen::Array2i> DiscreteScan2D;  // reference :33
+using DiscreteScan2D = std::vector<Eigen::Array2i>;  // :33
 
-// Generates a collection of rotated scans (reference :62-65, .cc:93-109).  Runs on the calling
-// thread's default device context (csm_rotate_scans2d); the matchers do not call it -- their
-// kernels rotate, discretise and score in one pass -- it exists for callers and tests that use
-// the reference's public helper.
+// The two public helpers of the reference header (:62-72, .cc:93-127), for callers and tests that
+// use them: the matchers themselves rotate, discretise and score inside one kernel pass.  Both run
+// on the calling thread's default device context (csm_rotate_scans2d, csm_discretize_points2d).
 std::vector<sensor::PointCloud> GenerateRotatedScans(const sensor::PointCloud& point_cloud,
                                                      const SearchParameters& search_parameters);
-
-// Translates and discretizes the rotated scans into a vector of integer indices (reference
-// :67-72, .cc:111-127; csm_discretize_points2d).
 std::vector<DiscreteScan2D> DiscretizeScans(const MapLimits& map_limits,
                                             const std::vector<sensor::PointCloud>& scans,
                                             const Eigen::Translation2f& initial_translation);
 
-// A possible solution (reference: correlative_scan_matcher_2d.h:74-103).
+// One pose hypothesis (:74-103): which rotated scan, which cell offset, and the same as metres /
+// radians relative to the initial pose estimate; ordered by score.
 struct Candidate2D {
-  Candidate2D(const int init_scan_index, const int init_x_index_offset,
-              const int init_y_index_offset, const SearchParameters& search_parameters)
-      : scan_index(init_scan_index),
-        x_index_offset(init_x_index_offset),
-        y_index_offset(init_y_index_offset),
-        x(-y_index_offset * search_parameters.resolution),
-        y(-x_index_offset * search_parameters.resolution),
-        orientation((scan_index - search_parameters.num_angular_perturbations) *
-                    search_parameters.angular_perturbation_step_size) {}
-
   int scan_index = 0;
   int x_index_offset = 0;
   int y_index_offset = 0;
-  double x = 0.;
+  double x = 0.;  // metres; the grid's x axis runs along -y of the cell index
   double y = 0.;
   double orientation = 0.;
   float score = 0.f;
 
-  bool operator<(const Candidate2D& other) const { return score < other.score; }
-  bool operator>(const Candidate2D& other) const { return score > other.score; }
+  Candidate2D(const int scan, const int x_offset, const int y_offset, const SearchParameters& sp)
+      : scan_index(scan), x_index_offset(x_offset), y_index_offset(y_offset) {
+    x = -y_index_offset * sp.resolution;
+    y = -x_index_offset * sp.resolution;
+    orientation = (scan_index - sp.num_angular_perturbations) * sp.angular_perturbation_step_size;
+  }
+
+  bool operator<(const Candidate2D& rhs) const { return score < rhs.score; }
+  bool operator>(const Candidate2D& rhs) const { return score > rhs.score; }
 };
 
 }  // namespace scan_matching

@@ -13,17 +13,26 @@ namespace cartographer {
 namespace mapping {
 namespace scan_matching {
 
+// The yaw prefilter of the 3D matcher: a node's histogram of surface directions (angles folded into
+// [0, pi), one weight per bucket; made by the sensor pipeline, rotational_scan_matcher.cc:164-176) is
+// turned by every candidate yaw and compared with the submap's.  A candidate whose score stays
+// under min_rotational_score never reaches the device.
 class RotationalScanMatcher {
  public:
-  // Rotates 'histogram' by 'angle'; a fractional bucket is interpolated linearly.
-  static Eigen::VectorXf RotateHistogram(const Eigen::VectorXf& histogram, float angle);
-
+  // The submap's histogram; borrowed, must outlive the matcher.
   explicit RotationalScanMatcher(const Eigen::VectorXf* histogram);
 
-  // Scores in [0, 1] of 'histogram' rotated by 'initial_angle' + each of 'angles'
-  // against the submap histogram given at construction.
+  // One score in [0, 1] per entry of `angles`: the histogram turned by initial_angle + angles[i]
+  // against the submap's, as the dot product of the two normalised vectors -- 1.f outright when the
+  // product of the norms is under 1e-3 (rotational_scan_matcher.cc:121-133,178-189).  fp32 in the
+  // reference's operation order.
   std::vector<float> Match(const Eigen::VectorXf& histogram, float initial_angle,
                            const std::vector<float>& angles) const;
+
+  // `histogram` turned by `angle`: the turn is a (generally fractional) number of buckets, and each
+  // output bucket is the linear blend of the two input buckets it falls between, the sequence
+  // wrapping around at pi (rotational_scan_matcher.cc:135-162).
+  static Eigen::VectorXf RotateHistogram(const Eigen::VectorXf& histogram, float angle);
 
  private:
   const Eigen::VectorXf* histogram_;
